@@ -1,0 +1,21 @@
+"""CPU oracle for the Point-NeRF per-ray hot path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing in ``pointnerf_b200/`` may import this
+package; only ``tests/``, ``__graft_entry__.smoke()`` and the ``cpu_baseline`` /
+``--impl reference`` legs of ``bench.py`` do, and there only as the checker.
+
+Parity status: the reference (yjcaimeow/pointnerf) ships no tests, golden
+vectors or fixtures for this path, so parity is pinned
+against OUTPUTS OF THE REFERENCE ITSELF produced in the build container:
+
+* ``PointAggregator`` / ``ray_march`` / ``near_far_linear_ray_generation`` /
+  ``positional_encoding`` are imported unmodified from ``/root/reference``
+  (``oracle/ref_import.py``) and their outputs + autograd gradients on seeded
+  inputs are committed under ``tests/golden/`` by ``oracle/make_golden.py``.
+* the six pycuda kernels of ``lighting_fast_querier`` are compiled, from the
+  source string where it lies in the reference tree, as serial host C++
+  (``oracle/build_ref.py`` -> ``oracle/_ref/libpn_ref_querier.so``) and run in
+  ascending-thread order (the canonical schedule).
+* ``oracle/querier_port.c`` and ``oracle/torch_port.py`` are the restatements
+  that travel to the GPU box; they are checked against the two items above.
+"""
