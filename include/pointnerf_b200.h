@@ -1,0 +1,255 @@
+/* pointnerf_b200 - C ABI of the B200-native Point-NeRF per-ray hot path.
+ *
+ * One shared library (pointnerf_b200/lib/libpointnerf_b200.so, nvcc -arch=sm_100a) replaces the
+ * pycuda-JIT kernels and the torch op chains of the reference (yjcaimeow/pointnerf) on the path
+ *   lighting_fast_querier.query_points -> NeuralPoints.forward -> PointAggregator.forward -> ray_march.
+ * The reference has no FFI: pycuda launches are inline Python
+ * (models/neural_points/query_point_indices_worldcoords.py:558-708).  Each entry point below names the
+ * reference function(s) whose work it does; INTEGRATION.md shows the ctypes binding a maintainer adds.
+ *
+ * Conventions
+ *   - plain C: raw DEVICE pointers, extents, POD structs; no torch / C++ types cross the boundary;
+ *   - the CALLER owns every buffer, including workspaces (sized by the *_workspace_bytes queries);
+ *     the library keeps no state besides a thread-local error string;
+ *   - all work is enqueued asynchronously on `stream` (a cudaStream_t passed as void*; torch's
+ *     current stream in the Python host); no call synchronises or allocates;
+ *   - return value: 0 = ok, negative = error (pn_last_error() has the message);
+ *   - B = 1 everywhere (the reference's only batch size, neural_points.py:648);
+ *   - float = IEEE binary32, int = int32; layouts are C-contiguous, innermost dimension last.
+ */
+#ifndef POINTNERF_B200_H
+#define POINTNERF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PN_OK 0
+#define PN_ERR_ARG (-1)
+#define PN_ERR_CUDA (-2)
+#define PN_ERR_UNSUPPORTED (-3)
+
+const char* pn_last_error(void);
+/* ABI version; bumped on any signature change. */
+int pn_abi_version(void);
+/* Number of kernel launches this library has enqueued since load / since the last reset
+ * (process-wide counter; bench.py reports it as `gpu_launches`). */
+int64_t pn_launch_count(void);
+void pn_launch_count_reset(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * 1. Voxel grid  (replaces claim_occ :243-303, map_coor2occ :305-340, fill_occ2pnts :342-387 and the
+ *    fills/launches of build_occ_vox :546-611 of query_point_indices_worldcoords.py)
+ *
+ * Representation in HBM (V = dims[0]*dims[1]*dims[2] cells, linear index (x*dims[1]+y)*dims[2]+z):
+ *   cell_start int32[V+1]  exclusive prefix of points per cell: cell c owns
+ *                          bucket_pidx[cell_start[c] .. cell_start[c+1])  (three z-neighbour cells = 4
+ *                          consecutive ints);
+ *   bucket_pidx int32[N]   point indices grouped by cell, ASCENDING point index inside a cell
+ *                          (= bucket order of the reference under the canonical schedule);
+ *   occ_bits uint32[(V+31)/32]  occupancy dilated by `dilate` (the reference's coor_occ);
+ *   info int32[PN_GRID_INFO_LEN]  see enum below.
+ * The reference's quirk `if (voxel_idx > 0)` (:372) - the voxel that owns slot 0 (canonically the voxel
+ * of the lowest-index in-grid point) never receives points - is kept through info[PN_GI_SLOT0_CELL].
+ * Buckets are exposed to queries truncated to the first P points by index; occupied voxels beyond
+ * max_o are kept (the reference drops/replaces them at random; documented divergence) and flagged.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pn_grid_params {
+    float shift[3];  /* ranges[:3] of get_hyperparameters (:71)                     */
+    float vsize[3];  /* scaled voxel size  vsize*vscale (:60)                       */
+    int32_t dims[3]; /* scaled_vdim (:75)                                           */
+    int32_t dilate[3]; /* query_size: dilation box of map_coor2occ (:330-332, :626) */
+    int32_t P;       /* bucket capacity                                             */
+    int32_t max_o;   /* occupied-voxel budget of the reference (only reported)      */
+} pn_grid_params;
+
+enum {
+    PN_GI_N_OCC = 0,      /* occupied cells                                              */
+    PN_GI_FIRST_POINT,    /* lowest point index that falls inside the grid (INT_MAX: none) */
+    PN_GI_SLOT0_CELL,     /* linear cell index that owns the reference's slot 0 (-1: none) */
+    PN_GI_N_INSIDE,       /* points inside the grid                                      */
+    PN_GI_MAX_COUNT,      /* largest per-cell point count                                */
+    PN_GI_OVER_P,         /* cells holding more than P points                            */
+    PN_GI_OVER_MAX_O,     /* 1 if n_occ > max_o                                          */
+    PN_GI_RESERVED,
+    PN_GRID_INFO_LEN
+};
+
+/* bytes of scratch pn_grid_build needs for N points in a grid of V cells */
+int64_t pn_grid_workspace_bytes(int64_t n_points, int64_t n_cells);
+
+int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_params* params,
+                  int32_t* cell_start, int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info,
+                  void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 2. Ray sampling  (replaces the raypos materialisation of near_far_linear_ray_generation
+ *    diff_ray_marching.py:387, mask_raypos :390-414, the host max/cumsum/select :655-666 and
+ *    get_shadingloc :417-439)
+ *
+ * One warp per ray walks the D candidate depths `ts` (middle_point_ts, computed by the caller with
+ * the reference's own linspace/cumsum chain so that sample positions are bit-identical), forms
+ * pos = campos + raydir * t with separately rounded mul and add, tests the dilated occupancy bit and
+ * keeps the first SR hits.
+ *   ts            float[ts_rows, D], ts_rows = 1 (no jitter: same depths for every ray) or R
+ *   sample_loc_w  float[R, SR, 3]  world positions of kept samples, 0 for unused slots (as :657)
+ *   sample_t      float[R, SR] or NULL  depth t of kept samples (0 unused)
+ *   hit_count     int32[R]  number of kept samples (<= SR); ray_mask of :655 is hit_count > 0
+ * ---------------------------------------------------------------------------------------------- */
+int pn_ray_sample(const float* campos, const float* raydir, const float* ts, int64_t ts_rows,
+                  int64_t n_rays, int32_t D, int32_t SR, const pn_grid_params* params,
+                  const uint32_t* occ_bits, float* sample_loc_w, float* sample_t, int32_t* hit_count,
+                  void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 3. Neighbour query  (replaces query_neigh_along_ray_layered :442-528)
+ *
+ * One warp per kept sample.  Candidates are visited in the reference's order - Chebyshev layer, then
+ * x, y, z ascending, then bucket position - with d^2 = fma(z,z,fma(x,x,y*y)) (what nvcc emits for :498);
+ * the K slots are filled and replaced exactly as :499-519 (so slot ARRANGEMENT matches, not only
+ * the set), and the search stops after the first layer that has seen >= K in-radius candidates (:526).
+ *   n_layers     (kernel_size[0]+1)/2   (:482 - only the x kernel size is used by the reference)
+ *   sample_pidx  int32[R, SR, K], -1 = empty (also written for unused slots)
+ *   ray_any      int32[R]  1 if the ray has at least one neighbour (masked_valid_ray of :715)
+ *   n_candidates uint64[1] or NULL: += bucket entries visited (roofline byte count)
+ * ---------------------------------------------------------------------------------------------- */
+int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
+                 const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
+                 const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
+                 float radius_limit2, int32_t* sample_pidx, int32_t* ray_any,
+                 unsigned long long* n_candidates, void* stream);
+
+/* Camera-frame "perspective" coordinates (x/z, y/z, z) of world positions
+ * (w2pers: worldcoords.py:102-109 for samples, neural_points.py:687-693 for points).
+ * camrot = camrotc2w row-major 3x3, campos 3 floats, both on the device. */
+int pn_w2pers(const float* xyz_w, int64_t n, const float* camrot, const float* campos, float* xyz_pers,
+              void* stream);
+
+/* Work lists for the aggregator: valid samples (>= 1 neighbour) and valid (sample, neighbour) pairs,
+ * both in ascending (ray, slot, k) order - replaces the boolean-mask compactions (nonzero syncs) of
+ * point_aggregators.py:521-538.
+ *   sample_list int32[n_slots]    indices r*SR+s of valid samples (first S entries used)
+ *   pair_start  int32[n_slots+1]  first compact pair of each valid sample; pair_start[S] = M
+ *   pair_src    int32[n_slots*K]  slot*K+k of each compact pair (first M entries used)
+ *   counts      int32[2]          [0] = S, [1] = M   (the caller reads these back: one host sync)
+ * workspace: pn_compact_workspace_bytes(n_slots). */
+int64_t pn_compact_workspace_bytes(int64_t n_slots);
+int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
+                       int32_t* pair_start, int32_t* pair_src, int32_t* counts, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 4. Point aggregator  (replaces the index_select gather of NeuralPoints.forward neural_points.py:788-799
+ *    and PointAggregator.forward / linear / viewmlp, point_aggregators.py:729-816, 421-429, 488-646,
+ *    for the shipped configuration: viewmlp, agg_intrp_order=2, linear kernel, agg_dist_pers=20,
+ *    apply_pnt_mask=1, LeakyReLU(0.01), act_super=1)
+ *
+ * The kernels read per-point rows THROUGH an index (`sample_pidx`): with the neural point tables and
+ * point indices this is the fused gather path; with the already gathered [R,SR,K,*] tensors of the
+ * reference API and identity indices it is the drop-in PointAggregator.forward.
+ * Work lists come from pn_compact_samples; S, M are read back by the caller (one host sync per call,
+ * where the reference has eight).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pn_agg_params {
+    int32_t F;          /* point_features_dim (32)                    */
+    int32_t feat_freqs; /* num_feat_freqs (3)                         */
+    int32_t dist_freqs; /* dist_xyz_freq (5); distance vector is 6-D  */
+    int32_t view_freqs; /* num_viewdir_freqs (4)                      */
+    int32_t W;          /* shading_feature_num (256)                  */
+    int32_t C;          /* shading_color_channel_num (128 in this fork) */
+    int32_t K;          /* neighbours per sample                      */
+    int32_t dirs_per_ray; /* 1: ray_dirs is [R,3] (row = slot / SR); 0: [n_slots,3] */
+    int32_t SR;
+    float leaky_slope;  /* nn.LeakyReLU default 0.01                  */
+    float dist_scale;   /* 1 if dist_xyz_deno == 0 else 1/(deno*|vsize|) (:524-525) */
+} pn_agg_params;
+
+/* nn.Linear parameters, weight [out,in] row-major fp32 (state_dict names of the reference) */
+typedef struct pn_agg_weights {
+    float *block1_0_w, *block1_0_b; /* [W, F+2*ff*F+12*df]  */
+    float *block1_2_w, *block1_2_b; /* [W, W]               */
+    float *block3_0_w, *block3_0_b; /* [W, W+7]             */
+    float *block3_2_w, *block3_2_b; /* [W, W]               */
+    float *alpha_0_w, *alpha_0_b;   /* [1, W]               */
+    float *color_0_w, *color_0_b;   /* [C, W+6*vf]          */
+    float *color_2_w, *color_2_b;   /* [C, C]               */
+    float *color_4_w, *color_4_b;   /* [C, C]               */
+} pn_agg_weights;
+
+typedef struct pn_agg_inputs {
+    const float* xyz;       /* [T,3] world position of row g                          */
+    const float* xyz_pers;  /* [T,3] (x/z, y/z, z) in the camera frame                */
+    const float* embedding; /* [T,F]                                                  */
+    const float* color;     /* [T,3]                                                  */
+    const float* dir;       /* [T,3]                                                  */
+    const float* conf;      /* [T]                                                    */
+    const float* Rw2c;      /* [9] device, row-major                                  */
+    const int32_t* sample_pidx; /* [n_slots,K] row index g or -1                      */
+    const float* sample_loc_w;  /* [n_slots,3]                                        */
+    const float* sample_loc;    /* [n_slots,3] perspective coords of the samples      */
+    const float* ray_dirs;      /* see dirs_per_ray                                   */
+    const int32_t* sample_list; /* [S] valid slots                                    */
+    const int32_t* pair_start;  /* [S+1] first compact pair of each valid sample      */
+    const int32_t* pair_src;    /* [M] slot*K+k of each compact pair                  */
+    int64_t n_slots, S, M, T;
+} pn_agg_inputs;
+
+int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t M);
+int64_t pn_agg_workspace_bytes(const pn_agg_params* p, int64_t S, int64_t M, int64_t T, int backward);
+
+/* decoded_features [n_slots, C+1]: column 0 density, 1..C colour feature; rows of invalid samples are
+ * zero-filled.  weight_out [n_slots,K] (normalised inverse-distance weights) may be NULL.
+ * saved: activations kept for pn_agg_backward (NULL = inference). */
+int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
+                   float* decoded_features, float* weight_out, void* saved, int64_t saved_bytes,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+
+/* grad_decoded [n_slots, C+1].  grad_w receives d/d(MLP parameters) (overwritten, deterministic
+ * fixed-order reductions).  Per-row gradients of embedding/color/dir/conf:
+ *   scatter_rows == 0: written per PAIR into [n_slots*K, *] arrays (zeros for empty slots) - the
+ *                      gradients of the reference's sampled_* tensors;
+ *   scatter_rows == 1: summed per table row g into [T, *] arrays by a sorted segmented reduction (no
+ *                      atomics; replaces the index_add_ backward of index_select), rows never referenced
+ *                      are zero-filled. */
+int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
+                    const float* grad_decoded, const void* saved, int64_t saved_bytes,
+                    const pn_agg_weights* grad_w, int scatter_rows, float* grad_embedding,
+                    float* grad_color, float* grad_dir, float* grad_conf, void* workspace,
+                    int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 5. Compositing  (replaces ray_march / alpha_ray_march diff_ray_marching.py:509-573 with
+ *    radiance_render and alpha_blend, diff_render_func.py:36-37,48-50, and the ray_dist block of
+ *    neural_points_volumetric_model.py:293-301)
+ *
+ * One warp per ray: opacity = 1-exp(-sigma*dist), transmittance = exclusive prefix product of
+ * (1-opacity+1e-10) by warp shuffles, blend weight = opacity*T, colour = sum_s w_s*feat_s[1:] (+bg*T_bg).
+ * Feature rows whose weight cannot matter (invalid sample, or T below 1e-8: early ray termination) are
+ * not read.  All per-sample outputs are still written in full.
+ *   ray_features [R,SR,C+1]; ray_dist [R,SR]; ray_valid uint8[R,SR]; bg_color [C] or NULL
+ *   ray_color [R,C] (NULL for alpha_ray_march); opacity, acc_T, blend_w [R,SR]; bg_T [R]
+ * ---------------------------------------------------------------------------------------------- */
+int pn_ray_dist(const float* sample_loc, const uint8_t* sample_valid, int64_t n_rays, int32_t SR,
+                float vsize_z, int32_t raydist_mode_unit, float* ray_dist, void* stream);
+
+int pn_composite_forward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
+                         const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
+                         float* opacity, float* acc_T, float* blend_w, float* bg_T, void* stream);
+
+/* Gradients w.r.t. ray_features [R,SR,C+1] and bg_color [C] (deterministic two-stage reduction over
+ * rays).  Upstream gradients g_opacity/g_acc_T/g_blend_w [R,SR], g_bg_T [R], g_ray_color [R,C] may each be
+ * NULL (= zero).  workspace: pn_composite_workspace_bytes(n_rays, C). */
+int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C);
+int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
+                          const float* bg_color, const float* opacity, const float* acc_T,
+                          const float* bg_T, const float* g_ray_color, const float* g_opacity,
+                          const float* g_acc_T, const float* g_blend_w, const float* g_bg_T,
+                          int64_t n_rays, int32_t SR, int32_t C, float* g_features, float* g_bg_color,
+                          void* workspace, int64_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POINTNERF_B200_H */

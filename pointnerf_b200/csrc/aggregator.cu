@@ -1,0 +1,310 @@
+// pn_agg_forward / pn_agg_backward: the fused gather + PointAggregator (viewmlp, order 2) pipeline.
+// Reference: models/aggregators/point_aggregators.py:729-816 (forward), 488-646 (viewmlp),
+// neural_points.py:788-799 (gather); backward replaces autograd through those ops.
+//
+// Layer plan (compact rows; M pairs, S samples; all operand widths padded to multiples of 16):
+//   prep    : X1[M,in1p] = [emb | PE(emb) | PE(dist)], X3[M, W..] = block3 extras, pairv = (w*conf, w)
+//   block1  : H1 = lrelu(X1 W1a^T + b), X3[:, :W] = lrelu(H1 W1b^T + b)
+//   block3  : H3 = lrelu(X3 W3a^T + b), H4 = lrelu(H3 W3b^T + b)
+//   reduce  : alpha_s = sum_k softplus(H4 w_a + b_a - 1) wc,  FS[S, :W] = sum_k H4 wc,  FS[S, W:] = PE(view)
+//   colour  : C1 = lrelu(FS Wc0^T + b), C2 = lrelu(C1 Wc2^T + b), C3 = lrelu(C2 Wc4^T + b)
+//   finish  : decoded[slot] = [alpha_s | C3]
+#include "agg_kernels.cuh"
+#include "gemm.cuh"
+
+namespace pn {
+
+static int make_dims(const pn_agg_params* p, AggDims& d) {
+    PN_CHECK_ARG(p, "aggregator: null params");
+    d.F = p->F; d.ff = p->feat_freqs; d.df = p->dist_freqs; d.vf = p->view_freqs;
+    d.W = p->W; d.C = p->C; d.K = p->K; d.SR = p->SR; d.dirs_per_ray = p->dirs_per_ray;
+    d.slope = p->leaky_slope; d.dist_scale = p->dist_scale;
+    PN_CHECK_ARG(d.F >= 1 && d.F <= 1024 && d.ff >= 0 && d.df >= 1 && d.df <= 16 && d.vf >= 1 && d.vf <= 16,
+                 "aggregator: unsupported feature/frequency counts");
+    PN_CHECK_ARG(d.W == 128 || d.W == 256, "aggregator: shading_feature_num %d unsupported (128 or 256)", d.W);
+    PN_CHECK_ARG(d.C % 16 == 0 && d.C >= 16 && d.C <= 256, "aggregator: shading_color_channel_num %d unsupported", d.C);
+    PN_CHECK_ARG(d.K >= 1 && d.K <= 32, "aggregator: K=%d unsupported (1..32)", d.K);
+    d.in1 = d.F + 2 * d.ff * d.F + 12 * d.df;
+    d.in3 = d.W + 7;
+    d.inc = d.W + 6 * d.vf;
+    d.in1p = (int)align_up(d.in1, 16);
+    d.in3p = (int)align_up(d.in3, 16);
+    d.incp = (int)align_up(d.inc, 16);
+    return PN_OK;
+}
+
+struct Saved {
+    float *X1, *H1, *X3, *H3, *H4, *FS, *C1, *C2, *C3, *alpha;
+    float4* pairv;
+};
+static int64_t carve_saved(const AggDims& d, int64_t S, int64_t M, void* p, int64_t bytes, Saved* sv) {
+    Carver c(p, bytes);
+    int64_t m = M > 0 ? M : 1, s = S > 0 ? S : 1;
+    Saved t;
+    t.X1 = c.take<float>(m * d.in1p);
+    t.H1 = c.take<float>(m * d.W);
+    t.X3 = c.take<float>(m * d.in3p);
+    t.H3 = c.take<float>(m * d.W);
+    t.H4 = c.take<float>(m * d.W);
+    t.pairv = c.take<float4>(m);
+    t.FS = c.take<float>(s * d.incp);
+    t.C1 = c.take<float>(s * d.C);
+    t.C2 = c.take<float>(s * d.C);
+    t.C3 = c.take<float>(s * d.C);
+    t.alpha = c.take<float>(s);
+    if (sv) *sv = t;
+    return c.off;
+}
+
+static int64_t max3(int64_t a, int64_t b, int64_t c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+
+}  // namespace pn
+
+using namespace pn;
+
+extern "C" int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t M) {
+    AggDims d;
+    if (make_dims(p, d)) return -1;
+    return carve_saved(d, S, M, nullptr, 0, nullptr);
+}
+
+namespace pn {
+struct FwdWs { float *W1a, *W3a, *Wc0; };
+struct BwdWs {
+    float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
+    float *GA, *GB, *GSa, *GSb, *galpha, *PG, *tn, *apart;
+    int *cnt, *rank, *tmp, *sorted, *scan;
+    int nblk_reduce;
+    int64_t chunk;
+};
+constexpr int kReduceBlocks = kNumSMs * 4;
+
+static int64_t carve_fwd(const AggDims& d, void* p, int64_t bytes, FwdWs* w) {
+    Carver c(p, bytes);
+    FwdWs t;
+    t.W1a = c.take<float>((int64_t)d.W * d.in1p);
+    t.W3a = c.take<float>((int64_t)d.W * d.in3p);
+    t.Wc0 = c.take<float>((int64_t)d.C * d.incp);
+    if (w) *w = t;
+    return c.off;
+}
+static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void* p, int64_t bytes, BwdWs* w) {
+    Carver c(p, bytes);
+    int64_t m = M > 0 ? M : 1, s = S > 0 ? S : 1;
+    BwdWs t;
+    t.W1aT = c.take<float>((int64_t)d.in1p * d.W);
+    t.W1bT = c.take<float>((int64_t)d.W * d.W);
+    t.W3aT = c.take<float>((int64_t)d.in3p * d.W);
+    t.W3bT = c.take<float>((int64_t)d.W * d.W);
+    t.Wc0T = c.take<float>((int64_t)d.incp * d.C);
+    t.Wc2T = c.take<float>((int64_t)d.C * d.C);
+    t.Wc4T = c.take<float>((int64_t)d.C * d.C);
+    int64_t wide = d.in1p > d.in3p ? d.in1p : d.in3p;
+    t.GA = c.take<float>(m * wide);
+    t.GB = c.take<float>(m * d.W);
+    t.GSa = c.take<float>(s * d.incp);
+    t.GSb = c.take<float>(s * d.incp);
+    t.galpha = c.take<float>(s);
+    t.PG = c.take<float>(m * (d.F + 8));
+    int64_t tn = max3(gemm_tn_scratch_floats(m, d.W, d.in1p), gemm_tn_scratch_floats(m, d.W, d.in3p),
+                      gemm_tn_scratch_floats(s, d.C, d.incp));
+    t.tn = c.take<float>(tn);
+    t.nblk_reduce = (int)(s < kReduceBlocks ? s : kReduceBlocks);
+    t.chunk = cdiv(s, t.nblk_reduce);
+    t.apart = c.take<float>((int64_t)kReduceBlocks * (d.W + 1));
+    int64_t tt = T > 0 ? T : 1;
+    t.cnt = c.take<int>(tt + 1);
+    t.rank = c.take<int>(m);
+    t.tmp = c.take<int>(m);
+    t.sorted = c.take<int>(m);
+    t.scan = c.take<int>(scan_scratch_elems_i32(tt + 1));
+    if (w) *w = t;
+    return c.off;
+}
+}  // namespace pn
+
+extern "C" int64_t pn_agg_workspace_bytes(const pn_agg_params* p, int64_t S, int64_t M, int64_t T, int backward) {
+    AggDims d;
+    if (make_dims(p, d)) return -1;
+    return backward ? carve_bwd(d, S, M, T, nullptr, 0, nullptr) : carve_fwd(d, nullptr, 0, nullptr);
+}
+
+static GemmNT nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int Kd,
+                 const float* bias, int leaky, float slope) {
+    GemmNT g;
+    g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.Kd = Kd;
+    g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr;
+    return g;
+}
+#define PN_TRY(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
+
+extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w, float* decoded,
+                              float* weight_out, void* saved, int64_t saved_bytes, void* workspace, int64_t workspace_bytes,
+                              void* stream) {
+    AggDims d;
+    PN_TRY(make_dims(p, d));
+    PN_CHECK_ARG(in && w && decoded && saved, "pn_agg_forward: null argument");
+    const int64_t S = in->S, M = in->M;
+    PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_forward: saved buffer too small");
+    PN_CHECK_ARG(workspace_bytes >= carve_fwd(d, nullptr, 0, nullptr), "pn_agg_forward: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    PN_CUDA(cudaMemsetAsync(decoded, 0, in->n_slots * (int64_t)(d.C + 1) * sizeof(float), st));
+    if (weight_out) PN_CUDA(cudaMemsetAsync(weight_out, 0, in->n_slots * (int64_t)d.K * sizeof(float), st));
+    if (S <= 0 || M <= 0) return PN_OK;
+    Saved sv;
+    carve_saved(d, S, M, saved, saved_bytes, &sv);
+    FwdWs ws;
+    carve_fwd(d, workspace, workspace_bytes, &ws);
+    // padded copies of the three weights whose input width is not a multiple of 16
+    PN_TRY(copy_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1a, d.in1p, st));
+    PN_TRY(copy_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3a, d.in3p, st));
+    PN_TRY(copy_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0, d.incp, st));
+
+    agg_prep_kernel<<<(unsigned)cdiv(S * 32, 256), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
+    PN_LAUNCH_CHECK("agg_prep");
+    PN_TRY(gemm_nt(nt(sv.X1, d.in1p, ws.W1a, d.in1p, sv.H1, d.W, M, d.W, d.in1p, w->block1_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H1, d.W, w->block1_2_w, d.W, sv.X3, d.in3p, M, d.W, d.W, w->block1_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.X3, d.in3p, ws.W3a, d.in3p, sv.H3, d.W, M, d.W, d.in3p, w->block3_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H3, d.W, w->block3_2_w, d.W, sv.H4, d.W, M, d.W, d.W, w->block3_2_b, 1, d.slope), st));
+    unsigned sblocks = (unsigned)cdiv(S * 32, 256);
+    if (d.W == 256)
+        agg_reduce_kernel<8><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
+    else
+        agg_reduce_kernel<4><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
+    PN_LAUNCH_CHECK("agg_reduce");
+    PN_TRY(gemm_nt(nt(sv.FS, d.incp, ws.Wc0, d.incp, sv.C1, d.C, S, d.C, d.incp, w->color_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C1, d.C, w->color_2_w, d.C, sv.C2, d.C, S, d.C, d.C, w->color_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C2, d.C, w->color_4_w, d.C, sv.C3, d.C, S, d.C, d.C, w->color_4_b, 1, d.slope), st));
+    agg_finish_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
+    PN_LAUNCH_CHECK("agg_finish");
+    return PN_OK;
+}
+
+static int zero_weight_grads(const AggDims& d, const pn_agg_weights* g, cudaStream_t st) {
+    struct { float* p; int64_t n; } items[] = {
+        {g->block1_0_w, (int64_t)d.W * d.in1}, {g->block1_0_b, d.W}, {g->block1_2_w, (int64_t)d.W * d.W}, {g->block1_2_b, d.W},
+        {g->block3_0_w, (int64_t)d.W * d.in3}, {g->block3_0_b, d.W}, {g->block3_2_w, (int64_t)d.W * d.W}, {g->block3_2_b, d.W},
+        {g->alpha_0_w, d.W}, {g->alpha_0_b, 1}, {g->color_0_w, (int64_t)d.C * d.inc}, {g->color_0_b, d.C},
+        {g->color_2_w, (int64_t)d.C * d.C}, {g->color_2_b, d.C}, {g->color_4_w, (int64_t)d.C * d.C}, {g->color_4_b, d.C}};
+    for (auto& it : items)
+        if (it.p) PN_CUDA(cudaMemsetAsync(it.p, 0, it.n * sizeof(float), st));
+    return PN_OK;
+}
+
+extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
+                               const float* grad_decoded, const void* saved, int64_t saved_bytes, const pn_agg_weights* gw,
+                               int scatter_rows, float* g_emb, float* g_color, float* g_dir, float* g_conf, void* workspace,
+                               int64_t workspace_bytes, void* stream) {
+    AggDims d;
+    PN_TRY(make_dims(p, d));
+    PN_CHECK_ARG(in && w && grad_decoded && saved && gw, "pn_agg_backward: null argument");
+    const int64_t S = in->S, M = in->M, T = in->T;
+    PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_backward: saved buffer too small");
+    PN_CHECK_ARG(workspace_bytes >= carve_bwd(d, S, M, T, nullptr, 0, nullptr), "pn_agg_backward: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    // row gradients default to zero (empty slots / unreferenced table rows)
+    int64_t rows = scatter_rows ? T : in->n_slots * (int64_t)d.K;
+    if (g_emb) PN_CUDA(cudaMemsetAsync(g_emb, 0, rows * d.F * sizeof(float), st));
+    if (g_color) PN_CUDA(cudaMemsetAsync(g_color, 0, rows * 3 * sizeof(float), st));
+    if (g_dir) PN_CUDA(cudaMemsetAsync(g_dir, 0, rows * 3 * sizeof(float), st));
+    if (g_conf) PN_CUDA(cudaMemsetAsync(g_conf, 0, rows * sizeof(float), st));
+    if (S <= 0 || M <= 0) return zero_weight_grads(d, gw, st);
+
+    Saved sv;
+    carve_saved(d, S, M, const_cast<void*>(saved), saved_bytes, &sv);
+    BwdWs ws;
+    carve_bwd(d, S, M, T, workspace, workspace_bytes, &ws);
+    const int pgw = d.F + 8;
+    // transposed (K-contiguous over the OUTPUT index) weight copies for the data-gradient GEMMs
+    PN_TRY(transpose_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1aT, d.W, d.in1p, st));
+    PN_TRY(transpose_pad(w->block1_2_w, d.W, d.W, d.W, ws.W1bT, d.W, d.W, st));
+    PN_TRY(transpose_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3aT, d.W, d.in3p, st));
+    PN_TRY(transpose_pad(w->block3_2_w, d.W, d.W, d.W, ws.W3bT, d.W, d.W, st));
+    PN_TRY(transpose_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0T, d.C, d.incp, st));
+    PN_TRY(transpose_pad(w->color_2_w, d.C, d.C, d.C, ws.Wc2T, d.C, d.C, st));
+    PN_TRY(transpose_pad(w->color_4_w, d.C, d.C, d.C, ws.Wc4T, d.C, d.C, st));
+
+    // ---- colour branch (S rows)
+    agg_gout_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
+    PN_LAUNCH_CHECK("agg_gout");
+    {   // color.4
+        GemmTN t{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        GemmNT g = nt(ws.GSa, d.C, ws.Wc4T, d.C, ws.GSb, d.C, S, d.C, d.C, nullptr, 0, d.slope);
+        g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
+        PN_TRY(gemm_nt(g, st));
+    }
+    {   // color.2
+        GemmTN t{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSa, d.C, S, d.C, d.C, nullptr, 0, d.slope);
+        g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
+        PN_TRY(gemm_nt(g, st));
+    }
+    {   // color.0: d/dFS (only the first W columns are consumed)
+        GemmTN t{ws.GSa, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(gemm_nt(nt(ws.GSa, d.C, ws.Wc0T, d.C, ws.GSb, d.incp, S, d.incp, d.C, nullptr, 0, d.slope), st));
+    }
+    // ---- K-reduction and density head
+    if (d.W == 256)
+        agg_reduce_bwd_kernel<8><<<ws.nblk_reduce, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSb, ws.galpha, ws.chunk,
+                                                                 ws.GA, d.W, ws.PG, pgw, ws.apart);
+    else
+        agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSb, ws.galpha, ws.chunk,
+                                                                 ws.GA, d.W, ws.PG, pgw, ws.apart);
+    PN_LAUNCH_CHECK("agg_reduce_bwd");
+    agg_alpha_final_kernel<<<(unsigned)cdiv(d.W + 1, 256), 256, 0, st>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
+    PN_LAUNCH_CHECK("agg_alpha_final");
+    // ---- block3 (M rows).  GA = dPre4 [M,W]
+    {   // block3.2
+        GemmTN t{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        GemmNT g = nt(ws.GA, d.W, ws.W3bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
+        g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
+        PN_TRY(gemm_nt(g, st));  // GB = dPre3
+    }
+    {   // block3.0: GA[M,in3p] = d/dX3, first W columns masked by lrelu'(H2) (H2 = X3[:, :W])
+        GemmTN t{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
+        g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
+        PN_TRY(gemm_nt(g, st));
+    }
+    agg_extras_bwd_kernel<<<(unsigned)cdiv(M, 256), 256, 0, st>>>(*in, d, ws.GA, ws.PG, pgw);
+    PN_LAUNCH_CHECK("agg_extras_bwd");
+    // ---- block1.  GA[:, :W] = dPre2 (row stride in3p)
+    {   // block1.2
+        GemmTN t{ws.GA, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        GemmNT g = nt(ws.GA, d.in3p, ws.W1bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
+        g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
+        PN_TRY(gemm_nt(g, st));  // GB = dPre1
+    }
+    {   // block1.0: GA[M,in1p] = d/dX1
+        GemmTN t{ws.GB, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
+        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(gemm_nt(nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, d.in1p, d.W, nullptr, 0, d.slope), st));
+    }
+    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, sv.X1, ws.GA, ws.PG, pgw);
+    PN_LAUNCH_CHECK("agg_prep_bwd");
+    // ---- per-row gradients out
+    if (!scatter_rows) {
+        agg_scatter_dense_kernel<<<(unsigned)cdiv(M * (d.F + 7), 256), 256, 0, st>>>(*in, d, ws.PG, pgw, g_emb, g_color, g_dir, g_conf);
+        PN_LAUNCH_CHECK("agg_scatter_dense");
+    } else {
+        PN_CUDA(cudaMemsetAsync(ws.cnt, 0, (T + 1) * sizeof(int), st));
+        unsigned mb = (unsigned)cdiv(M, 256);
+        agg_key_count_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.rank);
+        PN_LAUNCH_CHECK("agg_key_count");
+        PN_TRY(scan_exclusive_i32(ws.cnt, ws.cnt, T, true, ws.scan, st));
+        agg_key_place_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.rank, ws.tmp);
+        PN_LAUNCH_CHECK("agg_key_place");
+        agg_key_order_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.tmp, ws.sorted);
+        PN_LAUNCH_CHECK("agg_key_order");
+        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, ws.cnt, ws.sorted, ws.PG, pgw, g_emb, g_color,
+                                                                               g_dir, g_conf);
+        PN_LAUNCH_CHECK("agg_segment_reduce");
+    }
+    return PN_OK;
+}

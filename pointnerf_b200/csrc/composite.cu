@@ -1,0 +1,309 @@
+// Alpha compositing along rays, forward and backward, and the ray_dist block that feeds it.
+//
+// Replaces ray_march / alpha_ray_march (models/rendering/diff_ray_marching.py:509-573, with
+// radiance_render / alpha_blend of diff_render_func.py:36-37,48-50) - about ten torch kernels and the
+// generic cumprod backward - and the cummax/diff/clamp chain of
+// models/neural_points_volumetric_model.py:293-301.
+//
+// One warp per ray.  Per-sample scalars live one per lane (32 samples per step, running product
+// carried between steps); the transmittance is a warp prefix product by __shfl_up.  Feature rows
+// ([C+1] floats, C = 128 in this fork) are streamed with lanes across channels (coalesced 128-byte
+// segments) only for samples that can contribute: invalid samples have weight exactly 0, and once the
+// transmittance falls below kTermT every later weight is below 1e-8 of the accumulated colour (early
+// ray termination).  HBM-bound; algorithmic bytes forward 4*R*SR*(C+3) + 4*R*(C+1) + 12*R*SR.
+#include "common.cuh"
+
+namespace pn {
+
+constexpr float kTermT = 1e-8f;
+
+__device__ __forceinline__ float warp_prod_scan_incl(float v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v *= t;
+    }
+    return v;
+}
+
+template <int NC>  // channel registers per lane: C <= 32*NC
+__global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restrict__ feat, const float* __restrict__ dist,
+                                                            const uint8_t* __restrict__ valid, const float* __restrict__ bg,
+                                                            int64_t n_rays, int SR, int C, float* __restrict__ ray_color,
+                                                            float* __restrict__ opacity, float* __restrict__ acc_T,
+                                                            float* __restrict__ blend_w, float* __restrict__ bg_T) {
+    int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (ray >= n_rays) return;
+    const int C1 = C + 1;
+    const float* frow = feat + ray * SR * C1;
+    float acc[NC];
+#pragma unroll
+    for (int i = 0; i < NC; ++i) acc[i] = 0.f;
+    float carry = 1.f;  // product of (1 - o + 1e-10) over all previous samples
+    bool live = ray_color != nullptr;
+    for (int s0 = 0; s0 < SR; s0 += 32) {
+        int s = s0 + lane;
+        float o = 0.f, a = 1.f;
+        if (s < SR) {
+            float sigma = valid[ray * SR + s] ? frow[(int64_t)s * C1] : 0.f;
+            o = __fsub_rn(1.f, expf(-(sigma * dist[ray * SR + s])));
+            a = __fadd_rn(__fsub_rn(1.f, o), 1e-10f);
+        }
+        float incl = warp_prod_scan_incl(a, lane);
+        float prev = __shfl_up_sync(kFull, incl, 1);
+        float T = carry * (lane == 0 ? 1.f : prev);
+        float w = o * T;
+        if (s < SR) {
+            opacity[ray * SR + s] = o;
+            acc_T[ray * SR + s] = T;
+            blend_w[ray * SR + s] = w;
+        }
+        carry *= __shfl_sync(kFull, incl, 31);
+        if (live) {
+            unsigned m = __ballot_sync(kFull, s < SR && w != 0.f && T >= kTermT);
+            while (m) {
+                int j = __ffs(m) - 1;
+                m &= m - 1;
+                float wj = __shfl_sync(kFull, w, j);
+                const float* f = frow + (int64_t)(s0 + j) * C1 + 1;
+#pragma unroll
+                for (int i = 0; i < NC; ++i) {
+                    int c = lane + 32 * i;
+                    if (c < C) acc[i] = fmaf(wj, f[c], acc[i]);
+                }
+            }
+            if (carry < kTermT) live = false;
+        }
+    }
+    if (lane == 0) bg_T[ray] = carry;
+    if (ray_color) {
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            int c = lane + 32 * i;
+            if (c < C) ray_color[ray * C + c] = bg ? fmaf(bg[c], carry, acc[i]) : acc[i];
+        }
+    }
+}
+
+// Backward.  Pass 1 (forward order): per live sample dot = <g_color, f_s>, and g_f[s,1:] = w_s*g_color.
+// Pass 2 (reverse order): suffix sums give d/d(a_j); density gradient written to g_f[s,0].
+template <int NC>
+__global__ void __launch_bounds__(256) composite_bwd_kernel(
+    const float* __restrict__ feat, const float* __restrict__ dist, const uint8_t* __restrict__ valid,
+    const float* __restrict__ bg, const float* __restrict__ opacity, const float* __restrict__ acc_T,
+    const float* __restrict__ bg_T, const float* __restrict__ g_color, const float* __restrict__ g_opacity,
+    const float* __restrict__ g_acc_T, const float* __restrict__ g_blend_w, const float* __restrict__ g_bg_T, int64_t n_rays,
+    int SR, int C, float* g_feat) {
+    int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (ray >= n_rays) return;
+    const int C1 = C + 1;
+    const float* frow = feat + ray * SR * C1;
+    float* grow = g_feat + ray * SR * C1;
+    float gc[NC];
+    float gbg = 0.f;
+#pragma unroll
+    for (int i = 0; i < NC; ++i) {
+        int c = lane + 32 * i;
+        gc[i] = (g_color && c < C) ? g_color[ray * C + c] : 0.f;
+        if (bg && c < C) gbg = fmaf(gc[i], bg[c], gbg);
+    }
+    gbg = warp_sum(gbg);
+    float P_last = bg_T[ray];
+    float G_P = (g_bg_T ? g_bg_T[ray] : 0.f) + gbg;
+
+    // pass 1
+    for (int s = 0; s < SR; ++s) {
+        float T = acc_T[ray * SR + s], o = opacity[ray * SR + s];
+        float w = o * T;
+        bool live = g_color && valid[ray * SR + s] && T >= kTermT;  // warp-uniform
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+            int c = lane + 32 * i;
+            if (c < C) {
+                if (live) dot = fmaf(gc[i], frow[(int64_t)s * C1 + 1 + c], dot);
+                grow[(int64_t)s * C1 + 1 + c] = w * gc[i];
+            }
+        }
+        // <g_color, f_s> is parked in the density column of this sample's gradient row; pass 2 (same warp)
+        // consumes it and overwrites the column with the density gradient
+        if (live) dot = warp_sum(dot);
+        if (lane == 0) grow[(int64_t)s * C1] = live ? dot : 0.f;
+    }
+    __syncwarp();
+    // pass 2: chunks of 32 samples from the end
+    float carry = G_P * P_last;  // sum_{s > j} G_T[s]*T_s + G_P*P_last, for j = last sample of the chunk
+    int nchunk = (SR + 31) / 32;
+    for (int ch = nchunk - 1; ch >= 0; --ch) {
+        int s = ch * 32 + lane;
+        float term = 0.f, o = 0.f, T = 0.f, G_w = 0.f, d = 0.f, sigma = 0.f;
+        bool ok = s < SR;
+        bool v = false;
+        if (ok) {
+            int64_t i = ray * SR + s;
+            o = opacity[i];
+            T = acc_T[i];
+            d = dist[i];
+            v = valid[i] != 0;
+            sigma = v ? frow[(int64_t)s * C1] : 0.f;
+            G_w = (g_blend_w ? g_blend_w[i] : 0.f) + grow[(int64_t)s * C1];
+            float G_T = (g_acc_T ? g_acc_T[i] : 0.f) + G_w * o;
+            term = G_T * T;
+        }
+        // exclusive suffix sum of term inside the chunk
+        float incl = term;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            float t = __shfl_down_sync(kFull, incl, off);
+            if (lane + off < 32) incl += t;
+        }
+        float excl = __shfl_down_sync(kFull, incl, 1);
+        if (lane == 31) excl = 0.f;
+        float suffix = carry + excl;
+        carry += __shfl_sync(kFull, incl, 0);
+        if (ok) {
+            int64_t i = ray * SR + s;
+            float a = __fadd_rn(__fsub_rn(1.f, o), 1e-10f);
+            float G_o = (g_opacity ? g_opacity[i] : 0.f) + G_w * T - suffix / a;
+            float e = expf(-(sigma * d));
+            grow[(int64_t)s * C1] = v ? G_o * e * d : 0.f;
+        }
+    }
+}
+
+// g_bg[c] = sum_r g_color[r,c] * bg_T[r]; fixed-order two-stage reduction (no atomics)
+constexpr int kBgRaysPerBlock = 128;
+__global__ void __launch_bounds__(256) bg_grad_partial_kernel(const float* __restrict__ g_color, const float* __restrict__ bg_T,
+                                                              int64_t n_rays, int C, float* __restrict__ partial) {
+    int64_t r0 = (int64_t)blockIdx.x * kBgRaysPerBlock;
+    int64_t r1 = r0 + kBgRaysPerBlock < n_rays ? r0 + kBgRaysPerBlock : n_rays;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float acc = 0.f;
+        for (int64_t r = r0; r < r1; ++r) acc = fmaf(g_color[r * C + c], bg_T[r], acc);
+        partial[(int64_t)blockIdx.x * C + c] = acc;
+    }
+}
+__global__ void __launch_bounds__(256) bg_grad_final_kernel(const float* __restrict__ partial, int nblk, int C,
+                                                            float* __restrict__ g_bg) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float acc = 0.f;
+    for (int b = 0; b < nblk; ++b) acc += partial[(int64_t)b * C + c];
+    g_bg[c] = acc;
+}
+
+// ray_dist (neural_points_volumetric_model.py:293-301): running max of camera depth along the ray,
+// forward difference, last = vsize_z, tiny / too large steps -> vsize_z, masked by sample validity.
+__global__ void __launch_bounds__(256) ray_dist_kernel(const float* __restrict__ sample_loc, const uint8_t* __restrict__ valid,
+                                                       int64_t n_rays, int SR, float vz, int unit_mode,
+                                                       float* __restrict__ out) {
+    extern __shared__ float sm[];
+    int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int64_t ray = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    if (ray >= n_rays) return;
+    float* cm = sm + (size_t)wib * SR;
+    float carry = -INFINITY;
+    for (int s0 = 0; s0 < SR; s0 += 32) {
+        int s = s0 + lane;
+        float z = s < SR ? sample_loc[(ray * SR + s) * 3 + 2] : -INFINITY;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            float t = __shfl_up_sync(kFull, z, o);
+            if (lane >= o) z = fmaxf(z, t);
+        }
+        z = fmaxf(z, carry);
+        if (s < SR) cm[s] = z;
+        carry = __shfl_sync(kFull, z, 31);
+    }
+    __syncwarp();
+    float two_vz = 2.f * vz;
+    for (int s = lane; s < SR; s += 32) {
+        float d = (s + 1 < SR) ? __fsub_rn(cm[s + 1], cm[s]) : vz;
+        bool bad = d < 1e-8f;
+        if (unit_mode > 0) bad = bad || d > two_vz;
+        float m = bad ? 1.f : 0.f;
+        d = __fadd_rn(__fmul_rn(d, __fsub_rn(1.f, m)), __fmul_rn(m, vz));
+        out[ray * SR + s] = valid[ray * SR + s] ? d : __fmul_rn(d, 0.f);
+    }
+}
+
+}  // namespace pn
+
+using namespace pn;
+
+#define PN_DISPATCH_NC(C, ...)                       \
+    do {                                             \
+        if ((C) <= 32) { constexpr int NC = 1; __VA_ARGS__; }       \
+        else if ((C) <= 64) { constexpr int NC = 2; __VA_ARGS__; }  \
+        else if ((C) <= 128) { constexpr int NC = 4; __VA_ARGS__; } \
+        else { constexpr int NC = 8; __VA_ARGS__; }                 \
+    } while (0)
+
+extern "C" int pn_ray_dist(const float* sample_loc, const uint8_t* sample_valid, int64_t n_rays, int32_t SR, float vsize_z,
+                           int32_t raydist_mode_unit, float* ray_dist, void* stream) {
+    PN_CHECK_ARG(sample_loc && sample_valid && ray_dist, "pn_ray_dist: null argument");
+    PN_CHECK_ARG(SR > 0 && SR <= 4096, "pn_ray_dist: SR=%d unsupported", SR);
+    if (n_rays <= 0) return PN_OK;
+    int warps = 8;
+    size_t smem = (size_t)warps * SR * sizeof(float);
+    PN_CHECK_ARG(smem <= 48 * 1024 * 2, "pn_ray_dist: SR too large");
+    if (smem > 48 * 1024) cudaFuncSetAttribute(ray_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ray_dist_kernel<<<(unsigned)cdiv(n_rays, warps), warps * 32, smem, (cudaStream_t)stream>>>(
+        sample_loc, sample_valid, n_rays, SR, vsize_z, raydist_mode_unit, ray_dist);
+    PN_LAUNCH_CHECK("ray_dist");
+    return PN_OK;
+}
+
+extern "C" int pn_composite_forward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
+                                    const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
+                                    float* opacity, float* acc_T, float* blend_w, float* bg_T, void* stream) {
+    PN_CHECK_ARG(ray_features && ray_dist && ray_valid && opacity && acc_T && blend_w && bg_T, "pn_composite_forward: null argument");
+    PN_CHECK_ARG(C >= 1 && C <= 256 && SR > 0, "pn_composite_forward: C=%d SR=%d unsupported", C, SR);
+    if (n_rays <= 0) return PN_OK;
+    unsigned blocks = (unsigned)cdiv(n_rays * 32, 256);
+    PN_DISPATCH_NC(C, (composite_fwd_kernel<NC><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+                          ray_features, ray_dist, ray_valid, bg_color, n_rays, SR, C, ray_color, opacity, acc_T, blend_w, bg_T)));
+    PN_LAUNCH_CHECK("composite_fwd");
+    return PN_OK;
+}
+
+extern "C" int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C) {
+    int64_t r = n_rays > 0 ? n_rays : 1;
+    return align_up(cdiv(r, kBgRaysPerBlock) * (int64_t)C * 4, 256) + 256;
+}
+
+extern "C" int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
+                                     const float* bg_color, const float* opacity, const float* acc_T, const float* bg_T,
+                                     const float* g_ray_color, const float* g_opacity, const float* g_acc_T,
+                                     const float* g_blend_w, const float* g_bg_T, int64_t n_rays, int32_t SR, int32_t C,
+                                     float* g_features, float* g_bg_color, void* workspace, int64_t workspace_bytes,
+                                     void* stream) {
+    PN_CHECK_ARG(ray_features && ray_dist && ray_valid && opacity && acc_T && bg_T && g_features, "pn_composite_backward: null argument");
+    PN_CHECK_ARG(C >= 1 && C <= 256 && SR > 0, "pn_composite_backward: C=%d SR=%d unsupported", C, SR);
+    PN_CHECK_ARG(workspace_bytes >= pn_composite_workspace_bytes(n_rays, C), "pn_composite_backward: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_rays <= 0) {
+        if (g_bg_color) PN_CUDA(cudaMemsetAsync(g_bg_color, 0, C * sizeof(float), st));
+        return PN_OK;
+    }
+    unsigned blocks = (unsigned)cdiv(n_rays * 32, 256);
+    PN_DISPATCH_NC(C, (composite_bwd_kernel<NC><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, bg_color, opacity, acc_T,
+                                                                      bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w, g_bg_T,
+                                                                      n_rays, SR, C, g_features)));
+    PN_LAUNCH_CHECK("composite_bwd");
+    if (g_bg_color) {
+        if (g_ray_color && bg_color) {
+            int nblk = (int)cdiv(n_rays, kBgRaysPerBlock);
+            float* partial = (float*)workspace;
+            bg_grad_partial_kernel<<<nblk, 128, 0, st>>>(g_ray_color, bg_T, n_rays, C, partial);
+            PN_LAUNCH_CHECK("bg_grad_partial");
+            bg_grad_final_kernel<<<(unsigned)cdiv(C, 128), 128, 0, st>>>(partial, nblk, C, g_bg_color);
+            PN_LAUNCH_CHECK("bg_grad_final");
+        } else {
+            PN_CUDA(cudaMemsetAsync(g_bg_color, 0, C * sizeof(float), st));
+        }
+    }
+    return PN_OK;
+}

@@ -1,0 +1,47 @@
+// Internal GEMM building blocks of the aggregator MLP (not part of the C ABI).
+#pragma once
+#include "common.cuh"
+
+namespace pn {
+
+// C[m, n] = epilogue( sum_k A[m*lda + k] * B[n*ldb + k] ),  m < M, n < N, k < Kd  (Kd % 16 == 0,
+// lda % 4 == 0, ldb % 4 == 0, A/B 16-byte aligned: the callers pad their operands).
+// epilogue, in this order:
+//   v += bias[n]                                 (bias != null)
+//   v  = v > 0 ? v : slope * v                   (leaky != 0)
+//   v *= aux[m*ldaux + n] > 0 ? 1 : slope        (aux != null and n < aux_cols: LeakyReLU backward mask)
+//   C[rowmap ? rowmap[m] : m][n] = v             (row stride ldc)
+struct GemmNT {
+    const float* A; int64_t lda;
+    const float* B; int64_t ldb;
+    float* C; int64_t ldc;
+    int64_t M; int N; int Kd;
+    const float* bias;
+    int leaky; float slope;
+    const float* aux; int64_t ldaux; int aux_cols;
+    const int* rowmap;
+};
+int gemm_nt(const GemmNT& g, cudaStream_t st);
+
+// Weight gradient: C[n, k] = sum_m A[m*lda + n] * B[m*ldb + k]  for n < N, k < Kb, reduced over M rows in
+// fixed-size splits; partial sums are combined in split order by a second kernel (deterministic).
+// Output is written UNPADDED: C[n*ldc + k] for k < Kout (<= Kb).  colsum (optional, [N]) receives
+// sum_m A[m, n] (the bias gradient) through the same fixed-order reduction.
+// scratch: gemm_tn_scratch_floats(M, N, Kb) floats.
+struct GemmTN {
+    const float* A; int64_t lda;   // [M, N]  (dPre)
+    const float* B; int64_t ldb;   // [M, Kb] (layer input, padded)
+    float* C; int64_t ldc; int Kout;
+    float* colsum;
+    int64_t M; int N; int Kb;
+};
+int64_t gemm_tn_scratch_floats(int64_t M, int N, int Kb);
+int gemm_tn(const GemmTN& g, float* scratch, cudaStream_t st);
+
+// dst[c*ldd + r] = src[r*lds + c] for r < rows, c < cols; dst columns rows..ldd-1 zero (weights only: small)
+int transpose_pad(const float* src, int rows, int cols, int64_t lds, float* dst, int64_t ldd, int dst_rows_padded,
+                  cudaStream_t st);
+// dst[r*ldd + c] = c < cols ? src[r*lds + c] : 0   for r < rows, c < ldd
+int copy_pad(const float* src, int rows, int cols, int64_t lds, float* dst, int64_t ldd, cudaStream_t st);
+
+}  // namespace pn

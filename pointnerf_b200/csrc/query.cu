@@ -1,0 +1,333 @@
+// Ray sampling against the dilated occupancy bitset and the layered K-neighbour query.
+//
+// Replaces mask_raypos / get_shadingloc / query_neigh_along_ray_layered and the host glue between
+// them (models/neural_points/query_point_indices_worldcoords.py:390-528, 633-721).
+#include "common.cuh"
+
+namespace pn {
+
+struct QGrid {
+    float sx, sy, sz, vx, vy, vz;
+    int dx, dy, dz, P;
+};
+static QGrid to_q(const pn_grid_params* p) {
+    QGrid g;
+    g.sx = p->shift[0]; g.sy = p->shift[1]; g.sz = p->shift[2];
+    g.vx = p->vsize[0]; g.vy = p->vsize[1]; g.vz = p->vsize[2];
+    g.dx = p->dims[0]; g.dy = p->dims[1]; g.dz = p->dims[2];
+    g.P = p->P;
+    return g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Ray sampling.  One warp per ray, 32 candidate depths per step: position = campos + raydir*t with
+// separately rounded mul/add (torch evaluates diff_ray_marching.py:387 as two kernels), voxel test
+// against the bitset (1 bit per candidate instead of the reference's 12-byte raypos + 4-byte mask),
+// ballot + popc give each hit its slot.  The walk stops at SR hits.
+// Algorithmic bytes: 12R (dirs) + R*D/8 (bits) + 16 R'*SR (xyz + t out) + 4R.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ray_sample_kernel(const float* __restrict__ campos, const float* __restrict__ raydir,
+                                                         const float* __restrict__ ts, int64_t ts_stride, int64_t n_rays,
+                                                         int D, int SR, QGrid g, const unsigned* __restrict__ occ_bits,
+                                                         float* __restrict__ loc_w, float* __restrict__ sample_t,
+                                                         int* __restrict__ hit_count) {
+    int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (ray >= n_rays) return;
+    float ox = campos[0], oy = campos[1], oz = campos[2];
+    float rx = raydir[3 * ray], ry = raydir[3 * ray + 1], rz = raydir[3 * ray + 2];
+    const float* tr = ts + ray * ts_stride;
+    float* out = loc_w + ray * SR * 3;
+    int kept = 0;
+    for (int d0 = 0; d0 < D && kept < SR; d0 += 32) {
+        int d = d0 + lane;
+        bool hit = false;
+        float t = 0.f, px = 0.f, py = 0.f, pz = 0.f;
+        if (d < D) {
+            t = tr[d];
+            px = __fadd_rn(ox, __fmul_rn(rx, t));
+            py = __fadd_rn(oy, __fmul_rn(ry, t));
+            pz = __fadd_rn(oz, __fmul_rn(rz, t));
+            int cx = voxel_coord(px, g.sx, g.vx), cy = voxel_coord(py, g.sy, g.vy), cz = voxel_coord(pz, g.sz, g.vz);
+            if (cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz) {
+                int64_t b = ((int64_t)cx * g.dy + cy) * g.dz + cz;
+                hit = (occ_bits[b >> 5] >> (b & 31)) & 1u;
+            }
+        }
+        unsigned m = __ballot_sync(kFull, hit);
+        int slot = kept + __popc(m & ((1u << lane) - 1u));
+        if (hit && slot < SR) {
+            out[3 * slot] = px;
+            out[3 * slot + 1] = py;
+            out[3 * slot + 2] = pz;
+            if (sample_t) sample_t[ray * SR + slot] = t;
+        }
+        kept += __popc(m);
+    }
+    kept = min(kept, SR);
+    // unused slots are zero, as the reference's torch.zeros sample_loc_tensor (:657)
+    for (int s = kept + lane; s < SR; s += 32) {
+        out[3 * s] = 0.f;
+        out[3 * s + 1] = 0.f;
+        out[3 * s + 2] = 0.f;
+        if (sample_t) sample_t[ray * SR + s] = 0.f;
+    }
+    if (lane == 0) hit_count[ray] = kept;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Neighbour query.  One warp per (ray, slot).  Per layer the (2l+1)^3 cube is enumerated in x,y,z
+// order 32 cells at a time: each lane fetches one cell's [start, end) (non-ring / out-of-grid cells
+// count 0), a warp prefix sum lays the cells' buckets out as one candidate sequence in the
+// reference's visit order, and the sequence is consumed 32 candidates per step: every lane loads one
+// point and evaluates d^2 in parallel (the loads are the cost), then the in-radius candidates are
+// inserted ONE BY ONE in sequence order by warp-uniform code that mirrors :499-519 - lane k holds
+// slot k - so the slot arrangement, the strict-'<' replacement rule and the first-maximum rescan are
+// reproduced exactly.  Algorithmic bytes: S_q*(12 + 27*8) + 16*Cand + 4*S_q*K.
+// ------------------------------------------------------------------------------------------------
+template <bool kCount>
+__global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz, QGrid g, const int* __restrict__ cell_start,
+                                                  const int* __restrict__ bucket, const int* __restrict__ grid_info,
+                                                  const float* __restrict__ loc_w, const int* __restrict__ hit_count,
+                                                  int64_t n_rays, int SR, int K, int n_layers, float r2,
+                                                  int* __restrict__ sample_pidx, int* __restrict__ ray_any,
+                                                  unsigned long long* __restrict__ n_cand) {
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (w >= n_rays * SR) return;
+    int64_t ray = w / SR;
+    int slot = (int)(w - ray * SR);
+    int* out = sample_pidx + w * K;
+    if (slot >= hit_count[ray]) {
+        for (int k = lane; k < K; k += 32) out[k] = -1;
+        return;
+    }
+    float qx = loc_w[3 * w], qy = loc_w[3 * w + 1], qz = loc_w[3 * w + 2];
+    int fx = voxel_coord(qx, g.sx, g.vx), fy = voxel_coord(qy, g.sy, g.vy), fz = voxel_coord(qz, g.sz, g.vz);
+    int slot0_cell = grid_info[PN_GI_SLOT0_CELL];
+
+    // lane k (< K; K <= 32 per register set, larger K loops) keeps slot k
+    // K up to 64 is supported with two slots per lane
+    int my_pid[2] = {-1, -1};
+    float my_d2[2] = {0.f, 0.f};
+    int seen = 0, far_slot = 0;
+    float far2 = 0.f;
+    unsigned long long visited = 0;
+
+    for (int layer = 0; layer < n_layers; ++layer) {
+        int side = 2 * layer + 1, cube = side * side * side;
+        for (int c0 = 0; c0 < cube; c0 += 32) {
+            // --- one cell per lane
+            int ci = c0 + lane, start = 0, cnt = 0;
+            if (ci < cube) {
+                int ddx = ci / (side * side) - layer, rem = ci % (side * side);
+                int ddy = rem / side - layer, ddz = rem % side - layer;
+                int ring = max(abs(ddx), max(abs(ddy), abs(ddz)));
+                int cx = fx + ddx, cy = fy + ddy, cz = fz + ddz;
+                if (ring == layer && cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz) {
+                    int cell = (cx * g.dy + cy) * g.dz + cz;
+                    start = cell_start[cell];
+                    cnt = min(cell_start[cell + 1] - start, g.P);
+                    if (cell == slot0_cell) cnt = 0;  // `if (voxel_idx > 0)` of fill_occ2pnts (:372)
+                }
+            }
+            int incl = warp_scan_incl(cnt, lane);
+            int excl = incl - cnt;
+            int total = __shfl_sync(kFull, incl, 31);
+            if (kCount) visited += total;
+            // --- candidates, 32 per step, in sequence order
+            for (int b0 = 0; b0 < total; b0 += 32) {
+                int c = b0 + lane;
+                // owner cell of candidate c: the lane j with excl_j <= c < incl_j (binary search by shuffles)
+                int lo = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    int probe = __shfl_sync(kFull, excl, lo + step);  // excl is non-decreasing
+                    if (probe <= c) lo += step;
+                }
+                // lanes with empty cells share excl with their successor: move to the last lane whose excl <= c
+                // (binary search already lands on the LAST lane with excl <= c, whose cell is non-empty when c < total)
+                int o_start = __shfl_sync(kFull, start, lo), o_excl = __shfl_sync(kFull, excl, lo);
+                bool in = false;
+                int pid = -1;
+                float d2 = 0.f;
+                if (c < total) {
+                    pid = bucket[o_start + (c - o_excl)];
+                    float x = __fsub_rn(xyz[3 * (int64_t)pid], qx);
+                    float y = __fsub_rn(xyz[3 * (int64_t)pid + 1], qy);
+                    float z = __fsub_rn(xyz[3 * (int64_t)pid + 2], qz);
+                    d2 = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
+                    in = (r2 == 0.f) || (d2 <= r2);
+                }
+                unsigned m = __ballot_sync(kFull, in);
+                while (m) {
+                    int src = __ffs(m) - 1;
+                    m &= m - 1;
+                    float cd = __shfl_sync(kFull, d2, src);
+                    int cp = __shfl_sync(kFull, pid, src);
+                    if (seen < K) {
+                        if (lane == (seen & 31)) { my_pid[seen >> 5] = cp; my_d2[seen >> 5] = cd; }
+                        if (cd > far2) { far2 = cd; far_slot = seen; }
+                        ++seen;
+                    } else {
+                        ++seen;
+                        if (cd < far2) {
+                            if (lane == (far_slot & 31)) { my_pid[far_slot >> 5] = cp; my_d2[far_slot >> 5] = cd; }
+                            // rescan: first slot holding the maximum, only if it exceeds the new value (:511-517)
+                            float v0 = (lane < K) ? my_d2[0] : -1.f;
+                            float v1 = (lane + 32 < K) ? my_d2[1] : -1.f;
+                            float mx = fmaxf(v0, v1);
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, o));
+                            far2 = cd;
+                            if (mx > cd) {
+                                unsigned b0m = __ballot_sync(kFull, v0 == mx);
+                                unsigned b1m = __ballot_sync(kFull, v1 == mx);
+                                far_slot = b0m ? (__ffs(b0m) - 1) : (32 + __ffs(b1m) - 1);
+                                far2 = mx;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (seen >= K) break;  // tested only after a whole layer (:526)
+    }
+    for (int k = lane; k < K; k += 32) out[k] = my_pid[k >> 5];
+    if (lane == 0) {
+        if (seen > 0) ray_any[ray] = 1;  // benign same-value race across the ray's warps
+        if (kCount && n_cand) atomicAdd(n_cand, visited);
+    }
+}
+
+__global__ void __launch_bounds__(256) w2pers_kernel(const float* __restrict__ xyz, int64_t n, const float* __restrict__ rot,
+                                                     const float* __restrict__ campos, float* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // cam_j = sum_i R[i][j] * (p_i - c_i), summed in i order like torch.sum over 3 products
+    float s0 = __fsub_rn(xyz[3 * i], campos[0]), s1 = __fsub_rn(xyz[3 * i + 1], campos[1]), s2 = __fsub_rn(xyz[3 * i + 2], campos[2]);
+    float c[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        c[j] = __fadd_rn(__fadd_rn(__fmul_rn(rot[j], s0), __fmul_rn(rot[3 + j], s1)), __fmul_rn(rot[6 + j], s2));
+    out[3 * i] = __fdiv_rn(c[0], c[2]);
+    out[3 * i + 1] = __fdiv_rn(c[1], c[2]);
+    out[3 * i + 2] = c[2];
+}
+
+// ---- work lists -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) slot_count_kernel(const int* __restrict__ pidx, int64_t n_slots, int K,
+                                                         unsigned long long* __restrict__ packed) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    int c = 0;
+    for (int k = 0; k < K; ++k) c += pidx[s * K + k] >= 0;
+    packed[s] = ((unsigned long long)(c > 0) << 32) | (unsigned)c;  // (valid sample, pairs)
+}
+
+__global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict__ pidx, int64_t n_slots, int K,
+                                                           const unsigned long long* __restrict__ offs,
+                                                           const unsigned long long* __restrict__ total,
+                                                           int* __restrict__ sample_list, int* __restrict__ pair_start,
+                                                           int* __restrict__ pair_src, int* __restrict__ counts) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s == 0) {
+        unsigned long long t = *total;
+        counts[0] = (int)(t >> 32);
+        counts[1] = (int)(t & 0xffffffffu);
+        pair_start[t >> 32] = (int)(t & 0xffffffffu);
+    }
+    if (s >= n_slots) return;
+    unsigned long long o = offs[s];
+    int si = (int)(o >> 32), pi = (int)(o & 0xffffffffu);
+    bool any = false;
+    for (int k = 0; k < K; ++k)
+        if (pidx[s * K + k] >= 0) {
+            pair_src[pi++] = (int)(s * K + k);
+            any = true;
+        }
+    if (any) {
+        sample_list[si] = (int)s;
+        pair_start[si] = (int)(o & 0xffffffffu);
+    }
+}
+
+}  // namespace pn
+
+using namespace pn;
+
+extern "C" int pn_ray_sample(const float* campos, const float* raydir, const float* ts, int64_t ts_rows, int64_t n_rays,
+                             int32_t D, int32_t SR, const pn_grid_params* params, const uint32_t* occ_bits,
+                             float* sample_loc_w, float* sample_t, int32_t* hit_count, void* stream) {
+    PN_CHECK_ARG(campos && raydir && ts && params && occ_bits && sample_loc_w && hit_count, "pn_ray_sample: null argument");
+    PN_CHECK_ARG(ts_rows == 1 || ts_rows == n_rays, "pn_ray_sample: ts_rows must be 1 or n_rays");
+    PN_CHECK_ARG(D >= 0 && SR > 0, "pn_ray_sample: bad D/SR");
+    if (n_rays <= 0) return PN_OK;
+    ray_sample_kernel<<<(unsigned)cdiv(n_rays * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+        campos, raydir, ts, ts_rows == 1 ? 0 : D, n_rays, D, SR, to_q(params), occ_bits, sample_loc_w, sample_t, hit_count);
+    PN_LAUNCH_CHECK("ray_sample");
+    return PN_OK;
+}
+
+extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
+                            const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
+                            const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
+                            float radius_limit2, int32_t* sample_pidx, int32_t* ray_any, unsigned long long* n_candidates,
+                            void* stream) {
+    PN_CHECK_ARG(xyz && params && cell_start && bucket_pidx && grid_info && sample_loc_w && hit_count && sample_pidx && ray_any,
+                 "pn_knn_query: null argument");
+    PN_CHECK_ARG(K >= 1 && K <= 64, "pn_knn_query: K=%d unsupported (1..64)", K);
+    PN_CHECK_ARG(n_layers >= 1 && n_layers <= 8, "pn_knn_query: n_layers=%d unsupported", n_layers);
+    if (n_rays <= 0) return PN_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    PN_CUDA(cudaMemsetAsync(ray_any, 0, n_rays * sizeof(int), st));
+    unsigned blocks = (unsigned)cdiv(n_rays * SR * 32, 256);
+    if (n_candidates)
+        knn_kernel<true><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates);
+    else
+        knn_kernel<false><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr);
+    PN_LAUNCH_CHECK("knn_query");
+    return PN_OK;
+}
+
+extern "C" int pn_w2pers(const float* xyz_w, int64_t n, const float* camrot, const float* campos, float* xyz_pers, void* stream) {
+    PN_CHECK_ARG(xyz_w && camrot && campos && xyz_pers, "pn_w2pers: null argument");
+    if (n <= 0) return PN_OK;
+    w2pers_kernel<<<(unsigned)cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(xyz_w, n, camrot, campos, xyz_pers);
+    PN_LAUNCH_CHECK("w2pers");
+    return PN_OK;
+}
+
+extern "C" int64_t pn_compact_workspace_bytes(int64_t n_slots) {
+    int64_t n = n_slots > 0 ? n_slots : 1;
+    return 2 * align_up(n * 8, 256) + align_up(scan_scratch_elems(n) * 8, 256) + 512;
+}
+
+extern "C" int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
+                                  int32_t* pair_start, int32_t* pair_src, int32_t* counts, void* workspace,
+                                  int64_t workspace_bytes, void* stream) {
+    PN_CHECK_ARG(sample_pidx && sample_list && pair_start && pair_src && counts, "pn_compact_samples: null argument");
+    PN_CHECK_ARG(workspace_bytes >= pn_compact_workspace_bytes(n_slots), "pn_compact_samples: workspace too small");
+    PN_CHECK_ARG(n_slots * (int64_t)K < 2147483647LL, "pn_compact_samples: n_slots*K exceeds int32");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_slots <= 0) {
+        PN_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(int), st));
+        PN_CUDA(cudaMemsetAsync(pair_start, 0, sizeof(int), st));
+        return PN_OK;
+    }
+    Carver ws(workspace, workspace_bytes);
+    unsigned long long* packed = ws.take<unsigned long long>(n_slots);
+    unsigned long long* offs = ws.take<unsigned long long>(n_slots);
+    unsigned long long* scratch = ws.take<unsigned long long>(scan_scratch_elems(n_slots));
+    unsigned long long* total = ws.take<unsigned long long>(1);
+    slot_count_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, packed);
+    PN_LAUNCH_CHECK("slot_count");
+    int rc = scan_exclusive_u64(packed, offs, n_slots, total, scratch, st);
+    if (rc) return rc;
+    slot_scatter_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, offs, total, sample_list,
+                                                                      pair_start, pair_src, counts);
+    PN_LAUNCH_CHECK("slot_scatter");
+    return PN_OK;
+}
