@@ -1,0 +1,52 @@
+"""CPU oracle of the whole per-ray step: query -> gather -> aggregate -> ray_dist -> ray_march -> fill_invalid.
+
+TEST INFRASTRUCTURE (see oracle/__init__.py).  Restates NeuralPointsRayMarching.forward
+(models/neural_points_volumetric_model.py:272-352) on top of the querier oracle (oracle/querier_ref.py) and
+the torch restatements (oracle/torch_port.py), and differentiates it with autograd exactly as the
+reference's training step does (loss.backward through ray_march <- aggregator <- index_select).
+"""
+import torch
+
+from . import querier_ref, torch_port as tp
+
+
+def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend="port", uniform=None, need_grads=True,
+        loss_fn=None):
+    """tables: dict from pointnerf_b200.synthetic.make_scene (torch-CPU); cam: make_camera; raydir [1,R,3];
+    bg_color [C]; agg_state: state_dict of the aggregator (reference names).  loss = sum(coarse_raycolor * loss_weight)
+    unless ``loss_fn(out)`` is given.  Returns the fill_invalid dictionary plus query intermediates and ``grads``."""
+    xyz = tables["xyz"]
+    leaves = {k: tables[k].clone().requires_grad_(need_grads) for k in ("points_embeding", "points_conf", "points_dir", "points_color")}
+    bg = bg_color.clone().float().requires_grad_(need_grads)
+    agg = tp.AggregatorPort(opt)
+    agg.load_state_dict({k: v.detach().cpu().clone() for k, v in agg_state.items()})
+
+    (pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges), extras = querier_ref.query_points(
+        opt, xyz[None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend=backend, uniform=uniform)
+    xyz_pers = tp.w2pers_points(xyz, cam["camrotc2w"], cam["campos"])
+    g = tp.gather_point_tables(pidx, xyz, xyz_pers, leaves["points_embeding"], leaves["points_color"], leaves["points_dir"],
+                               leaves["points_conf"])
+    decoded, ray_valid, weight, conf_coef = agg(g["sampled_color"], tables["Rw2c"], g["sampled_dir"], g["sampled_conf"],
+                                                g["sampled_embedding"], g["sampled_xyz_pers"], g["sampled_xyz"],
+                                                g["sample_pnt_mask"], loc_pers, loc_w, dirs, vsize, 0)
+    ray_dist = tp.ray_dist_from_samples(loc_pers, ray_valid, vsize, opt.raydist_mode_unit)
+    ray_color, _, opacity, acc_T, blend_w, bg_T, _ = tp.ray_march(ray_dist, ray_valid, decoded, bg)
+    shading = torch.logical_not(torch.any(ray_valid, dim=-1, keepdim=True)).repeat(1, 1, 3).float()
+    out = tp.fill_invalid(ray_mask, bg, ray_color, bg_T, opacity, shading)
+    out.update(ray_mask=ray_mask, sample_pidx=pidx, sample_loc_w=loc_w, sample_loc=loc_pers, decoded_features=decoded.detach(),
+               ray_valid=ray_valid, ray_dist=ray_dist.detach(), weight=weight, conf_coefficient=conf_coef, extras=extras,
+               compact=dict(ray_color=ray_color.detach(), opacity=opacity.detach(), acc_T=acc_T.detach(), bg_T=bg_T.detach()))
+    if need_grads:
+        if loss_fn is not None:
+            loss = loss_fn(out)
+        else:
+            loss = (out["coarse_raycolor"] * loss_weight).sum()
+        params = dict(agg.named_parameters())
+        names = list(leaves) + ["bg_color"] + list(params)
+        tensors = list(leaves.values()) + [bg] + list(params.values())
+        grads = torch.autograd.grad(loss, tensors, allow_unused=True)
+        out["grads"] = {n: (gr if gr is not None else torch.zeros_like(t)) for n, gr, t in zip(names, grads, tensors)}
+        out["loss"] = loss.detach()
+    for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading"):
+        out[k] = out[k].detach()
+    return out

@@ -1,0 +1,330 @@
+"""Drop-in ``PointAggregator`` on the C ABI (pn_agg_forward / pn_agg_backward).
+
+Mirrors models/aggregators/point_aggregators.py of the reference: ``PointAggregator(opt)`` is an
+``nn.Module`` with the same parameter names and shapes (``block1.{0,2}``, ``block3.{0,2}``,
+``alpha_branch.0``, ``color_branch.{0,2,4}``; :276-348), the same xavier initialisation (``init_seq``,
+models/helpers/networks.py:163-172) and the same ``forward`` signature and return structure (:729-816),
+so reference checkpoints load unchanged and ``NeuralPointsRayMarching.forward`` can call it as is.
+
+Only the configuration every shipped script uses is implemented (viewmlp, agg_intrp_order=2, linear
+distance kernel, agg_dist_pers=20, apply_pnt_mask=1, LeakyReLU, act_super=1); anything else raises.
+
+Two entry points share one autograd function:
+  * ``PointAggregator.forward(...13 tensors...)``   - the reference API: already gathered
+    ``[1,R,SR,K,*]`` tensors; rows are addressed with identity indices;
+  * ``PointAggregator.forward_tables(...)``          - the fused gather path: the neural point tables and
+    ``sample_pidx`` go straight to the kernels (no ``[R,SR,K,38]`` intermediate, no N x 38 ``torch.cat``),
+    and the per-point gradients come back through a sorted segmented reduction instead of atomic
+    ``index_add_`` (the backward of ``index_select`` in neural_points.py:791-797).
+There is no CPU path: CPU tensors raise.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+from ._lib import AggInputs, AggParams, AggWeights, WEIGHT_FIELDS
+
+
+def _check_opt(opt):
+    def need(name, ok, got=None):
+        v = getattr(opt, name, None) if got is None else got
+        if not ok(v):
+            raise NotImplementedError("pointnerf_b200.PointAggregator: %s=%r is outside the hot path (SURVEY.md 2 #4)" % (name, v))
+
+    need("which_agg_model", lambda v: v == "viewmlp")
+    need("agg_intrp_order", lambda v: v == 2)
+    need("agg_distance_kernel", lambda v: v == "linear")
+    need("agg_dist_pers", lambda v: v == 20)
+    need("apply_pnt_mask", lambda v: v > 0)
+    need("agg_weight_norm", lambda v: v > 0)
+    need("act_type", lambda v: v == "LeakyReLU")
+    need("act_super", lambda v: v > 0)
+    need("shading_feature_mlp_layer0", lambda v: v in (0, 1))  # never built by viewmlp_init
+    need("shading_feature_mlp_layer1", lambda v: v == 2)
+    need("shading_feature_mlp_layer2", lambda v: v == 0)
+    need("shading_feature_mlp_layer3", lambda v: v == 2)
+    need("shading_alpha_mlp_layer", lambda v: v == 1)
+    need("shading_color_mlp_layer", lambda v: v == 4)
+    need("agg_feat_xyz_mode", lambda v: v == "None")
+    need("agg_alpha_xyz_mode", lambda v: v == "None")
+    need("agg_color_xyz_mode", lambda v: v == "None")
+    need("point_color_mode", lambda v: "1" in list(v))
+    need("point_dir_mode", lambda v: "1" in list(v))
+    need("view_ori", lambda v: v == 0)
+    need("num_feat_freqs", lambda v: v > 0)
+    need("dist_xyz_freq", lambda v: v > 0)
+    need("num_viewdir_freqs", lambda v: v > 0)
+    aw = getattr(opt, "agg_axis_weight", None)
+    if aw is not None and tuple(float(a) for a in aw) != (1.0, 1.0, 1.0):
+        raise NotImplementedError("agg_axis_weight != (1,1,1) is outside the hot path")
+
+
+def _xavier_like_reference(seq):
+    """init_seq (helpers/networks.py:163-172): xavier_uniform with the gain of the FOLLOWING activation,
+    zero bias; the last module of a Sequential gets gain 1 (it is the activation itself for block1/3 and
+    the colour branch, a no-op there)."""
+    mods = list(seq)
+    for a, b in zip(mods[:-1], mods[1:]):
+        if isinstance(a, nn.Linear):
+            gain = nn.init.calculate_gain("leaky_relu", b.negative_slope) if isinstance(b, nn.LeakyReLU) else 1.0
+            nn.init.xavier_uniform_(a.weight, gain=gain)
+            nn.init.zeros_(a.bias)
+    if isinstance(mods[-1], nn.Linear):
+        nn.init.xavier_uniform_(mods[-1].weight, gain=1.0)
+        nn.init.zeros_(mods[-1].bias)
+
+
+class _AggCall:
+    """Non-differentiable context of one aggregator call (plain Python object handed to the autograd function)."""
+
+    def __init__(self, params, xyz, xyz_pers, Rw2c, sample_pidx, sample_loc_w, sample_loc, ray_dirs, n_slots, T,
+                 scatter_rows, want_weight):
+        self.params, self.xyz, self.xyz_pers, self.Rw2c = params, xyz, xyz_pers, Rw2c
+        self.sample_pidx, self.sample_loc_w, self.sample_loc, self.ray_dirs = sample_pidx, sample_loc_w, sample_loc, ray_dirs
+        self.n_slots, self.T, self.scatter_rows, self.want_weight = n_slots, T, scatter_rows, want_weight
+        self.S = self.M = 0
+        self.sample_list = self.pair_start = self.pair_src = None
+
+
+def _weights_struct(tensors):
+    w = AggWeights()
+    for name, t in zip(WEIGHT_FIELDS, tensors):
+        setattr(w, name, _lib.ptr(t))
+    return w
+
+
+def _inputs_struct(call, embedding, color, pdir, conf):
+    a = AggInputs()
+    a.xyz, a.xyz_pers, a.embedding = _lib.ptr(call.xyz), _lib.ptr(call.xyz_pers), _lib.ptr(embedding)
+    a.color, a.dir, a.conf, a.Rw2c = _lib.ptr(color), _lib.ptr(pdir), _lib.ptr(conf), _lib.ptr(call.Rw2c)
+    a.sample_pidx, a.sample_loc_w, a.sample_loc = _lib.ptr(call.sample_pidx), _lib.ptr(call.sample_loc_w), _lib.ptr(call.sample_loc)
+    a.ray_dirs = _lib.ptr(call.ray_dirs)
+    a.sample_list, a.pair_start, a.pair_src = _lib.ptr(call.sample_list), _lib.ptr(call.pair_start), _lib.ptr(call.pair_src)
+    a.n_slots, a.S, a.M, a.T = call.n_slots, call.S, call.M, call.T
+    return a
+
+
+def compact_samples(sample_pidx, n_slots, K):
+    """Work lists of valid samples / pairs (pn_compact_samples) and the one host read-back of (S, M)."""
+    lib = _lib.lib()
+    dev = sample_pidx.device
+    if n_slots == 0:
+        z = torch.zeros(1, dtype=torch.int32, device=dev)
+        return z, z.clone(), z.clone(), 0, 0
+    sample_list = torch.empty(max(n_slots, 1), dtype=torch.int32, device=dev)
+    pair_start = torch.empty(n_slots + 1, dtype=torch.int32, device=dev)
+    pair_src = torch.empty(max(n_slots * K, 1), dtype=torch.int32, device=dev)
+    counts = torch.empty(2, dtype=torch.int32, device=dev)
+    ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    _lib.check(lib.pn_compact_samples(_lib.ptr(sample_pidx), n_slots, K, _lib.ptr(sample_list), _lib.ptr(pair_start),
+                                      _lib.ptr(pair_src), _lib.ptr(counts), _lib.ptr(ws), ws_bytes, _lib.stream()),
+               "pn_compact_samples")
+    S, M = (int(v) for v in counts.cpu().tolist())  # the single host sync of the aggregator
+    return sample_list, pair_start, pair_src, S, M
+
+
+class _AggFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, call, embedding, color, pdir, conf, *weights):
+        lib = _lib.lib()
+        p = call.params
+        dev = embedding.device
+        K = p.K
+        call.sample_list, call.pair_start, call.pair_src, call.S, call.M = compact_samples(call.sample_pidx, call.n_slots, K)
+        decoded = torch.empty((call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
+        weight_out = torch.empty((call.n_slots, K), dtype=torch.float32, device=dev) if call.want_weight else None
+        saved_bytes = lib.pn_agg_saved_bytes(ctypes.byref(p), call.S, call.M)
+        ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 0)
+        if saved_bytes < 0 or ws_bytes < 0:
+            raise _lib.LibraryError("pn_agg_*_bytes: " + lib.pn_last_error().decode())
+        saved = torch.empty(max(saved_bytes, 1), dtype=torch.uint8, device=dev)
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
+        weights = tuple(w.detach().contiguous() for w in weights)
+        embedding, color, pdir, conf = (t.detach().contiguous() for t in (embedding, color, pdir, conf))
+        ain = _inputs_struct(call, embedding, color, pdir, conf)
+        wst = _weights_struct(weights)
+        if call.n_slots > 0:
+            _lib.check(lib.pn_agg_forward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(decoded),
+                                          _lib.ptr(weight_out), _lib.ptr(saved), saved_bytes, _lib.ptr(ws), ws_bytes,
+                                          _lib.stream()), "pn_agg_forward")
+        ctx.call, ctx.saved, ctx.saved_bytes = call, saved, saved_bytes
+        ctx.tables = (embedding, color, pdir, conf)
+        ctx.weights = weights
+        if weight_out is None:
+            weight_out = torch.empty(0, device=dev)
+        ctx.mark_non_differentiable(weight_out)
+        return decoded, weight_out
+
+    @staticmethod
+    def backward(ctx, g_decoded, _g_weight):
+        lib = _lib.lib()
+        call, p = ctx.call, ctx.call.params
+        embedding, color, pdir, conf = ctx.tables
+        dev = embedding.device
+        g_decoded = g_decoded.contiguous()
+        need = ctx.needs_input_grad  # (call, embedding, color, dir, conf, *weights)
+        rows = call.T if call.scatter_rows else call.n_slots * p.K
+        g_emb = torch.empty((rows, p.F), dtype=torch.float32, device=dev) if need[1] else None
+        g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
+        g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[3] else None
+        g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[4] else None
+        g_w = tuple(torch.empty_like(w) for w in ctx.weights)
+        ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 1)
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
+        ain = _inputs_struct(call, embedding, color, pdir, conf)
+        wst, gst = _weights_struct(ctx.weights), _weights_struct(g_w)
+        if call.n_slots == 0:
+            for t in (g_emb, g_col, g_dir, g_cnf) + g_w:
+                if t is not None:
+                    t.zero_()
+            return (None, g_emb, g_col, g_dir, g_cnf) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
+        _lib.check(lib.pn_agg_backward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(g_decoded),
+                                       _lib.ptr(ctx.saved), ctx.saved_bytes, ctypes.byref(gst), 1 if call.scatter_rows else 0,
+                                       _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf), _lib.ptr(ws),
+                                       ws_bytes, _lib.stream()), "pn_agg_backward")
+        return (None, g_emb, g_col, g_dir, g_cnf) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
+
+
+class PointAggregator(nn.Module):
+    """Same constructor / parameters / forward as the reference class (point_aggregators.py:12-816)."""
+
+    @staticmethod
+    def modify_commandline_options(parser, is_train=True):
+        """Hot-path subset of the reference's flags (point_aggregators.py:14-217), same names and defaults."""
+        add = parser.add_argument
+        add('--feat_grad', type=int, default=1)
+        add('--conf_grad', type=int, default=1)
+        add('--dir_grad', type=int, default=1)
+        add('--color_grad', type=int, default=1)
+        add('--num_feat_freqs', type=int, default=0)
+        add('--dist_xyz_freq', type=int, default=2)
+        add('--dist_xyz_deno', type=float, default=0)
+        add('--agg_dist_pers', type=int, default=1)
+        add('--agg_intrp_order', type=int, default=0)
+        add('--agg_distance_kernel', type=str, default="quadric")
+        add('--agg_weight_norm', type=int, default=1)
+        add('--agg_axis_weight', type=float, nargs='+', default=None)
+        add('--apply_pnt_mask', type=int, default=1)
+        add('--which_agg_model', type=str, default="viewmlp")
+        add('--shading_feature_mlp_layer0', type=int, default=0)
+        add('--shading_feature_mlp_layer1', type=int, default=2)
+        add('--shading_feature_mlp_layer2', type=int, default=0)
+        add('--shading_feature_mlp_layer3', type=int, default=2)
+        add('--shading_alpha_mlp_layer', type=int, default=1)
+        add('--shading_color_mlp_layer', type=int, default=1)
+        add('--shading_feature_num', type=int, default=256)
+        add('--shading_color_channel_num', type=int, default=128)
+        add('--act_type', type=str, default="ReLU")
+        add('--act_super', type=int, default=1)
+        add('--view_ori', type=int, default=0)
+        add('--point_color_mode', type=str, default="0")
+        add('--point_dir_mode', type=str, default="0")
+        add('--point_conf_mode', type=str, default="0")
+
+    def __init__(self, opt):
+        super().__init__()
+        _check_opt(opt)
+        self.opt = opt
+        F_, W = int(opt.point_features_dim), int(opt.shading_feature_num)
+        self.dist_dim = 6
+        in1 = F_ + 2 * opt.num_feat_freqs * F_ + 2 * opt.dist_xyz_freq * self.dist_dim  # :278-280
+        in3 = W + 3 + 4                                                                  # :308-309
+        self.viewdir_channels = 2 * opt.num_viewdir_freqs * 3                            # :252
+        inc = W + self.viewdir_channels                                                  # :333
+        C = int(W / 2)                                                                   # :335 (fork: no final Linear)
+        if C != int(opt.shading_color_channel_num):
+            raise NotImplementedError("shading_color_channel_num must equal shading_feature_num/2 in this fork "
+                                      "(point_aggregators.py:335,343,644)")
+
+        def act():
+            return nn.LeakyReLU(inplace=True)
+
+        self.block1 = nn.Sequential(nn.Linear(in1, W), act(), nn.Linear(W, W), act())
+        self.block3 = nn.Sequential(nn.Linear(in3, W), act(), nn.Linear(W, W), act())
+        self.alpha_branch = nn.Sequential(nn.Linear(W, 1))
+        self.color_branch = nn.Sequential(nn.Linear(inc, C), act(), nn.Linear(C, C), act(), nn.Linear(C, C), act())
+        for m in (self.block1, self.block3, self.alpha_branch, self.color_branch):  # creation order of :276-348
+            _xavier_like_reference(m)
+        _lib.lib()  # fail now, loudly, if the CUDA library is missing
+
+    # ------------------------------------------------------------------------------------------
+    def _weights(self):
+        return (self.block1[0].weight, self.block1[0].bias, self.block1[2].weight, self.block1[2].bias,
+                self.block3[0].weight, self.block3[0].bias, self.block3[2].weight, self.block3[2].bias,
+                self.alpha_branch[0].weight, self.alpha_branch[0].bias,
+                self.color_branch[0].weight, self.color_branch[0].bias, self.color_branch[2].weight,
+                self.color_branch[2].bias, self.color_branch[4].weight, self.color_branch[4].bias)
+
+    def _params(self, K, SR, dirs_per_ray, vsize):
+        o = self.opt
+        p = AggParams()
+        p.F, p.feat_freqs, p.dist_freqs, p.view_freqs = int(o.point_features_dim), int(o.num_feat_freqs), int(o.dist_xyz_freq), int(o.num_viewdir_freqs)
+        p.W, p.C, p.K, p.SR = int(o.shading_feature_num), int(o.shading_color_channel_num), int(K), int(SR)
+        p.dirs_per_ray = int(dirs_per_ray)
+        p.leaky_slope = 0.01
+        p.dist_scale = 1.0 if o.dist_xyz_deno == 0 else 1.0 / float(o.dist_xyz_deno * np.linalg.norm(vsize))
+        return p
+
+    def _want_weight(self):
+        o = self.opt
+        return (o.sparse_loss_weight > 0) or ("conf_coefficient" in o.zero_one_loss_items) or o.prob != 0  # :814
+
+    @staticmethod
+    def gradiant_clamp(x, min=0.0001, max=1):
+        """Straight-through clamp (point_aggregators.py:724-726)."""
+        return x - (x - torch.clamp(x, min=min, max=max)).detach()
+
+    # ------------------------------------------------------------------------------------------
+    def forward_tables(self, xyz, xyz_pers, embedding, color, pdir, conf, Rw2c, sample_pidx, sample_loc, sample_loc_w,
+                       ray_dirs, vsize, dirs_per_ray=True, want_weight=False):
+        """Fused gather + aggregate.  xyz/xyz_pers [N,3], embedding [N,F], color/pdir [N,3], conf [N];
+        sample_pidx int32 [R,SR,K] (-1 empty); sample_loc / sample_loc_w [R,SR,3]; ray_dirs [R,3]
+        (``dirs_per_ray``) or [R,SR,3].  Returns decoded [R,SR,C+1], weight [R,SR,K] or None."""
+        if Rw2c.dim() != 2:
+            raise NotImplementedError("per-point Rw2c is outside the hot path (every shipped script uses one 3x3)")
+        R, SR, K = (int(v) for v in sample_pidx.shape)
+        T = int(embedding.shape[0])
+        call = _AggCall(self._params(K, SR, dirs_per_ray, vsize), xyz.detach().contiguous(), xyz_pers.detach().contiguous(),
+                        Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
+                        sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
+        decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
+        return decoded.view(R, SR, -1), (weight.view(R, SR, K) if want_weight else None)
+
+    def forward(self, sampled_color, sampled_Rw2c, sampled_dir, sampled_conf, sampled_embedding, sampled_xyz_pers, sampled_xyz,
+                sample_pnt_mask, sample_loc, sample_loc_w, sample_ray_dirs, vsize, grid_vox_sz):
+        """Reference signature (point_aggregators.py:729).  Returns (decoded_features [B,R,SR,C+1],
+        ray_valid bool [B,R,SR], weight | None, conf_coefficient | None)."""
+        o = self.opt
+        in_shape = sample_loc_w.shape
+        C1 = int(o.shading_color_channel_num) + 1
+        ray_valid = torch.any(sample_pnt_mask, dim=-1)
+        if ray_valid.numel() == 0:                                                      # :746-748
+            return torch.zeros(in_shape[:-1] + (C1,), device=sample_loc_w.device), ray_valid.view(in_shape[:-1]), None, None
+        if sampled_Rw2c.dim() != 2:
+            raise NotImplementedError("per-point Rw2c is outside the hot path")
+        if sampled_xyz.requires_grad or sampled_xyz_pers.requires_grad:
+            raise NotImplementedError("xyz_grad=1 is outside the hot path (every shipped script sets xyz_grad 0)")
+        B, R, SR, K = sample_pnt_mask.shape
+        assert B == 1, "B = 1 only, like every caller of the reference"
+        n_slots, T = R * SR, R * SR * K
+        dev = sample_loc_w.device
+        ident = torch.arange(T, dtype=torch.int32, device=dev)
+        pidx = torch.where(sample_pnt_mask.reshape(-1), ident, torch.full_like(ident, -1))
+        want_w = self._want_weight()
+        call = _AggCall(self._params(K, SR, False, vsize), sampled_xyz.detach().reshape(T, 3).contiguous(),
+                        sampled_xyz_pers.detach().reshape(T, 3).contiguous(), sampled_Rw2c.detach().contiguous().float(),
+                        pidx, sample_loc_w.detach().reshape(n_slots, 3).contiguous(),
+                        sample_loc.detach().reshape(n_slots, 3).contiguous(),
+                        sample_ray_dirs.detach().reshape(n_slots, 3).contiguous(), n_slots, T, False, want_w)
+        decoded, weight = _AggFunction.apply(call, sampled_embedding.reshape(T, -1), sampled_color.reshape(T, 3),
+                                             sampled_dir.reshape(T, 3), sampled_conf.reshape(T), *self._weights())
+        if not want_w:
+            return decoded.view(in_shape[:-1] + (C1,)), ray_valid.view(in_shape[:-1]), None, None
+        conf_coefficient = self.gradiant_clamp(sampled_conf[..., 0], min=0.0001, max=1)   # :809-811
+        return (decoded.view(in_shape[:-1] + (C1,)), ray_valid.view(in_shape[:-1]), weight.view(B, R, SR, K),
+                conf_coefficient)

@@ -1,0 +1,227 @@
+"""``NeuralPoints`` (point tables + query + gather) and the per-ray driver ``NeuralPointsRayMarching``.
+
+Mirrors, for the hot path only:
+  * models/neural_points/neural_points.py - ``NeuralPoints``: the ``nn.Parameter`` tables ``xyz``,
+    ``points_embeding``, ``points_conf``, ``points_dir``, ``points_color``, ``Rw2c`` (:246-326, 480-546, same
+    names / shapes so reference checkpoints load), ``set_points`` (:480-546), ``w2pers`` (:687-693),
+    ``get_point_indices`` (:634-660) and ``forward`` (:782-812, the 14-tuple of gathered tensors);
+  * models/neural_points_volumetric_model.py - ``NeuralPointsRayMarching.forward`` (:272-352): query ->
+    aggregate -> ray_dist -> ray_march -> ``fill_invalid`` (:354-389); the 2-D neural-render tail (:343-351)
+    is out of scope.
+
+``NeuralPointsRayMarching.forward`` runs the FUSED path by default: ``sample_pidx`` and the point tables go
+straight to the aggregator kernels (no gathered ``[R,SR,K,*]`` tensors), rays are never compacted (rays
+without neighbours composite to the background exactly as ``fill_invalid`` fills them), and the only host
+synchronisation of a step is the read-back of the (valid samples, valid pairs) counts.  ``fused=False``
+goes through the three reference seams one by one (query_points -> forward -> aggregator -> ray_march ->
+fill_invalid) and produces the same numbers.
+"""
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import query as _query
+from .aggregator import PointAggregator
+from .query import lighting_fast_querier
+from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march
+
+
+class NeuralPoints(nn.Module):
+    def __init__(self, num_channels, size, opt, device, checkpoint=None, feature_init_method='rand', reg_weight=0.,
+                 feedforward=0):
+        super().__init__()
+        if getattr(opt, "wcoord_query", 1) <= 0:
+            raise NotImplementedError("perspective-frustum querier (wcoord_query<=0) is outside the hot path (SURVEY.md 2 #3)")
+        self.opt = opt
+        self.device = device
+        self.grid_vox_sz = 0
+        self.points_conf = self.points_dir = self.points_color = None
+        self.xyz = self.points_embeding = None
+        self.Rw2c = nn.Parameter(torch.eye(3, device=device, dtype=torch.float32), requires_grad=False)
+        self.querier = lighting_fast_querier(device, opt)
+
+    def reset_querier(self):
+        self.querier.clean_up()
+        self.querier = lighting_fast_querier(self.device, self.opt)
+
+    def set_points(self, points_xyz, points_embeding, points_color=None, points_dir=None, points_conf=None,
+                   parameter=False, Rw2c=None, eulers=None):
+        """neural_points.py:480-546: tensors in the reference's layouts (xyz [N,3]; the others [1,N,*])."""
+        o = self.opt
+        dev = self.device
+        if points_embeding.shape[-1] > o.point_features_dim:
+            points_embeding = points_embeding[..., :o.point_features_dim]
+        self.xyz = nn.Parameter(points_xyz.to(dev).float().contiguous(), requires_grad=False)  # xyz_grad = 0 only
+        if getattr(o, "xyz_grad", 0) > 0:
+            raise NotImplementedError("xyz_grad=1 is outside the hot path")
+        self.points_embeding = nn.Parameter(points_embeding.to(dev).float().contiguous(), requires_grad=o.feat_grad > 0)
+        if points_conf is not None and "1" in list(o.point_conf_mode):
+            self.points_conf = nn.Parameter(points_conf.to(dev).float().contiguous(), requires_grad=o.conf_grad > 0)
+        if points_dir is not None and "1" in list(o.point_dir_mode):
+            self.points_dir = nn.Parameter(points_dir.to(dev).float().contiguous(), requires_grad=o.dir_grad > 0)
+        if points_color is not None and "1" in list(o.point_color_mode):
+            self.points_color = nn.Parameter(points_color.to(dev).float().contiguous(), requires_grad=o.color_grad > 0)
+        if Rw2c is not None:
+            self.Rw2c = nn.Parameter(Rw2c.to(dev).float().contiguous(), requires_grad=False)
+        self.querier.clean_up()  # the cached grid belongs to the old point set
+
+    def prune(self, thresh):
+        """neural_points.py:350-373: keep points with conf >= thresh; invalidates the grid."""
+        mask = self.points_conf[0, :, 0] >= thresh
+        self.xyz = nn.Parameter(self.xyz[mask].contiguous(), requires_grad=self.xyz.requires_grad)
+        for name in ("points_embeding", "points_conf", "points_dir", "points_color"):
+            t = getattr(self, name)
+            if t is not None:
+                setattr(self, name, nn.Parameter(t[:, mask].contiguous(), requires_grad=t.requires_grad))
+        self.querier.clean_up()
+        return int(mask.sum())
+
+    def grow_points(self, add_xyz, add_embedding, add_color, add_dir, add_conf):
+        """neural_points.py:376-402: append points; invalidates the grid."""
+        def cat(old, new, dim):
+            return nn.Parameter(torch.cat([old, new.to(old.device).float()], dim=dim).contiguous(), requires_grad=old.requires_grad)
+        self.xyz = cat(self.xyz, add_xyz, 0)
+        self.points_embeding = cat(self.points_embeding, add_embedding, 1)
+        if self.points_conf is not None:
+            self.points_conf = cat(self.points_conf, add_conf, 1)
+        if self.points_dir is not None:
+            self.points_dir = cat(self.points_dir, add_dir, 1)
+        if self.points_color is not None:
+            self.points_color = cat(self.points_color, add_color, 1)
+        self.querier.clean_up()
+
+    def w2pers(self, point_xyz, camrotc2w, campos):
+        """neural_points.py:687-693: [N,3] -> [1,N,3] (x/z, y/z, z) in the camera frame."""
+        return _query.w2pers(point_xyz.detach(), camrotc2w[0], campos[0])[None]
+
+    def get_point_indices(self, inputs, cam_rot_tensor, cam_pos_tensor, pixel_idx_tensor, near_plane, far_plane, h, w, intrinsic,
+                          vox_query=False):
+        """neural_points.py:634-660."""
+        if vox_query:
+            raise NotImplementedError("vox_query (NN<0) is outside the hot path")
+        point_xyz_pers_tensor = self.w2pers(self.xyz, cam_rot_tensor, cam_pos_tensor)
+        n = torch.full([1], self.xyz.shape[0], device=self.xyz.device, dtype=torch.int32)
+        (sample_pidx_tensor, sample_loc_tensor, sample_loc_w_tensor, sample_ray_dirs_tensor, ray_mask_tensor, vsize,
+         ranges) = self.querier.query_points(pixel_idx_tensor, point_xyz_pers_tensor, self.xyz[None, ...], n, h, w, intrinsic,
+                                             near_plane, far_plane, inputs["raydir"], cam_pos_tensor, cam_rot_tensor,
+                                             uniform=inputs.get("uniform"))
+        return (sample_pidx_tensor, sample_loc_tensor, ray_mask_tensor, point_xyz_pers_tensor, sample_loc_w_tensor,
+                sample_ray_dirs_tensor, vsize)
+
+    def forward(self, inputs):
+        """neural_points.py:782-812 (reference seam): the 14-tuple of gathered [1,R'',SR,K,*] tensors."""
+        camrotc2w, campos, near, far = inputs["camrotc2w"], inputs["campos"], inputs["near"], inputs["far"]
+        near = float(torch.as_tensor(near).min())
+        far = float(torch.as_tensor(far).max())
+        pixel_idx = inputs.get("pixel_idx")
+        sample_pidx, sample_loc, ray_mask_tensor, xyz_pers, sample_loc_w, sample_ray_dirs, vsize = self.get_point_indices(
+            inputs, camrotc2w, campos, pixel_idx, near, far, inputs.get("h"), inputs.get("w"), inputs.get("intrinsic"))
+        sample_pnt_mask = sample_pidx >= 0
+        B, R, SR, K = sample_pidx.shape
+        flat = torch.clamp(sample_pidx, min=0).view(-1).long()
+
+        def sel(t):
+            return None if t is None else torch.index_select(t, 1, flat).view(B, R, SR, K, t.shape[2])
+        return (sel(self.points_color), self.Rw2c, sel(self.points_dir), sel(self.points_conf), sel(self.points_embeding),
+                sel(xyz_pers), sel(self.xyz[None, ...]), sample_pnt_mask, sample_loc, sample_loc_w, sample_ray_dirs,
+                ray_mask_tensor, vsize, self.grid_vox_sz)
+
+
+class NeuralPointsRayMarching(nn.Module):
+    """Per-ray driver (neural_points_volumetric_model.py:272-389) without the 2-D neural-render tail."""
+
+    def __init__(self, opt, neural_points=None, aggregator=None, device=None):
+        super().__init__()
+        self.opt = opt
+        device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.aggregator = aggregator if aggregator is not None else PointAggregator(opt).to(device)
+        self.neural_points = neural_points if neural_points is not None else NeuralPoints(opt.point_features_dim, 0, opt, device)
+        self.render_func, self.blend_func = radiance_render, alpha_blend
+        self.return_color = True
+        if getattr(opt, "which_tonemap_func", "off") != "off":
+            raise NotImplementedError("tone mapping is outside the hot path (all scripts: which_tonemap_func='off')")
+
+    # ---- reference seams, one by one ------------------------------------------------------------
+    def forward_seams(self, campos, raydir, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None, h=None, w=None,
+                      intrinsic=None, uniform=None, **kargs):
+        o = self.opt
+        (sampled_color, sampled_Rw2c, sampled_dir, sampled_conf, sampled_embedding, sampled_xyz_pers, sampled_xyz,
+         sample_pnt_mask, sample_loc, sample_loc_w, sample_ray_dirs, ray_mask_tensor, vsize, grid_vox_sz) = self.neural_points(
+            {"pixel_idx": pixel_idx, "camrotc2w": camrotc2w, "campos": campos, "near": near, "far": far, "h": h, "w": w,
+             "intrinsic": intrinsic, "raydir": raydir, "uniform": uniform})
+        decoded_features, ray_valid, weight, conf_coefficient = self.aggregator(
+            sampled_color, sampled_Rw2c, sampled_dir, sampled_conf, sampled_embedding, sampled_xyz_pers, sampled_xyz,
+            sample_pnt_mask, sample_loc, sample_loc_w, sample_ray_dirs, vsize, grid_vox_sz)
+        ray_dist = ray_dist_from_samples(sample_loc, ray_valid, vsize, o.raydist_mode_unit)
+        output = {"queried_shading": torch.logical_not(torch.any(ray_valid, dim=-1, keepdims=True)).repeat(1, 1, 3).float()}
+        ray_color, _, opacity, _, blend_weight, background_transmission, _ = ray_march(
+            ray_dist, ray_valid, decoded_features, self.render_func, self.blend_func, bg_color)
+        output["coarse_raycolor"] = ray_color
+        output["coarse_point_opacity"] = opacity
+        output["coarse_is_background"] = background_transmission
+        output["ray_mask"] = ray_mask_tensor
+        if weight is not None:
+            output["weight"] = weight.detach()
+            output["blend_weight"] = blend_weight.detach()
+            output["conf_coefficient"] = conf_coefficient
+        return self.fill_invalid(output, bg_color)
+
+    @staticmethod
+    def fill_invalid(output, bg_color):
+        """neural_points_volumetric_model.py:354-389 (tone map off)."""
+        ray_mask = output["ray_mask"]
+        B, OR = ray_mask.shape
+        idx = torch.nonzero(ray_mask)
+        dev = output["coarse_raycolor"].device
+        is_bg = torch.ones([B, OR, 1], dtype=torch.float32, device=dev)
+        is_bg[idx[..., 0], idx[..., 1], :] = output["coarse_is_background"]
+        output["coarse_is_background"] = is_bg
+        output["coarse_mask"] = 1 - is_bg
+        colour = torch.ones([B, OR, output["coarse_raycolor"].shape[-1]], dtype=torch.float32, device=dev) * bg_color[None, ...]
+        colour[idx[..., 0], idx[..., 1], :] = output["coarse_raycolor"]
+        output["coarse_raycolor"] = colour
+        opac = torch.zeros([B, OR, output["coarse_point_opacity"].shape[2]], dtype=torch.float32, device=dev)
+        opac[idx[..., 0], idx[..., 1], :] = output["coarse_point_opacity"]
+        output["coarse_point_opacity"] = opac
+        shading = torch.ones([B, OR, output["queried_shading"].shape[2]], dtype=torch.float32, device=dev)
+        shading[idx[..., 0], idx[..., 1], :] = output["queried_shading"]
+        output["queried_shading"] = shading
+        return output
+
+    # ---- fused path -----------------------------------------------------------------------------
+    def forward(self, campos, raydir, gt_image=None, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None,
+                focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, **kargs):
+        """Same keyword interface as the reference driver (:272-286).  Returns the ``fill_invalid`` dictionary:
+        coarse_raycolor [1,R,C], coarse_is_background [1,R,1], coarse_mask, coarse_point_opacity [1,R,SR],
+        queried_shading [1,R,3], ray_mask int8 [1,R] (+ weight / blend_weight / conf_coefficient per sample when the
+        losses need them; in the fused path these are [1,R,SR,K] over ALL rays, zero on rays that miss)."""
+        if not fused:
+            return self.forward_seams(campos, raydir, bg_color=bg_color, camrotc2w=camrotc2w, pixel_idx=pixel_idx, near=near,
+                                      far=far, h=h, w=w, intrinsic=intrinsic, uniform=uniform, **kargs)
+        o, nps = self.opt, self.neural_points
+        near = float(torch.as_tensor(near).min())
+        far = float(torch.as_tensor(far).max())
+        xyz = nps.xyz
+        raw = nps.querier.query_raw(xyz.detach(), raydir, campos, near, far, uniform=uniform)
+        pidx, loc_w = raw["sample_pidx"], raw["sample_loc_w"]                     # [R,SR,K], [R,SR,3]
+        R, SR, K = pidx.shape
+        loc_pers = _query.w2pers(loc_w, camrotc2w[0], campos[0])
+        xyz_pers = _query.w2pers(xyz.detach(), camrotc2w[0], campos[0])
+        want_w = self.aggregator._want_weight()
+        decoded, weight = self.aggregator.forward_tables(
+            xyz, xyz_pers, nps.points_embeding[0], nps.points_color[0], nps.points_dir[0], nps.points_conf[0, :, 0], nps.Rw2c,
+            pidx, loc_pers, loc_w, raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w)
+        ray_valid = (pidx >= 0).any(dim=-1)[None]                                 # [1,R,SR]
+        ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)
+        ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march(ray_dist, ray_valid, decoded[None], self.render_func,
+                                                                    self.blend_func, bg_color)
+        out = {"coarse_raycolor": ray_color, "coarse_point_opacity": opacity, "coarse_is_background": bg_T,
+               "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).to(torch.int8)[None],
+               "queried_shading": torch.logical_not(torch.any(ray_valid, dim=-1, keepdims=True)).repeat(1, 1, 3).float()}
+        if want_w:
+            out["weight"] = weight.detach()[None]
+            out["blend_weight"] = blend_weight.detach()
+            conf = nps.points_conf[0, :, 0]
+            g = torch.clamp(pidx, min=0).long()
+            out["conf_coefficient"] = PointAggregator.gradiant_clamp(conf[g], min=0.0001, max=1)[None]
+        return out

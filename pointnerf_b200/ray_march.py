@@ -1,0 +1,145 @@
+"""Drop-in ``ray_march`` / ``alpha_ray_march`` on the C ABI (pn_composite_forward / _backward).
+
+Mirrors models/rendering/diff_ray_marching.py:509-573 of the reference with the only render / blend
+functions its scripts select - ``radiance_render`` (``feat[..., 1:]``, diff_render_func.py:48-50) and
+``alpha_blend`` (``opacity * acc_transmission``, :36-37): same signature, same 7-tuple / 5-tuple, same
+dtypes and shapes, differentiable w.r.t. ``ray_features`` and ``bg_color``.  Also ``ray_dist_from_samples``,
+the cummax / diff / clamp block of models/neural_points_volumetric_model.py:293-301.
+
+The reference hard-codes 128 colour channels (``.view(B, 1, 128)``, :546); here C = features - 1.
+There is no CPU path: CPU tensors raise.
+"""
+import torch
+
+from . import _lib
+
+
+def radiance_render(ray_feature):
+    """diff_render_func.py:48-50."""
+    return ray_feature[..., 1:]
+
+
+def alpha_blend(opacity, acc_transmission):
+    """diff_render_func.py:36-37."""
+    return opacity * acc_transmission
+
+
+def find_render_function(name):
+    if name == "radiance":
+        return radiance_render
+    raise NotImplementedError("render function %r is outside the hot path (all scripts: which_render_func='radiance')" % name)
+
+
+def find_blend_function(name):
+    if name == "alpha":
+        return alpha_blend
+    raise NotImplementedError("blend function %r is outside the hot path (all scripts: which_blend_func='alpha')" % name)
+
+
+def _check_funcs(render_func, blend_func):
+    if render_func is not None and getattr(render_func, "__name__", "") != "radiance_render":
+        raise NotImplementedError("ray_march: only radiance_render is implemented, got %r" % (render_func,))
+    if getattr(blend_func, "__name__", "") != "alpha_blend":
+        raise NotImplementedError("ray_march: only alpha_blend is implemented, got %r" % (blend_func,))
+
+
+class _Composite(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ray_features, ray_dist, ray_valid_u8, bg_color, want_color):
+        lib = _lib.lib()
+        R, SR, C1 = (int(v) for v in ray_features.shape)
+        C = C1 - 1
+        dev = ray_features.device
+        feats = ray_features.detach().contiguous()
+        dist = ray_dist.detach().contiguous().float()
+        bg = bg_color.detach().contiguous().float().view(-1) if bg_color is not None else None
+        if bg is not None and bg.numel() != C:
+            raise ValueError("bg_color has %d entries, features have %d colour channels" % (bg.numel(), C))
+        ray_color = torch.empty((R, C), dtype=torch.float32, device=dev) if want_color else None
+        opacity = torch.empty((R, SR), dtype=torch.float32, device=dev)
+        acc_T = torch.empty((R, SR), dtype=torch.float32, device=dev)
+        blend_w = torch.empty((R, SR), dtype=torch.float32, device=dev)
+        bg_T = torch.empty((R,), dtype=torch.float32, device=dev)
+        if R > 0:
+            _lib.check(lib.pn_composite_forward(_lib.ptr(feats), _lib.ptr(dist), _lib.ptr(ray_valid_u8), _lib.ptr(bg), R, SR, C,
+                                                _lib.ptr(ray_color), _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(blend_w),
+                                                _lib.ptr(bg_T), _lib.stream()), "pn_composite_forward")
+        ctx.save_for_backward(feats, dist, ray_valid_u8, bg if bg is not None else torch.empty(0, device=dev), opacity, acc_T, bg_T)
+        ctx.has_bg, ctx.want_color = bg is not None, want_color
+        ctx.bg_shape = tuple(bg_color.shape) if bg_color is not None else None
+        if ray_color is None:
+            ray_color = torch.empty(0, device=dev)
+        return ray_color, opacity, acc_T, blend_w, bg_T
+
+    @staticmethod
+    def backward(ctx, g_color, g_opacity, g_acc_T, g_blend_w, g_bg_T):
+        lib = _lib.lib()
+        feats, dist, valid, bg, opacity, acc_T, bg_T = ctx.saved_tensors
+        R, SR, C1 = (int(v) for v in feats.shape)
+        C = C1 - 1
+        dev = feats.device
+
+        def c(t):
+            return t.contiguous() if t is not None else None
+
+        g_color = c(g_color) if ctx.want_color else None
+        g_feat = torch.empty_like(feats)
+        need_bg = ctx.has_bg and ctx.needs_input_grad[3]
+        g_bg = torch.empty((C,), dtype=torch.float32, device=dev) if need_bg else None
+        if R == 0:
+            return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None
+        ws_bytes = lib.pn_composite_workspace_bytes(R, C)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.pn_composite_backward(_lib.ptr(feats), _lib.ptr(dist), _lib.ptr(valid), _lib.ptr(bg) if ctx.has_bg else None,
+                                             _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(bg_T), _lib.ptr(g_color),
+                                             _lib.ptr(c(g_opacity)), _lib.ptr(c(g_acc_T)), _lib.ptr(c(g_blend_w)),
+                                             _lib.ptr(c(g_bg_T)), R, SR, C, _lib.ptr(g_feat), _lib.ptr(g_bg), _lib.ptr(ws),
+                                             ws_bytes, _lib.stream()), "pn_composite_backward")
+        return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None
+
+
+def _flatten(ray_dist, ray_valid, ray_features):
+    B, R, SR = ray_dist.shape
+    if B != 1:
+        raise NotImplementedError("B = 1 only, like every caller of the reference")
+    return (ray_features.reshape(R, SR, ray_features.shape[-1]), ray_dist.reshape(R, SR),
+            ray_valid.reshape(R, SR).to(torch.uint8).contiguous(), B, R, SR)
+
+
+def ray_march(ray_dist, ray_valid, ray_features, render_func, blend_func, bg_color=None):
+    """diff_ray_marching.py:509-555.  ray_dist [1,R,SR], ray_valid bool [1,R,SR], ray_features [1,R,SR,C+1],
+    bg_color [.., C] or None -> (ray_color [1,R,C], point_color [1,R,SR,C], opacity [1,R,SR],
+    acc_transmission [1,R,SR], blend_weight [1,R,SR,1], background_transmission [1,R,1],
+    background_blend_weight [1,R,1])."""
+    _check_funcs(render_func, blend_func)
+    feats, dist, valid, B, R, SR = _flatten(ray_dist, ray_valid, ray_features)
+    point_color = ray_features[..., 1:]
+    ray_color, opacity, acc_T, blend_w, bg_T = _Composite.apply(feats, dist, valid, bg_color, True)
+    bg_T = bg_T.view(B, R, 1)
+    return (ray_color.view(B, R, -1), point_color, opacity.view(B, R, SR), acc_T.view(B, R, SR), blend_w.view(B, R, SR, 1),
+            bg_T, 1 * bg_T)
+
+
+def alpha_ray_march(ray_dist, ray_valid, ray_features, blend_func):
+    """diff_ray_marching.py:558-573 -> (opacity, acc_transmission, blend_weight, background_transmission,
+    background_blend_weight)."""
+    _check_funcs(None, blend_func)
+    feats, dist, valid, B, R, SR = _flatten(ray_dist, ray_valid, ray_features)
+    _, opacity, acc_T, blend_w, bg_T = _Composite.apply(feats, dist, valid, None, False)
+    bg_T = bg_T.view(B, R, 1)
+    return opacity.view(B, R, SR), acc_T.view(B, R, SR), blend_w.view(B, R, SR, 1), bg_T, 1 * bg_T
+
+
+def ray_dist_from_samples(sample_loc, ray_valid, vsize, raydist_mode_unit=1):
+    """neural_points_volumetric_model.py:293-301.  sample_loc [1,R,SR,3] (perspective coords: [...,2] is the
+    camera depth), ray_valid bool [1,R,SR] -> ray_dist [1,R,SR].  No gradient (the reference's flows only to xyz)."""
+    lib = _lib.lib()
+    B, R, SR = ray_valid.shape
+    loc = sample_loc.detach().reshape(B * R, SR, 3).contiguous()
+    valid = ray_valid.reshape(B * R, SR).to(torch.uint8).contiguous()
+    out = torch.empty((B * R, SR), dtype=torch.float32, device=loc.device)
+    if B * R == 0:
+        return out.view(B, R, SR)
+    _lib.check(lib.pn_ray_dist(_lib.ptr(loc), _lib.ptr(valid), B * R, SR, float(vsize[2]), int(raydist_mode_unit),
+                               _lib.ptr(out), _lib.stream()), "pn_ray_dist")
+    return out.view(B, R, SR)

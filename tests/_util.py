@@ -1,0 +1,31 @@
+import numpy as np
+import torch
+
+RTOL = 1e-4  # BASELINE.json north_star: "within 1e-4 relative in fp32"
+
+
+def rel_err(got, want):
+    """max |got - want| / max |want|  (relative to the tensor's scale, fp32)."""
+    got = torch.as_tensor(got).detach().cpu().double()
+    want = torch.as_tensor(want).detach().cpu().double()
+    assert got.shape == want.shape, (got.shape, want.shape)
+    if want.numel() == 0:
+        return 0.0
+    return float((got - want).abs().max() / want.abs().max().clamp_min(1e-30))
+
+
+def assert_close(got, want, name, tol=RTOL):
+    e = rel_err(got, want)
+    assert e <= tol, "%s: relative error %.3g > %.1g" % (name, e, tol)
+
+
+def canon_neighbours(pidx, xyz, loc_w):
+    """Sort each sample's K neighbour indices by (d^2, index) so that sets compare independent of slot order."""
+    pidx = np.asarray(pidx)
+    xyz = np.asarray(xyz, np.float64)
+    loc = np.asarray(loc_w, np.float64)
+    d = xyz[np.clip(pidx, 0, None)] - loc[..., None, :]
+    d2 = (d * d).sum(-1)
+    d2 = np.where(pidx >= 0, d2, np.inf)
+    order = np.lexsort((pidx, d2), axis=-1)
+    return np.take_along_axis(pidx, order, axis=-1)

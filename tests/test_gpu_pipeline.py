@@ -1,0 +1,109 @@
+"""Whole per-ray step on the GPU (fused path and seam-by-seam path) vs the CPU oracle pipeline."""
+import copy
+
+import pytest
+import torch
+
+from oracle import pipeline_ref
+from pointnerf_b200 import synthetic as syn
+from pointnerf_b200.neural_points import NeuralPointsRayMarching
+from _util import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(opt, tables, dev, alpha_bias=60.0, seed=0):
+    torch.manual_seed(seed)
+    m = NeuralPointsRayMarching(opt, device=dev)
+    with torch.no_grad():
+        # a live density head: sigma*dist ~ 0.5 so that transmittance actually decays along the ray
+        m.aggregator.alpha_branch[0].bias.fill_(alpha_bias)
+        for n, p in m.aggregator.named_parameters():
+            if p.dim() == 1 and not n.startswith("alpha"):
+                p.normal_(0, 0.05)
+    m.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                               tables["points_conf"], Rw2c=tables["Rw2c"])
+    return m
+
+
+def _step(model, cam, raydir, bg, wt, dev, fused, uniform=None):
+    for p in model.parameters():
+        p.grad = None
+    bg_d = bg.to(dev).clone().requires_grad_(True)
+    out = model(cam["campos"].to(dev), raydir.to(dev), bg_color=bg_d, camrotc2w=cam["camrotc2w"].to(dev), near=cam["near"],
+                far=cam["far"], h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"], fused=fused,
+                uniform=uniform.to(dev) if uniform is not None else None)
+    loss = (out["coarse_raycolor"] * wt.to(dev)).sum() + (out["coarse_point_opacity"] ** 2).sum() * 0.1
+    loss.backward()
+    grads = {n: p.grad.detach().cpu().clone() for n, p in model.aggregator.named_parameters()}
+    nps = model.neural_points
+    for n in ("points_embeding", "points_conf", "points_dir", "points_color"):
+        grads[n] = getattr(nps, n).grad.detach().cpu().clone()
+    grads["bg_color"] = bg_d.grad.detach().cpu().clone()
+    return out, grads
+
+
+@pytest.mark.parametrize("train", [0, 1])
+def test_step_matches_oracle(tiny_scene, cuda_dev, train):
+    opt, tables, cam = tiny_scene
+    opt = copy.copy(opt)
+    opt.is_train = train
+    R = 300
+    raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, R, seed=5))
+    g = torch.Generator().manual_seed(2)
+    bg = torch.rand(opt.shading_color_channel_num, generator=g)
+    wt = torch.randn(1, R, opt.shading_color_channel_num, generator=g)
+    uniform = torch.rand(1, R, opt.z_depth_dim, generator=g) if train else None
+    model = _model(opt, tables, cuda_dev)
+    ref = pipeline_ref.run(opt, tables, cam, raydir, bg, model.aggregator.state_dict(), uniform=uniform,
+                           loss_fn=lambda o: (o["coarse_raycolor"] * wt).sum() + (o["coarse_point_opacity"] ** 2).sum() * 0.1)
+    assert float(ref["coarse_is_background"].min()) < 0.5, "test scene must be opaque enough to exercise compositing"
+    for fused in (True, False):
+        out, grads = _step(model, cam, raydir, bg, wt, cuda_dev, fused, uniform)
+        tag = "fused" if fused else "seams"
+        if not torch.equal(out["ray_mask"].cpu(), ref["ray_mask"]):
+            # only possible when the device's cumsum chain rounds depths differently from the CPU (is_train jitter)
+            assert train == 1
+            pytest.skip("device depth chain differs from the CPU chain; bit-exact query is covered by test_gpu_query")
+        for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading"):
+            assert_close(out[k], ref[k], "%s %s" % (tag, k))
+        for n, gr in grads.items():
+            assert_close(gr, ref["grads"][n], "%s grad %s" % (tag, n))
+
+
+def test_fused_equals_seams_and_is_deterministic(tiny_scene, cuda_dev):
+    opt, tables, cam = tiny_scene
+    R = 500
+    raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, R, seed=8))
+    g = torch.Generator().manual_seed(4)
+    bg = torch.rand(opt.shading_color_channel_num, generator=g)
+    wt = torch.randn(1, R, opt.shading_color_channel_num, generator=g)
+    model = _model(opt, tables, cuda_dev)
+    o1, g1 = _step(model, cam, raydir, bg, wt, cuda_dev, True)
+    o2, g2 = _step(model, cam, raydir, bg, wt, cuda_dev, True)
+    o3, g3 = _step(model, cam, raydir, bg, wt, cuda_dev, False)
+    assert torch.equal(o1["coarse_raycolor"], o2["coarse_raycolor"])
+    for n in g1:
+        assert torch.equal(g1[n], g2[n]), "non-deterministic gradient " + n   # no atomics anywhere on the path
+    assert torch.equal(o1["ray_mask"], o3["ray_mask"])
+    assert_close(o1["coarse_raycolor"], o3["coarse_raycolor"], "fused vs seams colour", tol=1e-5)
+    for n in g1:
+        assert_close(g1[n], g3[n], "fused vs seams grad " + n, tol=2e-5)
+
+
+def test_all_rays_miss(tiny_scene, cuda_dev):
+    opt, tables, cam = tiny_scene
+    model = _model(opt, tables, cuda_dev)
+    raydir = -syn.make_rays(cam, syn.random_pixels(cam, 32))[0]
+    bg = torch.rand(opt.shading_color_channel_num)
+    for fused in (True, False):
+        out = model(cam["campos"].to(cuda_dev), raydir.to(cuda_dev), bg_color=bg.to(cuda_dev), camrotc2w=cam["camrotc2w"].to(cuda_dev),
+                    near=cam["near"], far=cam["far"], fused=fused)
+        assert int(out["ray_mask"].sum()) == 0
+        assert torch.equal(out["coarse_raycolor"].cpu(), bg[None, None, :].expand(1, 32, -1))
+        assert float(out["coarse_is_background"].min()) == 1.0
+
+
+def test_smoke_entry(cuda_dev):
+    import __graft_entry__ as ge
+    ge.smoke()

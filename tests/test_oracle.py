@@ -1,0 +1,214 @@
+"""The oracle itself (CPU): restatements vs the unmodified reference (build container) and vs committed golden vectors."""
+import copy
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import querier_ref as qr, ref_import, torch_port as tp
+from pointnerf_b200 import synthetic as syn
+from pointnerf_b200.options import make_opt
+from _util import rel_err
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+needs_ref = pytest.mark.skipif(not ref_import.available(), reason="reference tree not present (GPU box)")
+
+
+def _agg_inputs(seed=1, R=7, SR=5, K=8, F=32):
+    g = torch.Generator().manual_seed(seed)
+
+    def rn(*s):
+        return torch.randn(*s, generator=g)
+    B = 1
+    mask = torch.rand(B, R, SR, K, generator=g) > 0.4
+    mask[0, 1] = False
+    mask[0, 2, 3] = False
+    return dict(sampled_color=rn(B, R, SR, K, 3), sampled_Rw2c=torch.linalg.qr(rn(3, 3))[0], sampled_dir=rn(B, R, SR, K, 3),
+                sampled_conf=torch.rand(B, R, SR, K, 1, generator=g) * 1.2 - 0.1, sampled_embedding=rn(B, R, SR, K, F) * 0.3,
+                sampled_xyz_pers=rn(B, R, SR, K, 3) + torch.tensor([0, 0, 4.]), sampled_xyz=rn(B, R, SR, K, 3) * 0.01,
+                sample_pnt_mask=mask, sample_loc=rn(B, R, SR, 3) + torch.tensor([0, 0, 4.]), sample_loc_w=rn(B, R, SR, 3) * 0.01,
+                sample_ray_dirs=rn(B, R, SR, 3))
+
+
+@needs_ref
+def test_aggregator_port_equals_reference():
+    ns = ref_import.load()
+    opt = make_opt()
+    opt_ref = copy.copy(opt)
+    opt_ref.agg_axis_weight = None          # the reference builds this tensor on "cuda" (:247); None takes the same branch
+    torch.manual_seed(0)
+    ref = ns.PointAggregator(opt_ref)
+    port = tp.AggregatorPort(opt)
+    port.load_state_dict(ref.state_dict())
+    ins = _agg_inputs()
+    gk = ["sampled_color", "sampled_dir", "sampled_conf", "sampled_embedding"]
+    for k in gk:
+        ins[k].requires_grad_(True)
+    res = []
+    wt = None
+    for m in (ref, port):
+        o = m(*[ins[k] for k in ins], (0.004,) * 3, 0)
+        if wt is None:
+            wt = torch.randn(o[0].shape, generator=torch.Generator().manual_seed(3))
+        loss = (o[0] * wt).sum() + (o[3] ** 2).sum()
+        res.append((o, torch.autograd.grad(loss, [ins[k] for k in gk] + list(m.parameters()))))
+    (o1, g1), (o2, g2) = res
+    assert torch.equal(o1[0], o2[0]) and torch.equal(o1[1], o2[1]) and torch.equal(o1[2], o2[2]) and torch.equal(o1[3], o2[3])
+    for a, b in zip(g1, g2):
+        assert rel_err(b, a) < 1e-6
+
+
+@needs_ref
+def test_ray_march_port_equals_reference():
+    ns = ref_import.load()
+    g = torch.Generator().manual_seed(2)
+    R, SR, C = 11, 24, 128
+    feats = torch.randn(1, R, SR, C + 1, generator=g)
+    feats[..., 0] = torch.rand(1, R, SR, generator=g) * 40
+    dist = torch.rand(1, R, SR, generator=g) * 0.02
+    valid = torch.rand(1, R, SR, generator=g) < 0.7
+    bg = torch.rand(C, generator=g)
+    a = ns.ray_march(dist, valid, feats, ns.radiance_render, ns.alpha_blend, bg)
+    b = tp.ray_march(dist, valid, feats, bg)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    a5 = ns.alpha_ray_march(dist, valid, feats, ns.alpha_blend)
+    for x, y in zip(a5, (b[2], b[3], b[4], b[5], b[6])):
+        assert torch.equal(x, y)
+
+
+@needs_ref
+def test_sampler_and_pe_port_equal_reference():
+    ns = ref_import.load()
+    g = torch.Generator().manual_seed(4)
+    raydir = torch.randn(1, 9, 3, generator=g)
+    campos = torch.randn(1, 3, generator=g)
+    raypos, _, _, ts = ns.near_far_linear_ray_generation(campos, raydir, 64, torch.tensor([[[2.0]]]), torch.tensor([[[6.0]]]), jitter=0.)
+    ts_p = tp.sample_ts(raydir, 64, 2.0, 6.0)
+    assert torch.equal(ts, ts_p)
+    assert torch.equal(raypos, tp.raypos_from_ts(campos, raydir, ts_p))
+    x = torch.randn(5, 7, 3, generator=g)
+    for freqs, ori in ((4, True), (5, False), (3, False)):
+        assert torch.equal(ns.positional_encoding(x, freqs, ori=ori), tp.positional_encoding(x, freqs, ori=ori))
+
+
+def test_querier_backends_agree(tiny_scene):
+    """The reference's own kernel string compiled for the host (oracle/_ref) vs the C port: identical tables and results."""
+    opt, tables, cam = tiny_scene
+    if not os.path.isfile(qr.REF_SO):
+        pytest.skip("oracle/_ref not built (needs the reference tree once)")
+    raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, 400, seed=1))
+    outs = {}
+    for be in ("ref", "port"):
+        outs[be] = qr.query_points(opt, tables["xyz"][None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend=be)
+    (a, ea), (b, eb) = outs["ref"], outs["port"]
+    for i in (0, 1, 2, 3, 4):
+        assert torch.equal(a[i], b[i]), i
+    for k in ("coor_occ", "coor_2_occ", "occ_numpnts", "occ_2_pnts", "occ_2_coor"):
+        assert np.array_equal(ea["grid"][k], eb["grid"][k]), k
+    assert a[0].shape[1] > 100 and int((a[0] >= 0).sum()) > 10000
+
+
+def test_hyperparameters_host_arithmetic(tiny_scene):
+    """pointnerf_b200.synthetic.grid_hyperparameters (used by the product) == the oracle's get_hyperparameters."""
+    opt, tables, cam = tiny_scene
+    xyz = tables["xyz"]
+    a = qr.get_hyperparameters(opt, xyz[None])
+    b = syn.grid_hyperparameters(opt, xyz.min(0)[0].numpy(), xyz.max(0)[0].numpy())
+    for k in ("ranges", "scaled_vsize", "scaled_vdim", "radius_limit2"):
+        assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), k
+    for name in ("cfg2", "cfg3"):
+        o = syn.config_opt(name)
+        lo, hi = np.asarray(o.ranges[:3], np.float32) * 0.9, np.asarray(o.ranges[3:], np.float32) * 0.9
+        pts = torch.tensor(np.stack([lo, hi]))
+        a = qr.get_hyperparameters(o, pts[None])
+        b = syn.grid_hyperparameters(o, lo, hi)
+        for k in ("ranges", "scaled_vsize", "scaled_vdim", "radius_limit2"):
+            assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])), (name, k)
+
+
+def test_knn_oracle_properties(tiny_scene):
+    """Size-independent properties of the reference's layered query (documented quirks)."""
+    opt, tables, cam = tiny_scene
+    raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, 300, seed=6))
+    (pidx, _, loc_w, _, ray_mask, _, _), ex = qr.query_points(opt, tables["xyz"][None], raydir, cam["campos"], cam["camrotc2w"],
+                                                              cam["near"], cam["far"])
+    xyz = tables["xyz"].numpy()
+    p = pidx[0].numpy()
+    valid = p >= 0
+    d = np.linalg.norm(xyz[np.clip(p, 0, None)] - loc_w[0].numpy()[..., None, :], axis=-1)
+    assert (d[valid] <= float(ex["hp"]["radius_limit"]) * (1 + 1e-6)).all()          # radius limit respected
+    # filled slots are a prefix (first K accepted fill slots in arrival order)
+    assert (np.diff(valid.astype(np.int8), axis=-1) <= 0).all()
+    # no duplicate neighbours within a sample
+    srt = np.sort(np.where(valid, p, -np.arange(1, p.shape[-1] + 1)), axis=-1)
+    assert (np.diff(srt, axis=-1) != 0).all()
+    # the slot-0 voxel's points are never returned (fill_occ2pnts `voxel_idx > 0`)
+    g = ex["grid"]
+    c = syn.voxel_coords(xyz, g["shift"], ex["hp"]["scaled_vsize"])
+    dims = ex["hp"]["scaled_vdim"]
+    inside = np.all((c >= 0) & (c < np.asarray(dims)[None, :]), axis=1)
+    lin = np.where(inside, (c[:, 0] * dims[1] + c[:, 1]) * dims[2] + c[:, 2], 0)
+    slot0_pts = np.nonzero(inside & (g["coor_2_occ"][lin] == 0))[0]
+    assert len(slot0_pts) >= 1 and 0 in slot0_pts
+    assert not np.isin(p[valid], slot0_pts).any()
+    assert ray_mask.sum() == pidx.shape[1]
+
+
+def _load(name):
+    path = os.path.join(GOLDEN, name)
+    if not os.path.isfile(path):
+        pytest.skip("golden fixture %s not generated" % name)
+    return np.load(path)
+
+
+def test_golden_aggregator():
+    """AggregatorPort reproduces outputs + gradients recorded from the UNMODIFIED reference module."""
+    z = _load("aggregator_ref.npz")
+    opt = make_opt()
+    port = tp.AggregatorPort(opt)
+    port.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/")})
+    ins = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("in/")}
+    order = ["sampled_color", "sampled_Rw2c", "sampled_dir", "sampled_conf", "sampled_embedding", "sampled_xyz_pers", "sampled_xyz",
+             "sample_pnt_mask", "sample_loc", "sample_loc_w", "sample_ray_dirs"]
+    gk = ["sampled_color", "sampled_dir", "sampled_conf", "sampled_embedding"]
+    for k in gk:
+        ins[k].requires_grad_(True)
+    o = port(*[ins[k] for k in order], (0.004,) * 3, 0)
+    wt = torch.from_numpy(z["loss_weight"])
+    loss = (o[0] * wt).sum() + (o[3] ** 2).sum()
+    grads = torch.autograd.grad(loss, [ins[k] for k in gk] + list(port.parameters()))
+    assert rel_err(o[0], z["out/decoded"]) < 1e-6
+    assert np.array_equal(o[1].numpy(), z["out/ray_valid"])
+    assert rel_err(o[2], z["out/weight"]) < 1e-6
+    names = gk + [n for n, _ in port.named_parameters()]
+    for n, gr in zip(names, grads):
+        assert rel_err(gr, z["grad/" + n]) < 1e-5, n
+
+
+def test_golden_ray_march():
+    z = _load("ray_march_ref.npz")
+    feats = torch.from_numpy(z["in/feats"]).requires_grad_(True)
+    bg = torch.from_numpy(z["in/bg"]).requires_grad_(True)
+    o = tp.ray_march(torch.from_numpy(z["in/dist"]), torch.from_numpy(z["in/valid"]), feats, bg)
+    for i, n in enumerate(("ray_color", "point_color", "opacity", "acc_T", "blend_w", "bg_T", "bg_w")):
+        assert rel_err(o[i], z["out/" + n]) < 1e-6, n
+    loss = (o[0] * torch.from_numpy(z["w_color"])).sum() + (o[2] * torch.from_numpy(z["w_op"])).sum()
+    gf, gb = torch.autograd.grad(loss, [feats, bg])
+    assert rel_err(gf, z["grad/feats"]) < 1e-5 and rel_err(gb, z["grad/bg"]) < 1e-5
+
+
+def test_golden_querier(tiny_scene):
+    """The C port reproduces results recorded from the reference's own kernels (oracle/_ref build) on the tiny scene."""
+    z = _load("querier_ref.npz")
+    opt, tables, cam = tiny_scene
+    assert np.array_equal(tables["xyz"].numpy(), z["xyz"]), "synthetic scene generator changed: regenerate the golden files"
+    raydir = torch.from_numpy(z["raydir"])
+    (pidx, loc_pers, loc_w, dirs, ray_mask, _, ranges), ex = qr.query_points(
+        opt, tables["xyz"][None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend="port")
+    assert np.array_equal(pidx.numpy(), z["sample_pidx"])
+    assert np.array_equal(loc_w.numpy(), z["sample_loc_w"])
+    assert np.array_equal(ray_mask.numpy(), z["ray_mask"])
+    assert np.array_equal(ranges, z["ranges"])
+    assert np.array_equal(ex["grid"]["occ_numpnts"][:int(ex["grid"]["occ_idx"][0])], z["occ_numpnts"])
