@@ -1,0 +1,432 @@
+#!/usr/bin/env python
+"""bench.py - throughput of the Point-NeRF per-ray hot path on B200 (BASELINE.json metric: train rays/s fwd+bwd).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2]
+
+One "step" = one pass of the hot path over one batch of synthetic rays:
+    neighbour query (ray sampling + K-NN on the cached voxel grid) -> fused gather + PointAggregator ->
+    ray_dist -> ray_march -> colour MSE -> backward to the neural point tables, the MLP and bg_color
+    (-> one NCCL all-reduce of the flat gradient buffer when N > 1).
+Workload (N = 1 and per GPU for N > 1: weak scaling): BASELINE.json configs[1] - 1M points, 4096 rays/batch,
+80 samples/ray, K = 8, on the synthetic lego-shaped scene of pointnerf_b200/synthetic.py.
+
+Prints ONE JSON line (rank 0).  `value` = rays/s with the ray batches resident in HBM; `e2e` = the same step fed
+from pinned HOST buffers (H2D of rays/jitter/targets and D2H of the loss inside the timed region).
+`--impl reference` times the CPU oracle (the reference's algorithm restated, oracle/) on the host cores.
+"""
+import argparse
+import copy
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+METRIC = "train_rays_per_s_fwd_bwd"
+UNIT = "rays/s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d["bf16_tflops"]),
+                    bf16_tflops_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc, self.th = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.th = threading.Thread(target=self._read, daemon=True)
+        self.th.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------------------------
+def build_workload(name, rays, n_batches, seed_base, train=1):
+    """Scene + camera + a pool of ray batches (torch-CPU).  Same scene on every rank; batches differ per rank."""
+    from pointnerf_b200 import synthetic as syn
+    opt, tables = syn.make_scene(name)
+    opt = copy.copy(opt)
+    opt.is_train = train
+    C = int(opt.shading_color_channel_num)
+    batches = []
+    for b in range(n_batches):
+        cam = syn.make_camera(name, view=b % 4)
+        raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, rays, seed=seed_base + b))
+        g = torch.Generator().manual_seed(seed_base * 7919 + b)
+        uniform = torch.rand(1, rays, opt.z_depth_dim, generator=g) if train else None
+        gt = torch.rand(1, rays, C, generator=g)
+        batches.append(dict(cam=cam, raydir=raydir, uniform=uniform, gt=gt))
+    g = torch.Generator().manual_seed(5)
+    bg = torch.rand(C, generator=g)
+    return opt, tables, batches, bg
+
+
+def make_model(opt, tables, dev):
+    from pointnerf_b200.neural_points import NeuralPointsRayMarching
+    torch.manual_seed(0)
+    model = NeuralPointsRayMarching(opt, device=dev)
+    with torch.no_grad():
+        # live density head (sigma*dist ~ 0.5): transmittance decays along the ray as in a trained scene
+        model.aggregator.alpha_branch[0].bias.fill_(60.0)
+    model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                                   tables["points_conf"], Rw2c=tables["Rw2c"])
+    return model
+
+
+def to_dev(batch, dev, non_blocking=False):
+    cam = batch["cam"]
+    return dict(cam=dict(campos=cam["campos"].to(dev, non_blocking=non_blocking), camrotc2w=cam["camrotc2w"].to(dev, non_blocking=non_blocking),
+                         near=cam["near"], far=cam["far"]),
+                raydir=batch["raydir"].to(dev, non_blocking=non_blocking),
+                uniform=batch["uniform"].to(dev, non_blocking=non_blocking) if batch["uniform"] is not None else None,
+                gt=batch["gt"].to(dev, non_blocking=non_blocking))
+
+
+def pin(batch):
+    out = dict(batch)
+    for k in ("raydir", "uniform", "gt"):
+        if out[k] is not None:
+            out[k] = out[k].pin_memory()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# stage timing (CUDA events on the launching stream) -> roofline of the dominant stage
+# ---------------------------------------------------------------------------------------------------------
+class StageTimer:
+    """Wraps the C-ABI entry points with CUDA events (torch's current stream = the stream the kernels run on)."""
+    STAGES = {"pn_ray_sample": "ray_sample", "pn_knn_query": "knn_query", "pn_w2pers": "w2pers", "pn_compact_samples": "compact",
+              "pn_agg_forward": "agg_forward", "pn_agg_backward": "agg_backward", "pn_ray_dist": "ray_dist",
+              "pn_composite_forward": "composite_forward", "pn_composite_backward": "composite_backward"}
+
+    def __init__(self):
+        from pointnerf_b200 import _lib
+        self.lib = _lib.lib()
+        self.orig, self.events = {}, []
+
+    def __enter__(self):
+        for name, stage in self.STAGES.items():
+            fn = getattr(self.lib, name)
+            self.orig[name] = fn
+
+            def wrapped(*a, _fn=fn, _stage=stage):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                rc = _fn(*a)
+                e1.record()
+                self.events.append((_stage, e0, e1))
+                return rc
+            setattr(self.lib, name, wrapped)
+        return self
+
+    def __exit__(self, *exc):
+        for name, fn in self.orig.items():
+            setattr(self.lib, name, fn)
+
+    def totals_ms(self):
+        torch.cuda.synchronize()
+        tot, cnt = {}, {}
+        for stage, e0, e1 in self.events:
+            tot[stage] = tot.get(stage, 0.0) + e0.elapsed_time(e1)
+            cnt[stage] = cnt.get(stage, 0) + 1
+        return tot, cnt
+
+
+def work_counts(model, batch_dev, opt):
+    """Algorithmic work of one batch: valid samples S, valid pairs M, kept samples, candidates."""
+    nps = model.neural_points
+    with torch.no_grad():
+        raw = nps.querier.query_raw(nps.xyz.detach(), batch_dev["raydir"], batch_dev["cam"]["campos"], batch_dev["cam"]["near"],
+                                    batch_dev["cam"]["far"], uniform=batch_dev["uniform"], count_candidates=True)
+        pidx = raw["sample_pidx"]
+        M = int((pidx >= 0).sum())
+        S = int((pidx >= 0).any(-1).sum())
+        Sq = int(raw["hit_count"].sum())
+        cand = int(raw["candidates"].item())
+        rays_hit = int((raw["ray_any"] > 0).sum())
+    return dict(S=S, M=M, kept_samples=Sq, candidates=cand, rays_with_neighbours=rays_hit)
+
+
+def agg_flops(opt, S, M, backward=True):
+    F, W, C = int(opt.point_features_dim), int(opt.shading_feature_num), int(opt.shading_color_channel_num)
+    in1 = F + 2 * opt.num_feat_freqs * F + 12 * opt.dist_xyz_freq
+    in3, inc = W + 7, W + 6 * opt.num_viewdir_freqs
+    per_pair = 2 * (in1 * W + W * W + in3 * W + W * W + W)
+    per_sample = 2 * (inc * C + C * C + C * C)
+    f = per_pair * M + per_sample * S
+    return f * (3 if backward else 1)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU oracle arm (cpu_baseline / --impl reference)
+# ---------------------------------------------------------------------------------------------------------
+def cpu_oracle_steps(opt, tables, batches, bg, agg_state, rays, steps, warmup):
+    """Times the CPU oracle (oracle/pipeline_ref.py: reference querier kernels compiled for the host when
+    oracle/_ref is present, else the C port; reference torch aggregator + ray_march restated) fwd+bwd."""
+    from oracle import pipeline_ref, querier_ref
+    backend = "ref" if querier_ref.have_backend("ref") else "port"
+    C = int(opt.shading_color_channel_num)
+
+    def one(b):
+        bb = batches[b % len(batches)]
+        raydir = bb["raydir"][:, :rays].contiguous()
+        gt = bb["gt"][:, :rays]
+        uni = bb["uniform"][:, :rays].contiguous() if bb["uniform"] is not None else None
+        pipeline_ref.run(opt, tables, bb["cam"], raydir, bg, agg_state, backend=backend, uniform=uni,
+                         loss_fn=lambda o: ((o["coarse_raycolor"] - gt) ** 2).sum() / float(rays * C))
+    for w in range(warmup):
+        one(w)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        one(warmup + s)
+    dt = time.perf_counter() - t0
+    return rays * steps / dt, dt / steps, backend
+
+
+# ---------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2")
+    ap.add_argument("--rays", type=int, default=4096, help="rays per batch per GPU")
+    ap.add_argument("--cpu-rays", type=int, default=1024, help="rays per CPU-oracle step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stages", action="store_true")
+    args = ap.parse_args()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    n_pool = 8
+
+    # ------------------------------------------------------------------ reference arm: CPU oracle on rank 0
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        torch.set_num_threads(os.cpu_count() or 1)
+        opt, tables, batches, bg = build_workload(args.workload, args.rays, 4, seed_base=100)
+        from oracle import torch_port as tp
+        torch.manual_seed(0)
+        agg = tp.AggregatorPort(opt)
+        with torch.no_grad():
+            agg.alpha_branch[0].bias.fill_(60.0)
+        v, spstep, backend = cpu_oracle_steps(opt, tables, batches, bg, agg.state_dict(), args.cpu_rays, args.steps, args.warmup)
+        sample = ("%d of the %d rays of each batch per step (bounded sample), fwd+bwd, %s querier + torch aggregator/ray_march restatement"
+                  % (args.cpu_rays, args.rays, "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port"))
+        line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "%s: 1M-point neural cloud, %d rays/batch, SR=%d, K=%d, D=%d, fwd+bwd" %
+                           (args.workload, args.rays, opt.SR, opt.K, opt.z_depth_dim)},
+                "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
+                                 "sample": sample},
+                "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ our arm
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from pointnerf_b200 import _lib
+    from pointnerf_b200.ray_shard import RayShardedStep
+    peaks = load_peaks()
+
+    opt, tables, batches, bg = build_workload(args.workload, args.rays, n_pool, seed_base=100 + 1000 * rank)
+    model = make_model(opt, tables, dev)
+    bg_p = torch.nn.Parameter(bg.to(dev))
+    stepper = RayShardedStep(model, bg_p)
+    dev_batches = [to_dev(b, dev) for b in batches]
+    global_rays = args.rays * world
+
+    def step(i):
+        b = dev_batches[i % n_pool]
+        return stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for w in range(warmup):
+        step(w)
+    sync_all()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    _lib.reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(args.steps):
+        step(warmup + s)
+    e1.record()
+    sync_all()
+    launches = _lib.launch_count()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    value = global_rays * args.steps / (ms_total * 1e-3)
+
+    # ---- end to end: pinned host buffers -> H2D -> step -> D2H of the loss, every step
+    pinned = [pin(b) for b in batches]
+    h2d = sum(int(t_.numel()) * t_.element_size() for t_ in (pinned[0]["raydir"], pinned[0]["uniform"], pinned[0]["gt"]) if t_ is not None)
+    h2d += (3 + 9) * 4
+
+    def e2e_step(i):
+        b = to_dev(pinned[i % n_pool], dev, non_blocking=True)
+        loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays)
+        return float(loss.item())           # D2H read of the step's result
+
+    for w in range(2):
+        e2e_step(w)
+    sync_all()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for s in range(args.steps):
+        e2e_step(2 + s)
+    f1.record()
+    sync_all()
+    t = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = global_rays * args.steps / (float(t.item()) * 1e-3)
+
+    # ---- per-stage device time (events around each C-ABI call) and the roofline of the dominant stage
+    stages, roof, counts = None, None, None
+    if rank == 0 and not args.no_stages:
+        n_stage_steps = min(args.steps, 8)
+        cs = [work_counts(model, dev_batches[(warmup + s) % n_pool], opt) for s in range(n_stage_steps)]
+        counts = {k: float(np.mean([c[k] for c in cs])) for k in cs[0]}
+        torch.cuda.synchronize()
+        with StageTimer() as st:
+            for s in range(n_stage_steps):
+                b = dev_batches[(warmup + s) % n_pool]
+                stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, reduce=False)
+            tot, cnt = st.totals_ms()
+        stages = {k: round(v / n_stage_steps, 4) for k, v in sorted(tot.items())}
+        agg_ms = (tot.get("agg_forward", 0.0) + tot.get("agg_backward", 0.0)) / n_stage_steps
+        fl = agg_flops(opt, counts["S"], counts["M"], backward=True)
+        achieved = fl / (agg_ms * 1e-3) / 1e12 if agg_ms > 0 else 0.0
+        peak = peaks["bf16_tflops_sustained"]
+        roof = {"kernel": "aggregator MLP (pn_agg_forward + pn_agg_backward)", "bound": "tensor", "achieved": round(achieved, 3),
+                "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 5), "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (%s)" % peaks["source"],
+                "flops_per_step": fl, "ms_per_step": round(agg_ms, 4)}
+        # HBM-bound stages, reported alongside (algorithmic bytes of SURVEY.md 8(d))
+        C, SR, K, D = int(opt.shading_color_channel_num), int(opt.SR), int(opt.K), int(opt.z_depth_dim)
+        R = args.rays
+        hb = {}
+        b_knn = counts["kept_samples"] * (12 + 27 * 8) + counts["candidates"] * 16 + counts["kept_samples"] * K * 4
+        b_sample = R * 12 + R * D / 8 + counts["kept_samples"] * 16 + R
+        b_cf = R * SR * (C + 3) * 4 + R * (C + 1) * 4 + R * SR * 12
+        b_cb = R * C * 4 + 2 * R * SR * (C + 1) * 4
+        for nm, by in (("knn_query", b_knn), ("ray_sample", b_sample), ("composite_forward", b_cf), ("composite_backward", b_cb)):
+            if tot.get(nm):
+                gbs = by / (tot[nm] / n_stage_steps * 1e-3) / 1e9
+                hb[nm] = {"GB/s": round(gbs, 2), "frac_of_hbm": round(gbs / peaks["hbm_gbs"], 5), "bytes": int(by)}
+        roof["hbm_stages"] = hb
+
+    # ---- CPU baseline (rank 0, N = 1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = {k: v.detach().cpu() for k, v in model.aggregator.state_dict().items()}
+        v, spstep, backend = cpu_oracle_steps(opt, tables, batches, bg, sd, args.cpu_rays, 3, 1)
+        cpu = {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
+               "sample": "3 steps of %d rays (first %d of a %d-ray batch), fwd+bwd, %.2f s/step; querier = %s, aggregator/ray_march = torch restatement of the reference modules"
+                         % (args.cpu_rays, args.cpu_rays, args.rays, spstep,
+                            "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port")}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "%s: %d-point neural cloud (F=%d), %d rays/batch/GPU, SR=%d, K=%d, D=%d, C=%d, train jitter on, fwd+bwd"
+                                       % (args.workload, tables["xyz"].shape[0], opt.point_features_dim, args.rays, opt.SR, opt.K,
+                                          opt.z_depth_dim, opt.shading_color_channel_num),
+                           "step": "query (cached grid) + fused gather/aggregator + ray_march + colour MSE, backward to point tables + MLP + bg"
+                                   + ("; NCCL all-reduce of %.1f MB flat gradients" % (stepper.grads.nbytes / 1e6) if world > 1 else ""),
+                           "parallelism": "ray-sharded x%d, points+MLP replicated" % world,
+                           "l2": "working set (point tables 168 MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled" % n_pool,
+                           "mean_valid_samples_per_batch": counts["S"] if counts else None,
+                           "mean_valid_pairs_per_batch": counts["M"] if counts else None},
+                "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4},
+                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -28,7 +28,7 @@ def positional_encoding(x, freqs, ori=False):
     ori=True : [x | sin(all d*F+f) | cos(all d*F+f)].
     Frequencies are 2**f (no pi).
     """
-    bands = (2.0 ** torch.arange(freqs, dtype=torch.float32)).to(x.device)
+    bands = (2.0 ** torch.arange(freqs, dtype=x.dtype)).to(x.device)
     ang = (x[..., None] * bands).reshape(x.shape[:-1] + (freqs * x.shape[-1],))
     if ori:
         return torch.cat([x, torch.sin(ang), torch.cos(ang)], dim=-1)
@@ -177,14 +177,14 @@ class AggregatorPort(nn.Module):
         x = self.block3(x)                                                             # :571
 
         a = F.softplus(self.alpha_branch(x) - 1)                                       # :262-265, 605
-        a_full = torch.zeros([B * R * SR * K, 1], dtype=torch.float32)
+        a_full = torch.zeros([B * R * SR * K, 1], dtype=a.dtype)
         a_full[pmask, :] = a                                                           # :608-610
         alpha = torch.sum(a_full.view(B * R * SR, K, 1) * wc, dim=-2)[sample_valid, :]  # :613-614
-        f_full = torch.zeros([B * R * SR * K, x.shape[-1]], dtype=torch.float32)
+        f_full = torch.zeros([B * R * SR * K, x.shape[-1]], dtype=x.dtype)
         f_full[pmask, :] = x                                                           # :622-624
         feat = torch.sum(f_full.view(B * R * SR, K, -1) * wc, dim=-2)[sample_valid, :]  # :627-628
         colour = self.color_branch(torch.cat([feat, view_pe], dim=-1))                 # :635-636 (no sigmoid)
-        out = torch.zeros([B * R * SR, C1], dtype=torch.float32)
+        out = torch.zeros([B * R * SR, C1], dtype=x.dtype)
         out[sample_valid] = torch.cat([alpha, colour], dim=-1)                         # :644-646
         ret_w = (opt.sparse_loss_weight > 0) or ("conf_coefficient" in opt.zero_one_loss_items) or opt.prob != 0
         return (out.view(shape3 + (C1,)), sample_valid.view(shape3),
@@ -198,28 +198,28 @@ def ray_dist_from_samples(sample_loc, sample_valid, vsize, raydist_mode_unit=1):
     """models/neural_points_volumetric_model.py:293-301."""
     z = torch.cummax(sample_loc[..., 2], dim=-1)[0]
     d = torch.cat([z[..., 1:] - z[..., :-1],
-                   torch.full((z.shape[0], z.shape[1], 1), vsize[2])], dim=-1)
+                   torch.full((z.shape[0], z.shape[1], 1), vsize[2], dtype=z.dtype)], dim=-1)
     bad = d < 1e-8
     if raydist_mode_unit > 0:
         bad = torch.logical_or(bad, d > 2 * vsize[2])
-    bad = bad.to(torch.float32)
+    bad = bad.to(d.dtype)
     d = d * (1.0 - bad) + bad * vsize[2]
-    return d * sample_valid.float()
+    return d * sample_valid.to(d.dtype)
 
 
 def ray_march(ray_dist, ray_valid, ray_features, bg_color=None):
     """models/rendering/diff_ray_marching.py:509-555 with radiance_render (diff_render_func.py:48-50)
     and alpha_blend (:36-37).  Returns the reference's 7-tuple."""
     point_color = ray_features[..., 1:]
-    sigma = ray_features[..., 0] * ray_valid.float()
+    sigma = ray_features[..., 0] * ray_valid.to(ray_features.dtype)
     opacity = 1 - torch.exp(-sigma * ray_dist)
     T = torch.cumprod(1.0 - opacity + 1e-10, dim=-1)
     bg_T = T[:, :, [-1]]
-    T = torch.cat([torch.ones(opacity.shape[0:2] + (1,)), T[:, :, :-1]], dim=-1)
+    T = torch.cat([torch.ones(opacity.shape[0:2] + (1,), dtype=T.dtype), T[:, :, :-1]], dim=-1)
     bw = (opacity * T)[..., None]
     ray_color = torch.sum(point_color * bw, dim=-2)
     if bg_color is not None:
-        ray_color = ray_color + bg_color.float().view(bg_T.shape[0], 1, -1) * bg_T
+        ray_color = ray_color + bg_color.to(bg_T.dtype).view(bg_T.shape[0], 1, -1) * bg_T
     return ray_color, point_color, opacity, T, bw, bg_T, 1 * bg_T
 
 
@@ -228,13 +228,14 @@ def fill_invalid(ray_mask, bg_color, coarse_raycolor, coarse_is_background, coar
     """models/neural_points_volumetric_model.py:354-389 (tone map 'off')."""
     B, OR = ray_mask.shape
     idx = torch.nonzero(ray_mask)
-    is_bg = torch.ones([B, OR, 1])
+    dt = coarse_raycolor.dtype
+    is_bg = torch.ones([B, OR, 1], dtype=dt)
     is_bg[idx[..., 0], idx[..., 1], :] = coarse_is_background
-    colour = torch.ones([B, OR, coarse_raycolor.shape[-1]]) * bg_color[None, ...]
+    colour = torch.ones([B, OR, coarse_raycolor.shape[-1]], dtype=dt) * bg_color[None, ...]
     colour[idx[..., 0], idx[..., 1], :] = coarse_raycolor
-    opac = torch.zeros([B, OR, coarse_point_opacity.shape[2]])
+    opac = torch.zeros([B, OR, coarse_point_opacity.shape[2]], dtype=dt)
     opac[idx[..., 0], idx[..., 1], :] = coarse_point_opacity
-    shading = torch.ones([B, OR, queried_shading.shape[2]])
+    shading = torch.ones([B, OR, queried_shading.shape[2]], dtype=dt)
     shading[idx[..., 0], idx[..., 1], :] = queried_shading
     return dict(coarse_is_background=is_bg, coarse_mask=1 - is_bg, coarse_raycolor=colour,
                 coarse_point_opacity=opac, queried_shading=shading)

@@ -116,7 +116,7 @@ def ray_march(ray_dist, ray_valid, ray_features, render_func, blend_func, bg_col
     point_color = ray_features[..., 1:]
     ray_color, opacity, acc_T, blend_w, bg_T = _Composite.apply(feats, dist, valid, bg_color, True)
     bg_T = bg_T.view(B, R, 1)
-    return (ray_color.view(B, R, -1), point_color, opacity.view(B, R, SR), acc_T.view(B, R, SR), blend_w.view(B, R, SR, 1),
+    return (ray_color.view(B, R, feats.shape[-1] - 1), point_color, opacity.view(B, R, SR), acc_T.view(B, R, SR), blend_w.view(B, R, SR, 1),
             bg_T, 1 * bg_T)
 
 

@@ -1,0 +1,106 @@
+"""Ray-sharded data parallelism for the per-ray hot path.
+
+One process per GPU.  The neural point tables, the voxel grid (a function of ``xyz`` only, built
+redundantly per rank) and the aggregator MLP are REPLICATED; a batch of rays is split into contiguous
+slices, one per rank; the forward needs no communication; the backward ends in ONE
+``all_reduce(SUM)`` over a flat fp32 buffer holding every trainable gradient
+(``points_embeding | points_conf | points_dir | points_color | MLP parameters | bg_color``).
+
+The reference's loss is a mean over the rays of the local batch (base_rendering_model.py:543-550).
+With ray sharding every rank divides its local SUM of squared errors by the GLOBAL number of rays
+(times channels), so that the all-reduced gradient equals the single-GPU gradient on the concatenated
+batch; nothing else is exchanged.
+
+The reference itself has no working multi-GPU path (``DataParallel`` over one id,
+neural_points_volumetric_model.py:173-176; ``train_ddp.py`` does not run) - this module is new.
+It is backend-agnostic (``nccl`` on the B200s, ``gloo`` in the CPU tests of the host logic).
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_bounds(n_rays, world_size, rank):
+    """Contiguous slice [lo, hi) of a batch of ``n_rays`` rays owned by ``rank`` (sizes differ by at most one)."""
+    base, rem = divmod(int(n_rays), int(world_size))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class FlatGrads:
+    """One contiguous fp32 buffer that aliases the ``.grad`` of every given parameter.
+
+    ``all_reduce()`` is then a single collective; parameters keep reading their own gradient views, so the
+    optimiser step needs no unflatten copy.  Parameter order is the caller's (it must be the same on every rank).
+    """
+
+    def __init__(self, params):
+        self.params = [p for p in params if p is not None and p.requires_grad]
+        if not self.params:
+            raise ValueError("FlatGrads: no trainable parameters")
+        dev = self.params[0].device
+        sizes = [p.numel() for p in self.params]
+        self.flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+        self.views, off = [], 0
+        for p, n in zip(self.params, sizes):
+            v = self.flat[off:off + n].view_as(p)
+            p.grad = v
+            self.views.append(v)
+            off += n
+
+    def zero(self):
+        self.flat.zero_()
+        for p, v in zip(self.params, self.views):  # autograd may have replaced .grad; re-alias
+            p.grad = v
+
+    def gather_from_params(self):
+        """Copies gradients that autograd allocated outside the flat buffer back into it (no-op when aliased)."""
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                v.zero_()
+            elif p.grad.data_ptr() != v.data_ptr():
+                v.copy_(p.grad)
+                p.grad = v
+
+    def all_reduce(self, group=None):
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+
+    @property
+    def nbytes(self):
+        return self.flat.numel() * 4
+
+
+class RayShardedStep:
+    """Forward + loss + backward (+ gradient all-reduce) of one batch of rays on this rank's shard.
+
+    model:      ``NeuralPointsRayMarching`` (replicated)
+    bg_color:   ``nn.Parameter`` [C] or a plain tensor
+    The loss is the reference's colour MSE (``compute_losses`` with ``color_loss_items=['coarse_raycolor']``,
+    base_rendering_model.py:533-606) normalised by the GLOBAL ray count.
+    """
+
+    def __init__(self, model, bg_color, group=None):
+        self.model, self.bg, self.group = model, bg_color, group
+        nps = model.neural_points
+        params = [nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color]
+        params += list(model.aggregator.parameters())
+        if isinstance(bg_color, torch.nn.Parameter):
+            params.append(bg_color)
+        self.grads = FlatGrads(params)
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+    def __call__(self, cam, raydir, gt, uniform=None, global_rays=None, reduce=True):
+        """cam: dict(campos [1,3], camrotc2w [1,3,3], near, far); raydir [1,R_local,3]; gt [1,R_local,C].
+        Returns (loss_local_sum / (global_rays*C)) as a 0-d tensor (the all-reduced SUM over ranks is the batch MSE)."""
+        R_local = raydir.shape[1]
+        global_rays = int(global_rays if global_rays is not None else R_local * self.world)
+        self.grads.zero()
+        out = self.model(cam["campos"], raydir, bg_color=self.bg, camrotc2w=cam["camrotc2w"], near=cam["near"], far=cam["far"],
+                         uniform=uniform)
+        diff = out["coarse_raycolor"] - gt
+        loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
+        loss.backward()
+        self.grads.gather_from_params()
+        if reduce:
+            self.grads.all_reduce(self.group)
+        return loss.detach()

@@ -14,8 +14,14 @@ def rel_err(got, want):
     return float((got - want).abs().max() / want.abs().max().clamp_min(1e-30))
 
 
-def assert_close(got, want, name, tol=RTOL):
+def assert_close(got, want, name, tol=RTOL, want64=None):
+    """``want`` = the reference evaluated in fp32 on the CPU.  ``want64`` (optional) = the same reference code on the
+    same fp32 inputs evaluated in fp64; it adjudicates LeakyReLU kinks (oracle/pipeline_ref.py): a pre-activation that
+    rounding puts on the other side of zero moves a gradient by a finite amount in any fp32 implementation, the
+    reference's own included, so the result must be within ``tol`` of the fp32 OR the fp64 evaluation."""
     e = rel_err(got, want)
+    if e > tol and want64 is not None:
+        e = min(e, rel_err(got, want64))
     assert e <= tol, "%s: relative error %.3g > %.1g" % (name, e, tol)
 
 

@@ -55,7 +55,7 @@ def test_early_termination_stays_within_tolerance(cuda_dev):
     R, SR, C = 64, 80, 128
     feats, dist, valid, bg = _inputs(R, SR, C, seed=7, sigma_scale=5000.0, valid_p=1.0)
     o_ref = tp.ray_march(dist, valid, feats, bg)
-    assert float(o_ref[5].max()) < 1e-8
+    assert float(o_ref[5][0, 1:].max()) < 1e-8      # ray 0 has no valid sample by construction (_inputs)
     d = cuda_dev
     o = rm.ray_march(dist.to(d), valid.to(d), feats.to(d), rm.radiance_render, rm.alpha_blend, bg.to(d))
     assert_close(o[0], o_ref[0], "ray_color (terminated rays)")
