@@ -39,6 +39,21 @@ int pn_abi_version(void);
 int64_t pn_launch_count(void);
 void pn_launch_count_reset(void);
 
+/* Arithmetic path of the aggregator MLP GEMMs (process-wide):
+ *   1 (default) tcgen05 tensor cores, 3xTF32 split products with fp32 accumulation in TMEM (fp32-class accuracy);
+ *   0           exact-fp32 SIMT GEMMs (the in-library reference the tensor-core path is validated against).
+ * Both replace the cuBLAS SGEMMs behind nn.Linear in point_aggregators.py:547,571,605,635. */
+int pn_set_mlp_path(int path);
+int pn_get_mlp_path(void);
+/* Test hooks: one GEMM through the selected path (not used by the product path).
+ *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias);  tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]
+ * Operands 16-byte aligned, leading dimensions multiples of 4.  scratch: pn_debug_gemm_tn_scratch_floats floats. */
+int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M,
+                     int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* stream);
+int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb);
+int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
+                     float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * 1. Voxel grid  (replaces claim_occ :243-303, map_coor2occ :305-340, fill_occ2pnts :342-387 and the
  *    fills/launches of build_occ_vox :546-611 of query_point_indices_worldcoords.py)

@@ -75,6 +75,11 @@ def _declare(lib):
         "pn_abi_version": (c_int, []),
         "pn_launch_count": (c_int64, []),
         "pn_launch_count_reset": (None, []),
+        "pn_set_mlp_path": (c_int, [c_int]),
+        "pn_get_mlp_path": (c_int, []),
+        "pn_debug_gemm_nt": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int64, c_int32, c_int32, P, c_int32, c_float, P]),
+        "pn_debug_gemm_tn_scratch_floats": (c_int64, [c_int64, c_int32, c_int32]),
+        "pn_debug_gemm_tn": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int32, P, c_int64, c_int32, c_int32, P, P]),
         "pn_grid_workspace_bytes": (c_int64, [c_int64, c_int64]),
         "pn_grid_build": (c_int, [P, c_int64, POINTER(GridParams), P, P, P, P, P, c_int64, P]),
         "pn_ray_sample": (c_int, [P, P, P, c_int64, c_int64, c_int32, c_int32, POINTER(GridParams), P, P, P, P, P]),

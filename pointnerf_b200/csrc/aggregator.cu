@@ -308,3 +308,21 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     return PN_OK;
 }
+
+// ---- MLP path selection and GEMM test hooks ---------------------------------------------------------------
+extern "C" int pn_set_mlp_path(int path) {
+    PN_CHECK_ARG(path == 0 || path == 1, "pn_set_mlp_path: 0 (SIMT fp32) or 1 (tcgen05 3xTF32)");
+    set_mlp_path(path);
+    return PN_OK;
+}
+extern "C" int pn_get_mlp_path(void) { return mlp_path(); }
+extern "C" int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int32_t N,
+                                int32_t Kd, const float* bias, int32_t leaky, float slope, void* stream) {
+    return gemm_nt(nt(A, lda, B, ldb, C, ldc, M, N, Kd, bias, leaky, slope), (cudaStream_t)stream);
+}
+extern "C" int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb) { return gemm_tn_scratch_floats(M, N, Kb); }
+extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
+                                float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream) {
+    GemmTN t{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb};
+    return gemm_tn(t, scratch, (cudaStream_t)stream);
+}

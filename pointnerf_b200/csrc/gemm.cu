@@ -210,7 +210,15 @@ static int64_t tn_rows_per_split(int64_t M) {
     return rps < 1024 ? 1024 : rps;
 }
 
+static int g_mlp_path = 1;   // 0 = exact-fp32 SIMT, 1 = tcgen05 3xTF32 (default)
+int mlp_path() { return g_mlp_path; }
+void set_mlp_path(int p) { g_mlp_path = p; }
+int gemm_nt_tc(const GemmNT& g, cudaStream_t st);
+int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st);
+int64_t gemm_tn_tc_scratch_floats(int64_t M, int N, int Kb);
+
 int gemm_nt(const GemmNT& g, cudaStream_t st) {
+    if (g_mlp_path == 1) return gemm_nt_tc(g, st);
     PN_CHECK_ARG(g.Kd % BK == 0 && g.lda % 4 == 0 && g.ldb % 4 == 0, "gemm_nt: operands must be padded (Kd %d lda %lld ldb %lld)",
                  g.Kd, (long long)g.lda, (long long)g.ldb);
     PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_nt: operands must be 16-byte aligned");
@@ -223,10 +231,23 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
 
 int64_t gemm_tn_scratch_floats(int64_t M, int N, int Kb) {
     int64_t splits = cdiv(M > 0 ? M : 1, tn_rows_per_split(M));
-    return splits * ((int64_t)N * Kb + N) + 64;
+    int64_t a = splits * ((int64_t)N * Kb + N) + 64, b = gemm_tn_tc_scratch_floats(M, N, Kb);
+    return a > b ? a : b;   // either path may be selected at run time
+}
+
+// second stage shared by both paths: partials are combined in split order (deterministic)
+int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st) {
+    tn_reduce_kernel<<<(unsigned)cdiv((int64_t)g.N * g.Kb, 256), 256, 0, st>>>(partial, splits, g.N, g.Kb, g.Kout, g.C, g.ldc);
+    PN_LAUNCH_CHECK("tn_reduce");
+    if (g.colsum && cpartial) {
+        colsum_final_kernel<<<(unsigned)cdiv(g.N, 128), 128, 0, st>>>(cpartial, splits, g.N, g.colsum);
+        PN_LAUNCH_CHECK("colsum_final");
+    }
+    return PN_OK;
 }
 
 int gemm_tn(const GemmTN& g, float* scratch, cudaStream_t st) {
+    if (g_mlp_path == 1) return gemm_tn_tc(g, scratch, st);
     PN_CHECK_ARG(g.lda % 4 == 0 && g.ldb % 4 == 0 && g.N % 4 == 0 && g.Kb % 4 == 0, "gemm_tn: operands must be padded");
     PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_tn: operands must be 16-byte aligned");
     int64_t rps = tn_rows_per_split(g.M);

@@ -38,6 +38,10 @@ struct GemmTN {
 int64_t gemm_tn_scratch_floats(int64_t M, int N, int Kb);
 int gemm_tn(const GemmTN& g, float* scratch, cudaStream_t st);
 
+// MLP arithmetic path (process-wide): 0 = exact-fp32 SIMT GEMMs, 1 = tcgen05 3xTF32 split products (default)
+int mlp_path();
+void set_mlp_path(int p);
+
 // dst[c*ldd + r] = src[r*lds + c] for r < rows, c < cols; dst columns rows..ldd-1 zero (weights only: small)
 int transpose_pad(const float* src, int rows, int cols, int64_t lds, float* dst, int64_t ldd, int dst_rows_padded,
                   cudaStream_t st);
