@@ -48,8 +48,14 @@ int pn_get_mlp_path(void);
 /* Test hooks: one GEMM through the selected path (not used by the product path).
  *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias);  tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]
  * Operands 16-byte aligned, leading dimensions multiples of 4.  scratch: pn_debug_gemm_tn_scratch_floats floats. */
+int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd);
+/* image_scratch (pn_debug_nt_image_bytes bytes, or NULL): when given, B is first packed into the pre-split
+ * pre-swizzled operand image the product path uses and streamed by TMA bulk copies. */
 int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M,
-                     int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* stream);
+                     int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch,
+                     void* stream);
+/* debug: device buffer (>= 64 int64) that receives clock64 phase stamps of CTA 0 of the image-path NT GEMM; NULL disables */
+int pn_debug_set_prof(void* buf);
 int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb);
 int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
                      float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream);

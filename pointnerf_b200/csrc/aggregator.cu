@@ -69,10 +69,11 @@ extern "C" int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t
 }
 
 namespace pn {
-struct FwdWs { float *W1a, *W3a, *Wc0; };
+struct FwdWs { float *W1a, *W3a, *Wc0; char *I1a, *I1b, *I3a, *I3b, *Ic0, *Ic2, *Ic4; };
 struct BwdWs {
     float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
     float *GA, *GB, *GSa, *GSb, *galpha, *PG, *tn, *apart;
+    char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
     int *cnt, *rank, *tmp, *sorted, *scan;
     int nblk_reduce;
     int64_t chunk;
@@ -85,6 +86,14 @@ static int64_t carve_fwd(const AggDims& d, void* p, int64_t bytes, FwdWs* w) {
     t.W1a = c.take<float>((int64_t)d.W * d.in1p);
     t.W3a = c.take<float>((int64_t)d.W * d.in3p);
     t.Wc0 = c.take<float>((int64_t)d.C * d.incp);
+    // operand images of the weights for the tensor-core path (gemm.cuh: pack_nt_image)
+    t.I1a = c.take<char>(nt_image_bytes(d.W, d.in1p));
+    t.I1b = c.take<char>(nt_image_bytes(d.W, d.W));
+    t.I3a = c.take<char>(nt_image_bytes(d.W, d.in3p));
+    t.I3b = c.take<char>(nt_image_bytes(d.W, d.W));
+    t.Ic0 = c.take<char>(nt_image_bytes(d.C, d.incp));
+    t.Ic2 = c.take<char>(nt_image_bytes(d.C, d.C));
+    t.Ic4 = c.take<char>(nt_image_bytes(d.C, d.C));
     if (w) *w = t;
     return c.off;
 }
@@ -99,6 +108,13 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     t.Wc0T = c.take<float>((int64_t)d.incp * d.C);
     t.Wc2T = c.take<float>((int64_t)d.C * d.C);
     t.Wc4T = c.take<float>((int64_t)d.C * d.C);
+    t.J1a = c.take<char>(nt_image_bytes(d.in1p, d.W));
+    t.J1b = c.take<char>(nt_image_bytes(d.W, d.W));
+    t.J3a = c.take<char>(nt_image_bytes(d.in3p, d.W));
+    t.J3b = c.take<char>(nt_image_bytes(d.W, d.W));
+    t.Jc0 = c.take<char>(nt_image_bytes(d.incp, d.C));
+    t.Jc2 = c.take<char>(nt_image_bytes(d.C, d.C));
+    t.Jc4 = c.take<char>(nt_image_bytes(d.C, d.C));
     int64_t wide = d.in1p > d.in3p ? d.in1p : d.in3p;
     t.GA = c.take<float>(m * wide);
     t.GB = c.take<float>(m * d.W);
@@ -133,7 +149,7 @@ static GemmNT nt(const float* A, int64_t lda, const float* B, int64_t ldb, float
                  const float* bias, int leaky, float slope) {
     GemmNT g;
     g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.Kd = Kd;
-    g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr;
+    g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr; g.Bimg = nullptr;
     return g;
 }
 #define PN_TRY(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
@@ -156,25 +172,38 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     FwdWs ws;
     carve_fwd(d, workspace, workspace_bytes, &ws);
     // padded copies of the three weights whose input width is not a multiple of 16
-    PN_TRY(copy_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1a, d.in1p, st));
-    PN_TRY(copy_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3a, d.in3p, st));
-    PN_TRY(copy_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0, d.incp, st));
+    if (mlp_path() != 1) {
+        PN_TRY(copy_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1a, d.in1p, st));
+        PN_TRY(copy_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3a, d.in3p, st));
+        PN_TRY(copy_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0, d.incp, st));
+    }
 
+    const bool tcp = mlp_path() == 1;
+    if (tcp) {
+        PN_TRY(pack_nt_image(w->block1_0_w, d.in1, 1, d.W, d.in1, d.W, d.in1p, ws.I1a, st));
+        PN_TRY(pack_nt_image(w->block1_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I1b, st));
+        PN_TRY(pack_nt_image(w->block3_0_w, d.in3, 1, d.W, d.in3, d.W, d.in3p, ws.I3a, st));
+        PN_TRY(pack_nt_image(w->block3_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I3b, st));
+        PN_TRY(pack_nt_image(w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0, st));
+        PN_TRY(pack_nt_image(w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2, st));
+        PN_TRY(pack_nt_image(w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4, st));
+    }
+    auto with_img = [&](GemmNT g, const char* img) { g.Bimg = tcp ? img : nullptr; return g; };
     agg_prep_kernel<<<(unsigned)cdiv(S * 32, 256), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
     PN_LAUNCH_CHECK("agg_prep");
-    PN_TRY(gemm_nt(nt(sv.X1, d.in1p, ws.W1a, d.in1p, sv.H1, d.W, M, d.W, d.in1p, w->block1_0_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.H1, d.W, w->block1_2_w, d.W, sv.X3, d.in3p, M, d.W, d.W, w->block1_2_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.X3, d.in3p, ws.W3a, d.in3p, sv.H3, d.W, M, d.W, d.in3p, w->block3_0_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.H3, d.W, w->block3_2_w, d.W, sv.H4, d.W, M, d.W, d.W, w->block3_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.X1, d.in1p, ws.W1a, d.in1p, sv.H1, d.W, M, d.W, d.in1p, w->block1_0_b, 1, d.slope), ws.I1a), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.H1, d.W, w->block1_2_w, d.W, sv.X3, d.in3p, M, d.W, d.W, w->block1_2_b, 1, d.slope), ws.I1b), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.X3, d.in3p, ws.W3a, d.in3p, sv.H3, d.W, M, d.W, d.in3p, w->block3_0_b, 1, d.slope), ws.I3a), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.H3, d.W, w->block3_2_w, d.W, sv.H4, d.W, M, d.W, d.W, w->block3_2_b, 1, d.slope), ws.I3b), st));
     unsigned sblocks = (unsigned)cdiv(S * 32, 256);
     if (d.W == 256)
         agg_reduce_kernel<8><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     else
         agg_reduce_kernel<4><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     PN_LAUNCH_CHECK("agg_reduce");
-    PN_TRY(gemm_nt(nt(sv.FS, d.incp, ws.Wc0, d.incp, sv.C1, d.C, S, d.C, d.incp, w->color_0_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.C1, d.C, w->color_2_w, d.C, sv.C2, d.C, S, d.C, d.C, w->color_2_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.C2, d.C, w->color_4_w, d.C, sv.C3, d.C, S, d.C, d.C, w->color_4_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.FS, d.incp, ws.Wc0, d.incp, sv.C1, d.C, S, d.C, d.incp, w->color_0_b, 1, d.slope), ws.Ic0), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.C1, d.C, w->color_2_w, d.C, sv.C2, d.C, S, d.C, d.C, w->color_2_b, 1, d.slope), ws.Ic2), st));
+    PN_TRY(gemm_nt(with_img(nt(sv.C2, d.C, w->color_4_w, d.C, sv.C3, d.C, S, d.C, d.C, w->color_4_b, 1, d.slope), ws.Ic4), st));
     agg_finish_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");
     return PN_OK;
@@ -216,13 +245,25 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     carve_bwd(d, S, M, T, workspace, workspace_bytes, &ws);
     const int pgw = d.F + 8;
     // transposed (K-contiguous over the OUTPUT index) weight copies for the data-gradient GEMMs
-    PN_TRY(transpose_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1aT, d.W, d.in1p, st));
-    PN_TRY(transpose_pad(w->block1_2_w, d.W, d.W, d.W, ws.W1bT, d.W, d.W, st));
-    PN_TRY(transpose_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3aT, d.W, d.in3p, st));
-    PN_TRY(transpose_pad(w->block3_2_w, d.W, d.W, d.W, ws.W3bT, d.W, d.W, st));
-    PN_TRY(transpose_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0T, d.C, d.incp, st));
-    PN_TRY(transpose_pad(w->color_2_w, d.C, d.C, d.C, ws.Wc2T, d.C, d.C, st));
-    PN_TRY(transpose_pad(w->color_4_w, d.C, d.C, d.C, ws.Wc4T, d.C, d.C, st));
+    const bool tcp = mlp_path() == 1;
+    if (tcp) {   // images of W^T: B[n = input column, k = output unit] = W[k, n]
+        PN_TRY(pack_nt_image(w->block1_0_w, 1, d.in1, d.in1, d.W, d.in1p, d.W, ws.J1a, st));
+        PN_TRY(pack_nt_image(w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b, st));
+        PN_TRY(pack_nt_image(w->block3_0_w, 1, d.in3, d.in3, d.W, d.in3p, d.W, ws.J3a, st));
+        PN_TRY(pack_nt_image(w->block3_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J3b, st));
+        PN_TRY(pack_nt_image(w->color_0_w, 1, d.inc, d.inc, d.C, d.incp, d.C, ws.Jc0, st));
+        PN_TRY(pack_nt_image(w->color_2_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc2, st));
+        PN_TRY(pack_nt_image(w->color_4_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc4, st));
+    } else {
+        PN_TRY(transpose_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1aT, d.W, d.in1p, st));
+        PN_TRY(transpose_pad(w->block1_2_w, d.W, d.W, d.W, ws.W1bT, d.W, d.W, st));
+        PN_TRY(transpose_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3aT, d.W, d.in3p, st));
+        PN_TRY(transpose_pad(w->block3_2_w, d.W, d.W, d.W, ws.W3bT, d.W, d.W, st));
+        PN_TRY(transpose_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0T, d.C, d.incp, st));
+        PN_TRY(transpose_pad(w->color_2_w, d.C, d.C, d.C, ws.Wc2T, d.C, d.C, st));
+        PN_TRY(transpose_pad(w->color_4_w, d.C, d.C, d.C, ws.Wc4T, d.C, d.C, st));
+    }
+    auto IMG = [&](const char* img) { return tcp ? img : (const char*)nullptr; };
 
     // ---- colour branch (S rows)
     agg_gout_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
@@ -231,6 +272,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmTN t{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GSa, d.C, ws.Wc4T, d.C, ws.GSb, d.C, S, d.C, d.C, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.Jc4);
         g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
         PN_TRY(gemm_nt(g, st));
     }
@@ -238,13 +280,16 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmTN t{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSa, d.C, S, d.C, d.C, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.Jc2);
         g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
         PN_TRY(gemm_nt(g, st));
     }
     {   // color.0: d/dFS (only the first W columns are consumed)
         GemmTN t{ws.GSa, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        PN_TRY(gemm_nt(nt(ws.GSa, d.C, ws.Wc0T, d.C, ws.GSb, d.incp, S, d.incp, d.C, nullptr, 0, d.slope), st));
+        GemmNT g = nt(ws.GSa, d.C, ws.Wc0T, d.C, ws.GSb, d.incp, S, d.incp, d.C, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.Jc0);
+        PN_TRY(gemm_nt(g, st));
     }
     // ---- K-reduction and density head
     if (d.W == 256)
@@ -261,6 +306,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmTN t{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GA, d.W, ws.W3bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.J3b);
         g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, st));  // GB = dPre3
     }
@@ -268,6 +314,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmTN t{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.J3a);
         g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, st));
     }
@@ -278,13 +325,16 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmTN t{ws.GA, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GA, d.in3p, ws.W1bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.J1b);
         g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, st));  // GB = dPre1
     }
     {   // block1.0: GA[M,in1p] = d/dX1
         GemmTN t{ws.GB, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        PN_TRY(gemm_nt(nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, d.in1p, d.W, nullptr, 0, d.slope), st));
+        GemmNT g = nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, d.in1p, d.W, nullptr, 0, d.slope);
+        g.Bimg = IMG(ws.J1a);
+        PN_TRY(gemm_nt(g, st));
     }
     agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, sv.X1, ws.GA, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_prep_bwd");
@@ -316,9 +366,15 @@ extern "C" int pn_set_mlp_path(int path) {
     return PN_OK;
 }
 extern "C" int pn_get_mlp_path(void) { return mlp_path(); }
+extern "C" int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd) { return nt_image_bytes(N, Kd); }
 extern "C" int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int32_t N,
-                                int32_t Kd, const float* bias, int32_t leaky, float slope, void* stream) {
-    return gemm_nt(nt(A, lda, B, ldb, C, ldc, M, N, Kd, bias, leaky, slope), (cudaStream_t)stream);
+                                int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream) {
+    GemmNT g = nt(A, lda, B, ldb, C, ldc, M, N, Kd, bias, leaky, slope);
+    if (image_scratch && mlp_path() == 1) {
+        PN_TRY(pack_nt_image(B, ldb, 1, N, Kd, N, Kd, (char*)image_scratch, (cudaStream_t)stream));
+        g.Bimg = (const char*)image_scratch;
+    }
+    return gemm_nt(g, (cudaStream_t)stream);
 }
 extern "C" int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb) { return gemm_tn_scratch_floats(M, N, Kb); }
 extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
@@ -326,3 +382,6 @@ extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int
     GemmTN t{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb};
     return gemm_tn(t, scratch, (cudaStream_t)stream);
 }
+namespace pn { void set_prof_buffer(long long* p); }
+/* debug: device buffer of >= 64 int64 receiving clock64 stamps of CTA 0 of the image-path NT GEMM (NULL disables) */
+extern "C" int pn_debug_set_prof(void* buf) { pn::set_prof_buffer((long long*)buf); return PN_OK; }

@@ -20,8 +20,14 @@ struct GemmNT {
     int leaky; float slope;
     const float* aux; int64_t ldaux; int aux_cols;
     const int* rowmap;
+    const char* Bimg;   // optional: pre-split, pre-swizzled operand image of B (pack_nt_image); tensor-core path only
 };
 int gemm_nt(const GemmNT& g, cudaStream_t st);
+// Operand image of a B matrix for the tensor-core NT GEMM: B[n, k] = src[n*s_n + k*s_k] for n < N, k < K, zero beyond,
+// logically padded to Np rows x Kp columns; split into TF32 hi/lo and stored tile by tile in the exact shared-memory
+// layout (128-byte swizzle) so that one TMA bulk copy per K chunk stages it.
+int64_t nt_image_bytes(int Np, int Kp);
+int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int Np, int Kp, char* img, cudaStream_t st);
 
 // Weight gradient: C[n, k] = sum_m A[m*lda + n] * B[m*ldb + k]  for n < N, k < Kb, reduced over M rows in
 // fixed-size splits; partial sums are combined in split order by a second kernel (deterministic).

@@ -43,6 +43,35 @@ __device__ __forceinline__ void split_store(char* hi_base, char* lo_base, uint32
     *reinterpret_cast<float4*>(hi_base + off) = h;
     *reinterpret_cast<float4*>(lo_base + off) = l;
 }
+// Epilogue of a 128 x BN accumulator tile.  TMEM hands every thread ONE ROW (lane = row), which would make global stores
+// 32 rows wide per instruction; the tile is therefore staged through shared memory (operand stages are free once the
+// accumulator is complete) and leaves as whole 512-byte row segments: emit(row, col, float4) with consecutive threads
+// on consecutive columns.  t in [0, 256): the eight staging warps.  stage: >= 128 * (BN + 4) floats.
+template <class Emit>
+__device__ __forceinline__ void epilogue_via_smem(uint32_t tmem_d, int BN, float* stage, int t, bool have_acc, Emit emit) {
+    const int warp = t >> 5, lane = t & 31, q = warp & 3, half = warp >> 2;
+    const int ld = BN + 4;
+    float* myrow = stage + (q * 32 + lane) * ld;
+    for (int j = half; j < (BN >> 4); j += 2) {
+        float v[16];
+        if (have_acc) {
+            tc::tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * 16), v);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<float4*>(myrow + j * 16 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+    tc::fence_before_sync();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const int c4n = BN >> 2;
+    for (int idx = t; idx < TBM * c4n; idx += 256) {
+        int row = idx / c4n, c4 = idx - row * c4n;
+        emit(row, 4 * c4, *reinterpret_cast<const float4*>(stage + row * ld + 4 * c4));
+    }
+}
 }  // namespace
 
 __global__ void __launch_bounds__(kThreads, 1) gemm_nt_tc_kernel(GemmNT g, int BN, int tmem_cols) {
@@ -260,30 +289,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int B
             tc::mbar_wait(&bars[4], 0);
             tc::fence_after_sync();
         }
-        const int q = warp & 3, half = warp >> 2;
-        const int n = i0 + q * 32 + lane;
         float* out = partial + (int64_t)blockIdx.z * g.N * g.Kb;
-        const int nchunks = BKt >> 4;
-        for (int j = half; j < nchunks; j += 2) {
-            float v[16];
-            if (nk > 0) {
-                tc::tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * 16), v);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = 0.f;
-            }
-            if (n < g.N) {
-                const int k0 = j0 + j * 16;
-                float* orow = out + (int64_t)n * g.Kb + k0;
-#pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (k0 + i < g.Kb) orow[i] = v[i];
-            }
-        }
+        epilogue_via_smem(tmem_d, BKt, reinterpret_cast<float*>(smem), t, nk > 0, [&](int row, int col, float4 v) {
+            const int n = i0 + row, k = j0 + col;
+            if (n >= g.N || k >= g.Kb) return;
+            *reinterpret_cast<float4*>(out + (int64_t)n * g.Kb + k) = v;     // Kb % 4 == 0, partial 256-byte aligned
+        });
         tc::fence_before_sync();
         // ---- bias gradient: column sums of A over this split (k tile 0 only), fixed order
         if (cpartial && blockIdx.x == 0) {
-            float4* red = reinterpret_cast<float4*>(smem);      // stage memory is free once the accumulator is complete
+            float4* red = reinterpret_cast<float4*>(smem);      // stage memory is free once the tile has left
             __syncwarp();
             asm volatile("bar.sync 1, %0;" ::"n"(kLoadThreads));
             red[t] = csum;
@@ -332,6 +347,196 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int B
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// NT with a pre-packed B image (the product path: B is always a weight matrix).
+//   warps 0-7  stage A: global fp32 -> registers (prefetched two K chunks ahead) -> split -> swizzled smem, 3 stages
+//   warp  8    one thread issues the MMAs
+//   warp  9    one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int NSA = 3, NSB = 2;
+constexpr int A_STAGE = 2 * A_BYTES;                 // 32 KB (hi | lo)
+constexpr int B_STAGE = 2 * B_BYTES;                 // 64 KB (hi | lo) at BN = 256
+constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + 1024 + 256;
+constexpr int kThreadsImg = kLoadThreads + 64;
+}  // namespace
+
+static long long* g_prof = nullptr;   // debug: per-phase clock64 stamps of CTA 0 (pn_debug_set_prof)
+void set_prof_buffer(long long* p) { g_prof = p; }
+#define PROF(i) do { if (prof && blockIdx.x == 0 && blockIdx.y == 0) prof[i] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int tmem_cols, long long* prof) {
+    extern __shared__ char smem_raw[];
+    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    char* smA = smem;
+    char* smB = smem + NSA * A_STAGE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NSA * A_STAGE + NSB * B_STAGE);
+    uint64_t *fullA = bars, *emptyA = bars + 3, *fullB = bars + 6, *emptyB = bars + 8, *done = bars + 10;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int64_t m0 = (int64_t)blockIdx.x * TBM;
+    const int n0 = blockIdx.y * BN;
+    const int nk = (g.Kd + TBK - 1) / TBK;
+    const uint32_t b_block = (uint32_t)(2 * BN * 128);
+    if (t == 0) PROF(0);
+
+    if (t == 0) {
+        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads); tc::mbar_init(&emptyA[i], 1); }
+        for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
+        tc::mbar_init(done, 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 8) tc::tmem_alloc(tmem_slot, (uint32_t)tmem_cols);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem_d = *tmem_slot;
+
+    if (warp < 8) {
+        const int c = t & 7, r0 = t >> 3;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 ra[4], rb[4], rc[4];
+        auto load = [&](int kc, float4 (&r)[4]) {
+            const int gk = kc * TBK + 4 * c;
+            const bool kok = gk < g.Kd;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int64_t m = m0 + r0 + 32 * i;
+                r[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
+            }
+        };
+        auto step = [&](int kc, float4 (&cur)[4], float4 (&pre)[4]) {
+            if (kc + 2 < nk) load(kc + 2, pre);
+            const int sa = kc % NSA;
+            tc::mbar_wait(&emptyA[sa], ((kc / NSA) & 1) ^ 1);
+            char* st = smA + sa * A_STAGE;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) split_store(st, st + A_BYTES, sw128_off(r0 + 32 * i, c), cur[i]);
+            tc::fence_proxy_async();
+            tc::mbar_arrive(&fullA[sa]);
+        };
+        if (t == 0) PROF(1);
+        load(0, ra);
+        if (nk > 1) load(1, rb);
+        for (int kc = 0; kc < nk; kc += 3) {
+            step(kc, ra, rc);
+            if (kc + 1 < nk) step(kc + 1, rb, ra);
+            if (kc + 2 < nk) step(kc + 2, rc, rb);
+        }
+        // ---- epilogue
+        if (t == 0) PROF(2);
+        tc::mbar_wait(done, 0);
+        tc::fence_after_sync();
+        if (t == 0) PROF(3);
+        const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
+                            (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0));
+        epilogue_via_smem(tmem_d, BN, reinterpret_cast<float*>(smem), t, true, [&](int row, int col, float4 v) {
+            const int64_t m = m0 + row;
+            const int n = n0 + col;
+            if (m >= g.M || n >= g.N) return;
+            float x[4] = {v.x, v.y, v.z, v.w};
+            if (vec_ok) {
+                if (g.bias) {
+                    float4 b = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                    x[0] += b.x; x[1] += b.y; x[2] += b.z; x[3] += b.w;
+                }
+                if (g.leaky) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) x[i] = x[i] > 0.f ? x[i] : g.slope * x[i];
+                }
+                if (g.aux && n < g.aux_cols) {
+                    float4 a = __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n));
+                    x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
+                    x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
+                }
+                *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (n + i >= g.N) break;
+                    float y = x[i];
+                    if (g.bias) y += __ldg(g.bias + n + i);
+                    if (g.leaky) y = y > 0.f ? y : g.slope * y;
+                    if (g.aux && n + i < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + i) > 0.f) ? 1.f : g.slope;
+                    g.C[m * g.ldc + n + i] = y;
+                }
+            }
+        });
+        tc::fence_before_sync();
+        if (t == 0) PROF(4);
+    } else if (warp == 8) {
+        if (lane == 0) {
+            const uint32_t idesc = tc::idesc_tf32(TBM, BN, 0, 0);
+            const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
+            for (int kc = 0; kc < nk; ++kc) {
+                const int sa = kc % NSA, sb = kc & 1;
+                tc::mbar_wait(&fullB[sb], (kc >> 1) & 1);
+                if (kc < 16) PROF(8 + 2 * kc);
+                tc::mbar_wait(&fullA[sa], (kc / NSA) & 1);
+                if (kc < 16) PROF(9 + 2 * kc);
+                tc::fence_after_sync();
+                const uint32_t a_hi = sA + sa * A_STAGE, a_lo = a_hi + A_BYTES;
+                const uint32_t b_hi = sB + sb * B_STAGE, b_lo = b_hi + (uint32_t)(BN * 128);
+                int ksteps = (g.Kd - kc * TBK + 7) >> 3;
+                if (ksteps > 4) ksteps = 4;
+                for (int k = 0; k < ksteps; ++k) {
+                    const uint32_t ko = 32u * k;
+                    uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
+                    uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
+                    tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
+                    tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
+                    tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
+                }
+                tc::mma_commit(&emptyA[sa]);
+                tc::mma_commit(&emptyB[sb]);
+            }
+            tc::mma_commit(done);
+        }
+        __syncwarp();
+    } else {
+        if (lane == 0) {
+            const char* src = g.Bimg + (int64_t)blockIdx.y * nk * b_block;
+            for (int kc = 0; kc < nk; ++kc) {
+                const int sb = kc & 1;
+                tc::mbar_wait(&emptyB[sb], ((kc >> 1) & 1) ^ 1);
+                tc::mbar_arrive_expect_tx(&fullB[sb], b_block);
+                tc::bulk_g2s(smB + sb * B_STAGE, src + (int64_t)kc * b_block, b_block, &fullB[sb]);
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    if (warp == 8) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc(tmem_d, (uint32_t)tmem_cols);
+    }
+    if (t == 0) PROF(5);
+}
+
+// image block (tile j, chunk kc) = [hi: BN rows x 128 B swizzled | lo: same]; one thread per (row, 16-byte chunk)
+__global__ void __launch_bounds__(256) pack_nt_image_kernel(const float* __restrict__ src, int64_t s_n, int64_t s_k, int N, int K,
+                                                            int BN, int n_tiles, int nk, char* __restrict__ img) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t total = (int64_t)n_tiles * nk * BN * 8;
+    if (idx >= total) return;
+    int c = (int)(idx & 7);
+    int64_t rest = idx >> 3;
+    int r = (int)(rest % BN);
+    rest /= BN;
+    int kc = (int)(rest % nk);
+    int j = (int)(rest / nk);
+    int n = j * BN + r;
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        int k = kc * TBK + 4 * c + e;
+        v[e] = (n < N && k < K) ? src[(int64_t)n * s_n + (int64_t)k * s_k] : 0.f;
+    }
+    char* blk = img + ((int64_t)j * nk + kc) * (2 * BN * 128);
+    split_store(blk, blk + BN * 128, sw128_off(r, c), make_float4(v[0], v[1], v[2], v[3]));
+}
+
 static int pick_bn(int N, int* n_tiles) {
     int nt = (N + TMAXN - 1) / TMAXN;
     int bn = (int)align_up(cdiv(N, nt), 16);
@@ -354,8 +559,34 @@ int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
     int n_tiles;
     int bn = pick_bn(g.N, &n_tiles);
     dim3 grid((unsigned)cdiv(g.M, TBM), (unsigned)n_tiles);
+    if (g.Bimg) {
+        static bool attr_img = false;
+        if (!attr_img) {
+            PN_CUDA(cudaFuncSetAttribute(gemm_nt_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG_SMEM));
+            attr_img = true;
+        }
+        gemm_nt_img_kernel<<<grid, kThreadsImg, IMG_SMEM, st>>>(g, bn, tmem_cols_for(bn), g_prof);
+        PN_LAUNCH_CHECK("gemm_nt_img");
+        return PN_OK;
+    }
     gemm_nt_tc_kernel<<<grid, kThreads, NT_SMEM, st>>>(g, bn, tmem_cols_for(bn));
     PN_LAUNCH_CHECK("gemm_nt_tc");
+    return PN_OK;
+}
+
+int64_t nt_image_bytes(int Np, int Kp) {
+    int n_tiles;
+    int bn = pick_bn(Np, &n_tiles);
+    int nk = (Kp + TBK - 1) / TBK;
+    return align_up((int64_t)n_tiles * nk * 2 * bn * 128, 256);
+}
+int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int Np, int Kp, char* img, cudaStream_t st) {
+    int n_tiles;
+    int bn = pick_bn(Np, &n_tiles);
+    int nk = (Kp + TBK - 1) / TBK;
+    int64_t total = (int64_t)n_tiles * nk * bn * 8;
+    pack_nt_image_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(src, s_n, s_k, N, K, bn, n_tiles, nk, img);
+    PN_LAUNCH_CHECK("pack_nt_image");
     return PN_OK;
 }
 

@@ -76,7 +76,7 @@ def test_forward_backward_matches_oracle(cuda_dev, R, SR, K, seed):
                                         ins64["sampled_embedding"], ins64["sampled_xyz_pers"], ins64["sampled_xyz"],
                                         ins64["sample_pnt_mask"], ins64["sample_loc"], ins64["sample_loc_w"],
                                         ins64["sample_ray_dirs"], (0.004,) * 3, 0), ins["sample_pnt_mask"])
-    assert float(amb.float().mean()) < 0.5
+    assert float(amb.float().mean()) < 0.8
     wt_dec = wt_dec * (~amb)[..., None]
     o_ref, g_ref = run(port, ins, torch.device("cpu"), wt_dec, wt_conf)
     o_64, g_64 = run(copy.deepcopy(port).double(), ins, torch.device("cpu"), wt_dec, wt_conf, dtype=torch.float64)

@@ -7,15 +7,16 @@ from pointnerf_b200 import _lib
 pytestmark = pytest.mark.gpu
 
 
-def _nt(A, B, bias, leaky, slope, path):
+def _nt(A, B, bias, leaky, slope, path, image=False):
     lib = _lib.lib()
     _lib.check(lib.pn_set_mlp_path(path), "pn_set_mlp_path")
     M, Kd = A.shape
     N = B.shape[0]
     C = torch.full((M, N), float("nan"), device=A.device)
+    img = torch.empty(lib.pn_debug_nt_image_bytes(N, Kd), dtype=torch.uint8, device=A.device) if image else None
     try:
         _lib.check(lib.pn_debug_gemm_nt(_lib.ptr(A), A.stride(0), _lib.ptr(B), B.stride(0), _lib.ptr(C), C.stride(0), M, N, Kd,
-                                        _lib.ptr(bias), int(leaky), float(slope), _lib.stream()), "pn_debug_gemm_nt")
+                                        _lib.ptr(bias), int(leaky), float(slope), _lib.ptr(img), _lib.stream()), "pn_debug_gemm_nt")
         torch.cuda.synchronize()
     finally:
         lib.pn_set_mlp_path(1)
@@ -52,10 +53,10 @@ def test_nt_matches_fp64(cuda_dev, M, N, Kd):
     bias = torch.randn(N, generator=g).to(cuda_dev)
     ref = A.double() @ B.double().T + bias.double()
     ref = torch.where(ref > 0, ref, 0.01 * ref)
-    for path in (1, 0):
-        C = _nt(A, B, bias, 1, 0.01, path)
+    for path, image in ((1, True), (1, False), (0, False)):
+        C = _nt(A, B, bias, 1, 0.01, path, image)
         assert not torch.isnan(C).any(), "path %d left outputs unwritten" % path
-        assert _rel(C, ref) < 5e-6, "path %d: rel err %.3g" % (path, _rel(C, ref))
+        assert _rel(C, ref) < 5e-6, "path %d image %d: rel err %.3g" % (path, image, _rel(C, ref))
     # no bias / no activation
     C = _nt(A, B, None, 0, 0.01, 1)
     assert _rel(C, A.double() @ B.double().T) < 5e-6

@@ -61,7 +61,7 @@ def test_step_matches_oracle(tiny_scene, cuda_dev, train):
     kr = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, uniform=uniform, need_grads=False, dtype=torch.float64,
                           kink_tau=kinks.TAU)["kink_rays"]
     keep = (~kr)[..., None].float()
-    assert float(keep.mean()) > 0.5
+    assert float(keep.mean()) > 0.2
     wt = wt * keep
     loss_fn = lambda o: ((o["coarse_raycolor"] * wt.to(o["coarse_raycolor"].dtype)).sum()
                          + (o["coarse_point_opacity"] ** 2 * keep.to(o["coarse_raycolor"].dtype)).sum() * 0.1)
