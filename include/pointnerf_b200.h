@@ -54,8 +54,6 @@ int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd);
 int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M,
                      int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch,
                      void* stream);
-/* debug: device buffer (>= 64 int64) that receives clock64 phase stamps of CTA 0 of the image-path NT GEMM; NULL disables */
-int pn_debug_set_prof(void* buf);
 int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb);
 int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
                      float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream);

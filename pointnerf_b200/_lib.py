@@ -77,7 +77,6 @@ def _declare(lib):
         "pn_launch_count_reset": (None, []),
         "pn_set_mlp_path": (c_int, [c_int]),
         "pn_get_mlp_path": (c_int, []),
-        "pn_debug_set_prof": (c_int, [P]),
         "pn_debug_nt_image_bytes": (c_int64, [c_int32, c_int32]),
         "pn_debug_gemm_nt": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int64, c_int32, c_int32, P, c_int32, c_float, P, P]),
         "pn_debug_gemm_tn_scratch_floats": (c_int64, [c_int64, c_int32, c_int32]),

@@ -382,6 +382,3 @@ extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int
     GemmTN t{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb};
     return gemm_tn(t, scratch, (cudaStream_t)stream);
 }
-namespace pn { void set_prof_buffer(long long* p); }
-/* debug: device buffer of >= 64 int64 receiving clock64 stamps of CTA 0 of the image-path NT GEMM (NULL disables) */
-extern "C" int pn_debug_set_prof(void* buf) { pn::set_prof_buffer((long long*)buf); return PN_OK; }

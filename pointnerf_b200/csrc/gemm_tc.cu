@@ -211,79 +211,97 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_tc_kernel(GemmNT g, int B
 // memory, i.e. both are MN-major for the tensor core: a chunk of 32 reduction rows is staged as 128-byte panels
 // (32 consecutive n or k per row), 4 reduction rows per 32-byte-base swizzle atom (tc.cuh).  grid = (k tiles, n tiles of 128, splits of m).
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int BKt, int tmem_cols, int64_t rows_per_split,
-                                                                 float* __restrict__ partial, float* __restrict__ cpartial) {
+// BKt <= 288 columns of B per CTA: above 256 the tile is issued as two MMAs per K-step (N1 = 160 and N2 = BKt - 160 columns,
+// both panel-aligned) into adjacent TMEM columns, so that A (the dPre tile) is staged ONCE for the whole weight row.
+constexpr int kTnLoad = 512;                 // staging threads of the TN kernel (16 warps) + 1 MMA warp
+constexpr int kTnThreads = kTnLoad + 32;
+__global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int BKt, int tmem_cols, int64_t rows_per_split,
+                                                                   float* __restrict__ partial, float* __restrict__ cpartial) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * STAGE_BYTES);
+    constexpr int PANEL = TBK * 128;                     // bytes of one 32-wide panel over a 32-row chunk
+    const int npan = (BKt + 31) >> 5;                    // B panels per stage
+    const int b_bytes = npan * PANEL;                    // per (hi | lo)
+    const int stage_bytes = 2 * A_BYTES + 2 * b_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * stage_bytes);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int j0 = blockIdx.x * BKt;       // first column of B (k of the weight)
     const int i0 = blockIdx.y * TBM;       // first column of A (n of the weight)
     const int64_t r_begin = (int64_t)blockIdx.z * rows_per_split;
     const int64_t r_end = r_begin + rows_per_split < g.M ? r_begin + rows_per_split : g.M;
-    const int nk = (int)((r_end - r_begin + TBK - 1) / TBK);
+    const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
 
     if (t == 0) {
-        tc::mbar_init(&bars[0], kLoadThreads);
-        tc::mbar_init(&bars[1], kLoadThreads);
+        tc::mbar_init(&bars[0], kTnLoad);
+        tc::mbar_init(&bars[1], kTnLoad);
         tc::mbar_init(&bars[2], 1);
         tc::mbar_init(&bars[3], 1);
         tc::mbar_init(&bars[4], 1);
         tc::mbar_fence_init();
     }
-    if (warp == 8) tc::tmem_alloc(tmem_slot, (uint32_t)tmem_cols);
+    if (warp == 16) tc::tmem_alloc(tmem_slot, (uint32_t)tmem_cols);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_d = *tmem_slot;
-    constexpr int PANEL = TBK * 128;       // bytes of one 32-wide panel over a 32-row chunk
 
-    if (warp < 8) {
+    if (warp < 16) {
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int ac4 = t & 31, ar0 = t >> 5;      // A: 32 float4 per row (128 columns), rows ar0 + 8 i
-        const int bc4 = t & 63, br0 = t >> 6;      // B: up to 64 float4 per row (256 columns), rows br0 + 4 i
+        const int ac4 = t & 31, ar0 = t >> 5;      // A: 32 float4 per row (128 columns), rows ar0 + 16 i
         const bool a_ok = i0 + 4 * ac4 < g.N;
-        const bool b_ok = 4 * bc4 < BKt && j0 + 4 * bc4 < g.Kb;
-        float4 ca[4], cb[8], na[4], nb4[8];
+        const int ncb = BKt >> 2;                  // float4 per B row (<= 72)
+        int brow[5], bc4[5];
+        bool bok[5];
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            int idx = t + kTnLoad * i;
+            brow[i] = idx / ncb;
+            bc4[i] = idx - brow[i] * ncb;
+            bok[i] = brow[i] < TBK && j0 + 4 * bc4[i] < g.Kb;
+        }
+        struct Regs { float4 a[2]; float4 b[5]; };
+        Regs r0, r1;
         float4 csum = z4;
-        auto load = [&](int kc, float4 (&ra)[4], float4 (&rb)[8]) {
+        auto load = [&](int kc, Regs& r) {
             const int64_t rb0 = r_begin + (int64_t)kc * TBK;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int64_t r = rb0 + ar0 + 8 * i;
-                ra[i] = (a_ok && r < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + r * g.lda + i0 + 4 * ac4)) : z4;
+            for (int i = 0; i < 2; ++i) {
+                int64_t rr = rb0 + ar0 + 16 * i;
+                r.a[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                int64_t r = rb0 + br0 + 4 * i;
-                rb[i] = (b_ok && r < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + r * g.ldb + j0 + 4 * bc4)) : z4;
+            for (int i = 0; i < 5; ++i) {
+                int64_t rr = rb0 + brow[i];
+                r.b[i] = (bok[i] && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
             }
         };
-        if (nk > 0) load(0, ca, cb);
-        for (int kc = 0; kc < nk; ++kc) {
+        // two chunks are always in flight with two register sets: a set is refilled (chunk kc + 2) as soon as it is stored
+        auto step = [&](int kc, Regs& cur) {
             const int s = kc & 1;
-            if (kc + 1 < nk) load(kc + 1, na, nb4);
             tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
-            char* st = smem + s * STAGE_BYTES;
+            char* st = smem + s * stage_bytes;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int row = ar0 + 8 * i;
-                split_store(st, st + A_BYTES, (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7), ca[i]);
-                csum.x += ca[i].x; csum.y += ca[i].y; csum.z += ca[i].z; csum.w += ca[i].w;
+            for (int i = 0; i < 2; ++i) {
+                int row = ar0 + 16 * i;
+                split_store(st, st + A_BYTES, (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7), cur.a[i]);
+                csum.x += cur.a[i].x; csum.y += cur.a[i].y; csum.z += cur.a[i].z; csum.w += cur.a[i].w;
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                int row = br0 + 4 * i;
-                split_store(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, (uint32_t)((bc4 >> 3) * PANEL) + sw128b32_off(row, bc4 & 7), cb[i]);
-            }
+            for (int i = 0; i < 5; ++i)
+                if (brow[i] < TBK)
+                    split_store(st + 2 * A_BYTES, st + 2 * A_BYTES + b_bytes, (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i], bc4[i] & 7), cur.b[i]);
             tc::fence_proxy_async();
             tc::mbar_arrive(&bars[s]);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) ca[i] = na[i];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) cb[i] = nb4[i];
+            if (kc + 2 < nk) load(kc + 2, cur);
+        };
+        if (nk > 0) load(0, r0);
+        if (nk > 1) load(1, r1);
+        for (int kc = 0; kc < nk; kc += 2) {
+            step(kc, r0);
+            if (kc + 1 < nk) step(kc + 1, r1);
         }
+      if (warp < 8) {
         // ---- epilogue: D[n, k] -> partial[split][n][k]
         if (nk > 0) {
             tc::mbar_wait(&bars[4], 0);
@@ -296,18 +314,19 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int B
             *reinterpret_cast<float4*>(out + (int64_t)n * g.Kb + k) = v;     // Kb % 4 == 0, partial 256-byte aligned
         });
         tc::fence_before_sync();
+      }
         // ---- bias gradient: column sums of A over this split (k tile 0 only), fixed order
         if (cpartial && blockIdx.x == 0) {
             float4* red = reinterpret_cast<float4*>(smem);      // stage memory is free once the tile has left
             __syncwarp();
-            asm volatile("bar.sync 1, %0;" ::"n"(kLoadThreads));
+            asm volatile("bar.sync 2, %0;" ::"n"(kTnLoad));
             red[t] = csum;
-            asm volatile("bar.sync 1, %0;" ::"n"(kLoadThreads));
+            asm volatile("bar.sync 2, %0;" ::"n"(kTnLoad));
             if (t < 32) {
                 float4 a = red[t];
 #pragma unroll
-                for (int w8 = 1; w8 < 8; ++w8) {
-                    float4 b = red[t + 32 * w8];
+                for (int w16 = 1; w16 < 16; ++w16) {
+                    float4 b = red[t + 32 * w16];
                     a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
                 }
                 int nn = i0 + 4 * t;
@@ -316,23 +335,32 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int B
         }
     } else {
       if (lane == 0) {
-        const uint32_t idesc = tc::idesc_tf32(TBM, BKt, 1, 1);
+        const int N1 = BKt > 256 ? 160 : BKt, N2 = BKt - N1;
+        const uint32_t idesc1 = tc::idesc_tf32(TBM, N1, 1, 1);
+        const uint32_t idesc2 = N2 > 0 ? tc::idesc_tf32(TBM, N2, 1, 1) : 0u;
         const uint32_t sbase = tc::smem_u32(smem);
+        const uint32_t off2 = (uint32_t)((N1 >> 5) * PANEL);      // second MMA starts at a panel boundary of B
         for (int kc = 0; kc < nk; ++kc) {
             const int s = kc & 1;
             tc::mbar_wait(&bars[s], (kc >> 1) & 1);
             tc::fence_after_sync();
-            const uint32_t a_hi = sbase + s * STAGE_BYTES, a_lo = a_hi + A_BYTES;
-            const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
+            const uint32_t a_hi = sbase + s * stage_bytes, a_lo = a_hi + A_BYTES;
+            const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + (uint32_t)b_bytes;
             int64_t rows = r_end - (r_begin + (int64_t)kc * TBK);
             int ksteps = rows >= TBK ? 4 : (int)((rows + 7) >> 3);
             for (int k = 0; k < ksteps; ++k) {
                 const uint32_t ko = 1024u * k;
                 uint64_t dah = tc::smem_desc_sw128(a_hi + ko, PANEL, 512, 1), dal = tc::smem_desc_sw128(a_lo + ko, PANEL, 512, 1);
                 uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, PANEL, 512, 1), dbl = tc::smem_desc_sw128(b_lo + ko, PANEL, 512, 1);
-                tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
-                tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
-                tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
+                tc::mma_tf32(tmem_d, dah, dbl, idesc1, (kc | k) != 0);
+                tc::mma_tf32(tmem_d, dal, dbh, idesc1, 1);
+                tc::mma_tf32(tmem_d, dah, dbh, idesc1, 1);
+                if (N2 > 0) {
+                    uint64_t dbh2 = tc::smem_desc_sw128(b_hi + off2 + ko, PANEL, 512, 1), dbl2 = tc::smem_desc_sw128(b_lo + off2 + ko, PANEL, 512, 1);
+                    tc::mma_tf32(tmem_d + (uint32_t)N1, dah, dbl2, idesc2, (kc | k) != 0);
+                    tc::mma_tf32(tmem_d + (uint32_t)N1, dal, dbh2, idesc2, 1);
+                    tc::mma_tf32(tmem_d + (uint32_t)N1, dah, dbh2, idesc2, 1);
+                }
             }
             tc::mma_commit(&bars[2 + s]);
         }
@@ -341,63 +369,69 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tn_tc_kernel(GemmTN g, int B
       __syncwarp();
     }
     __syncthreads();
-    if (warp == 8) {
+    if (warp == 16) {
         tc::fence_after_sync();
         tc::tmem_dealloc(tmem_d, (uint32_t)tmem_cols);
     }
 }
 
-
 // ---------------------------------------------------------------------------------------------------------------
-// NT with a pre-packed B image (the product path: B is always a weight matrix).
-//   warps 0-7  stage A: global fp32 -> registers (prefetched two K chunks ahead) -> split -> swizzled smem, 3 stages
-//   warp  8    one thread issues the MMAs
-//   warp  9    one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
+// NT with a pre-packed B image (the product path: B is always a weight matrix).  PERSISTENT: one CTA per SM walks the
+// output tiles; the accumulator is double-buffered in TMEM (2 x 256 columns) so that the epilogue of tile i (TMEM ->
+// registers -> per-warp shared-memory transpose -> coalesced global stores) overlaps the main loop of tile i + 1.
+//   warps 0-7    stage A: global fp32 -> registers (prefetched two K chunks ahead, across tile boundaries) -> split ->
+//                swizzled smem, 2 stages
+//   warp  8      one thread issues the MMAs
+//   warp  9      one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
+//   warps 10-13  epilogue, one TMEM lane quadrant (32 rows) each
 // ---------------------------------------------------------------------------------------------------------------
 namespace {
-constexpr int NSA = 3, NSB = 2;
+constexpr int NSA = 2, NSB = 2;
 constexpr int A_STAGE = 2 * A_BYTES;                 // 32 KB (hi | lo)
 constexpr int B_STAGE = 2 * B_BYTES;                 // 64 KB (hi | lo) at BN = 256
-constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + 1024 + 256;
-constexpr int kThreadsImg = kLoadThreads + 64;
+constexpr int SLAB_LD = 36;                          // floats per slab row (32 + 4: conflict-free float4 access)
+constexpr int SLAB_BYTES = 32 * SLAB_LD * 4;         // per epilogue warp
+constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + 4 * SLAB_BYTES + 1024 + 256;
+constexpr int kThreadsImg = kLoadThreads + 64 + 128;
 }  // namespace
 
-static long long* g_prof = nullptr;   // debug: per-phase clock64 stamps of CTA 0 (pn_debug_set_prof)
-void set_prof_buffer(long long* p) { g_prof = p; }
-#define PROF(i) do { if (prof && blockIdx.x == 0 && blockIdx.y == 0) prof[i] = clock64(); } while (0)
-
-__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int tmem_cols, long long* prof) {
+__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int n_tiles_n, int n_tiles_total) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     char* smA = smem;
     char* smB = smem + NSA * A_STAGE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NSA * A_STAGE + NSB * B_STAGE);
-    uint64_t *fullA = bars, *emptyA = bars + 3, *fullB = bars + 6, *emptyB = bars + 8, *done = bars + 10;
+    char* slabs = smB + NSB * B_STAGE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + 4 * SLAB_BYTES);
+    uint64_t *fullA = bars, *emptyA = bars + 2, *fullB = bars + 4, *emptyB = bars + 6, *accFull = bars + 8, *accEmpty = bars + 10;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int64_t m0 = (int64_t)blockIdx.x * TBM;
-    const int n0 = blockIdx.y * BN;
     const int nk = (g.Kd + TBK - 1) / TBK;
     const uint32_t b_block = (uint32_t)(2 * BN * 128);
-    if (t == 0) PROF(0);
+    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const int my_tiles = n_tiles_total > (int)blockIdx.x ? (n_tiles_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    const int total_chunks = my_tiles * nk;
 
     if (t == 0) {
         for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads); tc::mbar_init(&emptyA[i], 1); }
         for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
-        tc::mbar_init(done, 1);
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 4); }
         tc::mbar_fence_init();
     }
-    if (warp == 8) tc::tmem_alloc(tmem_slot, (uint32_t)tmem_cols);
+    if (warp == 8) tc::tmem_alloc(tmem_slot, 512u);
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    const uint32_t tmem_d = *tmem_slot;
+    const uint32_t tmem_base = *tmem_slot;
 
     if (warp < 8) {
+        // ---------------------------------------------------------------- A staging
         const int c = t & 7, r0 = t >> 3;
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 ra[4], rb[4], rc[4];
-        auto load = [&](int kc, float4 (&r)[4]) {
+        auto load = [&](int L, float4 (&r)[4]) {
+            const int it = L / nk, kc = L - it * nk;
+            const int tile = (int)blockIdx.x + it * (int)gridDim.x;
+            const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM;
             const int gk = kc * TBK + 4 * c;
             const bool kok = gk < g.Kd;
 #pragma unroll
@@ -406,112 +440,148 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                 r[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
             }
         };
-        auto step = [&](int kc, float4 (&cur)[4], float4 (&pre)[4]) {
-            if (kc + 2 < nk) load(kc + 2, pre);
-            const int sa = kc % NSA;
-            tc::mbar_wait(&emptyA[sa], ((kc / NSA) & 1) ^ 1);
+        auto step = [&](int L, float4 (&cur)[4], float4 (&pre)[4]) {
+            if (L + 2 < total_chunks) load(L + 2, pre);
+            const int sa = L % NSA;
+            tc::mbar_wait(&emptyA[sa], ((L / NSA) & 1) ^ 1);
             char* st = smA + sa * A_STAGE;
 #pragma unroll
             for (int i = 0; i < 4; ++i) split_store(st, st + A_BYTES, sw128_off(r0 + 32 * i, c), cur[i]);
             tc::fence_proxy_async();
             tc::mbar_arrive(&fullA[sa]);
         };
-        if (t == 0) PROF(1);
-        load(0, ra);
-        if (nk > 1) load(1, rb);
-        for (int kc = 0; kc < nk; kc += 3) {
-            step(kc, ra, rc);
-            if (kc + 1 < nk) step(kc + 1, rb, ra);
-            if (kc + 2 < nk) step(kc + 2, rc, rb);
+        if (total_chunks > 0) load(0, ra);
+        if (total_chunks > 1) load(1, rb);
+        for (int L = 0; L < total_chunks; L += 3) {
+            step(L, ra, rc);
+            if (L + 1 < total_chunks) step(L + 1, rb, ra);
+            if (L + 2 < total_chunks) step(L + 2, rc, rb);
         }
-        // ---- epilogue
-        if (t == 0) PROF(2);
-        tc::mbar_wait(done, 0);
-        tc::fence_after_sync();
-        if (t == 0) PROF(3);
-        const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
-                            (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0));
-        epilogue_via_smem(tmem_d, BN, reinterpret_cast<float*>(smem), t, true, [&](int row, int col, float4 v) {
-            const int64_t m = m0 + row;
-            const int n = n0 + col;
-            if (m >= g.M || n >= g.N) return;
-            float x[4] = {v.x, v.y, v.z, v.w};
-            if (vec_ok) {
-                if (g.bias) {
-                    float4 b = __ldg(reinterpret_cast<const float4*>(g.bias + n));
-                    x[0] += b.x; x[1] += b.y; x[2] += b.z; x[3] += b.w;
-                }
-                if (g.leaky) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) x[i] = x[i] > 0.f ? x[i] : g.slope * x[i];
-                }
-                if (g.aux && n < g.aux_cols) {
-                    float4 a = __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n));
-                    x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
-                    x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
-                }
-                *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    if (n + i >= g.N) break;
-                    float y = x[i];
-                    if (g.bias) y += __ldg(g.bias + n + i);
-                    if (g.leaky) y = y > 0.f ? y : g.slope * y;
-                    if (g.aux && n + i < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + i) > 0.f) ? 1.f : g.slope;
-                    g.C[m * g.ldc + n + i] = y;
-                }
-            }
-        });
-        tc::fence_before_sync();
-        if (t == 0) PROF(4);
     } else if (warp == 8) {
+        // ---------------------------------------------------------------- MMA issue
         if (lane == 0) {
             const uint32_t idesc = tc::idesc_tf32(TBM, BN, 0, 0);
             const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
-            for (int kc = 0; kc < nk; ++kc) {
-                const int sa = kc % NSA, sb = kc & 1;
-                tc::mbar_wait(&fullB[sb], (kc >> 1) & 1);
-                if (kc < 16) PROF(8 + 2 * kc);
-                tc::mbar_wait(&fullA[sa], (kc / NSA) & 1);
-                if (kc < 16) PROF(9 + 2 * kc);
+            int L = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int ab = it & 1;
+                tc::mbar_wait(&accEmpty[ab], ((it >> 1) & 1) ^ 1);
                 tc::fence_after_sync();
-                const uint32_t a_hi = sA + sa * A_STAGE, a_lo = a_hi + A_BYTES;
-                const uint32_t b_hi = sB + sb * B_STAGE, b_lo = b_hi + (uint32_t)(BN * 128);
-                int ksteps = (g.Kd - kc * TBK + 7) >> 3;
-                if (ksteps > 4) ksteps = 4;
-                for (int k = 0; k < ksteps; ++k) {
-                    const uint32_t ko = 32u * k;
-                    uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
-                    uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
-                    tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
-                    tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
-                    tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
+                const uint32_t tmem_d = tmem_base + (uint32_t)(ab * 256);
+                for (int kc = 0; kc < nk; ++kc, ++L) {
+                    const int sa = L % NSA, sb = L % NSB;
+                    tc::mbar_wait(&fullB[sb], (L / NSB) & 1);
+                    tc::mbar_wait(&fullA[sa], (L / NSA) & 1);
+                    tc::fence_after_sync();
+                    const uint32_t a_hi = sA + sa * A_STAGE, a_lo = a_hi + A_BYTES;
+                    const uint32_t b_hi = sB + sb * B_STAGE, b_lo = b_hi + (uint32_t)(BN * 128);
+                    int ksteps = (g.Kd - kc * TBK + 7) >> 3;
+                    if (ksteps > 4) ksteps = 4;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t ko = 32u * k;
+                        uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
+                        uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
+                        tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
+                        tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
+                        tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
+                    }
+                    tc::mma_commit(&emptyA[sa]);
+                    tc::mma_commit(&emptyB[sb]);
                 }
-                tc::mma_commit(&emptyA[sa]);
-                tc::mma_commit(&emptyB[sb]);
+                tc::mma_commit(&accFull[ab]);
             }
-            tc::mma_commit(done);
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ---------------------------------------------------------------- B image producer (TMA bulk copies)
+        if (lane == 0) {
+            int L = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int tile = (int)blockIdx.x + it * (int)gridDim.x;
+                const char* src = g.Bimg + (int64_t)(tile % n_tiles_n) * nk * b_block;
+                for (int kc = 0; kc < nk; ++kc, ++L) {
+                    const int sb = L % NSB;
+                    tc::mbar_wait(&emptyB[sb], ((L / NSB) & 1) ^ 1);
+                    tc::mbar_arrive_expect_tx(&fullB[sb], b_block);
+                    tc::bulk_g2s(smB + sb * B_STAGE, src + (int64_t)kc * b_block, b_block, &fullB[sb]);
+                }
+            }
         }
         __syncwarp();
     } else {
-        if (lane == 0) {
-            const char* src = g.Bimg + (int64_t)blockIdx.y * nk * b_block;
-            for (int kc = 0; kc < nk; ++kc) {
-                const int sb = kc & 1;
-                tc::mbar_wait(&emptyB[sb], ((kc >> 1) & 1) ^ 1);
-                tc::mbar_arrive_expect_tx(&fullB[sb], b_block);
-                tc::bulk_g2s(smB + sb * B_STAGE, src + (int64_t)kc * b_block, b_block, &fullB[sb]);
+        // ---------------------------------------------------------------- epilogue (warps 10..13)
+        const int q = warp & 3;                       // TMEM lane quadrant this warp may access
+        float* slab = reinterpret_cast<float*>(slabs + (warp - 10) * SLAB_BYTES);
+        const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
+                            (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
+                            (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
+        const int rsub = lane >> 3, c4 = lane & 7;
+        for (int it = 0; it < my_tiles; ++it) {
+            const int ab = it & 1;
+            const int tile = (int)blockIdx.x + it * (int)gridDim.x;
+            const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM + q * 32;
+            const int n0 = (tile % n_tiles_n) * BN;
+            tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
+            tc::fence_after_sync();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
+            const int ncol32 = (BN + 31) >> 5;
+            for (int cb = 0; cb < ncol32; ++cb) {
+                float v[32];
+                tc::tmem_ld32(taddr + (uint32_t)(cb * 32), v);
+                if (cb == ncol32 - 1) {               // accumulator fully read: hand the buffer back to the MMA warp
+                    tc::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4*>(slab + lane * SLAB_LD + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                __syncwarp();
+                const int n = n0 + cb * 32 + 4 * c4;
+                const bool ncol_ok = (cb * 32 + 4 * c4 < BN) && n < g.N;
+                float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (vec_ok && g.bias && ncol_ok) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+#pragma unroll 2
+                for (int rr = 0; rr < 32; rr += 4) {
+                    const int row = rr + rsub;
+                    const int64_t m = m0 + row;
+                    float4 x4 = *reinterpret_cast<const float4*>(slab + row * SLAB_LD + 4 * c4);
+                    if (m >= g.M || !ncol_ok) continue;
+                    float x[4] = {x4.x, x4.y, x4.z, x4.w};
+                    if (vec_ok) {
+                        x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
+                        if (g.leaky) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) x[i] = x[i] > 0.f ? x[i] : g.slope * x[i];
+                        }
+                        if (g.aux && n < g.aux_cols) {
+                            float4 a = __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n));
+                            x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
+                            x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
+                        }
+                        *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if (n + i >= g.N) break;
+                            float y = x[i];
+                            if (g.bias) y += __ldg(g.bias + n + i);
+                            if (g.leaky) y = y > 0.f ? y : g.slope * y;
+                            if (g.aux && n + i < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + i) > 0.f) ? 1.f : g.slope;
+                            g.C[m * g.ldc + n + i] = y;
+                        }
+                    }
+                }
+                __syncwarp();
             }
         }
-        __syncwarp();
     }
+    tc::fence_before_sync();
     __syncthreads();
     if (warp == 8) {
         tc::fence_after_sync();
-        tc::tmem_dealloc(tmem_d, (uint32_t)tmem_cols);
+        tc::tmem_dealloc(tmem_base, 512u);
     }
-    if (t == 0) PROF(5);
 }
 
 // image block (tile j, chunk kc) = [hi: BN rows x 128 B swizzled | lo: same]; one thread per (row, 16-byte chunk)
@@ -565,7 +635,9 @@ int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
             PN_CUDA(cudaFuncSetAttribute(gemm_nt_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG_SMEM));
             attr_img = true;
         }
-        gemm_nt_img_kernel<<<grid, kThreadsImg, IMG_SMEM, st>>>(g, bn, tmem_cols_for(bn), g_prof);
+        int total = (int)(cdiv(g.M, TBM) * n_tiles);
+        int ctas = total < kNumSMs ? total : kNumSMs;
+        gemm_nt_img_kernel<<<ctas, kThreadsImg, IMG_SMEM, st>>>(g, bn, n_tiles, total);
         PN_LAUNCH_CHECK("gemm_nt_img");
         return PN_OK;
     }
@@ -592,33 +664,45 @@ int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int 
 
 // second stage of the TN reduction (kernels in gemm.cu)
 int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st);
-int64_t tn_rows_per_split_tc(int64_t M) {
-    int64_t rps = align_up(cdiv(M > 0 ? M : 1, 128), TBK);
-    return rps < 512 ? 512 : rps;
+// one CTA per SM: k tiles x n tiles x splits <= 148, each split a contiguous slice of the reduction rows
+static void tn_plan(int64_t M, int N, int Kb, int* bkt, int* k_tiles, int* n_tiles, int* splits, int64_t* rps) {
+    if (Kb <= 288) { *bkt = (int)align_up(Kb, 16); *k_tiles = 1; }
+    else *bkt = pick_bn(Kb, k_tiles);
+    *n_tiles = (int)cdiv(N, TBM);
+    int s = kNumSMs / (*k_tiles * *n_tiles);
+    if (s < 1) s = 1;
+    int64_t r = align_up(cdiv(M > 0 ? M : 1, s), TBK);
+    if (r < 256) r = 256;
+    *rps = r;
+    *splits = (int)cdiv(M > 0 ? M : 1, r);
 }
 
 int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
     PN_CHECK_ARG(g.lda % 4 == 0 && g.ldb % 4 == 0 && g.N % 4 == 0 && g.Kb % 4 == 0, "gemm_tn_tc: operands must be padded");
     PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_tn_tc: operands must be 16-byte aligned");
-    static bool attr_set = false;
-    if (!attr_set) {
-        PN_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NT_SMEM));
-        attr_set = true;
+    int bkt, k_tiles, n_tiles, splits;
+    int64_t rps;
+    tn_plan(g.M, g.N, g.Kb, &bkt, &k_tiles, &n_tiles, &splits, &rps);
+    const int npan = (bkt + 31) / 32;
+    const int smem_bytes = 2 * (2 * A_BYTES + 2 * npan * TBK * 128) + 1024 + 256;
+    static int attr_bytes = 0;
+    if (smem_bytes > attr_bytes) {
+        PN_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        attr_bytes = smem_bytes;
     }
-    int64_t rps = tn_rows_per_split_tc(g.M);
-    int splits = (int)cdiv(g.M > 0 ? g.M : 1, rps);
     float* partial = scratch;
     float* cpartial = scratch + (int64_t)splits * g.N * g.Kb;
-    int k_tiles;
-    int bkt = pick_bn(g.Kb, &k_tiles);
-    dim3 grid((unsigned)k_tiles, (unsigned)cdiv(g.N, TBM), (unsigned)splits);
-    gemm_tn_tc_kernel<<<grid, kThreads, NT_SMEM, st>>>(g, bkt, tmem_cols_for(bkt), rps, partial, g.colsum ? cpartial : nullptr);
+    dim3 grid((unsigned)k_tiles, (unsigned)n_tiles, (unsigned)splits);
+    gemm_tn_tc_kernel<<<grid, kTnThreads, smem_bytes, st>>>(g, bkt, bkt > 256 ? 512 : tmem_cols_for(bkt), rps, partial,
+                                                         g.colsum ? cpartial : nullptr);
     PN_LAUNCH_CHECK("gemm_tn_tc");
     return tn_finish(g, partial, g.colsum ? cpartial : nullptr, splits, st);
 }
 int64_t gemm_tn_tc_scratch_floats(int64_t M, int N, int Kb) {
-    int64_t splits = cdiv(M > 0 ? M : 1, tn_rows_per_split_tc(M));
-    return splits * ((int64_t)N * Kb + N) + 64;
+    int bkt, k_tiles, n_tiles, splits;
+    int64_t rps;
+    tn_plan(M, N, Kb, &bkt, &k_tiles, &n_tiles, &splits, &rps);
+    return (int64_t)splits * ((int64_t)N * Kb + N) + 64;
 }
 
 }  // namespace pn

@@ -35,3 +35,20 @@ def canon_neighbours(pidx, xyz, loc_w):
     d2 = np.where(pidx >= 0, d2, np.inf)
     order = np.lexsort((pidx, d2), axis=-1)
     return np.take_along_axis(pidx, order, axis=-1)
+
+
+def group_linear_grads(grads):
+    """{name: grad} -> {name: grad} with every Linear's ``X.weight`` / ``X.bias`` pair merged into one ``X.[weight|bias]``
+    tensor [out, in + 1]: the bias is the weight of a constant-1 input column, so its gradient is compared on the scale of
+    the layer's gradient (a single-element bias gradient such as ``alpha_branch.0.bias`` is a sum of cancelling per-pair
+    terms, and "relative to its own value" would measure the cancellation, not the arithmetic)."""
+    out = {}
+    for n, g in grads.items():
+        if n.endswith(".weight") and n[:-7] + ".bias" in grads:
+            out[n[:-7] + ".[weight|bias]"] = torch.cat([torch.as_tensor(g).detach().cpu().double(),
+                                                        torch.as_tensor(grads[n[:-7] + ".bias"]).detach().cpu().double()[:, None]], dim=1)
+        elif n.endswith(".bias") and n[:-5] + ".weight" in grads:
+            continue
+        else:
+            out[n] = g
+    return out

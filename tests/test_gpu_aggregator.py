@@ -7,7 +7,7 @@ import torch
 from oracle import kinks, torch_port as tp
 from pointnerf_b200.aggregator import PointAggregator
 from pointnerf_b200.options import make_opt
-from _util import assert_close
+from _util import assert_close, group_linear_grads
 
 pytestmark = pytest.mark.gpu
 
@@ -88,8 +88,9 @@ def test_forward_backward_matches_oracle(cuda_dev, R, SR, K, seed):
     assert_close(o[2], o_ref[2], "weight")
     assert_close(o[3], o_ref[3], "conf_coefficient")
     names = list(GRAD_INPUTS) + [n for n, _ in port.named_parameters()]
-    for n, a, b, b64 in zip(names, gr, g_ref, g_64):
-        assert_close(a, b, "grad " + n, want64=b64)
+    ga, gb, gb64 = (group_linear_grads(dict(zip(names, x))) for x in (gr, g_ref, g_64))
+    for n in ga:
+        assert_close(ga[n], gb[n], "grad " + n, want64=gb64[n])
 
 
 def test_fused_tables_match_gathered(cuda_dev, tiny_scene):
@@ -133,8 +134,9 @@ def test_fused_tables_match_gathered(cuda_dev, tiny_scene):
     assert_close(dec, o_ref[0][0], "decoded (fused gather)")
     assert_close(w, o_ref[2][0], "weight (fused gather)")
     names = list(leaves) + [n for n, _ in port.named_parameters()]
-    for n, a, b in zip(names, grads, g_ref):
-        assert_close(a, b, "grad " + n)
+    ga, gb = group_linear_grads(dict(zip(names, grads))), group_linear_grads(dict(zip(names, g_ref)))
+    for n in ga:
+        assert_close(ga[n], gb[n], "grad " + n)
     # deterministic: the segmented reduction has a fixed order, so two runs are bit-identical
     dec2, _ = mod.forward_tables(xyz.to(d), xyz_pers.to(d), leaves["points_embeding"][0], leaves["points_color"][0],
                                  leaves["points_dir"][0], leaves["points_conf"][0, :, 0], Rw2c.to(d), pidx.to(d), loc_pers.to(d),

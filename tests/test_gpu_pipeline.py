@@ -7,7 +7,7 @@ import torch
 from oracle import kinks, pipeline_ref
 from pointnerf_b200 import synthetic as syn
 from pointnerf_b200.neural_points import NeuralPointsRayMarching
-from _util import assert_close
+from _util import assert_close, group_linear_grads
 
 pytestmark = pytest.mark.gpu
 
@@ -78,8 +78,9 @@ def test_step_matches_oracle(tiny_scene, cuda_dev, train):
             pytest.skip("device depth chain differs from the CPU chain; bit-exact query is covered by test_gpu_query")
         for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading"):
             assert_close(out[k], ref[k], "%s %s" % (tag, k), want64=ref64[k])
-        for n, gr in grads.items():
-            assert_close(gr, ref["grads"][n], "%s grad %s" % (tag, n), want64=ref64["grads"][n])
+        g_ref, g_ref64 = group_linear_grads(ref["grads"]), group_linear_grads(ref64["grads"])
+        for n, gr in group_linear_grads(grads).items():
+            assert_close(gr, g_ref[n], "%s grad %s" % (tag, n), want64=g_ref64[n])
 
 
 def test_fused_equals_seams_and_is_deterministic(tiny_scene, cuda_dev):
