@@ -387,8 +387,9 @@ def main():
         hb = {}
         b_knn = counts["kept_samples"] * (12 + 27 * 8) + counts["candidates"] * 16 + counts["kept_samples"] * K * 4
         b_sample = R * 12 + R * D / 8 + counts["kept_samples"] * 16 + R
-        b_cf = R * SR * (C + 3) * 4 + R * (C + 1) * 4 + R * SR * 12
-        b_cb = R * C * 4 + 2 * R * SR * (C + 1) * 4
+        # compact feature layout of the fused path: one [C+1] row per VALID sample + per-slot scalars (dist, valid, slot_row)
+        b_cf = counts["S"] * (C + 1) * 4 + R * SR * 9 + R * (C + 1) * 4 + R * SR * 12
+        b_cb = R * C * 4 + 2 * counts["S"] * (C + 1) * 4 + R * SR * (9 + 8)
         for nm, by in (("knn_query", b_knn), ("ray_sample", b_sample), ("composite_forward", b_cf), ("composite_backward", b_cb)):
             if tot.get(nm):
                 gbs = by / (tot[nm] / n_stage_steps * 1e-3) / 1e9
@@ -414,7 +415,7 @@ def main():
                                        % (args.workload, tables["xyz"].shape[0], opt.point_features_dim, args.rays, opt.SR, opt.K,
                                           opt.z_depth_dim, opt.shading_color_channel_num),
                            "step": "query (cached grid) + fused gather/aggregator + ray_march + colour MSE, backward to point tables + MLP + bg"
-                                   + ("; NCCL all-reduce of %.1f MB flat gradients" % (stepper.grads.nbytes / 1e6) if world > 1 else ""),
+                                   + ("; NCCL all-reduce of %.1f MB flat gradients" % (stepper.nbytes / 1e6) if world > 1 else ""),
                            "parallelism": "ray-sharded x%d, points+MLP replicated" % world,
                            "l2": "working set (point tables 168 MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled" % n_pool,
                            "mean_valid_samples_per_batch": counts["S"] if counts else None,

@@ -153,10 +153,11 @@ int pn_w2pers(const float* xyz_w, int64_t n, const float* camrot, const float* c
  *   pair_start  int32[n_slots+1]  first compact pair of each valid sample; pair_start[S] = M
  *   pair_src    int32[n_slots*K]  slot*K+k of each compact pair (first M entries used)
  *   counts      int32[2]          [0] = S, [1] = M   (the caller reads these back: one host sync)
+ *   slot_row    int32[n_slots] or NULL: inverse of sample_list (-1 for samples without neighbours)
  * workspace: pn_compact_workspace_bytes(n_slots). */
 int64_t pn_compact_workspace_bytes(int64_t n_slots);
 int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
-                       int32_t* pair_start, int32_t* pair_src, int32_t* counts, void* workspace,
+                       int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* workspace,
                        int64_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
@@ -183,6 +184,9 @@ typedef struct pn_agg_params {
     int32_t SR;
     float leaky_slope;  /* nn.LeakyReLU default 0.01                  */
     float dist_scale;   /* 1 if dist_xyz_deno == 0 else 1/(deno*|vsize|) (:524-525) */
+    int32_t compact_out; /* 0: decoded_features / grad_decoded are [n_slots, C+1] (reference layout, zero rows for
+                            invalid samples); 1: [S, C+1], row i = sample sample_list[i] (fused path, see
+                            pn_composite_forward slot_row) */
 } pn_agg_params;
 
 /* nn.Linear parameters, weight [out,in] row-major fp32 (state_dict names of the reference) */
@@ -248,13 +252,16 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
  * Feature rows whose weight cannot matter (invalid sample, or T below 1e-8: early ray termination) are
  * not read.  All per-sample outputs are still written in full.
  *   ray_features [R,SR,C+1]; ray_dist [R,SR]; ray_valid uint8[R,SR]; bg_color [C] or NULL
+ *   slot_row int32[R,SR] or NULL: COMPACT feature layout of the fused path - ray_features (and g_features) are then
+ *   [S, C+1] with the row of sample (r,s) at slot_row[r,s] (-1: the sample has no row and no density), so that the
+ *   dense, mostly empty [R,SR,C+1] tensor of the reference API is never materialised
  *   ray_color [R,C] (NULL for alpha_ray_march); opacity, acc_T, blend_w [R,SR]; bg_T [R]
  * ---------------------------------------------------------------------------------------------- */
 int pn_ray_dist(const float* sample_loc, const uint8_t* sample_valid, int64_t n_rays, int32_t SR,
                 float vsize_z, int32_t raydist_mode_unit, float* ray_dist, void* stream);
 
 int pn_composite_forward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
-                         const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
+                         const int32_t* slot_row, const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
                          float* opacity, float* acc_T, float* blend_w, float* bg_T, void* stream);
 
 /* Gradients w.r.t. ray_features [R,SR,C+1] and bg_color [C] (deterministic two-stage reduction over
@@ -262,7 +269,7 @@ int pn_composite_forward(const float* ray_features, const float* ray_dist, const
  * NULL (= zero).  workspace: pn_composite_workspace_bytes(n_rays, C). */
 int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C);
 int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
-                          const float* bg_color, const float* opacity, const float* acc_T,
+                          const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T,
                           const float* bg_T, const float* g_ray_color, const float* g_opacity,
                           const float* g_acc_T, const float* g_blend_w, const float* g_bg_T,
                           int64_t n_rays, int32_t SR, int32_t C, float* g_features, float* g_bg_color,

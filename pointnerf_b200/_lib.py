@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -28,7 +28,7 @@ class GridParams(Structure):
 class AggParams(Structure):
     _fields_ = [("F", c_int32), ("feat_freqs", c_int32), ("dist_freqs", c_int32), ("view_freqs", c_int32),
                 ("W", c_int32), ("C", c_int32), ("K", c_int32), ("dirs_per_ray", c_int32), ("SR", c_int32),
-                ("leaky_slope", c_float), ("dist_scale", c_float)]
+                ("leaky_slope", c_float), ("dist_scale", c_float), ("compact_out", c_int32)]
 
 
 WEIGHT_FIELDS = ("block1_0_w", "block1_0_b", "block1_2_w", "block1_2_b", "block3_0_w", "block3_0_b",
@@ -88,7 +88,7 @@ def _declare(lib):
                                  P, P, P, P]),
         "pn_w2pers": (c_int, [P, c_int64, P, P, P, P]),
         "pn_compact_workspace_bytes": (c_int64, [c_int64]),
-        "pn_compact_samples": (c_int, [P, c_int64, c_int32, P, P, P, P, P, c_int64, P]),
+        "pn_compact_samples": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, c_int64, P]),
         "pn_agg_saved_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64]),
         "pn_agg_workspace_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64, c_int64, c_int]),
         "pn_agg_forward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, P, c_int64, P,
@@ -96,9 +96,9 @@ def _declare(lib):
         "pn_agg_backward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, c_int64,
                                     POINTER(AggWeights), c_int, P, P, P, P, P, c_int64, P]),
         "pn_ray_dist": (c_int, [P, P, c_int64, c_int32, c_float, c_int32, P, P]),
-        "pn_composite_forward": (c_int, [P, P, P, P, c_int64, c_int32, c_int32, P, P, P, P, P, P]),
+        "pn_composite_forward": (c_int, [P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P, P, P, P]),
         "pn_composite_workspace_bytes": (c_int64, [c_int64, c_int32]),
-        "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P,
+        "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P,
                                           c_int64, P]),
     }
     for name, (res, args) in sig.items():

@@ -87,7 +87,7 @@ class _AggCall:
         self.sample_pidx, self.sample_loc_w, self.sample_loc, self.ray_dirs = sample_pidx, sample_loc_w, sample_loc, ray_dirs
         self.n_slots, self.T, self.scatter_rows, self.want_weight = n_slots, T, scatter_rows, want_weight
         self.S = self.M = 0
-        self.sample_list = self.pair_start = self.pair_src = None
+        self.sample_list = self.pair_start = self.pair_src = self.slot_row = None
 
 
 def _weights_struct(tensors):
@@ -114,18 +114,19 @@ def compact_samples(sample_pidx, n_slots, K):
     dev = sample_pidx.device
     if n_slots == 0:
         z = torch.zeros(1, dtype=torch.int32, device=dev)
-        return z, z.clone(), z.clone(), 0, 0
+        return z, z.clone(), z.clone(), 0, 0, torch.zeros(0, dtype=torch.int32, device=dev)
     sample_list = torch.empty(max(n_slots, 1), dtype=torch.int32, device=dev)
     pair_start = torch.empty(n_slots + 1, dtype=torch.int32, device=dev)
     pair_src = torch.empty(max(n_slots * K, 1), dtype=torch.int32, device=dev)
     counts = torch.empty(2, dtype=torch.int32, device=dev)
+    slot_row = torch.empty(n_slots, dtype=torch.int32, device=dev)
     ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     _lib.check(lib.pn_compact_samples(_lib.ptr(sample_pidx), n_slots, K, _lib.ptr(sample_list), _lib.ptr(pair_start),
-                                      _lib.ptr(pair_src), _lib.ptr(counts), _lib.ptr(ws), ws_bytes, _lib.stream()),
-               "pn_compact_samples")
+                                      _lib.ptr(pair_src), _lib.ptr(counts), _lib.ptr(slot_row), _lib.ptr(ws), ws_bytes,
+                                      _lib.stream()), "pn_compact_samples")
     S, M = (int(v) for v in counts.cpu().tolist())  # the single host sync of the aggregator
-    return sample_list, pair_start, pair_src, S, M
+    return sample_list, pair_start, pair_src, S, M, slot_row
 
 
 class _AggFunction(torch.autograd.Function):
@@ -135,8 +136,8 @@ class _AggFunction(torch.autograd.Function):
         p = call.params
         dev = embedding.device
         K = p.K
-        call.sample_list, call.pair_start, call.pair_src, call.S, call.M = compact_samples(call.sample_pidx, call.n_slots, K)
-        decoded = torch.empty((call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
+        call.sample_list, call.pair_start, call.pair_src, call.S, call.M, call.slot_row = compact_samples(call.sample_pidx, call.n_slots, K)
+        decoded = torch.empty((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
         weight_out = torch.empty((call.n_slots, K), dtype=torch.float32, device=dev) if call.want_weight else None
         saved_bytes = lib.pn_agg_saved_bytes(ctypes.byref(p), call.S, call.M)
         ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 0)
@@ -260,9 +261,10 @@ class PointAggregator(nn.Module):
                 self.color_branch[0].weight, self.color_branch[0].bias, self.color_branch[2].weight,
                 self.color_branch[2].bias, self.color_branch[4].weight, self.color_branch[4].bias)
 
-    def _params(self, K, SR, dirs_per_ray, vsize):
+    def _params(self, K, SR, dirs_per_ray, vsize, compact_out=False):
         o = self.opt
         p = AggParams()
+        p.compact_out = int(compact_out)
         p.F, p.feat_freqs, p.dist_freqs, p.view_freqs = int(o.point_features_dim), int(o.num_feat_freqs), int(o.dist_xyz_freq), int(o.num_viewdir_freqs)
         p.W, p.C, p.K, p.SR = int(o.shading_feature_num), int(o.shading_color_channel_num), int(K), int(SR)
         p.dirs_per_ray = int(dirs_per_ray)
@@ -281,19 +283,24 @@ class PointAggregator(nn.Module):
 
     # ------------------------------------------------------------------------------------------
     def forward_tables(self, xyz, xyz_pers, embedding, color, pdir, conf, Rw2c, sample_pidx, sample_loc, sample_loc_w,
-                       ray_dirs, vsize, dirs_per_ray=True, want_weight=False):
+                       ray_dirs, vsize, dirs_per_ray=True, want_weight=False, compact=False):
         """Fused gather + aggregate.  xyz/xyz_pers [N,3], embedding [N,F], color/pdir [N,3], conf [N];
         sample_pidx int32 [R,SR,K] (-1 empty); sample_loc / sample_loc_w [R,SR,3]; ray_dirs [R,3]
-        (``dirs_per_ray``) or [R,SR,3].  Returns decoded [R,SR,C+1], weight [R,SR,K] or None."""
+        (``dirs_per_ray``) or [R,SR,3].  Returns decoded [R,SR,C+1], weight [R,SR,K] or None.
+        ``compact=True``: returns (decoded [S,C+1] with one row per VALID sample, weight, slot_row int32 [R,SR]) -
+        the layout pn_composite_* consume directly, so the dense mostly-zero [R,SR,C+1] tensor is never written."""
         if Rw2c.dim() != 2:
             raise NotImplementedError("per-point Rw2c is outside the hot path (every shipped script uses one 3x3)")
         R, SR, K = (int(v) for v in sample_pidx.shape)
         T = int(embedding.shape[0])
-        call = _AggCall(self._params(K, SR, dirs_per_ray, vsize), xyz.detach().contiguous(), xyz_pers.detach().contiguous(),
+        call = _AggCall(self._params(K, SR, dirs_per_ray, vsize, compact), xyz.detach().contiguous(), xyz_pers.detach().contiguous(),
                         Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
                         sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
-        return decoded.view(R, SR, -1), (weight.view(R, SR, K) if want_weight else None)
+        weight = weight.view(R, SR, K) if want_weight else None
+        if compact:
+            return decoded, weight, call.slot_row.view(R, SR)
+        return decoded.view(R, SR, -1), weight
 
     def forward(self, sampled_color, sampled_Rw2c, sampled_dir, sampled_conf, sampled_embedding, sampled_xyz_pers, sampled_xyz,
                 sample_pnt_mask, sample_loc, sample_loc_w, sample_ray_dirs, vsize, grid_vox_sz):

@@ -11,7 +11,7 @@
 namespace pn {
 
 struct AggDims {
-    int F, ff, df, vf, W, C, K, SR, dirs_per_ray;
+    int F, ff, df, vf, W, C, K, SR, dirs_per_ray, compact_out;
     int in1, in1p, in3, in3p, inc, incp;  // logical / padded (to 16) input widths of block1.0, block3.0, color.0
     float slope, dist_scale;
 };
@@ -175,8 +175,8 @@ __global__ void __launch_bounds__(256) agg_finish_kernel(pn_agg_inputs in, AggDi
     if (idx >= in.S * C1) return;
     int64_t si = idx / C1;
     int c = (int)(idx - si * C1);
-    int slot = in.sample_list[si];
-    decoded[(int64_t)slot * C1 + c] = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
+    int64_t orow = d.compact_out ? si : (int64_t)in.sample_list[si];
+    decoded[orow * C1 + c] = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
 }
 
 // ------------------------------------ backward ------------------------------------------------
@@ -189,8 +189,8 @@ __global__ void __launch_bounds__(256) agg_gout_kernel(pn_agg_inputs in, AggDims
     if (idx >= in.S * C1) return;
     int64_t si = idx / C1;
     int c = (int)(idx - si * C1);
-    int slot = in.sample_list[si];
-    float gv = g_decoded[(int64_t)slot * C1 + c];
+    int64_t irow = d.compact_out ? si : (int64_t)in.sample_list[si];
+    float gv = g_decoded[irow * C1 + c];
     if (c == 0) galpha[si] = gv;
     else GC3[si * d.C + c - 1] = gv * (C3[si * d.C + c - 1] > 0.f ? 1.f : d.slope);
 }
@@ -248,11 +248,16 @@ __global__ void __launch_bounds__(256) agg_reduce_bwd_kernel(pn_agg_inputs in, A
 }
 __global__ void __launch_bounds__(256) agg_alpha_final_kernel(const float* __restrict__ partial, int nblk, int W,
                                                               float* __restrict__ g_wal, float* __restrict__ g_bal) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    // one warp per column; lane l sums partials l, l+32, ... in order, then a fixed butterfly: deterministic
+    int c = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    int lane = threadIdx.x & 31;
     if (c > W) return;
     float a = 0.f;
-    for (int b = 0; b < nblk; ++b) a += partial[(int64_t)b * (W + 1) + c];
-    if (c < W) g_wal[c] = a; else g_bal[0] = a;
+    for (int b = lane; b < nblk; b += 32) a += partial[(int64_t)b * (W + 1) + c];
+    a = warp_sum(a);
+    if (lane == 0) {
+        if (c < W) g_wal[c] = a; else g_bal[0] = a;
+    }
 }
 
 // block3 extras backward: thread per pair.  G3 [M, in3p] holds d/d(block3 input); columns W..W+6.

@@ -18,7 +18,7 @@ static int make_dims(const pn_agg_params* p, AggDims& d) {
     PN_CHECK_ARG(p, "aggregator: null params");
     d.F = p->F; d.ff = p->feat_freqs; d.df = p->dist_freqs; d.vf = p->view_freqs;
     d.W = p->W; d.C = p->C; d.K = p->K; d.SR = p->SR; d.dirs_per_ray = p->dirs_per_ray;
-    d.slope = p->leaky_slope; d.dist_scale = p->dist_scale;
+    d.slope = p->leaky_slope; d.dist_scale = p->dist_scale; d.compact_out = p->compact_out;
     PN_CHECK_ARG(d.F >= 1 && d.F <= 1024 && d.ff >= 0 && d.df >= 1 && d.df <= 16 && d.vf >= 1 && d.vf <= 16,
                  "aggregator: unsupported feature/frequency counts");
     PN_CHECK_ARG(d.W == 128 || d.W == 256, "aggregator: shading_feature_num %d unsupported (128 or 256)", d.W);
@@ -159,12 +159,12 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
                               void* stream) {
     AggDims d;
     PN_TRY(make_dims(p, d));
-    PN_CHECK_ARG(in && w && decoded && saved, "pn_agg_forward: null argument");
+    PN_CHECK_ARG(in && w && saved && (decoded || (p->compact_out && in->S == 0)), "pn_agg_forward: null argument");
     const int64_t S = in->S, M = in->M;
     PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_forward: saved buffer too small");
     PN_CHECK_ARG(workspace_bytes >= carve_fwd(d, nullptr, 0, nullptr), "pn_agg_forward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    PN_CUDA(cudaMemsetAsync(decoded, 0, in->n_slots * (int64_t)(d.C + 1) * sizeof(float), st));
+    if (!d.compact_out) PN_CUDA(cudaMemsetAsync(decoded, 0, in->n_slots * (int64_t)(d.C + 1) * sizeof(float), st));
     if (weight_out) PN_CUDA(cudaMemsetAsync(weight_out, 0, in->n_slots * (int64_t)d.K * sizeof(float), st));
     if (S <= 0 || M <= 0) return PN_OK;
     Saved sv;
@@ -226,7 +226,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
                                int64_t workspace_bytes, void* stream) {
     AggDims d;
     PN_TRY(make_dims(p, d));
-    PN_CHECK_ARG(in && w && grad_decoded && saved && gw, "pn_agg_backward: null argument");
+    PN_CHECK_ARG(in && w && saved && gw && (grad_decoded || (p->compact_out && in->S == 0)), "pn_agg_backward: null argument");
     const int64_t S = in->S, M = in->M, T = in->T;
     PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_backward: saved buffer too small");
     PN_CHECK_ARG(workspace_bytes >= carve_bwd(d, S, M, T, nullptr, 0, nullptr), "pn_agg_backward: workspace too small");
@@ -299,7 +299,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSb, ws.galpha, ws.chunk,
                                                                  ws.GA, d.W, ws.PG, pgw, ws.apart);
     PN_LAUNCH_CHECK("agg_reduce_bwd");
-    agg_alpha_final_kernel<<<(unsigned)cdiv(d.W + 1, 256), 256, 0, st>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
+    agg_alpha_final_kernel<<<(unsigned)cdiv((int64_t)(d.W + 1) * 32, 256), 256, 0, st>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
     PN_LAUNCH_CHECK("agg_alpha_final");
     // ---- block3 (M rows).  GA = dPre4 [M,W]
     {   // block3.2

@@ -28,7 +28,8 @@ __device__ __forceinline__ float warp_prod_scan_incl(float v, int lane) {
 
 template <int NC>  // channel registers per lane: C <= 32*NC
 __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restrict__ feat, const float* __restrict__ dist,
-                                                            const uint8_t* __restrict__ valid, const float* __restrict__ bg,
+                                                            const uint8_t* __restrict__ valid, const int* __restrict__ slot_row,
+                                                            const float* __restrict__ bg,
                                                             int64_t n_rays, int SR, int C, float* __restrict__ ray_color,
                                                             float* __restrict__ opacity, float* __restrict__ acc_T,
                                                             float* __restrict__ blend_w, float* __restrict__ bg_T) {
@@ -36,7 +37,6 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
     int lane = threadIdx.x & 31;
     if (ray >= n_rays) return;
     const int C1 = C + 1;
-    const float* frow = feat + ray * SR * C1;
     float acc[NC];
 #pragma unroll
     for (int i = 0; i < NC; ++i) acc[i] = 0.f;
@@ -45,8 +45,10 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
     for (int s0 = 0; s0 < SR; s0 += 32) {
         int s = s0 + lane;
         float o = 0.f, a = 1.f;
+        int64_t frow_i = -1;   // feature row of this lane's sample: dense (ray*SR+s) or compact (slot_row), -1 = no row
         if (s < SR) {
-            float sigma = valid[ray * SR + s] ? frow[(int64_t)s * C1] : 0.f;
+            frow_i = slot_row ? (int64_t)slot_row[ray * SR + s] : ray * SR + s;
+            float sigma = (valid[ray * SR + s] && frow_i >= 0) ? feat[frow_i * C1] : 0.f;
             o = __fsub_rn(1.f, expf(-(sigma * dist[ray * SR + s])));
             a = __fadd_rn(__fsub_rn(1.f, o), 1e-10f);
         }
@@ -66,7 +68,7 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
                 int j = __ffs(m) - 1;
                 m &= m - 1;
                 float wj = __shfl_sync(kFull, w, j);
-                const float* f = frow + (int64_t)(s0 + j) * C1 + 1;
+                const float* f = feat + __shfl_sync(kFull, frow_i, j) * C1 + 1;
 #pragma unroll
                 for (int i = 0; i < NC; ++i) {
                     int c = lane + 32 * i;
@@ -91,7 +93,7 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
 template <int NC>
 __global__ void __launch_bounds__(256) composite_bwd_kernel(
     const float* __restrict__ feat, const float* __restrict__ dist, const uint8_t* __restrict__ valid,
-    const float* __restrict__ bg, const float* __restrict__ opacity, const float* __restrict__ acc_T,
+    const int* __restrict__ slot_row, const float* __restrict__ bg, const float* __restrict__ opacity, const float* __restrict__ acc_T,
     const float* __restrict__ bg_T, const float* __restrict__ g_color, const float* __restrict__ g_opacity,
     const float* __restrict__ g_acc_T, const float* __restrict__ g_blend_w, const float* __restrict__ g_bg_T, int64_t n_rays,
     int SR, int C, float* g_feat) {
@@ -99,8 +101,6 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
     int lane = threadIdx.x & 31;
     if (ray >= n_rays) return;
     const int C1 = C + 1;
-    const float* frow = feat + ray * SR * C1;
-    float* grow = g_feat + ray * SR * C1;
     float gc[NC];
     float gbg = 0.f;
 #pragma unroll
@@ -113,24 +113,44 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
     float P_last = bg_T[ray];
     float G_P = (g_bg_T ? g_bg_T[ray] : 0.f) + gbg;
 
-    // pass 1
-    for (int s = 0; s < SR; ++s) {
-        float T = acc_T[ray * SR + s], o = opacity[ray * SR + s];
-        float w = o * T;
-        bool live = g_color && valid[ray * SR + s] && T >= kTermT;  // warp-uniform
-        float dot = 0.f;
-#pragma unroll
-        for (int i = 0; i < NC; ++i) {
-            int c = lane + 32 * i;
-            if (c < C) {
-                if (live) dot = fmaf(gc[i], frow[(int64_t)s * C1 + 1 + c], dot);
-                grow[(int64_t)s * C1 + 1 + c] = w * gc[i];
-            }
+    // pass 1: lanes fetch the per-sample scalars of 32 samples at once, then the warp walks the samples that own a row
+    for (int s0 = 0; s0 < SR; s0 += 32) {
+        const int sl = s0 + lane;
+        int64_t row_l = -1;
+        float T_l = 0.f, o_l = 0.f;
+        bool v_l = false;
+        if (sl < SR) {
+            const int64_t i = ray * SR + sl;
+            row_l = slot_row ? (int64_t)slot_row[i] : i;
+            T_l = acc_T[i];
+            o_l = opacity[i];
+            v_l = valid[i] != 0;
         }
-        // <g_color, f_s> is parked in the density column of this sample's gradient row; pass 2 (same warp)
-        // consumes it and overwrites the column with the density gradient
-        if (live) dot = warp_sum(dot);
-        if (lane == 0) grow[(int64_t)s * C1] = live ? dot : 0.f;
+        unsigned m = __ballot_sync(kFull, row_l >= 0);     // compact layout: samples without a row have no gradient row
+        while (m) {
+            const int j = __ffs(m) - 1;
+            m &= m - 1;
+            const int64_t row = __shfl_sync(kFull, row_l, j);
+            const float T = __shfl_sync(kFull, T_l, j), o = __shfl_sync(kFull, o_l, j);
+            const bool vj = __shfl_sync(kFull, (int)v_l, j) != 0;
+            const float* frow = feat + row * C1;
+            float* grow = g_feat + row * C1;
+            const float w = o * T;
+            const bool live = g_color && vj && T >= kTermT;  // warp-uniform
+            float dot = 0.f;
+#pragma unroll
+            for (int i = 0; i < NC; ++i) {
+                int c = lane + 32 * i;
+                if (c < C) {
+                    if (live) dot = fmaf(gc[i], frow[1 + c], dot);
+                    grow[1 + c] = w * gc[i];
+                }
+            }
+            // <g_color, f_s> is parked in the density column of this sample's gradient row; pass 2 (same warp)
+            // consumes it and overwrites the column with the density gradient
+            if (live) dot = warp_sum(dot);
+            if (lane == 0) grow[0] = live ? dot : 0.f;
+        }
     }
     __syncwarp();
     // pass 2: chunks of 32 samples from the end
@@ -141,14 +161,16 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
         float term = 0.f, o = 0.f, T = 0.f, G_w = 0.f, d = 0.f, sigma = 0.f;
         bool ok = s < SR;
         bool v = false;
+        int64_t row = -1;
         if (ok) {
             int64_t i = ray * SR + s;
+            row = slot_row ? (int64_t)slot_row[i] : i;
             o = opacity[i];
             T = acc_T[i];
             d = dist[i];
-            v = valid[i] != 0;
-            sigma = v ? frow[(int64_t)s * C1] : 0.f;
-            G_w = (g_blend_w ? g_blend_w[i] : 0.f) + grow[(int64_t)s * C1];
+            v = valid[i] != 0 && row >= 0;
+            sigma = v ? feat[row * C1] : 0.f;
+            G_w = (g_blend_w ? g_blend_w[i] : 0.f) + (row >= 0 ? g_feat[row * C1] : 0.f);
             float G_T = (g_acc_T ? g_acc_T[i] : 0.f) + G_w * o;
             term = G_T * T;
         }
@@ -168,7 +190,7 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
             float a = __fadd_rn(__fsub_rn(1.f, o), 1e-10f);
             float G_o = (g_opacity ? g_opacity[i] : 0.f) + G_w * T - suffix / a;
             float e = expf(-(sigma * d));
-            grow[(int64_t)s * C1] = v ? G_o * e * d : 0.f;
+            if (row >= 0) g_feat[row * C1] = v ? G_o * e * d : 0.f;
         }
     }
 }
@@ -257,14 +279,14 @@ extern "C" int pn_ray_dist(const float* sample_loc, const uint8_t* sample_valid,
 }
 
 extern "C" int pn_composite_forward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
-                                    const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
+                                    const int32_t* slot_row, const float* bg_color, int64_t n_rays, int32_t SR, int32_t C, float* ray_color,
                                     float* opacity, float* acc_T, float* blend_w, float* bg_T, void* stream) {
     PN_CHECK_ARG(ray_features && ray_dist && ray_valid && opacity && acc_T && blend_w && bg_T, "pn_composite_forward: null argument");
     PN_CHECK_ARG(C >= 1 && C <= 256 && SR > 0, "pn_composite_forward: C=%d SR=%d unsupported", C, SR);
     if (n_rays <= 0) return PN_OK;
     unsigned blocks = (unsigned)cdiv(n_rays * 32, 256);
     PN_DISPATCH_NC(C, (composite_fwd_kernel<NC><<<blocks, 256, 0, (cudaStream_t)stream>>>(
-                          ray_features, ray_dist, ray_valid, bg_color, n_rays, SR, C, ray_color, opacity, acc_T, blend_w, bg_T)));
+                          ray_features, ray_dist, ray_valid, slot_row, bg_color, n_rays, SR, C, ray_color, opacity, acc_T, blend_w, bg_T)));
     PN_LAUNCH_CHECK("composite_fwd");
     return PN_OK;
 }
@@ -275,7 +297,7 @@ extern "C" int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C) {
 }
 
 extern "C" int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
-                                     const float* bg_color, const float* opacity, const float* acc_T, const float* bg_T,
+                                     const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T, const float* bg_T,
                                      const float* g_ray_color, const float* g_opacity, const float* g_acc_T,
                                      const float* g_blend_w, const float* g_bg_T, int64_t n_rays, int32_t SR, int32_t C,
                                      float* g_features, float* g_bg_color, void* workspace, int64_t workspace_bytes,
@@ -289,7 +311,7 @@ extern "C" int pn_composite_backward(const float* ray_features, const float* ray
         return PN_OK;
     }
     unsigned blocks = (unsigned)cdiv(n_rays * 32, 256);
-    PN_DISPATCH_NC(C, (composite_bwd_kernel<NC><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, bg_color, opacity, acc_T,
+    PN_DISPATCH_NC(C, (composite_bwd_kernel<NC><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, slot_row, bg_color, opacity, acc_T,
                                                                       bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w, g_bg_T,
                                                                       n_rays, SR, C, g_features)));
     PN_LAUNCH_CHECK("composite_bwd");

@@ -229,7 +229,8 @@ __global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict
                                                            const unsigned long long* __restrict__ offs,
                                                            const unsigned long long* __restrict__ total,
                                                            int* __restrict__ sample_list, int* __restrict__ pair_start,
-                                                           int* __restrict__ pair_src, int* __restrict__ counts) {
+                                                           int* __restrict__ pair_src, int* __restrict__ counts,
+                                                           int* __restrict__ slot_row) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s == 0) {
         unsigned long long t = *total;
@@ -250,6 +251,7 @@ __global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict
         sample_list[si] = (int)s;
         pair_start[si] = (int)(o & 0xffffffffu);
     }
+    if (slot_row) slot_row[s] = any ? si : -1;
 }
 
 }  // namespace pn
@@ -306,7 +308,7 @@ extern "C" int64_t pn_compact_workspace_bytes(int64_t n_slots) {
 }
 
 extern "C" int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
-                                  int32_t* pair_start, int32_t* pair_src, int32_t* counts, void* workspace,
+                                  int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* workspace,
                                   int64_t workspace_bytes, void* stream) {
     PN_CHECK_ARG(sample_pidx && sample_list && pair_start && pair_src && counts, "pn_compact_samples: null argument");
     PN_CHECK_ARG(workspace_bytes >= pn_compact_workspace_bytes(n_slots), "pn_compact_samples: workspace too small");
@@ -327,7 +329,7 @@ extern "C" int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, i
     int rc = scan_exclusive_u64(packed, offs, n_slots, total, scratch, st);
     if (rc) return rc;
     slot_scatter_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, offs, total, sample_list,
-                                                                      pair_start, pair_src, counts);
+                                                                      pair_start, pair_src, counts, slot_row);
     PN_LAUNCH_CHECK("slot_scatter");
     return PN_OK;
 }

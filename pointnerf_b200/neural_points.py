@@ -23,7 +23,7 @@ import torch.nn as nn
 from . import query as _query
 from .aggregator import PointAggregator
 from .query import lighting_fast_querier
-from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march
+from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march, ray_march_compact
 
 
 class NeuralPoints(nn.Module):
@@ -208,13 +208,12 @@ class NeuralPointsRayMarching(nn.Module):
         loc_pers = _query.w2pers(loc_w, camrotc2w[0], campos[0])
         xyz_pers = _query.w2pers(xyz.detach(), camrotc2w[0], campos[0])
         want_w = self.aggregator._want_weight()
-        decoded, weight = self.aggregator.forward_tables(
+        decoded, weight, slot_row = self.aggregator.forward_tables(
             xyz, xyz_pers, nps.points_embeding[0], nps.points_color[0], nps.points_dir[0], nps.points_conf[0, :, 0], nps.Rw2c,
-            pidx, loc_pers, loc_w, raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w)
-        ray_valid = (pidx >= 0).any(dim=-1)[None]                                 # [1,R,SR]
+            pidx, loc_pers, loc_w, raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w, compact=True)
+        ray_valid = (slot_row >= 0)[None]                                         # [1,R,SR]
         ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)
-        ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march(ray_dist, ray_valid, decoded[None], self.render_func,
-                                                                    self.blend_func, bg_color)
+        ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march_compact(ray_dist, ray_valid, decoded, slot_row, bg_color)
         out = {"coarse_raycolor": ray_color, "coarse_point_opacity": opacity, "coarse_is_background": bg_T,
                "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).to(torch.int8)[None],
                "queried_shading": torch.logical_not(torch.any(ray_valid, dim=-1, keepdims=True)).repeat(1, 1, 3).float()}

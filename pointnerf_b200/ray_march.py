@@ -45,9 +45,10 @@ def _check_funcs(render_func, blend_func):
 
 class _Composite(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, ray_features, ray_dist, ray_valid_u8, bg_color, want_color):
+    def forward(ctx, ray_features, ray_dist, ray_valid_u8, bg_color, want_color, slot_row=None):
         lib = _lib.lib()
-        R, SR, C1 = (int(v) for v in ray_features.shape)
+        R, SR = (int(v) for v in ray_dist.shape)       # ray_features: [R,SR,C+1], or [S,C+1] with slot_row (compact)
+        C1 = int(ray_features.shape[-1])
         C = C1 - 1
         dev = ray_features.device
         feats = ray_features.detach().contiguous()
@@ -60,12 +61,13 @@ class _Composite(torch.autograd.Function):
         acc_T = torch.empty((R, SR), dtype=torch.float32, device=dev)
         blend_w = torch.empty((R, SR), dtype=torch.float32, device=dev)
         bg_T = torch.empty((R,), dtype=torch.float32, device=dev)
+        feats_k = feats if feats.numel() else feats.new_zeros((1, C1))     # compact layout with no valid sample at all
         if R > 0:
-            _lib.check(lib.pn_composite_forward(_lib.ptr(feats), _lib.ptr(dist), _lib.ptr(ray_valid_u8), _lib.ptr(bg), R, SR, C,
+            _lib.check(lib.pn_composite_forward(_lib.ptr(feats_k), _lib.ptr(dist), _lib.ptr(ray_valid_u8), _lib.ptr(slot_row), _lib.ptr(bg), R, SR, C,
                                                 _lib.ptr(ray_color), _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(blend_w),
                                                 _lib.ptr(bg_T), _lib.stream()), "pn_composite_forward")
         ctx.save_for_backward(feats, dist, ray_valid_u8, bg if bg is not None else torch.empty(0, device=dev), opacity, acc_T, bg_T)
-        ctx.has_bg, ctx.want_color = bg is not None, want_color
+        ctx.has_bg, ctx.want_color, ctx.slot_row = bg is not None, want_color, slot_row
         ctx.bg_shape = tuple(bg_color.shape) if bg_color is not None else None
         if ray_color is None:
             ray_color = torch.empty(0, device=dev)
@@ -75,7 +77,8 @@ class _Composite(torch.autograd.Function):
     def backward(ctx, g_color, g_opacity, g_acc_T, g_blend_w, g_bg_T):
         lib = _lib.lib()
         feats, dist, valid, bg, opacity, acc_T, bg_T = ctx.saved_tensors
-        R, SR, C1 = (int(v) for v in feats.shape)
+        R, SR = (int(v) for v in dist.shape)
+        C1 = int(feats.shape[-1])
         C = C1 - 1
         dev = feats.device
 
@@ -87,15 +90,32 @@ class _Composite(torch.autograd.Function):
         need_bg = ctx.has_bg and ctx.needs_input_grad[3]
         g_bg = torch.empty((C,), dtype=torch.float32, device=dev) if need_bg else None
         if R == 0:
-            return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None
+            return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None, None
         ws_bytes = lib.pn_composite_workspace_bytes(R, C)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        _lib.check(lib.pn_composite_backward(_lib.ptr(feats), _lib.ptr(dist), _lib.ptr(valid), _lib.ptr(bg) if ctx.has_bg else None,
+        feats_k = feats if feats.numel() else feats.new_zeros((1, C1))
+        g_k = g_feat if g_feat.numel() else g_feat.new_zeros((1, C1))
+        _lib.check(lib.pn_composite_backward(_lib.ptr(feats_k), _lib.ptr(dist), _lib.ptr(valid), _lib.ptr(ctx.slot_row),
+                                             _lib.ptr(bg) if ctx.has_bg else None,
                                              _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(bg_T), _lib.ptr(g_color),
                                              _lib.ptr(c(g_opacity)), _lib.ptr(c(g_acc_T)), _lib.ptr(c(g_blend_w)),
-                                             _lib.ptr(c(g_bg_T)), R, SR, C, _lib.ptr(g_feat), _lib.ptr(g_bg), _lib.ptr(ws),
+                                             _lib.ptr(c(g_bg_T)), R, SR, C, _lib.ptr(g_k), _lib.ptr(g_bg), _lib.ptr(ws),
                                              ws_bytes, _lib.stream()), "pn_composite_backward")
-        return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None
+        return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None, None
+
+
+def ray_march_compact(ray_dist, ray_valid, features_compact, slot_row, bg_color=None):
+    """Fused-path variant of ``ray_march``: ``features_compact`` [S,C+1] holds one row per valid sample and
+    ``slot_row`` int32 [R,SR] maps sample (r,s) to its row (-1: none).  Same 7-tuple minus ``point_color`` (None)."""
+    B, R, SR = ray_dist.shape
+    if B != 1:
+        raise NotImplementedError("B = 1 only, like every caller of the reference")
+    valid = ray_valid.reshape(R, SR).to(torch.uint8).contiguous()
+    ray_color, opacity, acc_T, blend_w, bg_T = _Composite.apply(features_compact, ray_dist.reshape(R, SR), valid, bg_color, True,
+                                                                slot_row.reshape(R, SR).contiguous())
+    bg_T = bg_T.view(B, R, 1)
+    return (ray_color.view(B, R, features_compact.shape[-1] - 1), None, opacity.view(B, R, SR), acc_T.view(B, R, SR),
+            blend_w.view(B, R, SR, 1), bg_T, 1 * bg_T)
 
 
 def _flatten(ray_dist, ray_valid, ray_features):

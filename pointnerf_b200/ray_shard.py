@@ -2,9 +2,9 @@
 
 One process per GPU.  The neural point tables, the voxel grid (a function of ``xyz`` only, built
 redundantly per rank) and the aggregator MLP are REPLICATED; a batch of rays is split into contiguous
-slices, one per rank; the forward needs no communication; the backward ends in ONE
-``all_reduce(SUM)`` over a flat fp32 buffer holding every trainable gradient
-(``points_embeding | points_conf | points_dir | points_color | MLP parameters | bg_color``).
+slices, one per rank; the forward needs no communication; the backward ends in the gradient
+``all_reduce(SUM)``: the four per-point tables (``points_embeding | points_conf | points_dir |
+points_color``, N x 39 floats) in place, and the MLP parameters + ``bg_color`` coalesced in one flat buffer.
 
 The reference's loss is a mean over the rays of the local batch (base_rendering_model.py:543-550).
 With ray sharding every rank divides its local SUM of squared errors by the GLOBAL number of rays
@@ -77,7 +77,13 @@ class RayShardedStep:
     bg_color:   ``nn.Parameter`` [C] or a plain tensor
     The loss is the reference's colour MSE (``compute_losses`` with ``color_loss_items=['coarse_raycolor']``,
     base_rendering_model.py:533-606) normalised by the GLOBAL ray count.
+
+    Gradients: ``.grad`` is reset to None every step, so autograd adopts the buffers the backward kernels wrote (no
+    zero-fill and no accumulate pass over the N x 39 point tables).  With more than one rank the large per-point
+    tables are all-reduced in place, one collective each, and the ~341 k MLP / bg parameters travel in ONE flat buffer.
     """
+
+    BIG = 1 << 18   # parameters at least this large are reduced in place; smaller ones are coalesced
 
     def __init__(self, model, bg_color, group=None):
         self.model, self.bg, self.group = model, bg_color, group
@@ -86,21 +92,47 @@ class RayShardedStep:
         params += list(model.aggregator.parameters())
         if isinstance(bg_color, torch.nn.Parameter):
             params.append(bg_color)
-        self.grads = FlatGrads(params)
+        self.params = [p for p in params if p is not None and p.requires_grad]
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.nbytes = sum(p.numel() for p in self.params) * 4
+        self._small_flat = None
+
+    def all_reduce(self):
+        if self.world <= 1:
+            return
+        big = [p for p in self.params if p.numel() >= self.BIG]
+        small = [p for p in self.params if p.numel() < self.BIG]
+        for p in self.params:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+        handles = [dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for p in big]
+        if small:
+            flat = torch.cat([p.grad.reshape(-1) for p in small])
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+            off = 0
+            for p in small:
+                n = p.numel()
+                p.grad.copy_(flat[off:off + n].view_as(p))
+                off += n
+        for h in handles:
+            h.wait()
 
     def __call__(self, cam, raydir, gt, uniform=None, global_rays=None, reduce=True):
         """cam: dict(campos [1,3], camrotc2w [1,3,3], near, far); raydir [1,R_local,3]; gt [1,R_local,C].
         Returns (loss_local_sum / (global_rays*C)) as a 0-d tensor (the all-reduced SUM over ranks is the batch MSE)."""
         R_local = raydir.shape[1]
         global_rays = int(global_rays if global_rays is not None else R_local * self.world)
-        self.grads.zero()
+        for p in self.params:
+            p.grad = None
         out = self.model(cam["campos"], raydir, bg_color=self.bg, camrotc2w=cam["camrotc2w"], near=cam["near"], far=cam["far"],
                          uniform=uniform)
         diff = out["coarse_raycolor"] - gt
         loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
         loss.backward()
-        self.grads.gather_from_params()
         if reduce:
-            self.grads.all_reduce(self.group)
+            self.all_reduce()
         return loss.detach()
+
+    def flat_grads(self):
+        """All gradients as one vector (parameter order of the constructor); for tests and checks."""
+        return torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in self.params])
