@@ -253,6 +253,7 @@ def main():
     ap.add_argument("--cpu-rays", type=int, default=1024, help="rays per CPU-oracle step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
     args = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -301,7 +302,7 @@ def main():
     opt, tables, batches, bg = build_workload(args.workload, args.rays, n_pool, seed_base=100 + 1000 * rank)
     model = make_model(opt, tables, dev)
     bg_p = torch.nn.Parameter(bg.to(dev))
-    stepper = RayShardedStep(model, bg_p)
+    stepper = RayShardedStep(model, bg_p, sparse=not args.dense_allreduce)
     dev_batches = [to_dev(b, dev) for b in batches]
     global_rays = args.rays * world
 
@@ -415,7 +416,9 @@ def main():
                                        % (args.workload, tables["xyz"].shape[0], opt.point_features_dim, args.rays, opt.SR, opt.K,
                                           opt.z_depth_dim, opt.shading_color_channel_num),
                            "step": "query (cached grid) + fused gather/aggregator + ray_march + colour MSE, backward to point tables + MLP + bg"
-                                   + ("; NCCL all-reduce of %.1f MB flat gradients" % (stepper.nbytes / 1e6) if world > 1 else ""),
+                                   + (("; NCCL: " + ("dense all-reduce of %.1f MB gradients" % (stepper.nbytes / 1e6) if args.dense_allreduce else
+                                                 "all-gather of the touched point-table gradient rows (ids + 39 floats, rank-ordered sum) + all-reduce of the 1.4 MB MLP gradients"))
+                                      if world > 1 else ""),
                            "parallelism": "ray-sharded x%d, points+MLP replicated" % world,
                            "l2": "working set (point tables 168 MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled" % n_pool,
                            "mean_valid_samples_per_batch": counts["S"] if counts else None,

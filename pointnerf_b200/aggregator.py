@@ -297,6 +297,7 @@ class PointAggregator(nn.Module):
                         Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
                         sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
+        self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)
         weight = weight.view(R, SR, K) if want_weight else None
         if compact:
             return decoded, weight, call.slot_row.view(R, SR)

@@ -188,6 +188,14 @@ class NeuralPointsRayMarching(nn.Module):
         output["queried_shading"] = shading
         return output
 
+    def touched_point_ids(self):
+        """Point indices referenced by the most recent fused forward (one entry per valid (sample, neighbour) pair,
+        duplicates included; no host sync) - the rows of the point tables that can carry gradient this step."""
+        call = getattr(self.aggregator, "last_call", None)
+        if call is None or call.M == 0:
+            return None if call is None else torch.zeros(0, dtype=torch.long, device=call.sample_pidx.device)
+        return call.sample_pidx.view(-1)[call.pair_src[:call.M].long()].long()
+
     # ---- fused path -----------------------------------------------------------------------------
     def forward(self, campos, raydir, gt_image=None, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None,
                 focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, **kargs):

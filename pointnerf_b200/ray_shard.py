@@ -85,8 +85,8 @@ class RayShardedStep:
 
     BIG = 1 << 18   # parameters at least this large are reduced in place; smaller ones are coalesced
 
-    def __init__(self, model, bg_color, group=None):
-        self.model, self.bg, self.group = model, bg_color, group
+    def __init__(self, model, bg_color, group=None, sparse=True):
+        self.model, self.bg, self.group, self.sparse = model, bg_color, group, sparse
         nps = model.neural_points
         params = [nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color]
         params += list(model.aggregator.parameters())
@@ -97,6 +97,44 @@ class RayShardedStep:
         self.nbytes = sum(p.numel() for p in self.params) * 4
         self._small_flat = None
 
+    def _sparse_tables(self, tables, pid):
+        """Sparse exchange of the per-point gradients: only rows referenced this step are non-zero (<= valid pairs of
+        the batch, ~10 % of a 1M-point cloud, ~0.5 % of a 20M-point one), so each rank all-gathers (row ids, rows) of ITS
+        touched rows and every rank rebuilds the touched rows as the sum over ranks IN RANK ORDER (identical bits on every
+        replica).  One host sync per step (the padded row count, max over ranks).  Bytes per GPU:
+        (G-1) * U * 4*(39+1) against 2*(G-1)/G * 4*39*N for the dense all-reduce."""
+        G, dev = self.world, tables[0].grad.device
+        N = tables[0].shape[1]
+        mark = torch.zeros(N, dtype=torch.int32, device=dev)
+        if pid.numel():
+            mark[pid] = 1
+        pos = torch.cumsum(mark, 0, dtype=torch.int64) - 1
+        umax = (pos[-1] + 1).reshape(1).clone()
+        dist.all_reduce(umax, op=dist.ReduceOp.MAX, group=self.group)
+        cap = max(1024, (int(umax.item()) + 1023) // 1024 * 1024)             # the host sync
+        ids = torch.full((cap + 1,), -1, dtype=torch.int64, device=dev)
+        ids.scatter_(0, torch.where(mark > 0, pos, torch.full_like(pos, cap)), torch.arange(N, device=dev))
+        ids = ids[:cap]
+        safe = ids.clamp(min=0)
+        live = (ids >= 0).to(torch.float32)[:, None]
+        widths = [t.shape[2] for t in tables]
+        rows = torch.cat([t.grad[0].index_select(0, safe) for t in tables], dim=1) * live          # [cap, 39]
+        rows_all = torch.empty((G * cap, rows.shape[1]), dtype=torch.float32, device=dev)
+        ids_all = torch.empty((G * cap,), dtype=torch.int64, device=dev)
+        h1 = dist.all_gather_into_tensor(rows_all, rows.contiguous(), group=self.group, async_op=True)
+        h2 = dist.all_gather_into_tensor(ids_all, ids.contiguous(), group=self.group, async_op=True)
+        for t in tables:                       # own contribution is re-added from the gathered buffer, in rank order
+            t.grad[0].index_fill_(0, safe, 0.0)
+        h1.wait()
+        h2.wait()
+        for r in range(G):
+            idr = ids_all[r * cap:(r + 1) * cap].clamp(min=0)                  # unique inside a rank: deterministic
+            blk = rows_all[r * cap:(r + 1) * cap]
+            off = 0
+            for t, wd in zip(tables, widths):
+                t.grad[0].index_add_(0, idr, blk[:, off:off + wd])
+                off += wd
+
     def all_reduce(self):
         if self.world <= 1:
             return
@@ -105,6 +143,15 @@ class RayShardedStep:
         for p in self.params:
             if p.grad is None:
                 p.grad = torch.zeros_like(p)
+        pid = self.model.touched_point_ids() if (self.sparse and hasattr(self.model, "touched_point_ids")) else None
+        nps = self.model.neural_points
+        tables = [t for t in (nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color)
+                  if t is not None and t.requires_grad]
+        if pid is not None and tables and all(t.dim() == 3 and t.shape[0] == 1 for t in tables):
+            self._sparse_tables(tables, pid)
+            tset = {id(t) for t in tables}
+            big = [p for p in big if id(p) not in tset]
+            small = [p for p in small if id(p) not in tset]
         handles = [dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for p in big]
         if small:
             flat = torch.cat([p.grad.reshape(-1) for p in small])

@@ -35,10 +35,14 @@ class _Driver(nn.Module):
         self.neural_points = _Points()
         self.aggregator = nn.Sequential(nn.Linear(8 + 1 + 3 + 3, 16), nn.LeakyReLU(), nn.Linear(16, C))
 
+    def touched_point_ids(self):
+        return self._idx
+
     def forward(self, campos, raydir, bg_color=None, camrotc2w=None, near=None, far=None, uniform=None):
         nps = self.neural_points
         n = nps.points_embeding.shape[1]
         idx = (raydir[0].abs().sum(-1) * 1000).long() % n
+        self._idx = idx
         x = torch.cat([nps.points_embeding[0, idx], nps.points_conf[0, idx], nps.points_dir[0, idx], nps.points_color[0, idx]], -1)
         miss = (idx % 3 == 0).float()[:, None]
         return {"coarse_raycolor": (self.aggregator(x) * (1 - miss) + bg_color[None] * miss)[None]}
@@ -57,12 +61,13 @@ def _batch(R=37, C=6):
     return torch.randn(1, R, 3, generator=g), torch.rand(1, R, C, generator=g)
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, sparse):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     model = _Driver()
     bg = nn.Parameter(torch.full((6,), 0.25))
-    step = RayShardedStep(model, bg)
+    step = RayShardedStep(model, bg, sparse=sparse)
+    step.BIG = 64          # the stand-in tables are tiny: exercise the in-place path as well
     raydir, gt = _batch()
     lo, hi = shard_bounds(raydir.shape[1], world, rank)
     cam = dict(campos=torch.zeros(1, 3), camrotc2w=torch.eye(3)[None], near=0.1, far=1.0)
@@ -94,9 +99,10 @@ def test_flat_grads_alias_and_zero():
     assert float(lin.weight.grad.abs().sum()) == 0.0
 
 
-def test_two_rank_gradients_equal_single_process(tmp_path):
+@pytest.mark.parametrize("sparse", [True, False])
+def test_two_rank_gradients_equal_single_process(tmp_path, sparse):
     out = str(tmp_path / "g.pt")
-    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), out, sparse), nprocs=2, join=True)
     got = torch.load(out)
     model = _Driver()
     bg = nn.Parameter(torch.full((6,), 0.25))
