@@ -35,6 +35,28 @@ METRIC = "train_rays_per_s_fwd_bwd"
 UNIT = "rays/s"
 
 
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """stdout carries the ONE JSON line only: libraries that print there from C (NCCL's version banner) go to stderr."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -244,6 +266,7 @@ def cpu_oracle_steps(opt, tables, batches, bg, agg_state, rays, steps, warmup):
 # ---------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
+    _quiet_stdout()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
@@ -284,7 +307,7 @@ def main():
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
                                  "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        _emit(line)
         return 0
 
     # ------------------------------------------------------------------ our arm
@@ -426,7 +449,7 @@ def main():
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4},
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0

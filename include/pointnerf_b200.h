@@ -239,8 +239,22 @@ int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg
 int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
                     const float* grad_decoded, const void* saved, int64_t saved_bytes,
                     const pn_agg_weights* grad_w, int scatter_rows, float* grad_embedding,
-                    float* grad_color, float* grad_dir, float* grad_conf, void* workspace,
-                    int64_t workspace_bytes, void* stream);
+                    float* grad_color, float* grad_dir, float* grad_conf, int32_t* touched_ids,
+                    int32_t* n_touched, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 4b. Sparse exchange of per-point gradient rows between ranks (new: the reference has no multi-GPU path).
+ * With scatter_rows == 1, pn_agg_backward can also return touched_ids int32[M] - the table rows that received
+ * gradient, ascending and unique, padded with -1 - and n_touched int32[1].
+ *   pn_rows_pack : out[cap, F+8] = [id bits | embedding F | conf | dir 3 | color 3] of rows ids[0..n_ids);
+ *                  rows n_ids..cap are padding (id -1, zeros)
+ *   pn_rows_merge: gathered [n_ranks, cap, F+8] (all-gather of the packed buffers): every touched table row
+ *                  becomes the sum over ranks IN RANK ORDER (bit-identical on every replica, no atomics).
+ * ---------------------------------------------------------------------------------------------- */
+int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb,
+                 const float* g_conf, const float* g_dir, const float* g_color, float* out, void* stream);
+int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, float* g_emb, float* g_conf,
+                  float* g_dir, float* g_color, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 5. Compositing  (replaces ray_march / alpha_ray_march diff_ray_marching.py:509-573 with

@@ -88,6 +88,9 @@ class _AggCall:
         self.n_slots, self.T, self.scatter_rows, self.want_weight = n_slots, T, scatter_rows, want_weight
         self.S = self.M = 0
         self.sample_list = self.pair_start = self.pair_src = self.slot_row = None
+        self.collect_touched = False          # ask the backward for the sorted unique list of table rows it touched
+        self.touched_ids = self.n_touched = None
+        self.grad_flat = None                 # backward: the MLP weight gradients, one contiguous buffer
 
 
 def _weights_struct(tensors):
@@ -129,6 +132,10 @@ def compact_samples(sample_pidx, n_slots, K):
     return sample_list, pair_start, pair_src, S, M, slot_row
 
 
+def _shaped(grads, shapes):
+    return tuple(None if g is None else g.view(sh) for g, sh in zip(grads, shapes))
+
+
 class _AggFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, call, embedding, color, pdir, conf, *weights):
@@ -146,6 +153,7 @@ class _AggFunction(torch.autograd.Function):
         saved = torch.empty(max(saved_bytes, 1), dtype=torch.uint8, device=dev)
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
         weights = tuple(w.detach().contiguous() for w in weights)
+        ctx.table_shapes = tuple(t.shape for t in (embedding, color, pdir, conf))
         embedding, color, pdir, conf = (t.detach().contiguous() for t in (embedding, color, pdir, conf))
         ain = _inputs_struct(call, embedding, color, pdir, conf)
         wst = _weights_struct(weights)
@@ -174,7 +182,10 @@ class _AggFunction(torch.autograd.Function):
         g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
         g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[3] else None
         g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[4] else None
-        g_w = tuple(torch.empty_like(w) for w in ctx.weights)
+        # all MLP gradients live in ONE flat buffer (256-byte aligned segments): ray_shard all-reduces it in place
+        sizes = [(w.numel() + 63) // 64 * 64 for w in ctx.weights]
+        call.grad_flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+        g_w = tuple(seg[:w.numel()].view(w.shape) for seg, w in zip(call.grad_flat.split(sizes), ctx.weights))
         ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 1)
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
         ain = _inputs_struct(call, embedding, color, pdir, conf)
@@ -183,12 +194,16 @@ class _AggFunction(torch.autograd.Function):
             for t in (g_emb, g_col, g_dir, g_cnf) + g_w:
                 if t is not None:
                     t.zero_()
-            return (None, g_emb, g_col, g_dir, g_cnf) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
+            return (None,) + _shaped((g_emb, g_col, g_dir, g_cnf), ctx.table_shapes) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
+        if call.collect_touched and call.scatter_rows:
+            call.touched_ids = torch.empty(max(call.M, 1), dtype=torch.int32, device=dev)
+            call.n_touched = torch.empty(1, dtype=torch.int32, device=dev)
         _lib.check(lib.pn_agg_backward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(g_decoded),
                                        _lib.ptr(ctx.saved), ctx.saved_bytes, ctypes.byref(gst), 1 if call.scatter_rows else 0,
-                                       _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf), _lib.ptr(ws),
+                                       _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf),
+                                       _lib.ptr(call.touched_ids), _lib.ptr(call.n_touched), _lib.ptr(ws),
                                        ws_bytes, _lib.stream()), "pn_agg_backward")
-        return (None, g_emb, g_col, g_dir, g_cnf) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
+        return (None,) + _shaped((g_emb, g_col, g_dir, g_cnf), ctx.table_shapes) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
 
 
 class PointAggregator(nn.Module):
@@ -284,7 +299,9 @@ class PointAggregator(nn.Module):
     # ------------------------------------------------------------------------------------------
     def forward_tables(self, xyz, xyz_pers, embedding, color, pdir, conf, Rw2c, sample_pidx, sample_loc, sample_loc_w,
                        ray_dirs, vsize, dirs_per_ray=True, want_weight=False, compact=False):
-        """Fused gather + aggregate.  xyz/xyz_pers [N,3], embedding [N,F], color/pdir [N,3], conf [N];
+        """Fused gather + aggregate.  xyz/xyz_pers [N,3], embedding [N,F], color/pdir [N,3], conf [N] - the tables may also
+        keep the reference's leading batch / trailing unit axes ([1,N,F], [1,N,3], [1,N,1]): passing the parameters
+        themselves makes the backward's buffers their .grad with no select-backward fill + copy of the whole table;
         sample_pidx int32 [R,SR,K] (-1 empty); sample_loc / sample_loc_w [R,SR,3]; ray_dirs [R,3]
         (``dirs_per_ray``) or [R,SR,3].  Returns decoded [R,SR,C+1], weight [R,SR,K] or None.
         ``compact=True``: returns (decoded [S,C+1] with one row per VALID sample, weight, slot_row int32 [R,SR]) -
@@ -292,10 +309,11 @@ class PointAggregator(nn.Module):
         if Rw2c.dim() != 2:
             raise NotImplementedError("per-point Rw2c is outside the hot path (every shipped script uses one 3x3)")
         R, SR, K = (int(v) for v in sample_pidx.shape)
-        T = int(embedding.shape[0])
+        T = int(embedding.shape[-2])
         call = _AggCall(self._params(K, SR, dirs_per_ray, vsize, compact), xyz.detach().contiguous(), xyz_pers.detach().contiguous(),
                         Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
                         sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
+        call.collect_touched = bool(getattr(self, "collect_touched", False))
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
         self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)
         weight = weight.view(R, SR, K) if want_weight else None

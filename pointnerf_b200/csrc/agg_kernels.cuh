@@ -364,4 +364,24 @@ __global__ void __launch_bounds__(256) agg_segment_reduce_kernel(pn_agg_inputs i
     }
 }
 
+// ---- touched rows (multi-GPU sparse gradient exchange) ----------------------------------------------------
+// flag[i] = 1 iff sorted position i is the head of its per-point segment
+__global__ void __launch_bounds__(256) agg_head_flag_kernel(pn_agg_inputs in, const int* __restrict__ start,
+                                                            const int* __restrict__ sorted, int* __restrict__ flag) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= in.M) return;
+    int g = in.sample_pidx[in.pair_src[sorted[i]]];
+    flag[i] = start[g] == (int)i ? 1 : 0;
+}
+// ids[rank of head i among heads] = point index; heads are in ascending point order, so ids is sorted and unique
+__global__ void __launch_bounds__(256) agg_head_ids_kernel(pn_agg_inputs in, const int* __restrict__ start,
+                                                           const int* __restrict__ sorted, const int* __restrict__ rank,
+                                                           int* __restrict__ ids, int* __restrict__ n_touched) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0 && n_touched) n_touched[0] = rank[in.M];
+    if (i >= in.M) return;
+    int g = in.sample_pidx[in.pair_src[sorted[i]]];
+    if (start[g] == (int)i) ids[rank[i]] = g;
+}
+
 }  // namespace pn

@@ -74,7 +74,7 @@ struct BwdWs {
     float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
     float *GA, *GB, *GSa, *GSb, *galpha, *PG, *tn, *apart;
     char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
-    int *cnt, *rank, *tmp, *sorted, *scan;
+    int *cnt, *rank, *tmp, *sorted, *scan, *hflag, *hscan;
     int nblk_reduce;
     int64_t chunk;
 };
@@ -134,6 +134,8 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     t.tmp = c.take<int>(m);
     t.sorted = c.take<int>(m);
     t.scan = c.take<int>(scan_scratch_elems_i32(tt + 1));
+    t.hflag = c.take<int>(m + 1);
+    t.hscan = c.take<int>(scan_scratch_elems_i32(m + 1));
     if (w) *w = t;
     return c.off;
 }
@@ -222,8 +224,9 @@ static int zero_weight_grads(const AggDims& d, const pn_agg_weights* g, cudaStre
 
 extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
                                const float* grad_decoded, const void* saved, int64_t saved_bytes, const pn_agg_weights* gw,
-                               int scatter_rows, float* g_emb, float* g_color, float* g_dir, float* g_conf, void* workspace,
-                               int64_t workspace_bytes, void* stream) {
+                               int scatter_rows, float* g_emb, float* g_color, float* g_dir, float* g_conf,
+                               int32_t* touched_ids, int32_t* n_touched, void* workspace, int64_t workspace_bytes,
+                               void* stream) {
     AggDims d;
     PN_TRY(make_dims(p, d));
     PN_CHECK_ARG(in && w && saved && gw && (grad_decoded || (p->compact_out && in->S == 0)), "pn_agg_backward: null argument");
@@ -237,6 +240,8 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     if (g_color) PN_CUDA(cudaMemsetAsync(g_color, 0, rows * 3 * sizeof(float), st));
     if (g_dir) PN_CUDA(cudaMemsetAsync(g_dir, 0, rows * 3 * sizeof(float), st));
     if (g_conf) PN_CUDA(cudaMemsetAsync(g_conf, 0, rows * sizeof(float), st));
+    if (touched_ids && scatter_rows) PN_CUDA(cudaMemsetAsync(touched_ids, 0xFF, (M > 0 ? M : 1) * sizeof(int), st));
+    if (n_touched) PN_CUDA(cudaMemsetAsync(n_touched, 0, sizeof(int), st));
     if (S <= 0 || M <= 0) return zero_weight_grads(d, gw, st);
 
     Saved sv;
@@ -355,6 +360,13 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, ws.cnt, ws.sorted, ws.PG, pgw, g_emb, g_color,
                                                                                g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_segment_reduce");
+        if (touched_ids) {   // sorted unique list of the table rows that received gradient
+            agg_head_flag_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.sorted, ws.hflag);
+            PN_LAUNCH_CHECK("agg_head_flag");
+            PN_TRY(scan_exclusive_i32(ws.hflag, ws.hflag, M, true, ws.hscan, st));
+            agg_head_ids_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.sorted, ws.hflag, touched_ids, n_touched);
+            PN_LAUNCH_CHECK("agg_head_ids");
+        }
     }
     return PN_OK;
 }
@@ -381,4 +393,96 @@ extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int
                                 float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream) {
     GemmTN t{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb};
     return gemm_tn(t, scratch, (cudaStream_t)stream);
+}
+
+// ---- sparse exchange of per-point gradient rows between ranks (ray_shard.py) ---------------------------------
+namespace pn {
+// out[u] = [id bits | emb(F) | conf(1) | dir(3) | color(3)] of table row ids[u]; u >= n_ids or id < 0 -> id = -1, zeros
+__global__ void __launch_bounds__(256) rows_pack_kernel(const int* __restrict__ ids, int64_t n_ids, int64_t cap, int F,
+                                                        const float* __restrict__ g_emb,
+                                                        const float* __restrict__ g_conf, const float* __restrict__ g_dir,
+                                                        const float* __restrict__ g_color, float* __restrict__ out) {
+    const int W = F + 8;
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= cap * W) return;
+    int64_t u = idx / W;
+    int c = (int)(idx - u * W);
+    int g = u < n_ids ? ids[u] : -1;
+    float v = 0.f;
+    if (c == 0) v = __int_as_float(g);
+    else if (g >= 0) {
+        int k = c - 1;
+        if (k < F) v = g_emb[(int64_t)g * F + k];
+        else if (k == F) v = g_conf ? g_conf[g] : 0.f;
+        else if (k < F + 4) v = g_dir ? g_dir[(int64_t)g * 3 + (k - F - 1)] : 0.f;
+        else v = g_color ? g_color[(int64_t)g * 3 + (k - F - 4)] : 0.f;
+    }
+    out[idx] = v;
+}
+// One warp per (rank r, row u) of the gathered buffer [G, cap, W].  Each rank's id list is sorted and unique.  The warp of
+// the LOWEST rank that holds an id owns that table row: it adds the contributions of the higher ranks in rank order
+// (binary search per rank) and stores the sum - every replica computes bit-identical rows.
+__global__ void __launch_bounds__(256) rows_merge_kernel(const float* __restrict__ all, int G, int64_t cap, int F, float* __restrict__ g_emb,
+                                                         float* __restrict__ g_conf, float* __restrict__ g_dir, float* __restrict__ g_color) {
+    const int W = F + 8;
+    int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (wid >= (int64_t)G * cap) return;
+    int r = (int)(wid / cap);
+    const float* mine = all + wid * W;
+    int g = __float_as_int(mine[0]);
+    if (g < 0) return;
+    auto find = [&](int rr) -> int64_t {     // position of id g in rank rr's list, or -1
+        const float* base = all + (int64_t)rr * cap * W;
+        int64_t lo = 0, hi = cap;            // valid ids first (ascending), then -1 padding
+        while (lo < hi) {
+            int64_t mid = (lo + hi) >> 1;
+            int v = __float_as_int(base[mid * W]);
+            if (v < 0 || v > g) hi = mid; else if (v < g) lo = mid + 1; else return mid;
+        }
+        return -1;
+    };
+    for (int rr = 0; rr < r; ++rr)
+        if (find(rr) >= 0) return;           // a lower rank owns this row
+    float acc[2] = {0.f, 0.f};               // W - 1 <= 64 columns: two per lane
+    for (int i = 0; i < 2; ++i) {
+        int c = lane + 32 * i;
+        if (c < W - 1) acc[i] = mine[1 + c];
+    }
+    for (int rr = r + 1; rr < G; ++rr) {
+        int64_t pos = find(rr);
+        if (pos < 0) continue;
+        const float* o = all + ((int64_t)rr * cap + pos) * W;
+        for (int i = 0; i < 2; ++i) {
+            int c = lane + 32 * i;
+            if (c < W - 1) acc[i] += o[1 + c];
+        }
+    }
+    for (int i = 0; i < 2; ++i) {
+        int k = lane + 32 * i;
+        if (k >= W - 1) continue;
+        if (k < F) g_emb[(int64_t)g * F + k] = acc[i];
+        else if (k == F) { if (g_conf) g_conf[g] = acc[i]; }
+        else if (k < F + 4) { if (g_dir) g_dir[(int64_t)g * 3 + (k - F - 1)] = acc[i]; }
+        else if (g_color) g_color[(int64_t)g * 3 + (k - F - 4)] = acc[i];
+    }
+}
+}  // namespace pn
+
+extern "C" int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb, const float* g_conf, const float* g_dir,
+                            const float* g_color, float* out, void* stream) {
+    PN_CHECK_ARG((ids || n_ids == 0) && n_ids >= 0 && g_emb && out && F >= 1 && F <= 56, "pn_rows_pack: bad argument (F <= 56)");
+    if (cap <= 0) return PN_OK;
+    rows_pack_kernel<<<(unsigned)cdiv(cap * (F + 8), 256), 256, 0, (cudaStream_t)stream>>>(ids, n_ids, cap, F, g_emb, g_conf, g_dir, g_color, out);
+    PN_LAUNCH_CHECK("rows_pack");
+    return PN_OK;
+}
+extern "C" int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, float* g_emb, float* g_conf, float* g_dir,
+                             float* g_color, void* stream) {
+    PN_CHECK_ARG(gathered && g_emb && n_ranks >= 1 && F >= 1 && F <= 56, "pn_rows_merge: bad argument (F <= 56)");
+    if (cap <= 0) return PN_OK;
+    rows_merge_kernel<<<(unsigned)cdiv((int64_t)n_ranks * cap * 32, 256), 256, 0, (cudaStream_t)stream>>>(gathered, n_ranks, cap, F, g_emb,
+                                                                                                  g_conf, g_dir, g_color);
+    PN_LAUNCH_CHECK("rows_merge");
+    return PN_OK;
 }

@@ -217,7 +217,7 @@ class NeuralPointsRayMarching(nn.Module):
         xyz_pers = _query.w2pers(xyz.detach(), camrotc2w[0], campos[0])
         want_w = self.aggregator._want_weight()
         decoded, weight, slot_row = self.aggregator.forward_tables(
-            xyz, xyz_pers, nps.points_embeding[0], nps.points_color[0], nps.points_dir[0], nps.points_conf[0, :, 0], nps.Rw2c,
+            xyz, xyz_pers, nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf, nps.Rw2c,
             pidx, loc_pers, loc_w, raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w, compact=True)
         ray_valid = (slot_row >= 0)[None]                                         # [1,R,SR]
         ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)

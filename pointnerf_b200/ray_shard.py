@@ -95,7 +95,51 @@ class RayShardedStep:
         self.params = [p for p in params if p is not None and p.requires_grad]
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.nbytes = sum(p.numel() for p in self.params) * 4
-        self._small_flat = None
+        self._cap_ev = self._cap_cpu = None
+        if self.world > 1 and sparse and hasattr(model.aggregator, "forward_tables"):
+            model.aggregator.collect_touched = True     # the fused backward returns the sorted unique touched rows
+
+    # ---- sparse exchange on the C ABI (CUDA tables) -------------------------------------------------------------
+    def _begin_cap_exchange(self, rest):
+        """Right after the backward: ONE small all-gather carries each rank's touched-row count (known only on the device)
+        and the gradients of the few parameters outside the tables and the MLP buffer (`rest`, e.g. the background
+        colour).  The counts go to a pinned host word; the read-back overlaps the MLP all-reduce issued next."""
+        call = getattr(self.model.aggregator, "last_call", None)
+        if call is None or call.n_touched is None:
+            return False
+        dev = call.n_touched.device
+        head = torch.cat([call.n_touched] + [p.grad.reshape(-1).view(torch.int32) for p in rest])
+        self._head_all = torch.empty((self.world, head.numel()), dtype=torch.int32, device=dev)
+        dist.all_gather_into_tensor(self._head_all, head, group=self.group)
+        if self._cap_cpu is None or self._cap_cpu.numel() != self.world:
+            self._cap_cpu = torch.zeros(self.world, dtype=torch.int32).pin_memory()
+        self._cap_cpu.copy_(self._head_all[:, 0], non_blocking=True)
+        self._cap_ev = torch.cuda.Event()
+        self._cap_ev.record(torch.cuda.current_stream(dev))
+        return True
+
+    def _sparse_tables_cuda(self, tables_by_name):
+        from . import _lib
+        lib = _lib.lib()
+        call = self.model.aggregator.last_call
+        self._cap_ev.synchronize()                          # the one host sync of the exchange (~tens of us)
+        cap = max(256, (int(self._cap_cpu.max()) + 255) // 256 * 256)
+        emb = tables_by_name["points_embeding"]
+        dev, F = emb.grad.device, int(emb.shape[2])
+        ids, n_ids = call.touched_ids, (int(call.M) if call.touched_ids is not None else 0)   # n_touched <= M entries, -1 beyond
+        g = {k_: (t.grad.contiguous() if t is not None else None) for k_, t in tables_by_name.items()}
+        packed = torch.empty((cap, F + 8), dtype=torch.float32, device=dev)
+        _lib.check(lib.pn_rows_pack(_lib.ptr(ids), n_ids, cap, F, _lib.ptr(g["points_embeding"]), _lib.ptr(g["points_conf"]),
+                                    _lib.ptr(g["points_dir"]), _lib.ptr(g["points_color"]), _lib.ptr(packed), _lib.stream()),
+                   "pn_rows_pack")
+        gathered = torch.empty((self.world * cap, F + 8), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(gathered, packed, group=self.group)
+        _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, _lib.ptr(g["points_embeding"]), _lib.ptr(g["points_conf"]),
+                                     _lib.ptr(g["points_dir"]), _lib.ptr(g["points_color"]), _lib.stream()), "pn_rows_merge")
+        for k_, t in tables_by_name.items():
+            if t is not None and t.grad.data_ptr() != g[k_].data_ptr():
+                t.grad = g[k_]
+        self.last_cap = cap
 
     def _sparse_tables(self, tables, pid):
         """Sparse exchange of the per-point gradients: only rows referenced this step are non-zero (<= valid pairs of
@@ -138,29 +182,50 @@ class RayShardedStep:
     def all_reduce(self):
         if self.world <= 1:
             return
-        big = [p for p in self.params if p.numel() >= self.BIG]
-        small = [p for p in self.params if p.numel() < self.BIG]
         for p in self.params:
             if p.grad is None:
                 p.grad = torch.zeros_like(p)
-        pid = self.model.touched_point_ids() if (self.sparse and hasattr(self.model, "touched_point_ids")) else None
         nps = self.model.neural_points
-        tables = [t for t in (nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color)
-                  if t is not None and t.requires_grad]
-        if pid is not None and tables and all(t.dim() == 3 and t.shape[0] == 1 for t in tables):
-            self._sparse_tables(tables, pid)
-            tset = {id(t) for t in tables}
-            big = [p for p in big if id(p) not in tset]
-            small = [p for p in small if id(p) not in tset]
-        handles = [dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for p in big]
-        if small:
-            flat = torch.cat([p.grad.reshape(-1) for p in small])
-            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
-            off = 0
-            for p in small:
-                n = p.numel()
-                p.grad.copy_(flat[off:off + n].view_as(p))
-                off += n
+        names = ("points_embeding", "points_conf", "points_dir", "points_color")
+        tables = [t for t in (getattr(nps, n) for n in names) if t is not None and t.requires_grad]
+        tset = {id(t) for t in tables}
+        # the fused backward leaves every MLP gradient inside one flat buffer: reduce that buffer in place
+        flat = getattr(getattr(self.model.aggregator, "last_call", None), "grad_flat", None)
+        lo, hi = (flat.data_ptr(), flat.data_ptr() + 4 * flat.numel()) if flat is not None else (0, 0)
+        rest = [p for p in self.params if id(p) not in tset and not (lo <= p.grad.data_ptr() < hi)]
+        mode = None
+        if self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._begin_cap_exchange(rest):
+            mode = "cuda"        # ids from the fused backward, pack / merge kernels of the C ABI
+        elif self.sparse and hasattr(self.model, "touched_point_ids") and tables and not tables[0].is_cuda:
+            pid = self.model.touched_point_ids()     # device-agnostic torch formulation (CPU tests of the host logic)
+            if pid is not None and all(t.dim() == 3 and t.shape[0] == 1 for t in tables):
+                self._sparse_tables(tables, pid)
+                mode = "torch"
+        handles = []
+        if flat is not None and hi > lo:
+            handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        if mode is None:
+            handles += [dist.all_reduce(t.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for t in tables]
+        if mode == "cuda":
+            self._sparse_tables_cuda({n: (getattr(nps, n) if getattr(nps, n) is not None and getattr(nps, n).requires_grad else None)
+                                      for n in names})
+            if rest:             # rank-ordered sum of the gathered head columns: identical bits on every replica
+                tot = self._head_all[:, 1:].view(torch.float32).sum(0)
+                off = 0
+                for p in rest:
+                    p.grad.copy_(tot[off:off + p.numel()].view_as(p))
+                    off += p.numel()
+        elif rest:
+            big = [p for p in rest if p.numel() >= self.BIG]
+            small = [p for p in rest if p.numel() < self.BIG]
+            handles += [dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for p in big]
+            if small:
+                buf = torch.cat([p.grad.reshape(-1) for p in small])
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
+                off = 0
+                for p in small:
+                    p.grad.copy_(buf[off:off + p.numel()].view_as(p))
+                    off += p.numel()
         for h in handles:
             h.wait()
 
@@ -173,6 +238,7 @@ class RayShardedStep:
             p.grad = None
         out = self.model(cam["campos"], raydir, bg_color=self.bg, camrotc2w=cam["camrotc2w"], near=cam["near"], far=cam["far"],
                          uniform=uniform)
+        self._cap_ev = None
         diff = out["coarse_raycolor"] - gt
         loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
         loss.backward()
