@@ -383,16 +383,17 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
 //                swizzled smem, 2 stages
 //   warp  8      one thread issues the MMAs
 //   warp  9      one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
-//   warps 10-13  epilogue, one TMEM lane quadrant (32 rows) each
+//   warps 10-17  epilogue: TMEM lane quadrant (warp & 3), 32 rows; the two warps of a quadrant alternate 16-column
+//                chunks; the TMEM load of the next chunk and the bias / mask loads are in flight while one is stored
 // ---------------------------------------------------------------------------------------------------------------
 namespace {
 constexpr int NSA = 2, NSB = 2;
 constexpr int A_STAGE = 2 * A_BYTES;                 // 32 KB (hi | lo)
 constexpr int B_STAGE = 2 * B_BYTES;                 // 64 KB (hi | lo) at BN = 256
-constexpr int SLAB_LD = 36;                          // floats per slab row (32 + 4: conflict-free float4 access)
-constexpr int SLAB_BYTES = 32 * SLAB_LD * 4;         // per epilogue warp
-constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + 4 * SLAB_BYTES + 1024 + 256;
-constexpr int kThreadsImg = kLoadThreads + 64 + 128;
+constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant, alternating 16-column chunks
+constexpr int SLAB_BYTES = 32 * 16 * 4;              // per epilogue warp: 32 rows x 16 floats, 16-byte chunks XOR-swizzled
+constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + kEpiWarps * SLAB_BYTES + 1024 + 256;
+constexpr int kThreadsImg = kLoadThreads + 64 + 32 * kEpiWarps;
 }  // namespace
 
 __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int n_tiles_n, int n_tiles_total) {
@@ -401,7 +402,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
     char* smA = smem;
     char* smB = smem + NSA * A_STAGE;
     char* slabs = smB + NSB * B_STAGE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + 4 * SLAB_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kEpiWarps * SLAB_BYTES);
     uint64_t *fullA = bars, *emptyA = bars + 2, *fullB = bars + 4, *emptyB = bars + 6, *accFull = bars + 8, *accEmpty = bars + 10;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -414,7 +415,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
     if (t == 0) {
         for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads); tc::mbar_init(&emptyA[i], 1); }
         for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 4); }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], kEpiWarps); }
         tc::mbar_fence_init();
     }
     if (warp == 8) tc::tmem_alloc(tmem_slot, 512u);
@@ -509,13 +510,17 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
         }
         __syncwarp();
     } else {
-        // ---------------------------------------------------------------- epilogue (warps 10..13)
+        // ---------------------------------------------------------------- epilogue (warps 10..17)
         const int q = warp & 3;                       // TMEM lane quadrant this warp may access
+        const int half = (warp - 10) >> 2;            // chunks j with (j & 1) == half
         float* slab = reinterpret_cast<float*>(slabs + (warp - 10) * SLAB_BYTES);
         const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
                             (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
                             (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
-        const int rsub = lane >> 3, c4 = lane & 7;
+        const int rsub = lane >> 2, c4 = lane & 3;    // store phase: 8 rows x 64 B per instruction
+        const int nch = (BN + 15) >> 4;
+        const int my_last = ((nch - 1 - half) & ~1) + half;            // last chunk of this warp (may be < half: none)
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int it = 0; it < my_tiles; ++it) {
             const int ab = it & 1;
             const int tile = (int)blockIdx.x + it * (int)gridDim.x;
@@ -524,55 +529,75 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
             tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
-            const int ncol32 = (BN + 31) >> 5;
-            for (int cb = 0; cb < ncol32; ++cb) {
-                float v[32];
-                tc::tmem_ld32(taddr + (uint32_t)(cb * 32), v);
-                if (cb == ncol32 - 1) {               // accumulator fully read: hand the buffer back to the MMA warp
+            uint32_t cur[16], nxt[16];
+            if (half < nch) tc::tmem_ld16_issue(taddr + (uint32_t)(half * 16), cur);
+            for (int j = half; j < nch; j += 2) {
+                const int n = n0 + j * 16 + 4 * c4;
+                const bool ncol_ok = (j * 16 + 4 * c4 < BN) && n < g.N;
+                // global operands of this chunk first: their latency hides behind the TMEM wait and the transpose
+                float4 bias4 = z4, aux4[4];
+                if (vec_ok && ncol_ok) {
+                    if (g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                    if (g.aux && n < g.aux_cols) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int64_t m = m0 + 8 * i + rsub;
+                            aux4[i] = m < g.M ? __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n)) : z4;
+                        }
+                    }
+                }
+                tc::tmem_ld_wait();
+                if (j + 2 < nch) tc::tmem_ld16_issue(taddr + (uint32_t)((j + 2) * 16), nxt);
+                if (j == my_last) {                   // accumulator fully read by this warp: hand it back to the MMA warp
                     tc::fence_before_sync();
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
                 }
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    *reinterpret_cast<float4*>(slab + lane * SLAB_LD + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                for (int i = 0; i < 4; ++i)           // row = lane; chunk i lands at i ^ ((lane >> 1) & 3): conflict-free both ways
+                    *reinterpret_cast<float4*>(slab + lane * 16 + 4 * (i ^ ((lane >> 1) & 3))) =
+                        make_float4(__uint_as_float(cur[4 * i]), __uint_as_float(cur[4 * i + 1]), __uint_as_float(cur[4 * i + 2]),
+                                    __uint_as_float(cur[4 * i + 3]));
                 __syncwarp();
-                const int n = n0 + cb * 32 + 4 * c4;
-                const bool ncol_ok = (cb * 32 + 4 * c4 < BN) && n < g.N;
-                float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (vec_ok && g.bias && ncol_ok) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
-#pragma unroll 2
-                for (int rr = 0; rr < 32; rr += 4) {
-                    const int row = rr + rsub;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int row = 8 * i + rsub;
                     const int64_t m = m0 + row;
-                    float4 x4 = *reinterpret_cast<const float4*>(slab + row * SLAB_LD + 4 * c4);
+                    float4 x4 = *reinterpret_cast<const float4*>(slab + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
                     if (m >= g.M || !ncol_ok) continue;
                     float x[4] = {x4.x, x4.y, x4.z, x4.w};
                     if (vec_ok) {
                         x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
                         if (g.leaky) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) x[i] = x[i] > 0.f ? x[i] : g.slope * x[i];
+                            for (int e = 0; e < 4; ++e) x[e] = x[e] > 0.f ? x[e] : g.slope * x[e];
                         }
                         if (g.aux && n < g.aux_cols) {
-                            float4 a = __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n));
+                            const float4 a = aux4[i];
                             x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
                             x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
                         }
                         *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
                     } else {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            if (n + i >= g.N) break;
-                            float y = x[i];
-                            if (g.bias) y += __ldg(g.bias + n + i);
+                        for (int e = 0; e < 4; ++e) {
+                            if (n + e >= g.N) break;
+                            float y = x[e];
+                            if (g.bias) y += __ldg(g.bias + n + e);
                             if (g.leaky) y = y > 0.f ? y : g.slope * y;
-                            if (g.aux && n + i < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + i) > 0.f) ? 1.f : g.slope;
-                            g.C[m * g.ldc + n + i] = y;
+                            if (g.aux && n + e < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + e) > 0.f) ? 1.f : g.slope;
+                            g.C[m * g.ldc + n + e] = y;
                         }
                     }
                 }
                 __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) cur[i] = nxt[i];
+            }
+            if (my_last < half) {                     // this warp owns no chunk of the tile (BN <= 16): still release
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
             }
         }
     }
