@@ -280,14 +280,16 @@ int pn_composite_forward(const float* ray_features, const float* ray_dist, const
 
 /* Gradients w.r.t. ray_features [R,SR,C+1] and bg_color [C] (deterministic two-stage reduction over
  * rays).  Upstream gradients g_opacity/g_acc_T/g_blend_w [R,SR], g_bg_T [R], g_ray_color [R,C] may each be
- * NULL (= zero).  workspace: pn_composite_workspace_bytes(n_rays, C). */
-int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C);
+ * NULL (= zero).  n_rows: rows of the compact ray_features (with slot_row; 0 / ignored for the dense layout) - the
+ * per-row part of the backward then runs one warp per feature row instead of walking each ray.
+ * workspace: pn_composite_workspace_bytes(n_rays, C, n_rows). */
+int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C, int64_t n_rows);
 int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
                           const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T,
                           const float* bg_T, const float* g_ray_color, const float* g_opacity,
                           const float* g_acc_T, const float* g_blend_w, const float* g_bg_T,
-                          int64_t n_rays, int32_t SR, int32_t C, float* g_features, float* g_bg_color,
-                          void* workspace, int64_t workspace_bytes, void* stream);
+                          int64_t n_rays, int32_t SR, int32_t C, int64_t n_rows, float* g_features,
+                          float* g_bg_color, void* workspace, int64_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -86,36 +86,55 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
         pairv[p0 + lane] = make_float4(w * cf, w, 0.f, 0.f);
         if (weight_out) weight_out[src] = w;
     }
-    // ---- phase 2: lane = channel, one row per pair
-    for (int jj = 0; jj < np; ++jj) {
-        int m = p0 + jj;
-        int gj = __shfl_sync(kFull, g, jj);
-        float r0 = __shfl_sync(kFull, dd[0], jj), r1 = __shfl_sync(kFull, dd[1], jj), r2 = __shfl_sync(kFull, dd[2], jj);
-        float r3 = __shfl_sync(kFull, dd[3], jj), r4 = __shfl_sync(kFull, dd[4], jj), r5 = __shfl_sync(kFull, dd[5], jj);
-        float* row = X1 + (int64_t)m * d.in1p;
-        for (int c = lane; c < d.F; c += 32) {
-            float e = in.embedding[(int64_t)gj * d.F + c];
-            row[c] = e;
-            float fr = 1.f;
-            for (int f = 0; f < d.ff; ++f) {
-                float s, co;
-                sincosf(e * fr, &s, &co);
-                row[d.F + (c * d.ff + f) * 2] = s;
-                row[d.F + (c * d.ff + f) * 2 + 1] = co;
-                fr *= 2.f;
-            }
-        }
-        int pe0 = d.F + 2 * d.ff * d.F;
-        for (int q = lane; q < 6 * d.df; q += 32) {
-            int a = q / d.df, f = q - a * d.df;
-            float v = a == 0 ? r0 : a == 1 ? r1 : a == 2 ? r2 : a == 3 ? r3 : a == 4 ? r4 : r5;
-            float s, co;
-            sincosf(v * (float)(1 << f), &s, &co);
-            row[pe0 + 2 * q] = s;
-            row[pe0 + 2 * q + 1] = co;
-        }
-        for (int c = d.in1 + lane; c < d.in1p; c += 32) row[c] = 0.f;
+    // the six scaled offsets of each pair are parked, raw, at the head of the row's distance-encoding block:
+    // agg_prep_rows_kernel (one warp per PAIR) reads them and writes the whole block1 input row
+    if (act) {
+        float* park = X1 + (int64_t)(p0 + lane) * d.in1p + d.F + 2 * d.ff * d.F;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) park[i] = dd[i];
     }
+}
+
+// phase 2 of prep: block1 input row [emb | PE_ff(emb) | PE_df(dist) | 0-pad] of pair m; lane = channel.  The encoding
+// interleaves (sin, cos) per (channel, frequency), so a lane owns short scattered runs of the row - stored directly,
+// every instruction would touch every 32-byte sector of the row (6x the L2 write transactions).  The row is assembled
+// in shared memory and leaves as whole float4s.
+__global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1) {
+    extern __shared__ float prep_rows[];                 // blockDim.x / 32 rows of in1p floats
+    int64_t m = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (m >= in.M) return;
+    float* srow = prep_rows + (threadIdx.x >> 5) * d.in1p;
+    const int gj = in.sample_pidx[in.pair_src[m]];
+    float* row = X1 + m * d.in1p;
+    const int pe0 = d.F + 2 * d.ff * d.F;
+    float r[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) r[i] = row[pe0 + i];
+    for (int c = lane; c < d.F; c += 32) {
+        float e = in.embedding[(int64_t)gj * d.F + c];
+        srow[c] = e;
+        float fr = 1.f;
+        for (int f = 0; f < d.ff; ++f) {
+            float s, co;
+            sincosf(e * fr, &s, &co);
+            srow[d.F + (c * d.ff + f) * 2] = s;
+            srow[d.F + (c * d.ff + f) * 2 + 1] = co;
+            fr *= 2.f;
+        }
+    }
+    for (int q = lane; q < 6 * d.df; q += 32) {
+        int a = q / d.df, f = q - a * d.df;
+        float v = a == 0 ? r[0] : a == 1 ? r[1] : a == 2 ? r[2] : a == 3 ? r[3] : a == 4 ? r[4] : r[5];
+        float s, co;
+        sincosf(v * (float)(1 << f), &s, &co);
+        srow[pe0 + 2 * q] = s;
+        srow[pe0 + 2 * q + 1] = co;
+    }
+    for (int c = d.in1 + lane; c < d.in1p; c += 32) srow[c] = 0.f;
+    __syncwarp();
+    float4* row4 = reinterpret_cast<float4*>(row);       // in1p % 4 == 0 and X1 is 16-byte aligned
+    for (int c4 = lane; c4 < (d.in1p >> 2); c4 += 32) row4[c4] = *reinterpret_cast<const float4*>(srow + 4 * c4);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -331,57 +350,69 @@ __global__ void __launch_bounds__(256) agg_key_place_kernel(pn_agg_inputs in, co
     tmp[start[g] + rank[m]] = (int)m;
 }
 __global__ void __launch_bounds__(256) agg_key_order_kernel(pn_agg_inputs in, const int* __restrict__ start,
-                                                            const int* __restrict__ tmp, int* __restrict__ sorted) {
+                                                            const int* __restrict__ tmp, int* __restrict__ sorted,
+                                                            int* __restrict__ skey) {
     int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= in.M) return;
     int g = in.sample_pidx[in.pair_src[m]];
     int s = start[g], e = start[g + 1], smaller = 0;
     for (int j = s; j < e; ++j) smaller += (tmp[j] < (int)m);
     sorted[s + smaller] = (int)m;
+    skey[s + smaller] = g;          // point index at each sorted position: segment boundaries without a gather chain
 }
 // one warp per sorted position; only segment heads work.  Lanes own columns; rows are added in ascending
 // pair order, so the sum is reproducible run to run.
-__global__ void __launch_bounds__(256) agg_segment_reduce_kernel(pn_agg_inputs in, AggDims d, const int* __restrict__ start,
+__global__ void __launch_bounds__(256) agg_segment_reduce_kernel(pn_agg_inputs in, AggDims d, const int* __restrict__ skey,
                                                                  const int* __restrict__ sorted, const float* __restrict__ PG,
                                                                  int pgw, float* __restrict__ g_emb, float* __restrict__ g_color,
                                                                  float* __restrict__ g_dir, float* __restrict__ g_conf) {
     int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (i >= in.M) return;
-    int m0 = sorted[i];
-    int g = in.sample_pidx[in.pair_src[m0]];
-    int s = start[g];
-    if (s != (int)i) return;  // not the head of its segment
-    int e = start[g + 1];
-    int cols = d.F + 7;
-    for (int c = lane; c < cols; c += 32) {
-        float a = 0.f;
-        for (int j = s; j < e; ++j) a += PG[(int64_t)sorted[j] * pgw + c];
-        if (c < d.F) { if (g_emb) g_emb[(int64_t)g * d.F + c] = a; }
-        else if (c < d.F + 3) { if (g_color) g_color[(int64_t)g * 3 + (c - d.F)] = a; }
-        else if (c < d.F + 6) { if (g_dir) g_dir[(int64_t)g * 3 + (c - d.F - 3)] = a; }
-        else if (g_conf) g_conf[g] = a;
+    const int g = skey[i];
+    if (i > 0 && skey[i - 1] == g) return;  // not the head of its segment
+    const int cols = d.F + 7;
+    for (int c0 = 0; c0 < cols; c0 += 64) {               // 64 columns per walk of the segment (one walk when F <= 57)
+        float a[2] = {0.f, 0.f};
+        for (int64_t j0 = i; j0 < in.M; j0 += 32) {       // rows of the segment, 32 sorted positions per probe
+            const int64_t j = j0 + lane;
+            const bool mine = j < in.M && skey[j] == g;
+            const int mrow = mine ? sorted[j] : -1;
+            const unsigned mask = __ballot_sync(kFull, mine);
+            const int cnt = mask == kFull ? 32 : __ffs(~mask) - 1;   // leading run that belongs to this segment
+            for (int t = 0; t < cnt; ++t) {               // ascending pair order: reproducible sums
+                const int64_t m = __shfl_sync(kFull, mrow, t);
+                if (c0 + lane < cols) a[0] += PG[m * pgw + c0 + lane];
+                if (c0 + lane + 32 < cols) a[1] += PG[m * pgw + c0 + lane + 32];
+            }
+            if (cnt < 32) break;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int c = c0 + lane + 32 * h;
+            if (c >= cols) continue;
+            if (c < d.F) { if (g_emb) g_emb[(int64_t)g * d.F + c] = a[h]; }
+            else if (c < d.F + 3) { if (g_color) g_color[(int64_t)g * 3 + (c - d.F)] = a[h]; }
+            else if (c < d.F + 6) { if (g_dir) g_dir[(int64_t)g * 3 + (c - d.F - 3)] = a[h]; }
+            else if (g_conf) g_conf[g] = a[h];
+        }
     }
 }
 
 // ---- touched rows (multi-GPU sparse gradient exchange) ----------------------------------------------------
 // flag[i] = 1 iff sorted position i is the head of its per-point segment
-__global__ void __launch_bounds__(256) agg_head_flag_kernel(pn_agg_inputs in, const int* __restrict__ start,
-                                                            const int* __restrict__ sorted, int* __restrict__ flag) {
+__global__ void __launch_bounds__(256) agg_head_flag_kernel(int64_t M, const int* __restrict__ skey, int* __restrict__ flag) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= in.M) return;
-    int g = in.sample_pidx[in.pair_src[sorted[i]]];
-    flag[i] = start[g] == (int)i ? 1 : 0;
+    if (i >= M) return;
+    flag[i] = (i == 0 || skey[i - 1] != skey[i]) ? 1 : 0;
 }
 // ids[rank of head i among heads] = point index; heads are in ascending point order, so ids is sorted and unique
-__global__ void __launch_bounds__(256) agg_head_ids_kernel(pn_agg_inputs in, const int* __restrict__ start,
-                                                           const int* __restrict__ sorted, const int* __restrict__ rank,
+__global__ void __launch_bounds__(256) agg_head_ids_kernel(int64_t M, const int* __restrict__ skey, const int* __restrict__ rank,
                                                            int* __restrict__ ids, int* __restrict__ n_touched) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0 && n_touched) n_touched[0] = rank[in.M];
-    if (i >= in.M) return;
-    int g = in.sample_pidx[in.pair_src[sorted[i]]];
-    if (start[g] == (int)i) ids[rank[i]] = g;
+    if (i == 0 && n_touched) n_touched[0] = rank[M];
+    if (i >= M) return;
+    if (i == 0 || skey[i - 1] != skey[i]) ids[rank[i]] = skey[i];
 }
 
 }  // namespace pn

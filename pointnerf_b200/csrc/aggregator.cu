@@ -74,7 +74,7 @@ struct BwdWs {
     float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
     float *GA, *GB, *GSa, *GSb, *galpha, *PG, *tn, *apart;
     char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
-    int *cnt, *rank, *tmp, *sorted, *scan, *hflag, *hscan;
+    int *cnt, *rank, *tmp, *sorted, *skey, *scan, *hflag, *hscan;
     int nblk_reduce;
     int64_t chunk;
 };
@@ -133,6 +133,7 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     t.rank = c.take<int>(m);
     t.tmp = c.take<int>(m);
     t.sorted = c.take<int>(m);
+    t.skey = c.take<int>(m);
     t.scan = c.take<int>(scan_scratch_elems_i32(tt + 1));
     t.hflag = c.take<int>(m + 1);
     t.hscan = c.take<int>(scan_scratch_elems_i32(m + 1));
@@ -182,17 +183,17 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
 
     const bool tcp = mlp_path() == 1;
     if (tcp) {
-        PN_TRY(pack_nt_image(w->block1_0_w, d.in1, 1, d.W, d.in1, d.W, d.in1p, ws.I1a, st));
-        PN_TRY(pack_nt_image(w->block1_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I1b, st));
-        PN_TRY(pack_nt_image(w->block3_0_w, d.in3, 1, d.W, d.in3, d.W, d.in3p, ws.I3a, st));
-        PN_TRY(pack_nt_image(w->block3_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I3b, st));
-        PN_TRY(pack_nt_image(w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0, st));
-        PN_TRY(pack_nt_image(w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2, st));
-        PN_TRY(pack_nt_image(w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4, st));
+        const PackJob jobs[7] = {{w->block1_0_w, d.in1, 1, d.W, d.in1, d.W, d.in1p, ws.I1a}, {w->block1_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I1b},
+                                 {w->block3_0_w, d.in3, 1, d.W, d.in3, d.W, d.in3p, ws.I3a}, {w->block3_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I3b},
+                                 {w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0},  {w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2},
+                                 {w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4}};
+        PN_TRY(pack_nt_images(jobs, 7, st));
     }
     auto with_img = [&](GemmNT g, const char* img) { g.Bimg = tcp ? img : nullptr; return g; };
     agg_prep_kernel<<<(unsigned)cdiv(S * 32, 256), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
     PN_LAUNCH_CHECK("agg_prep");
+    agg_prep_rows_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
+    PN_LAUNCH_CHECK("agg_prep_rows");
     PN_TRY(gemm_nt(with_img(nt(sv.X1, d.in1p, ws.W1a, d.in1p, sv.H1, d.W, M, d.W, d.in1p, w->block1_0_b, 1, d.slope), ws.I1a), st));
     PN_TRY(gemm_nt(with_img(nt(sv.H1, d.W, w->block1_2_w, d.W, sv.X3, d.in3p, M, d.W, d.W, w->block1_2_b, 1, d.slope), ws.I1b), st));
     PN_TRY(gemm_nt(with_img(nt(sv.X3, d.in3p, ws.W3a, d.in3p, sv.H3, d.W, M, d.W, d.in3p, w->block3_0_b, 1, d.slope), ws.I3a), st));
@@ -252,13 +253,11 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // transposed (K-contiguous over the OUTPUT index) weight copies for the data-gradient GEMMs
     const bool tcp = mlp_path() == 1;
     if (tcp) {   // images of W^T: B[n = input column, k = output unit] = W[k, n]
-        PN_TRY(pack_nt_image(w->block1_0_w, 1, d.in1, d.in1, d.W, d.in1p, d.W, ws.J1a, st));
-        PN_TRY(pack_nt_image(w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b, st));
-        PN_TRY(pack_nt_image(w->block3_0_w, 1, d.in3, d.in3, d.W, d.in3p, d.W, ws.J3a, st));
-        PN_TRY(pack_nt_image(w->block3_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J3b, st));
-        PN_TRY(pack_nt_image(w->color_0_w, 1, d.inc, d.inc, d.C, d.incp, d.C, ws.Jc0, st));
-        PN_TRY(pack_nt_image(w->color_2_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc2, st));
-        PN_TRY(pack_nt_image(w->color_4_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc4, st));
+        const PackJob jobs[7] = {{w->block1_0_w, 1, d.in1, d.in1, d.W, d.in1p, d.W, ws.J1a}, {w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b},
+                                 {w->block3_0_w, 1, d.in3, d.in3, d.W, d.in3p, d.W, ws.J3a}, {w->block3_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J3b},
+                                 {w->color_0_w, 1, d.inc, d.inc, d.C, d.incp, d.C, ws.Jc0},  {w->color_2_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc2},
+                                 {w->color_4_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc4}};
+        PN_TRY(pack_nt_images(jobs, 7, st));
     } else {
         PN_TRY(transpose_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1aT, d.W, d.in1p, st));
         PN_TRY(transpose_pad(w->block1_2_w, d.W, d.W, d.W, ws.W1bT, d.W, d.W, st));
@@ -355,16 +354,16 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         PN_TRY(scan_exclusive_i32(ws.cnt, ws.cnt, T, true, ws.scan, st));
         agg_key_place_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.rank, ws.tmp);
         PN_LAUNCH_CHECK("agg_key_place");
-        agg_key_order_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.tmp, ws.sorted);
+        agg_key_order_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.tmp, ws.sorted, ws.skey);
         PN_LAUNCH_CHECK("agg_key_order");
-        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, ws.cnt, ws.sorted, ws.PG, pgw, g_emb, g_color,
+        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, ws.skey, ws.sorted, ws.PG, pgw, g_emb, g_color,
                                                                                g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_segment_reduce");
         if (touched_ids) {   // sorted unique list of the table rows that received gradient
-            agg_head_flag_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.sorted, ws.hflag);
+            agg_head_flag_kernel<<<mb, 256, 0, st>>>(M, ws.skey, ws.hflag);
             PN_LAUNCH_CHECK("agg_head_flag");
             PN_TRY(scan_exclusive_i32(ws.hflag, ws.hflag, M, true, ws.hscan, st));
-            agg_head_ids_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.sorted, ws.hflag, touched_ids, n_touched);
+            agg_head_ids_kernel<<<mb, 256, 0, st>>>(M, ws.skey, ws.hflag, touched_ids, n_touched);
             PN_LAUNCH_CHECK("agg_head_ids");
         }
     }

@@ -90,7 +90,51 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
 
 // Backward.  Pass 1 (forward order): per live sample dot = <g_color, f_s>, and g_f[s,1:] = w_s*g_color.
 // Pass 2 (reverse order): suffix sums give d/d(a_j); density gradient written to g_f[s,0].
+// row_slot[row] = slot (ray * SR + s) of every compact feature row: inverse of slot_row
+__global__ void __launch_bounds__(256) slot_invert_kernel(const int* __restrict__ slot_row, int64_t n_slots, int64_t n_rows,
+                                                          int* __restrict__ row_slot) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_slots) return;
+    int r = slot_row[i];
+    if (r >= 0 && r < n_rows) row_slot[r] = (int)i;
+}
+// Pass 1 over the COMPACT layout, one warp per feature row (no walk along the ray: a ray crossing a dense region owns
+// up to SR rows and a per-ray walk pays one DRAM round trip per row, in sequence).
 template <int NC>
+__global__ void __launch_bounds__(256) composite_bwd_rows_kernel(const float* __restrict__ feat, const uint8_t* __restrict__ valid,
+                                                                 const int* __restrict__ row_slot, const float* __restrict__ opacity,
+                                                                 const float* __restrict__ acc_T, const float* __restrict__ g_color,
+                                                                 int64_t n_rows, int SR, int C, float* __restrict__ g_feat) {
+    int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (row >= n_rows) return;
+    const int C1 = C + 1;
+    const int64_t slot = row_slot[row];
+    float* grow = g_feat + row * C1;
+    if (slot < 0) {                                     // row referenced by no slot: zero gradient
+        for (int c = lane; c < C1; c += 32) grow[c] = 0.f;
+        return;
+    }
+    const int64_t ray = slot / SR;
+    const float T = acc_T[slot], o = opacity[slot];
+    const bool live = g_color && valid[slot] != 0 && T >= kTermT;
+    const float w = o * T;
+    const float* frow = feat + row * C1;
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NC; ++i) {
+        int c = lane + 32 * i;
+        if (c < C) {
+            float gc = g_color ? g_color[ray * C + c] : 0.f;
+            if (live) dot = fmaf(gc, frow[1 + c], dot);
+            grow[1 + c] = w * gc;
+        }
+    }
+    if (live) dot = warp_sum(dot);
+    if (lane == 0) grow[0] = live ? dot : 0.f;          // parked for pass 2, as in the per-ray kernel
+}
+
+template <int NC, bool PASS1>
 __global__ void __launch_bounds__(256) composite_bwd_kernel(
     const float* __restrict__ feat, const float* __restrict__ dist, const uint8_t* __restrict__ valid,
     const int* __restrict__ slot_row, const float* __restrict__ bg, const float* __restrict__ opacity, const float* __restrict__ acc_T,
@@ -114,7 +158,7 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
     float G_P = (g_bg_T ? g_bg_T[ray] : 0.f) + gbg;
 
     // pass 1: lanes fetch the per-sample scalars of 32 samples at once, then the warp walks the samples that own a row
-    for (int s0 = 0; s0 < SR; s0 += 32) {
+    for (int s0 = 0; PASS1 && s0 < SR; s0 += 32) {
         const int sl = s0 + lane;
         int64_t row_l = -1;
         float T_l = 0.f, o_l = 0.f;
@@ -291,29 +335,45 @@ extern "C" int pn_composite_forward(const float* ray_features, const float* ray_
     return PN_OK;
 }
 
-extern "C" int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C) {
+static int64_t bg_partial_bytes(int64_t n_rays, int32_t C) {
     int64_t r = n_rays > 0 ? n_rays : 1;
     return align_up(cdiv(r, kBgRaysPerBlock) * (int64_t)C * 4, 256) + 256;
+}
+extern "C" int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C, int64_t n_rows) {
+    return bg_partial_bytes(n_rays, C) + align_up((n_rows > 0 ? n_rows : 0) * 4, 256);
 }
 
 extern "C" int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
                                      const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T, const float* bg_T,
                                      const float* g_ray_color, const float* g_opacity, const float* g_acc_T,
                                      const float* g_blend_w, const float* g_bg_T, int64_t n_rays, int32_t SR, int32_t C,
-                                     float* g_features, float* g_bg_color, void* workspace, int64_t workspace_bytes,
-                                     void* stream) {
+                                     int64_t n_rows, float* g_features, float* g_bg_color, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
     PN_CHECK_ARG(ray_features && ray_dist && ray_valid && opacity && acc_T && bg_T && g_features, "pn_composite_backward: null argument");
     PN_CHECK_ARG(C >= 1 && C <= 256 && SR > 0, "pn_composite_backward: C=%d SR=%d unsupported", C, SR);
-    PN_CHECK_ARG(workspace_bytes >= pn_composite_workspace_bytes(n_rays, C), "pn_composite_backward: workspace too small");
+    PN_CHECK_ARG(workspace_bytes >= pn_composite_workspace_bytes(n_rays, C, slot_row ? n_rows : 0), "pn_composite_backward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
     if (n_rays <= 0) {
         if (g_bg_color) PN_CUDA(cudaMemsetAsync(g_bg_color, 0, C * sizeof(float), st));
         return PN_OK;
     }
     unsigned blocks = (unsigned)cdiv(n_rays * 32, 256);
-    PN_DISPATCH_NC(C, (composite_bwd_kernel<NC><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, slot_row, bg_color, opacity, acc_T,
-                                                                      bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w, g_bg_T,
-                                                                      n_rays, SR, C, g_features)));
+    if (slot_row && n_rows > 0) {   // compact layout: pass 1 runs one warp per feature row, the per-ray kernel keeps pass 2
+        int* row_slot = (int*)((char*)workspace + bg_partial_bytes(n_rays, C));
+        PN_CUDA(cudaMemsetAsync(row_slot, 0xFF, n_rows * sizeof(int), st));
+        slot_invert_kernel<<<(unsigned)cdiv(n_rays * SR, 256), 256, 0, st>>>(slot_row, n_rays * SR, n_rows, row_slot);
+        PN_LAUNCH_CHECK("slot_invert");
+        PN_DISPATCH_NC(C, (composite_bwd_rows_kernel<NC><<<(unsigned)cdiv(n_rows * 32, 256), 256, 0, st>>>(
+                              ray_features, ray_valid, row_slot, opacity, acc_T, g_ray_color, n_rows, SR, C, g_features)));
+        PN_LAUNCH_CHECK("composite_bwd_rows");
+        PN_DISPATCH_NC(C, (composite_bwd_kernel<NC, false><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, slot_row, bg_color, opacity,
+                                                                                 acc_T, bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w,
+                                                                                 g_bg_T, n_rays, SR, C, g_features)));
+    } else {
+        PN_DISPATCH_NC(C, (composite_bwd_kernel<NC, true><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, slot_row, bg_color, opacity,
+                                                                                acc_T, bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w,
+                                                                                g_bg_T, n_rays, SR, C, g_features)));
+    }
     PN_LAUNCH_CHECK("composite_bwd");
     if (g_bg_color) {
         if (g_ray_color && bg_color) {

@@ -171,6 +171,25 @@ __global__ void __launch_bounds__(256) tn_reduce_kernel(const float* __restrict_
     C[(int64_t)n * ldc + k] = acc;
 }
 
+// tensor-core path: matrix and (optional) column-sum partials reduced in ONE launch, fixed order over the splits
+__global__ void __launch_bounds__(256) tn_finish_kernel(const float* __restrict__ partial, const float* __restrict__ cpartial, int splits,
+                                                        int N, int Kb, int Kout, float* __restrict__ C, int64_t ldc,
+                                                        float* __restrict__ colsum) {
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < N * Kb) {
+        int n = idx / Kb, k = idx - n * Kb;
+        if (k >= Kout) return;
+        float acc = 0.f;
+        for (int z = 0; z < splits; ++z) acc += partial[(int64_t)z * N * Kb + idx];
+        C[(int64_t)n * ldc + k] = acc;
+    } else if (colsum && idx - N * Kb < N) {
+        int n = idx - N * Kb;
+        float acc = 0.f;
+        for (int z = 0; z < splits; ++z) acc += cpartial[(int64_t)z * N + n];
+        colsum[n] = acc;
+    }
+}
+
 __global__ void __launch_bounds__(128) colsum_partial_kernel(const float* __restrict__ A, int64_t lda, int64_t M, int N,
                                                              int64_t rows_per_split, float* __restrict__ partial) {
     int n = blockIdx.x * blockDim.x + threadIdx.x;
@@ -237,12 +256,10 @@ int64_t gemm_tn_scratch_floats(int64_t M, int N, int Kb) {
 
 // second stage shared by both paths: partials are combined in split order (deterministic)
 int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st) {
-    tn_reduce_kernel<<<(unsigned)cdiv((int64_t)g.N * g.Kb, 256), 256, 0, st>>>(partial, splits, g.N, g.Kb, g.Kout, g.C, g.ldc);
-    PN_LAUNCH_CHECK("tn_reduce");
-    if (g.colsum && cpartial) {
-        colsum_final_kernel<<<(unsigned)cdiv(g.N, 128), 128, 0, st>>>(cpartial, splits, g.N, g.colsum);
-        PN_LAUNCH_CHECK("colsum_final");
-    }
+    float* cs = cpartial ? g.colsum : nullptr;
+    tn_finish_kernel<<<(unsigned)cdiv((int64_t)g.N * g.Kb + (cs ? g.N : 0), 256), 256, 0, st>>>(partial, cpartial, splits, g.N, g.Kb, g.Kout,
+                                                                                             g.C, g.ldc, cs);
+    PN_LAUNCH_CHECK("tn_finish");
     return PN_OK;
 }
 

@@ -687,6 +687,49 @@ int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int 
     return PN_OK;
 }
 
+// several images in ONE launch (blockIdx.y = job): the aggregator packs its seven weight matrices per pass
+struct PackJobDev { const float* src; int64_t s_n, s_k; int N, K, BN, n_tiles, nk; char* img; };
+struct PackBatchDev { PackJobDev j[kMaxPackJobs]; };
+__global__ void __launch_bounds__(256) pack_nt_image_batch_kernel(PackBatchDev b) {
+    const PackJobDev& d = b.j[blockIdx.y];
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t total = (int64_t)d.n_tiles * d.nk * d.BN * 8;
+    if (idx >= total) return;
+    int c = (int)(idx & 7);
+    int64_t rest = idx >> 3;
+    int r = (int)(rest % d.BN);
+    rest /= d.BN;
+    int kc = (int)(rest % d.nk);
+    int j = (int)(rest / d.nk);
+    int n = j * d.BN + r;
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        int k = kc * TBK + 4 * c + e;
+        v[e] = (n < d.N && k < d.K) ? d.src[(int64_t)n * d.s_n + (int64_t)k * d.s_k] : 0.f;
+    }
+    char* blk = d.img + ((int64_t)j * d.nk + kc) * (2 * d.BN * 128);
+    split_store(blk, blk + d.BN * 128, sw128_off(r, c), make_float4(v[0], v[1], v[2], v[3]));
+}
+int pack_nt_images(const PackJob* jobs, int n, cudaStream_t st) {
+    PN_CHECK_ARG(n >= 0 && n <= kMaxPackJobs, "pack_nt_images: at most %d jobs", kMaxPackJobs);
+    if (n == 0) return PN_OK;
+    PackBatchDev b;
+    int64_t max_total = 0;
+    for (int i = 0; i < n; ++i) {
+        PackJobDev& d = b.j[i];
+        d.src = jobs[i].src; d.s_n = jobs[i].s_n; d.s_k = jobs[i].s_k; d.N = jobs[i].N; d.K = jobs[i].K; d.img = jobs[i].img;
+        d.BN = pick_bn(jobs[i].Np, &d.n_tiles);
+        d.nk = (jobs[i].Kp + TBK - 1) / TBK;
+        int64_t total = (int64_t)d.n_tiles * d.nk * d.BN * 8;
+        if (total > max_total) max_total = total;
+    }
+    for (int i = n; i < kMaxPackJobs; ++i) b.j[i] = b.j[0];
+    pack_nt_image_batch_kernel<<<dim3((unsigned)cdiv(max_total, 256), (unsigned)n), 256, 0, st>>>(b);
+    PN_LAUNCH_CHECK("pack_nt_images");
+    return PN_OK;
+}
+
 // second stage of the TN reduction (kernels in gemm.cu)
 int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st);
 // one CTA per SM: k tiles x n tiles x splits <= 148, each split a contiguous slice of the reduction rows

@@ -92,16 +92,15 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
                                                   int64_t n_rays, int SR, int K, int n_layers, float r2,
                                                   int* __restrict__ sample_pidx, int* __restrict__ ray_any,
                                                   unsigned long long* __restrict__ n_cand) {
-    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (w >= n_rays * SR) return;
-    int64_t ray = w / SR;
-    int slot = (int)(w - ray * SR);
+    // one block per ray: its warps take the hit slots round-robin, then the block blanks the unused slots
+    const int64_t ray = blockIdx.x;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int hits = min(hit_count[ray], SR);
+    for (int i = hits * K + (int)threadIdx.x; i < SR * K; i += blockDim.x) sample_pidx[ray * SR * K + i] = -1;
+    bool any_seen = false;
+    for (int slot = wib; slot < hits; slot += nw) {
+    const int64_t w = ray * SR + slot;
     int* out = sample_pidx + w * K;
-    if (slot >= hit_count[ray]) {
-        for (int k = lane; k < K; k += 32) out[k] = -1;
-        return;
-    }
     float qx = loc_w[3 * w], qy = loc_w[3 * w + 1], qz = loc_w[3 * w + 2];
     int fx = voxel_coord(qx, g.sx, g.vx), fy = voxel_coord(qy, g.sy, g.vy), fz = voxel_coord(qz, g.sz, g.vz);
     int slot0_cell = grid_info[PN_GI_SLOT0_CELL];
@@ -161,6 +160,10 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
                 }
                 unsigned m = __ballot_sync(kFull, in);
                 while (m) {
+                    if (seen >= K) {   // slots full: only candidates closer than the current maximum can change anything,
+                        m &= __ballot_sync(kFull, in && d2 < far2);   // and that maximum never grows - drop the rest at once
+                        if (!m) break;
+                    }
                     int src = __ffs(m) - 1;
                     m &= m - 1;
                     float cd = __shfl_sync(kFull, d2, src);
@@ -194,10 +197,10 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
         if (seen >= K) break;  // tested only after a whole layer (:526)
     }
     for (int k = lane; k < K; k += 32) out[k] = my_pid[k >> 5];
-    if (lane == 0) {
-        if (seen > 0) ray_any[ray] = 1;  // benign same-value race across the ray's warps
-        if (kCount && n_cand) atomicAdd(n_cand, visited);
+    any_seen |= seen > 0;
+    if (kCount && n_cand && lane == 0) atomicAdd(n_cand, visited);
     }
+    if (lane == 0 && any_seen) ray_any[ray] = 1;  // benign same-value race across the ray's warps
 }
 
 __global__ void __launch_bounds__(256) w2pers_kernel(const float* __restrict__ xyz, int64_t n, const float* __restrict__ rot,
@@ -283,7 +286,7 @@ extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, cons
     if (n_rays <= 0) return PN_OK;
     cudaStream_t st = (cudaStream_t)stream;
     PN_CUDA(cudaMemsetAsync(ray_any, 0, n_rays * sizeof(int), st));
-    unsigned blocks = (unsigned)cdiv(n_rays * SR * 32, 256);
+    unsigned blocks = (unsigned)n_rays;
     if (n_candidates)
         knn_kernel<true><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates);

@@ -91,7 +91,8 @@ class _Composite(torch.autograd.Function):
         g_bg = torch.empty((C,), dtype=torch.float32, device=dev) if need_bg else None
         if R == 0:
             return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None, None
-        ws_bytes = lib.pn_composite_workspace_bytes(R, C)
+        n_rows = int(feats.shape[0]) if ctx.slot_row is not None else 0
+        ws_bytes = lib.pn_composite_workspace_bytes(R, C, n_rows)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         feats_k = feats if feats.numel() else feats.new_zeros((1, C1))
         g_k = g_feat if g_feat.numel() else g_feat.new_zeros((1, C1))
@@ -99,7 +100,7 @@ class _Composite(torch.autograd.Function):
                                              _lib.ptr(bg) if ctx.has_bg else None,
                                              _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(bg_T), _lib.ptr(g_color),
                                              _lib.ptr(c(g_opacity)), _lib.ptr(c(g_acc_T)), _lib.ptr(c(g_blend_w)),
-                                             _lib.ptr(c(g_bg_T)), R, SR, C, _lib.ptr(g_k), _lib.ptr(g_bg), _lib.ptr(ws),
+                                             _lib.ptr(c(g_bg_T)), R, SR, C, n_rows, _lib.ptr(g_k), _lib.ptr(g_bg), _lib.ptr(ws),
                                              ws_bytes, _lib.stream()), "pn_composite_backward")
         return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None, None
 

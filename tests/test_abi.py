@@ -41,7 +41,7 @@ def test_size_queries_need_no_gpu():
     l = _lib.lib()
     assert l.pn_grid_workspace_bytes(1000, 4096) > 0
     assert l.pn_compact_workspace_bytes(1000) > 0
-    assert l.pn_composite_workspace_bytes(4096, 128) > 0
+    assert l.pn_composite_workspace_bytes(4096, 128, 20000) > 0
     p = _lib.AggParams(32, 3, 5, 4, 256, 128, 8, 1, 80, 0.01, 1.0)
     assert l.pn_agg_saved_bytes(ctypes.byref(p), 100, 700) > 0
     assert l.pn_agg_workspace_bytes(ctypes.byref(p), 100, 700, 5000, 1) > l.pn_agg_workspace_bytes(ctypes.byref(p), 100, 700, 5000, 0)
