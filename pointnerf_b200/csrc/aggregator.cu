@@ -377,6 +377,7 @@ extern "C" int pn_set_mlp_path(int path) {
     return PN_OK;
 }
 extern "C" int pn_get_mlp_path(void) { return mlp_path(); }
+extern "C" void pn_debug_gemm_flags(int flags) { set_gemm_debug_flags(flags); }
 extern "C" int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd) { return nt_image_bytes(N, Kd); }
 extern "C" int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int32_t N,
                                 int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream) {

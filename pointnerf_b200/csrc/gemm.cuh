@@ -28,6 +28,7 @@ int gemm_nt(const GemmNT& g, cudaStream_t st);
 // layout (128-byte swizzle) so that one TMA bulk copy per K chunk stages it.
 int64_t nt_image_bytes(int Np, int Kp);
 int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int Np, int Kp, char* img, cudaStream_t st);
+void set_gemm_debug_flags(int f);   // ablation switches of the NT image kernel (results become garbage)
 constexpr int kMaxPackJobs = 8;
 struct PackJob { const float* src; int64_t s_n, s_k; int N, K, Np, Kp; char* img; };
 int pack_nt_images(const PackJob* jobs, int n, cudaStream_t st);   // same images, one launch

@@ -43,6 +43,15 @@ __device__ __forceinline__ void split_store(char* hi_base, char* lo_base, uint32
     *reinterpret_cast<float4*>(hi_base + off) = h;
     *reinterpret_cast<float4*>(lo_base + off) = l;
 }
+__device__ __forceinline__ void split_store_s(uint32_t hi_addr, uint32_t lo_addr, float4 v) {
+    float4 h, l;
+    tc::split_tf32(v.x, h.x, l.x);
+    tc::split_tf32(v.y, h.y, l.y);
+    tc::split_tf32(v.z, h.z, l.z);
+    tc::split_tf32(v.w, h.w, l.w);
+    tc::sts128(hi_addr, h);
+    tc::sts128(lo_addr, l);
+}
 // Epilogue of a 128 x BN accumulator tile.  TMEM hands every thread ONE ROW (lane = row), which would make global stores
 // 32 rows wide per instruction; the tile is therefore staged through shared memory (operand stages are free once the
 // accumulator is complete) and leaves as whole 512-byte row segments: emit(row, col, float4) with consecutive threads
@@ -51,7 +60,8 @@ template <class Emit>
 __device__ __forceinline__ void epilogue_via_smem(uint32_t tmem_d, int BN, float* stage, int t, bool have_acc, Emit emit) {
     const int warp = t >> 5, lane = t & 31, q = warp & 3, half = warp >> 2;
     const int ld = BN + 4;
-    float* myrow = stage + (q * 32 + lane) * ld;
+    const uint32_t sbase = tc::smem_u32(stage);
+    const uint32_t myrow = sbase + (uint32_t)((q * 32 + lane) * ld) * 4u;
     for (int j = half; j < (BN >> 4); j += 2) {
         float v[16];
         if (have_acc) {
@@ -62,14 +72,14 @@ __device__ __forceinline__ void epilogue_via_smem(uint32_t tmem_d, int BN, float
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-            *reinterpret_cast<float4*>(myrow + j * 16 + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            tc::sts128(myrow + (uint32_t)(j * 16 + 4 * i) * 4u, make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]));
     }
     tc::fence_before_sync();
     asm volatile("bar.sync 1, 256;" ::: "memory");
     const int c4n = BN >> 2;
     for (int idx = t; idx < TBM * c4n; idx += 256) {
         int row = idx / c4n, c4 = idx - row * c4n;
-        emit(row, 4 * c4, *reinterpret_cast<const float4*>(stage + row * ld + 4 * c4));
+        emit(row, 4 * c4, tc::lds128(sbase + (uint32_t)(row * ld + 4 * c4) * 4u));
     }
 }
 }  // namespace
@@ -262,6 +272,7 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
         }
         struct Regs { float4 a[2]; float4 b[5]; };
         Regs r0, r1;
+        const uint32_t smem_u = tc::smem_u32(smem);
         float4 csum = z4;
         auto load = [&](int kc, Regs& r) {
             const int64_t rb0 = r_begin + (int64_t)kc * TBK;
@@ -280,17 +291,20 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
         auto step = [&](int kc, Regs& cur) {
             const int s = kc & 1;
             tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
-            char* st = smem + s * stage_bytes;
+            const uint32_t st = smem_u + (uint32_t)(s * stage_bytes);
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
                 int row = ar0 + 16 * i;
-                split_store(st, st + A_BYTES, (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7), cur.a[i]);
+                const uint32_t off = (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7);
+                split_store_s(st + off, st + A_BYTES + off, cur.a[i]);
                 csum.x += cur.a[i].x; csum.y += cur.a[i].y; csum.z += cur.a[i].z; csum.w += cur.a[i].w;
             }
 #pragma unroll
             for (int i = 0; i < 5; ++i)
-                if (brow[i] < TBK)
-                    split_store(st + 2 * A_BYTES, st + 2 * A_BYTES + b_bytes, (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i], bc4[i] & 7), cur.b[i]);
+                if (brow[i] < TBK) {
+                    const uint32_t off = (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i], bc4[i] & 7);
+                    split_store_s(st + 2 * A_BYTES + off, st + 2 * A_BYTES + (uint32_t)b_bytes + off, cur.b[i]);
+                }
             tc::fence_proxy_async();
             tc::mbar_arrive(&bars[s]);
             if (kc + 2 < nk) load(kc + 2, cur);
@@ -379,24 +393,25 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
 // NT with a pre-packed B image (the product path: B is always a weight matrix).  PERSISTENT: one CTA per SM walks the
 // output tiles; the accumulator is double-buffered in TMEM (2 x 256 columns) so that the epilogue of tile i (TMEM ->
 // registers -> per-warp shared-memory transpose -> coalesced global stores) overlaps the main loop of tile i + 1.
-//   warps 0-7    stage A: global fp32 -> registers (prefetched two K chunks ahead, across tile boundaries) -> split ->
-//                swizzled smem, 2 stages
+//   warps 0-7    stage A: global fp32 -> registers (prefetched four K chunks ahead, across tile boundaries) -> split ->
+//                swizzled smem, 2 stages; warps 0-3 take the even chunks, warps 4-7 the odd ones
 //   warp  8      one thread issues the MMAs
 //   warp  9      one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
-//   warps 10-17  epilogue: TMEM lane quadrant (warp & 3), 32 rows; the two warps of a quadrant alternate 16-column
-//                chunks; the TMEM load of the next chunk and the bias / mask loads are in flight while one is stored
+//   warps 10-17  epilogue: TMEM lane quadrant (warp & 3), 32 rows; the two warps of a quadrant alternate 32-column
+//                chunks (whole 128-byte row segments per store); the activation-mask rows of the NEXT tile are
+//                prefetched into L2 while the current one is written
 // ---------------------------------------------------------------------------------------------------------------
 namespace {
 constexpr int NSA = 2, NSB = 2;
 constexpr int A_STAGE = 2 * A_BYTES;                 // 32 KB (hi | lo)
 constexpr int B_STAGE = 2 * B_BYTES;                 // 64 KB (hi | lo) at BN = 256
-constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant, alternating 16-column chunks
-constexpr int SLAB_BYTES = 32 * 16 * 4;              // per epilogue warp: 32 rows x 16 floats, 16-byte chunks XOR-swizzled
+constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant, alternating 32-column chunks
+constexpr int SLAB_BYTES = 32 * 32 * 4;              // per epilogue warp: 32 rows x 32 floats, 16-byte chunks XOR-swizzled
 constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + kEpiWarps * SLAB_BYTES + 1024 + 256;
 constexpr int kThreadsImg = kLoadThreads + 64 + 32 * kEpiWarps;
 }  // namespace
 
-__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int n_tiles_n, int n_tiles_total) {
+__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int n_tiles_n, int n_tiles_total, int dbg) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     char* smA = smem;
@@ -413,7 +428,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
     const int total_chunks = my_tiles * nk;
 
     if (t == 0) {
-        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads); tc::mbar_init(&emptyA[i], 1); }
+        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads / 2); tc::mbar_init(&emptyA[i], 1); }
         for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], kEpiWarps); }
         tc::mbar_fence_init();
@@ -426,37 +441,47 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
 
     if (warp < 8) {
         // ---------------------------------------------------------------- A staging
-        const int c = t & 7, r0 = t >> 3;
+        // Two groups of four warps alternate K chunks (group 0: even, group 1: odd).  fence.proxy.async carries a
+        // CTA-scope membar that waits for every outstanding access of the thread, prefetch loads included; with one
+        // group per chunk a thread's prefetch (issued right after its arrive, two of ITS chunks = four chunks ahead)
+        // has two chunk periods to land before the thread's next fence, so the DRAM round trip stays off the
+        // producer -> MMA critical path.
+        const int grp = warp >> 2, tt = t & 127;
+        const int c = tt & 7, r0 = tt >> 3;          // rows r0 + 16 i, 16-byte chunk c
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 ra[4], rb[4], rc[4];
-        auto load = [&](int L, float4 (&r)[4]) {
+        const uint32_t sA_u32 = tc::smem_u32(smA);
+        float4 ra[8], rb[8];
+        auto load = [&](int L, float4 (&r)[8]) {
             const int it = L / nk, kc = L - it * nk;
             const int tile = (int)blockIdx.x + it * (int)gridDim.x;
             const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM;
             const int gk = kc * TBK + 4 * c;
-            const bool kok = gk < g.Kd;
+            const bool kok = gk < g.Kd && !(dbg & 2);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int64_t m = m0 + r0 + 32 * i;
+            for (int i = 0; i < 8; ++i) {
+                int64_t m = m0 + r0 + 16 * i;
                 r[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
             }
         };
-        auto step = [&](int L, float4 (&cur)[4], float4 (&pre)[4]) {
-            if (L + 2 < total_chunks) load(L + 2, pre);
+        auto step = [&](int L, float4 (&cur)[8]) {
             const int sa = L % NSA;
             tc::mbar_wait(&emptyA[sa], ((L / NSA) & 1) ^ 1);
-            char* st = smA + sa * A_STAGE;
+            const uint32_t st = sA_u32 + (uint32_t)(sa * A_STAGE);
+            if (!(dbg & 16))
 #pragma unroll
-            for (int i = 0; i < 4; ++i) split_store(st, st + A_BYTES, sw128_off(r0 + 32 * i, c), cur[i]);
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t off = sw128_off(r0 + 16 * i, c);
+                split_store_s(st + off, st + A_BYTES + off, cur[i]);
+            }
             tc::fence_proxy_async();
             tc::mbar_arrive(&fullA[sa]);
+            if (L + 4 < total_chunks) load(L + 4, cur);
         };
-        if (total_chunks > 0) load(0, ra);
-        if (total_chunks > 1) load(1, rb);
-        for (int L = 0; L < total_chunks; L += 3) {
-            step(L, ra, rc);
-            if (L + 1 < total_chunks) step(L + 1, rb, ra);
-            if (L + 2 < total_chunks) step(L + 2, rc, rb);
+        if (grp < total_chunks) load(grp, ra);
+        if (grp + 2 < total_chunks) load(grp + 2, rb);
+        for (int L = grp; L < total_chunks; L += 4) {
+            step(L, ra);
+            if (L + 2 < total_chunks) step(L + 2, rb);
         }
     } else if (warp == 8) {
         // ---------------------------------------------------------------- MMA issue
@@ -478,6 +503,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                     const uint32_t b_hi = sB + sb * B_STAGE, b_lo = b_hi + (uint32_t)(BN * 128);
                     int ksteps = (g.Kd - kc * TBK + 7) >> 3;
                     if (ksteps > 4) ksteps = 4;
+                    if (dbg & 1) ksteps = 0;
                     for (int k = 0; k < ksteps; ++k) {
                         const uint32_t ko = 32u * k;
                         uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
@@ -503,6 +529,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                 for (int kc = 0; kc < nk; ++kc, ++L) {
                     const int sb = L % NSB;
                     tc::mbar_wait(&emptyB[sb], ((L / NSB) & 1) ^ 1);
+                    if (dbg & 4) { tc::mbar_arrive(&fullB[sb]); continue; }
                     tc::mbar_arrive_expect_tx(&fullB[sb], b_block);
                     tc::bulk_g2s(smB + sb * B_STAGE, src + (int64_t)kc * b_block, b_block, &fullB[sb]);
                 }
@@ -513,58 +540,74 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
         // ---------------------------------------------------------------- epilogue (warps 10..17)
         const int q = warp & 3;                       // TMEM lane quadrant this warp may access
         const int half = (warp - 10) >> 2;            // chunks j with (j & 1) == half
-        float* slab = reinterpret_cast<float*>(slabs + (warp - 10) * SLAB_BYTES);
+        const uint32_t slab = tc::smem_u32(slabs + (warp - 10) * SLAB_BYTES);
         const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
                             (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
                             (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
-        const int rsub = lane >> 2, c4 = lane & 3;    // store phase: 8 rows x 64 B per instruction
-        const int nch = (BN + 15) >> 4;
-        const int my_last = ((nch - 1 - half) & ~1) + half;            // last chunk of this warp (may be < half: none)
+        const int rsub = lane >> 3, c8 = lane & 7;    // store phase: 4 rows x 128 B per instruction
+        const int nch = (BN + 31) >> 5;
+        const int my_last = ((nch - 1 - half) & ~1) + half;            // last chunk of this warp (< half: it owns none)
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        // lane = row: one 128-byte line of the mask matrix per (row, chunk) of a tile, pulled into L2 ahead of its use
+        auto prefetch_aux = [&](int tile) {
+            if (!g.aux) return;
+            const int64_t m = (int64_t)(tile / n_tiles_n) * TBM + q * 32 + lane;
+            const int n0 = (tile % n_tiles_n) * BN;
+            if (m >= g.M) return;
+            for (int j = half; j < nch; j += 2) {
+                const int n = n0 + j * 32;
+                if (n < g.aux_cols) asm volatile("prefetch.global.L2 [%0];" ::"l"(g.aux + m * g.ldaux + n));
+            }
+        };
+        if (my_tiles > 0) prefetch_aux((int)blockIdx.x);
         for (int it = 0; it < my_tiles; ++it) {
             const int ab = it & 1;
             const int tile = (int)blockIdx.x + it * (int)gridDim.x;
             const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM + q * 32;
             const int n0 = (tile % n_tiles_n) * BN;
+            if (it + 1 < my_tiles) prefetch_aux(tile + (int)gridDim.x);
             tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
-            uint32_t cur[16], nxt[16];
-            if (half < nch) tc::tmem_ld16_issue(taddr + (uint32_t)(half * 16), cur);
             for (int j = half; j < nch; j += 2) {
-                const int n = n0 + j * 16 + 4 * c4;
-                const bool ncol_ok = (j * 16 + 4 * c4 < BN) && n < g.N;
-                // global operands of this chunk first: their latency hides behind the TMEM wait and the transpose
-                float4 bias4 = z4, aux4[4];
-                if (vec_ok && ncol_ok) {
-                    if (g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
-                    if (g.aux && n < g.aux_cols) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const int64_t m = m0 + 8 * i + rsub;
-                            aux4[i] = m < g.M ? __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n)) : z4;
-                        }
-                    }
-                }
+                uint32_t lo16[16], hi16[16];
+                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32), lo16);
+                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32 + 16), hi16);   // columns past BN: inside the 256 allocated, masked below
+                const int n = n0 + j * 32 + 4 * c8;
+                const bool ncol_ok = (j * 32 + 4 * c8 < BN) && n < g.N;
+                float4 bias4 = z4;
+                if (vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
                 tc::tmem_ld_wait();
-                if (j + 2 < nch) tc::tmem_ld16_issue(taddr + (uint32_t)((j + 2) * 16), nxt);
                 if (j == my_last) {                   // accumulator fully read by this warp: hand it back to the MMA warp
                     tc::fence_before_sync();
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
                 }
 #pragma unroll
-                for (int i = 0; i < 4; ++i)           // row = lane; chunk i lands at i ^ ((lane >> 1) & 3): conflict-free both ways
-                    *reinterpret_cast<float4*>(slab + lane * 16 + 4 * (i ^ ((lane >> 1) & 3))) =
-                        make_float4(__uint_as_float(cur[4 * i]), __uint_as_float(cur[4 * i + 1]), __uint_as_float(cur[4 * i + 2]),
-                                    __uint_as_float(cur[4 * i + 3]));
+                for (int i = 0; i < 4; ++i) {         // row = lane; 16-byte chunk i lands at i ^ (lane & 7): conflict-free both ways
+                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u,
+                               make_float4(__uint_as_float(lo16[4 * i]), __uint_as_float(lo16[4 * i + 1]), __uint_as_float(lo16[4 * i + 2]),
+                                           __uint_as_float(lo16[4 * i + 3])));
+                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u,
+                               make_float4(__uint_as_float(hi16[4 * i]), __uint_as_float(hi16[4 * i + 1]), __uint_as_float(hi16[4 * i + 2]),
+                                           __uint_as_float(hi16[4 * i + 3])));
+                }
                 __syncwarp();
+                const bool use_aux = vec_ok && ncol_ok && g.aux && n < g.aux_cols;
+                float4 aux4[8];
+                if (use_aux) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int row = 8 * i + rsub;
+                    for (int i = 0; i < 8; ++i) {
+                        const int64_t m = m0 + 4 * i + rsub;
+                        aux4[i] = m < g.M ? __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n)) : z4;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int row = 4 * i + rsub;
                     const int64_t m = m0 + row;
-                    float4 x4 = *reinterpret_cast<const float4*>(slab + row * 16 + 4 * (c4 ^ ((row >> 1) & 3)));
-                    if (m >= g.M || !ncol_ok) continue;
+                    float4 x4 = tc::lds128(slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u);
+                    if (m >= g.M || !ncol_ok || (dbg & 8)) continue;
                     float x[4] = {x4.x, x4.y, x4.z, x4.w};
                     if (vec_ok) {
                         x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
@@ -572,7 +615,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
 #pragma unroll
                             for (int e = 0; e < 4; ++e) x[e] = x[e] > 0.f ? x[e] : g.slope * x[e];
                         }
-                        if (g.aux && n < g.aux_cols) {
+                        if (use_aux) {
                             const float4 a = aux4[i];
                             x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
                             x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
@@ -591,10 +634,8 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                     }
                 }
                 __syncwarp();
-#pragma unroll
-                for (int i = 0; i < 16; ++i) cur[i] = nxt[i];
             }
-            if (my_last < half) {                     // this warp owns no chunk of the tile (BN <= 16): still release
+            if (my_last < half) {                     // this warp owns no chunk of the tile (BN <= 32): still release
                 tc::fence_before_sync();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
@@ -640,6 +681,9 @@ static int pick_bn(int N, int* n_tiles) {
 }
 static int tmem_cols_for(int bn) { return bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256; }
 
+static int g_gemm_dbg = 0;   // bench-only ablation switches of the NT image kernel (pn_debug_gemm_flags)
+void set_gemm_debug_flags(int f) { g_gemm_dbg = f; }
+
 int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
     PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0 && g.ldb % 4 == 0, "gemm_nt_tc: operands must be padded to 4 (Kd %d lda %lld ldb %lld)",
                  g.Kd, (long long)g.lda, (long long)g.ldb);
@@ -662,7 +706,7 @@ int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
         }
         int total = (int)(cdiv(g.M, TBM) * n_tiles);
         int ctas = total < kNumSMs ? total : kNumSMs;
-        gemm_nt_img_kernel<<<ctas, kThreadsImg, IMG_SMEM, st>>>(g, bn, n_tiles, total);
+        gemm_nt_img_kernel<<<ctas, kThreadsImg, IMG_SMEM, st>>>(g, bn, n_tiles, total, g_gemm_dbg);
         PN_LAUNCH_CHECK("gemm_nt_img");
         return PN_OK;
     }
