@@ -271,6 +271,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",
+                    help="do not queue the next batch's sampling/query between this batch's forward and backward")
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--rays", type=int, default=4096, help="rays per batch per GPU")
     ap.add_argument("--cpu-rays", type=int, default=1024, help="rays per CPU-oracle step (bounded sample)")
@@ -330,8 +332,10 @@ def main():
     global_rays = args.rays * world
 
     def step(i):
-        b = dev_batches[i % n_pool]
-        return stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays)
+        # the training loop hands the NEXT batch along: its sampling / neighbour query is queued between this batch's
+        # forward and backward (RayShardedStep.prefetch), so every step still runs one full query + forward + backward
+        b, nb = dev_batches[i % n_pool], (dev_batches[(i + 1) % n_pool] if args.prefetch else None)
+        return stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, next_batch=nb)
 
     def sync_all():
         if world > 1:
@@ -365,9 +369,16 @@ def main():
     h2d = sum(int(t_.numel()) * t_.element_size() for t_ in (pinned[0]["raydir"], pinned[0]["uniform"], pinned[0]["gt"]) if t_ is not None)
     h2d += (3 + 9) * 4
 
+    e2e_next = {}
+
     def e2e_step(i):
-        b = to_dev(pinned[i % n_pool], dev, non_blocking=True)
-        loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays)
+        # step i uses the device copy made (from pinned host memory, inside the timed region) during step i - 1 when
+        # prefetching; the H2D of batch i + 1 is issued before this step's kernels so that its sampling can be queued
+        b = e2e_next.pop(i, None) or to_dev(pinned[i % n_pool], dev, non_blocking=True)
+        nb = None
+        if args.prefetch:
+            nb = e2e_next[i + 1] = to_dev(pinned[(i + 1) % n_pool], dev, non_blocking=True)
+        loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, next_batch=nb)
         return float(loss.item())           # D2H read of the step's result
 
     for w in range(2):

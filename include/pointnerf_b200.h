@@ -254,6 +254,11 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
  *   pn_rows_merge: gathered [n_ranks, cap, F+8] (all-gather of the packed buffers): every touched table row
  *                  becomes the sum over ranks IN RANK ORDER (bit-identical on every replica, no atomics).
  * ---------------------------------------------------------------------------------------------- */
+/* count[0] = number of distinct table rows referenced by sample_pidx int32[n] (-1 = empty): the touched-row count of the
+ * coming backward, available as soon as the neighbour query is - ranks agree on the exchange capacity without a host
+ * sync after the backward.  mark: int32[n_points] scratch. */
+int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int64_t n_points, int32_t* mark, int32_t* count,
+                          void* stream);
 int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb,
                  const float* g_conf, const float* g_dir, const float* g_color, float* out, void* stream);
 int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, float* g_emb, float* g_conf,

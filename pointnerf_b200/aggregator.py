@@ -91,6 +91,7 @@ class _AggCall:
         self.collect_touched = False          # ask the backward for the sorted unique list of table rows it touched
         self.touched_ids = self.n_touched = None
         self.grad_flat = None                 # backward: the MLP weight gradients, one contiguous buffer
+        self.compact = None                   # optional CompactSamples built ahead of the call
 
 
 def _weights_struct(tensors):
@@ -111,25 +112,50 @@ def _inputs_struct(call, embedding, color, pdir, conf):
     return a
 
 
+class CompactSamples:
+    """Work lists of valid samples / pairs (pn_compact_samples).  The kernels and the device->host copy of the two counts
+    are queued at construction; ``counts()`` waits for that copy only - a caller that builds the lists early (the next
+    batch's sampling, queued before this batch's backward) never stalls the GPU on the read-back."""
+
+    def __init__(self, sample_pidx, n_slots, K):
+        lib = _lib.lib()
+        dev = sample_pidx.device
+        self.n_slots = n_slots
+        self._sm = None
+        if n_slots == 0:
+            z = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.sample_list, self.pair_start, self.pair_src = z, z.clone(), z.clone()
+            self.slot_row = torch.zeros(0, dtype=torch.int32, device=dev)
+            self._sm = (0, 0)
+            return
+        self.sample_list = torch.empty(max(n_slots, 1), dtype=torch.int32, device=dev)
+        self.pair_start = torch.empty(n_slots + 1, dtype=torch.int32, device=dev)
+        self.pair_src = torch.empty(max(n_slots * K, 1), dtype=torch.int32, device=dev)
+        self.slot_row = torch.empty(n_slots, dtype=torch.int32, device=dev)
+        counts = torch.empty(2, dtype=torch.int32, device=dev)
+        ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _lib.check(lib.pn_compact_samples(_lib.ptr(sample_pidx), n_slots, K, _lib.ptr(self.sample_list), _lib.ptr(self.pair_start),
+                                          _lib.ptr(self.pair_src), _lib.ptr(counts), _lib.ptr(self.slot_row), _lib.ptr(ws), ws_bytes,
+                                          _lib.stream()), "pn_compact_samples")
+        self._host = torch.empty(2, dtype=torch.int32).pin_memory()
+        self._host.copy_(counts, non_blocking=True)
+        self._event = torch.cuda.Event()
+        self._event.record(torch.cuda.current_stream(dev))
+
+    def counts(self):
+        """(S, M): valid samples and valid (sample, neighbour) pairs - the one host read-back of the aggregator."""
+        if self._sm is None:
+            self._event.synchronize()
+            self._sm = (int(self._host[0]), int(self._host[1]))
+        return self._sm
+
+
 def compact_samples(sample_pidx, n_slots, K):
-    """Work lists of valid samples / pairs (pn_compact_samples) and the one host read-back of (S, M)."""
-    lib = _lib.lib()
-    dev = sample_pidx.device
-    if n_slots == 0:
-        z = torch.zeros(1, dtype=torch.int32, device=dev)
-        return z, z.clone(), z.clone(), 0, 0, torch.zeros(0, dtype=torch.int32, device=dev)
-    sample_list = torch.empty(max(n_slots, 1), dtype=torch.int32, device=dev)
-    pair_start = torch.empty(n_slots + 1, dtype=torch.int32, device=dev)
-    pair_src = torch.empty(max(n_slots * K, 1), dtype=torch.int32, device=dev)
-    counts = torch.empty(2, dtype=torch.int32, device=dev)
-    slot_row = torch.empty(n_slots, dtype=torch.int32, device=dev)
-    ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    _lib.check(lib.pn_compact_samples(_lib.ptr(sample_pidx), n_slots, K, _lib.ptr(sample_list), _lib.ptr(pair_start),
-                                      _lib.ptr(pair_src), _lib.ptr(counts), _lib.ptr(slot_row), _lib.ptr(ws), ws_bytes,
-                                      _lib.stream()), "pn_compact_samples")
-    S, M = (int(v) for v in counts.cpu().tolist())  # the single host sync of the aggregator
-    return sample_list, pair_start, pair_src, S, M, slot_row
+    """Synchronous form: (sample_list, pair_start, pair_src, S, M, slot_row)."""
+    c = CompactSamples(sample_pidx, n_slots, K)
+    S, M = c.counts()
+    return c.sample_list, c.pair_start, c.pair_src, S, M, c.slot_row
 
 
 def _shaped(grads, shapes):
@@ -143,7 +169,9 @@ class _AggFunction(torch.autograd.Function):
         p = call.params
         dev = embedding.device
         K = p.K
-        call.sample_list, call.pair_start, call.pair_src, call.S, call.M, call.slot_row = compact_samples(call.sample_pidx, call.n_slots, K)
+        cs = call.compact if call.compact is not None else CompactSamples(call.sample_pidx, call.n_slots, K)
+        call.S, call.M = cs.counts()
+        call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
         decoded = torch.empty((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
         weight_out = torch.empty((call.n_slots, K), dtype=torch.float32, device=dev) if call.want_weight else None
         saved_bytes = lib.pn_agg_saved_bytes(ctypes.byref(p), call.S, call.M)
@@ -298,7 +326,7 @@ class PointAggregator(nn.Module):
 
     # ------------------------------------------------------------------------------------------
     def forward_tables(self, xyz, xyz_pers, embedding, color, pdir, conf, Rw2c, sample_pidx, sample_loc, sample_loc_w,
-                       ray_dirs, vsize, dirs_per_ray=True, want_weight=False, compact=False):
+                       ray_dirs, vsize, dirs_per_ray=True, want_weight=False, compact=False, work_lists=None):
         """Fused gather + aggregate.  xyz/xyz_pers [N,3], embedding [N,F], color/pdir [N,3], conf [N] - the tables may also
         keep the reference's leading batch / trailing unit axes ([1,N,F], [1,N,3], [1,N,1]): passing the parameters
         themselves makes the backward's buffers their .grad with no select-backward fill + copy of the whole table;
@@ -314,6 +342,7 @@ class PointAggregator(nn.Module):
                         Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
                         sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
         call.collect_touched = bool(getattr(self, "collect_touched", False))
+        call.compact = work_lists             # CompactSamples of sample_pidx queued earlier (None: built here, with its sync)
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
         self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)
         weight = weight.view(R, SR, K) if want_weight else None

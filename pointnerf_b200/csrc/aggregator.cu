@@ -469,6 +469,36 @@ __global__ void __launch_bounds__(256) rows_merge_kernel(const float* __restrict
 }
 }  // namespace pn
 
+namespace pn {
+__global__ void __launch_bounds__(256) rows_mark_kernel(const int* __restrict__ pidx, int64_t n, int64_t n_points, int* __restrict__ mark) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int g = pidx[i];
+    if (g >= 0 && g < n_points) mark[g] = 1;      // benign same-value race
+}
+__global__ void __launch_bounds__(256) rows_count_kernel(const int* __restrict__ mark, int64_t n_points, int* __restrict__ count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int v = i < n_points ? mark[i] : 0;
+    v = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(count, v);   // integer sum: order-independent
+}
+}  // namespace pn
+
+extern "C" int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int64_t n_points, int32_t* mark, int32_t* count,
+                                     void* stream) {
+    PN_CHECK_ARG(mark && count && n_points > 0 && (sample_pidx || n == 0), "pn_count_touched_rows: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    PN_CUDA(cudaMemsetAsync(mark, 0, n_points * sizeof(int), st));
+    PN_CUDA(cudaMemsetAsync(count, 0, sizeof(int), st));
+    if (n > 0) {
+        rows_mark_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(sample_pidx, n, n_points, mark);
+        PN_LAUNCH_CHECK("rows_mark");
+    }
+    rows_count_kernel<<<(unsigned)cdiv(n_points, 256), 256, 0, st>>>(mark, n_points, count);
+    PN_LAUNCH_CHECK("rows_count");
+    return PN_OK;
+}
+
 extern "C" int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb, const float* g_conf, const float* g_dir,
                             const float* g_color, float* out, void* stream) {
     PN_CHECK_ARG((ids || n_ids == 0) && n_ids >= 0 && g_emb && out && F >= 1 && F <= 56, "pn_rows_pack: bad argument (F <= 56)");

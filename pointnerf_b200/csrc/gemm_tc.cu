@@ -243,8 +243,8 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
     const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
 
     if (t == 0) {
-        tc::mbar_init(&bars[0], kTnLoad);
-        tc::mbar_init(&bars[1], kTnLoad);
+        tc::mbar_init(&bars[0], kTnLoad / 2);
+        tc::mbar_init(&bars[1], kTnLoad / 2);
         tc::mbar_init(&bars[2], 1);
         tc::mbar_init(&bars[3], 1);
         tc::mbar_init(&bars[4], 1);
@@ -257,63 +257,61 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
     const uint32_t tmem_d = *tmem_slot;
 
     if (warp < 16) {
+        // Two groups of eight warps alternate the 32-row chunks (group 0: even, group 1: odd): a thread reloads its ONE
+        // register set right after its arrive, so the loads have two chunk periods to land before the thread's next
+        // fence.proxy.async (whose membar waits for them) and before they are needed.
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int ac4 = t & 31, ar0 = t >> 5;      // A: 32 float4 per row (128 columns), rows ar0 + 16 i
+        const int grp = t >> 8, tt = t & 255;
+        const int ac4 = tt & 31, ar0 = tt >> 5;    // A: 32 float4 per row (128 columns), rows ar0 + 8 i
         const bool a_ok = i0 + 4 * ac4 < g.N;
         const int ncb = BKt >> 2;                  // float4 per B row (<= 72)
-        int brow[5], bc4[5];
-        bool bok[5];
+        constexpr int NB = 9;                      // 256 threads x 9 >= 32 rows x 72 float4
+        int brow[NB], bc4[NB];
 #pragma unroll
-        for (int i = 0; i < 5; ++i) {
-            int idx = t + kTnLoad * i;
-            brow[i] = idx / ncb;
-            bc4[i] = idx - brow[i] * ncb;
-            bok[i] = brow[i] < TBK && j0 + 4 * bc4[i] < g.Kb;
+        for (int i = 0; i < NB; ++i) {
+            int idx = tt + 256 * i;
+            const int br = idx / ncb;
+            bc4[i] = idx - br * ncb;
+            // -1: no shared-memory slot; bit 8: a slot (zero-filled) with no global column behind it
+            brow[i] = br >= TBK ? -1 : (br | (j0 + 4 * bc4[i] >= g.Kb ? 0x100 : 0));
         }
-        struct Regs { float4 a[2]; float4 b[5]; };
-        Regs r0, r1;
-        const uint32_t smem_u = tc::smem_u32(smem);
+        float4 ra[4], rb[NB];
         float4 csum = z4;
-        auto load = [&](int kc, Regs& r) {
+        const uint32_t smem_u = tc::smem_u32(smem);
+        auto load = [&](int kc) {
             const int64_t rb0 = r_begin + (int64_t)kc * TBK;
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                int64_t rr = rb0 + ar0 + 16 * i;
-                r.a[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
+            for (int i = 0; i < 4; ++i) {
+                int64_t rr = rb0 + ar0 + 8 * i;
+                ra[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
             }
 #pragma unroll
-            for (int i = 0; i < 5; ++i) {
-                int64_t rr = rb0 + brow[i];
-                r.b[i] = (bok[i] && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
+            for (int i = 0; i < NB; ++i) {
+                int64_t rr = rb0 + (brow[i] & 0xFF);
+                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
             }
         };
-        // two chunks are always in flight with two register sets: a set is refilled (chunk kc + 2) as soon as it is stored
-        auto step = [&](int kc, Regs& cur) {
+        if (grp < nk) load(grp);
+        for (int kc = grp; kc < nk; kc += 2) {
             const int s = kc & 1;
             tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
             const uint32_t st = smem_u + (uint32_t)(s * stage_bytes);
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                int row = ar0 + 16 * i;
+            for (int i = 0; i < 4; ++i) {
+                int row = ar0 + 8 * i;
                 const uint32_t off = (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7);
-                split_store_s(st + off, st + A_BYTES + off, cur.a[i]);
-                csum.x += cur.a[i].x; csum.y += cur.a[i].y; csum.z += cur.a[i].z; csum.w += cur.a[i].w;
+                split_store_s(st + off, st + A_BYTES + off, ra[i]);
+                csum.x += ra[i].x; csum.y += ra[i].y; csum.z += ra[i].z; csum.w += ra[i].w;
             }
 #pragma unroll
-            for (int i = 0; i < 5; ++i)
-                if (brow[i] < TBK) {
-                    const uint32_t off = (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i], bc4[i] & 7);
-                    split_store_s(st + 2 * A_BYTES + off, st + 2 * A_BYTES + (uint32_t)b_bytes + off, cur.b[i]);
+            for (int i = 0; i < NB; ++i)
+                if (brow[i] >= 0) {
+                    const uint32_t off = (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i] & 0xFF, bc4[i] & 7);
+                    split_store_s(st + 2 * A_BYTES + off, st + 2 * A_BYTES + (uint32_t)b_bytes + off, rb[i]);
                 }
             tc::fence_proxy_async();
             tc::mbar_arrive(&bars[s]);
-            if (kc + 2 < nk) load(kc + 2, cur);
-        };
-        if (nk > 0) load(0, r0);
-        if (nk > 1) load(1, r1);
-        for (int kc = 0; kc < nk; kc += 2) {
-            step(kc, r0);
-            if (kc + 1 < nk) step(kc + 1, r1);
+            if (kc + 2 < nk) load(kc + 2);
         }
       if (warp < 8) {
         // ---- epilogue: D[n, k] -> partial[split][n][k]
@@ -473,7 +471,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                 const uint32_t off = sw128_off(r0 + 16 * i, c);
                 split_store_s(st + off, st + A_BYTES + off, cur[i]);
             }
-            tc::fence_proxy_async();
+            if (!(dbg & 32)) tc::fence_proxy_async();
             tc::mbar_arrive(&fullA[sa]);
             if (L + 4 < total_chunks) load(L + 4, cur);
         };
@@ -569,6 +567,12 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
             tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
+            if (dbg & 64) {
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
+                continue;
+            }
             for (int j = half; j < nch; j += 2) {
                 uint32_t lo16[16], hi16[16];
                 tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32), lo16);

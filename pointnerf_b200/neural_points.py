@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import query as _query
-from .aggregator import PointAggregator
+from .aggregator import CompactSamples, PointAggregator
 from .query import lighting_fast_querier
 from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march, ray_march_compact
 
@@ -127,6 +127,12 @@ class NeuralPoints(nn.Module):
                 ray_mask_tensor, vsize, self.grid_vox_sz)
 
 
+class RayPlan:
+    """Weight-independent part of one batch (NeuralPointsRayMarching.sample): raw query results, perspective coordinates
+    of samples and points, and the aggregator's work lists (CompactSamples)."""
+    __slots__ = ("raw", "pidx", "loc_w", "loc_pers", "xyz_pers", "raydir", "work_lists")
+
+
 class NeuralPointsRayMarching(nn.Module):
     """Per-ray driver (neural_points_volumetric_model.py:272-389) without the 2-D neural-render tail."""
 
@@ -197,8 +203,27 @@ class NeuralPointsRayMarching(nn.Module):
         return call.sample_pidx.view(-1)[call.pair_src[:call.M].long()].long()
 
     # ---- fused path -----------------------------------------------------------------------------
+    def sample(self, campos, raydir, camrotc2w, near, far, uniform=None):
+        """Everything of one batch that does not depend on the trainable tensors: ray sampling, neighbour query,
+        perspective coordinates and the work lists, queued on the current stream with NO host sync.  ``forward(plan=...)``
+        consumes it; a training loop calls this for batch i+1 before the backward of batch i so that the (S, M)
+        read-back the aggregator needs is complete long before it is waited for."""
+        nps = self.neural_points
+        near = float(torch.as_tensor(near).min())
+        far = float(torch.as_tensor(far).max())
+        xyz = nps.xyz.detach()
+        raw = nps.querier.query_raw(xyz, raydir, campos, near, far, uniform=uniform)
+        pidx, loc_w = raw["sample_pidx"], raw["sample_loc_w"]                     # [R,SR,K], [R,SR,3]
+        R, SR, K = pidx.shape
+        plan = RayPlan()
+        plan.raw, plan.pidx, plan.loc_w, plan.raydir = raw, pidx, loc_w, raydir
+        plan.loc_pers = _query.w2pers(loc_w, camrotc2w[0], campos[0])
+        plan.xyz_pers = _query.w2pers(xyz, camrotc2w[0], campos[0])
+        plan.work_lists = CompactSamples(pidx.contiguous(), R * SR, K)
+        return plan
+
     def forward(self, campos, raydir, gt_image=None, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None,
-                focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, **kargs):
+                focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, plan=None, **kargs):
         """Same keyword interface as the reference driver (:272-286).  Returns the ``fill_invalid`` dictionary:
         coarse_raycolor [1,R,C], coarse_is_background [1,R,1], coarse_mask, coarse_point_opacity [1,R,SR],
         queried_shading [1,R,3], ray_mask int8 [1,R] (+ weight / blend_weight / conf_coefficient per sample when the
@@ -207,18 +232,15 @@ class NeuralPointsRayMarching(nn.Module):
             return self.forward_seams(campos, raydir, bg_color=bg_color, camrotc2w=camrotc2w, pixel_idx=pixel_idx, near=near,
                                       far=far, h=h, w=w, intrinsic=intrinsic, uniform=uniform, **kargs)
         o, nps = self.opt, self.neural_points
-        near = float(torch.as_tensor(near).min())
-        far = float(torch.as_tensor(far).max())
-        xyz = nps.xyz
-        raw = nps.querier.query_raw(xyz.detach(), raydir, campos, near, far, uniform=uniform)
-        pidx, loc_w = raw["sample_pidx"], raw["sample_loc_w"]                     # [R,SR,K], [R,SR,3]
+        if plan is None:
+            plan = self.sample(campos, raydir, camrotc2w, near, far, uniform=uniform)
+        raw, pidx, loc_w, loc_pers, xyz_pers = plan.raw, plan.pidx, plan.loc_w, plan.loc_pers, plan.xyz_pers
         R, SR, K = pidx.shape
-        loc_pers = _query.w2pers(loc_w, camrotc2w[0], campos[0])
-        xyz_pers = _query.w2pers(xyz.detach(), camrotc2w[0], campos[0])
         want_w = self.aggregator._want_weight()
         decoded, weight, slot_row = self.aggregator.forward_tables(
-            xyz, xyz_pers, nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf, nps.Rw2c,
-            pidx, loc_pers, loc_w, raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w, compact=True)
+            nps.xyz, xyz_pers, nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf, nps.Rw2c,
+            pidx, loc_pers, loc_w, plan.raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w, compact=True,
+            work_lists=plan.work_lists)
         ray_valid = (slot_row >= 0)[None]                                         # [1,R,SR]
         ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)
         ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march_compact(ray_dist, ray_valid, decoded, slot_row, bg_color)

@@ -96,34 +96,39 @@ class RayShardedStep:
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.nbytes = sum(p.numel() for p in self.params) * 4
         self._cap_ev = self._cap_cpu = None
+        self._plan = None
+        self._mark = None
         if self.world > 1 and sparse and hasattr(model.aggregator, "forward_tables"):
             model.aggregator.collect_touched = True     # the fused backward returns the sorted unique touched rows
 
     # ---- sparse exchange on the C ABI (CUDA tables) -------------------------------------------------------------
-    def _begin_cap_exchange(self, rest):
-        """Right after the backward: ONE small all-gather carries each rank's touched-row count (known only on the device)
-        and the gradients of the few parameters outside the tables and the MLP buffer (`rest`, e.g. the background
-        colour).  The counts go to a pinned host word; the read-back overlaps the MLP all-reduce issued next."""
+    def _begin_cap_exchange(self):
+        """Right after the forward: the number of distinct table rows the batch references (= the touched rows of the
+        coming backward) is counted on the device, max-reduced over ranks and copied to a pinned host word - all queued
+        BEFORE the backward, so the exchange after it finds the capacity on the host without stalling anything."""
+        from . import _lib
         call = getattr(self.model.aggregator, "last_call", None)
-        if call is None or call.n_touched is None:
-            return False
-        dev = call.n_touched.device
-        head = torch.cat([call.n_touched] + [p.grad.reshape(-1).view(torch.int32) for p in rest])
-        self._head_all = torch.empty((self.world, head.numel()), dtype=torch.int32, device=dev)
-        dist.all_gather_into_tensor(self._head_all, head, group=self.group)
-        if self._cap_cpu is None or self._cap_cpu.numel() != self.world:
-            self._cap_cpu = torch.zeros(self.world, dtype=torch.int32).pin_memory()
-        self._cap_cpu.copy_(self._head_all[:, 0], non_blocking=True)
+        if call is None or not call.sample_pidx.is_cuda:
+            return
+        dev = call.sample_pidx.device
+        if self._cap_cpu is None:
+            self._cap_cpu = torch.zeros(1, dtype=torch.int32).pin_memory()
+        if self._mark is None or self._mark.numel() < call.T:
+            self._mark = torch.empty(max(call.T, 1), dtype=torch.int32, device=dev)
+        cnt = torch.empty(1, dtype=torch.int32, device=dev)
+        _lib.check(_lib.lib().pn_count_touched_rows(_lib.ptr(call.sample_pidx), call.sample_pidx.numel(), call.T, _lib.ptr(self._mark),
+                                                    _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+        dist.all_reduce(cnt, op=dist.ReduceOp.MAX, group=self.group)
+        self._cap_cpu.copy_(cnt, non_blocking=True)
         self._cap_ev = torch.cuda.Event()
         self._cap_ev.record(torch.cuda.current_stream(dev))
-        return True
 
     def _sparse_tables_cuda(self, tables_by_name):
         from . import _lib
         lib = _lib.lib()
         call = self.model.aggregator.last_call
-        self._cap_ev.synchronize()                          # the one host sync of the exchange (~tens of us)
-        cap = max(256, (int(self._cap_cpu.max()) + 255) // 256 * 256)
+        self._cap_ev.synchronize()                          # queued before the backward: complete by now
+        cap = max(256, (int(self._cap_cpu[0]) + 255) // 256 * 256)
         emb = tables_by_name["points_embeding"]
         dev, F = emb.grad.device, int(emb.shape[2])
         ids, n_ids = call.touched_ids, (int(call.M) if call.touched_ids is not None else 0)   # n_touched <= M entries, -1 beyond
@@ -194,8 +199,12 @@ class RayShardedStep:
         lo, hi = (flat.data_ptr(), flat.data_ptr() + 4 * flat.numel()) if flat is not None else (0, 0)
         rest = [p for p in self.params if id(p) not in tset and not (lo <= p.grad.data_ptr() < hi)]
         mode = None
-        if self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._begin_cap_exchange(rest):
+        if self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._cap_ev is not None:
             mode = "cuda"        # ids from the fused backward, pack / merge kernels of the C ABI
+            if rest:             # one small all-gather for the few gradients outside the tables and the MLP buffer
+                head = torch.cat([p.grad.reshape(-1) for p in rest])
+                self._head_all = torch.empty((self.world, head.numel()), dtype=torch.float32, device=head.device)
+                dist.all_gather_into_tensor(self._head_all, head, group=self.group)
         elif self.sparse and hasattr(self.model, "touched_point_ids") and tables and not tables[0].is_cuda:
             pid = self.model.touched_point_ids()     # device-agnostic torch formulation (CPU tests of the host logic)
             if pid is not None and all(t.dim() == 3 and t.shape[0] == 1 for t in tables):
@@ -210,7 +219,7 @@ class RayShardedStep:
             self._sparse_tables_cuda({n: (getattr(nps, n) if getattr(nps, n) is not None and getattr(nps, n).requires_grad else None)
                                       for n in names})
             if rest:             # rank-ordered sum of the gathered head columns: identical bits on every replica
-                tot = self._head_all[:, 1:].view(torch.float32).sum(0)
+                tot = self._head_all.sum(0)
                 off = 0
                 for p in rest:
                     p.grad.copy_(tot[off:off + p.numel()].view_as(p))
@@ -229,18 +238,40 @@ class RayShardedStep:
         for h in handles:
             h.wait()
 
-    def __call__(self, cam, raydir, gt, uniform=None, global_rays=None, reduce=True):
+    def prefetch(self, cam, raydir, uniform=None):
+        """Queue the weight-independent part of a FUTURE batch (ray sampling, neighbour query, work lists) now.  Called by
+        ``__call__(next_batch=...)`` between the forward and the backward of the current batch: the GPU runs it there, and
+        the (S, M) read-back the next forward needs has completed long before the host asks for it - no idle gap."""
+        if not hasattr(self.model, "sample"):
+            return
+        plan = self.model.sample(cam["campos"], raydir, cam["camrotc2w"], cam["near"], cam["far"], uniform=uniform)
+        self._plan = (raydir, uniform, plan)
+
+    def _take_plan(self, raydir, uniform):
+        held, self._plan = self._plan, None
+        if held is not None and held[0] is raydir and held[1] is uniform:
+            return held[2]
+        return None
+
+    def __call__(self, cam, raydir, gt, uniform=None, global_rays=None, reduce=True, next_batch=None):
         """cam: dict(campos [1,3], camrotc2w [1,3,3], near, far); raydir [1,R_local,3]; gt [1,R_local,C].
+        next_batch: optional dict(cam=, raydir=, uniform=) of the batch the NEXT call will get (see ``prefetch``).
         Returns (loss_local_sum / (global_rays*C)) as a 0-d tensor (the all-reduced SUM over ranks is the batch MSE)."""
         R_local = raydir.shape[1]
         global_rays = int(global_rays if global_rays is not None else R_local * self.world)
         for p in self.params:
             p.grad = None
+        plan = self._take_plan(raydir, uniform)
+        kw = dict(plan=plan) if plan is not None else {}
         out = self.model(cam["campos"], raydir, bg_color=self.bg, camrotc2w=cam["camrotc2w"], near=cam["near"], far=cam["far"],
-                         uniform=uniform)
+                         uniform=uniform, **kw)
         self._cap_ev = None
+        if self.world > 1 and self.sparse:
+            self._begin_cap_exchange()
         diff = out["coarse_raycolor"] - gt
         loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
+        if next_batch is not None:
+            self.prefetch(next_batch["cam"], next_batch["raydir"], next_batch.get("uniform"))
         loss.backward()
         if reduce:
             self.all_reduce()

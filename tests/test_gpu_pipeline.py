@@ -119,3 +119,34 @@ def test_all_rays_miss(tiny_scene, cuda_dev):
 def test_smoke_entry(cuda_dev):
     import __graft_entry__ as ge
     ge.smoke()
+
+
+def test_prefetched_plan_gives_identical_step(tiny_scene, cuda_dev):
+    """RayShardedStep(next_batch=...) queues the next batch's sampling / query between forward and backward; the step that
+    consumes the plan must produce the same bits as a step that samples inside its own forward."""
+    from pointnerf_b200.ray_shard import RayShardedStep
+    opt, tables, cam = tiny_scene
+    opt = copy.copy(opt)
+    opt.is_train = 1
+    d = cuda_dev
+    R = 200
+    g = torch.Generator().manual_seed(4)
+    batches = []
+    for k in range(2):
+        raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, R, seed=10 + k))
+        batches.append(dict(cam=dict(campos=cam["campos"].to(d), camrotc2w=cam["camrotc2w"].to(d), near=cam["near"], far=cam["far"]),
+                            raydir=raydir.to(d), uniform=torch.rand(1, R, opt.z_depth_dim, generator=g).to(d),
+                            gt=torch.rand(1, R, opt.shading_color_channel_num, generator=g).to(d)))
+    model = _model(opt, tables, d)
+    bg = torch.nn.Parameter(torch.rand(opt.shading_color_channel_num, generator=g).to(d))
+    st = RayShardedStep(model, bg)
+    b0, b1 = batches
+    st(b0["cam"], b0["raydir"], b0["gt"], uniform=b0["uniform"], next_batch=b1)
+    assert st._plan is not None
+    l1 = st(b1["cam"], b1["raydir"], b1["gt"], uniform=b1["uniform"])           # consumes the plan
+    assert st._plan is None
+    g1 = st.flat_grads().clone()
+    l2 = st(b1["cam"], b1["raydir"], b1["gt"], uniform=b1["uniform"])           # samples inside the forward
+    g2 = st.flat_grads().clone()
+    assert torch.equal(l1, l2) and torch.equal(g1, g2)
+    assert float(g1.abs().max()) > 0

@@ -71,3 +71,18 @@ def test_backward_reports_touched_rows(cuda_dev, tiny_scene):
     assert bool((call.touched_ids[n:] == -1).all())
     nz = torch.nonzero(leaves["points_embeding"].grad[0].abs().sum(-1)).flatten().cpu()
     assert set(nz.tolist()) <= set(want.long().tolist())
+
+
+def test_count_touched_rows(cuda_dev):
+    lib = _lib.lib()
+    d, N = cuda_dev, 50000
+    g = torch.Generator().manual_seed(1)
+    pidx = torch.randint(0, N, (3000, 8), generator=g, dtype=torch.int32)
+    pidx[torch.rand(3000, 8, generator=g) < 0.7] = -1
+    mark = torch.empty(N, dtype=torch.int32, device=d)
+    cnt = torch.empty(1, dtype=torch.int32, device=d)
+    pd = pidx.to(d)
+    _lib.check(lib.pn_count_touched_rows(_lib.ptr(pd), pd.numel(), N, _lib.ptr(mark), _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+    assert int(cnt.item()) == torch.unique(pidx[pidx >= 0]).numel()
+    _lib.check(lib.pn_count_touched_rows(None, 0, N, _lib.ptr(mark), _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+    assert int(cnt.item()) == 0
