@@ -369,27 +369,46 @@ def main():
     h2d = sum(int(t_.numel()) * t_.element_size() for t_ in (pinned[0]["raydir"], pinned[0]["uniform"], pinned[0]["gt"]) if t_ is not None)
     h2d += (3 + 9) * 4
 
-    e2e_next = {}
+    e2e_next, e2e_pending = {}, []
+    loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    e2e_losses = []
 
     def e2e_step(i):
         # step i uses the device copy made (from pinned host memory, inside the timed region) during step i - 1 when
-        # prefetching; the H2D of batch i + 1 is issued before this step's kernels so that its sampling can be queued
+        # prefetching; the H2D of batch i + 1 is issued before this step's kernels so that its sampling can be queued.
+        # The loss of every step is copied to pinned host memory inside the step and read by the host one step later
+        # (asynchronous logging): the host never drains the GPU queue in the middle of the loop.
         b = e2e_next.pop(i, None) or to_dev(pinned[i % n_pool], dev, non_blocking=True)
         nb = None
         if args.prefetch:
             nb = e2e_next[i + 1] = to_dev(pinned[(i + 1) % n_pool], dev, non_blocking=True)
         loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, next_batch=nb)
-        return float(loss.item())           # D2H read of the step's result
+        buf = loss_host[i % 2]
+        buf.copy_(loss.reshape(1), non_blocking=True)          # D2H read of the step's result
+        ev = torch.cuda.Event()
+        ev.record()
+        e2e_pending.append((ev, buf))
+        if len(e2e_pending) > 1:
+            e2e_drain(1)
+
+    def e2e_drain(keep):
+        while len(e2e_pending) > keep:
+            ev, buf = e2e_pending.pop(0)
+            ev.synchronize()
+            e2e_losses.append(float(buf[0]))
 
     for w in range(2):
         e2e_step(w)
+    e2e_drain(0)
     sync_all()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     for s in range(args.steps):
         e2e_step(2 + s)
+    e2e_drain(0)                 # the last step's loss is on the host before the timer stops
     f1.record()
     sync_all()
+    assert len(e2e_losses) == args.steps + 2 and all(np.isfinite(v) for v in e2e_losses)
     t = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
