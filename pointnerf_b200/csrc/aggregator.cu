@@ -419,52 +419,30 @@ __global__ void __launch_bounds__(256) rows_pack_kernel(const int* __restrict__ 
     }
     out[idx] = v;
 }
-// One warp per (rank r, row u) of the gathered buffer [G, cap, W].  Each rank's id list is sorted and unique.  The warp of
-// the LOWEST rank that holds an id owns that table row: it adds the contributions of the higher ranks in rank order
-// (binary search per rank) and stores the sum - every replica computes bit-identical rows.
-__global__ void __launch_bounds__(256) rows_merge_kernel(const float* __restrict__ all, int G, int64_t cap, int F, float* __restrict__ g_emb,
-                                                         float* __restrict__ g_conf, float* __restrict__ g_dir, float* __restrict__ g_color) {
+// Merge of the gathered buffer [G, cap, W] into the dense tables.  Each rank's id list is unique, so "add rank r's rows" is
+// race-free; the ranks are added one launch after the other IN RANK ORDER onto rows zeroed first - every replica computes
+// (((0 + g0) + g1) + ...) and therefore identical bits, with no search and no atomics.  mode 0: zero the row; 1: add.
+__global__ void __launch_bounds__(256) rows_apply_kernel(const float* __restrict__ rows, int64_t n_rows, int F, int mode,
+                                                         float* __restrict__ g_emb, float* __restrict__ g_conf,
+                                                         float* __restrict__ g_dir, float* __restrict__ g_color) {
     const int W = F + 8;
     int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
-    if (wid >= (int64_t)G * cap) return;
-    int r = (int)(wid / cap);
-    const float* mine = all + wid * W;
-    int g = __float_as_int(mine[0]);
+    if (wid >= n_rows) return;
+    const float* mine = rows + wid * W;
+    const int g = __float_as_int(mine[0]);
     if (g < 0) return;
-    auto find = [&](int rr) -> int64_t {     // position of id g in rank rr's list, or -1
-        const float* base = all + (int64_t)rr * cap * W;
-        int64_t lo = 0, hi = cap;            // valid ids first (ascending), then -1 padding
-        while (lo < hi) {
-            int64_t mid = (lo + hi) >> 1;
-            int v = __float_as_int(base[mid * W]);
-            if (v < 0 || v > g) hi = mid; else if (v < g) lo = mid + 1; else return mid;
-        }
-        return -1;
-    };
-    for (int rr = 0; rr < r; ++rr)
-        if (find(rr) >= 0) return;           // a lower rank owns this row
-    float acc[2] = {0.f, 0.f};               // W - 1 <= 64 columns: two per lane
-    for (int i = 0; i < 2; ++i) {
-        int c = lane + 32 * i;
-        if (c < W - 1) acc[i] = mine[1 + c];
-    }
-    for (int rr = r + 1; rr < G; ++rr) {
-        int64_t pos = find(rr);
-        if (pos < 0) continue;
-        const float* o = all + ((int64_t)rr * cap + pos) * W;
-        for (int i = 0; i < 2; ++i) {
-            int c = lane + 32 * i;
-            if (c < W - 1) acc[i] += o[1 + c];
-        }
-    }
-    for (int i = 0; i < 2; ++i) {
-        int k = lane + 32 * i;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {            // W - 1 <= 64 columns: two per lane
+        const int k = lane + 32 * i;
         if (k >= W - 1) continue;
-        if (k < F) g_emb[(int64_t)g * F + k] = acc[i];
-        else if (k == F) { if (g_conf) g_conf[g] = acc[i]; }
-        else if (k < F + 4) { if (g_dir) g_dir[(int64_t)g * 3 + (k - F - 1)] = acc[i]; }
-        else if (g_color) g_color[(int64_t)g * 3 + (k - F - 4)] = acc[i];
+        float* dst;
+        if (k < F) dst = g_emb + (int64_t)g * F + k;
+        else if (k == F) dst = g_conf ? g_conf + g : nullptr;
+        else if (k < F + 4) dst = g_dir ? g_dir + (int64_t)g * 3 + (k - F - 1) : nullptr;
+        else dst = g_color ? g_color + (int64_t)g * 3 + (k - F - 4) : nullptr;
+        if (!dst) continue;
+        *dst = mode == 0 ? 0.f : *dst + mine[1 + k];
     }
 }
 }  // namespace pn
@@ -511,8 +489,14 @@ extern "C" int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap
                              float* g_color, void* stream) {
     PN_CHECK_ARG(gathered && g_emb && n_ranks >= 1 && F >= 1 && F <= 56, "pn_rows_merge: bad argument (F <= 56)");
     if (cap <= 0) return PN_OK;
-    rows_merge_kernel<<<(unsigned)cdiv((int64_t)n_ranks * cap * 32, 256), 256, 0, (cudaStream_t)stream>>>(gathered, n_ranks, cap, F, g_emb,
-                                                                                                  g_conf, g_dir, g_color);
-    PN_LAUNCH_CHECK("rows_merge");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t all_rows = (int64_t)n_ranks * cap;
+    rows_apply_kernel<<<(unsigned)cdiv(all_rows * 32, 256), 256, 0, st>>>(gathered, all_rows, F, 0, g_emb, g_conf, g_dir, g_color);
+    PN_LAUNCH_CHECK("rows_zero");
+    for (int r = 0; r < n_ranks; ++r) {
+        rows_apply_kernel<<<(unsigned)cdiv(cap * 32, 256), 256, 0, st>>>(gathered + (int64_t)r * cap * (F + 8), cap, F, 1, g_emb, g_conf,
+                                                                       g_dir, g_color);
+        PN_LAUNCH_CHECK("rows_add");
+    }
     return PN_OK;
 }
