@@ -120,6 +120,12 @@ int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_params* para
  *   sample_t      float[R, SR] or NULL  depth t of kept samples (0 unused)
  *   hit_count     int32[R]  number of kept samples (<= SR); ray_mask of :655 is hit_count > 0
  * ---------------------------------------------------------------------------------------------- */
+/* Jittered candidate depths (the per-ray part of near_far_linear_ray_generation, diff_ray_marching.py:369-386):
+ *   seg = seg_base[d] * (1 + jitter * (uniform[r,d] - 0.5)); ends = near + cumsum(seg) (left to right, as the CPU chain);
+ *   ts[r,d] = (ends[d-1] + ends[d]) / 2 with ends[-1] = near.  seg_base float[D] = t[1:] - t[:-1] of the linspace chain
+ *   (caller, D+1 elements); uniform float[R,D] stands for the torch.rand draw of :373; ts float[R,D]. */
+int pn_sample_depths(const float* seg_base, const float* uniform, int64_t n_rays, int32_t D, float near_depth,
+                     float jitter, float* ts, void* stream);
 int pn_ray_sample(const float* campos, const float* raydir, const float* ts, int64_t ts_rows,
                   int64_t n_rays, int32_t D, int32_t SR, const pn_grid_params* params,
                   const uint32_t* occ_bits, float* sample_loc_w, float* sample_t, int32_t* hit_count,

@@ -83,6 +83,7 @@ def _declare(lib):
         "pn_debug_gemm_tn": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int32, P, c_int64, c_int32, c_int32, P, P]),
         "pn_grid_workspace_bytes": (c_int64, [c_int64, c_int64]),
         "pn_grid_build": (c_int, [P, c_int64, POINTER(GridParams), P, P, P, P, P, c_int64, P]),
+        "pn_sample_depths": (c_int, [P, P, c_int64, c_int32, c_float, c_float, P, P]),
         "pn_ray_sample": (c_int, [P, P, P, c_int64, c_int64, c_int32, c_int32, POINTER(GridParams), P, P, P, P, P]),
         "pn_knn_query": (c_int, [P, POINTER(GridParams), P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float,
                                  P, P, P, P]),

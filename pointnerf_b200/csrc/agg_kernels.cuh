@@ -114,22 +114,28 @@ __global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, Ag
     for (int c = lane; c < d.F; c += 32) {
         float e = in.embedding[(int64_t)gj * d.F + c];
         srow[c] = e;
-        float fr = 1.f;
+        // frequencies are powers of two: one accurate sincosf, then double-angle steps (each adds ~2 ulp of absolute
+        // error on values in [-1, 1]; at most 15 steps, far inside the 1e-4 budget)
+        float s, co;
+        sincosf(e, &s, &co);
         for (int f = 0; f < d.ff; ++f) {
-            float s, co;
-            sincosf(e * fr, &s, &co);
             srow[d.F + (c * d.ff + f) * 2] = s;
             srow[d.F + (c * d.ff + f) * 2 + 1] = co;
-            fr *= 2.f;
+            const float s2 = 2.f * s * co, c2 = (co - s) * (co + s);
+            s = s2; co = c2;
         }
     }
-    for (int q = lane; q < 6 * d.df; q += 32) {
-        int a = q / d.df, f = q - a * d.df;
-        float v = a == 0 ? r[0] : a == 1 ? r[1] : a == 2 ? r[2] : a == 3 ? r[3] : a == 4 ? r[4] : r[5];
+    if (lane < 6) {                                       // lane = axis: all df frequencies of one offset component
+        const float v = lane == 0 ? r[0] : lane == 1 ? r[1] : lane == 2 ? r[2] : lane == 3 ? r[3] : lane == 4 ? r[4] : r[5];
         float s, co;
-        sincosf(v * (float)(1 << f), &s, &co);
-        srow[pe0 + 2 * q] = s;
-        srow[pe0 + 2 * q + 1] = co;
+        sincosf(v, &s, &co);
+        for (int f = 0; f < d.df; ++f) {
+            const int q = lane * d.df + f;
+            srow[pe0 + 2 * q] = s;
+            srow[pe0 + 2 * q + 1] = co;
+            const float s2 = 2.f * s * co, c2 = (co - s) * (co + s);
+            s = s2; co = c2;
+        }
     }
     for (int c = d.in1 + lane; c < d.in1p; c += 32) srow[c] = 0.f;
     __syncwarp();

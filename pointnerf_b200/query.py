@@ -22,9 +22,10 @@ from .synthetic import grid_hyperparameters
 
 def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
     """Depths of the candidate samples: the scalar chain of near_far_linear_ray_generation
-    (models/rendering/diff_ray_marching.py:369-386) with the SAME torch ops, so positions are bit-identical
-    to what the reference would compute on this device.  Without jitter every ray has the same depths and
-    one row [1,1,D] is returned; with jitter [1,R,D] (``uniform`` stands for the torch.rand draw of :373)."""
+    (models/rendering/diff_ray_marching.py:369-386), every operation rounded separately like the reference's torch ops.
+    Without jitter every ray has the same depths and one row [1,1,D] is returned (torch ops on D elements); with jitter
+    [1,R,D] from ONE kernel (pn_sample_depths) whose running sum goes left to right - bit-identical to the CPU chain,
+    which torch's device cumsum is not guaranteed to be (``uniform`` stands for the torch.rand draw of :373)."""
     dev = raydir.device
     t = torch.linspace(0, 1, D + 1, device=dev).view(1, -1)
     t = near * (1 - t) + far * t
@@ -35,6 +36,14 @@ def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
     else:
         if uniform is None:
             uniform = torch.rand((raydir.shape[0], R, D), device=dev)
+        if uniform.is_cuda and raydir.shape[0] == 1:
+            # one kernel for the per-ray part ([R,D] tensors); sums run left to right like the CPU chain
+            base = (t[..., 1:] - t[..., :-1]).reshape(-1).contiguous()
+            u = uniform.reshape(R, D).float().contiguous()
+            ts = torch.empty((1, R, D), dtype=torch.float32, device=dev)
+            _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base), _lib.ptr(u), R, D, float(near), float(jitter), _lib.ptr(ts),
+                                                   _lib.stream()), "pn_sample_depths")
+            return ts
         seg = (t[..., 1:] - t[..., :-1]) * (1 + jitter * (uniform - 0.5))
         rows = R
     ends = torch.cumsum(seg, dim=2)
