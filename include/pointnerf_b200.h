@@ -45,8 +45,9 @@ void pn_launch_count_reset(void);
  * Both replace the cuBLAS SGEMMs behind nn.Linear in point_aggregators.py:547,571,605,635. */
 int pn_set_mlp_path(int path);
 int pn_get_mlp_path(void);
-/* bench-only ablation of the NT GEMM pipeline (1: no MMA, 2: no A loads, 4: no B copies, 8: no C stores, 16: no A
- * staging stores); results are garbage while non-zero. */
+/* bench-only switches of the NT GEMM: 256 selects the single-CTA kernel instead of the CTA-pair (cta_group::2) one;
+ * on the single-CTA kernel 1: no MMA, 2: no A loads, 4: no B copies, 8: no C stores, 16: no A staging stores,
+ * 32: no proxy fence, 64: no epilogue (results are garbage while any of bits 0-7 is set). */
 void pn_debug_gemm_flags(int flags);
 /* Test hooks: one GEMM through the selected path (not used by the product path).
  *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias);  tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]

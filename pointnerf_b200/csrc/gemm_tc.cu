@@ -654,6 +654,271 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// NT on CTA PAIRS (cta_group::2).  The two CTAs of a cluster sit on the two SMs of one TPC and compute one 256 x BN tile:
+// each stages ITS 128 rows of A and loads HALF of the weight block (BN / 2 rows); the leader (rank 0) issues one MMA of
+// M = 256 that reads both halves.  Per SM this halves the weight bytes copied into and read from shared memory - the
+// resource that bounds the single-CTA kernel - and leaves room for a third A / B stage.
+//   fullA / fullB   per CTA, local producers          emptyA / emptyB / accFull   per CTA, multicast tcgen05.commit of the leader
+//   peerFull        on the leader: the peer's relay thread (its otherwise idle MMA warp) forwards "my stage s is full"
+//   accEmpty        on the leader: 8 local + 8 remote epilogue warps
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int NS2 = 3;
+constexpr int B2_STAGE = B_BYTES;                    // 2 x (128 rows x 128 B): half of a 256-row block, hi | lo
+constexpr int IMG2_SMEM = NS2 * A_STAGE + NS2 * B2_STAGE + kEpiWarps * SLAB_BYTES + 1024 + 256;
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
+    gemm_nt_img2_kernel(GemmNT g, int BN, int n_tiles_n, int n_ptiles_total) {
+    extern __shared__ char smem_raw[];
+    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    char* smA = smem;
+    char* smB = smem + NS2 * A_STAGE;
+    char* slabs = smB + NS2 * B2_STAGE;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kEpiWarps * SLAB_BYTES);
+    uint64_t *fullA = bars, *emptyA = bars + 3, *fullB = bars + 6, *emptyB = bars + 9, *peerFull = bars + 12, *accFull = bars + 15,
+             *accEmpty = bars + 17;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
+    const int nk = (g.Kd + TBK - 1) / TBK;
+    const uint32_t b_half = (uint32_t)(BN * 64);          // bytes of (BN / 2 rows x 128 B): one of hi | lo in this CTA
+    const uint32_t b_block = (uint32_t)(2 * BN * 128);    // image block of one (n tile, K chunk)
+    const int my_tiles = n_ptiles_total > pair ? (n_ptiles_total - pair + n_pairs - 1) / n_pairs : 0;
+    const int total_chunks = my_tiles * nk;
+
+    if (t == 0) {
+        for (int i = 0; i < NS2; ++i) {
+            tc::mbar_init(&fullA[i], kLoadThreads / 2); tc::mbar_init(&emptyA[i], 1);
+            tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1);
+            tc::mbar_init(&peerFull[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 2 * kEpiWarps); }
+        tc::mbar_fence_init();
+    }
+    if (warp == 8) tc::tmem_alloc2(tmem_slot, 512u);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync();                                   // both CTAs' barriers exist before any remote arrive / multicast commit
+    tc::fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp < 8) {
+        // ---------------------------------------------------------------- A staging (as the single-CTA kernel; own 128 rows)
+        const int grp = warp >> 2, tt = t & 127;
+        const int c = tt & 7, r0 = tt >> 3;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t sA_u32 = tc::smem_u32(smA);
+        float4 ra[8], rb[8];
+        auto load = [&](int L, float4 (&r)[8]) {
+            const int it = L / nk, kc = L - it * nk;
+            const int ptile = pair + it * n_pairs;
+            const int64_t m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM;
+            const int gk = kc * TBK + 4 * c;
+            const bool kok = gk < g.Kd;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                int64_t m = m0 + r0 + 16 * i;
+                r[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
+            }
+        };
+        auto step = [&](int L, float4 (&cur)[8]) {
+            const int sa = L % NS2;
+            tc::mbar_wait(&emptyA[sa], ((L / NS2) & 1) ^ 1);
+            const uint32_t st = sA_u32 + (uint32_t)(sa * A_STAGE);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t off = sw128_off(r0 + 16 * i, c);
+                split_store_s(st + off, st + A_BYTES + off, cur[i]);
+            }
+            tc::fence_proxy_async();
+            tc::mbar_arrive(&fullA[sa]);
+            if (L + 4 < total_chunks) load(L + 4, cur);
+        };
+        if (grp < total_chunks) load(grp, ra);
+        if (grp + 2 < total_chunks) load(grp + 2, rb);
+        for (int L = grp; L < total_chunks; L += 4) {
+            step(L, ra);
+            if (L + 2 < total_chunks) step(L + 2, rb);
+        }
+    } else if (warp == 8) {
+        if (lane == 0 && rank == 0) {
+            // ---------------------------------------------------------------- MMA issue (leader)
+            const uint32_t idesc = tc::idesc_tf32(2 * TBM, BN, 0, 0);
+            const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
+            int L = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int ab = it & 1;
+                tc::mbar_wait_cluster(&accEmpty[ab], ((it >> 1) & 1) ^ 1);
+                tc::fence_after_sync();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(ab * 256);
+                for (int kc = 0; kc < nk; ++kc, ++L) {
+                    const int s = L % NS2;
+                    const uint32_t ph = (uint32_t)((L / NS2) & 1);
+                    tc::mbar_wait(&fullB[s], ph);
+                    tc::mbar_wait(&fullA[s], ph);
+                    tc::mbar_wait_cluster(&peerFull[s], ph);
+                    tc::fence_after_sync();
+                    const uint32_t a_hi = sA + s * A_STAGE, a_lo = a_hi + A_BYTES;
+                    const uint32_t b_hi = sB + s * B2_STAGE, b_lo = b_hi + b_half;
+                    int ksteps = (g.Kd - kc * TBK + 7) >> 3;
+                    if (ksteps > 4) ksteps = 4;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t ko = 32u * k;
+                        uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
+                        uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
+                        tc::mma_tf32_2(tmem_d, dah, dbl, idesc, (kc | k) != 0);
+                        tc::mma_tf32_2(tmem_d, dal, dbh, idesc, 1);
+                        tc::mma_tf32_2(tmem_d, dah, dbh, idesc, 1);
+                    }
+                    tc::mma_commit_2(&emptyA[s]);
+                    tc::mma_commit_2(&emptyB[s]);
+                }
+                tc::mma_commit_2(&accFull[ab]);
+            }
+        } else if (lane == 0) {
+            // ---------------------------------------------------------------- relay (peer): forward "stage full" to the leader
+            for (int L = 0; L < total_chunks; ++L) {
+                const int s = L % NS2;
+                const uint32_t ph = (uint32_t)((L / NS2) & 1);
+                tc::mbar_wait(&fullB[s], ph);
+                tc::mbar_wait(&fullA[s], ph);
+                tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&peerFull[s]), 0));
+            }
+        }
+        __syncwarp();
+    } else if (warp == 9) {
+        // ---------------------------------------------------------------- B image producer: this CTA's half of every block
+        if (lane == 0) {
+            int L = 0;
+            for (int it = 0; it < my_tiles; ++it) {
+                const int ptile = pair + it * n_pairs;
+                const char* src = g.Bimg + (int64_t)(ptile % n_tiles_n) * nk * b_block + (int64_t)rank * b_half;
+                for (int kc = 0; kc < nk; ++kc, ++L) {
+                    const int s = L % NS2;
+                    tc::mbar_wait(&emptyB[s], ((L / NS2) & 1) ^ 1);
+                    tc::mbar_arrive_expect_tx(&fullB[s], 2 * b_half);
+                    const char* blk = src + (int64_t)kc * b_block;
+                    tc::bulk_g2s(smB + s * B2_STAGE, blk, b_half, &fullB[s]);                               // hi rows of this CTA
+                    tc::bulk_g2s(smB + s * B2_STAGE + b_half, blk + (int64_t)BN * 128, b_half, &fullB[s]);  // lo rows
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---------------------------------------------------------------- epilogue (warps 10..17), own 128 rows
+        const int q = warp & 3;
+        const int half = (warp - 10) >> 2;
+        const uint32_t slab = tc::smem_u32(slabs + (warp - 10) * SLAB_BYTES);
+        const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
+                            (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
+                            (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
+        const int rsub = lane >> 3, c8 = lane & 7;
+        const int nch = (BN + 31) >> 5;
+        const int my_last = ((nch - 1 - half) & ~1) + half;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint32_t accEmpty0 = tc::mapa(tc::smem_u32(&accEmpty[0]), 0);     // the leader's barriers
+        auto release = [&](int ab) {
+            tc::fence_before_sync();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive_cluster(accEmpty0 + 8u * (uint32_t)ab);
+        };
+        auto prefetch_aux = [&](int ptile) {
+            if (!g.aux) return;
+            const int64_t m = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM + q * 32 + lane;
+            const int n0 = (ptile % n_tiles_n) * BN;
+            if (m >= g.M) return;
+            for (int j = half; j < nch; j += 2) {
+                const int n = n0 + j * 32;
+                if (n < g.aux_cols) asm volatile("prefetch.global.L2 [%0];" ::"l"(g.aux + m * g.ldaux + n));
+            }
+        };
+        if (my_tiles > 0) prefetch_aux(pair);
+        for (int it = 0; it < my_tiles; ++it) {
+            const int ab = it & 1;
+            const int ptile = pair + it * n_pairs;
+            const int64_t m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM + q * 32;
+            const int n0 = (ptile % n_tiles_n) * BN;
+            if (it + 1 < my_tiles) prefetch_aux(ptile + n_pairs);
+            tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
+            tc::fence_after_sync();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
+            for (int j = half; j < nch; j += 2) {
+                uint32_t lo16[16], hi16[16];
+                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32), lo16);
+                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32 + 16), hi16);
+                const int n = n0 + j * 32 + 4 * c8;
+                const bool ncol_ok = (j * 32 + 4 * c8 < BN) && n < g.N;
+                float4 bias4 = z4;
+                if (vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                tc::tmem_ld_wait();
+                if (j == my_last) release(ab);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u,
+                               make_float4(__uint_as_float(lo16[4 * i]), __uint_as_float(lo16[4 * i + 1]), __uint_as_float(lo16[4 * i + 2]),
+                                           __uint_as_float(lo16[4 * i + 3])));
+                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u,
+                               make_float4(__uint_as_float(hi16[4 * i]), __uint_as_float(hi16[4 * i + 1]), __uint_as_float(hi16[4 * i + 2]),
+                                           __uint_as_float(hi16[4 * i + 3])));
+                }
+                __syncwarp();
+                const bool use_aux = vec_ok && ncol_ok && g.aux && n < g.aux_cols;
+                float4 aux4[8];
+                if (use_aux) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int64_t m = m0 + 4 * i + rsub;
+                        aux4[i] = m < g.M ? __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n)) : z4;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int row = 4 * i + rsub;
+                    const int64_t m = m0 + row;
+                    float4 x4 = tc::lds128(slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u);
+                    if (m >= g.M || !ncol_ok) continue;
+                    float x[4] = {x4.x, x4.y, x4.z, x4.w};
+                    if (vec_ok) {
+                        x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
+                        if (g.leaky) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) x[e] = x[e] > 0.f ? x[e] : g.slope * x[e];
+                        }
+                        if (use_aux) {
+                            const float4 a = aux4[i];
+                            x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
+                            x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
+                        }
+                        *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            if (n + e >= g.N) break;
+                            float y = x[e];
+                            if (g.bias) y += __ldg(g.bias + n + e);
+                            if (g.leaky) y = y > 0.f ? y : g.slope * y;
+                            if (g.aux && n + e < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + e) > 0.f) ? 1.f : g.slope;
+                            g.C[m * g.ldc + n + e] = y;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+            if (my_last < half) release(ab);
+        }
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync();                                   // the peer's smem / TMEM / barriers stay alive until the leader is done
+    if (warp == 8) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc2(tmem_base, 512u);
+    }
+}
+
 // image block (tile j, chunk kc) = [hi: BN rows x 128 B swizzled | lo: same]; one thread per (row, 16-byte chunk)
 __global__ void __launch_bounds__(256) pack_nt_image_kernel(const float* __restrict__ src, int64_t s_n, int64_t s_k, int N, int K,
                                                             int BN, int n_tiles, int nk, char* __restrict__ img) {
@@ -686,7 +951,8 @@ static int pick_bn(int N, int* n_tiles) {
 static int tmem_cols_for(int bn) { return bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256; }
 
 static int g_gemm_dbg = 0;   // bench-only ablation switches of the NT image kernel (pn_debug_gemm_flags)
-void set_gemm_debug_flags(int f) { g_gemm_dbg = f; }
+static int g_nt_pairs = 1;   // NT GEMMs run on CTA pairs (cta_group::2); debug flag bit 8 selects the single-CTA kernel instead
+void set_gemm_debug_flags(int f) { g_gemm_dbg = f & 0xFF; g_nt_pairs = ((f >> 8) & 1) ^ 1; }
 
 int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
     PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0 && g.ldb % 4 == 0, "gemm_nt_tc: operands must be padded to 4 (Kd %d lda %lld ldb %lld)",
@@ -707,6 +973,18 @@ int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
         if (!attr_img) {
             PN_CUDA(cudaFuncSetAttribute(gemm_nt_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG_SMEM));
             attr_img = true;
+        }
+        if (g_nt_pairs && g.M > TBM) {     // CTA pairs: 256-row tiles, one cluster of two CTAs per TPC
+            static bool attr_img2 = false;
+            if (!attr_img2) {
+                PN_CUDA(cudaFuncSetAttribute(gemm_nt_img2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG2_SMEM));
+                attr_img2 = true;
+            }
+            int ptotal = (int)(cdiv(g.M, 2 * TBM) * n_tiles);
+            int pairs = ptotal < kNumSMs / 2 ? ptotal : kNumSMs / 2;
+            gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles, ptotal);
+            PN_LAUNCH_CHECK("gemm_nt_img2");
+            return PN_OK;
         }
         int total = (int)(cdiv(g.M, TBM) * n_tiles);
         int ctas = total < kNumSMs ? total : kNumSMs;
