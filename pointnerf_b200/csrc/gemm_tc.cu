@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_tc_kernel(GemmNT g, int B
 constexpr int kTnLoad = 512;                 // staging threads of the TN kernel (16 warps) + 1 MMA warp
 constexpr int kTnThreads = kTnLoad + 32;
 __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int BKt, int tmem_cols, int64_t rows_per_split,
-                                                                   float* __restrict__ partial, float* __restrict__ cpartial) {
+                                                                   float* __restrict__ partial, float* __restrict__ cpartial, int dbg) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     constexpr int PANEL = TBK * 128;                     // bytes of one 32-wide panel over a 32-row chunk
@@ -283,12 +283,12 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int64_t rr = rb0 + ar0 + 8 * i;
-                ra[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
+                ra[i] = (a_ok && rr < r_end && !(dbg & 2)) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
             }
 #pragma unroll
             for (int i = 0; i < NB; ++i) {
                 int64_t rr = rb0 + (brow[i] & 0xFF);
-                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
+                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end && !(dbg & 2)) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
             }
         };
         if (grp < nk) load(grp);
@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
             const int s = kc & 1;
             tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
             const uint32_t st = smem_u + (uint32_t)(s * stage_bytes);
+            if (!(dbg & 16)) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int row = ar0 + 8 * i;
@@ -309,6 +310,7 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
                     const uint32_t off = (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i] & 0xFF, bc4[i] & 7);
                     split_store_s(st + 2 * A_BYTES + off, st + 2 * A_BYTES + (uint32_t)b_bytes + off, rb[i]);
                 }
+            }
             tc::fence_proxy_async();
             tc::mbar_arrive(&bars[s]);
             if (kc + 2 < nk) load(kc + 2);
@@ -360,6 +362,7 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
             const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + (uint32_t)b_bytes;
             int64_t rows = r_end - (r_begin + (int64_t)kc * TBK);
             int ksteps = rows >= TBK ? 4 : (int)((rows + 7) >> 3);
+            if (dbg & 1) ksteps = 0;
             for (int k = 0; k < ksteps; ++k) {
                 const uint32_t ko = 1024u * k;
                 uint64_t dah = tc::smem_desc_sw128(a_hi + ko, PANEL, 512, 1), dal = tc::smem_desc_sw128(a_lo + ko, PANEL, 512, 1);
@@ -1088,7 +1091,7 @@ int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
     float* cpartial = scratch + (int64_t)splits * g.N * g.Kb;
     dim3 grid((unsigned)k_tiles, (unsigned)n_tiles, (unsigned)splits);
     gemm_tn_tc_kernel<<<grid, kTnThreads, smem_bytes, st>>>(g, bkt, bkt > 256 ? 512 : tmem_cols_for(bkt), rps, partial,
-                                                         g.colsum ? cpartial : nullptr);
+                                                         g.colsum ? cpartial : nullptr, g_gemm_dbg);
     PN_LAUNCH_CHECK("gemm_tn_tc");
     return tn_finish(g, partial, g.colsum ? cpartial : nullptr, splits, st);
 }

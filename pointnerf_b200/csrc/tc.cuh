@@ -216,13 +216,15 @@ __device__ __forceinline__ void mma_commit_2(uint64_t* bar) {
 // ---- 3xTF32 split ----------------------------------------------------------------------------
 // v = hi + lo with hi = rna_tf32(v) (low 13 mantissa bits zero) and lo = rna_tf32(v - hi):
 // a*b ~= hi_a*hi_b + hi_a*lo_b + lo_a*hi_b, dropped terms <= ~2^-21 |a b|.
+__device__ __forceinline__ float rna_tf32(float v) {
+    // round to nearest, ties away from zero, onto the 10-bit TF32 mantissa - what cvt.rna.tf32.f32 computes, done on the
+    // integer ALU (IADD + LOP3 at full rate; the cvt runs on a quarter-rate pipe and was the staging bottleneck):
+    // float bits are sign-magnitude, so adding half a TF32 ulp to the bit pattern and clearing 13 bits rounds the magnitude
+    return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+}
 __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
-    uint32_t h, l;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
-    hi = __uint_as_float(h);
-    float r = v - hi;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
-    lo = __uint_as_float(l);
+    hi = rna_tf32(v);
+    lo = rna_tf32(v - hi);
 }
 
 }  // namespace tc
