@@ -370,6 +370,7 @@ def main():
     h2d += (3 + 9) * 4
 
     e2e_next, e2e_pending = {}, []
+    copy_stream = torch.cuda.Stream()
     loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
     e2e_losses = []
 
@@ -381,7 +382,17 @@ def main():
         b = e2e_next.pop(i, None) or to_dev(pinned[i % n_pool], dev, non_blocking=True)
         nb = None
         if args.prefetch:
-            nb = e2e_next[i + 1] = to_dev(pinned[(i + 1) % n_pool], dev, non_blocking=True)
+            # upload of batch i + 1 on a side stream (overlaps this batch's kernels); the stepper waits for `ready`
+            # right before it queues that batch's sampling
+            main = torch.cuda.current_stream()
+            with torch.cuda.stream(copy_stream):
+                nb = to_dev(pinned[(i + 1) % n_pool], dev, non_blocking=True)
+                nb["ready"] = torch.cuda.Event()
+                nb["ready"].record(copy_stream)
+            for t_ in (nb["raydir"], nb["uniform"], nb["gt"], nb["cam"]["campos"], nb["cam"]["camrotc2w"]):
+                if t_ is not None:
+                    t_.record_stream(main)
+            e2e_next[i + 1] = nb
         loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, next_batch=nb)
         buf = loss_host[i % 2]
         buf.copy_(loss.reshape(1), non_blocking=True)          # D2H read of the step's result

@@ -243,8 +243,8 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
     const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
 
     if (t == 0) {
-        tc::mbar_init(&bars[0], kTnLoad / 2);
-        tc::mbar_init(&bars[1], kTnLoad / 2);
+        tc::mbar_init(&bars[0], kTnLoad / 64);
+        tc::mbar_init(&bars[1], kTnLoad / 64);
         tc::mbar_init(&bars[2], 1);
         tc::mbar_init(&bars[3], 1);
         tc::mbar_init(&bars[4], 1);
@@ -312,7 +312,8 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
                 }
             }
             tc::fence_proxy_async();
-            tc::mbar_arrive(&bars[s]);
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&bars[s]);
             if (kc + 2 < nk) load(kc + 2);
         }
       if (warp < 8) {
@@ -429,7 +430,7 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
     const int total_chunks = my_tiles * nk;
 
     if (t == 0) {
-        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads / 2); tc::mbar_init(&emptyA[i], 1); }
+        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads / 64); tc::mbar_init(&emptyA[i], 1); }
         for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
         for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], kEpiWarps); }
         tc::mbar_fence_init();
@@ -475,7 +476,8 @@ __global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, i
                 split_store_s(st + off, st + A_BYTES + off, cur[i]);
             }
             if (!(dbg & 32)) tc::fence_proxy_async();
-            tc::mbar_arrive(&fullA[sa]);
+            __syncwarp();                                   // one arrival per warp: arrivals on one barrier word serialise
+            if (lane == 0) tc::mbar_arrive(&fullA[sa]);
             if (L + 4 < total_chunks) load(L + 4, cur);
         };
         if (grp < total_chunks) load(grp, ra);
@@ -694,7 +696,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
 
     if (t == 0) {
         for (int i = 0; i < NS2; ++i) {
-            tc::mbar_init(&fullA[i], kLoadThreads / 2); tc::mbar_init(&emptyA[i], 1);
+            tc::mbar_init(&fullA[i], kLoadThreads / 64); tc::mbar_init(&emptyA[i], 1);
             tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1);
             tc::mbar_init(&peerFull[i], 1);
         }
@@ -737,7 +739,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                 split_store_s(st + off, st + A_BYTES + off, cur[i]);
             }
             tc::fence_proxy_async();
-            tc::mbar_arrive(&fullA[sa]);
+            __syncwarp();                                   // one arrival per warp: arrivals on one barrier word serialise
+            if (lane == 0) tc::mbar_arrive(&fullA[sa]);
             if (L + 4 < total_chunks) load(L + 4, cur);
         };
         if (grp < total_chunks) load(grp, ra);

@@ -255,7 +255,8 @@ class RayShardedStep:
 
     def __call__(self, cam, raydir, gt, uniform=None, global_rays=None, reduce=True, next_batch=None):
         """cam: dict(campos [1,3], camrotc2w [1,3,3], near, far); raydir [1,R_local,3]; gt [1,R_local,C].
-        next_batch: optional dict(cam=, raydir=, uniform=) of the batch the NEXT call will get (see ``prefetch``).
+        next_batch: optional dict(cam=, raydir=, uniform=[, ready=cuda event]) of the batch the NEXT call will get (see
+        ``prefetch``); ``ready`` lets the caller upload it on a side stream while this batch computes.
         Returns (loss_local_sum / (global_rays*C)) as a 0-d tensor (the all-reduced SUM over ranks is the batch MSE)."""
         R_local = raydir.shape[1]
         global_rays = int(global_rays if global_rays is not None else R_local * self.world)
@@ -271,6 +272,8 @@ class RayShardedStep:
         diff = out["coarse_raycolor"] - gt
         loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
         if next_batch is not None:
+            if next_batch.get("ready") is not None:        # event of the side-stream H2D copy that produced the batch
+                torch.cuda.current_stream().wait_event(next_batch["ready"])
             self.prefetch(next_batch["cam"], next_batch["raydir"], next_batch.get("uniform"))
         loss.backward()
         if reduce:
