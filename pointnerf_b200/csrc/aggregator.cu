@@ -251,9 +251,12 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     carve_bwd(d, S, M, T, workspace, workspace_bytes, &ws);
     const int pgw = d.F + 8;
     // transposed (K-contiguous over the OUTPUT index) weight copies for the data-gradient GEMMs
+    // block1.0's data gradient is only needed for the embedding-derived input columns [emb | PE(emb)]: the distance
+    // encoding behind them has no trainable input (xyz_grad = 0), so the GEMM stops at column ng1 (224 of 288)
+    const int ng1 = (int)align_up(d.F + 2 * d.ff * d.F, 16) < d.in1p ? (int)align_up(d.F + 2 * d.ff * d.F, 16) : d.in1p;
     const bool tcp = mlp_path() == 1;
     if (tcp) {   // images of W^T: B[n = input column, k = output unit] = W[k, n]
-        const PackJob jobs[7] = {{w->block1_0_w, 1, d.in1, d.in1, d.W, d.in1p, d.W, ws.J1a}, {w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b},
+        const PackJob jobs[7] = {{w->block1_0_w, 1, d.in1, ng1 < d.in1 ? ng1 : d.in1, d.W, ng1, d.W, ws.J1a}, {w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b},
                                  {w->block3_0_w, 1, d.in3, d.in3, d.W, d.in3p, d.W, ws.J3a}, {w->block3_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J3b},
                                  {w->color_0_w, 1, d.inc, d.inc, d.C, d.incp, d.C, ws.Jc0},  {w->color_2_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc2},
                                  {w->color_4_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc4}};
@@ -336,7 +339,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     {   // block1.0: GA[M,in1p] = d/dX1
         GemmTN t{ws.GB, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, d.in1p, d.W, nullptr, 0, d.slope);
+        GemmNT g = nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J1a);
         PN_TRY(gemm_nt(g, st));
     }
