@@ -262,23 +262,35 @@ __global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict
 using namespace pn;
 
 namespace pn {
-// Jittered mid-point depths of one ray per thread: the scalar chain of near_far_linear_ray_generation
+// Jittered mid-point depths: the scalar chain of near_far_linear_ray_generation
 // (diff_ray_marching.py:369-386) with every product and sum rounded separately and the running sum taken left to right,
 // i.e. exactly what the reference's torch ops compute on the CPU (torch's device cumsum associates differently).
-__global__ void __launch_bounds__(128) sample_depths_kernel(const float* __restrict__ seg_base, const float* __restrict__ uniform,
+__global__ void __launch_bounds__(256) sample_depths_kernel(const float* __restrict__ seg_base, const float* __restrict__ uniform,
                                                             int64_t n_rays, int D, float near, float jitter, float* __restrict__ ts) {
-    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // one warp per ray: lanes load / store 32 consecutive depths (coalesced) and form their segment lengths in parallel;
+    // the running sum itself is taken strictly left to right - every lane walks the same 32-step chain over the
+    // shuffled segment values (SIMT: the cost of one lane) and keeps the step that is its own
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (r >= n_rays) return;
     const float* u = uniform + r * D;
     float* out = ts + r * D;
     float c = 0.f, prev_end = __fadd_rn(near, 0.f);
-    for (int d = 0; d < D; ++d) {
-        float f = __fadd_rn(1.f, __fmul_rn(jitter, __fsub_rn(u[d], 0.5f)));
-        float seg = __fmul_rn(seg_base[d], f);
-        c = __fadd_rn(c, seg);
-        float end = __fadd_rn(near, c);
-        out[d] = __fmul_rn(__fadd_rn(prev_end, end), 0.5f);
-        prev_end = end;
+    for (int d0 = 0; d0 < D; d0 += 32) {
+        const int d = d0 + lane;
+        float seg = 0.f;
+        if (d < D) seg = __fmul_rn(seg_base[d], __fadd_rn(1.f, __fmul_rn(jitter, __fsub_rn(u[d], 0.5f))));
+        float mine = 0.f;
+        const int n = D - d0 < 32 ? D - d0 : 32;
+        for (int j = 0; j < n; ++j) {
+            const float v = __shfl_sync(0xffffffffu, seg, j);
+            c = __fadd_rn(c, v);
+            const float end = __fadd_rn(near, c);
+            const float mid = __fmul_rn(__fadd_rn(prev_end, end), 0.5f);
+            if (lane == j) mine = mid;
+            prev_end = end;
+        }
+        if (d < D) out[d] = mine;
     }
 }
 }  // namespace pn
@@ -287,7 +299,7 @@ extern "C" int pn_sample_depths(const float* seg_base, const float* uniform, int
                                 float* ts, void* stream) {
     PN_CHECK_ARG(seg_base && uniform && ts && D > 0, "pn_sample_depths: bad argument");
     if (n_rays <= 0) return PN_OK;
-    sample_depths_kernel<<<(unsigned)cdiv(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(seg_base, uniform, n_rays, D, near_depth, jitter, ts);
+    sample_depths_kernel<<<(unsigned)cdiv(n_rays * 32, 256), 256, 0, (cudaStream_t)stream>>>(seg_base, uniform, n_rays, D, near_depth, jitter, ts);
     PN_LAUNCH_CHECK("sample_depths");
     return PN_OK;
 }
