@@ -957,8 +957,10 @@ static int pick_bn(int N, int* n_tiles) {
 static int tmem_cols_for(int bn) { return bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256; }
 
 static int g_gemm_dbg = 0;   // bench-only ablation switches of the NT image kernel (pn_debug_gemm_flags)
+static int g_tn_pairs = 1;   // TN GEMMs with two n tiles run on CTA pairs; debug flag bit 9 selects the single-CTA kernel
+static bool nk_rows_ok(int64_t rps) { return rps % 32 == 0; }
 static int g_nt_pairs = 1;   // NT GEMMs run on CTA pairs (cta_group::2); debug flag bit 8 selects the single-CTA kernel instead
-void set_gemm_debug_flags(int f) { g_gemm_dbg = f & 0xFF; g_nt_pairs = ((f >> 8) & 1) ^ 1; }
+void set_gemm_debug_flags(int f) { g_gemm_dbg = f & 0xFF; g_nt_pairs = ((f >> 8) & 1) ^ 1; g_tn_pairs = ((f >> 9) & 1) ^ 1; }
 
 int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
     PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0 && g.ldb % 4 == 0, "gemm_nt_tc: operands must be padded to 4 (Kd %d lda %lld ldb %lld)",
@@ -1062,6 +1064,186 @@ int pack_nt_images(const PackJob* jobs, int n, cudaStream_t st) {
     return PN_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// TN on CTA PAIRS (cta_group::2) for N = 129..256 output rows: the two n tiles of one row split form a cluster.  Each CTA
+// stages ITS 128 columns of A (dY) and HALF of the columns of B (X); the leader issues MMAs of M = 256 that read both
+// halves.  Per CTA that is 272 instead of 416 staged columns per chunk and 68 KB instead of 104 KB per stage, which makes
+// room for a third stage (the two-stage kernel is bound by the producer -> MMA -> producer round trip).
+// BKt2 = Kb rounded up to 64 (<= 320): columns 0..255 go through an MMA of N = 256 (128 per CTA), the rest through a second
+// one of N = 64 (32 per CTA); CTA r therefore stages k columns [128 r, 128 r + 128) and [256 + 32 r, 256 + 32 r + 32).
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int TNP_STAGES = 3;
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTnThreads, 1)
+    gemm_tn_pair_kernel(GemmTN g, int BKt2, int64_t rows_per_split, float* __restrict__ partial, float* __restrict__ cpartial) {
+    extern __shared__ char smem_raw[];
+    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    constexpr int PANEL = TBK * 128;
+    const int N2 = BKt2 - 256 > 0 ? BKt2 - 256 : 0, N1 = BKt2 - N2;    // 256 | 0..64, or BKt2 | 0 below 256
+    const int npan = (N1 >> 6) + (N2 >> 6);                            // B panels of this CTA: half of each MMA's columns
+    const int b_bytes = npan * PANEL;
+    const int stage_bytes = 2 * A_BYTES + 2 * b_bytes;
+    const int region = TNP_STAGES * stage_bytes > TBM * (BKt2 + 4) * 4 ? TNP_STAGES * stage_bytes : TBM * (BKt2 + 4) * 4;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + ((region + 15) & ~15));
+    uint64_t *full = bars, *empty = bars + 3, *peerFull = bars + 6, *done = bars + 9;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const int split = (int)blockIdx.x >> 1;
+    const int i0 = (int)rank * TBM;        // first column of A (n of the weight) of this CTA
+    const int64_t r_begin = (int64_t)split * rows_per_split;
+    const int64_t r_end = r_begin + rows_per_split < g.M ? r_begin + rows_per_split : g.M;
+    const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
+
+    if (t == 0) {
+        for (int i = 0; i < TNP_STAGES; ++i) { tc::mbar_init(&full[i], kTnLoad / 64); tc::mbar_init(&empty[i], 1); tc::mbar_init(&peerFull[i], 1); }
+        tc::mbar_init(done, 1);
+        tc::mbar_fence_init();
+    }
+    if (warp == 16) tc::tmem_alloc2(tmem_slot, 512u);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync();
+    tc::fence_after_sync();
+    const uint32_t tmem_d = *tmem_slot;
+
+    if (warp < 16) {
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int grp = t >> 8, tt = t & 255;
+        const int ac4 = tt & 31, ar0 = tt >> 5;    // A: 32 float4 per row (128 columns), rows ar0 + 8 i
+        const bool a_ok = i0 + 4 * ac4 < g.N;
+        const int ncb = npan * 8;                  // float4 per local B row (<= 40)
+        constexpr int NB = 5;                      // 256 threads x 5 >= 32 rows x 40 float4
+        int brow[NB], bc4[NB], bgc[NB];            // row | flags, local float4 column, global k column
+#pragma unroll
+        for (int i = 0; i < NB; ++i) {
+            int idx = tt + 256 * i;
+            const int br = idx / ncb;
+            bc4[i] = idx - br * ncb;
+            const int cl = 4 * bc4[i];             // local column
+            bgc[i] = cl < (N1 >> 1) ? (int)rank * (N1 >> 1) + cl : N1 + (int)rank * (N2 >> 1) + (cl - (N1 >> 1));
+            brow[i] = br >= TBK ? -1 : (br | (bgc[i] >= g.Kb ? 0x100 : 0));
+        }
+        float4 ra[4], rb[NB];
+        float4 csum = z4;
+        const uint32_t smem_u = tc::smem_u32(smem);
+        auto load = [&](int kc) {
+            const int64_t rb0 = r_begin + (int64_t)kc * TBK;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int64_t rr = rb0 + ar0 + 8 * i;
+                ra[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
+            }
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                int64_t rr = rb0 + (brow[i] & 0xFF);
+                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + bgc[i])) : z4;
+            }
+        };
+        if (grp < nk) load(grp);
+        for (int kc = grp; kc < nk; kc += 2) {
+            const int s = kc % TNP_STAGES;
+            tc::mbar_wait(&empty[s], ((kc / TNP_STAGES) & 1) ^ 1);
+            const uint32_t st = smem_u + (uint32_t)(s * stage_bytes);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int row = ar0 + 8 * i;
+                const uint32_t off = (uint32_t)((ac4 >> 3) * PANEL) + sw128b32_off(row, ac4 & 7);
+                split_store_s(st + off, st + A_BYTES + off, ra[i]);
+                csum.x += ra[i].x; csum.y += ra[i].y; csum.z += ra[i].z; csum.w += ra[i].w;
+            }
+#pragma unroll
+            for (int i = 0; i < NB; ++i)
+                if (brow[i] >= 0) {
+                    const uint32_t off = (uint32_t)((bc4[i] >> 3) * PANEL) + sw128b32_off(brow[i] & 0xFF, bc4[i] & 7);
+                    split_store_s(st + 2 * A_BYTES + off, st + 2 * A_BYTES + (uint32_t)b_bytes + off, rb[i]);
+                }
+            tc::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(&full[s]);
+            if (kc + 2 < nk) load(kc + 2);
+        }
+      if (warp < 8) {
+        // ---- epilogue: D[n, k] -> partial[split][n][k] (own 128 rows n; TMEM column = k)
+        if (nk > 0) {
+            tc::mbar_wait(done, 0);
+            tc::fence_after_sync();
+        }
+        float* out = partial + (int64_t)split * g.N * g.Kb;
+        epilogue_via_smem(tmem_d, BKt2, reinterpret_cast<float*>(smem), t, nk > 0, [&](int row, int col, float4 v) {
+            const int n = i0 + row, k = col;
+            if (n >= g.N || k >= g.Kb) return;
+            *reinterpret_cast<float4*>(out + (int64_t)n * g.Kb + k) = v;
+        });
+        tc::fence_before_sync();
+      }
+        if (cpartial) {      // bias gradient: column sums of A over this split, fixed order
+            float4* red = reinterpret_cast<float4*>(smem);
+            __syncwarp();
+            asm volatile("bar.sync 2, %0;" ::"n"(kTnLoad));
+            red[t] = csum;
+            asm volatile("bar.sync 2, %0;" ::"n"(kTnLoad));
+            if (t < 32) {
+                float4 a = red[t];
+#pragma unroll
+                for (int w16 = 1; w16 < 16; ++w16) {
+                    float4 b = red[t + 32 * w16];
+                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                }
+                int nn = i0 + 4 * t;
+                if (nn < g.N) *reinterpret_cast<float4*>(cpartial + (int64_t)split * g.N + nn) = a;
+            }
+        }
+    } else {
+      if (lane == 0 && rank == 0) {
+        const uint32_t idesc1 = tc::idesc_tf32(2 * TBM, N1, 1, 1);
+        const uint32_t idesc2 = N2 > 0 ? tc::idesc_tf32(2 * TBM, N2, 1, 1) : 0u;
+        const uint32_t sbase = tc::smem_u32(smem);
+        const uint32_t off2 = (uint32_t)((N1 >> 6) * PANEL);      // this CTA's columns of the second MMA follow those of the first
+        for (int kc = 0; kc < nk; ++kc) {
+            const int s = kc % TNP_STAGES;
+            const uint32_t ph = (uint32_t)((kc / TNP_STAGES) & 1);
+            tc::mbar_wait(&full[s], ph);
+            tc::mbar_wait_cluster(&peerFull[s], ph);
+            tc::fence_after_sync();
+            const uint32_t a_hi = sbase + s * stage_bytes, a_lo = a_hi + A_BYTES;
+            const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + (uint32_t)b_bytes;
+            int64_t rows = r_end - (r_begin + (int64_t)kc * TBK);
+            int ksteps = rows >= TBK ? 4 : (int)((rows + 7) >> 3);
+            for (int k = 0; k < ksteps; ++k) {
+                const uint32_t ko = 1024u * k;
+                uint64_t dah = tc::smem_desc_sw128(a_hi + ko, PANEL, 512, 1), dal = tc::smem_desc_sw128(a_lo + ko, PANEL, 512, 1);
+                uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, PANEL, 512, 1), dbl = tc::smem_desc_sw128(b_lo + ko, PANEL, 512, 1);
+                tc::mma_tf32_2(tmem_d, dah, dbl, idesc1, (kc | k) != 0);
+                tc::mma_tf32_2(tmem_d, dal, dbh, idesc1, 1);
+                tc::mma_tf32_2(tmem_d, dah, dbh, idesc1, 1);
+                if (N2 > 0) {
+                    uint64_t dbh2 = tc::smem_desc_sw128(b_hi + off2 + ko, PANEL, 512, 1), dbl2 = tc::smem_desc_sw128(b_lo + off2 + ko, PANEL, 512, 1);
+                    tc::mma_tf32_2(tmem_d + (uint32_t)N1, dah, dbl2, idesc2, (kc | k) != 0);
+                    tc::mma_tf32_2(tmem_d + (uint32_t)N1, dal, dbh2, idesc2, 1);
+                    tc::mma_tf32_2(tmem_d + (uint32_t)N1, dah, dbh2, idesc2, 1);
+                }
+            }
+            tc::mma_commit_2(&empty[s]);
+        }
+        tc::mma_commit_2(done);
+      } else if (lane == 0) {
+        for (int kc = 0; kc < nk; ++kc) {       // relay: this CTA's stage is full -> the leader's peerFull
+            const int s = kc % TNP_STAGES;
+            tc::mbar_wait(&full[s], (uint32_t)((kc / TNP_STAGES) & 1));
+            tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&peerFull[s]), 0));
+        }
+      }
+      __syncwarp();
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::cluster_sync();
+    if (warp == 16) {
+        tc::fence_after_sync();
+        tc::tmem_dealloc2(tmem_d, 512u);
+    }
+}
+
 // second stage of the TN reduction (kernels in gemm.cu)
 int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st);
 // one CTA per SM: k tiles x n tiles x splits <= 148, each split a contiguous slice of the reduction rows
@@ -1083,6 +1265,23 @@ int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
     int bkt, k_tiles, n_tiles, splits;
     int64_t rps;
     tn_plan(g.M, g.N, g.Kb, &bkt, &k_tiles, &n_tiles, &splits, &rps);
+    float* partial = scratch;
+    float* cpartial = scratch + (int64_t)splits * g.N * g.Kb;
+    const int bkt2 = (int)align_up(g.Kb, 64);
+    if (g_tn_pairs && n_tiles == 2 && k_tiles == 1 && bkt2 <= 320 && nk_rows_ok(rps)) {   // CTA pairs: the two n tiles of a split
+        const int n2 = bkt2 > 256 ? bkt2 - 256 : 0, n1 = bkt2 - n2;
+        const int np2 = (n1 >> 6) + (n2 >> 6);
+        const int stages_b = TNP_STAGES * (2 * A_BYTES + 2 * np2 * TBK * 128), tile_b = TBM * (bkt2 + 4) * 4;
+        const int smem2 = (stages_b > tile_b ? stages_b : tile_b) + 16 + 1024 + 256;
+        static int attr2 = 0;
+        if (smem2 > attr2) {
+            PN_CUDA(cudaFuncSetAttribute(gemm_tn_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+            attr2 = smem2;
+        }
+        gemm_tn_pair_kernel<<<2 * splits, kTnThreads, smem2, st>>>(g, bkt2, rps, partial, g.colsum ? cpartial : nullptr);
+        PN_LAUNCH_CHECK("gemm_tn_pair");
+        return tn_finish(g, partial, g.colsum ? cpartial : nullptr, splits, st);
+    }
     const int npan = (bkt + 31) / 32;
     const int smem_bytes = 2 * (2 * A_BYTES + 2 * npan * TBK * 128) + 1024 + 256;
     static int attr_bytes = 0;
@@ -1090,8 +1289,6 @@ int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
         PN_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
         attr_bytes = smem_bytes;
     }
-    float* partial = scratch;
-    float* cpartial = scratch + (int64_t)splits * g.N * g.Kb;
     dim3 grid((unsigned)k_tiles, (unsigned)n_tiles, (unsigned)splits);
     gemm_tn_tc_kernel<<<grid, kTnThreads, smem_bytes, st>>>(g, bkt, bkt > 256 ? 512 : tmem_cols_for(bkt), rps, partial,
                                                          g.colsum ? cpartial : nullptr, g_gemm_dbg);
