@@ -306,6 +306,15 @@ int pn_composite_backward(const float* ray_features, const float* ray_dist, cons
                           int64_t n_rays, int32_t SR, int32_t C, int64_t n_rows, float* g_features,
                           float* g_bg_color, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Colour MSE of a batch of rays and its gradient in one pass (replaces torch.nn.MSELoss on coarse_raycolor,
+ * base_rendering_model.py:543-550 `compute_losses`, and its autograd chain).
+ *   loss[0] = inv_norm * sum_r w_r * sum_c (pred[r,c]-target[r,c])^2      grad[r,c] = 2*inv_norm*w_r*(pred-target)
+ *   ray_weight float[n_rays] or NULL (=1; the reference's ray_mask selection is w in {0,1} with inv_norm = 1/(n_masked*C));
+ *   grad float[n_rays,C] or NULL.  Fixed-tree reduction: deterministic.  workspace >= pn_color_mse_workspace_bytes(). */
+int64_t pn_color_mse_workspace_bytes(void);
+int pn_color_mse(const float* pred, const float* target, const float* ray_weight, int64_t n_rays, int32_t C,
+                 float inv_norm, float* loss, float* grad, void* workspace, int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

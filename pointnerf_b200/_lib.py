@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -105,6 +105,8 @@ def _declare(lib):
         "pn_composite_workspace_bytes": (c_int64, [c_int64, c_int32, c_int64]),
         "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int64, P, P, P,
                                           c_int64, P]),
+        "pn_color_mse_workspace_bytes": (c_int64, []),
+        "pn_color_mse": (c_int, [P, P, P, c_int64, c_int32, c_float, P, P, P, c_int64, P]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: loud by design

@@ -260,6 +260,50 @@ __global__ void __launch_bounds__(256) bg_grad_final_kernel(const float* __restr
     g_bg[c] = acc;
 }
 
+// Colour loss of the rendering model (base_rendering_model.py:543-550, torch.nn.MSELoss over the rays of the batch):
+// loss = inv_norm * sum_r w_r * sum_c (pred-target)^2, grad = 2*inv_norm*w_r*(pred-target).  Fixed block count and a fixed
+// summation tree: the value is a pure function of the inputs (run-to-run and rank-count independent).
+constexpr int kLossBlocks = 128;
+__global__ void __launch_bounds__(256) color_mse_partial_kernel(const float* __restrict__ pred, const float* __restrict__ target,
+                                                                const float* __restrict__ ray_weight, int64_t n, int C,
+                                                                float inv_norm, float* __restrict__ partial,
+                                                                float* __restrict__ grad) {
+    __shared__ float red[8];
+    const float g2 = 2.f * inv_norm;
+    float acc = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float d = pred[i] - target[i];
+        float w = ray_weight ? ray_weight[i / C] : 1.f;
+        acc = __fmaf_rn(w * d, d, acc);
+        if (grad) grad[i] = ray_weight ? (g2 * w) * d : g2 * d;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w];
+        partial[blockIdx.x] = t;
+    }
+}
+__global__ void __launch_bounds__(kLossBlocks) color_mse_final_kernel(const float* __restrict__ partial, float inv_norm,
+                                                                       float* __restrict__ loss) {
+    __shared__ float red[kLossBlocks / 32];
+    float acc = partial[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kLossBlocks / 32; ++w) t += red[w];
+        *loss = t * inv_norm;
+    }
+}
+
 // ray_dist (neural_points_volumetric_model.py:293-301): running max of camera depth along the ray,
 // forward difference, last = vsize_z, tiny / too large steps -> vsize_z, masked by sample validity.
 __global__ void __launch_bounds__(256) ray_dist_kernel(const float* __restrict__ sample_loc, const uint8_t* __restrict__ valid,
@@ -387,5 +431,21 @@ extern "C" int pn_composite_backward(const float* ray_features, const float* ray
             PN_CUDA(cudaMemsetAsync(g_bg_color, 0, C * sizeof(float), st));
         }
     }
+    return PN_OK;
+}
+
+extern "C" int64_t pn_color_mse_workspace_bytes(void) { return (int64_t)kLossBlocks * sizeof(float); }
+
+extern "C" int pn_color_mse(const float* pred, const float* target, const float* ray_weight, int64_t n_rays, int32_t C,
+                            float inv_norm, float* loss, float* grad, void* workspace, int64_t workspace_bytes, void* stream) {
+    PN_CHECK_ARG(loss && workspace, "pn_color_mse: null argument");
+    PN_CHECK_ARG(n_rays >= 0 && C >= 1, "pn_color_mse: n_rays=%lld C=%d", (long long)n_rays, C);
+    PN_CHECK_ARG(n_rays == 0 || (pred && target), "pn_color_mse: null argument");
+    PN_CHECK_ARG(workspace_bytes >= pn_color_mse_workspace_bytes(), "pn_color_mse: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    color_mse_partial_kernel<<<kLossBlocks, 256, 0, st>>>(pred, target, ray_weight, n_rays * C, C, inv_norm, (float*)workspace, grad);
+    PN_LAUNCH_CHECK("color_mse_partial");
+    color_mse_final_kernel<<<1, kLossBlocks, 0, st>>>((const float*)workspace, inv_norm, loss);
+    PN_LAUNCH_CHECK("color_mse_final");
     return PN_OK;
 }

@@ -164,3 +164,41 @@ def ray_dist_from_samples(sample_loc, ray_valid, vsize, raydist_mode_unit=1):
     _lib.check(lib.pn_ray_dist(_lib.ptr(loc), _lib.ptr(valid), B * R, SR, float(vsize[2]), int(raydist_mode_unit),
                                _lib.ptr(out), _lib.stream()), "pn_ray_dist")
     return out.view(B, R, SR)
+
+
+class _ColorMSE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target, ray_weight, inv_norm):
+        lib = _lib.lib()
+        C = int(pred.shape[-1])
+        p = pred.detach().reshape(-1, C).contiguous().float()
+        t = target.detach().reshape(-1, C).contiguous().float()
+        if p.shape != t.shape:
+            raise ValueError("color_mse: prediction %s and target %s differ" % (tuple(pred.shape), tuple(target.shape)))
+        w = ray_weight.detach().reshape(-1).contiguous().float() if ray_weight is not None else None
+        if w is not None and w.numel() != p.shape[0]:
+            raise ValueError("color_mse: %d ray weights for %d rays" % (w.numel(), p.shape[0]))
+        loss = torch.empty((), dtype=torch.float32, device=p.device)
+        grad = torch.empty_like(p) if ctx.needs_input_grad[0] else None
+        ws_bytes = lib.pn_color_mse_workspace_bytes()
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=p.device)
+        _lib.check(lib.pn_color_mse(_lib.ptr(p), _lib.ptr(t), _lib.ptr(w), int(p.shape[0]), C, float(inv_norm), _lib.ptr(loss),
+                                    _lib.ptr(grad), _lib.ptr(ws), ws_bytes, _lib.stream()), "pn_color_mse")
+        ctx.grad, ctx.shape = grad, tuple(pred.shape)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        grad, ctx.grad = ctx.grad, None
+        return (grad * g).view(ctx.shape), None, None, None
+
+
+def color_mse(pred, target, ray_weight=None, norm=None):
+    """Colour loss of ``compute_losses`` (base_rendering_model.py:543-550: ``torch.nn.MSELoss`` of ``coarse_raycolor`` against
+    ``gt_image``) with its gradient produced in the same pass.  pred, target [..., C]; ray_weight [...] or None (the
+    ``ray_masked_*`` items: a {0,1} mask, ``norm`` = number of selected elements); norm: the divisor (default: pred.numel()).
+    Returns the 0-d loss; deterministic (fixed reduction tree)."""
+    if not pred.is_cuda:
+        raise _lib.LibraryError("color_mse needs CUDA tensors (there is no CPU path in this package)")
+    n = float(norm) if norm is not None else float(max(pred.numel(), 1))
+    return _ColorMSE.apply(pred, target, ray_weight, 1.0 / n)

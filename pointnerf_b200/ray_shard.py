@@ -18,6 +18,8 @@ It is backend-agnostic (``nccl`` on the B200s, ``gloo`` in the CPU tests of the 
 import torch
 import torch.distributed as dist
 
+from .ray_march import color_mse
+
 
 def shard_bounds(n_rays, world_size, rank):
     """Contiguous slice [lo, hi) of a batch of ``n_rays`` rays owned by ``rank`` (sizes differ by at most one)."""
@@ -269,8 +271,12 @@ class RayShardedStep:
         self._cap_ev = None
         if self.world > 1 and self.sparse:
             self._begin_cap_exchange()
-        diff = out["coarse_raycolor"] - gt
-        loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
+        pred = out["coarse_raycolor"]
+        if pred.is_cuda:               # one fused kernel pair: loss and d(loss)/d(colour) (pn_color_mse)
+            loss = color_mse(pred, gt, norm=global_rays * gt.shape[-1])
+        else:                          # gloo tests of this module's host logic drive it with a CPU toy model
+            diff = pred - gt
+            loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
         if next_batch is not None:
             if next_batch.get("ready") is not None:        # event of the side-stream H2D copy that produced the batch
                 torch.cuda.current_stream().wait_event(next_batch["ready"])
