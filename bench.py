@@ -390,8 +390,10 @@ def main():
     _lib.reset_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    th0 = time.perf_counter()
     for s in range(args.steps):
         step(warmup + s)
+    host_ms = (time.perf_counter() - th0) * 1e3 / args.steps      # host time to QUEUE a step (its only wait: the (S, M) counts)
     e1.record()
     sync_all()
     launches = _lib.launch_count()
@@ -411,7 +413,7 @@ def main():
     e2e_next, e2e_pending = {}, []
     copy_stream = torch.cuda.Stream()
     loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
-    e2e_losses = []
+    e2e_losses, e2e_wait = [], [0.0]
 
     def e2e_step(i):
         # step i uses the device copy made (from pinned host memory, inside the timed region) during step i - 1 when
@@ -444,7 +446,9 @@ def main():
     def e2e_drain(keep):
         while len(e2e_pending) > keep:
             ev, buf = e2e_pending.pop(0)
+            tw = time.perf_counter()
             ev.synchronize()
+            e2e_wait[0] += time.perf_counter() - tw
             e2e_losses.append(float(buf[0]))
 
     for w in range(2):
@@ -453,9 +457,13 @@ def main():
     sync_all()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
+    e2e_wait[0] = 0.0
+    th0 = time.perf_counter()
     for s in range(args.steps):
         e2e_step(2 + s)
     e2e_drain(0)                 # the last step's loss is on the host before the timer stops
+    e2e_host_ms = (time.perf_counter() - th0) * 1e3 / args.steps
+    e2e_wait_ms = e2e_wait[0] * 1e3 / args.steps
     f1.record()
     sync_all()
     assert len(e2e_losses) == args.steps + 2 and all(np.isfinite(v) for v in e2e_losses)
@@ -530,7 +538,9 @@ def main():
                            "mean_valid_samples_per_batch": counts["S"] if counts else None,
                            "mean_valid_pairs_per_batch": counts["M"] if counts else None},
                 "clocks": clocks, "gpu_launches": int(launches),
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+                        "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
+                "host_queue_ms_per_step": round(host_ms, 4),
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages}
         _emit(line)
     if world > 1:

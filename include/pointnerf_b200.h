@@ -252,6 +252,13 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
                     float* grad_color, float* grad_dir, float* grad_conf, int32_t* touched_ids,
                     int32_t* n_touched, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* conf_coefficient of the aggregator output (point_aggregators.py:809-811 applied to neural_points.py's index_select of
+ * points_conf with sample_pidx.clamp(min=0)): out[i] = clamp(table[max(idx[i],0)], lo, hi) for the whole query result in one
+ * pass (evaluated as x - (x - clamp(x)) like the reference, bit-identical).  table float[n_points]; idx int32[n] (-1 = empty slot -> row 0, as in the reference); idx/out 16-byte aligned.
+ * The clamp is straight-through for gradients (gradiant_clamp): the host scatters d(out) back to the table rows. */
+int pn_gather_clamp(const float* table, int64_t n_points, const int32_t* idx, int64_t n, float lo, float hi, float* out,
+                    void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * 4b. Sparse exchange of per-point gradient rows between ranks (new: the reference has no multi-GPU path).
  * With scatter_rows == 1, pn_agg_backward can also return touched_ids int32[M] - the table rows that received

@@ -105,6 +105,7 @@ def _declare(lib):
         "pn_composite_workspace_bytes": (c_int64, [c_int64, c_int32, c_int64]),
         "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int64, P, P, P,
                                           c_int64, P]),
+        "pn_gather_clamp": (c_int, [P, c_int64, P, c_int64, c_float, c_float, P, P]),
         "pn_color_mse_workspace_bytes": (c_int64, []),
         "pn_color_mse": (c_int, [P, P, P, c_int64, c_int32, c_float, P, P, P, c_int64, P]),
     }

@@ -234,6 +234,36 @@ class _AggFunction(torch.autograd.Function):
         return (None,) + _shaped((g_emb, g_col, g_dir, g_cnf), ctx.table_shapes) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
 
 
+class _GatherClamp(torch.autograd.Function):
+    """conf_coefficient of the fused path: clamp(table[max(idx,0)], lo, hi) with the straight-through gradient of
+    ``gradiant_clamp`` (point_aggregators.py:724-726, :809-811) scattered back to the table rows."""
+
+    @staticmethod
+    def forward(ctx, table, idx, lo, hi):
+        lib = _lib.lib()
+        flat = table.detach().reshape(-1).contiguous().float()
+        idx = idx.contiguous()
+        out = torch.empty(idx.shape, dtype=torch.float32, device=flat.device)
+        _lib.check(lib.pn_gather_clamp(_lib.ptr(flat), int(flat.numel()), _lib.ptr(idx), int(idx.numel()), float(lo), float(hi),
+                                       _lib.ptr(out), _lib.stream()), "pn_gather_clamp")
+        ctx.idx, ctx.shape = idx, tuple(table.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        n = 1
+        for v in ctx.shape:
+            n *= v
+        gt = torch.zeros(n, dtype=torch.float32, device=g.device)
+        gt.index_put_((ctx.idx.reshape(-1).clamp(min=0).long(),), g.reshape(-1).float(), accumulate=True)   # sort-based: deterministic
+        return gt.view(ctx.shape), None, None, None
+
+
+def gather_clamp(table, idx, lo=0.0001, hi=1.0):
+    """table [..N..] (any shape with N elements), idx int32 [...] (-1 -> row 0) -> float32 [...] = clamp(table[idx], lo, hi)."""
+    return _GatherClamp.apply(table, idx, lo, hi)
+
+
 class PointAggregator(nn.Module):
     """Same constructor / parameters / forward as the reference class (point_aggregators.py:12-816)."""
 

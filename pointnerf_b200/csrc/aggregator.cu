@@ -463,6 +463,28 @@ __global__ void __launch_bounds__(256) rows_count_kernel(const int* __restrict__
     v = __reduce_add_sync(0xffffffffu, v);
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(count, v);   // integer sum: order-independent
 }
+// conf_coefficient of the aggregator (point_aggregators.py:809-811 on the gathered points_conf of neural_points.py:
+// index_select with sample_pidx.clamp(min=0)): out[i] = clamp(table[max(idx[i], 0)], lo, hi), one pass over the query result.
+// The reference's straight-through clamp evaluates x - (x - clamp(x)) (:724-726), which is NOT always clamp(x) in fp32 when
+// the clamp is active; the same two subtractions are done here so the values are bit-identical.
+__device__ __forceinline__ float st_clamp(float x, float lo, float hi) {
+    return __fsub_rn(x, __fsub_rn(x, fminf(fmaxf(x, lo), hi)));
+}
+__global__ void __launch_bounds__(256) gather_clamp_kernel(const float* __restrict__ table, const int32_t* __restrict__ idx, int64_t n,
+                                                           float lo, float hi, float* __restrict__ out) {
+    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 3 < n) {
+        int4 p = *reinterpret_cast<const int4*>(idx + i);
+        float4 v;
+        v.x = st_clamp(__ldg(table + max(p.x, 0)), lo, hi);
+        v.y = st_clamp(__ldg(table + max(p.y, 0)), lo, hi);
+        v.z = st_clamp(__ldg(table + max(p.z, 0)), lo, hi);
+        v.w = st_clamp(__ldg(table + max(p.w, 0)), lo, hi);
+        *reinterpret_cast<float4*>(out + i) = v;
+    } else {
+        for (; i < n; ++i) out[i] = st_clamp(__ldg(table + max(idx[i], 0)), lo, hi);
+    }
+}
 }  // namespace pn
 
 extern "C" int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int64_t n_points, int32_t* mark, int32_t* count,
@@ -477,6 +499,16 @@ extern "C" int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int6
     }
     rows_count_kernel<<<(unsigned)cdiv(n_points, 256), 256, 0, st>>>(mark, n_points, count);
     PN_LAUNCH_CHECK("rows_count");
+    return PN_OK;
+}
+
+extern "C" int pn_gather_clamp(const float* table, int64_t n_points, const int32_t* idx, int64_t n, float lo, float hi, float* out,
+                               void* stream) {
+    PN_CHECK_ARG(table && n_points > 0 && (n == 0 || (idx && out)) && n >= 0, "pn_gather_clamp: bad argument");
+    PN_CHECK_ARG((((uintptr_t)idx | (uintptr_t)out) & 15) == 0, "pn_gather_clamp: idx / out must be 16-byte aligned");
+    if (n == 0) return PN_OK;
+    gather_clamp_kernel<<<(unsigned)cdiv(cdiv(n, 4), 256), 256, 0, (cudaStream_t)stream>>>(table, idx, n, lo, hi, out);
+    PN_LAUNCH_CHECK("gather_clamp");
     return PN_OK;
 }
 

@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import query as _query
-from .aggregator import CompactSamples, PointAggregator
+from .aggregator import CompactSamples, PointAggregator, gather_clamp
 from .query import lighting_fast_querier
 from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march, ray_march_compact
 
@@ -245,12 +245,10 @@ class NeuralPointsRayMarching(nn.Module):
         ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)
         ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march_compact(ray_dist, ray_valid, decoded, slot_row, bg_color)
         out = {"coarse_raycolor": ray_color, "coarse_point_opacity": opacity, "coarse_is_background": bg_T,
-               "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).to(torch.int8)[None],
+               "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).view(torch.int8)[None],
                "queried_shading": torch.logical_not(torch.any(ray_valid, dim=-1, keepdims=True)).repeat(1, 1, 3).float()}
         if want_w:
             out["weight"] = weight.detach()[None]
             out["blend_weight"] = blend_weight.detach()
-            conf = nps.points_conf[0, :, 0]
-            g = torch.clamp(pidx, min=0).long()
-            out["conf_coefficient"] = PointAggregator.gradiant_clamp(conf[g], min=0.0001, max=1)[None]
+            out["conf_coefficient"] = gather_clamp(nps.points_conf, pidx, 0.0001, 1.0)[None]
         return out

@@ -105,13 +105,19 @@ class _Composite(torch.autograd.Function):
         return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None, None
 
 
+def _as_u8(mask):
+    """bool / integer validity mask -> contiguous uint8 (a bool tensor is reinterpreted, not converted)."""
+    mask = mask.contiguous()
+    return mask.view(torch.uint8) if mask.dtype in (torch.bool, torch.int8) else mask.to(torch.uint8)
+
+
 def ray_march_compact(ray_dist, ray_valid, features_compact, slot_row, bg_color=None):
     """Fused-path variant of ``ray_march``: ``features_compact`` [S,C+1] holds one row per valid sample and
     ``slot_row`` int32 [R,SR] maps sample (r,s) to its row (-1: none).  Same 7-tuple minus ``point_color`` (None)."""
     B, R, SR = ray_dist.shape
     if B != 1:
         raise NotImplementedError("B = 1 only, like every caller of the reference")
-    valid = ray_valid.reshape(R, SR).to(torch.uint8).contiguous()
+    valid = _as_u8(ray_valid.reshape(R, SR))
     ray_color, opacity, acc_T, blend_w, bg_T = _Composite.apply(features_compact, ray_dist.reshape(R, SR), valid, bg_color, True,
                                                                 slot_row.reshape(R, SR).contiguous())
     bg_T = bg_T.view(B, R, 1)
@@ -124,7 +130,7 @@ def _flatten(ray_dist, ray_valid, ray_features):
     if B != 1:
         raise NotImplementedError("B = 1 only, like every caller of the reference")
     return (ray_features.reshape(R, SR, ray_features.shape[-1]), ray_dist.reshape(R, SR),
-            ray_valid.reshape(R, SR).to(torch.uint8).contiguous(), B, R, SR)
+            _as_u8(ray_valid.reshape(R, SR)), B, R, SR)
 
 
 def ray_march(ray_dist, ray_valid, ray_features, render_func, blend_func, bg_color=None):
@@ -157,7 +163,7 @@ def ray_dist_from_samples(sample_loc, ray_valid, vsize, raydist_mode_unit=1):
     lib = _lib.lib()
     B, R, SR = ray_valid.shape
     loc = sample_loc.detach().reshape(B * R, SR, 3).contiguous()
-    valid = ray_valid.reshape(B * R, SR).to(torch.uint8).contiguous()
+    valid = _as_u8(ray_valid.reshape(B * R, SR))
     out = torch.empty((B * R, SR), dtype=torch.float32, device=loc.device)
     if B * R == 0:
         return out.view(B, R, SR)

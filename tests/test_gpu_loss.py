@@ -64,3 +64,23 @@ def test_color_mse_rejects_mismatched_shapes():
         color_mse(torch.zeros((1, 4, 3), device="cuda"), torch.zeros((1, 5, 3), device="cuda"))
     with pytest.raises(Exception):
         color_mse(torch.zeros((1, 4, 3)), torch.zeros((1, 4, 3)))
+
+
+def test_conf_coefficient_gather_matches_reference_expression():
+    """gather_clamp == gradiant_clamp(points_conf[sample_pidx.clamp(min=0)]) (point_aggregators.py:724-726, :809-811;
+    neural_points.py index_select) in value (bit-exact) and in the straight-through gradient."""
+    from pointnerf_b200.aggregator import PointAggregator, gather_clamp
+    N = 5000
+    g = torch.Generator(device="cuda").manual_seed(3)
+    for shape in [(7, 5, 8), (1, 3, 1), (33, 24, 8), (0, 4, 8)]:
+        conf = (torch.rand((1, N, 1), device="cuda", generator=g) * 1.2 - 0.1).requires_grad_(True)   # values outside [1e-4, 1] too
+        idx = torch.randint(-1, N, shape, device="cuda", generator=g, dtype=torch.int32)
+        idx[torch.rand(shape, device="cuda", generator=g) < 0.5] = -1
+        up = torch.rand(shape, device="cuda", generator=g)
+        out = gather_clamp(conf, idx)
+        (out * up).sum().backward()
+        c2 = conf.detach().clone().requires_grad_(True)
+        ref = PointAggregator.gradiant_clamp(c2[0, :, 0][idx.clamp(min=0).long()], min=0.0001, max=1)
+        (ref * up).sum().backward()
+        assert out.shape == ref.shape and torch.equal(out, ref)
+        assert torch.allclose(conf.grad, c2.grad, rtol=1e-5, atol=1e-6)
