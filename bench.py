@@ -162,6 +162,30 @@ def to_dev(batch, dev, non_blocking=False):
                 gt=batch["gt"].to(dev, non_blocking=non_blocking))
 
 
+def pack_pinned(batch):
+    """One pinned fp32 buffer per batch [campos 3 | camrotc2w 9 | raydir R*3 | gt R*C | jitter draw R*D], segments padded to
+    64 floats: the loader's upload is ONE host->device copy per step; ``unpack_dev`` slices the device copy (views only)."""
+    parts = [batch["cam"]["campos"], batch["cam"]["camrotc2w"], batch["raydir"], batch["gt"]]
+    if batch["uniform"] is not None:
+        parts.append(batch["uniform"])
+    offs, n = [], 0
+    for t_ in parts:
+        offs.append(n)
+        n += (t_.numel() + 63) // 64 * 64
+    buf = torch.zeros(n, dtype=torch.float32).pin_memory()
+    for t_, o in zip(parts, offs):
+        buf[o:o + t_.numel()].copy_(t_.reshape(-1).float())
+    meta = dict(offs=offs, shapes=[tuple(t_.shape) for t_ in parts], near=batch["cam"]["near"], far=batch["cam"]["far"],
+                bytes=sum(t_.numel() for t_ in parts) * 4)
+    return buf, meta
+
+
+def unpack_dev(buf, meta):
+    v = [buf[o:o + int(np.prod(sh))].view(sh) for o, sh in zip(meta["offs"], meta["shapes"])]
+    return dict(cam=dict(campos=v[0], camrotc2w=v[1], near=meta["near"], far=meta["far"]), raydir=v[2], gt=v[3],
+                uniform=v[4] if len(v) > 4 else None)
+
+
 def pin(batch):
     out = dict(batch)
     for k in ("raydir", "uniform", "gt"):
@@ -406,33 +430,34 @@ def main():
     value = global_rays * args.steps / (ms_total * 1e-3)
 
     # ---- end to end: pinned host buffers -> H2D -> step -> D2H of the loss, every step
-    pinned = [pin(b) for b in batches]
-    h2d = sum(int(t_.numel()) * t_.element_size() for t_ in (pinned[0]["raydir"], pinned[0]["uniform"], pinned[0]["gt"]) if t_ is not None)
-    h2d += (3 + 9) * 4
+    packed = [pack_pinned(b) for b in batches]
+    h2d = packed[0][1]["bytes"]
 
     e2e_next, e2e_pending = {}, []
     copy_stream = torch.cuda.Stream()
     loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
     e2e_losses, e2e_wait = [], [0.0]
 
+    def upload(i):
+        hbuf, meta = packed[i % n_pool]
+        return unpack_dev(hbuf.to(dev, non_blocking=True), meta)
+
     def e2e_step(i):
         # step i uses the device copy made (from pinned host memory, inside the timed region) during step i - 1 when
         # prefetching; the H2D of batch i + 1 is issued before this step's kernels so that its sampling can be queued.
         # The loss of every step is copied to pinned host memory inside the step and read by the host one step later
         # (asynchronous logging): the host never drains the GPU queue in the middle of the loop.
-        b = e2e_next.pop(i, None) or to_dev(pinned[i % n_pool], dev, non_blocking=True)
+        b = e2e_next.pop(i, None) or upload(i)
         nb = None
         if args.prefetch:
             # upload of batch i + 1 on a side stream (overlaps this batch's kernels); the stepper waits for `ready`
             # right before it queues that batch's sampling
             main = torch.cuda.current_stream()
             with torch.cuda.stream(copy_stream):
-                nb = to_dev(pinned[(i + 1) % n_pool], dev, non_blocking=True)
+                nb = upload(i + 1)
                 nb["ready"] = torch.cuda.Event()
                 nb["ready"].record(copy_stream)
-            for t_ in (nb["raydir"], nb["uniform"], nb["gt"], nb["cam"]["campos"], nb["cam"]["camrotc2w"]):
-                if t_ is not None:
-                    t_.record_stream(main)
+            nb["raydir"].record_stream(main)         # all fields are views of the one uploaded buffer
             e2e_next[i + 1] = nb
         loss = stepper(b["cam"], b["raydir"], b["gt"], uniform=b["uniform"], global_rays=global_rays, next_batch=nb)
         buf = loss_host[i % 2]
@@ -451,7 +476,8 @@ def main():
             e2e_wait[0] += time.perf_counter() - tw
             e2e_losses.append(float(buf[0]))
 
-    for w in range(2):
+    E2E_WARM = 3
+    for w in range(E2E_WARM):
         e2e_step(w)
     e2e_drain(0)
     sync_all()
@@ -460,13 +486,13 @@ def main():
     e2e_wait[0] = 0.0
     th0 = time.perf_counter()
     for s in range(args.steps):
-        e2e_step(2 + s)
+        e2e_step(E2E_WARM + s)
     e2e_drain(0)                 # the last step's loss is on the host before the timer stops
     e2e_host_ms = (time.perf_counter() - th0) * 1e3 / args.steps
     e2e_wait_ms = e2e_wait[0] * 1e3 / args.steps
     f1.record()
     sync_all()
-    assert len(e2e_losses) == args.steps + 2 and all(np.isfinite(v) for v in e2e_losses)
+    assert len(e2e_losses) == args.steps + E2E_WARM and all(np.isfinite(v) for v in e2e_losses)
     t = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

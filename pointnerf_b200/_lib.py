@@ -149,7 +149,13 @@ def ptr(t):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream():
+    """cudaStream_t of torch's current stream on the current device (every launch goes there)."""
+    if _raw_stream is not None:                   # ~0.3 us; torch.cuda.current_stream() builds a Stream object (~15 us)
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 

@@ -141,7 +141,7 @@ class CompactSamples:
         self._host = torch.empty(2, dtype=torch.int32).pin_memory()
         self._host.copy_(counts, non_blocking=True)
         self._event = torch.cuda.Event()
-        self._event.record(torch.cuda.current_stream(dev))
+        self._event.record()
 
     def counts(self):
         """(S, M): valid samples and valid (sample, neighbour) pairs - the one host read-back of the aggregator."""
@@ -195,6 +195,7 @@ class _AggFunction(torch.autograd.Function):
         if weight_out is None:
             weight_out = torch.empty(0, device=dev)
         ctx.mark_non_differentiable(weight_out)
+        ctx.set_materialize_grads(False)      # no zero tensor for the non-differentiable weight output
         return decoded, weight_out
 
     @staticmethod
@@ -203,6 +204,8 @@ class _AggFunction(torch.autograd.Function):
         call, p = ctx.call, ctx.call.params
         embedding, color, pdir, conf = ctx.tables
         dev = embedding.device
+        if g_decoded is None:
+            g_decoded = torch.zeros((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
         g_decoded = g_decoded.contiguous()
         need = ctx.needs_input_grad  # (call, embedding, color, dir, conf, *weights)
         rows = call.T if call.scatter_rows else call.n_slots * p.K

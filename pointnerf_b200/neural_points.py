@@ -111,8 +111,8 @@ class NeuralPoints(nn.Module):
     def forward(self, inputs):
         """neural_points.py:782-812 (reference seam): the 14-tuple of gathered [1,R'',SR,K,*] tensors."""
         camrotc2w, campos, near, far = inputs["camrotc2w"], inputs["campos"], inputs["near"], inputs["far"]
-        near = float(torch.as_tensor(near).min())
-        far = float(torch.as_tensor(far).max())
+        near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
+        far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
         pixel_idx = inputs.get("pixel_idx")
         sample_pidx, sample_loc, ray_mask_tensor, xyz_pers, sample_loc_w, sample_ray_dirs, vsize = self.get_point_indices(
             inputs, camrotc2w, campos, pixel_idx, near, far, inputs.get("h"), inputs.get("w"), inputs.get("intrinsic"))
@@ -209,8 +209,8 @@ class NeuralPointsRayMarching(nn.Module):
         consumes it; a training loop calls this for batch i+1 before the backward of batch i so that the (S, M)
         read-back the aggregator needs is complete long before it is waited for."""
         nps = self.neural_points
-        near = float(torch.as_tensor(near).min())
-        far = float(torch.as_tensor(far).max())
+        near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
+        far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
         xyz = nps.xyz.detach()
         raw = nps.querier.query_raw(xyz, raydir, campos, near, far, uniform=uniform)
         pidx, loc_w = raw["sample_pidx"], raw["sample_loc_w"]                     # [R,SR,K], [R,SR,3]
@@ -246,7 +246,9 @@ class NeuralPointsRayMarching(nn.Module):
         ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march_compact(ray_dist, ray_valid, decoded, slot_row, bg_color)
         out = {"coarse_raycolor": ray_color, "coarse_point_opacity": opacity, "coarse_is_background": bg_T,
                "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).view(torch.int8)[None],
-               "queried_shading": torch.logical_not(torch.any(ray_valid, dim=-1, keepdims=True)).repeat(1, 1, 3).float()}
+               # a ray has a valid sample exactly when the query found it a neighbour (ray_any): same values as
+               # logical_not(any(ray_valid)).repeat(1,1,3).float() of the reference (:162) in two launches
+               "queried_shading": (raw["ray_any"].view(1, R, 1) == 0).expand(1, R, 3).float()}
         if want_w:
             out["weight"] = weight.detach()[None]
             out["blend_weight"] = blend_weight.detach()

@@ -20,6 +20,24 @@ from ._lib import GridParams
 from .synthetic import grid_hyperparameters
 
 
+_EDGE_CACHE = {}
+
+
+def _depth_edges(dev, D, near, far):
+    """[1, D+1] bin edges near*(1-t)+far*t of :369-372; a pure function of (D, near, far), kept per device so that a
+    training loop does not re-issue the five tiny torch ops every batch."""
+    key = (str(dev), D, near, far)
+    e = _EDGE_CACHE.get(key)
+    if e is None:
+        if len(_EDGE_CACHE) > 64:
+            _EDGE_CACHE.clear()
+        t = torch.linspace(0, 1, D + 1, device=dev).view(1, -1)
+        e = near * (1 - t) + far * t
+        e = (e, (e[..., 1:] - e[..., :-1]).reshape(-1).contiguous())
+        _EDGE_CACHE[key] = e
+    return e
+
+
 def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
     """Depths of the candidate samples: the scalar chain of near_far_linear_ray_generation
     (models/rendering/diff_ray_marching.py:369-386), every operation rounded separately like the reference's torch ops.
@@ -27,8 +45,7 @@ def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
     [1,R,D] from ONE kernel (pn_sample_depths) whose running sum goes left to right - bit-identical to the CPU chain,
     which torch's device cumsum is not guaranteed to be (``uniform`` stands for the torch.rand draw of :373)."""
     dev = raydir.device
-    t = torch.linspace(0, 1, D + 1, device=dev).view(1, -1)
-    t = near * (1 - t) + far * t
+    t, base = _depth_edges(dev, int(D), float(near), float(far))
     R = raydir.shape[1]
     if jitter == 0.0:
         seg = (t[..., 1:] - t[..., :-1]).view(1, 1, D) * torch.ones((1, 1, D), device=dev)
@@ -38,7 +55,6 @@ def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
             uniform = torch.rand((raydir.shape[0], R, D), device=dev)
         if uniform.is_cuda and raydir.shape[0] == 1:
             # one kernel for the per-ray part ([R,D] tensors); sums run left to right like the CPU chain
-            base = (t[..., 1:] - t[..., :-1]).reshape(-1).contiguous()
             u = uniform.reshape(R, D).float().contiguous()
             ts = torch.empty((1, R, D), dtype=torch.float32, device=dev)
             _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base), _lib.ptr(u), R, D, float(near), float(jitter), _lib.ptr(ts),

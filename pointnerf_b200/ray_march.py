@@ -66,6 +66,7 @@ class _Composite(torch.autograd.Function):
             _lib.check(lib.pn_composite_forward(_lib.ptr(feats_k), _lib.ptr(dist), _lib.ptr(ray_valid_u8), _lib.ptr(slot_row), _lib.ptr(bg), R, SR, C,
                                                 _lib.ptr(ray_color), _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(blend_w),
                                                 _lib.ptr(bg_T), _lib.stream()), "pn_composite_forward")
+        ctx.set_materialize_grads(False)    # unused outputs arrive as None (NULL for the kernel), not as zero tensors to fill and read
         ctx.save_for_backward(feats, dist, ray_valid_u8, bg if bg is not None else torch.empty(0, device=dev), opacity, acc_T, bg_T)
         ctx.has_bg, ctx.want_color, ctx.slot_row = bg is not None, want_color, slot_row
         ctx.bg_shape = tuple(bg_color.shape) if bg_color is not None else None
@@ -122,7 +123,7 @@ def ray_march_compact(ray_dist, ray_valid, features_compact, slot_row, bg_color=
                                                                 slot_row.reshape(R, SR).contiguous())
     bg_T = bg_T.view(B, R, 1)
     return (ray_color.view(B, R, features_compact.shape[-1] - 1), None, opacity.view(B, R, SR), acc_T.view(B, R, SR),
-            blend_w.view(B, R, SR, 1), bg_T, 1 * bg_T)
+            blend_w.view(B, R, SR, 1), bg_T, bg_T)      # background_blend_weight = 1 * T: the same values
 
 
 def _flatten(ray_dist, ray_valid, ray_features):
