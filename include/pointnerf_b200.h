@@ -265,8 +265,11 @@ int pn_gather_clamp(const float* table, int64_t n_points, const int32_t* idx, in
  * gradient, ascending and unique, padded with -1 - and n_touched int32[1].
  *   pn_rows_pack : out[cap, F+8] = [id bits | embedding F | conf | dir 3 | color 3] of rows ids[0..n_ids);
  *                  rows n_ids..cap are padding (id -1, zeros)
- *   pn_rows_merge: gathered [n_ranks, cap, F+8] (all-gather of the packed buffers): every touched table row
- *                  becomes the sum over ranks IN RANK ORDER (bit-identical on every replica, no atomics).
+ *   pn_rows_merge: gathered [n_ranks, cap, F+8] (all-gather of the packed buffers): every table row named there
+ *                  becomes the sum over ranks IN RANK ORDER of the rows carrying its id (bit-identical on every
+ *                  replica, no atomics; at two ranks the v0 + v1 of a dense all-reduce).  One pass, rows are written,
+ *                  not accumulated.  slots: int32[n_points * n_ranks] owned by the caller, ALL -1 on entry; it is
+ *                  all -1 again on return (allocate and fill once, reuse every step).  n_ranks <= 32.
  * ---------------------------------------------------------------------------------------------- */
 /* count[0] = number of distinct table rows referenced by sample_pidx int32[n] (-1 = empty): the touched-row count of the
  * coming backward, available as soon as the neighbour query is - ranks agree on the exchange capacity without a host
@@ -275,8 +278,8 @@ int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int64_t n_point
                           void* stream);
 int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb,
                  const float* g_conf, const float* g_dir, const float* g_color, float* out, void* stream);
-int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, float* g_emb, float* g_conf,
-                  float* g_dir, float* g_color, void* stream);
+int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, int64_t n_points, int32_t* slots,
+                  float* g_emb, float* g_conf, float* g_dir, float* g_color, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 5. Compositing  (replaces ray_march / alpha_ray_march diff_ray_marching.py:509-573 with

@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -99,7 +99,7 @@ def _declare(lib):
         "pn_debug_gemm_flags": (None, [c_int]),
         "pn_count_touched_rows": (c_int, [P, c_int64, c_int64, P, P, P]),
         "pn_rows_pack": (c_int, [P, c_int64, c_int64, c_int32, P, P, P, P, P, P]),
-        "pn_rows_merge": (c_int, [P, c_int32, c_int64, c_int32, P, P, P, P, P]),
+        "pn_rows_merge": (c_int, [P, c_int32, c_int64, c_int32, c_int64, P, P, P, P, P, P]),
         "pn_ray_dist": (c_int, [P, P, c_int64, c_int32, c_float, c_int32, P, P]),
         "pn_composite_forward": (c_int, [P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P, P, P, P]),
         "pn_composite_workspace_bytes": (c_int64, [c_int64, c_int32, c_int64]),

@@ -91,6 +91,7 @@ class _AggCall:
         self.collect_touched = False          # ask the backward for the sorted unique list of table rows it touched
         self.touched_ids = self.n_touched = None
         self.grad_flat = None                 # backward: the MLP weight gradients, one contiguous buffer
+        self.flat_tail, self.flat_tail_off = 0, 0   # extra zeroed floats appended to grad_flat for the caller, and where they start
         self.compact = None                   # optional CompactSamples built ahead of the call
 
 
@@ -215,8 +216,9 @@ class _AggFunction(torch.autograd.Function):
         g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[4] else None
         # all MLP gradients live in ONE flat buffer (256-byte aligned segments): ray_shard all-reduces it in place
         sizes = [(w.numel() + 63) // 64 * 64 for w in ctx.weights]
-        call.grad_flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
-        g_w = tuple(seg[:w.numel()].view(w.shape) for seg, w in zip(call.grad_flat.split(sizes), ctx.weights))
+        call.flat_tail_off = sum(sizes)       # + a caller-owned tail (ray_shard: bg gradient and row counts ride the same all-reduce)
+        call.grad_flat = torch.zeros(call.flat_tail_off + int(call.flat_tail), dtype=torch.float32, device=dev)
+        g_w = tuple(seg[:w.numel()].view(w.shape) for seg, w in zip(call.grad_flat.split(sizes + [int(call.flat_tail)]), ctx.weights))
         ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 1)
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
         ain = _inputs_struct(call, embedding, color, pdir, conf)
@@ -375,6 +377,7 @@ class PointAggregator(nn.Module):
                         Rw2c.detach().contiguous().float(), sample_pidx.contiguous(), sample_loc_w.detach().contiguous(),
                         sample_loc.detach().contiguous(), ray_dirs.detach().contiguous(), R * SR, T, True, want_weight)
         call.collect_touched = bool(getattr(self, "collect_touched", False))
+        call.flat_tail = int(getattr(self, "flat_tail_floats", 0))
         call.compact = work_lists             # CompactSamples of sample_pidx queued earlier (None: built here, with its sync)
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
         self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)

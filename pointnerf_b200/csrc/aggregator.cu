@@ -422,30 +422,70 @@ __global__ void __launch_bounds__(256) rows_pack_kernel(const int* __restrict__ 
     }
     out[idx] = v;
 }
-// Merge of the gathered buffer [G, cap, W] into the dense tables.  Each rank's id list is unique, so "add rank r's rows" is
-// race-free; the ranks are added one launch after the other IN RANK ORDER onto rows zeroed first - every replica computes
-// (((0 + g0) + g1) + ...) and therefore identical bits, with no search and no atomics.  mode 0: zero the row; 1: add.
-__global__ void __launch_bounds__(256) rows_apply_kernel(const float* __restrict__ rows, int64_t n_rows, int F, int mode,
-                                                         float* __restrict__ g_emb, float* __restrict__ g_conf,
-                                                         float* __restrict__ g_dir, float* __restrict__ g_color) {
-    const int W = F + 8;
-    int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (wid >= n_rows) return;
-    const float* mine = rows + wid * W;
-    const int g = __float_as_int(mine[0]);
+// pn_rows_merge: every table row named in the gathered buffer becomes the sum over ranks IN RANK ORDER of the rows carrying
+// its id (identical bits on every replica, and the plain v0 + v1 of a dense all-reduce at two ranks).  One pass: a slot table
+// [n_points, n_ranks] (persistent, -1 outside this call) records where each rank holds each id; the FIRST rank that holds an id
+// owns it: its warp walks the ranks in order, reads each present row once, and WRITES the table row (no read-modify-write, no
+// zero pass: rows touched only by this rank's own backward are among the gathered rows and get overwritten).
+__global__ void __launch_bounds__(256) rows_slot_kernel(const float* __restrict__ rows, int64_t cap, int n_ranks, int W, int set,
+                                                        int* __restrict__ slots) {
+    int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= cap * n_ranks) return;
+    const int g = __float_as_int(rows[e * W]);
     if (g < 0) return;
+    const int r = (int)(e / cap);
+    slots[(int64_t)g * n_ranks + r] = set ? (int)(e - (int64_t)r * cap) : -1;
+}
+__global__ void __launch_bounds__(256) rows_sum_kernel(const float* __restrict__ rows, int64_t cap, int n_ranks, int F,
+                                                       const int* __restrict__ slots, float* __restrict__ g_emb,
+                                                       float* __restrict__ g_conf, float* __restrict__ g_dir,
+                                                       float* __restrict__ g_color) {
+    // eight lanes per gathered entry (four entries per warp: the chain id -> slots -> rows -> store is latency bound, so
+    // entries in flight are what counts); lane j of a group owns columns j, j + 8, ... of the W - 1 <= 63 value columns
+    const int W = F + 8;
+    const int lane = threadIdx.x & 31, j = lane & 7, grp = lane >> 3;
+    const unsigned gmask = 0xffu << (grp * 8);
+    const int64_t e = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 4 + grp;
+    const bool in_range = e < cap * n_ranks;
+    const int g = in_range ? __float_as_int(rows[e * W]) : -1;
+    const int r = in_range ? (int)(e / cap) : 0;
+    int slotv[4];
+    unsigned present = 0;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {            // W - 1 <= 64 columns: two per lane
-        const int k = lane + 32 * i;
-        if (k >= W - 1) continue;
+    for (int k = 0; k < 4; ++k) {            // n_ranks <= 32: four rounds of eight ranks; whole-warp ballots, so no early exit above
+        const int rr = j + 8 * k;
+        slotv[k] = (g >= 0 && rr < n_ranks) ? slots[(int64_t)g * n_ranks + rr] : -1;
+        const unsigned b = __ballot_sync(0xffffffffu, slotv[k] >= 0);
+        present |= ((b >> (grp * 8)) & 0xffu) << (8 * k);
+    }
+    if (g < 0 || __ffs(present) - 1 != r) return;      // padding, or an earlier rank owns this id (uniform inside the group)
+    float acc[8];
+    bool first = true;
+    while (present) {
+        const int rr = __ffs(present) - 1;
+        present &= present - 1;
+        const int k = rr >> 3;
+        const int sv = k == 0 ? slotv[0] : k == 1 ? slotv[1] : k == 2 ? slotv[2] : slotv[3];
+        const int u = __shfl_sync(gmask, sv, (grp << 3) | (rr & 7));
+        const float* src = rows + ((int64_t)rr * cap + u) * W + 1;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = j + 8 * i;
+            const float v = c < W - 1 ? src[c] : 0.f;
+            acc[i] = first ? v : acc[i] + v;
+        }
+        first = false;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = j + 8 * i;
+        if (c >= W - 1) continue;
         float* dst;
-        if (k < F) dst = g_emb + (int64_t)g * F + k;
-        else if (k == F) dst = g_conf ? g_conf + g : nullptr;
-        else if (k < F + 4) dst = g_dir ? g_dir + (int64_t)g * 3 + (k - F - 1) : nullptr;
-        else dst = g_color ? g_color + (int64_t)g * 3 + (k - F - 4) : nullptr;
-        if (!dst) continue;
-        *dst = mode == 0 ? 0.f : *dst + mine[1 + k];
+        if (c < F) dst = g_emb + (int64_t)g * F + c;
+        else if (c == F) dst = g_conf ? g_conf + g : nullptr;
+        else if (c < F + 4) dst = g_dir ? g_dir + (int64_t)g * 3 + (c - F - 1) : nullptr;
+        else dst = g_color ? g_color + (int64_t)g * 3 + (c - F - 4) : nullptr;
+        if (dst) *dst = acc[i];
     }
 }
 }  // namespace pn
@@ -520,18 +560,18 @@ extern "C" int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int3
     PN_LAUNCH_CHECK("rows_pack");
     return PN_OK;
 }
-extern "C" int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, float* g_emb, float* g_conf, float* g_dir,
-                             float* g_color, void* stream) {
-    PN_CHECK_ARG(gathered && g_emb && n_ranks >= 1 && F >= 1 && F <= 56, "pn_rows_merge: bad argument (F <= 56)");
+extern "C" int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, int64_t n_points, int32_t* slots,
+                             float* g_emb, float* g_conf, float* g_dir, float* g_color, void* stream) {
+    PN_CHECK_ARG(gathered && g_emb && slots && n_points > 0 && n_ranks >= 1 && n_ranks <= 32 && F >= 1 && F <= 56,
+                 "pn_rows_merge: bad argument (F <= 56, n_ranks <= 32)");
     if (cap <= 0) return PN_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t all_rows = (int64_t)n_ranks * cap;
-    rows_apply_kernel<<<(unsigned)cdiv(all_rows * 32, 256), 256, 0, st>>>(gathered, all_rows, F, 0, g_emb, g_conf, g_dir, g_color);
-    PN_LAUNCH_CHECK("rows_zero");
-    for (int r = 0; r < n_ranks; ++r) {
-        rows_apply_kernel<<<(unsigned)cdiv(cap * 32, 256), 256, 0, st>>>(gathered + (int64_t)r * cap * (F + 8), cap, F, 1, g_emb, g_conf,
-                                                                       g_dir, g_color);
-        PN_LAUNCH_CHECK("rows_add");
-    }
+    rows_slot_kernel<<<(unsigned)cdiv(all_rows, 256), 256, 0, st>>>(gathered, cap, n_ranks, F + 8, 1, slots);
+    PN_LAUNCH_CHECK("rows_slot_set");
+    rows_sum_kernel<<<(unsigned)cdiv(cdiv(all_rows, 4) * 32, 256), 256, 0, st>>>(gathered, cap, n_ranks, F, slots, g_emb, g_conf, g_dir, g_color);
+    PN_LAUNCH_CHECK("rows_sum");
+    rows_slot_kernel<<<(unsigned)cdiv(all_rows, 256), 256, 0, st>>>(gathered, cap, n_ranks, F + 8, 0, slots);
+    PN_LAUNCH_CHECK("rows_slot_clear");
     return PN_OK;
 }

@@ -100,30 +100,44 @@ class RayShardedStep:
         self._cap_ev = self._cap_cpu = None
         self._plan = None
         self._mark = None
+        self._slots = None           # slot table of pn_rows_merge (int32 [n_points * world], all -1 between calls)
+        self.caps_piggybacked = 0    # exchanges whose capacity arrived with the previous step's all-reduce (introspection)
+        self._next_cnt = None        # (plan, device count) of the NEXT batch's touched rows, queued by __call__ after prefetch
+        self._cap_next = None        # (plan, event, pinned int32) capacity of the next exchange, produced by this step's all-reduce
         if self.world > 1 and sparse and hasattr(model.aggregator, "forward_tables"):
             model.aggregator.collect_touched = True     # the fused backward returns the sorted unique touched rows
+            # tail of the MLP gradient buffer: [gradients outside tables and MLP (bg_color) | one row-count slot per rank]
+            n_rest = sum(p.numel() for p in self.params if isinstance(bg_color, torch.nn.Parameter) and p is bg_color)
+            self._tail_rest = (n_rest + 63) // 64 * 64
+            model.aggregator.flat_tail_floats = self._tail_rest + (self.world + 63) // 64 * 64
 
     # ---- sparse exchange on the C ABI (CUDA tables) -------------------------------------------------------------
     def _begin_cap_exchange(self):
         """Right after the forward: the number of distinct table rows the batch references (= the touched rows of the
         coming backward) is counted on the device, max-reduced over ranks and copied to a pinned host word - all queued
         BEFORE the backward, so the exchange after it finds the capacity on the host without stalling anything."""
-        from . import _lib
         call = getattr(self.model.aggregator, "last_call", None)
         if call is None or not call.sample_pidx.is_cuda:
             return
         dev = call.sample_pidx.device
         if self._cap_cpu is None:
             self._cap_cpu = torch.zeros(1, dtype=torch.int32).pin_memory()
-        if self._mark is None or self._mark.numel() < call.T:
-            self._mark = torch.empty(max(call.T, 1), dtype=torch.int32, device=dev)
-        cnt = torch.empty(1, dtype=torch.int32, device=dev)
-        _lib.check(_lib.lib().pn_count_touched_rows(_lib.ptr(call.sample_pidx), call.sample_pidx.numel(), call.T, _lib.ptr(self._mark),
-                                                    _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+        cnt = self._count_rows(call.sample_pidx, call.T)
         dist.all_reduce(cnt, op=dist.ReduceOp.MAX, group=self.group)
         self._cap_cpu.copy_(cnt, non_blocking=True)
         self._cap_ev = torch.cuda.Event()
         self._cap_ev.record(torch.cuda.current_stream(dev))
+
+    def _count_rows(self, sample_pidx, T):
+        """Device int32[1]: distinct table rows referenced by a query result (pn_count_touched_rows), no host sync."""
+        from . import _lib
+        dev = sample_pidx.device
+        if self._mark is None or self._mark.numel() < T:
+            self._mark = torch.empty(max(T, 1), dtype=torch.int32, device=dev)
+        cnt = torch.empty(1, dtype=torch.int32, device=dev)
+        _lib.check(_lib.lib().pn_count_touched_rows(_lib.ptr(sample_pidx), sample_pidx.numel(), T, _lib.ptr(self._mark),
+                                                    _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+        return cnt
 
     def _sparse_tables_cuda(self, tables_by_name):
         from . import _lib
@@ -141,7 +155,11 @@ class RayShardedStep:
                    "pn_rows_pack")
         gathered = torch.empty((self.world * cap, F + 8), dtype=torch.float32, device=dev)
         dist.all_gather_into_tensor(gathered, packed, group=self.group)
-        _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, _lib.ptr(g["points_embeding"]), _lib.ptr(g["points_conf"]),
+        T = int(emb.shape[1])
+        if self._slots is None or self._slots.numel() != T * self.world:
+            self._slots = torch.full((T * self.world,), -1, dtype=torch.int32, device=dev)   # once: the merge leaves it all -1
+        _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, T, _lib.ptr(self._slots),
+                                     _lib.ptr(g["points_embeding"]), _lib.ptr(g["points_conf"]),
                                      _lib.ptr(g["points_dir"]), _lib.ptr(g["points_color"]), _lib.stream()), "pn_rows_merge")
         for k_, t in tables_by_name.items():
             if t is not None and t.grad.data_ptr() != g[k_].data_ptr():
@@ -200,10 +218,22 @@ class RayShardedStep:
         flat = getattr(getattr(self.model.aggregator, "last_call", None), "grad_flat", None)
         lo, hi = (flat.data_ptr(), flat.data_ptr() + 4 * flat.numel()) if flat is not None else (0, 0)
         rest = [p for p in self.params if id(p) not in tset and not (lo <= p.grad.data_ptr() < hi)]
-        mode = None
+        mode, tail = None, None
         if self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._cap_ev is not None:
             mode = "cuda"        # ids from the fused backward, pack / merge kernels of the C ABI
-            if rest:             # one small all-gather for the few gradients outside the tables and the MLP buffer
+            call = self.model.aggregator.last_call
+            n_rest = sum(p.numel() for p in rest)
+            if flat is not None and n_rest <= self._tail_rest and call.flat_tail >= self._tail_rest + self.world:
+                # the few gradients outside the tables and the MLP (bg_color) and the NEXT batch's touched-row count ride in
+                # the zeroed tail of the MLP gradient buffer: one all-reduce(SUM) instead of three small collectives
+                tail = off = call.flat_tail_off
+                for p in rest:
+                    flat[off:off + p.numel()].copy_(p.grad.reshape(-1))
+                    off += p.numel()
+                if self._next_cnt is not None:          # one slot per rank: SUM leaves every rank's count in place
+                    slot = tail + self._tail_rest + dist.get_rank(self.group)
+                    flat[slot:slot + 1].copy_(self._next_cnt[1])
+            elif rest:           # one small all-gather for them
                 head = torch.cat([p.grad.reshape(-1) for p in rest])
                 self._head_all = torch.empty((self.world, head.numel()), dtype=torch.float32, device=head.device)
                 dist.all_gather_into_tensor(self._head_all, head, group=self.group)
@@ -220,7 +250,7 @@ class RayShardedStep:
         if mode == "cuda":
             self._sparse_tables_cuda({n: (getattr(nps, n) if getattr(nps, n) is not None and getattr(nps, n).requires_grad else None)
                                       for n in names})
-            if rest:             # rank-ordered sum of the gathered head columns: identical bits on every replica
+            if rest and tail is None:   # rank-ordered sum of the gathered head columns: identical bits on every replica
                 tot = self._head_all.sum(0)
                 off = 0
                 for p in rest:
@@ -239,6 +269,22 @@ class RayShardedStep:
                     off += p.numel()
         for h in handles:
             h.wait()
+        if tail is not None:
+            off = tail
+            for p in rest:       # the reduced values, in place in the tail (same bits on every replica)
+                p.grad = flat[off:off + p.numel()].view_as(p)
+                off += p.numel()
+            if self._next_cnt is not None:
+                # capacity of the NEXT exchange = max over ranks of the counts just summed into their slots: on its way to
+                # the host a whole step before it is needed, and the 4-byte MAX all-reduce of that step is not issued
+                a = tail + self._tail_rest
+                if self._cap_cpu is None:
+                    self._cap_cpu = torch.zeros(1, dtype=torch.int32).pin_memory()
+                self._cap_cpu.copy_(flat[a:a + self.world].max().to(torch.int32).reshape(1), non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                self._cap_next = (self._next_cnt[0], ev)
+        self._next_cnt = None
 
     def prefetch(self, cam, raydir, uniform=None):
         """Queue the weight-independent part of a FUTURE batch (ray sampling, neighbour query, work lists) now.  Called by
@@ -270,7 +316,12 @@ class RayShardedStep:
                          uniform=uniform, **kw)
         self._cap_ev = None
         if self.world > 1 and self.sparse:
-            self._begin_cap_exchange()
+            held, self._cap_next = self._cap_next, None
+            if held is not None and plan is not None and held[0] is plan:
+                self._cap_ev = held[1]                  # agreed during the previous step's all-reduce
+                self.caps_piggybacked += 1
+            else:
+                self._begin_cap_exchange()
         pred = out["coarse_raycolor"]
         if pred.is_cuda:               # one fused kernel pair: loss and d(loss)/d(colour) (pn_color_mse)
             loss = color_mse(pred, gt, norm=global_rays * gt.shape[-1])
@@ -281,6 +332,9 @@ class RayShardedStep:
             if next_batch.get("ready") is not None:        # event of the side-stream H2D copy that produced the batch
                 torch.cuda.current_stream().wait_event(next_batch["ready"])
             self.prefetch(next_batch["cam"], next_batch["raydir"], next_batch.get("uniform"))
+            if self.world > 1 and self.sparse and reduce and self._plan is not None and self._cap_ev is not None:
+                nxt = self._plan[2]
+                self._next_cnt = (nxt, self._count_rows(nxt.pidx, int(self.model.neural_points.points_embeding.shape[-2])))
         loss.backward()
         if reduce:
             self.all_reduce()

@@ -9,14 +9,15 @@ from oracle import torch_port as tp
 pytestmark = pytest.mark.gpu
 
 
-def test_pack_merge_equals_rank_ordered_sum(cuda_dev):
+@pytest.mark.parametrize("G", [2, 3, 8])
+def test_pack_merge_equals_rank_ordered_sum(cuda_dev, G):
     lib = _lib.lib()
-    d, N, F, G, cap = cuda_dev, 5000, 32, 3, 2048
+    d, N, F, cap = cuda_dev, 5000, 32, 2048
     g = torch.Generator().manual_seed(0)
     dense = []          # per-rank dense gradient tables, non-zero on that rank's touched rows only
     packed = []
     for r in range(G):
-        n_t = [700, 1500, 33][r]
+        n_t = [700, 1500, 33, 0, 2048, 1, 999, 1200][r]       # an empty rank, a full list, a single row
         ids = torch.sort(torch.randperm(N, generator=g)[:n_t])[0].to(torch.int32)
         tabs = dict(emb=torch.zeros(N, F), conf=torch.zeros(N), dir=torch.zeros(N, 3), color=torch.zeros(N, 3))
         for k, t in tabs.items():
@@ -32,12 +33,16 @@ def test_pack_merge_equals_rank_ordered_sum(cuda_dev):
     gathered = torch.cat(packed, 0).contiguous()
     for r in range(G):   # every rank starts from ITS OWN dense table and must end with the same bits
         td = {k: v.to(d).clone() for k, v in dense[r].items()}
-        _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), G, cap, F, _lib.ptr(td["emb"]), _lib.ptr(td["conf"]), _lib.ptr(td["dir"]),
-                                     _lib.ptr(td["color"]), _lib.stream()), "pn_rows_merge")
+        n_points = int(td["emb"].shape[0])
+        slots = torch.full((n_points * G,), -1, dtype=torch.int32, device=d)
+        for _ in range(2):      # the slot table is left all -1, so a second merge over the same buffer is idempotent
+            _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), G, cap, F, n_points, _lib.ptr(slots), _lib.ptr(td["emb"]),
+                                         _lib.ptr(td["conf"]), _lib.ptr(td["dir"]), _lib.ptr(td["color"]), _lib.stream()), "pn_rows_merge")
+            assert bool((slots == -1).all())
         for k in td:
             want = dense[0][k].clone()
             for rr in range(1, G):
-                want = want + dense[rr][k]          # rank order 0, 1, 2: fp32 adds in the same order as the kernel
+                want = want + dense[rr][k]          # rank order 0, 1, 2, ...: fp32 adds in the same order as the kernel
             # rows touched by no rank keep the local value (zero); rows touched only by other ranks are filled in
             assert torch.equal(td[k].cpu(), want), (r, k)
 
