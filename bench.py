@@ -57,6 +57,12 @@ def _emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+def _phase(msg):
+    """Progress marker on stderr (rank-tagged): a hung multi-GPU run shows where it stopped."""
+    sys.stderr.write("[bench rank %s] %s\n" % (os.environ.get("RANK", "0"), msg))
+    sys.stderr.flush()
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -288,6 +294,92 @@ def cpu_oracle_steps(opt, tables, batches, bg, agg_state, rays, steps, warmup):
 
 
 # ---------------------------------------------------------------------------------------------------------
+# full-frame inference (BASELINE.json metric, second item: ms per 800x800 frame) and PSNR against the oracle
+# ---------------------------------------------------------------------------------------------------------
+def frame_bench(model, opt, name, bg_dev, dev, rank, world, chunk, frames=3):
+    """Forward-only render of the workload's full frame (cfg2/cfg5 camera: 800x800 = 640 000 rays) through
+    NeuralPointsRayMarching.render_frame, is_train = 0 (no jitter).  N > 1: each rank renders its block of rows; the time is
+    the max over ranks.  `ms` has the rays resident in HBM; `e2e_ms` uploads the ray directions from pinned host memory and
+    reads the [R, C] image back to pinned host memory inside the timed region."""
+    from pointnerf_b200 import synthetic as syn
+    cam = syn.make_camera(name, view=1)
+    raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
+    R_all = raydir.shape[1]
+    lo, hi = R_all * rank // world, R_all * (rank + 1) // world
+    ray_host = raydir[:, lo:hi].contiguous().pin_memory()
+    campos, rot = cam["campos"].to(dev), cam["camrotc2w"].to(dev)
+    C = int(opt.shading_color_channel_num)
+    img_host = torch.empty((1, hi - lo, C), dtype=torch.float32).pin_memory()
+    was = opt.is_train
+    opt.is_train = 0
+    try:
+        ray_dev = ray_host.to(dev)
+        warm = model.render_frame(campos, ray_dev, bg_dev, rot, cam["near"], cam["far"], chunk=chunk, keys=("coarse_raycolor", "ray_mask"))   # warm-up
+        frac_hit = float((warm["ray_mask"] > 0).float().mean())
+        del warm
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(frames):
+            img = model.render_frame(campos, ray_dev, bg_dev, rot, cam["near"], cam["far"], chunk=chunk)["coarse_raycolor"]
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / frames
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(frames):
+            rd = ray_host.to(dev, non_blocking=True)
+            img = model.render_frame(campos, rd, bg_dev, rot, cam["near"], cam["far"], chunk=chunk)["coarse_raycolor"]
+            img_host.copy_(img, non_blocking=True)
+        f1.record()
+        torch.cuda.synchronize()
+        e2e_ms = f0.elapsed_time(f1) / frames
+    finally:
+        opt.is_train = was
+    t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    assert bool(torch.isfinite(img_host).all())
+    return {"ms": round(ms, 3), "e2e_ms": round(e2e_ms, 3), "h": cam["h"], "w": cam["w"], "rays": R_all, "SR": int(opt.SR), "K": int(opt.K),
+            "chunk_rays": int(chunk), "rays_per_s": round(R_all / (ms * 1e-3), 1), "frac_rays_with_neighbours": round(frac_hit, 4),
+            "h2d_bytes": int(ray_host.numel() * 4), "d2h_bytes": int(img_host.numel() * 4),
+            "note": "forward only, grid cached, %d GPU(s) by row blocks" % world}
+
+
+def psnr_vs_oracle(dev):
+    """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
+    oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
+    perturbed embeddings).  Part of the cpu_baseline leg (the oracle is the checker here, never the thing shipped)."""
+    from oracle import pipeline_ref
+    from pointnerf_b200 import synthetic as syn
+    opt, tables = syn.make_scene("tiny")
+    opt = copy.copy(opt)
+    opt.is_train = 0
+    cam = syn.make_camera("tiny")
+    raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
+    model = make_model(opt, tables, dev)
+    g = torch.Generator().manual_seed(5)
+    bg = torch.rand(int(opt.shading_color_channel_num), generator=g)
+    sd = {k: v.detach().cpu() for k, v in model.aggregator.state_dict().items()}
+    ours = model.render_frame(cam["campos"].to(dev), raydir.to(dev), bg.to(dev), cam["camrotc2w"].to(dev), cam["near"], cam["far"],
+                              chunk=1024)["coarse_raycolor"].cpu()
+    ref = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, need_grads=False)["coarse_raycolor"]
+    t2 = dict(tables)
+    t2["points_embeding"] = tables["points_embeding"] + 0.05 * torch.randn(tables["points_embeding"].shape, generator=g)
+    gt = pipeline_ref.run(opt, t2, cam, raydir, bg, sd, need_grads=False)["coarse_raycolor"]
+
+    def psnr(a, b):
+        mse = float(((a.double() - b.double()) ** 2).mean())
+        peak = float(gt.abs().max())
+        return 10.0 * np.log10(peak * peak / max(mse, 1e-300))
+    po, pr = psnr(ours, gt), psnr(ref, gt)
+    return {"scene": "tiny, full %dx%d frame, C=%d feature channels, peak = max|gt|" % (cam["h"], cam["w"], ref.shape[-1]),
+            "ours_vs_oracle_db": round(psnr(ours, ref), 2), "ours_vs_gt_db": round(po, 4), "oracle_vs_gt_db": round(pr, 4),
+            "delta_db": round(abs(po - pr), 6), "max_abs_diff": float((ours - ref).abs().max())}
+
+
+# ---------------------------------------------------------------------------------------------------------
 def dominant_kernel_roofline(_lib, dev, M, peak, peaks, N=256, K=256, reps=20):
     """gemm_nt_img2_kernel at [M,K] x [N,K]^T through the C ABI's GEMM hook, CUDA events on the launching stream.
     ALGORITHMIC flops = 2*M*N*K (the kernel issues 3x that as TF32 MMAs: hi*lo, lo*hi, hi*hi); traffic = DRAM bytes of one
@@ -341,6 +433,8 @@ def main():
     ap.add_argument("--cpu-rays", type=int, default=1024, help="rays per CPU-oracle step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
+    ap.add_argument("--no-frame", action="store_true", help="skip the full-frame inference timing (ms per 800x800 frame)")
+    ap.add_argument("--frame-chunk", type=int, default=65536, help="rays per render_frame chunk")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
     args = ap.parse_args()
 
@@ -405,9 +499,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    _phase("model built; warm-up")
     for w in range(warmup):
         step(w)
     sync_all()
+    _phase("timed loop")
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -430,6 +526,7 @@ def main():
     value = global_rays * args.steps / (ms_total * 1e-3)
 
     # ---- end to end: pinned host buffers -> H2D -> step -> D2H of the loss, every step
+    _phase("timed loop done (%.3f ms/step); e2e loop" % (ms_total / args.steps))
     packed = [pack_pinned(b) for b in batches]
     h2d = packed[0][1]["bytes"]
 
@@ -498,7 +595,14 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = global_rays * args.steps / (float(t.item()) * 1e-3)
 
+    # ---- full-frame inference (all ranks: row blocks)
+    _phase("e2e done; frame render")
+    frame = None
+    if not args.no_frame:
+        frame = frame_bench(model, opt, args.workload, bg_p.detach(), dev, rank, world, args.frame_chunk)
+
     # ---- per-stage device time (events around each C-ABI call) and the roofline of the dominant stage
+    _phase("stages / roofline / cpu baseline (rank 0 only, no collectives)")
     stages, roof, counts = None, None, None
     if rank == 0 and not args.no_stages:
         n_stage_steps = min(args.steps, 8)
@@ -547,6 +651,7 @@ def main():
                "sample": "3 steps of %d rays (first %d of a %d-ray batch), fwd+bwd, %.2f s/step; querier = %s, aggregator/ray_march = torch restatement of the reference modules"
                          % (args.cpu_rays, args.cpu_rays, args.rays, spstep,
                             "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port")}
+        cpu["psnr"] = psnr_vs_oracle(dev)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
@@ -567,10 +672,12 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
-                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages}
+                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, "frame_800x800": frame}
         _emit(line)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    _phase("done")
     return 0
 
 

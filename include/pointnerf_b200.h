@@ -325,6 +325,40 @@ int64_t pn_color_mse_workspace_bytes(void);
 int pn_color_mse(const float* pred, const float* target, const float* ray_weight, int64_t n_rays, int32_t C,
                  float inv_norm, float* loss, float* grad, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 5. Point-cloud maintenance between passes
+ *
+ * pn_probe_rays - the probe outputs of one batch of rays (models/neural_points_volumetric_model_ori.py:351-372,
+ *   consumed by probe_hole, run/train_ft.py:420-533): per ray the sample of largest opacity (first among ties, like
+ *   torch.max), its world location, the distance to the nearest of its K neighbour rows (empty neighbour slots read
+ *   table row 0, as the reference's clamp(min=0) gather does) and the (weight * clamp(conf, lo, hi))-weighted sums of
+ *   the neighbours' colour / dir / conf / embedding.  Uncompacted ray layout: rays with ray_any <= 0 get zeros and
+ *   max_slot = -1, which is what `unmask` (:131-137) leaves for them.
+ *     opacity [R,SR]; ray_any int32[R]; sample_loc_w [R,SR,3]; sample_pidx int32[R,SR,K]; weight [R,SR,K] (weight_out
+ *     of pn_agg_forward); tables xyz [N,3], embedding [N,F], color/dir [N,3], conf [N]
+ *     -> max_opacity [R], max_slot int32[R], max_loc_w [R,3], far_dist [R], avg_color/avg_dir [R,3], avg_conf [R],
+ *        avg_embedding [R,F]
+ *
+ * pn_prune_mark + pn_points_compact - NeuralPoints.prune (models/neural_points/neural_points.py:350-373):
+ *   dst_index int32[N+1] = exclusive scan of (conf[i] >= thresh), dst_index[N] = rows kept (the caller reads it to size
+ *   the new tables); pn_points_compact then moves every kept row of all five tables in ONE pass (a warp per row) where
+ *   the reference runs a boolean-mask gather per table.  conf/dir/color (and their outputs) may be NULL.
+ *   The output tables may be LARGER than the kept count: NeuralPoints.grow_points (:376-402) appends its rows behind
+ *   them in the same allocation instead of a second torch.cat pass over every table.
+ * ---------------------------------------------------------------------------------------------- */
+int pn_probe_rays(const float* opacity, const int32_t* ray_any, const float* sample_loc_w, const int32_t* sample_pidx,
+                  const float* weight, const float* xyz, const float* embedding, const float* color, const float* dir,
+                  const float* conf, int64_t n_rays, int32_t SR, int32_t K, int32_t F, float conf_lo, float conf_hi,
+                  float* max_opacity, int32_t* max_slot, float* max_loc_w, float* far_dist, float* avg_color,
+                  float* avg_dir, float* avg_conf, float* avg_embedding, void* stream);
+
+int64_t pn_prune_workspace_bytes(int64_t n_points);
+int pn_prune_mark(const float* conf, int64_t n_points, float thresh, int32_t* dst_index, void* workspace,
+                  int64_t workspace_bytes, void* stream);
+int pn_points_compact(const int32_t* dst_index, int64_t n_points, int32_t F, const float* xyz, const float* embedding,
+                      const float* conf, const float* dir, const float* color, float* out_xyz, float* out_embedding,
+                      float* out_conf, float* out_dir, float* out_color, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

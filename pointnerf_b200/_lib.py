@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -108,6 +108,11 @@ def _declare(lib):
         "pn_gather_clamp": (c_int, [P, c_int64, P, c_int64, c_float, c_float, P, P]),
         "pn_color_mse_workspace_bytes": (c_int64, []),
         "pn_color_mse": (c_int, [P, P, P, c_int64, c_int32, c_float, P, P, P, c_int64, P]),
+        "pn_probe_rays": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float, c_float,
+                                  P, P, P, P, P, P, P, P, P]),
+        "pn_prune_workspace_bytes": (c_int64, [c_int64]),
+        "pn_prune_mark": (c_int, [P, c_int64, c_float, P, P, c_int64, P]),
+        "pn_points_compact": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, P, P, P, P, P]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: loud by design

@@ -20,6 +20,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
+from . import _lib
 from . import query as _query
 from .aggregator import CompactSamples, PointAggregator, gather_clamp
 from .query import lighting_fast_querier
@@ -65,30 +66,66 @@ class NeuralPoints(nn.Module):
             self.Rw2c = nn.Parameter(Rw2c.to(dev).float().contiguous(), requires_grad=False)
         self.querier.clean_up()  # the cached grid belongs to the old point set
 
+    _TABLES = ("points_embeding", "points_conf", "points_dir", "points_color")
+
     def prune(self, thresh):
-        """neural_points.py:350-373: keep points with conf >= thresh; invalidates the grid."""
-        mask = self.points_conf[0, :, 0] >= thresh
-        self.xyz = nn.Parameter(self.xyz[mask].contiguous(), requires_grad=self.xyz.requires_grad)
-        for name in ("points_embeding", "points_conf", "points_dir", "points_color"):
-            t = getattr(self, name)
-            if t is not None:
-                setattr(self, name, nn.Parameter(t[:, mask].contiguous(), requires_grad=t.requires_grad))
-        self.querier.clean_up()
-        return int(mask.sum())
+        """neural_points.py:350-373: keep points with conf >= thresh; invalidates the grid.  Returns the kept count."""
+        return self.prune_and_grow(thresh)
 
     def grow_points(self, add_xyz, add_embedding, add_color, add_dir, add_conf):
-        """neural_points.py:376-402: append points; invalidates the grid."""
-        def cat(old, new, dim):
-            return nn.Parameter(torch.cat([old, new.to(old.device).float()], dim=dim).contiguous(), requires_grad=old.requires_grad)
-        self.xyz = cat(self.xyz, add_xyz, 0)
-        self.points_embeding = cat(self.points_embeding, add_embedding, 1)
-        if self.points_conf is not None:
-            self.points_conf = cat(self.points_conf, add_conf, 1)
-        if self.points_dir is not None:
-            self.points_dir = cat(self.points_dir, add_dir, 1)
-        if self.points_color is not None:
-            self.points_color = cat(self.points_color, add_color, 1)
-        self.querier.clean_up()
+        """neural_points.py:376-402: append points (add_* are [n,*] like the reference's); invalidates the grid."""
+        self.prune_and_grow(None, add_xyz, add_embedding, add_color, add_dir, add_conf)
+
+    def prune_and_grow(self, thresh=None, add_xyz=None, add_embedding=None, add_color=None, add_dir=None, add_conf=None):
+        """``prune(thresh)`` followed by ``grow_points(add_*)`` (the pair run/train_ft.py:841-849 issues between passes)
+        with ONE allocation and one pass per table: kept rows are moved by pn_points_compact (all five tables in one
+        launch, order preserved like boolean-mask indexing) and the new rows are written behind them.  Either half may be
+        omitted.  Same resulting tables / requires_grad flags as the reference's two methods.  Returns the kept count."""
+        lib = _lib.lib()
+        dev = self.xyz.device
+        N, F_ = int(self.xyz.shape[0]), int(self.points_embeding.shape[-1])
+        n_add = 0 if add_xyz is None else int(add_xyz.shape[0])
+        dst = None
+        kept = N
+        if thresh is not None:
+            if self.points_conf is None:
+                raise RuntimeError("prune needs points_conf")
+            dst = torch.empty(N + 1, dtype=torch.int32, device=dev)
+            ws_bytes = lib.pn_prune_workspace_bytes(N)
+            ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
+            _lib.check(lib.pn_prune_mark(_lib.ptr(self.points_conf.detach()), N, float(thresh), _lib.ptr(dst), _lib.ptr(ws), ws_bytes,
+                                         _lib.stream()), "pn_prune_mark")
+            kept = int(dst[N].item())            # host sync: the new tables' size (the reference syncs in every mask index)
+        if dst is None and n_add == 0:
+            return kept
+        total = kept + n_add
+        old = {n: getattr(self, n) for n in self._TABLES}
+        new_xyz = torch.empty((total, 3), dtype=torch.float32, device=dev)
+        new = {n: (None if t is None else torch.empty((1, total, t.shape[-1]), dtype=torch.float32, device=dev)) for n, t in old.items()}
+        if dst is not None:
+            _lib.check(lib.pn_points_compact(
+                _lib.ptr(dst), N, F_, _lib.ptr(self.xyz.detach()), _lib.ptr(old["points_embeding"].detach()),
+                _lib.ptr(old["points_conf"].detach()), _lib.ptr(None if old["points_dir"] is None else old["points_dir"].detach()),
+                _lib.ptr(None if old["points_color"] is None else old["points_color"].detach()),
+                _lib.ptr(new_xyz), _lib.ptr(new["points_embeding"]), _lib.ptr(new["points_conf"]), _lib.ptr(new["points_dir"]),
+                _lib.ptr(new["points_color"]), _lib.stream()), "pn_points_compact")
+        else:
+            new_xyz[:N].copy_(self.xyz.detach())
+            for n, t in old.items():
+                if t is not None:
+                    new[n][0, :N].copy_(t.detach()[0])
+        if n_add:
+            adds = {"points_embeding": add_embedding, "points_conf": add_conf, "points_dir": add_dir, "points_color": add_color}
+            new_xyz[kept:].copy_(add_xyz)
+            for n, t in new.items():
+                if t is not None:
+                    t[0, kept:].copy_(adds[n].reshape(n_add, -1))
+        self.xyz = nn.Parameter(new_xyz, requires_grad=self.xyz.requires_grad)
+        for n, t in new.items():
+            if t is not None:
+                setattr(self, n, nn.Parameter(t, requires_grad=old[n].requires_grad))
+        self.querier.clean_up()                  # the cached grid belongs to the old point set
+        return kept
 
     def w2pers(self, point_xyz, camrotc2w, campos):
         """neural_points.py:687-693: [N,3] -> [1,N,3] (x/z, y/z, z) in the camera frame."""
@@ -203,7 +240,7 @@ class NeuralPointsRayMarching(nn.Module):
         return call.sample_pidx.view(-1)[call.pair_src[:call.M].long()].long()
 
     # ---- fused path -----------------------------------------------------------------------------
-    def sample(self, campos, raydir, camrotc2w, near, far, uniform=None):
+    def sample(self, campos, raydir, camrotc2w, near, far, uniform=None, xyz_pers=None):
         """Everything of one batch that does not depend on the trainable tensors: ray sampling, neighbour query,
         perspective coordinates and the work lists, queued on the current stream with NO host sync.  ``forward(plan=...)``
         consumes it; a training loop calls this for batch i+1 before the backward of batch i so that the (S, M)
@@ -218,9 +255,34 @@ class NeuralPointsRayMarching(nn.Module):
         plan = RayPlan()
         plan.raw, plan.pidx, plan.loc_w, plan.raydir = raw, pidx, loc_w, raydir
         plan.loc_pers = _query.w2pers(loc_w, camrotc2w[0], campos[0])
-        plan.xyz_pers = _query.w2pers(xyz, camrotc2w[0], campos[0])
+        # the points' camera-frame coordinates depend on the camera only: a frame renderer passes them along
+        plan.xyz_pers = xyz_pers if xyz_pers is not None else _query.w2pers(xyz, camrotc2w[0], campos[0])
         plan.work_lists = CompactSamples(pidx.contiguous(), R * SR, K)
         return plan
+
+    @torch.no_grad()
+    def render_frame(self, campos, raydir, bg_color, camrotc2w, near, far, chunk=65536, keys=("coarse_raycolor",)):
+        """Full-frame inference: the chunk loop of run/train_ft.py:test (:284-340, ``chunk_size = random_sample_size**2``
+        rays per ``model.test()`` call) over raydir [1,R,3], forward only.  The sampling / neighbour query / work lists of
+        chunk i+1 are queued before the aggregator of chunk i, so the (S, M) read-back of a chunk never drains the GPU
+        queue; chunks reuse the same activation buffers through the caching allocator (nothing is kept for a backward).
+        Returns {key: [1,R,...]} for ``keys`` (any of the ``forward`` outputs)."""
+        R = int(raydir.shape[1])
+        starts = list(range(0, R, int(chunk)))
+        outs = {k: [] for k in keys}
+        xp = _query.w2pers(self.neural_points.xyz.detach(), camrotc2w[0], campos[0])
+        plan = self.sample(campos, raydir[:, :chunk], camrotc2w, near, far, xyz_pers=xp) if R else None
+        for i, s in enumerate(starts):
+            nxt = None
+            if i + 1 < len(starts):
+                s2 = starts[i + 1]
+                nxt = self.sample(campos, raydir[:, s2:s2 + chunk], camrotc2w, near, far, xyz_pers=xp)
+            o = self.forward(campos, raydir[:, s:s + chunk], bg_color=bg_color, camrotc2w=camrotc2w, near=near, far=far, plan=plan)
+            for k in keys:
+                outs[k].append(o[k])
+            plan = nxt
+        return {k: (torch.cat(v, dim=1) if len(v) != 1 else v[0]) for k, v in outs.items()} if R else \
+            {k: torch.zeros((1, 0, 0), device=raydir.device) for k in keys}
 
     def forward(self, campos, raydir, gt_image=None, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None,
                 focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, plan=None, **kargs):
@@ -253,4 +315,32 @@ class NeuralPointsRayMarching(nn.Module):
             out["weight"] = weight.detach()[None]
             out["blend_weight"] = blend_weight.detach()
             out["conf_coefficient"] = gather_clamp(nps.points_conf, pidx, 0.0001, 1.0)[None]
+            if getattr(o, "prob", 0) == 1:
+                out.update(self.probe_outputs(opacity, raw["ray_any"], loc_w, pidx, weight))
         return out
+
+    @torch.no_grad()
+    def probe_outputs(self, opacity, ray_any, sample_loc_w, sample_pidx, weight):
+        """The ``opt.prob == 1`` block of neural_points_volumetric_model_ori.py:351-372 in one launch (pn_probe_rays), on
+        the UNCOMPACTED ray layout: every output is [1,R,...] with zeros on rays the query dropped - what ``unmask``
+        (:126-137) hands to probe_hole (run/train_ft.py:420-533).  Keys / shapes as the reference's:
+        ray_max_shading_opacity [1,R,1], ray_max_sample_loc_w [1,R,3], ray_max_far_dist [1,R,1], shading_avg_color /
+        shading_avg_dir [1,R,3], shading_avg_conf [1,R,1], shading_avg_embedding [1,R,F] (+ ray_max_slot int32 [1,R])."""
+        nps = self.neural_points
+        if nps.points_color is None or nps.points_dir is None or nps.points_conf is None:
+            raise NotImplementedError("probe outputs need points_color / points_dir / points_conf (every shipped script has them)")
+        R, SR, K = (int(v) for v in sample_pidx.shape)
+        F_ = int(nps.points_embeding.shape[-1])
+        dev = sample_pidx.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        o_op, o_slot = torch.empty((1, R, 1), **f32), torch.empty((1, R), dtype=torch.int32, device=dev)
+        o_loc, o_far = torch.empty((1, R, 3), **f32), torch.empty((1, R, 1), **f32)
+        o_col, o_dir, o_cnf, o_emb = torch.empty((1, R, 3), **f32), torch.empty((1, R, 3), **f32), torch.empty((1, R, 1), **f32), torch.empty((1, R, F_), **f32)
+        _lib.check(_lib.lib().pn_probe_rays(
+            _lib.ptr(opacity.detach().reshape(R, SR).contiguous()), _lib.ptr(ray_any.contiguous()), _lib.ptr(sample_loc_w.contiguous()),
+            _lib.ptr(sample_pidx.contiguous()), _lib.ptr(weight.detach().contiguous()), _lib.ptr(nps.xyz.detach()),
+            _lib.ptr(nps.points_embeding.detach()), _lib.ptr(nps.points_color.detach()), _lib.ptr(nps.points_dir.detach()),
+            _lib.ptr(nps.points_conf.detach()), R, SR, K, F_, 0.0001, 1.0, _lib.ptr(o_op), _lib.ptr(o_slot), _lib.ptr(o_loc),
+            _lib.ptr(o_far), _lib.ptr(o_col), _lib.ptr(o_dir), _lib.ptr(o_cnf), _lib.ptr(o_emb), _lib.stream()), "pn_probe_rays")
+        return {"ray_max_shading_opacity": o_op, "ray_max_sample_loc_w": o_loc, "ray_max_far_dist": o_far, "shading_avg_color": o_col,
+                "shading_avg_dir": o_dir, "shading_avg_conf": o_cnf, "shading_avg_embedding": o_emb, "ray_max_slot": o_slot}

@@ -315,7 +315,7 @@ class RayShardedStep:
         out = self.model(cam["campos"], raydir, bg_color=self.bg, camrotc2w=cam["camrotc2w"], near=cam["near"], far=cam["far"],
                          uniform=uniform, **kw)
         self._cap_ev = None
-        if self.world > 1 and self.sparse:
+        if self.world > 1 and self.sparse and reduce:   # (reduce=False: a rank-local step, e.g. per-stage timing on one rank, issues NO collective)
             held, self._cap_next = self._cap_next, None
             if held is not None and plan is not None and held[0] is plan:
                 self._cap_ev = held[1]                  # agreed during the previous step's all-reduce

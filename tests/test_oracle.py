@@ -212,3 +212,29 @@ def test_golden_querier(tiny_scene):
     assert np.array_equal(ray_mask.numpy(), z["ray_mask"])
     assert np.array_equal(ranges, z["ranges"])
     assert np.array_equal(ex["grid"]["occ_numpnts"][:int(ex["grid"]["occ_idx"][0])], z["occ_numpnts"])
+
+
+def test_probe_restatement_against_per_ray_loop():
+    """oracle/maintenance_port.probe_outputs (vectorised gathers of neural_points_volumetric_model_ori.py:351-372) against
+    a plain per-ray loop of the same definition."""
+    from oracle import maintenance_port as mp
+    g = torch.Generator().manual_seed(4)
+    R, SR, K, F_ = 7, 5, 4, 6
+    op = torch.rand(1, R, SR, generator=g)
+    op[0, 2] = 0.0                                   # all-equal opacities: first index wins
+    loc = torch.randn(1, R, SR, 3, generator=g)
+    w, cc = torch.rand(1, R, SR, K, generator=g), torch.rand(1, R, SR, K, generator=g)
+    sx, sc, sd = (torch.randn(1, R, SR, K, 3, generator=g) for _ in range(3))
+    sf, se = torch.rand(1, R, SR, K, 1, generator=g), torch.randn(1, R, SR, K, F_, generator=g)
+    out = mp.probe_outputs(op, loc, w, cc, sx, sc, sd, sf, se)
+    for r in range(R):
+        s = int(torch.argmax(op[0, r]))
+        assert int(out["ray_max_slot"][0, r]) == s and (s == 0 if r == 2 else True)
+        assert torch.equal(out["ray_max_sample_loc_w"][0, r], loc[0, r, s])
+        ww = (w[0, r, s] * cc[0, r, s])[:, None]
+        assert torch.allclose(out["shading_avg_embedding"][0, r], (se[0, r, s] * ww).sum(0))
+        assert torch.allclose(out["shading_avg_conf"][0, r], (sf[0, r, s] * ww).sum(0))
+        assert torch.allclose(out["ray_max_far_dist"][0, r, 0], (sx[0, r, s] - loc[0, r, s]).norm(dim=-1).min())
+    mask = torch.tensor([[1, 0, 1, 1, 0, 1, 1, 1, 0, 1]], dtype=torch.int8)
+    full = mp.unmask(mask, {"a": out["shading_avg_color"]})["a"]
+    assert full.shape == (1, 10, 3) and bool((full[0, 1] == 0).all()) and torch.equal(full[0, 2], out["shading_avg_color"][0, 1])
