@@ -435,6 +435,7 @@ def main():
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-frame", action="store_true", help="skip the full-frame inference timing (ms per 800x800 frame)")
     ap.add_argument("--frame-chunk", type=int, default=65536, help="rays per render_frame chunk")
+    ap.add_argument("--no-adam", action="store_true", help="skip the secondary timing of the step WITH the Adam updates")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
     args = ap.parse_args()
 
@@ -601,6 +602,39 @@ def main():
     if not args.no_frame:
         frame = frame_bench(model, opt, args.workload, bg_p.detach(), dev, rank, world, args.frame_chunk)
 
+    # ---- the same step followed by the optimiser updates (secondary number; the headline metric is fwd+bwd as BASELINE.json
+    #      words it): the reference's two Adam optimisers (MLP lr, point tables + bg plr; mvs_points_volumetric_model.py:47-125)
+    #      as one multi-tensor launch each (pn_adam_step)
+    _phase("step + Adam")
+    with_adam = None
+    if not args.no_adam:
+        from pointnerf_b200.optim import Adam
+        nps_ = model.neural_points
+        opt_mlp = Adam(list(model.aggregator.parameters()), lr=5e-4, betas=(0.9, 0.999))
+        opt_pts = Adam([t for t in (nps_.points_embeding, nps_.points_conf, nps_.points_dir, nps_.points_color) if t is not None and t.requires_grad] + [bg_p],
+                       lr=2e-3, betas=(0.9, 0.999))
+
+        def step_adam(i):
+            step(i)
+            opt_mlp.step()
+            opt_pts.step()
+        for w in range(3):
+            step_adam(w)
+        sync_all()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for s in range(args.steps):
+            step_adam(3 + s)
+        a1.record()
+        sync_all()
+        t = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        n_el = sum(p.numel() for g_ in (opt_mlp.param_groups + opt_pts.param_groups) for p in g_["params"])
+        with_adam = {"ms_per_step": round(float(t.item()) / args.steps, 4), "rays_per_s": round(global_rays * args.steps / (float(t.item()) * 1e-3), 1),
+                     "adam_elements": int(n_el), "adam_bytes_per_step": int(n_el * 28),
+                     "note": "dense Adam over every point row and MLP weight each step (exact torch.optim.Adam semantics), 2 launches"}
+
     # ---- per-stage device time (events around each C-ABI call) and the roofline of the dominant stage
     _phase("stages / roofline / cpu baseline (rank 0 only, no collectives)")
     stages, roof, counts = None, None, None
@@ -672,7 +706,8 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
-                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, "frame_800x800": frame}
+                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, "frame_800x800": frame,
+                "train_step_with_adam": with_adam}
         _emit(line)
     if world > 1:
         dist.barrier()

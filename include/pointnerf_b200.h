@@ -359,6 +359,47 @@ int pn_points_compact(const int32_t* dst_index, int64_t n_points, int32_t F, con
                       const float* conf, const float* dir, const float* color, float* out_xyz, float* out_embedding,
                       float* out_conf, float* out_dir, float* out_color, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 6. Voxel down-sampling of a point cloud
+ *
+ * pn_voxel_downsample - models/mvs/mvs_utils.py:537-561 `construct_vox_points_closest` (called when points are
+ *   (re)voxelised: run/train_ft.py:141-146,693, train_waymo.py:531): voxel coordinate floor((p - space_min) / vox_size)
+ *   per point, the distinct voxels in lexicographic (x, y, z) order (= torch.unique(dim=0)), each voxel's centroid
+ *   (= torch_scatter.scatter_mean, summed in ascending point index) and the index of the point nearest to that centroid
+ *   (= scatter_min's argmin; the smallest index among ties).  One stable LSD radix sort of (voxel key, point index)
+ *   replaces unique + the two atomic scatters.
+ *     xyz [N,3] device; space_min, vox_size: HOST float[3]; coord_base: HOST int32[3], the smallest voxel coordinate per
+ *     axis (coordinates may be negative: the reference's box filter `prod(...) > 0` lets points through that are outside
+ *     on two axes); bits: key bits per axis (coordinate - coord_base must lie in [0, 2^bits); 3*bits <= 63) -
+ *     coordinates outside are clamped and counted in n_outside (device int32[1], may be NULL)
+ *     -> centroid [N,3], grid_idx int32[N,3], min_idx int64[N], inv_idx int32[N] (voxel of every point) - only the
+ *        first n_voxels[0] (device int32[1]) rows of the first three are written
+ * ---------------------------------------------------------------------------------------------- */
+int64_t pn_voxel_downsample_workspace_bytes(int64_t n_points);
+int pn_voxel_downsample(const float* xyz, int64_t n_points, const float* space_min, const float* vox_size,
+                        const int32_t* coord_base, int32_t bits, float* centroid, int32_t* grid_idx, int64_t* min_idx, int32_t* inv_idx, int32_t* n_voxels,
+                        int32_t* n_outside, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * 7. Optimiser step
+ *
+ * pn_adam_step - torch.optim.Adam(lr, betas=(0.9, 0.999), eps=1e-8; no weight decay, no amsgrad) as the reference sets
+ *   it up for the MLP (`optimizer`) and for the point tables + bg_color (`neural_point_optimizer`),
+ *   models/mvs_points_volumetric_model.py:47-100, stepped at :103-125.  ONE launch per 32 tensors; the arithmetic
+ *   follows torch's single-tensor Adam op by op in fp32 (lerp, mul+addcmul, sqrt/div/add, addcdiv).
+ *   segs: HOST array; every tensor is a contiguous fp32 device buffer of n elements; step = 1 for the first update.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pn_adam_segment {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t n;
+} pn_adam_segment;
+
+int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, float lr, float beta1, float beta2, float eps, int64_t step,
+                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,3 +62,34 @@ def grow_points(tables, add_xyz, add_embedding, add_color, add_dir, add_conf):
     for k, a in (("points_embeding", add_embedding), ("points_conf", add_conf), ("points_dir", add_dir), ("points_color", add_color)):
         out[k] = torch.cat([tables[k], a[None, ...]], dim=1)
     return out
+
+
+def construct_vox_points_closest(xyz_val, vox_res, space_min=None, space_max=None):
+    """models/mvs/mvs_utils.py:537-561 with torch_scatter's two calls restated: ``scatter_mean`` = serial index_add_ in
+    ascending point index / count, ``scatter_min`` (arg) = first index of the smallest residual per voxel.  With a box the
+    filter applies to the coordinates too (the reference only works when nothing is filtered).
+    Returns (xyz_centroid [U,3], sparse_grid_idx int32 [U,3], min_idx int64 [U], inv_idx int64 [N], residual [N])."""
+    import numpy as np
+    if space_min is None:
+        xyz_min, xyz_max = torch.min(xyz_val, dim=-2)[0], torch.max(xyz_val, dim=-2)[0]
+        space_edge = torch.max(xyz_max - xyz_min) * 1.05
+        xyz_mid = (xyz_max + xyz_min) / 2
+        space_min = xyz_mid - space_edge / 2
+    else:
+        space_edge = space_max - space_min
+        mask = torch.prod((xyz_val - space_min[None, ...]) * (space_max[None, ...] - xyz_val), dim=-1) > 0
+        xyz_val = xyz_val[mask, :]
+    construct_vox_sz = space_edge / vox_res
+    xyz_shift = xyz_val - space_min[None, ...]
+    coords = torch.floor(xyz_shift / construct_vox_sz[None, ...]).to(torch.int32)
+    sparse_grid_idx, inv_idx = torch.unique(coords, dim=0, return_inverse=True)
+    U = sparse_grid_idx.shape[0]
+    acc = np.zeros((U, 3), np.float32)
+    np.add.at(acc, inv_idx.numpy(), xyz_val.numpy())          # unbuffered: a serial accumulation in ascending point index
+    count = torch.from_numpy(np.bincount(inv_idx.numpy(), minlength=U).astype(np.float32))
+    xyz_centroid = torch.from_numpy(acc) / count[:, None]
+    xyz_residual = torch.norm(xyz_val - xyz_centroid[inv_idx, :], dim=-1)
+    order = np.lexsort((np.arange(len(xyz_val)), xyz_residual.numpy(), inv_idx.numpy()))
+    first = np.r_[True, inv_idx.numpy()[order][1:] != inv_idx.numpy()[order][:-1]]
+    min_idx = torch.from_numpy(order[first].astype(np.int64))
+    return xyz_centroid, sparse_grid_idx, min_idx, inv_idx, xyz_residual

@@ -51,6 +51,10 @@ class AggInputs(Structure):
                [(n, c_int64) for n in ("n_slots", "S", "M", "T")]
 
 
+class AdamSegment(Structure):
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p), ("n", c_int64)]
+
+
 class LibraryError(RuntimeError):
     pass
 
@@ -111,6 +115,9 @@ def _declare(lib):
         "pn_probe_rays": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float, c_float,
                                   P, P, P, P, P, P, P, P, P]),
         "pn_prune_workspace_bytes": (c_int64, [c_int64]),
+        "pn_adam_step": (c_int, [POINTER(AdamSegment), c_int32, c_float, c_float, c_float, c_float, c_int64, P]),
+        "pn_voxel_downsample_workspace_bytes": (c_int64, [c_int64]),
+        "pn_voxel_downsample": (c_int, [P, c_int64, POINTER(c_float), POINTER(c_float), POINTER(c_int32), c_int32, P, P, P, P, P, P, P, c_int64, P]),
         "pn_prune_mark": (c_int, [P, c_int64, c_float, P, P, c_int64, P]),
         "pn_points_compact": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, P, P, P, P, P]),
     }

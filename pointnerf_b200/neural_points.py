@@ -102,14 +102,14 @@ class NeuralPoints(nn.Module):
         old = {n: getattr(self, n) for n in self._TABLES}
         new_xyz = torch.empty((total, 3), dtype=torch.float32, device=dev)
         new = {n: (None if t is None else torch.empty((1, total, t.shape[-1]), dtype=torch.float32, device=dev)) for n, t in old.items()}
-        if dst is not None:
+        if dst is not None and kept > 0:
             _lib.check(lib.pn_points_compact(
                 _lib.ptr(dst), N, F_, _lib.ptr(self.xyz.detach()), _lib.ptr(old["points_embeding"].detach()),
                 _lib.ptr(old["points_conf"].detach()), _lib.ptr(None if old["points_dir"] is None else old["points_dir"].detach()),
                 _lib.ptr(None if old["points_color"] is None else old["points_color"].detach()),
                 _lib.ptr(new_xyz), _lib.ptr(new["points_embeding"]), _lib.ptr(new["points_conf"]), _lib.ptr(new["points_dir"]),
                 _lib.ptr(new["points_color"]), _lib.stream()), "pn_points_compact")
-        else:
+        elif dst is None:
             new_xyz[:N].copy_(self.xyz.detach())
             for n, t in old.items():
                 if t is not None:
