@@ -347,6 +347,58 @@ def frame_bench(model, opt, name, bg_dev, dev, rank, world, chunk, frames=3):
             "note": "forward only, grid cached, %d GPU(s) by row blocks" % world}
 
 
+def frame_sweep(model, opt, name, bg_dev, dev, chunk):
+    """BASELINE.json configs[4]: full-frame inference over K = 8/16 and 40/80/160 samples per ray, with a prune (conf below
+    a threshold that removes ~1 % of the points) + grow (1 % new points) between passes.  The maintenance step and the grid
+    rebuild it forces are timed separately (wall clock around a device sync: both contain a host read-back)."""
+    import warnings
+    from pointnerf_b200 import synthetic as syn
+    cam = syn.make_camera(name, view=1)
+    raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
+    ray_dev = raydir.to(dev)
+    campos, rot = cam["campos"].to(dev), cam["camrotc2w"].to(dev)
+    nps = model.neural_points
+    keep = (opt.is_train, opt.K, opt.SR)
+    gen = torch.Generator(device=dev).manual_seed(17)
+    out = []
+    try:
+        opt.is_train = 0
+        for K in (8, 16):
+            for SR in (40, 80, 160):
+                opt.K, opt.SR = K, SR
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")          # grown points may overfill a voxel beyond P (first P kept)
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    nps.querier.grid_for(nps.xyz.detach())   # rebuild after the previous pass's prune/grow
+                    torch.cuda.synchronize()
+                    grid_ms = (time.perf_counter() - t0) * 1e3
+                model.render_frame(campos, ray_dev, bg_dev, rot, cam["near"], cam["far"], chunk=chunk)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(2):
+                    model.render_frame(campos, ray_dev, bg_dev, rot, cam["near"], cam["far"], chunk=chunk)
+                e1.record()
+                torch.cuda.synchronize()
+                N = int(nps.xyz.shape[0])
+                n_add = N // 100
+                pick = torch.randint(0, N, (n_add,), device=dev, generator=gen)
+                add = dict(add_xyz=nps.xyz.detach()[pick] + 0.002 * torch.randn(n_add, 3, device=dev, generator=gen),
+                           add_embedding=nps.points_embeding.detach()[0, pick], add_color=nps.points_color.detach()[0, pick],
+                           add_dir=nps.points_dir.detach()[0, pick], add_conf=nps.points_conf.detach()[0, pick])
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                kept = nps.prune_and_grow(0.109, **add)
+                torch.cuda.synchronize()
+                maint_ms = (time.perf_counter() - t0) * 1e3
+                out.append({"K": K, "SR": SR, "frame_ms": round(e0.elapsed_time(e1) / 2, 3), "points": N, "grid_build_ms": round(grid_ms, 3),
+                            "prune_grow_ms": round(maint_ms, 3), "pruned": N - kept, "grown": n_add})
+    finally:
+        opt.is_train, opt.K, opt.SR = keep
+    return out
+
+
 def psnr_vs_oracle(dev):
     """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
     oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
@@ -435,6 +487,7 @@ def main():
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-frame", action="store_true", help="skip the full-frame inference timing (ms per 800x800 frame)")
     ap.add_argument("--frame-chunk", type=int, default=65536, help="rays per render_frame chunk")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the cfg5 inference sweep (K x SR, prune/grow between passes)")
     ap.add_argument("--no-adam", action="store_true", help="skip the secondary timing of the step WITH the Adam updates")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
     args = ap.parse_args()
@@ -462,8 +515,8 @@ def main():
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "%s: 1M-point neural cloud, %d rays/batch, SR=%d, K=%d, D=%d, fwd+bwd" %
-                           (args.workload, args.rays, opt.SR, opt.K, opt.z_depth_dim)},
+                "config": {"workload": "%s: %d-point neural cloud, %d rays/batch, SR=%d, K=%d, D=%d, fwd+bwd" %
+                           (args.workload, tables["xyz"].shape[0], args.rays, opt.SR, opt.K, opt.z_depth_dim)},
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
                                  "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -687,6 +740,12 @@ def main():
                             "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port")}
         cpu["psnr"] = psnr_vs_oracle(dev)
 
+    # ---- cfg5 sweep (N = 1, after everything else: it prunes / grows the point cloud)
+    sweep = None
+    if rank == 0 and world == 1 and not args.no_sweep and not args.no_frame:
+        _phase("cfg5 inference sweep")
+        sweep = frame_sweep(model, opt, args.workload, bg_p.detach(), dev, args.frame_chunk)
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -699,15 +758,16 @@ def main():
                                                  "all-gather of the touched point-table gradient rows (ids + 39 floats, rank-ordered sum) + all-reduce of the 1.4 MB MLP gradients"))
                                       if world > 1 else ""),
                            "parallelism": "ray-sharded x%d, points+MLP replicated" % world,
-                           "l2": "working set (point tables 168 MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled" % n_pool,
+                           "l2": "working set (point tables %.0f MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled"
+                                 % (tables["xyz"].shape[0] * 42 * 4 / 1e6, n_pool),
                            "mean_valid_samples_per_batch": counts["S"] if counts else None,
                            "mean_valid_pairs_per_batch": counts["M"] if counts else None},
                 "clocks": clocks, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
-                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, "frame_800x800": frame,
-                "train_step_with_adam": with_adam}
+                "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, ("frame_%dx%d" % (frame["w"], frame["h"]) if frame else "frame_800x800"): frame,
+                "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep}
         _emit(line)
     if world > 1:
         dist.barrier()

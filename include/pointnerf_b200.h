@@ -397,7 +397,7 @@ typedef struct pn_adam_segment {
     int64_t n;
 } pn_adam_segment;
 
-int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, float lr, float beta1, float beta2, float eps, int64_t step,
+int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, double lr, double beta1, double beta2, double eps, int64_t step,
                  void* stream);
 
 #ifdef __cplusplus

@@ -7,7 +7,7 @@ enqueued on torch's current CUDA stream.
 import ctypes
 import os
 import subprocess
-from ctypes import POINTER, Structure, c_float, c_int, c_int32, c_int64, c_void_p, c_char_p
+from ctypes import POINTER, Structure, c_double, c_float, c_int, c_int32, c_int64, c_void_p, c_char_p
 
 import torch
 
@@ -115,7 +115,7 @@ def _declare(lib):
         "pn_probe_rays": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float, c_float,
                                   P, P, P, P, P, P, P, P, P]),
         "pn_prune_workspace_bytes": (c_int64, [c_int64]),
-        "pn_adam_step": (c_int, [POINTER(AdamSegment), c_int32, c_float, c_float, c_float, c_float, c_int64, P]),
+        "pn_adam_step": (c_int, [POINTER(AdamSegment), c_int32, c_double, c_double, c_double, c_double, c_int64, P]),
         "pn_voxel_downsample_workspace_bytes": (c_int64, [c_int64]),
         "pn_voxel_downsample": (c_int, [P, c_int64, POINTER(c_float), POINTER(c_float), POINTER(c_int32), c_int32, P, P, P, P, P, P, P, c_int64, P]),
         "pn_prune_mark": (c_int, [P, c_int64, c_float, P, P, c_int64, P]),

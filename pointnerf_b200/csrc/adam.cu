@@ -71,14 +71,15 @@ __global__ void __launch_bounds__(kAdamThreads) adam_kernel(AdamBatch b, float w
 
 using namespace pn;
 
-extern "C" int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, float lr, float beta1, float beta2, float eps, int64_t step,
-                            void* stream) {
+extern "C" int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, double lr, double beta1, double beta2, double eps,
+                            int64_t step, void* stream) {
     PN_CHECK_ARG(n_segs >= 0 && (segs || n_segs == 0), "pn_adam_step: null segment list");
     PN_CHECK_ARG(step >= 1, "pn_adam_step: step counts from 1");
     // scalars exactly as torch's python side computes them (double), rounded to fp32 where the kernels take them
-    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-    const float w1 = (float)(1.0 - (double)beta1), w2 = (float)(1.0 - (double)beta2);
-    const float bc2_sqrt = (float)sqrt(bc2), neg_step = (float)(-((double)lr / bc1));
+    // (the hyper-parameters arrive as doubles: 1 - (double)0.999f is off by 1.3e-5 relative)
+    const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+    const float w1 = (float)(1.0 - beta1), w2 = (float)(1.0 - beta2);
+    const float bc2_sqrt = (float)sqrt(bc2), neg_step = (float)(-(lr / bc1));
     for (int s0 = 0; s0 < n_segs; s0 += kAdamMaxSegs) {
         AdamBatch b;
         b.n_segs = 0;
@@ -93,7 +94,7 @@ extern "C" int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, float l
         }
         if (b.n_segs == 0) continue;
         b.first_block[b.n_segs] = blocks;
-        adam_kernel<<<blocks, kAdamThreads, 0, (cudaStream_t)stream>>>(b, w1, beta2, w2, bc2_sqrt, eps, neg_step);
+        adam_kernel<<<blocks, kAdamThreads, 0, (cudaStream_t)stream>>>(b, w1, (float)beta2, w2, bc2_sqrt, (float)eps, neg_step);
         PN_LAUNCH_CHECK("adam");
     }
     return PN_OK;

@@ -1,4 +1,5 @@
-"""BASELINE config 2 at FULL size (1 M points, 4096 rays, SR = 80, K = 8, fwd + bwd) on the GPU.  The CPU oracle needs
+"""BASELINE config 2 at FULL size (1 M points, 4096 rays, SR = 80, K = 8, fwd + bwd) on the GPU; the query and compositing
+properties also on config 3 (3 M points, P = 30, SR = 24).  The CPU oracle needs
 minutes for this size, so the checks are size-independent properties of the path: neighbour lists are valid / unique /
 inside the radius and reproduce bit for bit, the tensor-core MLP agrees with the exact-fp32 SIMT MLP, compositing obeys
 its telescoping identity and is linear in the background colour, gradients are linear over rays (what ray sharding
@@ -24,13 +25,26 @@ def cfg2(cuda_dev):
     return opt, tables, [bench.to_dev(b, cuda_dev) for b in batches], bg.to(cuda_dev), model
 
 
+@pytest.fixture(scope="module")
+def cfg3(cuda_dev):
+    """BASELINE config 3 (ScanNet-shaped: 3 M points, 16 mm voxels with P = 30, SR = 24, camera inside the room)."""
+    opt, tables, batches, bg = bench.build_workload("cfg3", 4096, 1, seed_base=654)
+    model = bench.make_model(opt, tables, cuda_dev)
+    return opt, tables, [bench.to_dev(b, cuda_dev) for b in batches], bg.to(cuda_dev), model
+
+
+@pytest.fixture(params=["cfg2", "cfg3"])
+def cfg(request):
+    return request.getfixturevalue(request.param)
+
+
 def _forward(model, b, bg):
     return model(b["cam"]["campos"], b["raydir"], bg_color=bg, camrotc2w=b["cam"]["camrotc2w"], near=b["cam"]["near"],
                  far=b["cam"]["far"], uniform=b["uniform"])
 
 
-def test_neighbour_lists_valid_unique_in_radius_and_reproducible(cfg2):
-    opt, tables, batches, bg, model = cfg2
+def test_neighbour_lists_valid_unique_in_radius_and_reproducible(cfg):
+    opt, tables, batches, bg, model = cfg
     b = batches[0]
     plan = model.sample(b["cam"]["campos"], b["raydir"], b["cam"]["camrotc2w"], b["cam"]["near"], b["cam"]["far"], uniform=b["uniform"])
     pidx, loc = plan.pidx, plan.loc_w                      # [R,SR,K], [R,SR,3]
@@ -40,7 +54,7 @@ def test_neighbour_lists_valid_unique_in_radius_and_reproducible(cfg2):
     assert int(pidx.max()) < N and int(pidx.min()) >= -1
     valid = pidx >= 0
     S, M = plan.work_lists.counts()
-    assert M == int(valid.sum()) and S == int(valid.any(-1).sum()) and M > 50000
+    assert M == int(valid.sum()) and S == int(valid.any(-1).sum()) and M > (50000 if opt.SR == 80 else 500)
     # inside the radius of radius_limit_scale * vsize, measured from the sample
     xyz = model.neural_points.xyz
     d2 = ((xyz[pidx.clamp(min=0).long()] - loc[:, :, None, :]) ** 2).sum(-1)
@@ -58,8 +72,8 @@ def test_neighbour_lists_valid_unique_in_radius_and_reproducible(cfg2):
     assert torch.equal(plan2.pidx, pidx) and torch.equal(plan2.loc_w, loc)
 
 
-def test_compositing_identities(cfg2):
-    opt, tables, batches, bg, model = cfg2
+def test_compositing_identities(cfg):
+    opt, tables, batches, bg, model = cfg
     b = batches[0]
     with torch.no_grad():
         out1 = _forward(model, b, bg)
@@ -72,7 +86,7 @@ def test_compositing_identities(cfg2):
     assert float((lin - T_bg * bg.view(1, 1, -1)).abs().max()) < 2e-6
     # rays that hit nothing show the background, untouched
     miss = out1["ray_mask"][0] == 0
-    assert bool(miss.any())
+    assert bool(miss.any()) or opt.SR != 80          # (inside cfg3's room nearly every ray meets a wall)
     assert torch.equal(out1["coarse_raycolor"][0][miss], bg.view(1, -1).expand(int(miss.sum()), -1))
     assert bool((T_bg[0][miss] == 1).all())
 
