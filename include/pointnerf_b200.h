@@ -197,6 +197,9 @@ typedef struct pn_agg_params {
     int32_t compact_out; /* 0: decoded_features / grad_decoded are [n_slots, C+1] (reference layout, zero rows for
                             invalid samples); 1: [S, C+1], row i = sample sample_list[i] (fused path, see
                             pn_composite_forward slot_row) */
+    int32_t intrp_order; /* agg_intrp_order: 2 (or 0) = one density per neighbour, interpolated over K (:603-646, every shipped
+                            per-scene script); 1 = features interpolated over K, then one density per sample and
+                            raw2out_color (sigmoid, act_super scaling) on the colour (:573-599, the DTU feed-forward configs) */
 } pn_agg_params;
 
 /* nn.Linear parameters, weight [out,in] row-major fp32 (state_dict names of the reference) */

@@ -2,6 +2,7 @@
 
 TEST INFRASTRUCTURE (see oracle/__init__.py).  ``python -m oracle.make_golden`` from the repository root.
   aggregator_ref.npz  PointAggregator (models/aggregators/point_aggregators.py) outputs + autograd gradients
+  aggregator_order1_ref.npz  the same with agg_intrp_order=1, point_features_dim=63
   ray_march_ref.npz   ray_march (models/rendering/diff_ray_marching.py:509-555) outputs + gradients
   querier_ref.npz     lighting_fast_querier kernels (the reference's CUDA string host-compiled by oracle/build_ref.py,
                       canonical ascending-thread schedule) on the seeded ``tiny`` scene
@@ -23,11 +24,11 @@ from pointnerf_b200.options import make_opt  # noqa: E402
 OUT = os.path.join(ROOT, "tests", "golden")
 
 
-def aggregator():
+def aggregator(name="aggregator_ref.npz", F=32, **opt_kw):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from test_oracle import _agg_inputs
     ns = ref_import.load()
-    opt = make_opt()
+    opt = make_opt(point_features_dim=F, **opt_kw)
     opt.agg_axis_weight = None
     torch.manual_seed(0)
     ref = ns.PointAggregator(opt)
@@ -35,7 +36,7 @@ def aggregator():
         for p in ref.parameters():
             if p.dim() == 1:
                 p.normal_(0, 0.1)
-    ins = _agg_inputs(seed=11, R=6, SR=4, K=8)
+    ins = _agg_inputs(seed=11, R=6, SR=4, K=8, F=F)
     gk = ["sampled_color", "sampled_dir", "sampled_conf", "sampled_embedding"]
     for k in gk:
         ins[k].requires_grad_(True)
@@ -49,7 +50,7 @@ def aggregator():
               "out/conf_coefficient": o[3].detach().numpy(), "loss_weight": wt.numpy()})
     for n, g in zip(gk + [n for n, _ in ref.named_parameters()], grads):
         d["grad/" + n] = g.numpy()
-    np.savez_compressed(os.path.join(OUT, "aggregator_ref.npz"), **d)
+    np.savez_compressed(os.path.join(OUT, name), **d)
 
 
 def ray_march():
@@ -90,6 +91,7 @@ def querier():
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     aggregator()
+    aggregator("aggregator_order1_ref.npz", F=63, agg_intrp_order=1)      # the DTU feed-forward configuration (63-d features)
     ray_march()
     querier()
     for f in sorted(os.listdir(OUT)):

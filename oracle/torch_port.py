@@ -176,14 +176,19 @@ class AggregatorPort(nn.Module):
         x = torch.cat([x, col, pd - ov, torch.sum(pd * ov, dim=-1, keepdim=True)], dim=-1)  # :570
         x = self.block3(x)                                                             # :571
 
-        a = F.softplus(self.alpha_branch(x) - 1)                                       # :262-265, 605
-        a_full = torch.zeros([B * R * SR * K, 1], dtype=a.dtype)
-        a_full[pmask, :] = a                                                           # :608-610
-        alpha = torch.sum(a_full.view(B * R * SR, K, 1) * wc, dim=-2)[sample_valid, :]  # :613-614
         f_full = torch.zeros([B * R * SR * K, x.shape[-1]], dtype=x.dtype)
-        f_full[pmask, :] = x                                                           # :622-624
-        feat = torch.sum(f_full.view(B * R * SR, K, -1) * wc, dim=-2)[sample_valid, :]  # :627-628
-        colour = self.color_branch(torch.cat([feat, view_pe], dim=-1))                 # :635-636 (no sigmoid)
+        f_full[pmask, :] = x                                                           # :622-624 (order 1: :575-579)
+        feat = torch.sum(f_full.view(B * R * SR, K, -1) * wc, dim=-2)[sample_valid, :]  # :627-628 (order 1: :580)
+        if opt.agg_intrp_order == 1:          # interpolate the features, then ONE density per sample (:573-588)
+            alpha = F.softplus(self.alpha_branch(feat) - 1)
+        else:                                 # order 2: a density per neighbour, interpolated (:603-614)
+            a = F.softplus(self.alpha_branch(x) - 1)                                   # :262-265, 605
+            a_full = torch.zeros([B * R * SR * K, 1], dtype=a.dtype)
+            a_full[pmask, :] = a                                                       # :608-610
+            alpha = torch.sum(a_full.view(B * R * SR, K, 1) * wc, dim=-2)[sample_valid, :]  # :613-614
+        colour = self.color_branch(torch.cat([feat, view_pe], dim=-1))                 # :635-636 (order 2 in this fork: no sigmoid)
+        if opt.agg_intrp_order == 1:
+            colour = torch.sigmoid(colour) * (1 + 2 * 0.001) - 0.001                   # :596 raw2out_color (:269-273, act_super)
         out = torch.zeros([B * R * SR, C1], dtype=x.dtype)
         out[sample_valid] = torch.cat([alpha, colour], dim=-1)                         # :644-646
         ret_w = (opt.sparse_loss_weight > 0) or ("conf_coefficient" in opt.zero_one_loss_items) or opt.prob != 0

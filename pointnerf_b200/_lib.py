@@ -28,7 +28,7 @@ class GridParams(Structure):
 class AggParams(Structure):
     _fields_ = [("F", c_int32), ("feat_freqs", c_int32), ("dist_freqs", c_int32), ("view_freqs", c_int32),
                 ("W", c_int32), ("C", c_int32), ("K", c_int32), ("dirs_per_ray", c_int32), ("SR", c_int32),
-                ("leaky_slope", c_float), ("dist_scale", c_float), ("compact_out", c_int32)]
+                ("leaky_slope", c_float), ("dist_scale", c_float), ("compact_out", c_int32), ("intrp_order", c_int32)]
 
 
 WEIGHT_FIELDS = ("block1_0_w", "block1_0_b", "block1_2_w", "block1_2_b", "block3_0_w", "block3_0_b",

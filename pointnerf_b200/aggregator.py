@@ -6,7 +6,7 @@ Mirrors models/aggregators/point_aggregators.py of the reference: ``PointAggrega
 models/helpers/networks.py:163-172) and the same ``forward`` signature and return structure (:729-816),
 so reference checkpoints load unchanged and ``NeuralPointsRayMarching.forward`` can call it as is.
 
-Only the configuration every shipped script uses is implemented (viewmlp, agg_intrp_order=2, linear
+Only the configurations the shipped scripts use are implemented (viewmlp, agg_intrp_order=2 or 1, linear
 distance kernel, agg_dist_pers=20, apply_pnt_mask=1, LeakyReLU, act_super=1); anything else raises.
 
 Two entry points share one autograd function:
@@ -36,7 +36,7 @@ def _check_opt(opt):
             raise NotImplementedError("pointnerf_b200.PointAggregator: %s=%r is outside the hot path (SURVEY.md 2 #4)" % (name, v))
 
     need("which_agg_model", lambda v: v == "viewmlp")
-    need("agg_intrp_order", lambda v: v == 2)
+    need("agg_intrp_order", lambda v: v in (1, 2))
     need("agg_distance_kernel", lambda v: v == "linear")
     need("agg_dist_pers", lambda v: v == 20)
     need("apply_pnt_mask", lambda v: v > 0)
@@ -343,6 +343,7 @@ class PointAggregator(nn.Module):
         o = self.opt
         p = AggParams()
         p.compact_out = int(compact_out)
+        p.intrp_order = int(o.agg_intrp_order)
         p.F, p.feat_freqs, p.dist_freqs, p.view_freqs = int(o.point_features_dim), int(o.num_feat_freqs), int(o.dist_xyz_freq), int(o.num_viewdir_freqs)
         p.W, p.C, p.K, p.SR = int(o.shading_feature_num), int(o.shading_color_channel_num), int(K), int(SR)
         p.dirs_per_ray = int(dirs_per_ray)

@@ -12,6 +12,7 @@ namespace pn {
 
 struct AggDims {
     int F, ff, df, vf, W, C, K, SR, dirs_per_ray, compact_out;
+    int order;  // agg_intrp_order: 2 = a density per neighbour, interpolated; 1 = interpolate features, one density per sample, sigmoid colour
     int in1, in1p, in3, in3p, inc, incp;  // logical / padded (to 16) input widths of block1.0, block3.0, color.0
     float slope, dist_scale;
 };
@@ -24,6 +25,7 @@ __device__ __forceinline__ void rot3(const float* __restrict__ R, float x, float
 }
 __device__ __forceinline__ float softplus1(float x) { return x > 20.f ? x : log1pf(expf(x)); }  // torch Softplus(beta=1, threshold=20)
 __device__ __forceinline__ float sigmoid1(float x) { return x > 20.f ? 1.f : 1.f / (1.f + expf(-x)); }
+__device__ __forceinline__ float sigmoid_exact(float x) { return 1.f / (1.f + expf(-x)); }   // torch.sigmoid
 
 __device__ __forceinline__ void load_view(const pn_agg_inputs& in, const AggDims& d, int slot, float& vx, float& vy, float& vz) {
     int64_t row = d.dirs_per_ray ? (slot / d.SR) : slot;
@@ -168,11 +170,24 @@ __global__ void __launch_bounds__(256) agg_reduce_kernel(pn_agg_inputs in, AggDi
         float h[NW], dot = 0.f;
 #pragma unroll
         for (int i = 0; i < NW; ++i) { h[i] = H4[m * d.W + lane + 32 * i]; dot = fmaf(h[i], wa[i], dot); }
-        float araw = warp_sum(dot) + b;
-        if (lane == 0) pairv[m] = make_float4(pv.x, pv.y, araw, 0.f);
-        a_s = fmaf(softplus1(araw - 1.f), pv.x, a_s);
+        if (d.order != 1) {
+            float araw = warp_sum(dot) + b;
+            if (lane == 0) pairv[m] = make_float4(pv.x, pv.y, araw, 0.f);
+            a_s = fmaf(softplus1(araw - 1.f), pv.x, a_s);
+        }
 #pragma unroll
         for (int i = 0; i < NW; ++i) acc[i] = fmaf(h[i], pv.x, acc[i]);
+    }
+    if (d.order == 1) {   // point_aggregators.py:573-588: the density head reads the INTERPOLATED feature
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) dot = fmaf(acc[i], wa[i], dot);
+        float araw = warp_sum(dot) + b;
+        a_s = softplus1(araw - 1.f);
+        if (lane == 0) {      // kept for the backward in the unused 4th lane of the sample's first pair
+            float4 pv = pairv[p0];
+            pairv[p0] = make_float4(pv.x, pv.y, pv.z, araw);
+        }
     }
     float* row = FS + si * d.incp;
 #pragma unroll
@@ -201,7 +216,9 @@ __global__ void __launch_bounds__(256) agg_finish_kernel(pn_agg_inputs in, AggDi
     int64_t si = idx / C1;
     int c = (int)(idx - si * C1);
     int64_t orow = d.compact_out ? si : (int64_t)in.sample_list[si];
-    decoded[orow * C1 + c] = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
+    float v = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
+    if (c > 0 && d.order == 1) v = sigmoid_exact(v) * 1.002f - 0.001f;   // raw2out_color (:268-273), order 1 only in this fork
+    decoded[orow * C1 + c] = v;
 }
 
 // ------------------------------------ backward ------------------------------------------------
@@ -217,7 +234,14 @@ __global__ void __launch_bounds__(256) agg_gout_kernel(pn_agg_inputs in, AggDims
     int64_t irow = d.compact_out ? si : (int64_t)in.sample_list[si];
     float gv = g_decoded[irow * C1 + c];
     if (c == 0) galpha[si] = gv;
-    else GC3[si * d.C + c - 1] = gv * (C3[si * d.C + c - 1] > 0.f ? 1.f : d.slope);
+    else {
+        float c3 = C3[si * d.C + c - 1];
+        if (d.order == 1) {
+            float o = sigmoid_exact(c3);
+            gv *= 1.002f * o * (1.f - o);
+        }
+        GC3[si * d.C + c - 1] = gv * (c3 > 0.f ? 1.f : d.slope);
+    }
 }
 
 // reduce backward: CTA b owns the contiguous sample range [b*chunk, (b+1)*chunk); its warps stride over
@@ -241,6 +265,32 @@ __global__ void __launch_bounds__(256) agg_reduce_bwd_kernel(pn_agg_inputs in, A
         float ga = galpha[si], gf[NW];
 #pragma unroll
         for (int i = 0; i < NW; ++i) gf[i] = GFS[si * d.incp + lane + 32 * i];
+        if (d.order == 1) {
+            // one density per sample from the interpolated feature FS = sum_k wc_k H4_k: d/dFS gains g_araw * w_alpha,
+            // the head's parameter gradients read FS (recomputed here), and the per-pair work is the plain weighted split
+            float garaw = np > 0 ? ga * sigmoid1(pairv[p0].w - 1.f) : 0.f;
+            float fs[NW];
+#pragma unroll
+            for (int i = 0; i < NW; ++i) { gf[i] = fmaf(garaw, wa[i], gf[i]); fs[i] = 0.f; }
+            for (int j = 0; j < np; ++j) {
+                int64_t m = p0 + j;
+                float4 pv = pairv[m];
+                float h[NW], dot = 0.f;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) { h[i] = H4[m * d.W + lane + 32 * i]; dot = fmaf(gf[i], h[i], dot); }
+                dot = warp_sum(dot);
+                if (lane == 0) PG[m * pgw + d.F + 6] = dot * pv.y;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    dPre4[m * ld4 + lane + 32 * i] = pv.x * gf[i] * (h[i] > 0.f ? 1.f : d.slope);
+                    fs[i] = fmaf(h[i], pv.x, fs[i]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < NW; ++i) gw[i] = fmaf(garaw, fs[i], gw[i]);
+            gb += garaw;
+            continue;
+        }
         for (int j = 0; j < np; ++j) {
             int64_t m = p0 + j;
             float4 pv = pairv[m];  // (wc, wn, araw)

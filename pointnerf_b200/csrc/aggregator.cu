@@ -19,6 +19,8 @@ static int make_dims(const pn_agg_params* p, AggDims& d) {
     d.F = p->F; d.ff = p->feat_freqs; d.df = p->dist_freqs; d.vf = p->view_freqs;
     d.W = p->W; d.C = p->C; d.K = p->K; d.SR = p->SR; d.dirs_per_ray = p->dirs_per_ray;
     d.slope = p->leaky_slope; d.dist_scale = p->dist_scale; d.compact_out = p->compact_out;
+    d.order = p->intrp_order == 0 ? 2 : p->intrp_order;
+    PN_CHECK_ARG(d.order == 1 || d.order == 2, "aggregator: agg_intrp_order %d unsupported (1 or 2)", d.order);
     PN_CHECK_ARG(d.F >= 1 && d.F <= 1024 && d.ff >= 0 && d.df >= 1 && d.df <= 16 && d.vf >= 1 && d.vf <= 16,
                  "aggregator: unsupported feature/frequency counts");
     PN_CHECK_ARG(d.W == 128 || d.W == 256, "aggregator: shading_feature_num %d unsupported (128 or 256)", d.W);

@@ -53,9 +53,12 @@ def run(mod, ins, dev, wt_dec, wt_conf, vsize=(0.004, 0.004, 0.004), dtype=torch
     return out, grads
 
 
-@pytest.mark.parametrize("R,SR,K,seed", [(7, 5, 8, 1), (33, 24, 8, 2), (3, 4, 1, 3), (5, 6, 16, 4)])
-def test_forward_backward_matches_oracle(cuda_dev, R, SR, K, seed):
-    opt = make_opt(K=K, SR=SR)
+@pytest.mark.parametrize("R,SR,K,seed,kw", [(7, 5, 8, 1, {}), (33, 24, 8, 2, {}), (3, 4, 1, 3, {}), (5, 6, 16, 4, {}),
+                                            (33, 24, 8, 5, dict(agg_intrp_order=1)),
+                                            (9, 7, 8, 6, dict(agg_intrp_order=1, point_features_dim=63)),     # DTU feed-forward configuration
+                                            (9, 7, 8, 7, dict(point_features_dim=63))])
+def test_forward_backward_matches_oracle(cuda_dev, R, SR, K, seed, kw):
+    opt = make_opt(K=K, SR=SR, **kw)
     torch.manual_seed(seed)
     port = tp.AggregatorPort(opt)
     with torch.no_grad():               # non-zero biases (xavier init zeroes them) and a live density head
@@ -179,6 +182,6 @@ def test_state_dict_keys_match_reference_names():
 
 def test_unsupported_configuration_raises():
     with pytest.raises(NotImplementedError):
-        PointAggregator(make_opt(agg_intrp_order=1))
+        PointAggregator(make_opt(agg_intrp_order=0))
     with pytest.raises(NotImplementedError):
         PointAggregator(make_opt(agg_distance_kernel="quadric"))

@@ -32,16 +32,17 @@ def _agg_inputs(seed=1, R=7, SR=5, K=8, F=32):
 
 
 @needs_ref
-def test_aggregator_port_equals_reference():
+@pytest.mark.parametrize("kw", [{}, dict(agg_intrp_order=1), dict(agg_intrp_order=1, point_features_dim=63)])
+def test_aggregator_port_equals_reference(kw):
     ns = ref_import.load()
-    opt = make_opt()
+    opt = make_opt(**kw)
     opt_ref = copy.copy(opt)
     opt_ref.agg_axis_weight = None          # the reference builds this tensor on "cuda" (:247); None takes the same branch
     torch.manual_seed(0)
     ref = ns.PointAggregator(opt_ref)
     port = tp.AggregatorPort(opt)
     port.load_state_dict(ref.state_dict())
-    ins = _agg_inputs()
+    ins = _agg_inputs(F=opt.point_features_dim)
     gk = ["sampled_color", "sampled_dir", "sampled_conf", "sampled_embedding"]
     for k in gk:
         ins[k].requires_grad_(True)
@@ -163,10 +164,11 @@ def _load(name):
     return np.load(path)
 
 
-def test_golden_aggregator():
+@pytest.mark.parametrize("name,kw", [("aggregator_ref.npz", {}), ("aggregator_order1_ref.npz", dict(agg_intrp_order=1, point_features_dim=63))])
+def test_golden_aggregator(name, kw):
     """AggregatorPort reproduces outputs + gradients recorded from the UNMODIFIED reference module."""
-    z = _load("aggregator_ref.npz")
-    opt = make_opt()
+    z = _load(name)
+    opt = make_opt(**kw)
     port = tp.AggregatorPort(opt)
     port.load_state_dict({k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("sd/")})
     ins = {k[3:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("in/")}
