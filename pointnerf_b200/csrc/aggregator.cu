@@ -74,7 +74,7 @@ namespace pn {
 struct FwdWs { float *W1a, *W3a, *Wc0; char *I1a, *I1b, *I3a, *I3b, *Ic0, *Ic2, *Ic4; };
 struct BwdWs {
     float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
-    float *GA, *GB, *GSa, *GSb, *galpha, *PG, *tn, *apart;
+    float *GA, *GB, *GA2, *GB2, *GSa, *GSb, *GSc, *GSd, *galpha, *PG, *tn, *apart;
     char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
     int *cnt, *rank, *tmp, *sorted, *skey, *scan, *hflag, *hscan;
     int nblk_reduce;
@@ -120,8 +120,14 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     int64_t wide = d.in1p > d.in3p ? d.in1p : d.in3p;
     t.GA = c.take<float>(m * wide);
     t.GB = c.take<float>(m * d.W);
+    // second pair of gradient buffers: every data gradient keeps its own buffer until the weight-gradient GEMM that reads
+    // it has run, so the weight gradients can trail the data-gradient chain on another stream (pn_agg_backward)
+    t.GA2 = c.take<float>(m * d.in3p);
+    t.GB2 = c.take<float>(m * d.W);
     t.GSa = c.take<float>(s * d.incp);
     t.GSb = c.take<float>(s * d.incp);
+    t.GSc = c.take<float>(s * d.incp);
+    t.GSd = c.take<float>(s * d.incp);
     t.galpha = c.take<float>(s);
     t.PG = c.take<float>(m * (d.F + 8));
     int64_t tn = max3(gemm_tn_scratch_floats(m, d.W, d.in1p), gemm_tn_scratch_floats(m, d.W, d.in3p),
@@ -214,6 +220,40 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     return PN_OK;
 }
 
+// ---- two-stream backward -------------------------------------------------------------------------------------------
+// The backward is a CHAIN of data-gradient kernels (each needs the previous one's output) plus seven weight-gradient
+// GEMMs that only read what the chain left behind.  Every GEMM is a persistent kernel on all SMs whose last wave leaves
+// most SMs idle (527 tiles on 74 CTA pairs: 9 pairs run an 8th tile) and whose prologue (barriers, TMEM, first loads) is
+// exposed.  The chain runs on a library-owned high-priority stream, the weight gradients on the caller's stream: CTAs of
+// whichever kernel is queued fill the SMs the other one's tail frees.  Events order the two (RAW per gradient buffer, one
+// WAR before the last chain GEMM reuses GA); the caller's stream joins the chain at the end, so for the caller the call is
+// still "enqueued on the given stream".
+namespace pn {
+struct BwdStreams {
+    cudaStream_t chain = nullptr;
+    cudaEvent_t ev[12] = {};
+    int device = -1;
+    bool ok = false;
+};
+static BwdStreams* bwd_streams() {
+    static BwdStreams per_dev[16];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+    BwdStreams& b = per_dev[dev];
+    if (!b.ok) {
+        int lo = 0, hi = 0;
+        if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) return nullptr;
+        if (cudaStreamCreateWithPriority(&b.chain, cudaStreamNonBlocking, hi) != cudaSuccess) return nullptr;
+        for (auto& e : b.ev)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        b.device = dev;
+        b.ok = true;
+    }
+    return &b;
+}
+static int g_bwd_two_streams = 1;
+}  // namespace pn
+
 static int zero_weight_grads(const AggDims& d, const pn_agg_weights* g, cudaStream_t st) {
     struct { float* p; int64_t n; } items[] = {
         {g->block1_0_w, (int64_t)d.W * d.in1}, {g->block1_0_b, d.W}, {g->block1_2_w, (int64_t)d.W * d.W}, {g->block1_2_b, d.W},
@@ -274,42 +314,58 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     auto IMG = [&](const char* img) { return tcp ? img : (const char*)nullptr; };
 
-    // ---- colour branch (S rows)
-    agg_gout_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
+    // ---- streams: hs = data-gradient chain, st = weight gradients (see BwdStreams); one stream when disabled / SIMT path
+    BwdStreams* bs = (g_bwd_two_streams && tcp) ? bwd_streams() : nullptr;
+    cudaStream_t hs = bs ? bs->chain : st;
+    int evi = 0;
+    auto order = [&](cudaStream_t from, cudaStream_t to) -> int {   // work queued on `to` from now on sees everything queued on `from` so far
+        if (!bs) return PN_OK;
+        cudaEvent_t e = bs->ev[evi++];
+        PN_CUDA(cudaEventRecord(e, from));
+        PN_CUDA(cudaStreamWaitEvent(to, e, 0));
+        return PN_OK;
+    };
+    PN_TRY(order(st, hs));                      // inputs, zero-fills and weight images are ready
+    // ---- colour branch (S rows): gradient buffers GSa -> GSb -> GSc -> GSd
+    agg_gout_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, hs>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
     PN_LAUNCH_CHECK("agg_gout");
+    PN_TRY(order(hs, st));
     {   // color.4
         GemmTN t{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C};
         PN_TRY(gemm_tn(t, ws.tn, st));
         GemmNT g = nt(ws.GSa, d.C, ws.Wc4T, d.C, ws.GSb, d.C, S, d.C, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc4);
         g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
-        PN_TRY(gemm_nt(g, st));
+        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(order(hs, st));
     }
     {   // color.2
         GemmTN t{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSa, d.C, S, d.C, d.C, nullptr, 0, d.slope);
+        GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSc, d.C, S, d.C, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc2);
         g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
-        PN_TRY(gemm_nt(g, st));
+        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(order(hs, st));
     }
     {   // color.0: d/dFS (only the first W columns are consumed)
-        GemmTN t{ws.GSa, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
+        GemmTN t{ws.GSc, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GSa, d.C, ws.Wc0T, d.C, ws.GSb, d.incp, S, d.incp, d.C, nullptr, 0, d.slope);
+        GemmNT g = nt(ws.GSc, d.C, ws.Wc0T, d.C, ws.GSd, d.incp, S, d.incp, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc0);
-        PN_TRY(gemm_nt(g, st));
+        PN_TRY(gemm_nt(g, hs));
     }
     // ---- K-reduction and density head
     if (d.W == 256)
-        agg_reduce_bwd_kernel<8><<<ws.nblk_reduce, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSb, ws.galpha, ws.chunk,
+        agg_reduce_bwd_kernel<8><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha, ws.chunk,
                                                                  ws.GA, d.W, ws.PG, pgw, ws.apart);
     else
-        agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSb, ws.galpha, ws.chunk,
+        agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha, ws.chunk,
                                                                  ws.GA, d.W, ws.PG, pgw, ws.apart);
     PN_LAUNCH_CHECK("agg_reduce_bwd");
-    agg_alpha_final_kernel<<<(unsigned)cdiv((int64_t)(d.W + 1) * 32, 256), 256, 0, st>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
+    agg_alpha_final_kernel<<<(unsigned)cdiv((int64_t)(d.W + 1) * 32, 256), 256, 0, hs>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
     PN_LAUNCH_CHECK("agg_alpha_final");
+    PN_TRY(order(hs, st));
     // ---- block3 (M rows).  GA = dPre4 [M,W]
     {   // block3.2
         GemmTN t{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W};
@@ -317,61 +373,71 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         GemmNT g = nt(ws.GA, d.W, ws.W3bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J3b);
         g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, st));  // GB = dPre3
+        PN_TRY(gemm_nt(g, hs));  // GB = dPre3
+        PN_TRY(order(hs, st));
     }
-    {   // block3.0: GA[M,in3p] = d/dX3, first W columns masked by lrelu'(H2) (H2 = X3[:, :W])
+    cudaEvent_t ga_free = nullptr;              // recorded on st once block3.2's weight gradient has read GA (dPre4)
+    {   // block3.0: GA2[M,in3p] = d/dX3, first W columns masked by lrelu'(H2) (H2 = X3[:, :W])
+        if (bs) {                               // st so far: ... TN(block3.2).  Mark the point where GA becomes reusable.
+            ga_free = bs->ev[evi++];
+            PN_CUDA(cudaEventRecord(ga_free, st));
+        }
         GemmTN t{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
+        GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA2, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J3a);
         g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, st));
+        PN_TRY(gemm_nt(g, hs));
     }
-    agg_extras_bwd_kernel<<<(unsigned)cdiv(M, 256), 256, 0, st>>>(*in, d, ws.GA, ws.PG, pgw);
+    agg_extras_bwd_kernel<<<(unsigned)cdiv(M, 256), 256, 0, hs>>>(*in, d, ws.GA2, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_extras_bwd");
-    // ---- block1.  GA[:, :W] = dPre2 (row stride in3p)
+    PN_TRY(order(hs, st));
+    // ---- block1.  GA2[:, :W] = dPre2 (row stride in3p)
     {   // block1.2
-        GemmTN t{ws.GA, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
+        GemmTN t{ws.GA2, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GA, d.in3p, ws.W1bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
+        GemmNT g = nt(ws.GA2, d.in3p, ws.W1bT, d.W, ws.GB2, d.W, M, d.W, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J1b);
         g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, st));  // GB = dPre1
+        PN_TRY(gemm_nt(g, hs));  // GB2 = dPre1
+        PN_TRY(order(hs, st));
     }
-    {   // block1.0: GA[M,in1p] = d/dX1
-        GemmTN t{ws.GB, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
+    {   // block1.0: GA[M,in1p] = d/dX1 (GA is free again once block3.2's weight gradient has read dPre4)
+        GemmTN t{ws.GB2, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
         PN_TRY(gemm_tn(t, ws.tn, st));
-        GemmNT g = nt(ws.GB, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
+        if (ga_free) PN_CUDA(cudaStreamWaitEvent(hs, ga_free, 0));
+        GemmNT g = nt(ws.GB2, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J1a);
-        PN_TRY(gemm_nt(g, st));
+        PN_TRY(gemm_nt(g, hs));
     }
-    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, sv.X1, ws.GA, ws.PG, pgw);
+    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, sv.X1, ws.GA, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_prep_bwd");
     // ---- per-row gradients out
     if (!scatter_rows) {
-        agg_scatter_dense_kernel<<<(unsigned)cdiv(M * (d.F + 7), 256), 256, 0, st>>>(*in, d, ws.PG, pgw, g_emb, g_color, g_dir, g_conf);
+        agg_scatter_dense_kernel<<<(unsigned)cdiv(M * (d.F + 7), 256), 256, 0, hs>>>(*in, d, ws.PG, pgw, g_emb, g_color, g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_scatter_dense");
     } else {
-        PN_CUDA(cudaMemsetAsync(ws.cnt, 0, (T + 1) * sizeof(int), st));
+        PN_CUDA(cudaMemsetAsync(ws.cnt, 0, (T + 1) * sizeof(int), hs));
         unsigned mb = (unsigned)cdiv(M, 256);
-        agg_key_count_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.rank);
+        agg_key_count_kernel<<<mb, 256, 0, hs>>>(*in, ws.cnt, ws.rank);
         PN_LAUNCH_CHECK("agg_key_count");
-        PN_TRY(scan_exclusive_i32(ws.cnt, ws.cnt, T, true, ws.scan, st));
-        agg_key_place_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.rank, ws.tmp);
+        PN_TRY(scan_exclusive_i32(ws.cnt, ws.cnt, T, true, ws.scan, hs));
+        agg_key_place_kernel<<<mb, 256, 0, hs>>>(*in, ws.cnt, ws.rank, ws.tmp);
         PN_LAUNCH_CHECK("agg_key_place");
-        agg_key_order_kernel<<<mb, 256, 0, st>>>(*in, ws.cnt, ws.tmp, ws.sorted, ws.skey);
+        agg_key_order_kernel<<<mb, 256, 0, hs>>>(*in, ws.cnt, ws.tmp, ws.sorted, ws.skey);
         PN_LAUNCH_CHECK("agg_key_order");
-        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, st>>>(*in, d, ws.skey, ws.sorted, ws.PG, pgw, g_emb, g_color,
+        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, ws.skey, ws.sorted, ws.PG, pgw, g_emb, g_color,
                                                                                g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_segment_reduce");
         if (touched_ids) {   // sorted unique list of the table rows that received gradient
-            agg_head_flag_kernel<<<mb, 256, 0, st>>>(M, ws.skey, ws.hflag);
+            agg_head_flag_kernel<<<mb, 256, 0, hs>>>(M, ws.skey, ws.hflag);
             PN_LAUNCH_CHECK("agg_head_flag");
-            PN_TRY(scan_exclusive_i32(ws.hflag, ws.hflag, M, true, ws.hscan, st));
-            agg_head_ids_kernel<<<mb, 256, 0, st>>>(M, ws.skey, ws.hflag, touched_ids, n_touched);
+            PN_TRY(scan_exclusive_i32(ws.hflag, ws.hflag, M, true, ws.hscan, hs));
+            agg_head_ids_kernel<<<mb, 256, 0, hs>>>(M, ws.skey, ws.hflag, touched_ids, n_touched);
             PN_LAUNCH_CHECK("agg_head_ids");
         }
     }
+    PN_TRY(order(hs, st));                      // the caller's stream joins the chain
     return PN_OK;
 }
 
@@ -382,7 +448,10 @@ extern "C" int pn_set_mlp_path(int path) {
     return PN_OK;
 }
 extern "C" int pn_get_mlp_path(void) { return mlp_path(); }
-extern "C" void pn_debug_gemm_flags(int flags) { set_gemm_debug_flags(flags); }
+extern "C" void pn_debug_gemm_flags(int flags) {
+    set_gemm_debug_flags(flags);
+    pn::g_bwd_two_streams = ((flags >> 10) & 1) ^ 1;   // 1024: the whole backward on the caller's stream
+}
 extern "C" int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd) { return nt_image_bytes(N, Kd); }
 extern "C" int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int32_t N,
                                 int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream) {
