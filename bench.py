@@ -554,6 +554,8 @@ def main():
         torch.cuda.synchronize()
 
     _phase("model built; warm-up")
+    for w in range(3 * n_pool):      # every batch of the pool a few times: the caching allocator's pools (two streams) reach steady state
+        step(w)
     for w in range(warmup):
         step(w)
     sync_all()

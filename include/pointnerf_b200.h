@@ -49,7 +49,7 @@ int pn_get_mlp_path(void);
  * on the single-CTA kernel 1: no MMA, 2: no A loads, 4: no B copies, 8: no C stores, 16: no A staging stores,
  * 32: no proxy fence, 64: no epilogue (results are garbage while any of bits 0-7 is set); 512: single-CTA TN kernel;
  * 1024: pn_agg_backward keeps everything on the caller's stream (default: the weight-gradient GEMMs trail the
- * data-gradient chain on a second stream, see aggregator.cu BwdStreams). */
+ * data-gradient chain on a second stream, see aggregator.cu BwdStreams); 2048: 128-thread blocks in pn_knn_query. */
 void pn_debug_gemm_flags(int flags);
 /* Test hooks: one GEMM through the selected path (not used by the product path).
  *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias);  tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]

@@ -252,6 +252,7 @@ static BwdStreams* bwd_streams() {
     return &b;
 }
 static int g_bwd_two_streams = 1;
+extern int g_knn_threads;
 }  // namespace pn
 
 static int zero_weight_grads(const AggDims& d, const pn_agg_weights* g, cudaStream_t st) {

@@ -317,6 +317,7 @@ extern "C" int pn_ray_sample(const float* campos, const float* raydir, const flo
     return PN_OK;
 }
 
+namespace pn { int g_knn_threads = 256; }
 extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
                             const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
                             const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
@@ -330,11 +331,15 @@ extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, cons
     cudaStream_t st = (cudaStream_t)stream;
     PN_CUDA(cudaMemsetAsync(ray_any, 0, n_rays * sizeof(int), st));
     unsigned blocks = (unsigned)n_rays;
+    // (pn_debug_gemm_flags(2048) selects 128-thread blocks, which fit next to a resident GEMM CTA of 576 threads x 96
+    // registers when the next batch's query runs under this batch's backward (ray_shard.py); measured: no difference there,
+    // and 110 us instead of 74 us when the query runs alone)
+    const int kKnnThreads = g_knn_threads;
     if (n_candidates)
-        knn_kernel<true><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+        knn_kernel<true><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates);
     else
-        knn_kernel<false><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+        knn_kernel<false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
                                                  n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr);
     PN_LAUNCH_CHECK("knn_query");
     return PN_OK;

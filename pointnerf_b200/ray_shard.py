@@ -87,8 +87,13 @@ class RayShardedStep:
 
     BIG = 1 << 18   # parameters at least this large are reduced in place; smaller ones are coalesced
 
-    def __init__(self, model, bg_color, group=None, sparse=True):
+    def __init__(self, model, bg_color, group=None, sparse=True, side_prefetch=True):
         self.model, self.bg, self.group, self.sparse = model, bg_color, group, sparse
+        # the next batch's sampling / neighbour query runs on a SECOND stream, concurrently with this batch's backward: its
+        # kernels are small and latency-bound (one block per ray, 27 dependent cell reads), the backward's GEMMs leave issue
+        # slots and a few registers per SM free, and the GEMM tails leave whole SMs free
+        self._side = torch.cuda.Stream() if (side_prefetch and torch.cuda.is_available()) else None
+        self._side_done = None
         nps = model.neural_points
         params = [nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color]
         params += list(model.aggregator.parameters())
@@ -231,6 +236,8 @@ class RayShardedStep:
                     flat[off:off + p.numel()].copy_(p.grad.reshape(-1))
                     off += p.numel()
                 if self._next_cnt is not None:          # one slot per rank: SUM leaves every rank's count in place
+                    if self._side_done is not None:     # the count was produced on the prefetch stream
+                        torch.cuda.current_stream().wait_event(self._side_done)
                     slot = tail + self._tail_rest + dist.get_rank(self.group)
                     flat[slot:slot + 1].copy_(self._next_cnt[1])
             elif rest:           # one small all-gather for them
@@ -292,11 +299,25 @@ class RayShardedStep:
         the (S, M) read-back the next forward needs has completed long before the host asks for it - no idle gap."""
         if not hasattr(self.model, "sample"):
             return
-        plan = self.model.sample(cam["campos"], raydir, cam["camrotc2w"], cam["near"], cam["far"], uniform=uniform)
+        if self._side is not None and raydir.is_cuda:
+            main = torch.cuda.current_stream()
+            self._side.wait_stream(main)             # inputs are ready; every block freed so far is safe to reuse over there
+            with torch.cuda.stream(self._side):
+                plan = self.model.sample(cam["campos"], raydir, cam["camrotc2w"], cam["near"], cam["far"], uniform=uniform)
+                self._side_done = torch.cuda.Event()
+                self._side_done.record(self._side)
+            # no record_stream on the plan's tensors: they are allocated from the side stream's pool, and the only later
+            # allocations from that pool happen in a later prefetch, after its wait_stream(main) above - i.e. after every
+            # main-stream kernel that was queued while those tensors were alive
+        else:
+            plan = self.model.sample(cam["campos"], raydir, cam["camrotc2w"], cam["near"], cam["far"], uniform=uniform)
         self._plan = (raydir, uniform, plan)
 
     def _take_plan(self, raydir, uniform):
         held, self._plan = self._plan, None
+        done, self._side_done = self._side_done, None
+        if done is not None:
+            torch.cuda.current_stream().wait_event(done)      # whatever the side stream queued is ordered before this step
         if held is not None and held[0] is raydir and held[1] is uniform:
             return held[2]
         return None
@@ -330,11 +351,19 @@ class RayShardedStep:
             loss = (diff * diff).sum() / float(global_rays * gt.shape[-1])
         if next_batch is not None:
             if next_batch.get("ready") is not None:        # event of the side-stream H2D copy that produced the batch
-                torch.cuda.current_stream().wait_event(next_batch["ready"])
+                (self._side if self._side is not None else torch.cuda.current_stream()).wait_event(next_batch["ready"])
             self.prefetch(next_batch["cam"], next_batch["raydir"], next_batch.get("uniform"))
             if self.world > 1 and self.sparse and reduce and self._plan is not None and self._cap_ev is not None:
                 nxt = self._plan[2]
-                self._next_cnt = (nxt, self._count_rows(nxt.pidx, int(self.model.neural_points.points_embeding.shape[-2])))
+                T = int(self.model.neural_points.points_embeding.shape[-2])
+                if self._side is not None and self._side_done is not None:     # behind the query, on its stream
+                    with torch.cuda.stream(self._side):
+                        cnt = self._count_rows(nxt.pidx, T)
+                        self._side_done = torch.cuda.Event()
+                        self._side_done.record(self._side)
+                else:
+                    cnt = self._count_rows(nxt.pidx, T)
+                self._next_cnt = (nxt, cnt)
         loss.backward()
         if reduce:
             self.all_reduce()
