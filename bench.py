@@ -298,18 +298,19 @@ def cpu_oracle_steps(opt, tables, batches, bg, agg_state, rays, steps, warmup):
 # ---------------------------------------------------------------------------------------------------------
 def frame_bench(model, opt, name, bg_dev, dev, rank, world, chunk, frames=3):
     """Forward-only render of the workload's full frame (cfg2/cfg5 camera: 800x800 = 640 000 rays) through
-    NeuralPointsRayMarching.render_frame, is_train = 0 (no jitter).  N > 1: each rank renders its block of rows; the time is
+    NeuralPointsRayMarching.render_frame, is_train = 0 (no jitter).  N > 1: each rank renders every N-th pixel; the time is
     the max over ranks.  `ms` has the rays resident in HBM; `e2e_ms` uploads the ray directions from pinned host memory and
     reads the [R, C] image back to pinned host memory inside the timed region."""
     from pointnerf_b200 import synthetic as syn
     cam = syn.make_camera(name, view=1)
     raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
     R_all = raydir.shape[1]
-    lo, hi = R_all * rank // world, R_all * (rank + 1) // world
-    ray_host = raydir[:, lo:hi].contiguous().pin_memory()
+    # N > 1: the pixels are dealt to the ranks round-robin (pixel p -> rank p mod N): every rank sees the same mix of
+    # rays that hit the object and rays that miss it
+    ray_host = raydir[:, rank::world].contiguous().pin_memory()
     campos, rot = cam["campos"].to(dev), cam["camrotc2w"].to(dev)
     C = int(opt.shading_color_channel_num)
-    img_host = torch.empty((1, hi - lo, C), dtype=torch.float32).pin_memory()
+    img_host = torch.empty((1, ray_host.shape[1], C), dtype=torch.float32).pin_memory()
     was = opt.is_train
     opt.is_train = 0
     try:
@@ -344,7 +345,7 @@ def frame_bench(model, opt, name, bg_dev, dev, rank, world, chunk, frames=3):
     return {"ms": round(ms, 3), "e2e_ms": round(e2e_ms, 3), "h": cam["h"], "w": cam["w"], "rays": R_all, "SR": int(opt.SR), "K": int(opt.K),
             "chunk_rays": int(chunk), "rays_per_s": round(R_all / (ms * 1e-3), 1), "frac_rays_with_neighbours": round(frac_hit, 4),
             "h2d_bytes": int(ray_host.numel() * 4), "d2h_bytes": int(img_host.numel() * 4),
-            "note": "forward only, grid cached, %d GPU(s) by row blocks" % world}
+            "note": "forward only, grid cached, %d GPU(s), pixels dealt round-robin" % world}
 
 
 def frame_sweep(model, opt, name, bg_dev, dev, chunk):
@@ -488,6 +489,7 @@ def main():
     ap.add_argument("--no-frame", action="store_true", help="skip the full-frame inference timing (ms per 800x800 frame)")
     ap.add_argument("--frame-chunk", type=int, default=65536, help="rays per render_frame chunk")
     ap.add_argument("--no-sweep", action="store_true", help="skip the cfg5 inference sweep (K x SR, prune/grow between passes)")
+    ap.add_argument("--bwd-schedule", type=int, default=None, help="pn_set_backward_schedule: 0 one stream, 1 interleaved, 2 chain first")
     ap.add_argument("--no-adam", action="store_true", help="skip the secondary timing of the step WITH the Adam updates")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
     args = ap.parse_args()
@@ -534,6 +536,8 @@ def main():
     from pointnerf_b200 import _lib
     from pointnerf_b200.ray_shard import RayShardedStep
     peaks = load_peaks()
+    if args.bwd_schedule is not None:
+        _lib.check(_lib.lib().pn_set_backward_schedule(args.bwd_schedule), "pn_set_backward_schedule")
 
     opt, tables, batches, bg = build_workload(args.workload, args.rays, n_pool, seed_base=100 + 1000 * rank)
     model = make_model(opt, tables, dev)

@@ -257,6 +257,21 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
                     float* grad_color, float* grad_dir, float* grad_conf, int32_t* touched_ids,
                     int32_t* n_touched, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Makes `stream` wait for the point where the most recent pn_agg_backward on this device had produced its per-row
+ * gradients (grad_embedding / grad_color / grad_dir / grad_conf, touched_ids, n_touched) - BEFORE the weight-gradient GEMMs
+ * that trail on the caller's stream.  A multi-GPU host starts the exchange of the touched rows there (ray_shard.py), so
+ * that it runs under the remaining GEMMs.  Returns 1 if the wait was queued, 0 if no such point exists (single-stream
+ * backward: order `stream` after the caller's stream instead), < 0 on error. */
+int pn_agg_backward_wait_rows(void* stream);
+/* Kernel schedule of pn_agg_backward (process-wide; results are bit-identical in all three):
+ *   0  everything on the caller's stream, each layer's weight gradient next to its data gradient;
+ *   1  (default) the data-gradient chain on a library-owned high-priority stream, the weight-gradient GEMMs trailing it on
+ *      the caller's stream: tails and prologues of the persistent GEMMs overlap (fastest on one GPU);
+ *   2  the whole chain first, then the seven weight-gradient GEMMs: pn_agg_backward_wait_rows marks the end of the chain,
+ *      and a multi-GPU host runs the gradient-row exchange under those GEMMs. */
+int pn_set_backward_schedule(int schedule);
+int pn_get_backward_schedule(void);
+
 /* conf_coefficient of the aggregator output (point_aggregators.py:809-811 applied to neural_points.py's index_select of
  * points_conf with sample_pidx.clamp(min=0)): out[i] = clamp(table[max(idx[i],0)], lo, hi) for the whole query result in one
  * pass (evaluated as x - (x - clamp(x)) like the reference, bit-identical).  table float[n_points]; idx int32[n] (-1 = empty slot -> row 0, as in the reference); idx/out 16-byte aligned.

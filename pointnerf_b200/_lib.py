@@ -101,6 +101,9 @@ def _declare(lib):
         "pn_agg_backward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, c_int64,
                                     POINTER(AggWeights), c_int, P, P, P, P, P, P, P, c_int64, P]),
         "pn_debug_gemm_flags": (None, [c_int]),
+        "pn_agg_backward_wait_rows": (c_int, [P]),
+        "pn_set_backward_schedule": (c_int, [c_int]),
+        "pn_get_backward_schedule": (c_int, []),
         "pn_count_touched_rows": (c_int, [P, c_int64, c_int64, P, P, P]),
         "pn_rows_pack": (c_int, [P, c_int64, c_int64, c_int32, P, P, P, P, P, P]),
         "pn_rows_merge": (c_int, [P, c_int32, c_int64, c_int32, c_int64, P, P, P, P, P, P]),

@@ -74,7 +74,7 @@ namespace pn {
 struct FwdWs { float *W1a, *W3a, *Wc0; char *I1a, *I1b, *I3a, *I3b, *Ic0, *Ic2, *Ic4; };
 struct BwdWs {
     float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
-    float *GA, *GB, *GA2, *GB2, *GSa, *GSb, *GSc, *GSd, *galpha, *PG, *tn, *apart;
+    float *GA, *GB, *GA2, *GB2, *GA3, *GSa, *GSb, *GSc, *GSd, *galpha, *PG, *tn, *apart;
     char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
     int *cnt, *rank, *tmp, *sorted, *skey, *scan, *hflag, *hscan;
     int nblk_reduce;
@@ -124,6 +124,7 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     // it has run, so the weight gradients can trail the data-gradient chain on another stream (pn_agg_backward)
     t.GA2 = c.take<float>(m * d.in3p);
     t.GB2 = c.take<float>(m * d.W);
+    t.GA3 = c.take<float>(m * d.in1p);   // d/dX1 in the chain-first schedule: every other gradient buffer is still awaited by a held-back weight gradient
     t.GSa = c.take<float>(s * d.incp);
     t.GSb = c.take<float>(s * d.incp);
     t.GSc = c.take<float>(s * d.incp);
@@ -232,6 +233,8 @@ namespace pn {
 struct BwdStreams {
     cudaStream_t chain = nullptr;
     cudaEvent_t ev[12] = {};
+    cudaEvent_t chain_end = nullptr;     // end of the data-gradient chain of the most recent backward (pn_agg_backward_wait_rows)
+    bool chain_end_valid = false;
     int device = -1;
     bool ok = false;
 };
@@ -246,12 +249,14 @@ static BwdStreams* bwd_streams() {
         if (cudaStreamCreateWithPriority(&b.chain, cudaStreamNonBlocking, hi) != cudaSuccess) return nullptr;
         for (auto& e : b.ev)
             if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&b.chain_end, cudaEventDisableTiming) != cudaSuccess) return nullptr;
         b.device = dev;
         b.ok = true;
     }
     return &b;
 }
 static int g_bwd_two_streams = 1;
+static int g_bwd_chain_first = 0;    // pn_set_backward_schedule(2): all weight-gradient GEMMs after the data-gradient chain
 extern int g_knn_threads;
 }  // namespace pn
 
@@ -316,11 +321,24 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     auto IMG = [&](const char* img) { return tcp ? img : (const char*)nullptr; };
 
     // ---- streams: hs = data-gradient chain, st = weight gradients (see BwdStreams); one stream when disabled / SIMT path
-    BwdStreams* bs = (g_bwd_two_streams && tcp) ? bwd_streams() : nullptr;
-    cudaStream_t hs = bs ? bs->chain : st;
+    const bool chain_first = g_bwd_chain_first && tcp;
+    BwdStreams* bs = ((g_bwd_two_streams || chain_first) && tcp) ? bwd_streams() : nullptr;
+    if (!bs) {
+        BwdStreams* any = bwd_streams();
+        if (any) any->chain_end_valid = false;
+    }
+    // chain_first: one stream, but the weight-gradient GEMMs are held back until the chain has finished and its end is
+    // marked (chain_end) - a multi-GPU host exchanges the per-row gradients on another stream under those GEMMs
+    cudaStream_t hs = (bs && !chain_first) ? bs->chain : st;
+    GemmTN held[8];
+    int n_held = 0;
+    auto wgrad = [&](const GemmTN& t) -> int {
+        if (chain_first) { held[n_held++] = t; return PN_OK; }
+        return gemm_tn(t, ws.tn, st);
+    };
     int evi = 0;
     auto order = [&](cudaStream_t from, cudaStream_t to) -> int {   // work queued on `to` from now on sees everything queued on `from` so far
-        if (!bs) return PN_OK;
+        if (!bs || chain_first) return PN_OK;
         cudaEvent_t e = bs->ev[evi++];
         PN_CUDA(cudaEventRecord(e, from));
         PN_CUDA(cudaStreamWaitEvent(to, e, 0));
@@ -333,7 +351,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     PN_TRY(order(hs, st));
     {   // color.4
         GemmTN t{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GSa, d.C, ws.Wc4T, d.C, ws.GSb, d.C, S, d.C, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc4);
         g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
@@ -342,7 +360,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     {   // color.2
         GemmTN t{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSc, d.C, S, d.C, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc2);
         g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
@@ -351,7 +369,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     {   // color.0: d/dFS (only the first W columns are consumed)
         GemmTN t{ws.GSc, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GSc, d.C, ws.Wc0T, d.C, ws.GSd, d.incp, S, d.incp, d.C, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.Jc0);
         PN_TRY(gemm_nt(g, hs));
@@ -370,7 +388,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // ---- block3 (M rows).  GA = dPre4 [M,W]
     {   // block3.2
         GemmTN t{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GA, d.W, ws.W3bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J3b);
         g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
@@ -379,12 +397,12 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     cudaEvent_t ga_free = nullptr;              // recorded on st once block3.2's weight gradient has read GA (dPre4)
     {   // block3.0: GA2[M,in3p] = d/dX3, first W columns masked by lrelu'(H2) (H2 = X3[:, :W])
-        if (bs) {                               // st so far: ... TN(block3.2).  Mark the point where GA becomes reusable.
+        if (bs && !chain_first) {               // st so far: ... TN(block3.2).  Mark the point where GA becomes reusable.
             ga_free = bs->ev[evi++];
             PN_CUDA(cudaEventRecord(ga_free, st));
         }
         GemmTN t{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA2, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J3a);
         g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
@@ -396,7 +414,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // ---- block1.  GA2[:, :W] = dPre2 (row stride in3p)
     {   // block1.2
         GemmTN t{ws.GA2, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         GemmNT g = nt(ws.GA2, d.in3p, ws.W1bT, d.W, ws.GB2, d.W, M, d.W, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J1b);
         g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
@@ -405,13 +423,14 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     }
     {   // block1.0: GA[M,in1p] = d/dX1 (GA is free again once block3.2's weight gradient has read dPre4)
         GemmTN t{ws.GB2, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
-        PN_TRY(gemm_tn(t, ws.tn, st));
+        PN_TRY(wgrad(t));
         if (ga_free) PN_CUDA(cudaStreamWaitEvent(hs, ga_free, 0));
-        GemmNT g = nt(ws.GB2, d.W, ws.W1aT, d.W, ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
+        // (chain_first: all four earlier gradient buffers are still awaited by held-back weight gradients -> GA3)
+        GemmNT g = nt(ws.GB2, d.W, ws.W1aT, d.W, chain_first ? ws.GA3 : ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
         g.Bimg = IMG(ws.J1a);
         PN_TRY(gemm_nt(g, hs));
     }
-    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, sv.X1, ws.GA, ws.PG, pgw);
+    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, sv.X1, chain_first ? ws.GA3 : ws.GA, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_prep_bwd");
     // ---- per-row gradients out
     if (!scatter_rows) {
@@ -438,8 +457,28 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
             PN_LAUNCH_CHECK("agg_head_ids");
         }
     }
+    if (bs) {                                   // per-row gradients and touched ids are final here, before the trailing weight gradients
+        PN_CUDA(cudaEventRecord(bs->chain_end, hs));
+        bs->chain_end_valid = true;
+    }
     PN_TRY(order(hs, st));                      // the caller's stream joins the chain
+    for (int i = 0; i < n_held; ++i) PN_TRY(gemm_tn(held[i], ws.tn, st));
     return PN_OK;
+}
+
+extern "C" int pn_set_backward_schedule(int schedule) {
+    PN_CHECK_ARG(schedule >= 0 && schedule <= 2, "pn_set_backward_schedule: 0 (one stream), 1 (interleaved on two streams), 2 (chain first)");
+    g_bwd_two_streams = schedule == 1;
+    g_bwd_chain_first = schedule == 2;
+    return PN_OK;
+}
+extern "C" int pn_get_backward_schedule(void) { return g_bwd_chain_first ? 2 : (g_bwd_two_streams ? 1 : 0); }
+
+extern "C" int pn_agg_backward_wait_rows(void* stream) {
+    BwdStreams* bs = (g_bwd_two_streams || g_bwd_chain_first) ? bwd_streams() : nullptr;
+    if (!bs || !bs->chain_end_valid) return 0;
+    PN_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, bs->chain_end, 0));
+    return 1;
 }
 
 // ---- MLP path selection and GEMM test hooks ---------------------------------------------------------------

@@ -94,6 +94,7 @@ class RayShardedStep:
         # slots and a few registers per SM free, and the GEMM tails leave whole SMs free
         self._side = torch.cuda.Stream() if (side_prefetch and torch.cuda.is_available()) else None
         self._side_done = None
+        self._comm = None            # stream of the touched-row exchange (starts at the end of the backward's data-gradient chain)
         nps = model.neural_points
         params = [nps.points_embeding, nps.points_conf, nps.points_dir, nps.points_color]
         params += list(model.aggregator.parameters())
@@ -250,13 +251,29 @@ class RayShardedStep:
                 self._sparse_tables(tables, pid)
                 mode = "torch"
         handles = []
+        joined = None
+        if mode == "cuda":
+            # the touched rows are final at the end of the backward's data-gradient chain; the weight-gradient GEMMs still
+            # trail on this stream: pack / all-gather / merge run on their own stream, under those GEMMs.  Issued BEFORE the
+            # MLP all-reduce: the process group runs collectives in issue order, and that one has to wait for the GEMMs
+            from . import _lib
+            main = torch.cuda.current_stream()
+            if self._comm is None:
+                self._comm = torch.cuda.Stream()
+            rc = _lib.lib().pn_agg_backward_wait_rows(self._comm.cuda_stream)
+            if rc < 0:
+                _lib.check(rc, "pn_agg_backward_wait_rows")
+            if rc != 1:
+                self._comm.wait_stream(main)
+            with torch.cuda.stream(self._comm):
+                self._sparse_tables_cuda({n: (getattr(nps, n) if getattr(nps, n) is not None and getattr(nps, n).requires_grad else None)
+                                          for n in names})
+            joined = (main, self._comm)
         if flat is not None and hi > lo:
             handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
         if mode is None:
             handles += [dist.all_reduce(t.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for t in tables]
         if mode == "cuda":
-            self._sparse_tables_cuda({n: (getattr(nps, n) if getattr(nps, n) is not None and getattr(nps, n).requires_grad else None)
-                                      for n in names})
             if rest and tail is None:   # rank-ordered sum of the gathered head columns: identical bits on every replica
                 tot = self._head_all.sum(0)
                 off = 0
@@ -276,6 +293,8 @@ class RayShardedStep:
                     off += p.numel()
         for h in handles:
             h.wait()
+        if joined is not None:
+            joined[0].wait_stream(joined[1])
         if tail is not None:
             off = tail
             for p in rest:       # the reduced values, in place in the tail (same bits on every replica)
