@@ -261,28 +261,47 @@ class NeuralPointsRayMarching(nn.Module):
         return plan
 
     @torch.no_grad()
-    def render_frame(self, campos, raydir, bg_color, camrotc2w, near, far, chunk=65536, keys=("coarse_raycolor",)):
+    def render_frame(self, campos, raydir, bg_color, camrotc2w, near, far, chunk=65536, keys=("coarse_raycolor",), side_stream=True):
         """Full-frame inference: the chunk loop of run/train_ft.py:test (:284-340, ``chunk_size = random_sample_size**2``
         rays per ``model.test()`` call) over raydir [1,R,3], forward only.  The sampling / neighbour query / work lists of
-        chunk i+1 are queued before the aggregator of chunk i, so the (S, M) read-back of a chunk never drains the GPU
-        queue; chunks reuse the same activation buffers through the caching allocator (nothing is kept for a backward).
+        chunk i+1 run on a second stream under the aggregator of chunk i (they are small latency-bound kernels, ~20 % of a
+        frame when serialised), so neither they nor the (S, M) read-back of a chunk sit on the critical path; chunks reuse
+        the same activation buffers through the caching allocator (nothing is kept for a backward).
         Returns {key: [1,R,...]} for ``keys`` (any of the ``forward`` outputs)."""
         R = int(raydir.shape[1])
+        if R == 0:
+            return {k: torch.zeros((1, 0, 0), device=raydir.device) for k in keys}
         starts = list(range(0, R, int(chunk)))
         outs = {k: [] for k in keys}
+        main = torch.cuda.current_stream()
+        side = None
+        if side_stream and raydir.is_cuda:
+            side = getattr(self, "_frame_stream", None)
+            if side is None:
+                side = self._frame_stream = torch.cuda.Stream()
         xp = _query.w2pers(self.neural_points.xyz.detach(), camrotc2w[0], campos[0])
-        plan = self.sample(campos, raydir[:, :chunk], camrotc2w, near, far, xyz_pers=xp) if R else None
+
+        def sample(s):
+            if side is None:
+                return self.sample(campos, raydir[:, s:s + chunk], camrotc2w, near, far, xyz_pers=xp), None
+            # allocations from the side stream's pool only happen after this wait: every main-stream kernel that used the
+            # plans freed so far has been queued before it
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                plan = self.sample(campos, raydir[:, s:s + chunk], camrotc2w, near, far, xyz_pers=xp)
+                done = torch.cuda.Event()
+                done.record(side)
+            return plan, done
+        plan, done = sample(starts[0])
         for i, s in enumerate(starts):
-            nxt = None
-            if i + 1 < len(starts):
-                s2 = starts[i + 1]
-                nxt = self.sample(campos, raydir[:, s2:s2 + chunk], camrotc2w, near, far, xyz_pers=xp)
+            nxt, nxt_done = sample(starts[i + 1]) if i + 1 < len(starts) else (None, None)
+            if done is not None:
+                main.wait_event(done)
             o = self.forward(campos, raydir[:, s:s + chunk], bg_color=bg_color, camrotc2w=camrotc2w, near=near, far=far, plan=plan)
             for k in keys:
                 outs[k].append(o[k])
-            plan = nxt
-        return {k: (torch.cat(v, dim=1) if len(v) != 1 else v[0]) for k, v in outs.items()} if R else \
-            {k: torch.zeros((1, 0, 0), device=raydir.device) for k in keys}
+            plan, done = nxt, nxt_done
+        return {k: (torch.cat(v, dim=1) if len(v) != 1 else v[0]) for k, v in outs.items()}
 
     def forward(self, campos, raydir, gt_image=None, bg_color=None, camrotc2w=None, pixel_idx=None, near=None, far=None,
                 focal=None, h=None, w=None, style_code=None, intrinsic=None, uniform=None, fused=True, plan=None, **kargs):

@@ -150,3 +150,27 @@ def test_prefetched_plan_gives_identical_step(tiny_scene, cuda_dev):
     g2 = st.flat_grads().clone()
     assert torch.equal(l1, l2) and torch.equal(g1, g2)
     assert float(g1.abs().max()) > 0
+
+
+@pytest.mark.parametrize("side", [True, False])
+def test_render_frame_equals_one_forward(tiny_scene, cuda_dev, side):
+    """Chunked full-frame inference (run/train_ft.py:test loop) gives the bits of ONE forward over all rays: a row's result
+    does not depend on which other rows share its GEMM tile, nor on the stream its query ran on."""
+    opt, tables, cam = tiny_scene
+    opt = copy.copy(opt)
+    opt.is_train = 0
+    raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
+    R = raydir.shape[1]
+    bg = torch.rand(opt.shading_color_channel_num, generator=torch.Generator().manual_seed(4)).to(cuda_dev)
+    model = _model(opt, tables, cuda_dev)
+    args = (cam["campos"].to(cuda_dev), raydir.to(cuda_dev), bg, cam["camrotc2w"].to(cuda_dev), cam["near"], cam["far"])
+    with torch.no_grad():
+        whole = model(args[0], args[1], bg_color=bg, camrotc2w=args[3], near=cam["near"], far=cam["far"])
+    keys = ("coarse_raycolor", "coarse_point_opacity", "ray_mask", "coarse_is_background")
+    for chunk in (R, 1000, 333):
+        out = model.render_frame(*args, chunk=chunk, keys=keys, side_stream=side)
+        for k in keys:
+            assert out[k].shape == whole[k].shape, (k, chunk)
+            assert torch.equal(out[k], whole[k]), (k, chunk)
+    empty = model.render_frame(args[0], args[1][:, :0], bg, args[3], cam["near"], cam["far"])
+    assert empty["coarse_raycolor"].shape[1] == 0

@@ -113,3 +113,38 @@ def test_two_rank_gradients_equal_single_process(tmp_path, sparse):
     assert torch.allclose(got["loss"], loss, rtol=1e-6, atol=1e-8)
     assert torch.allclose(got["flat"], step.flat_grads(), rtol=1e-5, atol=1e-7)
     assert float(step.flat_grads().abs().max()) > 0
+
+
+def test_rank_local_step_issues_no_collective(monkeypatch):
+    """A step with reduce=False (per-stage timing on one rank, single-process reference gradients) must not touch the
+    process group: rank 0 once queued the capacity all-reduce alone there and every multi-GPU bench run hung."""
+    import torch.distributed as dist
+    from pointnerf_b200.ray_shard import RayShardedStep
+
+    class Toy(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.neural_points = torch.nn.Module()
+            for n, w in (("points_embeding", 4), ("points_conf", 1), ("points_dir", 3), ("points_color", 3)):
+                setattr(self.neural_points, n, torch.nn.Parameter(torch.ones(1, 10, w)))
+            self.aggregator = torch.nn.Linear(3, 2)
+
+        def forward(self, campos, raydir, bg_color=None, **kw):
+            s = sum(getattr(self.neural_points, n).sum() for n in ("points_embeding", "points_conf", "points_dir", "points_color"))
+            return {"coarse_raycolor": self.aggregator(raydir) * s + bg_color}
+
+    m = Toy()
+    bg = torch.nn.Parameter(torch.zeros(2))
+    st = RayShardedStep(m, bg, sparse=True)
+    st.world = 2                                            # as on a 2-rank job, without a process group behind it
+
+    def boom(*a, **k):
+        raise AssertionError("collective issued by a rank-local step")
+    for fn in ("all_reduce", "all_gather_into_tensor", "all_gather", "barrier"):
+        monkeypatch.setattr(dist, fn, boom)
+    monkeypatch.setattr(st, "_begin_cap_exchange", boom)
+    cam = dict(campos=torch.zeros(1, 3), camrotc2w=torch.eye(3)[None], near=0.1, far=1.0)
+    loss = st(cam, torch.randn(1, 5, 3), torch.zeros(1, 5, 2), global_rays=10, reduce=False)
+    assert torch.isfinite(loss) and bg.grad is not None
+    with pytest.raises(AssertionError):                     # and the same call WITH the exchange does reach the group
+        st(cam, torch.randn(1, 5, 3), torch.zeros(1, 5, 2), global_rays=10, reduce=True)
