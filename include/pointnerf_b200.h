@@ -251,6 +251,9 @@ int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg
  *   scatter_rows == 1: summed per table row g into [T, *] arrays by a sorted segmented reduction (no
  *                      atomics; replaces the index_add_ backward of index_select), rows never referenced
  *                      are zero-filled. */
+/* Streams: with the default schedule (pn_set_backward_schedule) part of the work runs on a library-owned stream that is
+ * forked from and joined back into `stream` by events, so for the caller everything is still ordered on `stream`: work
+ * queued on it afterwards sees every output, and the call never blocks the host. */
 int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
                     const float* grad_decoded, const void* saved, int64_t saved_bytes,
                     const pn_agg_weights* grad_w, int scatter_rows, float* grad_embedding,

@@ -42,6 +42,10 @@ def test_size_queries_need_no_gpu():
     assert l.pn_grid_workspace_bytes(1000, 4096) > 0
     assert l.pn_compact_workspace_bytes(1000) > 0
     assert l.pn_composite_workspace_bytes(4096, 128, 20000) > 0
+    assert l.pn_prune_workspace_bytes(1000) > 0 and l.pn_voxel_downsample_workspace_bytes(1000) > 0
+    assert l.pn_color_mse_workspace_bytes() > 0
+    assert l.pn_get_backward_schedule() == 1 and l.pn_set_backward_schedule(7) < 0 and b"pn_set_backward_schedule" in l.pn_last_error()
+    assert l.pn_set_backward_schedule(0) == 0 and l.pn_get_backward_schedule() == 0 and l.pn_set_backward_schedule(1) == 0
     p = _lib.AggParams(32, 3, 5, 4, 256, 128, 8, 1, 80, 0.01, 1.0)
     assert l.pn_agg_saved_bytes(ctypes.byref(p), 100, 700) > 0
     assert l.pn_agg_workspace_bytes(ctypes.byref(p), 100, 700, 5000, 1) > l.pn_agg_workspace_bytes(ctypes.byref(p), 100, 700, 5000, 0)
