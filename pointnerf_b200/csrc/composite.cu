@@ -64,15 +64,29 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
         carry *= __shfl_sync(kFull, incl, 31);
         if (live) {
             unsigned m = __ballot_sync(kFull, s < SR && w != 0.f && T >= kTermT);
+            // four feature rows in flight per round (a ray is one dependent chain of row loads otherwise: ~0.4 us per
+            // sample, and the longest ray sets the kernel's time); the sums keep their sample order
             while (m) {
-                int j = __ffs(m) - 1;
-                m &= m - 1;
-                float wj = __shfl_sync(kFull, w, j);
-                const float* f = feat + __shfl_sync(kFull, frow_i, j) * C1 + 1;
+                float wj[4], v[4][NC];
 #pragma unroll
-                for (int i = 0; i < NC; ++i) {
-                    int c = lane + 32 * i;
-                    if (c < C) acc[i] = fmaf(wj, f[c], acc[i]);
+                for (int u = 0; u < 4; ++u) {
+                    const int j = m ? __ffs(m) - 1 : 0;
+                    wj[u] = m ? __shfl_sync(kFull, w, j) : 0.f;
+                    const int64_t row = __shfl_sync(kFull, frow_i, j);
+                    const bool on = m != 0;
+                    m &= m - 1;
+                    const float* f = feat + row * C1 + 1;
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) {
+                        int c = lane + 32 * i;
+                        v[u][i] = (on && c < C) ? f[c] : 0.f;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (wj[u] == 0.f) continue;          // unused slot of the round (a live sample never has w == 0)
+#pragma unroll
+                    for (int i = 0; i < NC; ++i) acc[i] = fmaf(wj[u], v[u][i], acc[i]);
                 }
             }
             if (carry < kTermT) live = false;
