@@ -400,6 +400,55 @@ def frame_sweep(model, opt, name, bg_dev, dev, chunk):
     return out
 
 
+def maintenance_bench(model, opt, batch_dev, bg_dev, dev):
+    """The between-pass kernels of SURVEY.md 8(f) on the workload's cloud: voxel down-sampling (construct_vox_points_closest,
+    wall clock: it ends in a host read-back of the voxel count) and the probe outputs of one batch (pn_probe_rays)."""
+    from pointnerf_b200.voxelize import construct_vox_points_closest
+    nps = model.neural_points
+    xyz = nps.xyz.detach()
+    N = int(xyz.shape[0])
+    out = {}
+    for res in (320, 1000):
+        construct_vox_points_closest(xyz, res)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            c, _, _ = construct_vox_points_closest(xyz, res)
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3 / 3
+        passes = (3 * int(np.ceil(np.log2(res * 1.05 + 2))) + 7) // 8
+        algo = N * (12 + passes * 48 + 24) + 36 * int(c.shape[0])
+        out["voxel_downsample_res%d" % res] = {"ms": round(ms, 3), "points": N, "voxels": int(c.shape[0]), "radix_passes": passes,
+                                               "GB/s": round(algo / (ms * 1e-3) / 1e9, 1),
+                                               "note": "wall clock of construct_vox_points_closest: bbox reductions, 2 host read-backs, %d launches" % (6 + 4 * passes)}
+    keep = (opt.prob, opt.is_train)
+    try:
+        opt.prob, opt.is_train = 1, 0
+        with torch.no_grad():
+            o = model(batch_dev["cam"]["campos"], batch_dev["raydir"], bg_color=bg_dev, camrotc2w=batch_dev["cam"]["camrotc2w"],
+                      near=batch_dev["cam"]["near"], far=batch_dev["cam"]["far"])
+            plan = model.sample(batch_dev["cam"]["campos"], batch_dev["raydir"], batch_dev["cam"]["camrotc2w"], batch_dev["cam"]["near"],
+                                batch_dev["cam"]["far"])
+            args = (o["coarse_point_opacity"][0], plan.raw["ray_any"], plan.loc_w, plan.pidx, o["weight"][0])
+            model.probe_outputs(*args)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                model.probe_outputs(*args)
+            e1.record()
+            torch.cuda.synchronize()
+        R, SR, K = (int(v) for v in plan.pidx.shape)
+        F_ = int(opt.point_features_dim)
+        hit = int((plan.raw["ray_any"] > 0).sum())
+        algo = 4 * R * SR + hit * (16 + K * (8 + 4 * (F_ + 10))) + 4 * R * (F_ + 12)
+        us = e0.elapsed_time(e1) / 20 * 1e3
+        out["probe_rays"] = {"us": round(us, 2), "rays": R, "rays_with_neighbours": hit, "GB/s": round(algo / (us * 1e-6) / 1e9, 1),
+                             "note": "per call of NeuralPointsRayMarching.probe_outputs (8 output allocations + one launch): host-bound at this ray count"}
+    finally:
+        opt.prob, opt.is_train = keep
+    return out
+
+
 def psnr_vs_oracle(dev):
     """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
     oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
@@ -749,6 +798,11 @@ def main():
                             "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port")}
         cpu["psnr"] = psnr_vs_oracle(dev)
 
+    maint = None
+    if rank == 0 and world == 1 and not args.no_sweep:
+        _phase("maintenance kernels")
+        maint = maintenance_bench(model, opt, dev_batches[0], bg_p.detach(), dev)
+
     # ---- cfg5 sweep (N = 1, after everything else: it prunes / grows the point cloud)
     sweep = None
     if rank == 0 and world == 1 and not args.no_sweep and not args.no_frame:
@@ -776,7 +830,7 @@ def main():
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, ("frame_%dx%d" % (frame["w"], frame["h"]) if frame else "frame_800x800"): frame,
-                "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep}
+                "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint}
         _emit(line)
     if world > 1:
         dist.barrier()
