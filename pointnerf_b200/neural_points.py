@@ -351,10 +351,15 @@ class NeuralPointsRayMarching(nn.Module):
         R, SR, K = (int(v) for v in sample_pidx.shape)
         F_ = int(nps.points_embeding.shape[-1])
         dev = sample_pidx.device
-        f32 = dict(dtype=torch.float32, device=dev)
-        o_op, o_slot = torch.empty((1, R, 1), **f32), torch.empty((1, R), dtype=torch.int32, device=dev)
-        o_loc, o_far = torch.empty((1, R, 3), **f32), torch.empty((1, R, 1), **f32)
-        o_col, o_dir, o_cnf, o_emb = torch.empty((1, R, 3), **f32), torch.empty((1, R, 3), **f32), torch.empty((1, R, 1), **f32), torch.empty((1, R, F_), **f32)
+        # one allocation carved into the eight outputs (sections of whole rows: every view is contiguous)
+        widths = (1, 3, 1, 3, 3, 1, F_)
+        flat = torch.empty(R * (sum(widths) + 1), dtype=torch.float32, device=dev)
+        views, off = [], 0
+        for wd in widths:
+            views.append(flat[off:off + R * wd].view(1, R, wd))
+            off += R * wd
+        o_op, o_loc, o_far, o_col, o_dir, o_cnf, o_emb = views
+        o_slot = flat[off:off + R].view(torch.int32).view(1, R)
         _lib.check(_lib.lib().pn_probe_rays(
             _lib.ptr(opacity.detach().reshape(R, SR).contiguous()), _lib.ptr(ray_any.contiguous()), _lib.ptr(sample_loc_w.contiguous()),
             _lib.ptr(sample_pidx.contiguous()), _lib.ptr(weight.detach().contiguous()), _lib.ptr(nps.xyz.detach()),

@@ -13,10 +13,11 @@ import torch
 from . import _lib
 
 
-def construct_vox_points_closest(xyz_val, vox_res, partition_xyz=None, space_min=None, space_max=None):
+def construct_vox_points_closest(xyz_val, vox_res, partition_xyz=None, space_min=None, space_max=None, return_inverse=False):
     """xyz_val [N,3] float32 CUDA; vox_res: number (or [3] tensor); optional bounding box ``space_min`` / ``space_max`` [3].
     Returns (xyz_centroid [U,3], sparse_grid_idx int32 [U,3] in lexicographic order, min_idx int64 [U]): the occupied
-    voxels, their centroids and the index of the point closest to each centroid - as the reference.
+    voxels, their centroids and the index of the point closest to each centroid - as the reference
+    (``return_inverse=True`` appends inv_idx int32 [N], the voxel of every point: torch.unique's inverse).
 
     With a bounding box the reference filters ``xyz_val`` by the (open) box but keeps computing the voxel coordinates from
     the unfiltered array (:539,547,552), which only works when nothing is filtered; here the filter applies to both and
@@ -67,5 +68,6 @@ def construct_vox_points_closest(xyz_val, vox_res, partition_xyz=None, space_min
     U, outside = (int(v) for v in counts.cpu())      # host sync: the number of occupied voxels sizes the result
     if outside:
         raise _lib.LibraryError("pn_voxel_downsample: %d points fall outside the %d-bit voxel key range" % (outside, bits))
-    construct_vox_points_closest.last_inverse = inv_idx
+    if return_inverse:
+        return centroid[:U], grid_idx[:U], min_idx[:U], inv_idx
     return centroid[:U], grid_idx[:U], min_idx[:U]

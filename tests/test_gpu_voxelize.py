@@ -11,10 +11,10 @@ pytestmark = pytest.mark.gpu
 
 def _check(xyz, vox_res, dev, **box):
     want_c, want_g, want_m, inv, res = mp.construct_vox_points_closest(xyz, vox_res, **box)
-    got_c, got_g, got_m = construct_vox_points_closest(xyz.to(dev), vox_res, **{k: v.to(dev) for k, v in box.items()})
+    got_c, got_g, got_m, got_inv = construct_vox_points_closest(xyz.to(dev), vox_res, return_inverse=True, **{k: v.to(dev) for k, v in box.items()})
     assert got_g.dtype == torch.int32 and got_m.dtype == torch.int64
     assert torch.equal(got_g.cpu(), want_g), "voxel set / order differs"               # integer work: bit-exact
-    assert torch.equal(construct_vox_points_closest.last_inverse.cpu().long(), inv)
+    assert torch.equal(got_inv.cpu().long(), inv)
     assert torch.equal(got_c.cpu(), want_c), "centroids (serial fp32 sums in point order) differ"
     gm = got_m.cpu()
     diff = gm != want_m
@@ -54,8 +54,8 @@ def test_full_size_properties(cuda_dev):
     g = torch.Generator(device="cuda").manual_seed(3)
     N, res = 3_000_000, 320
     xyz = torch.rand(N, 3, device=cuda_dev, generator=g)
-    c, gidx, m = construct_vox_points_closest(xyz, res)
-    inv = construct_vox_points_closest.last_inverse.long()
+    c, gidx, m, inv = construct_vox_points_closest(xyz, res, return_inverse=True)
+    inv = inv.long()
     lo, hi = xyz.min(0)[0], xyz.max(0)[0]
     edge = (hi - lo).max() * 1.05
     smin = (hi + lo) / 2 - edge / 2
