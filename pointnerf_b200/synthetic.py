@@ -22,6 +22,14 @@ CONFIGS = {
     "tiny": dict(n_points=6000, opt=dict(SR=24, K=8, P=9, max_o=20000, z_depth_dim=96,
                                          ranges=(-0.12, -0.12, -0.12, 0.12, 0.12, 0.12)),
                  near=0.3, far=0.9, cam_dist=0.6, h=48, w=48, focal=110.0, surfaces="small"),
+    # miniatures of cfg3 / cfg4 for the oracle-parity tests: their voxel sizes, bucket capacities, SR, near / far and
+    # camera-inside-the-scene geometry on a few thousand points
+    "tiny3": dict(n_points=40000, opt=dict(SR=24, K=8, P=30, max_o=30000, z_depth_dim=128, vsize=(0.008, 0.008, 0.008),
+                                          ranges=(-0.4, -0.4, -0.15, 0.4, 0.4, 0.15), radius_limit_scale=4.0),
+                  near=0.1, far=0.9, cam_dist=0.0, h=48, w=64, focal=57.0, surfaces="room"),
+    "tiny4": dict(n_points=12000, opt=dict(SR=24, K=8, P=26, max_o=30000, z_depth_dim=160, vsize=(0.08, 0.08, 0.08),
+                                           ranges=(-10.0, -5.0, -1.0, 10.0, 5.0, 1.0)),
+                  near=0.1, far=12.0, cam_dist=0.0, h=64, w=96, focal=100.0, surfaces="street"),
     "cfg1": dict(n_points=200_000, opt=dict(SR=40, K=8, P=9, max_o=400_000), near=2.0, far=6.0, cam_dist=4.0,
                  h=400, w=400, focal=555.0, surfaces="lego"),
     "cfg2": dict(n_points=1_000_000, opt=dict(SR=80, K=8, P=9, max_o=830_000), near=2.0, far=6.0, cam_dist=4.0,

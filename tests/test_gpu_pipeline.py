@@ -174,3 +174,24 @@ def test_render_frame_equals_one_forward(tiny_scene, cuda_dev, side):
             assert torch.equal(out[k], whole[k]), (k, chunk)
     empty = model.render_frame(args[0], args[1][:, :0], bg, args[3], cam["near"], cam["far"])
     assert empty["coarse_raycolor"].shape[1] == 0
+
+
+@pytest.mark.parametrize("name", ["tiny3", "tiny4"])
+def test_forward_on_other_scene_shapes(cuda_dev, name):
+    """Whole forward on the miniatures of BASELINE configs 3 / 4 against the CPU oracle pipeline."""
+    opt, tables = syn.make_scene(name)
+    cam = syn.make_camera(name)
+    raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, 300, seed=8))
+    bg = torch.rand(opt.shading_color_channel_num, generator=torch.Generator().manual_seed(2))
+    model = _model(opt, tables, cuda_dev, alpha_bias=20.0 if name == "tiny4" else 60.0)
+    sd = model.aggregator.state_dict()
+    sd = {k: v.detach().cpu() for k, v in sd.items()}
+    with torch.no_grad():
+        out = model(cam["campos"].to(cuda_dev), raydir.to(cuda_dev), bg_color=bg.to(cuda_dev), camrotc2w=cam["camrotc2w"].to(cuda_dev),
+                    near=cam["near"], far=cam["far"])
+    ref = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, need_grads=False)
+    ref64 = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, need_grads=False, dtype=torch.float64)
+    assert torch.equal(out["ray_mask"].cpu(), ref["ray_mask"])
+    assert_close(out["coarse_raycolor"], ref["coarse_raycolor"], "coarse_raycolor", want64=ref64["coarse_raycolor"])
+    assert_close(out["coarse_point_opacity"], ref["coarse_point_opacity"], "coarse_point_opacity", want64=ref64["coarse_point_opacity"])
+    assert_close(out["coarse_is_background"], ref["coarse_is_background"], "coarse_is_background", want64=ref64["coarse_is_background"])

@@ -163,3 +163,27 @@ def test_knn_other_K(tiny_scene, cuda_dev, K):
     sel = raw["ray_any"].cpu() > 0
     assert torch.equal(sel.to(torch.int8)[None], ray_mask)
     assert torch.equal(raw["sample_pidx"].cpu()[sel][None], pidx)
+
+
+@pytest.mark.parametrize("name", ["tiny3", "tiny4"])
+def test_query_on_other_scene_shapes(cuda_dev, name):
+    """Miniatures of BASELINE configs 3 / 4 (16 mm voxels with P = 30 inside a room; 16 cm voxels with P = 26 on a street
+    slab; SR = 24, near = 0.1, camera inside the point cloud): neighbour slots, positions and masks bit-exact against the
+    oracle, with the sample depths handed to both sides."""
+    opt, tables = syn.make_scene(name)
+    cam = syn.make_camera(name)
+    raydir, pix = syn.make_rays(cam, syn.random_pixels(cam, 600, seed=3))
+    (pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges), ex = _oracle(opt, tables, cam, raydir)
+    assert int(ray_mask.sum()) > 50 and int((pidx >= 0).sum()) > 2000
+    d = cuda_dev
+    q = query.lighting_fast_querier(d, opt)
+    raw = q.query_raw(tables["xyz"].to(d), raydir.to(d), cam["campos"].to(d), cam["near"], cam["far"], ts=ex["ts"].to(d))
+    info = raw["grid"].info_host()
+    assert info[_lib.GI_OVER_P] == 0 and info[_lib.GI_OVER_MAX_O] == 0
+    if name == "tiny3":
+        assert int(ex["grid"]["occ_numpnts"].max()) > 9      # buckets deeper than the lego P = 9
+    sel = torch.nonzero(raw["ray_any"] > 0).squeeze(1)
+    assert torch.equal((raw["ray_any"] > 0).cpu()[None].to(torch.int8), ray_mask)
+    assert torch.equal(raw["sample_loc_w"][sel].cpu()[None], loc_w)
+    assert torch.equal(raw["sample_pidx"][sel].cpu()[None], pidx), "neighbour slots differ from the oracle"
+    assert np.array_equal(raw["grid"].hp["ranges"], ranges)
