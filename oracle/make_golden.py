@@ -6,6 +6,9 @@ TEST INFRASTRUCTURE (see oracle/__init__.py).  ``python -m oracle.make_golden`` 
   ray_march_ref.npz   ray_march (models/rendering/diff_ray_marching.py:509-555) outputs + gradients
   querier_ref.npz     lighting_fast_querier kernels (the reference's CUDA string host-compiled by oracle/build_ref.py,
                       canonical ascending-thread schedule) on the seeded ``tiny`` scene
+  frustum_{dtu,crop}_ref.npz  the perspective-frustum lighting_fast_querier (query_point_indices.py) the same way, through
+                      oracle/frustum_ref.py, on synthetic.frustum_case(...)   (``python -m oracle.make_golden frustum`` writes
+                      only these)
 """
 import copy
 import os
@@ -17,7 +20,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from oracle import build_ref, querier_ref as qr, ref_import  # noqa: E402
+from oracle import build_ref, frustum_ref as fr, querier_ref as qr, ref_import, torch_port as tp  # noqa: E402
 from pointnerf_b200 import synthetic as syn  # noqa: E402
 from pointnerf_b200.options import make_opt  # noqa: E402
 
@@ -88,11 +91,33 @@ def querier():
                         occ_numpnts=ex["grid"]["occ_numpnts"][:n_occ])
 
 
+def frustum():
+    build_ref.build()
+    for name in syn.FRUSTUM_CASES:
+        opt, xyz, cam, pix = syn.frustum_case(name)
+        xyz_pers = tp.w2pers_points(xyz, cam["camrotc2w"], cam["campos"])
+        opt.is_train = 0
+        pidx, loc, loc_w, dirs, ray_mask, vsize, ranges = fr.query_points(
+            opt, pix, xyz_pers, cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"], cam["campos"], cam["camrotc2w"])
+        opt.is_train = 1
+        u = torch.rand(loc.shape[:3], generator=torch.Generator().manual_seed(5))
+        jit = fr.query_points(opt, pix, xyz_pers, cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"], cam["campos"],
+                              cam["camrotc2w"], uniform=u)
+        np.savez_compressed(os.path.join(OUT, "frustum_%s_ref.npz" % name), xyz_pers=xyz_pers.numpy(), pixel_idx=pix.numpy(),
+                            sample_pidx=pidx.numpy(), sample_loc=loc.numpy(), sample_loc_w=loc_w.numpy(), ray_dirs=dirs.numpy(),
+                            ray_mask=ray_mask.numpy(), vsize=vsize, ranges=ranges, uniform=u.numpy(),
+                            jitter_sample_loc=jit[1].numpy(), jitter_sample_loc_w=jit[2].numpy())
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["frustum"]:
+        frustum()
+        sys.exit(0)
     aggregator()
     aggregator("aggregator_order1_ref.npz", F=63, agg_intrp_order=1)      # the DTU feed-forward configuration (63-d features)
     ray_march()
     querier()
+    frustum()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -1,5 +1,6 @@
 // Host stand-in for <cuda_runtime.h>: just enough of the CUDA dialect for the six kernels of
-// models/neural_points/query_point_indices_worldcoords.py:114-530 to compile with g++ and run
+// models/neural_points/query_point_indices_worldcoords.py:114-530 and the five of query_point_indices.py:135-600
+// (the perspective-frustum querier) to compile with g++ and run
 // one "thread" at a time.  Atomics are plain read-modify-write because execution is serial
 // (ascending global thread index = the canonical schedule of DESIGN.md).
 #pragma once
@@ -26,6 +27,8 @@ static inline unsigned long long atomicCAS(unsigned long long* p, unsigned long 
 static inline int atomicAdd(int* p, int v) { int o = *p; *p = o + v; return o; }
 static inline unsigned int atomicAdd(unsigned int* p, unsigned int v) { unsigned int o = *p; *p = o + v; return o; }
 static inline unsigned int atomicSub(unsigned int* p, unsigned int v) { unsigned int o = *p; *p = o - v; return o; }
+static inline int atomicMin(int* p, int v) { int o = *p; if (v < o) *p = v; return o; }
+static inline int atomicMax(int* p, int v) { int o = *p; if (v > o) *p = v; return o; }
 
 static inline unsigned int __byte_perm(unsigned int x, unsigned int y, unsigned int s) {
     unsigned long long src = ((unsigned long long)y << 32) | x; unsigned int r = 0;

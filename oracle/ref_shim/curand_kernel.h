@@ -36,4 +36,16 @@ static inline pn_gfloat operator+(pn_gprod p, pn_gprod q) { return pn_gfloat(fma
 static inline pn_gfloat operator+(pn_gfloat s, pn_gprod q) { return pn_gfloat(fmaf(q.a, q.b, s.v)); }
 static inline pn_gfloat operator+(pn_gprod p, pn_gfloat s) { return pn_gfloat(fmaf(p.a, p.b, s.v)); }
 
+// The frustum querier (query_point_indices.py:532-553) adds: int * float (voxel index times voxel size, contracted into the
+// following add), (int + 0.5) * float evaluated in double and contracted into a double fma with the float partial sum, a
+// difference of two products that nvcc leaves as mul, mul, sub, and a ?: whose arms must have one type (so float - float
+// is declared to return the wrapper).  All checked against `nvcc -arch=sm_100a -ptx` of the kernel string, CUDA 12.9.
+struct pn_gdprod { double a, b; };
+static inline pn_gprod operator*(int a, pn_gfloat b) { return pn_gprod{(float)a, b.v}; }
+static inline pn_gdprod operator*(double a, pn_gfloat b) { return pn_gdprod{a, (double)b.v}; }
+static inline double operator+(pn_gfloat s, pn_gdprod q) { return fma(q.a, q.b, (double)s.v); }
+static inline pn_gfloat operator-(pn_gfloat a, pn_gfloat b) { return pn_gfloat(a.v - b.v); }
+static inline pn_gfloat operator-(pn_gprod p, pn_gprod q) { return pn_gfloat(p.a * p.b - q.a * q.b); }
+static inline bool operator<=(pn_gprod p, pn_gfloat s) { return p.a * p.b <= s.v; }   // only query_rand_along_ray (:416-492, not a parity target)
+
 #define float pn_gfloat

@@ -23,7 +23,7 @@ _LEGO = dict(
     kernel_size=(3, 3, 3), query_size=(3, 3, 3),
     ranges=(-0.638, -1.141, -0.346, 0.634, 1.149, 1.141),
     z_depth_dim=400, radius_limit_scale=4.0, depth_limit_scale=0.0,
-    wcoord_query=1, inverse=0, gpu_maxthr=1024, is_train=0,
+    wcoord_query=1, inverse=0, gpu_maxthr=1024, is_train=0, shpnt_jitter="uniform",
     point_features_dim=32, xyz_grad=0, feat_grad=1, conf_grad=1, dir_grad=1, color_grad=1,
     load_points=0, feature_init_method="rand", default_conf=0.15,
     # ---- aggregator (point_aggregators.py:15-217)

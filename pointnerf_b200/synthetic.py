@@ -248,3 +248,32 @@ def random_pixels(cam, n, seed=0):
 def all_pixels(cam):
     ys, xs = np.meshgrid(np.arange(cam["h"]), np.arange(cam["w"]), indexing="ij")
     return np.stack([xs.reshape(-1), ys.reshape(-1)], axis=1)
+
+
+# ---- perspective-frustum querier cases: the "tiny" cloud seen through two cameras ------------------
+FRUSTUM_CASES = {
+    # the 63-channel DTU feed-forward settings (dev_scripts/ete/dtu_dgt_d012_img0123_conf_color_dir_agg2.sh:39-46) in small
+    "dtu": dict(opt=dict(vscale=(2, 2, 1), kernel_size=(3, 3, 3), query_size=(3, 3, 3), SR=24, K=8, P=20, NN=2,
+                         radius_limit_scale=0.0, depth_limit_scale=0.0, z_depth_dim=96), crop=None, n_pix=500),
+    # a cropped view: the left / top / near faces of the frustum cut through the cloud (points up to one voxel below a low
+    # face are filed by truncation), odd vscale, radius + depth limits, perspective-space distances, SR < occupied depths
+    "crop": dict(opt=dict(vscale=(3, 2, 2), kernel_size=(5, 5, 3), query_size=(5, 5, 3), SR=6, K=4, P=48, NN=1,
+                          radius_limit_scale=3.0, depth_limit_scale=2.0, z_depth_dim=64), crop=(17, 11, 40, 30, 0.6, 0.8),
+                 n_pix=None),
+}
+
+
+def frustum_case(name):
+    """-> opt, xyz_w [N,3], cam dict, pixel_idx int32 [1,R,2] for a perspective-querier parity case."""
+    c = FRUSTUM_CASES[name]
+    opt = config_opt("tiny", wcoord_query=0, max_o=None, **c["opt"])
+    _, tables = make_scene("tiny")
+    cam = make_camera("tiny")
+    if c["crop"] is not None:
+        x0, y0, w, h, near, far = c["crop"]
+        K = cam["intrinsic"].copy()
+        K[0, 2] -= x0
+        K[1, 2] -= y0
+        cam = dict(cam, intrinsic=K, w=w, h=h, near=near, far=far)
+    pix = all_pixels(cam) if c["n_pix"] is None else random_pixels(cam, c["n_pix"])
+    return opt, tables["xyz"], cam, torch.as_tensor(pix, dtype=torch.int32)[None]

@@ -240,3 +240,53 @@ def test_probe_restatement_against_per_ray_loop():
     mask = torch.tensor([[1, 0, 1, 1, 0, 1, 1, 1, 0, 1]], dtype=torch.int8)
     full = mp.unmask(mask, {"a": out["shading_avg_color"]})["a"]
     assert full.shape == (1, 10, 3) and bool((full[0, 1] == 0).all()) and torch.equal(full[0, 2], out["shading_avg_color"][0, 1])
+
+
+# ---- perspective-frustum querier -------------------------------------------------------------------
+def _frustum_inputs(name):
+    from oracle import frustum_ref as fr
+    opt, xyz, cam, pix = syn.frustum_case(name)
+    xyz_pers = tp.w2pers_points(xyz, cam["camrotc2w"], cam["campos"])
+    hp = fr.get_hyperparameters(opt, cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"])
+    return opt, cam, pix, xyz_pers, hp
+
+
+@pytest.mark.parametrize("name", ["dtu", "crop"])
+def test_golden_frustum_querier(name):
+    """The reference's own four kernels (host-compiled, canonical schedule) still give the committed vectors."""
+    from oracle import frustum_ref as fr
+    if not fr.available():
+        pytest.skip("oracle/_ref/libpn_ref_querier_frustum.so not built")
+    g = np.load(os.path.join(GOLDEN, "frustum_%s_ref.npz" % name))
+    opt, cam, pix, xyz_pers, hp = _frustum_inputs(name)
+    assert np.array_equal(xyz_pers.numpy(), g["xyz_pers"]) and np.array_equal(pix.numpy(), g["pixel_idx"])
+    out = fr.query_points(opt, pix, xyz_pers, cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"], cam["campos"],
+                          cam["camrotc2w"])
+    assert np.array_equal(out[0].numpy(), g["sample_pidx"]) and np.array_equal(out[1].numpy(), g["sample_loc"])
+    assert np.array_equal(out[4].numpy(), g["ray_mask"]) and np.array_equal(out[2].numpy(), g["sample_loc_w"])
+    assert np.array_equal(out[6], g["ranges"]) and np.array_equal(out[5], g["vsize"])
+
+
+@pytest.mark.parametrize("name", ["dtu", "crop"])
+def test_frustum_csr_formulation_equals_reference_tables(name):
+    """The product's data structure (one CSR over claimed cells, (int)-truncated membership, bitset column walk - restated in
+    numpy by oracle/frustum_model.py) reproduces the reference's dense tables / per-column buckets: neighbour indices,
+    slot arrangement, sample centres and ray mask bit for bit against the golden vectors."""
+    from oracle import frustum_model as fm
+    g = np.load(os.path.join(GOLDEN, "frustum_%s_ref.npz" % name))
+    opt, cam, pix, xyz_pers, hp = _frustum_inputs(name)
+    xp, px = xyz_pers.reshape(-1, 3).numpy(), pix[0].numpy()
+    cells, occ, dims = fm.build(xp, hp)
+    sz, mask = fm.sample(px, occ, dims, hp["vscale"], opt.SR)
+    assert np.array_equal(mask, g["ray_mask"][0])
+    sel = mask > 0
+    pidx, loc = fm.knn(xp, cells, dims, hp, px[sel], sz[sel], opt)
+    assert np.array_equal(pidx, g["sample_pidx"][0]) and np.array_equal(loc, g["sample_loc"][0])
+    if name == "crop":
+        # the case must expose the truncation rule of insert_vox_points (:394-399): a floor()-only grid gives other neighbours
+        t = (xp - hp["ranges"][:3][None]) / hp["scaled_vsize"][None]
+        assert int(((t > -1) & (t < 0)).any(1).sum()) > 100
+        keep = np.all(np.floor(t) >= 0, axis=1)
+        cells_f, _, _ = fm.build(np.where(keep[:, None], xp, np.float32(1e9)), hp)
+        assert not np.array_equal(fm.knn(xp, cells_f, dims, hp, px[sel], sz[sel], opt)[0], pidx)
+        assert int((sz >= 0).sum(1).max()) == opt.SR
