@@ -152,6 +152,50 @@ int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* 
                  float radius_limit2, int32_t* sample_pidx, int32_t* ray_any,
                  unsigned long long* n_candidates, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * 3b. Perspective-frustum querier  (replaces get_occ_vox :265-314, near_vox_full :316-365,
+ *     insert_vox_points :368-413, query_neigh_along_ray_layered :495-600 and the fills / cumsum / launches of
+ *     query_grid_point_index :617-786 of models/neural_points/query_point_indices.py - `wcoord_query = 0`)
+ *
+ * The grid lives in the camera's perspective space (x/z, y/z, z): dims = ceil([w, h, z_depth_dim] / vscale), rebuilt for
+ * every view.  Same CSR representation as section 1 (pn_grid_params: shift = ranges[:3], vsize = scaled voxel size,
+ * dilate = query_size), with the two rules of this querier: occupancy comes from floor() voxel coordinates (:290-297),
+ * bucket membership from (int) truncation (:394-399) restricted to voxels that hold a floor()-valid point.  The
+ * reference's per-column slot table ([w, h, max_o] buckets of the voxels "needed" by this batch's rays, :697-727) is
+ * replaced by the CSR over all claimed voxels; that is equivalent whenever query_size covers the cube the query visits
+ * (query_size[0], [1] >= kernel_size[0] and query_size[2] >= kernel_size[2]; the host class refuses anything else,
+ * because the reference's result then depends on which other rays are in the batch).  Buckets are the first P points
+ * by index (the reference: arrival order, then a time-seeded reservoir); `inverse` (disparity-linear z) is not offered.
+ *   pixel_idx  int32[R,2]  (x, y) of every ray
+ *   sample_z   int32[R,SR] depth-voxel index of the kept samples (first SR occupied depths of the ray's column), -1 unused
+ *   hit_count  int32[R]    kept samples
+ *   ray_mask   int32[R]    the reference's `far_id > 0` (:339)
+ *   sample_loc float[R,SR,3] perspective coordinates of the sample centres, written for every slot as :532-540
+ *   sample_pidx int32[R,SR,K], -1 = empty
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct pn_frustum_query {
+    float ray_vsize[2];   /* scaled voxel size / vscale, x and y (:707)                          */
+    int32_t vscale[2];    /* opt.vscale x and y                                                  */
+    float radius_limit2;  /* (radius_limit_scale * max(vsize_x, vsize_y))^2, 0 = off (:571)      */
+    float depth_limit2;   /* (depth_limit_scale * vsize_z)^2, 0 = off                            */
+    int32_t n_layers;     /* (kernel_size[0]+1)/2 (:548)                                         */
+    int32_t z_layers;     /* (kernel_size[2]+1)/2 (:549)                                         */
+    int32_t nn;           /* opt.NN: 1 = distances in perspective space, >= 2 = x, y scaled by z */
+} pn_frustum_query;
+
+int64_t pn_frustum_grid_workspace_bytes(int64_t n_points, int64_t n_cells);
+int pn_frustum_grid_build(const float* xyz_pers, int64_t n_points, const pn_grid_params* params, int32_t* cell_start,
+                          int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info, void* workspace,
+                          int64_t workspace_bytes, void* stream);
+/* vscale_xy: HOST int32[2] */
+int pn_frustum_sample(const int32_t* pixel_idx, int64_t n_rays, int32_t SR, const pn_grid_params* params,
+                      const int32_t* vscale_xy, const uint32_t* occ_bits, int32_t* sample_z, int32_t* hit_count,
+                      int32_t* ray_mask, void* stream);
+int pn_frustum_knn_query(const float* xyz_pers, const pn_grid_params* params, const pn_frustum_query* q,
+                         const int32_t* cell_start, const int32_t* bucket_pidx, const int32_t* pixel_idx,
+                         const int32_t* sample_z, const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K,
+                         int32_t* sample_pidx, float* sample_loc, unsigned long long* n_candidates, void* stream);
+
 /* Camera-frame "perspective" coordinates (x/z, y/z, z) of world positions
  * (w2pers: worldcoords.py:102-109 for samples, neural_points.py:687-693 for points).
  * camrot = camrotc2w row-major 3x3, campos 3 floats, both on the device. */

@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -23,6 +23,11 @@ GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, G
 class GridParams(Structure):
     _fields_ = [("shift", c_float * 3), ("vsize", c_float * 3), ("dims", c_int32 * 3), ("dilate", c_int32 * 3),
                 ("P", c_int32), ("max_o", c_int32)]
+
+
+class FrustumQuery(Structure):
+    _fields_ = [("ray_vsize", c_float * 2), ("vscale", c_int32 * 2), ("radius_limit2", c_float), ("depth_limit2", c_float),
+                ("n_layers", c_int32), ("z_layers", c_int32), ("nn", c_int32)]
 
 
 class AggParams(Structure):
@@ -91,6 +96,11 @@ def _declare(lib):
         "pn_ray_sample": (c_int, [P, P, P, c_int64, c_int64, c_int32, c_int32, POINTER(GridParams), P, P, P, P, P]),
         "pn_knn_query": (c_int, [P, POINTER(GridParams), P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float,
                                  P, P, P, P]),
+        "pn_frustum_grid_workspace_bytes": (c_int64, [c_int64, c_int64]),
+        "pn_frustum_grid_build": (c_int, [P, c_int64, POINTER(GridParams), P, P, P, P, P, c_int64, P]),
+        "pn_frustum_sample": (c_int, [P, c_int64, c_int32, POINTER(GridParams), POINTER(c_int32), P, P, P, P, P]),
+        "pn_frustum_knn_query": (c_int, [P, POINTER(GridParams), POINTER(FrustumQuery), P, P, P, P, P, c_int64, c_int32,
+                                         c_int32, P, P, P, P]),
         "pn_w2pers": (c_int, [P, c_int64, P, P, P, P]),
         "pn_compact_workspace_bytes": (c_int64, [c_int64]),
         "pn_compact_samples": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, c_int64, P]),

@@ -45,14 +45,40 @@ __device__ __forceinline__ int cell_index(const GridDev& g, float x, float y, fl
 }
 
 // 3 consecutive floats per point; a warp reads 384 contiguous bytes (coalesced through L1)
+// Frustum grids (query_point_indices.py): get_occ_vox (:290-297) takes floor() of the scaled coordinate, insert_vox_points
+// (:394-399) converts it with (int), i.e. toward zero - a point up to one voxel below a low face of the grid is not a
+// source of occupancy but IS filed into the boundary voxel, provided that voxel was claimed by a floor()-valid point
+// (only claimed voxels get a bucket, :345-349, :400).  So: a first pass sets `src_bits` for the cells that hold a
+// floor()-valid point, and bucket membership follows the (int) rule restricted to those cells.
+__device__ __forceinline__ int cell_index_trunc(const GridDev& g, float x, float y, float z) {
+    float tx = __fdiv_rn(__fsub_rn(x, g.sx), g.vx), ty = __fdiv_rn(__fsub_rn(y, g.sy), g.vy), tz = __fdiv_rn(__fsub_rn(z, g.sz), g.vz);
+    int cx = (int)tx, cy = (int)ty, cz = (int)tz;
+    if (cx < 0 || cx >= g.dx || cy < 0 || cy >= g.dy || cz < 0 || cz >= g.dz) return -1;
+    return (cx * g.dy + cy) * g.dz + cz;
+}
+
+__global__ void __launch_bounds__(256) grid_mark_src_kernel(const float* __restrict__ xyz, int n, GridDev g,
+                                                            unsigned* __restrict__ src_bits) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int cell = cell_index(g, xyz[3 * (int64_t)i], xyz[3 * (int64_t)i + 1], xyz[3 * (int64_t)i + 2]);
+    if (cell >= 0 && !((src_bits[cell >> 5] >> (cell & 31)) & 1u)) atomicOr(&src_bits[cell >> 5], 1u << (cell & 31));
+}
+
 __global__ void __launch_bounds__(256) grid_count_kernel(const float* __restrict__ xyz, int n, GridDev g,
                                                          int* __restrict__ cell_cnt, int* __restrict__ pt_cell,
-                                                         int* __restrict__ pt_rank, int* __restrict__ info) {
+                                                         int* __restrict__ pt_rank, int* __restrict__ info,
+                                                         const unsigned* __restrict__ src_bits) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     int cell = -1;
     if (i < n) {
         float x = xyz[3 * (int64_t)i], y = xyz[3 * (int64_t)i + 1], z = xyz[3 * (int64_t)i + 2];
-        cell = cell_index(g, x, y, z);
+        if (src_bits) {
+            cell = cell_index_trunc(g, x, y, z);
+            if (cell >= 0 && !((src_bits[cell >> 5] >> (cell & 31)) & 1u)) cell = -1;
+        } else {
+            cell = cell_index(g, x, y, z);
+        }
         pt_cell[i] = cell;
         pt_rank[i] = cell >= 0 ? atomicAdd(&cell_cnt[cell], 1) : 0;
     }
@@ -78,7 +104,7 @@ __global__ void __launch_bounds__(256) grid_place_kernel(int n, const int* __res
 __global__ void __launch_bounds__(256) grid_order_kernel(int n, const int* __restrict__ pt_cell,
                                                          const int* __restrict__ cell_start,
                                                          const int* __restrict__ tmp, int* __restrict__ bucket,
-                                                         int* __restrict__ info) {
+                                                         int* __restrict__ info, int slot0_quirk) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     int cell = pt_cell[i];
@@ -87,7 +113,7 @@ __global__ void __launch_bounds__(256) grid_order_kernel(int n, const int* __res
     int smaller = 0;
     for (int j = s; j < e; ++j) smaller += (tmp[j] < i);
     bucket[s + smaller] = i;
-    if (i == info[PN_GI_FIRST_POINT]) info[PN_GI_SLOT0_CELL] = cell;  // the reference's slot-0 voxel (:372)
+    if (slot0_quirk && i == info[PN_GI_FIRST_POINT]) info[PN_GI_SLOT0_CELL] = cell;  // the reference's slot-0 voxel (:372)
 }
 
 __global__ void __launch_bounds__(256) grid_dilate_kernel(GridDev g, int64_t n_cells, const int* __restrict__ cell_start,
@@ -143,16 +169,21 @@ extern "C" int64_t pn_grid_workspace_bytes(int64_t n_points, int64_t n_cells) {
     return 3 * align_up(n * 4, 256) + align_up(scan_scratch_elems_i32(n_cells + 1) * 4, 256) + 256;
 }
 
-extern "C" int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_params* params, int32_t* cell_start,
-                             int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info, void* workspace,
-                             int64_t workspace_bytes, void* stream) {
+extern "C" int64_t pn_frustum_grid_workspace_bytes(int64_t n_points, int64_t n_cells) {
+    return pn_grid_workspace_bytes(n_points, n_cells) + align_up(cdiv(n_cells, 32) * 4, 256);
+}
+
+static int grid_build_impl(const float* xyz, int64_t n_points, const pn_grid_params* params, int32_t* cell_start,
+                           int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info, void* workspace,
+                           int64_t workspace_bytes, void* stream, bool frustum) {
     PN_CHECK_ARG(params && cell_start && bucket_pidx && occ_bits && info, "pn_grid_build: null argument");
     PN_CHECK_ARG(n_points >= 0 && n_points < INT_MAX, "pn_grid_build: n_points out of range");
     int64_t V = (int64_t)params->dims[0] * params->dims[1] * params->dims[2];
     PN_CHECK_ARG(params->dims[0] > 0 && params->dims[1] > 0 && params->dims[2] > 0 && V < INT_MAX - 1,
                  "pn_grid_build: grid of %lld cells unsupported (dims %d %d %d)", (long long)V, params->dims[0],
                  params->dims[1], params->dims[2]);
-    PN_CHECK_ARG(workspace_bytes >= pn_grid_workspace_bytes(n_points, V), "pn_grid_build: workspace too small");
+    PN_CHECK_ARG(workspace_bytes >= (frustum ? pn_frustum_grid_workspace_bytes(n_points, V) : pn_grid_workspace_bytes(n_points, V)),
+                 "pn_grid_build: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
     GridDev g = to_dev(params);
     int n = (int)n_points;
@@ -161,13 +192,22 @@ extern "C" int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_p
     int* pt_rank = ws.take<int>(n > 0 ? n : 1);
     int* tmp = ws.take<int>(n > 0 ? n : 1);
     int* scratch = ws.take<int>(scan_scratch_elems_i32(V + 1));
+    unsigned* src_bits = nullptr;
+    if (frustum) {
+        src_bits = ws.take<unsigned>(cdiv(V, 32));
+        PN_CUDA(cudaMemsetAsync(src_bits, 0, cdiv(V, 32) * sizeof(unsigned), st));
+    }
 
     PN_CUDA(cudaMemsetAsync(cell_start, 0, (V + 1) * sizeof(int), st));
     PN_CUDA(cudaMemsetAsync(occ_bits, 0, cdiv(V, 32) * sizeof(unsigned), st));
     grid_init_info_kernel<<<1, 32, 0, st>>>(info);
     PN_LAUNCH_CHECK("grid_init_info");
+    if (n > 0 && frustum) {
+        grid_mark_src_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(xyz, n, g, src_bits);
+        PN_LAUNCH_CHECK("grid_mark_src");
+    }
     if (n > 0) {
-        grid_count_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(xyz, n, g, cell_start, pt_cell, pt_rank, info);
+        grid_count_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(xyz, n, g, cell_start, pt_cell, pt_rank, info, src_bits);
         PN_LAUNCH_CHECK("grid_count");
     }
     int rc = scan_exclusive_i32(cell_start, cell_start, V, true, scratch, st);
@@ -175,7 +215,7 @@ extern "C" int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_p
     if (n > 0) {
         grid_place_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, pt_cell, pt_rank, cell_start, tmp);
         PN_LAUNCH_CHECK("grid_place");
-        grid_order_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, pt_cell, cell_start, tmp, bucket_pidx, info);
+        grid_order_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, pt_cell, cell_start, tmp, bucket_pidx, info, frustum ? 0 : 1);
         PN_LAUNCH_CHECK("grid_order");
     }
     grid_dilate_kernel<<<(unsigned)cdiv(V, 256), 256, 0, st>>>(g, V, cell_start, occ_bits, info);
@@ -183,4 +223,16 @@ extern "C" int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_p
     grid_finish_kernel<<<1, 1, 0, st>>>(g, info);
     PN_LAUNCH_CHECK("grid_finish");
     return PN_OK;
+}
+
+extern "C" int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_params* params, int32_t* cell_start,
+                             int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info, void* workspace,
+                             int64_t workspace_bytes, void* stream) {
+    return grid_build_impl(xyz, n_points, params, cell_start, bucket_pidx, occ_bits, info, workspace, workspace_bytes, stream, false);
+}
+
+extern "C" int pn_frustum_grid_build(const float* xyz_pers, int64_t n_points, const pn_grid_params* params, int32_t* cell_start,
+                                     int32_t* bucket_pidx, uint32_t* occ_bits, int32_t* info, void* workspace,
+                                     int64_t workspace_bytes, void* stream) {
+    return grid_build_impl(xyz_pers, n_points, params, cell_start, bucket_pidx, occ_bits, info, workspace, workspace_bytes, stream, true);
 }

@@ -76,6 +76,59 @@ __global__ void __launch_bounds__(256) ray_sample_kernel(const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------------------
+// Frustum sampling (perspective grid, query_point_indices.py).  One warp per ray walks the z column of the ray's
+// (pixel / vscale) frustum cell through the dilated occupancy bitset, 32 depths per step, and keeps the first SR occupied
+// depth indices - what near_vox_full (:316-365) stores per column in voxel_to_coorz_idx; ray_mask is its `far_id > 0`
+// (:339: the deepest occupied index must be positive, so a column occupied only at depth 0 is masked out).
+// Algorithmic bytes: 8R (pixels) + R*dz/8 (bits) + 4 R*SR (depth ids out) + 8R.
+// ------------------------------------------------------------------------------------------------
+struct FrustumArgs {
+    const int* pixel_idx;   // [R,2] (x, y)
+    const int* sample_z;    // [R,SR] depth index of every kept sample, -1 unused
+    float* sample_loc;      // [R,SR,3] perspective coordinates of the sample centres (written for every slot, :532-540)
+    float rvx, rvy;         // ray voxel size: scaled voxel size / vscale (:707)
+    float depth_limit2;
+    int vsx, vsy;           // vscale
+    int nn;                 // opt.NN
+    int z_layers;           // (kernel_size[2]+1)/2
+};
+
+__global__ void __launch_bounds__(256) frustum_sample_kernel(const int* __restrict__ pixel_idx, int64_t n_rays, int SR, QGrid g,
+                                                             int vsx, int vsy, const unsigned* __restrict__ occ_bits,
+                                                             int* __restrict__ sample_z, int* __restrict__ hit_count,
+                                                             int* __restrict__ ray_mask) {
+    int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (ray >= n_rays) return;
+    int cx = pixel_idx[2 * ray] / vsx, cy = pixel_idx[2 * ray + 1] / vsy;
+    int* out = sample_z + ray * SR;
+    int kept = 0;
+    bool deep = false;   // an occupied depth index > 0 exists
+    if (cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy) {
+        const int64_t base = ((int64_t)cx * g.dy + cy) * g.dz;
+        for (int z0 = 0; z0 < g.dz && (kept < SR || !deep); z0 += 32) {
+            int z = z0 + lane;
+            bool hit = false;
+            if (z < g.dz) {
+                int64_t b = base + z;
+                hit = (occ_bits[b >> 5] >> (b & 31)) & 1u;
+            }
+            unsigned m = __ballot_sync(kFull, hit);
+            int slot = kept + __popc(m & ((1u << lane) - 1u));
+            if (hit && slot < SR) out[slot] = z;
+            kept += __popc(m);
+            deep |= (z0 == 0 ? (m & ~1u) : m) != 0u;
+        }
+    }
+    kept = min(kept, SR);
+    for (int s = kept + lane; s < SR; s += 32) out[s] = -1;
+    if (lane == 0) {
+        hit_count[ray] = kept;
+        ray_mask[ray] = deep ? 1 : 0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Neighbour query.  One warp per (ray, slot).  Per layer the (2l+1)^3 cube is enumerated in x,y,z
 // order 32 cells at a time: each lane fetches one cell's [start, end) (non-ring / out-of-grid cells
 // count 0), a warp prefix sum lays the cells' buckets out as one candidate sequence in the
@@ -85,25 +138,45 @@ __global__ void __launch_bounds__(256) ray_sample_kernel(const float* __restrict
 // slot k - so the slot arrangement, the strict-'<' replacement rule and the first-maximum rescan are
 // reproduced exactly.  Algorithmic bytes: S_q*(12 + 27*8) + 16*Cand + 4*S_q*K.
 // ------------------------------------------------------------------------------------------------
-template <bool kCount>
+//
+// kFrustum = true is the perspective-grid variant (query_point_indices.py:495-600): the query centre comes from the ray's
+// pixel and the sample's depth index (:532-536: float partial sums, the half-voxel offsets in double), the cube is
+// (2l+1)^2 x (2*min(l, z_layers-1)+1) with the visit rule of :555, distances are taken in perspective coordinates (NN < 2) or
+// after multiplying x and y by z (NN >= 2, :565-566), the radius limit applies to the xy part and a separate depth limit
+// to the z part (:571), there is no early exit between layers, and the sample centre is written out for every slot.
+template <bool kCount, bool kFrustum>
 __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz, QGrid g, const int* __restrict__ cell_start,
                                                   const int* __restrict__ bucket, const int* __restrict__ grid_info,
                                                   const float* __restrict__ loc_w, const int* __restrict__ hit_count,
                                                   int64_t n_rays, int SR, int K, int n_layers, float r2,
                                                   int* __restrict__ sample_pidx, int* __restrict__ ray_any,
-                                                  unsigned long long* __restrict__ n_cand) {
+                                                  unsigned long long* __restrict__ n_cand, FrustumArgs fa) {
     // one block per ray: its warps take the hit slots round-robin, then the block blanks the unused slots
     const int64_t ray = blockIdx.x;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int hits = min(hit_count[ray], SR);
     for (int i = hits * K + (int)threadIdx.x; i < SR * K; i += blockDim.x) sample_pidx[ray * SR * K + i] = -1;
     bool any_seen = false;
-    for (int slot = wib; slot < hits; slot += nw) {
+    // frustum: every slot of the ray (kept or not) gets its centre written, so the loop covers all SR slots
+    for (int slot = wib; slot < (kFrustum ? SR : hits); slot += nw) {
     const int64_t w = ray * SR + slot;
     int* out = sample_pidx + w * K;
-    float qx = loc_w[3 * w], qy = loc_w[3 * w + 1], qz = loc_w[3 * w + 2];
-    int fx = voxel_coord(qx, g.sx, g.vx), fy = voxel_coord(qy, g.sy, g.vy), fz = voxel_coord(qz, g.sz, g.vz);
-    int slot0_cell = grid_info[PN_GI_SLOT0_CELL];
+    float qx, qy, qz, qxz = 0.f, qyz = 0.f;
+    int fx, fy, fz, slot0_cell = -1;
+    if (kFrustum) {
+        const int px = fa.pixel_idx[2 * ray], py = fa.pixel_idx[2 * ray + 1];
+        fx = px / fa.vsx; fy = py / fa.vsy; fz = fa.sample_z[w];
+        qx = __double2float_rn(__fma_rn((double)(px % fa.vsx) + 0.5, (double)fa.rvx, (double)__fmaf_rn(g.vx, (float)fx, g.sx)));
+        qy = __double2float_rn(__fma_rn((double)(py % fa.vsy) + 0.5, (double)fa.rvy, (double)__fmaf_rn(g.vy, (float)fy, g.sy)));
+        qz = __double2float_rn(__fma_rn((double)fz + 0.5, (double)g.vz, (double)g.sz));
+        if (lane == 0) { fa.sample_loc[3 * w] = qx; fa.sample_loc[3 * w + 1] = qy; fa.sample_loc[3 * w + 2] = qz; }
+        if (slot >= hits) continue;   // fz < 0 (:541); the block-wide fill above has blanked the indices
+        qxz = __fmul_rn(qz, qx); qyz = __fmul_rn(qz, qy);
+    } else {
+        qx = loc_w[3 * w]; qy = loc_w[3 * w + 1]; qz = loc_w[3 * w + 2];
+        fx = voxel_coord(qx, g.sx, g.vx); fy = voxel_coord(qy, g.sy, g.vy); fz = voxel_coord(qz, g.sz, g.vz);
+        slot0_cell = grid_info[PN_GI_SLOT0_CELL];
+    }
 
     // lane k (< K; K <= 32 per register set, larger K loops) keeps slot k
     // K up to 64 is supported with two slots per lane
@@ -114,16 +187,19 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
     unsigned long long visited = 0;
 
     for (int layer = 0; layer < n_layers; ++layer) {
-        int side = 2 * layer + 1, cube = side * side * side;
+        const int zlayer = kFrustum ? min(fa.z_layers - 1, layer) : layer;
+        int side = 2 * layer + 1, zside = 2 * zlayer + 1, cube = side * side * zside;
         for (int c0 = 0; c0 < cube; c0 += 32) {
             // --- one cell per lane
             int ci = c0 + lane, start = 0, cnt = 0;
             if (ci < cube) {
-                int ddx = ci / (side * side) - layer, rem = ci % (side * side);
-                int ddy = rem / side - layer, ddz = rem % side - layer;
-                int ring = max(abs(ddx), max(abs(ddy), abs(ddz)));
+                int ddx = ci / (side * zside) - layer, rem = ci % (side * zside);
+                int ddy = rem / zside - layer, ddz = rem % zside - zlayer;
+                bool visit;
+                if (kFrustum) visit = max(abs(ddx), abs(ddy)) == layer || (zlayer == layer && abs(ddz) == zlayer);   // :555
+                else visit = max(abs(ddx), max(abs(ddy), abs(ddz))) == layer;
                 int cx = fx + ddx, cy = fy + ddy, cz = fz + ddz;
-                if (ring == layer && cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz) {
+                if (visit && cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz) {
                     int cell = (cx * g.dy + cy) * g.dz + cz;
                     start = cell_start[cell];
                     cnt = min(cell_start[cell + 1] - start, g.P);
@@ -152,11 +228,22 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
                 float d2 = 0.f;
                 if (c < total) {
                     pid = bucket[o_start + (c - o_excl)];
-                    float x = __fsub_rn(xyz[3 * (int64_t)pid], qx);
-                    float y = __fsub_rn(xyz[3 * (int64_t)pid + 1], qy);
-                    float z = __fsub_rn(xyz[3 * (int64_t)pid + 2], qz);
-                    d2 = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
-                    in = (r2 == 0.f) || (d2 <= r2);
+                    if (kFrustum) {
+                        float px = xyz[3 * (int64_t)pid], py = xyz[3 * (int64_t)pid + 1], pz = xyz[3 * (int64_t)pid + 2];
+                        float x = fa.nn < 2 ? __fsub_rn(px, qx) : __fsub_rn(__fmul_rn(px, pz), qxz);
+                        float y = fa.nn < 2 ? __fsub_rn(py, qy) : __fsub_rn(__fmul_rn(py, pz), qyz);
+                        float xy2 = __fmaf_rn(x, x, __fmul_rn(y, y));
+                        float z = __fsub_rn(pz, qz);
+                        float z2 = __fmul_rn(z, z);
+                        d2 = __fadd_rn(xy2, z2);
+                        in = (r2 == 0.f || xy2 <= r2) && (fa.depth_limit2 == 0.f || z2 <= fa.depth_limit2);
+                    } else {
+                        float x = __fsub_rn(xyz[3 * (int64_t)pid], qx);
+                        float y = __fsub_rn(xyz[3 * (int64_t)pid + 1], qy);
+                        float z = __fsub_rn(xyz[3 * (int64_t)pid + 2], qz);
+                        d2 = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
+                        in = (r2 == 0.f) || (d2 <= r2);
+                    }
                 }
                 unsigned m = __ballot_sync(kFull, in);
                 while (m) {
@@ -194,13 +281,13 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
                 }
             }
         }
-        if (seen >= K) break;  // tested only after a whole layer (:526)
+        if (!kFrustum && seen >= K) break;  // tested only after a whole layer (:526); the frustum kernel has no such exit
     }
     for (int k = lane; k < K; k += 32) out[k] = my_pid[k >> 5];
     any_seen |= seen > 0;
     if (kCount && n_cand && lane == 0) atomicAdd(n_cand, visited);
     }
-    if (lane == 0 && any_seen) ray_any[ray] = 1;  // benign same-value race across the ray's warps
+    if (!kFrustum && lane == 0 && any_seen) ray_any[ray] = 1;  // benign same-value race across the ray's warps
 }
 
 __global__ void __launch_bounds__(256) w2pers_kernel(const float* __restrict__ xyz, int64_t n, const float* __restrict__ rot,
@@ -336,12 +423,53 @@ extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, cons
     // and 110 us instead of 74 us when the query runs alone)
     const int kKnnThreads = g_knn_threads;
     if (n_candidates)
-        knn_kernel<true><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
-                                                n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates);
+        knn_kernel<true, false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates, FrustumArgs{});
     else
-        knn_kernel<false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
-                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr);
+        knn_kernel<false, false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr, FrustumArgs{});
     PN_LAUNCH_CHECK("knn_query");
+    return PN_OK;
+}
+
+extern "C" int pn_frustum_sample(const int32_t* pixel_idx, int64_t n_rays, int32_t SR, const pn_grid_params* params,
+                                 const int32_t* vscale_xy, const uint32_t* occ_bits, int32_t* sample_z, int32_t* hit_count,
+                                 int32_t* ray_mask, void* stream) {
+    PN_CHECK_ARG(pixel_idx && params && vscale_xy && occ_bits && sample_z && hit_count && ray_mask, "pn_frustum_sample: null argument");
+    PN_CHECK_ARG(SR > 0 && vscale_xy[0] > 0 && vscale_xy[1] > 0, "pn_frustum_sample: bad SR / vscale");
+    if (n_rays <= 0) return PN_OK;
+    frustum_sample_kernel<<<(unsigned)cdiv(n_rays * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+        pixel_idx, n_rays, SR, to_q(params), vscale_xy[0], vscale_xy[1], occ_bits, sample_z, hit_count, ray_mask);
+    PN_LAUNCH_CHECK("frustum_sample");
+    return PN_OK;
+}
+
+extern "C" int pn_frustum_knn_query(const float* xyz_pers, const pn_grid_params* params, const pn_frustum_query* q,
+                                    const int32_t* cell_start, const int32_t* bucket_pidx, const int32_t* pixel_idx,
+                                    const int32_t* sample_z, const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K,
+                                    int32_t* sample_pidx, float* sample_loc, unsigned long long* n_candidates, void* stream) {
+    PN_CHECK_ARG(xyz_pers && params && q && cell_start && bucket_pidx && pixel_idx && sample_z && hit_count && sample_pidx && sample_loc,
+                 "pn_frustum_knn_query: null argument");
+    PN_CHECK_ARG(K >= 1 && K <= 64, "pn_frustum_knn_query: K=%d unsupported (1..64)", K);
+    PN_CHECK_ARG(q->n_layers >= 1 && q->n_layers <= 8 && q->z_layers >= 1, "pn_frustum_knn_query: n_layers=%d z_layers=%d unsupported",
+                 q->n_layers, q->z_layers);
+    PN_CHECK_ARG(q->vscale[0] > 0 && q->vscale[1] > 0 && q->nn >= 1, "pn_frustum_knn_query: bad vscale / NN");
+    if (n_rays <= 0) return PN_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    FrustumArgs fa;
+    fa.pixel_idx = pixel_idx; fa.sample_z = sample_z; fa.sample_loc = sample_loc;
+    fa.rvx = q->ray_vsize[0]; fa.rvy = q->ray_vsize[1];
+    fa.depth_limit2 = q->depth_limit2;
+    fa.vsx = q->vscale[0]; fa.vsy = q->vscale[1];
+    fa.nn = q->nn; fa.z_layers = q->z_layers;
+    unsigned blocks = (unsigned)n_rays;
+    if (n_candidates)
+        knn_kernel<true, true><<<blocks, 256, 0, st>>>(xyz_pers, to_q(params), cell_start, bucket_pidx, nullptr, nullptr, hit_count, n_rays,
+                                                       SR, K, q->n_layers, q->radius_limit2, sample_pidx, nullptr, n_candidates, fa);
+    else
+        knn_kernel<false, true><<<blocks, 256, 0, st>>>(xyz_pers, to_q(params), cell_start, bucket_pidx, nullptr, nullptr, hit_count, n_rays,
+                                                        SR, K, q->n_layers, q->radius_limit2, sample_pidx, nullptr, nullptr, fa);
+    PN_LAUNCH_CHECK("frustum_knn_query");
     return PN_OK;
 }
 
