@@ -11,7 +11,7 @@ from . import querier_ref, torch_port as tp
 
 
 def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend="port", uniform=None, need_grads=True,
-        loss_fn=None, dtype=torch.float32, kink_tau=None):
+        loss_fn=None, dtype=torch.float32, kink_tau=None, frustum_pix=None):
     """tables: dict from pointnerf_b200.synthetic.make_scene (torch-CPU); cam: make_camera; raydir [1,R,3];
     bg_color [C]; agg_state: state_dict of the aggregator (reference names).  loss = sum(coarse_raycolor * loss_weight)
     unless ``loss_fn(out)`` is given.  Returns the fill_invalid dictionary plus query intermediates and ``grads``.
@@ -23,7 +23,11 @@ def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend
     the reference evaluated in fp32 OR in fp64 (tests/_util.py).
 
     ``kink_tau``: additionally report ``out["kink_rays"]`` (bool [1,R_full]) - rays holding a sample with a hidden unit at
-    a LeakyReLU kink (oracle/kinks.py); gradient tests give those rays zero loss weight."""
+    a LeakyReLU kink (oracle/kinks.py); gradient tests give those rays zero loss weight.
+
+    ``frustum_pix`` (int32 [1,R,2]): query with the perspective-frustum querier (oracle/frustum_ref.py, wcoord_query = 0)
+    instead of the world-coordinate one; ``raydir`` is then unused (pers2w gives per-sample directions) and ``uniform`` is
+    the [1,R',SR] draw of its sample jitter."""
     dt = dtype
     xyz = tables["xyz"]
     leaves = {k: tables[k].clone().to(dt).requires_grad_(need_grads) for k in ("points_embeding", "points_conf", "points_dir", "points_color")}
@@ -32,8 +36,15 @@ def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend
     agg.load_state_dict({k: v.detach().cpu().clone() for k, v in agg_state.items()})
     agg = agg.to(dt)
 
-    (pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges), extras = querier_ref.query_points(
-        opt, xyz[None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend=backend, uniform=uniform)
+    if frustum_pix is not None:
+        from . import frustum_ref
+        pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges = frustum_ref.query_points(
+            opt, frustum_pix, tp.w2pers_points(xyz, cam["camrotc2w"], cam["campos"]), cam["h"], cam["w"], cam["intrinsic"],
+            cam["near"], cam["far"], cam["campos"], cam["camrotc2w"], uniform=uniform)
+        extras = {}
+    else:
+        (pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges), extras = querier_ref.query_points(
+            opt, xyz[None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend=backend, uniform=uniform)
     xyz_pers = tp.w2pers_points(xyz, cam["camrotc2w"], cam["campos"]).to(dt)   # fp32 arithmetic, as the inputs of the aggregator
     loc_pers, loc_w, dirs = loc_pers.to(dt), loc_w.to(dt), dirs.to(dt)
     g = tp.gather_point_tables(pidx, xyz.to(dt), xyz_pers, leaves["points_embeding"], leaves["points_color"], leaves["points_dir"],

@@ -23,7 +23,8 @@ import torch.nn as nn
 from . import _lib
 from . import query as _query
 from .aggregator import CompactSamples, PointAggregator, gather_clamp
-from .query import lighting_fast_querier
+from .query import lighting_fast_querier as lighting_fast_querier_w
+from .query_frustum import lighting_fast_querier as lighting_fast_querier_p
 from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march, ray_march_compact
 
 
@@ -31,19 +32,21 @@ class NeuralPoints(nn.Module):
     def __init__(self, num_channels, size, opt, device, checkpoint=None, feature_init_method='rand', reg_weight=0.,
                  feedforward=0):
         super().__init__()
-        if getattr(opt, "wcoord_query", 1) <= 0:
-            raise NotImplementedError("perspective-frustum querier (wcoord_query<=0) is outside the hot path (SURVEY.md 2 #3)")
         self.opt = opt
         self.device = device
         self.grid_vox_sz = 0
         self.points_conf = self.points_dir = self.points_color = None
         self.xyz = self.points_embeding = None
         self.Rw2c = nn.Parameter(torch.eye(3, device=device, dtype=torch.float32), requires_grad=False)
-        self.querier = lighting_fast_querier(device, opt)
+        # neural_points.py:329-331: query_size defaults to kernel_size; world-coordinate or perspective-frustum querier
+        if opt.query_size[0] == 0:
+            opt.query_size = opt.kernel_size
+        self.lighting_fast_querier = lighting_fast_querier_w if getattr(opt, "wcoord_query", 1) > 0 else lighting_fast_querier_p
+        self.querier = self.lighting_fast_querier(device, opt)
 
     def reset_querier(self):
         self.querier.clean_up()
-        self.querier = lighting_fast_querier(self.device, self.opt)
+        self.querier = self.lighting_fast_querier(self.device, self.opt)
 
     def set_points(self, points_xyz, points_embeding, points_color=None, points_dir=None, points_conf=None,
                    parameter=False, Rw2c=None, eulers=None):
@@ -148,8 +151,12 @@ class NeuralPoints(nn.Module):
     def forward(self, inputs):
         """neural_points.py:782-812 (reference seam): the 14-tuple of gathered [1,R'',SR,K,*] tensors."""
         camrotc2w, campos, near, far = inputs["camrotc2w"], inputs["campos"], inputs["near"], inputs["far"]
-        near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
-        far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
+        if getattr(self.opt, "wcoord_query", 1) > 0:
+            near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
+            far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
+        else:   # the frustum grid's voxel size is numpy arithmetic on these: tensors become 0-d arrays like :786
+            near = near if isinstance(near, (int, float)) else torch.as_tensor(near).min().cpu().numpy()
+            far = far if isinstance(far, (int, float)) else torch.as_tensor(far).max().cpu().numpy()
         pixel_idx = inputs.get("pixel_idx")
         sample_pidx, sample_loc, ray_mask_tensor, xyz_pers, sample_loc_w, sample_ray_dirs, vsize = self.get_point_indices(
             inputs, camrotc2w, campos, pixel_idx, near, far, inputs.get("h"), inputs.get("w"), inputs.get("intrinsic"))
@@ -246,6 +253,9 @@ class NeuralPointsRayMarching(nn.Module):
         consumes it; a training loop calls this for batch i+1 before the backward of batch i so that the (S, M)
         read-back the aggregator needs is complete long before it is waited for."""
         nps = self.neural_points
+        if getattr(self.opt, "wcoord_query", 1) <= 0:
+            raise NotImplementedError("the fused path is built on the world-coordinate querier; with wcoord_query = 0 use "
+                                      "forward_seams(...) (perspective-frustum querier + aggregator + ray_march seams)")
         near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
         far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
         xyz = nps.xyz.detach()
