@@ -1,5 +1,6 @@
 // Error state, launch counter and the device-wide scan used by the grid build and the work lists.
 #include <stdarg.h>
+#include <stdint.h>
 
 #include <atomic>
 
@@ -94,18 +95,42 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const T* in, T
     __shared__ T sm[32];
     // thread t owns kScanItems CONSECUTIVE elements so that one block scan suffices
     int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
-    T v[kScanItems];
+    // a thread's 8 elements are 32 / 64 contiguous bytes: moved as 16-byte vectors when the tile is whole and the
+    // pointers are aligned (element-wise loads touch 32 sectors per instruction and ran at a quarter of HBM speed)
+    constexpr int kVec = (int)(sizeof(T) * kScanItems / 16);
+    const bool vec = base + kScanItems <= n && (((uintptr_t)in | (uintptr_t)out) & 15) == 0;
+    union { uint4 q[kVec]; T v[kScanItems]; } u;
     T acc = 0;
+    if (vec) {
+        const uint4* src = reinterpret_cast<const uint4*>(in + base);
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        v[i] = (base + i < n) ? in[base + i] : (T)0;
-        acc += v[i];
+        for (int i = 0; i < kVec; ++i) u.q[i] = src[i];
+#pragma unroll
+        for (int i = 0; i < kScanItems; ++i) acc += u.v[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; ++i) {
+            u.v[i] = (base + i < n) ? in[base + i] : (T)0;
+            acc += u.v[i];
+        }
     }
     T off = block_scan_excl<T>(acc, (T*)nullptr, sm) + bsum[blockIdx.x];
+    if (vec) {
 #pragma unroll
-    for (int i = 0; i < kScanItems; ++i) {
-        if (base + i < n) out[base + i] = off;
-        off += v[i];
+        for (int i = 0; i < kScanItems; ++i) {
+            T t = u.v[i];
+            u.v[i] = off;
+            off += t;
+        }
+        uint4* dst = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+        for (int i = 0; i < kVec; ++i) dst[i] = u.q[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < kScanItems; ++i) {
+            if (base + i < n) out[base + i] = off;
+            off += u.v[i];
+        }
     }
 }
 

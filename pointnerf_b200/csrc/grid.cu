@@ -10,8 +10,8 @@
 //            arrival rank inside the cell (any permutation), warp-aggregated min of in-grid index
 //   scan   : exclusive prefix over the V+1 cell counters (pn::scan_exclusive_i32)
 //   place  : tmp[start[cell] + rank] = point
-//   order  : bucket[start + #{members < point}] = point   (ascending index inside each cell)
-//   dilate : one thread per cell, occupied cells OR their dilation box into the bitset
+//   order  : bucket[start + #{members < point}] = point   (ascending index inside each cell); the thread of a cell's
+//            first member ORs the cell's dilation box into the bitset
 //
 // All kernels are HBM/L2-bound integer work; algorithmic bytes: 12N (xyz) + 4N (bucket list)
 // + 4(V+1) (cell_start) + V/8 (bitset).
@@ -100,43 +100,41 @@ __global__ void __launch_bounds__(256) grid_place_kernel(int n, const int* __res
     if (cell >= 0) tmp[cell_start[cell] + pt_rank[i]] = i;
 }
 
-// ascending point index inside each cell: position = number of smaller members (cells are small)
-__global__ void __launch_bounds__(256) grid_order_kernel(int n, const int* __restrict__ pt_cell,
+// ascending point index inside each cell: position = number of smaller members (cells are small).  The thread of a
+// cell's lowest-index member also ORs the cell's dilation box into the occupancy bitset and feeds the statistics, so the
+// cost of the dilation follows the number of occupied cells (<= N), not the number of cells of the grid (a per-view
+// frustum grid has 16-33 M cells of which ~1 % are occupied).
+__global__ void __launch_bounds__(256) grid_order_kernel(int n, GridDev g, const int* __restrict__ pt_cell,
                                                          const int* __restrict__ cell_start,
                                                          const int* __restrict__ tmp, int* __restrict__ bucket,
-                                                         int* __restrict__ info, int slot0_quirk) {
+                                                         unsigned* __restrict__ occ_bits, int* __restrict__ info,
+                                                         int slot0_quirk) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int cell = pt_cell[i];
-    if (cell < 0) return;
-    int s = cell_start[cell], e = cell_start[cell + 1];
-    int smaller = 0;
-    for (int j = s; j < e; ++j) smaller += (tmp[j] < i);
-    bucket[s + smaller] = i;
-    if (slot0_quirk && i == info[PN_GI_FIRST_POINT]) info[PN_GI_SLOT0_CELL] = cell;  // the reference's slot-0 voxel (:372)
-}
-
-__global__ void __launch_bounds__(256) grid_dilate_kernel(GridDev g, int64_t n_cells, const int* __restrict__ cell_start,
-                                                          unsigned* __restrict__ occ_bits, int* __restrict__ info) {
-    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int cnt = 0;
-    if (c < n_cells) cnt = cell_start[c + 1] - cell_start[c];
-    if (cnt > 0) {
-        int cz = (int)(c % g.dz);
-        int64_t t = c / g.dz;
-        int cy = (int)(t % g.dy), cx = (int)(t / g.dy);
-        int x0 = max(0, cx - g.kx / 2), x1 = min(g.dx, cx + (g.kx + 1) / 2);
-        int y0 = max(0, cy - g.ky / 2), y1 = min(g.dy, cy + (g.ky + 1) / 2);
-        int z0 = max(0, cz - g.kz / 2), z1 = min(g.dz, cz + (g.kz + 1) / 2);
-        for (int x = x0; x < x1; ++x)
-            for (int y = y0; y < y1; ++y) {
-                int64_t row = ((int64_t)x * g.dy + y) * g.dz;
-                for (int z = z0; z < z1; ++z) {
-                    int64_t b = row + z;
-                    unsigned bit = 1u << (b & 31);
-                    if (!(occ_bits[b >> 5] & bit)) atomicOr(&occ_bits[b >> 5], bit);
+    int cell = i < n ? pt_cell[i] : -1;
+    int cnt = 0;   // > 0 only on the thread of the cell's first member
+    if (cell >= 0) {
+        int s = cell_start[cell], e = cell_start[cell + 1];
+        int smaller = 0;
+        for (int j = s; j < e; ++j) smaller += (tmp[j] < i);
+        bucket[s + smaller] = i;
+        if (slot0_quirk && i == info[PN_GI_FIRST_POINT]) info[PN_GI_SLOT0_CELL] = cell;  // the reference's slot-0 voxel (:372)
+        if (smaller == 0) {
+            cnt = e - s;
+            int cz = cell % g.dz, t = cell / g.dz;
+            int cy = t % g.dy, cx = t / g.dy;
+            int x0 = max(0, cx - g.kx / 2), x1 = min(g.dx, cx + (g.kx + 1) / 2);
+            int y0 = max(0, cy - g.ky / 2), y1 = min(g.dy, cy + (g.ky + 1) / 2);
+            int z0 = max(0, cz - g.kz / 2), z1 = min(g.dz, cz + (g.kz + 1) / 2);
+            for (int x = x0; x < x1; ++x)
+                for (int y = y0; y < y1; ++y) {
+                    int64_t row = ((int64_t)x * g.dy + y) * g.dz;
+                    for (int z = z0; z < z1; ++z) {
+                        int64_t b = row + z;
+                        unsigned bit = 1u << (b & 31);
+                        if (!(occ_bits[b >> 5] & bit)) atomicOr(&occ_bits[b >> 5], bit);
+                    }
                 }
-            }
+        }
     }
     // statistics: one atomic per warp
     unsigned occ = __ballot_sync(kFull, cnt > 0);
@@ -215,11 +213,10 @@ static int grid_build_impl(const float* xyz, int64_t n_points, const pn_grid_par
     if (n > 0) {
         grid_place_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, pt_cell, pt_rank, cell_start, tmp);
         PN_LAUNCH_CHECK("grid_place");
-        grid_order_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, pt_cell, cell_start, tmp, bucket_pidx, info, frustum ? 0 : 1);
+        grid_order_kernel<<<(unsigned)cdiv(n, 256), 256, 0, st>>>(n, g, pt_cell, cell_start, tmp, bucket_pidx, occ_bits, info,
+                                                                  frustum ? 0 : 1);
         PN_LAUNCH_CHECK("grid_order");
     }
-    grid_dilate_kernel<<<(unsigned)cdiv(V, 256), 256, 0, st>>>(g, V, cell_start, occ_bits, info);
-    PN_LAUNCH_CHECK("grid_dilate");
     grid_finish_kernel<<<1, 1, 0, st>>>(g, info);
     PN_LAUNCH_CHECK("grid_finish");
     return PN_OK;

@@ -75,7 +75,8 @@ def main():
     res["grid_build_ms"] = round(timed(lambda: q.query_raw(empty, xp_d, hp)), 4)
     V = int(np.prod(hp["scaled_vdim"]))
     N = int(xp_d.shape[0])
-    res["grid_build_algorithmic_bytes"] = 2 * 12 * N + 3 * 4 * (V + 1) + V // 8 + 3 * 4 * N
+    # points read twice (mark, count) + cell / rank / tmp / bucket lists; cell_start: memset, scan read twice + write; two bitsets
+    res["grid_build_algorithmic_bytes"] = 2 * 12 * N + 5 * 4 * N + 4 * 4 * (V + 1) + 2 * (V // 8)
     res["grid_build_GBps"] = round(res["grid_build_algorithmic_bytes"] / res["grid_build_ms"] / 1e6, 1)
     print(json.dumps(res))
 
