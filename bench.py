@@ -449,6 +449,71 @@ def maintenance_bench(model, opt, batch_dev, bg_dev, dev):
     return out
 
 
+def frustum_bench(dev):
+    """the perspective-frustum querier (wcoord_query = 0) on the DTU feed-forward settings
+    (dev_scripts/ete/dtu_dgt_d012_img0123_conf_color_dir_agg2.sh: vscale 2 2 1, kernel 3 3 3, SR 40, K 8, P 20, NN 2, no limits,
+    400 depth bins) over the cfg1 cloud (200 K points, 400x400 view): a 200x200x400 frustum grid rebuilt per call, (a) a
+    4096-ray batch, (b) the whole 160 000-pixel frame in one call.  The reference's own kernels (host-compiled, oracle/_ref,
+    one thread) run on the same inputs as the checker (results must be bit-identical) and as this row's CPU baseline."""
+    from oracle import frustum_ref as fr, torch_port as tp
+    from pointnerf_b200 import _lib, query_frustum, synthetic as syn
+
+    def timed(fn, warm=3, reps=10):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        for _ in range(reps):
+            fn()
+        ev[1].record()
+        torch.cuda.synchronize()
+        return ev[0].elapsed_time(ev[1]) / reps
+
+    opt = syn.config_opt("cfg1", wcoord_query=0, max_o=None, vscale=(2, 2, 1), kernel_size=(3, 3, 3), query_size=(3, 3, 3), SR=40,
+                         K=8, P=20, NN=2, radius_limit_scale=0.0, depth_limit_scale=0.0, z_depth_dim=400)
+    _, tables = syn.make_scene("cfg1")
+    cam = syn.make_camera("cfg1")
+    xp = tp.w2pers_points(tables["xyz"], cam["camrotc2w"], cam["campos"])
+    xp_d = xp.to(dev).reshape(-1, 3).contiguous()
+    q = query_frustum.lighting_fast_querier(dev, opt)
+    hp = q.get_hyperparameters(cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"])
+    res = {"workload": "frustum querier, DTU feed-forward settings on the cfg1 cloud: %d points, grid %s, SR=40 K=8 P=20 NN=2"
+           % (xp_d.shape[0], "x".join(str(int(v)) for v in hp["scaled_vdim"]))}
+    have_ref = fr.available()
+    for tag, pix in (("batch_4096", syn.random_pixels(cam, 4096)), ("frame_400x400", syn.all_pixels(cam))):
+        pix_d = torch.as_tensor(pix, dtype=torch.int32).to(dev).contiguous()
+        l0 = _lib.lib().pn_launch_count()
+        raw = q.query_raw(pix_d, xp_d, hp, count_candidates=True)
+        launches = _lib.lib().pn_launch_count() - l0
+        torch.cuda.synchronize()
+        R = int(pix.shape[0])
+        entry = {"rays": R, "rays_kept": int((raw["ray_mask"] > 0).sum()), "pairs": int((raw["sample_pidx"] >= 0).sum()),
+                 "candidates": int(raw["candidates"].item()), "launches": int(launches)}
+        if have_ref:
+            t0 = time.perf_counter()
+            pidx, sloc, _, mask = fr.query_grid_point_index(opt, hp, pix, xp.reshape(-1, 3).numpy())
+            cpu_s = time.perf_counter() - t0
+            sel = mask > 0
+            entry.update(bit_identical_to_reference_kernels=bool(
+                np.array_equal(raw["ray_mask"].cpu().numpy(), mask) and np.array_equal(raw["sample_pidx"].cpu().numpy()[sel], pidx)
+                and np.array_equal(raw["sample_loc"].cpu().numpy()[sel], sloc)),
+                cpu_reference_s=round(cpu_s, 4), cpu_rays_per_s=round(R / cpu_s, 1),
+                cpu_kind="reference kernels host-compiled (oracle/_ref), 1 thread")
+        ms_raw = timed(lambda: q.query_raw(pix_d, xp_d, hp))
+        ms_api = timed(lambda: q.query_points(pix_d[None], xp_d[None], None, None, cam["h"], cam["w"], cam["intrinsic"], cam["near"],
+                                              cam["far"], None, cam["campos"].to(dev), cam["camrotc2w"].to(dev)))
+        entry.update(gpu_ms_kernels=round(ms_raw, 4), gpu_ms_query_points=round(ms_api, 4), rays_per_s=round(R / ms_api * 1e3, 1))
+        res[tag] = entry
+    empty = torch.zeros((0, 2), dtype=torch.int32, device=dev)
+    res["grid_build_ms"] = round(timed(lambda: q.query_raw(empty, xp_d, hp)), 4)
+    V, N = int(np.prod(hp["scaled_vdim"])), int(xp_d.shape[0])
+    # points read twice (mark, count) + cell / rank / tmp / bucket lists; cell_start: memset, scan read twice + write; two bitsets
+    res["grid_build_algorithmic_bytes"] = 2 * 12 * N + 5 * 4 * N + 4 * 4 * (V + 1) + 2 * (V // 8)
+    res["grid_build_GBps"] = round(res["grid_build_algorithmic_bytes"] / res["grid_build_ms"] / 1e6, 1)
+    return res
+
+
 def psnr_vs_oracle(dev):
     """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
     oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
@@ -803,6 +868,14 @@ def main():
         _phase("maintenance kernels")
         maint = maintenance_bench(model, opt, dev_batches[0], bg_p.detach(), dev)
 
+    frustum = None
+    if rank == 0 and world == 1 and not args.no_sweep:
+        _phase("frustum querier (wcoord_query = 0)")
+        try:
+            frustum = frustum_bench(dev)
+        except Exception as e:   # an auxiliary row: report the failure in the line instead of losing the headline
+            frustum = {"error": repr(e)}
+
     # ---- cfg5 sweep (N = 1, after everything else: it prunes / grows the point cloud)
     sweep = None
     if rank == 0 and world == 1 and not args.no_sweep and not args.no_frame:
@@ -830,7 +903,7 @@ def main():
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, ("frame_%dx%d" % (frame["w"], frame["h"]) if frame else "frame_800x800"): frame,
-                "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint}
+                "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint, "frustum_querier_wcoord0": frustum}
         _emit(line)
     if world > 1:
         dist.barrier()
