@@ -167,7 +167,8 @@ int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* 
  * because the reference's result then depends on which other rays are in the batch).  Buckets are the first P points
  * by index (the reference: arrival order, then a time-seeded reservoir); `inverse` (disparity-linear z) is not offered.
  *   pixel_idx  int32[R,2]  (x, y) of every ray
- *   sample_z   int32[R,SR] depth-voxel index of the kept samples (first SR occupied depths of the ray's column), -1 unused
+ *   sample_z   int32[R,SR] depth-voxel index of the kept samples (first SR occupied depths of the ray's column), -1 unused;
+ *                          a ray whose mask is 0 keeps none (the reference drops such rays before the query, :691-695)
  *   hit_count  int32[R]    kept samples
  *   ray_mask   int32[R]    the reference's `far_id > 0` (:339)
  *   sample_loc float[R,SR,3] perspective coordinates of the sample centres, written for every slot as :532-540

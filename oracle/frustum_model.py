@@ -47,8 +47,9 @@ def sample(pix, occ, dims, vscale, SR):
     for r in range(R):
         col = occ[pix[r, 0] // vscale[0], pix[r, 1] // vscale[1]]
         zs = np.nonzero(col)[0]
-        sz[r, :min(SR, len(zs))] = zs[:SR]
         mask[r] = 1 if (len(zs) and zs[-1] > 0) else 0
+        if mask[r]:                                                 # rays the reference drops keep no samples
+            sz[r, :min(SR, len(zs))] = zs[:SR]
     return sz, mask
 
 

@@ -120,7 +120,8 @@ __global__ void __launch_bounds__(256) frustum_sample_kernel(const int* __restri
             deep |= (z0 == 0 ? (m & ~1u) : m) != 0u;
         }
     }
-    kept = min(kept, SR);
+    // a ray the reference drops (mask 0) keeps no samples: drivers that do not compact rays see it as a miss
+    kept = deep ? min(kept, SR) : 0;
     for (int s = kept + lane; s < SR; s += 32) out[s] = -1;
     if (lane == 0) {
         hit_count[ray] = kept;

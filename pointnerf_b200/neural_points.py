@@ -174,7 +174,7 @@ class NeuralPoints(nn.Module):
 class RayPlan:
     """Weight-independent part of one batch (NeuralPointsRayMarching.sample): raw query results, perspective coordinates
     of samples and points, and the aggregator's work lists (CompactSamples)."""
-    __slots__ = ("raw", "pidx", "loc_w", "loc_pers", "xyz_pers", "raydir", "work_lists")
+    __slots__ = ("raw", "pidx", "loc_w", "loc_pers", "xyz_pers", "raydir", "work_lists", "vsize", "ray_mask", "sample_dirs")
 
 
 class NeuralPointsRayMarching(nn.Module):
@@ -247,15 +247,15 @@ class NeuralPointsRayMarching(nn.Module):
         return call.sample_pidx.view(-1)[call.pair_src[:call.M].long()].long()
 
     # ---- fused path -----------------------------------------------------------------------------
-    def sample(self, campos, raydir, camrotc2w, near, far, uniform=None, xyz_pers=None):
+    def sample(self, campos, raydir, camrotc2w, near, far, uniform=None, xyz_pers=None, pixel_idx=None, h=None, w=None,
+               intrinsic=None):
         """Everything of one batch that does not depend on the trainable tensors: ray sampling, neighbour query,
         perspective coordinates and the work lists, queued on the current stream with NO host sync.  ``forward(plan=...)``
         consumes it; a training loop calls this for batch i+1 before the backward of batch i so that the (S, M)
         read-back the aggregator needs is complete long before it is waited for."""
         nps = self.neural_points
         if getattr(self.opt, "wcoord_query", 1) <= 0:
-            raise NotImplementedError("the fused path is built on the world-coordinate querier; with wcoord_query = 0 use "
-                                      "forward_seams(...) (perspective-frustum querier + aggregator + ray_march seams)")
+            return self._sample_frustum(campos, camrotc2w, near, far, pixel_idx, h, w, intrinsic, uniform, xyz_pers)
         near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
         far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
         xyz = nps.xyz.detach()
@@ -268,6 +268,34 @@ class NeuralPointsRayMarching(nn.Module):
         # the points' camera-frame coordinates depend on the camera only: a frame renderer passes them along
         plan.xyz_pers = xyz_pers if xyz_pers is not None else _query.w2pers(xyz, camrotc2w[0], campos[0])
         plan.work_lists = CompactSamples(pidx.contiguous(), R * SR, K)
+        plan.vsize, plan.ray_mask, plan.sample_dirs = self.opt.vsize, None, None
+        return plan
+
+    def _sample_frustum(self, campos, camrotc2w, near, far, pixel_idx, h, w, intrinsic, uniform, xyz_pers):
+        """``sample`` on the perspective-frustum querier (wcoord_query = 0): rays come as pixel indices, the grid is built in
+        this view's perspective space, sample centres are perspective coordinates (jittered in z when training, then
+        pers2w gives world positions and per-sample directions, query_point_indices.py:100-108).  Rays are not compacted:
+        the ones the reference drops (ray_mask 0) simply keep no samples.  ``uniform``: [1,R,SR] draw of the jitter."""
+        nps, o = self.neural_points, self.opt
+        if pixel_idx is None or h is None or w is None or intrinsic is None:
+            raise NotImplementedError("wcoord_query = 0 queries by pixel: pass pixel_idx, h, w and intrinsic (the ray-direction "
+                                      "only callers - render_frame, RayShardedStep - are world-coordinate)")
+        q = nps.querier
+        near = near if isinstance(near, (int, float)) else torch.as_tensor(near).min().cpu().numpy()
+        far = far if isinstance(far, (int, float)) else torch.as_tensor(far).max().cpu().numpy()
+        hp = q.get_hyperparameters(h, w, np.asarray(intrinsic), near, far)
+        xp = xyz_pers if xyz_pers is not None else _query.w2pers(nps.xyz.detach(), camrotc2w[0], campos[0])
+        raw = q.query_raw(pixel_idx.reshape(-1, 2).to(torch.int32).contiguous(), xp.reshape(-1, 3), hp)
+        pidx, loc_pers = raw["sample_pidx"], raw["sample_loc"]                    # [R,SR,K], [R,SR,3]
+        R, SR, K = pidx.shape
+        if o.is_train:
+            loc_pers = getattr(q, o.shpnt_jitter)(loc_pers[None], hp["vsize"], uniform=uniform)[0]
+        loc_w, dirs = q.pers2w(loc_pers[None], camrotc2w, campos)
+        plan = RayPlan()
+        plan.raw, plan.pidx, plan.loc_w, plan.loc_pers, plan.raydir = raw, pidx, loc_w[0].contiguous(), loc_pers, None
+        plan.xyz_pers = xp.reshape(-1, 3)
+        plan.work_lists = CompactSamples(pidx.contiguous(), R * SR, K)
+        plan.vsize, plan.ray_mask, plan.sample_dirs = hp["vsize"], raw["ray_mask"], dirs[0].contiguous()
         return plan
 
     @torch.no_grad()
@@ -324,28 +352,37 @@ class NeuralPointsRayMarching(nn.Module):
                                       far=far, h=h, w=w, intrinsic=intrinsic, uniform=uniform, **kargs)
         o, nps = self.opt, self.neural_points
         if plan is None:
-            plan = self.sample(campos, raydir, camrotc2w, near, far, uniform=uniform)
+            plan = self.sample(campos, raydir, camrotc2w, near, far, uniform=uniform, pixel_idx=pixel_idx, h=h, w=w,
+                               intrinsic=intrinsic)
         raw, pidx, loc_w, loc_pers, xyz_pers = plan.raw, plan.pidx, plan.loc_w, plan.loc_pers, plan.xyz_pers
         R, SR, K = pidx.shape
         want_w = self.aggregator._want_weight()
+        frustum = plan.sample_dirs is not None       # per-sample directions from pers2w, the view's own voxel size
         decoded, weight, slot_row = self.aggregator.forward_tables(
             nps.xyz, xyz_pers, nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf, nps.Rw2c,
-            pidx, loc_pers, loc_w, plan.raydir[0], o.vsize, dirs_per_ray=True, want_weight=want_w, compact=True,
-            work_lists=plan.work_lists)
+            pidx, loc_pers, loc_w, plan.sample_dirs if frustum else plan.raydir[0], plan.vsize, dirs_per_ray=not frustum,
+            want_weight=want_w, compact=True, work_lists=plan.work_lists)
         ray_valid = (slot_row >= 0)[None]                                         # [1,R,SR]
-        ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, o.vsize, o.raydist_mode_unit)
+        ray_dist = ray_dist_from_samples(loc_pers[None], ray_valid, plan.vsize, o.raydist_mode_unit)
         ray_color, _, opacity, _, blend_weight, bg_T, _ = ray_march_compact(ray_dist, ray_valid, decoded, slot_row, bg_color)
+        if frustum:
+            # the frustum querier's ray mask says "the ray's column holds an occupied depth", not "a neighbour was found"
+            ray_any = ray_valid[0].any(-1).to(torch.int32)
+            ray_mask = (plan.ray_mask > 0).view(torch.int8)[None]
+        else:
+            ray_any = raw["ray_any"]
+            ray_mask = (ray_any > 0).view(torch.int8)[None]
         out = {"coarse_raycolor": ray_color, "coarse_point_opacity": opacity, "coarse_is_background": bg_T,
-               "coarse_mask": 1 - bg_T, "ray_mask": (raw["ray_any"] > 0).view(torch.int8)[None],
+               "coarse_mask": 1 - bg_T, "ray_mask": ray_mask,
                # a ray has a valid sample exactly when the query found it a neighbour (ray_any): same values as
                # logical_not(any(ray_valid)).repeat(1,1,3).float() of the reference (:162) in two launches
-               "queried_shading": (raw["ray_any"].view(1, R, 1) == 0).expand(1, R, 3).float()}
+               "queried_shading": (ray_any.view(1, R, 1) == 0).expand(1, R, 3).float()}
         if want_w:
             out["weight"] = weight.detach()[None]
             out["blend_weight"] = blend_weight.detach()
             out["conf_coefficient"] = gather_clamp(nps.points_conf, pidx, 0.0001, 1.0)[None]
             if getattr(o, "prob", 0) == 1:
-                out.update(self.probe_outputs(opacity, raw["ray_any"], loc_w, pidx, weight))
+                out.update(self.probe_outputs(opacity, ray_any, loc_w, pidx, weight))
         return out
 
     @torch.no_grad()

@@ -111,8 +111,9 @@ def test_frustum_edge_cases_and_refusals(cuda_dev):
 
 @pytest.mark.skipif(not frustum_ref.available(), reason="oracle/_ref/libpn_ref_querier_frustum.so not built")
 def test_step_with_frustum_querier_matches_oracle(cuda_dev):
-    """wcoord_query = 0 through the reference seams (NeuralPoints -> PointAggregator -> ray_march), forward and backward,
-    against the CPU oracle pipeline on the frustum querier: 1e-4 relative (fp32 or fp64 evaluation at LeakyReLU kinks)."""
+    """wcoord_query = 0 through the reference seams (NeuralPoints -> PointAggregator -> ray_march) and through the fused
+    driver, forward and backward, against the CPU oracle pipeline on the frustum querier: 1e-4 relative (fp32 or fp64
+    evaluation at LeakyReLU kinks)."""
     opt, xyz, cam, pix = syn.frustum_case("dtu")
     opt = copy.copy(opt)
     opt.is_train = 0
@@ -143,21 +144,59 @@ def test_step_with_frustum_querier_matches_oracle(cuda_dev):
     ref64 = pipeline_ref.run(opt, tables, cam, None, bg, sd, loss_fn=loss_fn, dtype=torch.float64, frustum_pix=pix)
     assert float(ref["coarse_is_background"].min()) < 0.5
     dev = cuda_dev
-    bg_d = bg.to(dev).clone().requires_grad_(True)
-    out = model(cam["campos"].to(dev), None, bg_color=bg_d, camrotc2w=cam["camrotc2w"].to(dev), pixel_idx=pix.to(dev),
-                near=cam["near"], far=cam["far"], h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"], fused=False)
-    assert torch.equal(out["ray_mask"].cpu(), ref["ray_mask"])
-    for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading"):
-        assert_close(out[k], ref[k], "frustum seams " + k, want64=ref64[k])
-    loss = (out["coarse_raycolor"] * wt.to(dev)).sum() + (out["coarse_point_opacity"] ** 2 * keep.to(dev)).sum() * 0.1
-    loss.backward()
-    grads = {n: p.grad.detach().cpu().clone() for n, p in model.aggregator.named_parameters()}
-    for n in ("points_embeding", "points_conf", "points_dir", "points_color"):
-        grads[n] = getattr(model.neural_points, n).grad.detach().cpu().clone()
-    grads["bg_color"] = bg_d.grad.detach().cpu().clone()
     g_ref, g_ref64 = group_linear_grads(ref["grads"]), group_linear_grads(ref64["grads"])
-    for n, gr in group_linear_grads(grads).items():
-        assert_close(gr, g_ref[n], "frustum seams grad " + n, want64=g_ref64[n])
-    with pytest.raises(NotImplementedError):   # the fused path is world-coordinate only
+    for fused in (False, True):   # the reference seams, then the fused driver (no ray compaction, no [R,SR,K,*] gathers)
+        tag = "frustum fused " if fused else "frustum seams "
+        for p_ in model.parameters():
+            p_.grad = None
+        bg_d = bg.to(dev).clone().requires_grad_(True)
+        out = model(cam["campos"].to(dev), None, bg_color=bg_d, camrotc2w=cam["camrotc2w"].to(dev), pixel_idx=pix.to(dev),
+                    near=cam["near"], far=cam["far"], h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"], fused=fused)
+        assert torch.equal(out["ray_mask"].cpu(), ref["ray_mask"])
+        for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading"):
+            assert_close(out[k], ref[k], tag + k, want64=ref64[k])
+        loss = (out["coarse_raycolor"] * wt.to(dev)).sum() + (out["coarse_point_opacity"] ** 2 * keep.to(dev)).sum() * 0.1
+        loss.backward()
+        grads = {n: p.grad.detach().cpu().clone() for n, p in model.aggregator.named_parameters()}
+        for n in ("points_embeding", "points_conf", "points_dir", "points_color"):
+            grads[n] = getattr(model.neural_points, n).grad.detach().cpu().clone()
+        grads["bg_color"] = bg_d.grad.detach().cpu().clone()
+        for n, gr in group_linear_grads(grads).items():
+            assert_close(gr, g_ref[n], tag + "grad " + n, want64=g_ref64[n])
+    with pytest.raises(NotImplementedError):   # the frustum querier is addressed by pixel, not by ray direction
         model(cam["campos"].to(dev), torch.zeros(1, R, 3, device=dev), bg_color=bg_d, camrotc2w=cam["camrotc2w"].to(dev),
               near=cam["near"], far=cam["far"])
+
+
+def test_frustum_fused_equals_seams_with_jitter(cuda_dev):
+    """Training-time sample jitter: the fused driver draws for all R rays, the seams for the R' kept ones; fed the same draw
+    they render the same colours."""
+    opt, xyz, cam, pix = syn.frustum_case("dtu")
+    opt = copy.copy(opt)
+    opt.is_train, opt.shpnt_jitter = 1, "uniform"
+    _, tables = syn.make_scene("tiny")
+    dev = cuda_dev
+    pix = pix[:, :300]
+    R = pix.shape[1]
+    torch.manual_seed(0)
+    model = NeuralPointsRayMarching(opt, device=dev)
+    with torch.no_grad():
+        model.aggregator.alpha_branch[0].bias.fill_(60.0)
+    model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                                   tables["points_conf"], Rw2c=tables["Rw2c"])
+    bg = torch.rand(opt.shading_color_channel_num, generator=torch.Generator().manual_seed(4)).to(dev)
+    u = torch.rand(1, R, opt.SR, generator=torch.Generator().manual_seed(9)).to(dev)
+    kw = dict(bg_color=bg, camrotc2w=cam["camrotc2w"].to(dev), pixel_idx=pix.to(dev), near=cam["near"], far=cam["far"], h=cam["h"],
+              w=cam["w"], intrinsic=cam["intrinsic"])
+    with torch.no_grad():
+        of = model(cam["campos"].to(dev), None, fused=True, uniform=u, **kw)
+        keep = of["ray_mask"][0] > 0
+        assert 0 < int(keep.sum()) < R
+        os_ = model(cam["campos"].to(dev), None, fused=False, uniform=u[:, keep], **kw)
+    assert torch.equal(of["ray_mask"], os_["ray_mask"])
+    for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "queried_shading"):
+        assert_close(of[k], os_[k], "jitter fused vs seams " + k, tol=1e-5)
+    opt.is_train = 0
+    with torch.no_grad():
+        o0 = model(cam["campos"].to(dev), None, fused=True, **kw)
+    assert rel_err(o0["coarse_raycolor"], of["coarse_raycolor"]) > 1e-4      # the jitter did move the samples
