@@ -199,4 +199,4 @@ def test_frustum_fused_equals_seams_with_jitter(cuda_dev):
     opt.is_train = 0
     with torch.no_grad():
         o0 = model(cam["campos"].to(dev), None, fused=True, **kw)
-    assert rel_err(o0["coarse_raycolor"], of["coarse_raycolor"]) > 1e-4      # the jitter did move the samples
+    assert rel_err(o0["coarse_raycolor"], of["coarse_raycolor"]) > 1e-5      # the jitter did move the samples
