@@ -70,3 +70,24 @@ def test_product_does_not_import_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert "from .. import oracle" not in src and "/root/reference" not in src, f
+
+
+def test_frustum_host_arithmetic_matches_oracle():
+    """get_hyperparameters of the perspective-frustum querier (query_point_indices.py:52-81) is host numpy in the product too:
+    same ranges / voxel sizes / dims / limits as the oracle's restatement, for python floats and for the float32 0-d arrays the
+    reference's caller passes (neural_points.py:786), whose promotion rules differ."""
+    import numpy as np
+    from oracle import frustum_ref
+    from pointnerf_b200 import synthetic as syn
+    from pointnerf_b200.query_frustum import frustum_hyperparameters
+    for name in syn.FRUSTUM_CASES:
+        opt, _, cam, _ = syn.frustum_case(name)
+        for conv in (lambda v: v, lambda v: np.asarray(v, np.float32)):
+            near, far = conv(cam["near"]), conv(cam["far"])
+            a = frustum_hyperparameters(opt, cam["h"], cam["w"], cam["intrinsic"], near, far)
+            b = frustum_ref.get_hyperparameters(opt, cam["h"], cam["w"], cam["intrinsic"], near, far)
+            assert set(a) == set(b)
+            for k in a:
+                assert np.array_equal(np.asarray(a[k]), np.asarray(b[k])) and np.asarray(a[k]).dtype == np.asarray(b[k]).dtype, k
+    l = _lib.lib()
+    assert l.pn_frustum_grid_workspace_bytes(1000, 4096) > l.pn_grid_workspace_bytes(1000, 4096)
