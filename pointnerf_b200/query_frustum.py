@@ -10,6 +10,7 @@ warp-per-sample K-NN, no pycuda.  Results equal the reference's under the canoni
 than ``P`` points (pointnerf_b200.h section 3b); options whose reference behaviour is not reproducible raise.
 """
 import ctypes
+import warnings
 
 import numpy as np
 import torch
@@ -51,6 +52,21 @@ class lighting_fast_querier:
 
     def get_hyperparameters(self, h, w, intrinsic, near_depth, far_depth):
         return frustum_hyperparameters(self.opt, h, w, intrinsic, near_depth, far_depth)
+
+    def grid_report(self):
+        """Statistics of the last view's grid (one small device read-back, so not part of ``query_points``): claimed voxels,
+        points inside the frustum, the fullest voxel and how many voxels hold more than ``P`` points - there the reference
+        keeps a time-seeded random subset (:404-411) and this implementation the first P by index."""
+        if self.last_info is None:
+            return None
+        info = self.last_info.cpu().numpy()
+        rep = dict(n_occ=int(info[_lib.GI_N_OCC]), n_inside=int(info[_lib.GI_N_INSIDE]), max_count=int(info[_lib.GI_MAX_COUNT]),
+                   over_P=int(info[_lib.GI_OVER_P]))
+        if rep["over_P"]:
+            warnings.warn("pointnerf_b200: %d frustum voxels hold more than P=%d points (fullest: %d): the reference keeps a "
+                          "time-seeded random subset there, this implementation the first P by index"
+                          % (rep["over_P"], self.opt.P, rep["max_count"]))
+        return rep
 
     def _check(self, hp):
         o = self.opt

@@ -52,6 +52,9 @@ def test_frustum_stages_match_model(name, cuda_dev):
     assert np.array_equal(raw["ray_mask"].cpu().numpy(), mask), "ray mask"
     assert np.array_equal(raw["sample_z"].cpu().numpy(), sz), "depth indices"
     assert np.array_equal(raw["hit_count"].cpu().numpy(), (sz >= 0).sum(1)), "hit count"
+    rep = q.grid_report()
+    assert rep["n_occ"] == len(cells) and rep["max_count"] == max(len(v) for v in cells.values()) and rep["over_P"] == 0
+    assert rep["n_inside"] == sum(len(v) for v in cells.values())
 
 
 @pytest.mark.parametrize("name", CASES)
