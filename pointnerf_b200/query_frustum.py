@@ -127,7 +127,7 @@ class lighting_fast_querier:
             _lib.check(lib.pn_frustum_knn_query(_lib.ptr(xyz_pers), ctypes.byref(gp), ctypes.byref(q), _lib.ptr(cell_start),
                                                 _lib.ptr(bucket), _lib.ptr(pixel_idx), _lib.ptr(sample_z), _lib.ptr(hit), R, SR, K,
                                                 _lib.ptr(pidx), _lib.ptr(loc), _lib.ptr(cand), st), "pn_frustum_knn_query")
-        self.last_info = info
+        self.last_info = info.clone()          # 8 ints; a view would keep the whole per-view store alive until the next call
         res = dict(sample_pidx=pidx, sample_loc=loc, sample_z=sample_z, hit_count=hit, ray_mask=mask, grid_info=info,
                    occ_bits=occ_bits, cell_start=cell_start, bucket_pidx=bucket, dims=dims)
         if count_candidates:
