@@ -16,6 +16,11 @@ against OUTPUTS OF THE REFERENCE ITSELF produced in the build container:
   source string where it lies in the reference tree, as serial host C++
   (``oracle/build_ref.py`` -> ``oracle/_ref/libpn_ref_querier.so``) and run in
   ascending-thread order (the canonical schedule).
+* the four kernels of the second, perspective-frustum ``lighting_fast_querier``
+  (``models/neural_points/query_point_indices.py``) the same way ->
+  ``oracle/_ref/libpn_ref_querier_frustum.so``, driven by ``oracle/frustum_ref.py``;
+  golden vectors ``tests/golden/frustum_*_ref.npz``; ``oracle/frustum_model.py`` is
+  a numpy statement of the product's CSR formulation, checked against them.
 * ``oracle/querier_port.c`` and ``oracle/torch_port.py`` are the restatements
   that travel to the GPU box; they are checked against the two items above.
 """
