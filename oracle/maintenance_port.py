@@ -2,8 +2,10 @@
 
 TEST INFRASTRUCTURE (see oracle/__init__.py).  The reference modules holding these steps import pycuda at module
 level (models/neural_points/neural_points.py:3-4, neural_points_volumetric_model_ori.py through its base class), so
-they cannot be imported here; the few lines are restated with the same torch ops, each citing its source.  Parity
-unpinned by reference-run outputs for this file: the checks are against this restatement only.
+they cannot be imported here; the few lines are restated with the same torch ops, each citing its source.  Pinned in
+the build container by executing the reference's own source fragments on CPU tensors (oracle/ref_fragments.py;
+tests/test_oracle.py: prune / grow_points / the opt.prob block / unmask bit for bit; the voxel down-sampling through the
+reference's call site with torch_scatter 2.0.8's two calls restated - that dependency is absent).
 """
 import torch
 

@@ -290,3 +290,94 @@ def test_frustum_csr_formulation_equals_reference_tables(name):
         cells_f, _, _ = fm.build(np.where(keep[:, None], xp, np.float32(1e9)), hp)
         assert not np.array_equal(fm.knn(xp, cells_f, dims, hp, px[sel], sz[sel], opt)[0], pidx)
         assert int((sz >= 0).sum(1).max()) == opt.SR
+
+
+# ---- maintenance steps: the restatements vs the reference's own source, executed as fragments (oracle/ref_fragments.py) ------
+def _maint_tables(n=500, F=32, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    return {"xyz": torch.randn(n, 3, generator=g), "points_embeding": torch.randn(1, n, F, generator=g),
+            "points_conf": torch.rand(1, n, 1, generator=g), "points_dir": torch.randn(1, n, 3, generator=g),
+            "points_color": torch.randn(1, n, 3, generator=g)}
+
+
+@needs_ref
+def test_prune_and_grow_restatements_equal_reference_methods():
+    import types
+    from oracle import maintenance_port as mp, ref_fragments as rf
+    rel = "models/neural_points/neural_points.py"
+    opt = types.SimpleNamespace(xyz_grad=0, feat_grad=1, conf_grad=1, dir_grad=1, color_grad=1)
+    t = _maint_tables()
+    me = types.SimpleNamespace(opt=opt, eulers=None, Rw2c=torch.nn.Parameter(torch.eye(3)),
+                               **{k: torch.nn.Parameter(v.clone()) for k, v in t.items()})
+    rf.function(rel, "prune", class_name="NeuralPoints")(me, 0.4)
+    want = mp.prune(t, 0.4)
+    assert 0 < want["xyz"].shape[0] < t["xyz"].shape[0]
+    for k in t:
+        assert torch.equal(getattr(me, k).data, want[k]), k
+    g = torch.Generator().manual_seed(8)
+    add = dict(add_xyz=torch.randn(40, 3, generator=g), add_embedding=torch.randn(40, 32, generator=g), add_color=torch.randn(40, 3, generator=g),
+               add_dir=torch.randn(40, 3, generator=g), add_conf=torch.rand(40, 1, generator=g))
+    rf.function(rel, "grow_points", class_name="NeuralPoints")(me, **add)
+    want = mp.grow_points(want, **add)
+    for k in t:
+        assert torch.equal(getattr(me, k).data, want[k]), k
+    assert me.points_embeding.requires_grad and not me.xyz.requires_grad
+
+
+@needs_ref
+def test_probe_and_unmask_restatements_equal_reference_block():
+    """The ``opt.prob == 1`` block of neural_points_volumetric_model_ori.py (:351-372) and ``unmask`` (:131-137), executed from the
+    reference's source on CPU tensors, against oracle/maintenance_port.py - bit for bit."""
+    import types
+    from oracle import maintenance_port as mp, ref_fragments as rf
+    rel = "models/neural_points_volumetric_model_ori.py"
+    g = torch.Generator().manual_seed(6)
+    R, SR, K, F = 9, 7, 8, 32
+    ins = dict(sample_pnt_mask=torch.rand(1, R, SR, K, generator=g) > 0.3, weight=torch.rand(1, R, SR, K, generator=g),
+               conf_coefficient=torch.rand(1, R, SR, K, generator=g), sample_loc_w=torch.randn(1, R, SR, 3, generator=g),
+               sampled_xyz=torch.randn(1, R, SR, K, 3, generator=g), sampled_color=torch.randn(1, R, SR, K, 3, generator=g),
+               sampled_dir=torch.randn(1, R, SR, K, 3, generator=g), sampled_conf=torch.rand(1, R, SR, K, 1, generator=g),
+               sampled_embedding=torch.randn(1, R, SR, K, F, generator=g))
+    opac = torch.rand(1, R, SR, generator=g)
+    opac[0, 2, 3] = opac[0, 2, 5] = 2.0                       # a tie: torch.max keeps the first index
+    src, line = rf.if_block(rel, 'output["coarse_point_opacity"].shape[1] > 0')
+    assert 300 < line < 400
+    ns = dict(ins, output={"coarse_point_opacity": opac}, self=types.SimpleNamespace(opt=types.SimpleNamespace(prob=1)), torch=torch)
+    exec(compile(src, rel + ":probe", "exec"), ns)
+    got = ns["output"]
+    want = mp.probe_outputs(opac, ins["sample_loc_w"], ins["weight"], ins["conf_coefficient"], ins["sampled_xyz"], ins["sampled_color"],
+                            ins["sampled_dir"], ins["sampled_conf"], ins["sampled_embedding"])
+    for k in ("ray_max_shading_opacity", "ray_max_sample_loc_w", "ray_max_far_dist", "shading_avg_color", "shading_avg_dir",
+              "shading_avg_conf", "shading_avg_embedding"):
+        assert got[k].shape == want[k].shape and torch.equal(got[k], want[k]), k
+    assert int(want["ray_max_slot"][0, 2]) == 3
+    # unmask: scatter the R'' rows back over all rays
+    mask = torch.zeros(1, 20, dtype=torch.int8)
+    mask[0, torch.randperm(20, generator=g)[:R].sort()[0]] = 1
+    names = ["ray_max_sample_loc_w", "ray_max_shading_opacity", "shading_avg_color", "shading_avg_embedding", "ray_max_far_dist"]
+    out_ref = rf.function(rel, "unmask", class_name="NeuralPointsVolumetricModel")(None, torch.nonzero(mask > 0), {k: got[k] for k in names}, names, 1, 20)
+    out_port = mp.unmask(mask, {k: want[k] for k in names})
+    for k in names:
+        assert torch.equal(out_ref[k], out_port[k]), k
+
+
+@needs_ref
+def test_voxel_downsampling_restatement_equals_reference_call_site():
+    """construct_vox_points_closest (models/mvs/mvs_utils.py:537-561) executed from the reference's source with torch_scatter's
+    two calls restated (oracle/ref_fragments.py: version and algorithm named there)."""
+    from oracle import maintenance_port as mp, ref_fragments as rf
+    fn = rf.function("models/mvs/mvs_utils.py", "construct_vox_points_closest",
+                     extra_globals={"scatter_mean": rf.scatter_mean, "scatter_min": rf.scatter_min})
+    g = torch.Generator().manual_seed(12)
+    xyz = torch.rand(3000, 3, generator=g) * torch.tensor([2.0, 1.0, 0.5]) - 0.3
+    xyz[100:140] = xyz[60:100]                               # exact duplicates: equal residuals, the first index wins
+    for res in (16, 40):
+        c_ref, grid_ref, min_ref = fn(xyz.clone(), res)
+        c, grid, mn, inv, _ = mp.construct_vox_points_closest(xyz.clone(), res)
+        assert torch.equal(grid_ref, grid) and torch.equal(min_ref, mn)
+        assert torch.equal(c_ref, c)
+    # inside a box that filters nothing the reference's box branch gives the same voxels as the port's
+    lo, hi = xyz.min(0)[0] - 0.01, xyz.max(0)[0] + 0.01
+    c_ref, grid_ref, min_ref = fn(xyz.clone(), 16, space_min=lo, space_max=hi)
+    c, grid, mn, _, _ = mp.construct_vox_points_closest(xyz.clone(), 16, space_min=lo, space_max=hi)
+    assert torch.equal(grid_ref, grid) and torch.equal(min_ref, mn) and torch.equal(c_ref, c)
