@@ -381,3 +381,62 @@ def test_voxel_downsampling_restatement_equals_reference_call_site():
     c_ref, grid_ref, min_ref = fn(xyz.clone(), 16, space_min=lo, space_max=hi)
     c, grid, mn, _, _ = mp.construct_vox_points_closest(xyz.clone(), 16, space_min=lo, space_max=hi)
     assert torch.equal(grid_ref, grid) and torch.equal(min_ref, mn) and torch.equal(c_ref, c)
+
+
+@needs_ref
+def test_querier_host_glue_equals_reference_methods(tiny_scene):
+    """get_hyperparameters / w2pers of the world-coordinate querier (worldcoords.py:48-81, 102-109) and get_hyperparameters /
+    pers2w / uniform of the perspective-frustum one (query_point_indices.py:52-81, 110-123, 131-135), executed from the
+    reference's source (oracle/ref_fragments.py; np_to_gpuarray - the pycuda upload - replaced by a pass-through), against
+    the oracle's restatements and the product's host arithmetic."""
+    import types
+    from oracle import frustum_ref as fr, ref_fragments as rf
+    from pointnerf_b200.query_frustum import frustum_hyperparameters
+    glob = {"np": np, "np_to_gpuarray": lambda *a: list(a)}
+    # ---- world-coordinate querier
+    rel = "models/neural_points/query_point_indices_worldcoords.py"
+    ghp = rf.function(rel, "get_hyperparameters", class_name="lighting_fast_querier", extra_globals=glob)
+    cases = [(tiny_scene[0], tiny_scene[1]["xyz"])]
+    for name in ("cfg2", "cfg3", "tiny4"):
+        o = syn.config_opt(name)
+        g = torch.Generator().manual_seed(len(name))
+        lo, hi = torch.tensor(o.ranges[:3]), torch.tensor(o.ranges[3:])
+        cases.append((o, lo + (hi - lo) * (torch.rand(200, 3, generator=g) * 1.1 - 0.05)))
+    for o, xyz in cases:
+        got = ghp(types.SimpleNamespace(opt=o), o.vsize, xyz[None], ranges=o.ranges)
+        want = qr.get_hyperparameters(o, xyz[None])
+        assert np.array_equal(got[0], want["radius_limit"]) and np.array_equal(got[2], want["ranges"])
+        assert np.array_equal(got[5], want["scaled_vsize"]) and np.array_equal(got[6], want["scaled_vdim"])
+        prod = syn.grid_hyperparameters(o, xyz.min(0)[0].numpy(), xyz.max(0)[0].numpy())
+        assert np.array_equal(got[2], prod["ranges"]) and np.array_equal(got[6], prod["scaled_vdim"]) and np.array_equal(got[5], prod["scaled_vsize"])
+    cam = tiny_scene[2]
+    w2p = rf.function(rel, "w2pers", class_name="lighting_fast_querier", extra_globals=glob)
+    pts = tiny_scene[1]["xyz"][:777]
+    assert torch.equal(w2p(None, pts[None], cam["camrotc2w"], cam["campos"]), tp.w2pers_samples(pts[None], cam["camrotc2w"], cam["campos"]))
+    # ---- perspective-frustum querier
+    rel = "models/neural_points/query_point_indices.py"
+    ghp = rf.function(rel, "get_hyperparameters", class_name="lighting_fast_querier", extra_globals=glob)
+    for name in syn.FRUSTUM_CASES:
+        o, _, cam, _ = syn.frustum_case(name)
+        for conv in (lambda v: v, lambda v: np.asarray(v, np.float32)):
+            near, far = conv(cam["near"]), conv(cam["far"])
+            got = ghp(types.SimpleNamespace(opt=o, inverse=0), cam["h"], cam["w"], cam["intrinsic"], near, far)
+            for want in (fr.get_hyperparameters(o, cam["h"], cam["w"], cam["intrinsic"], near, far),
+                         frustum_hyperparameters(o, cam["h"], cam["w"], cam["intrinsic"], near, far)):
+                for i, k in ((0, "radius_limit"), (1, "depth_limit"), (2, "ranges"), (3, "vsize"), (4, "vdim"), (5, "scaled_vsize"),
+                             (6, "scaled_vdim"), (7, "vscale")):
+                    assert np.array_equal(np.asarray(got[i]), np.asarray(want[k])) and np.asarray(got[i]).dtype == np.asarray(want[k]).dtype, (name, k)
+    p2w = rf.function(rel, "pers2w", class_name="lighting_fast_querier", extra_globals=glob)
+    g = torch.Generator().manual_seed(4)
+    loc = torch.rand(1, 50, 6, 3, generator=g) + torch.tensor([-0.5, -0.5, 0.3])
+    a, b = p2w(None, loc, cam["camrotc2w"], cam["campos"]), fr.pers2w(loc, cam["camrotc2w"], cam["campos"])
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    uni = rf.function(rel, "uniform", class_name="lighting_fast_querier", extra_globals=glob)
+    vsize = np.array([0.01, 0.01, 0.006], np.float32)
+    torch.manual_seed(77)
+    u = torch.rand(1, 50, 6)
+    torch.manual_seed(77)
+    got = uni(None, loc.clone(), vsize)
+    want = loc.clone()
+    want[..., 2] = want[..., 2] + (u - 0.5) * vsize[2]                     # the line of oracle/frustum_ref.py:query_points
+    assert torch.equal(got, want)
