@@ -21,6 +21,11 @@ against OUTPUTS OF THE REFERENCE ITSELF produced in the build container:
   ``oracle/_ref/libpn_ref_querier_frustum.so``, driven by ``oracle/frustum_ref.py``;
   golden vectors ``tests/golden/frustum_*_ref.npz``; ``oracle/frustum_model.py`` is
   a numpy statement of the product's CSR formulation, checked against them.
+* ``oracle/ref_fragments.py`` compiles whole classes / single functions / one ``if``
+  block of reference files that cannot be imported (pycuda, cv2, torch_scatter at
+  module scope) from their source where it lies: both ``lighting_fast_querier``
+  classes run end to end on the CPU (own glue + own kernels), and the maintenance
+  steps (prune, grow, probe block, unmask, voxel down-sampling) are pinned this way.
 * ``oracle/querier_port.c`` and ``oracle/torch_port.py`` are the restatements
   that travel to the GPU box; they are checked against the two items above.
 """

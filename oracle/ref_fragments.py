@@ -77,3 +77,80 @@ def scatter_min(src, index, dim=0):
         if s[e] < o[ix[e]]:
             o[ix[e]], a[ix[e]] = s[e], e
     return torch.tensor(o, dtype=src.dtype), torch.tensor(a, dtype=torch.long)
+
+
+# ---- the reference's querier classes, whole, on the CPU -------------------------------------------------------------------
+class _TorchOnCpu:
+    """``torch`` as the glue sees it: the two CUDA-only helper calls it makes (a scratch ``torch.cuda.ByteTensor(8)`` at
+    worldcoords.py:558, commented ``synchronize``s) do nothing; everything else is torch."""
+    def __init__(self):
+        import types
+        self.cuda = types.SimpleNamespace(ByteTensor=lambda *a, **k: None, synchronize=lambda *a, **k: None)
+
+    def __getattr__(self, name):
+        return getattr(torch, name)
+
+
+def _launcher(lib, cname):
+    """A pycuda-style ``kernel(*args, block=, grid=)`` that runs the host-compiled reference kernel (oracle/_ref): tensors
+    and numpy arrays pass as pointers, np.int32 / np.float32 by value, the np.uint64 time seed is dropped (the launchers of
+    oracle/build_ref.py pass 0)."""
+    import ctypes
+    import numpy as np
+    fn = getattr(lib, cname)
+    fn.restype = None
+
+    def launch(*args, block, grid):
+        conv, keep = [], []
+        for a in args:
+            if isinstance(a, torch.Tensor):
+                assert a.is_contiguous() and not a.is_cuda
+                conv.append(ctypes.c_void_p(a.data_ptr()))
+            elif isinstance(a, np.ndarray):
+                a = np.ascontiguousarray(a)
+                keep.append(a)
+                conv.append(a.ctypes.data_as(ctypes.c_void_p))
+            elif isinstance(a, np.uint64):
+                continue
+            elif isinstance(a, (np.int32, int)):
+                conv.append(ctypes.c_int(int(a)))
+            elif isinstance(a, (np.float32, float)):
+                conv.append(ctypes.c_float(float(a)))
+            else:
+                raise TypeError("kernel argument of type %s" % type(a))
+        fn(ctypes.c_int(int(grid[0])), ctypes.c_int(int(block[0])), *conv)
+    return launch
+
+
+def reference_querier(kind, opt):
+    """An instance of the reference's ``lighting_fast_querier`` (kind "world": query_point_indices_worldcoords.py, "frustum":
+    query_point_indices.py) whose every method except ``__init__`` / ``build_cuda`` / ``clean_up`` is compiled from the
+    reference's source, and whose kernel handles launch the reference's own kernels compiled for the host: the reference's
+    Python glue AND CUDA code, executed here serially.  Build container only (needs the tree and oracle/_ref)."""
+    import ctypes
+    import time
+    import numpy as np
+    from . import build_ref, ref_import
+    world = kind == "world"
+    rel = "models/neural_points/query_point_indices_worldcoords.py" if world else "models/neural_points/query_point_indices.py"
+    build_ref.build()
+    src, tree = _tree(rel)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "lighting_fast_querier")
+    ns = ref_import.load()
+    g = {"torch": _TorchOnCpu(), "np": np, "time": time, "Holder": lambda t: t, "np_to_gpuarray": lambda *a: list(a),
+         "near_far_linear_ray_generation": ns.near_far_linear_ray_generation, "print": lambda *a, **k: None}
+    methods = {}
+    for node in cls.body:
+        if isinstance(node, ast.FunctionDef) and node.name not in ("__init__", "build_cuda", "clean_up"):
+            exec(compile(textwrap.dedent(ast.get_source_segment(src, node, padded=True)), rel + ":" + node.name, "exec"), g)
+            methods[node.name] = g[node.name]
+    me = type("lighting_fast_querier", (), methods)()
+    me.opt, me.inverse, me.count = opt, opt.inverse, 0
+    lib = ctypes.CDLL(build_ref.OUT_SO if world else build_ref.OUT_SO_FRUSTUM)
+    if world:
+        for name in ("claim_occ", "map_coor2occ", "fill_occ2pnts", "mask_raypos", "get_shadingloc", "query_along_ray"):
+            setattr(me, name, _launcher(lib, "pn_ref_" + name))
+    else:
+        for name in ("get_occ_vox", "near_vox_full", "insert_vox_points", "query_along_ray"):
+            setattr(me, name, _launcher(lib, "pn_ref_" + name))
+    return me

@@ -440,3 +440,55 @@ def test_querier_host_glue_equals_reference_methods(tiny_scene):
     want = loc.clone()
     want[..., 2] = want[..., 2] + (u - 0.5) * vsize[2]                     # the line of oracle/frustum_ref.py:query_points
     assert torch.equal(got, want)
+
+
+# ---- the reference's querier classes executed WHOLE on the CPU (their own Python glue + their own kernels) -----------------
+@needs_ref
+@pytest.mark.parametrize("train", [0, 1])
+def test_reference_world_querier_class_equals_oracle_and_golden(tiny_scene, train):
+    """lighting_fast_querier of query_point_indices_worldcoords.py: every method compiled from the reference's source, kernels =
+    its CUDA string built for the host (oracle/ref_fragments.py).  Its 7-tuple equals the oracle's restated glue around the C
+    port bit for bit, and the committed golden vector - so the restatement that travels to the GPU box is the reference."""
+    from oracle import ref_fragments as rf
+    opt, tables, cam = tiny_scene
+    opt = copy.copy(opt)
+    opt.is_train = train
+    z = _load("querier_ref.npz")
+    raydir, xyz = torch.from_numpy(z["raydir"]), tables["xyz"]
+    R = raydir.shape[1]
+    q = rf.reference_querier("world", opt)
+    torch.manual_seed(31)
+    uniform = torch.rand(1, R, opt.z_depth_dim) if train else None       # the draw of diff_ray_marching.py:373
+    torch.manual_seed(31)
+    got = q.query_points(torch.zeros(1, R, 2, dtype=torch.int32), None, xyz[None], torch.tensor([xyz.shape[0]], dtype=torch.int32),
+                         cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"], raydir, cam["campos"], cam["camrotc2w"])
+    want, _ = qr.query_points(opt, xyz[None], raydir, cam["campos"], cam["camrotc2w"], cam["near"], cam["far"], backend="port",
+                              uniform=uniform)
+    for i in range(5):
+        assert got[i].shape == want[i].shape and got[i].dtype == want[i].dtype and torch.equal(got[i], want[i]), i
+    assert np.array_equal(got[6], want[6]) and tuple(got[5]) == tuple(want[5])
+    if not train:
+        assert np.array_equal(got[0].numpy(), z["sample_pidx"]) and np.array_equal(got[2].numpy(), z["sample_loc_w"])
+        assert np.array_equal(got[4].numpy(), z["ray_mask"])
+    else:
+        assert not np.array_equal(got[2].numpy(), z["sample_loc_w"][:, :got[2].shape[1]]) or got[2].shape[1] != z["sample_loc_w"].shape[1]
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["dtu", "crop"])
+def test_reference_frustum_querier_class_equals_oracle_and_golden(name):
+    """The same for the perspective-frustum lighting_fast_querier (query_point_indices.py), without and with its ``uniform``
+    sample jitter: the golden vectors the GPU tests compare against ARE what the reference's class returns."""
+    from oracle import ref_fragments as rf
+    g = _load("frustum_%s_ref.npz" % name)
+    opt, cam, pix, xyz_pers, hp = _frustum_inputs(name)
+    n_act = torch.tensor([xyz_pers.shape[1]], dtype=torch.int32)
+    args = (cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"], None, cam["campos"], cam["camrotc2w"])
+    opt.is_train = 0
+    out = rf.reference_querier("frustum", opt).query_points(pix, xyz_pers, None, n_act, *args)
+    for i, k in enumerate(("sample_pidx", "sample_loc", "sample_loc_w", "ray_dirs", "ray_mask", "vsize", "ranges")):
+        assert np.array_equal(np.asarray(out[i]), g[k]) and np.asarray(out[i]).dtype == g[k].dtype, k
+    opt.is_train, opt.shpnt_jitter = 1, "uniform"
+    torch.manual_seed(5)                                                  # oracle/make_golden.py drew ``uniform`` from this seed
+    out = rf.reference_querier("frustum", opt).query_points(pix, xyz_pers, None, n_act, *args)
+    assert np.array_equal(out[1].numpy(), g["jitter_sample_loc"]) and np.array_equal(out[2].numpy(), g["jitter_sample_loc_w"])
