@@ -4,6 +4,10 @@ TEST INFRASTRUCTURE (see oracle/__init__.py).  Restates NeuralPointsRayMarching.
 (models/neural_points_volumetric_model.py:272-352) on top of the querier oracle (oracle/querier_ref.py) and
 the torch restatements (oracle/torch_port.py), and differentiates it with autograd exactly as the
 reference's training step does (loss.backward through ray_march <- aggregator <- index_select).
+
+Pinned in the build container against the reference's own driver assembled from its source and run whole on the CPU
+(oracle/ref_fragments.reference_hot_path, tests/test_oracle.py::test_reference_hot_path_whole_equals_pipeline_oracle):
+outputs bit for bit, gradients to 1e-6, with the world-coordinate and the perspective-frustum querier.
 """
 import torch
 

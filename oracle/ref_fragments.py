@@ -30,6 +30,20 @@ def available():
     return os.path.isfile(os.path.join(REF_ROOT, "models", "neural_points", "neural_points.py"))
 
 
+def _dedent(text):
+    """textwrap.dedent that tolerates the reference's column-0 comment lines inside indented methods."""
+    lines = text.split("\n")
+    indent = lines[0][:len(lines[0]) - len(lines[0].lstrip())]
+    out = []
+    for ln in lines:
+        if ln.startswith(indent):
+            out.append(ln[len(indent):])
+        else:
+            assert ln.strip() == "" or ln.lstrip().startswith("#"), ln
+            out.append(ln.lstrip())
+    return "\n".join(out)
+
+
 def _tree(relpath):
     src = open(os.path.join(REF_ROOT, relpath)).read()
     return src, ast.parse(src)
@@ -44,7 +58,7 @@ def function(relpath, name, class_name=None, extra_globals=None):
     node = next(n for n in scope if isinstance(n, ast.FunctionDef) and n.name == name)
     g = {"torch": torch, "nn": nn, "print": lambda *a, **k: None}
     g.update(extra_globals or {})
-    exec(compile(textwrap.dedent(ast.get_source_segment(src, node, padded=True)), relpath + ":" + name, "exec"), g)
+    exec(compile(_dedent(ast.get_source_segment(src, node, padded=True)), relpath + ":" + name, "exec"), g)
     return g[name]
 
 
@@ -53,7 +67,7 @@ def if_block(relpath, needle, occurrence=0):
     src, tree = _tree(relpath)
     hits = [n for n in ast.walk(tree) if isinstance(n, ast.If) and needle in ast.get_source_segment(src, n.test)]
     hits.sort(key=lambda n: n.lineno)
-    return textwrap.dedent(ast.get_source_segment(src, hits[occurrence], padded=True)), hits[occurrence].lineno
+    return _dedent(ast.get_source_segment(src, hits[occurrence], padded=True)), hits[occurrence].lineno
 
 
 # ---- torch_scatter 2.0.8, CPU semantics ------------------------------------------------------------------------------------
@@ -142,7 +156,7 @@ def reference_querier(kind, opt):
     methods = {}
     for node in cls.body:
         if isinstance(node, ast.FunctionDef) and node.name not in ("__init__", "build_cuda", "clean_up"):
-            exec(compile(textwrap.dedent(ast.get_source_segment(src, node, padded=True)), rel + ":" + node.name, "exec"), g)
+            exec(compile(_dedent(ast.get_source_segment(src, node, padded=True)), rel + ":" + node.name, "exec"), g)
             methods[node.name] = g[node.name]
     me = type("lighting_fast_querier", (), methods)()
     me.opt, me.inverse, me.count = opt, opt.inverse, 0
@@ -154,3 +168,52 @@ def reference_querier(kind, opt):
         for name in ("get_occ_vox", "near_vox_full", "insert_vox_points", "query_along_ray"):
             setattr(me, name, _launcher(lib, "pn_ref_" + name))
     return me
+
+
+def _class_from_source(relpath, class_name, keep, g, call=None):
+    """A fresh class holding the methods ``keep`` of the reference class, compiled from the reference's source."""
+    src, tree = _tree(relpath)
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == class_name)
+    methods = {}
+    for node in cls.body:
+        if isinstance(node, ast.FunctionDef) and node.name in keep:
+            exec(compile(_dedent(ast.get_source_segment(src, node, padded=True)), relpath + ":" + node.name, "exec"), g)
+            methods[node.name] = g[node.name]
+    assert set(methods) == set(keep), set(keep) - set(methods)
+    if call is not None:
+        methods["__call__"] = methods[call]
+    return type(class_name, (), methods)
+
+
+def reference_hot_path(kind, opt, tables, agg_state):
+    """The reference's per-ray driver assembled from ITS OWN code on the CPU: ``NeuralPointsRayMarching.forward`` +
+    ``fill_invalid`` (models/neural_points_volumetric_model.py:272-389) over ``NeuralPoints.forward`` / ``get_point_indices`` /
+    ``w2pers`` (models/neural_points/neural_points.py:634-660, 687-693, 782-812) - both compiled from source - the querier of
+    ``reference_querier(kind, opt)``, and the unmodified importable ``PointAggregator`` / ``ray_march`` (oracle/ref_import.py).
+    Returns (driver, leaves): call ``driver.forward(campos, raydir, bg_color=..., camrotc2w=..., pixel_idx=..., near=..., far=...,
+    h=..., w=..., intrinsic=...)`` with tensors as the reference's data loader provides them; ``leaves`` are the point tables
+    (nn.Parameters) for autograd."""
+    import copy
+    import types
+    import numpy as np
+    from . import ref_import
+    ns = ref_import.load()
+    g = {"torch": _TorchOnCpu(), "np": np, "nn": nn, "print": lambda *a, **k: None, "ray_march": ns.ray_march,
+         "alpha_ray_march": ns.alpha_ray_march}
+    nps = _class_from_source("models/neural_points/neural_points.py", "NeuralPoints", ("forward", "get_point_indices", "w2pers"),
+                             dict(g), call="forward")()
+    leaves = {k: nn.Parameter(tables[k].clone()) for k in ("points_embeding", "points_conf", "points_dir", "points_color")}
+    nps.xyz = tables["xyz"].clone()
+    for k, v in leaves.items():
+        setattr(nps, k, v)
+    nps.Rw2c, nps.grid_vox_sz, nps.opt = tables["Rw2c"].clone(), 0, opt
+    nps.querier = reference_querier(kind, opt)
+    drv = _class_from_source("models/neural_points_volumetric_model.py", "NeuralPointsRayMarching", ("forward", "fill_invalid"), dict(g))()
+    opt_ref = copy.copy(opt)
+    opt_ref.agg_axis_weight = None          # the reference builds this tensor on "cuda" (point_aggregators.py:247); None = same branch
+    drv.aggregator = ns.PointAggregator(opt_ref)
+    drv.aggregator.load_state_dict({k: v.detach().cpu().clone() for k, v in agg_state.items()})
+    drv.opt = types.SimpleNamespace(raydist_mode_unit=opt.raydist_mode_unit, neural_render="none", prob=0)
+    drv.neural_points, drv.return_color, drv.return_depth = nps, True, False
+    drv.render_func, drv.blend_func, drv.tone_map = ns.radiance_render, ns.alpha_blend, (lambda x: x)
+    return drv, leaves

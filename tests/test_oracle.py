@@ -492,3 +492,52 @@ def test_reference_frustum_querier_class_equals_oracle_and_golden(name):
     torch.manual_seed(5)                                                  # oracle/make_golden.py drew ``uniform`` from this seed
     out = rf.reference_querier("frustum", opt).query_points(pix, xyz_pers, None, n_act, *args)
     assert np.array_equal(out[1].numpy(), g["jitter_sample_loc"]) and np.array_equal(out[2].numpy(), g["jitter_sample_loc_w"])
+
+
+@needs_ref
+@pytest.mark.parametrize("kind", ["world", "frustum"])
+def test_reference_hot_path_whole_equals_pipeline_oracle(kind):
+    """The reference's per-ray driver assembled from ITS OWN code (NeuralPointsRayMarching.forward + fill_invalid over
+    NeuralPoints.forward over lighting_fast_querier over its kernels, with the unmodified PointAggregator / ray_march;
+    oracle/ref_fragments.reference_hot_path) against oracle/pipeline_ref.run - the oracle every GPU step test compares with:
+    outputs bit for bit, autograd gradients to 1e-6."""
+    from oracle import pipeline_ref, ref_fragments as rf
+    R = 150
+    if kind == "world":
+        opt, tables = syn.make_scene("tiny")
+        cam = syn.make_camera("tiny")
+        raydir, pix = syn.make_rays(cam, syn.random_pixels(cam, R, seed=5))
+        cam_o = cam
+    else:
+        opt, _, cam, pix = syn.frustum_case("dtu")
+        _, tables = syn.make_scene("tiny")
+        pix, raydir = pix[:, :R], torch.zeros(1, R, 3)
+        # the reference hands near / far to the frustum querier as float32 0-d arrays (neural_points.py:786)
+        cam_o = dict(cam, near=np.asarray(cam["near"], np.float32), far=np.asarray(cam["far"], np.float32))
+    opt = copy.copy(opt)
+    opt.is_train = 0
+    g = torch.Generator().manual_seed(1)
+    agg = tp.AggregatorPort(opt)
+    with torch.no_grad():
+        agg.alpha_branch[0].bias.fill_(60.0)
+        for n, p in agg.named_parameters():
+            if p.dim() == 1 and not n.startswith("alpha"):
+                p.normal_(0, 0.05, generator=g)
+    bg = torch.rand(opt.shading_color_channel_num, generator=g)
+    wt = torch.randn(1, R, opt.shading_color_channel_num, generator=g)
+    drv, leaves = rf.reference_hot_path(kind, opt, tables, agg.state_dict())
+    f32 = lambda v: torch.tensor([v], dtype=torch.float32)
+    bg_r = bg.clone().requires_grad_(True)
+    out = drv.forward(cam["campos"], raydir, bg_color=bg_r, camrotc2w=cam["camrotc2w"], pixel_idx=pix, near=f32(cam["near"]),
+                      far=f32(cam["far"]), h=torch.tensor([cam["h"]]), w=torch.tensor([cam["w"]]),
+                      intrinsic=torch.from_numpy(cam["intrinsic"])[None])
+    loss_fn = lambda o: (o["coarse_raycolor"] * wt).sum() + (o["coarse_point_opacity"] ** 2).sum() * 0.1
+    ref = pipeline_ref.run(opt, tables, cam_o, raydir, bg, agg.state_dict(), loss_fn=loss_fn, frustum_pix=pix if kind == "frustum" else None)
+    assert 0 < int(ref["ray_mask"].sum()) < R and float(ref["coarse_is_background"].min()) < 0.5
+    for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading", "ray_mask"):
+        assert out[k].shape == ref[k].shape and torch.equal(out[k].detach(), ref[k]), k
+    params = dict(drv.aggregator.named_parameters())
+    names = list(leaves) + ["bg_color"] + list(params)
+    grads = torch.autograd.grad(loss_fn(out), list(leaves.values()) + [bg_r] + list(params.values()), allow_unused=True)
+    for n, gr in zip(names, grads):
+        assert gr is not None and rel_err(gr, ref["grads"][n]) < 1e-6, n
