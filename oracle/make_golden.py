@@ -6,6 +6,10 @@ TEST INFRASTRUCTURE (see oracle/__init__.py).  ``python -m oracle.make_golden`` 
   ray_march_ref.npz   ray_march (models/rendering/diff_ray_marching.py:509-555) outputs + gradients
   querier_ref.npz     lighting_fast_querier kernels (the reference's CUDA string host-compiled by oracle/build_ref.py,
                       canonical ascending-thread schedule) on the seeded ``tiny`` scene
+  driver_{world,frustum}_ref.npz  the reference's WHOLE per-ray driver (NeuralPointsRayMarching.forward + fill_invalid over
+                      NeuralPoints.forward over lighting_fast_querier over its kernels, unmodified PointAggregator / ray_march;
+                      oracle/ref_fragments.reference_hot_path) on 200 rays of the tiny scene: inputs, aggregator weights, outputs
+                      (``python -m oracle.make_golden driver`` writes only these)
   frustum_{dtu,crop}_ref.npz  the perspective-frustum lighting_fast_querier (query_point_indices.py) the same way, through
                       oracle/frustum_ref.py, on synthetic.frustum_case(...)   (``python -m oracle.make_golden frustum`` writes
                       only these)
@@ -20,7 +24,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from oracle import build_ref, frustum_ref as fr, querier_ref as qr, ref_import, torch_port as tp  # noqa: E402
+from oracle import build_ref, frustum_ref as fr, querier_ref as qr, ref_fragments as rf, ref_import, torch_port as tp  # noqa: E402
 from pointnerf_b200 import synthetic as syn  # noqa: E402
 from pointnerf_b200.options import make_opt  # noqa: E402
 
@@ -109,8 +113,54 @@ def frustum():
                             jitter_sample_loc=jit[1].numpy(), jitter_sample_loc_w=jit[2].numpy())
 
 
+def driver_case(kind, R=200):
+    """Seeded inputs of the driver golden files (also used by the tests that replay them)."""
+    import copy
+    if kind == "world":
+        opt, tables = syn.make_scene("tiny")
+        cam = syn.make_camera("tiny")
+        raydir, pix = syn.make_rays(cam, syn.random_pixels(cam, R, seed=5))
+    else:
+        opt, _, cam, pix = syn.frustum_case("dtu")
+        _, tables = syn.make_scene("tiny")
+        pix, raydir = pix[:, :R].contiguous(), torch.zeros(1, R, 3)
+    opt = copy.copy(opt)
+    opt.is_train = 0
+    g = torch.Generator().manual_seed(1)
+    bg = torch.rand(opt.shading_color_channel_num, generator=g)
+    return opt, tables, cam, raydir, pix, bg
+
+
+def driver():
+    torch.manual_seed(0)
+    agg = tp.AggregatorPort(syn.config_opt("tiny"))
+    g = torch.Generator().manual_seed(3)
+    with torch.no_grad():
+        agg.alpha_branch[0].bias.fill_(60.0)                  # a live density head (transmittance decays along the ray)
+        for n, p in agg.named_parameters():
+            if p.dim() == 1 and not n.startswith("alpha"):
+                p.normal_(0, 0.05, generator=g)
+    sd = agg.state_dict()
+    np.savez_compressed(os.path.join(OUT, "driver_weights.npz"), **{k: v.numpy() for k, v in sd.items()})
+    for kind in ("world", "frustum"):
+        opt, tables, cam, raydir, pix, bg = driver_case(kind)
+        drv, _ = rf.reference_hot_path(kind, opt, tables, sd)
+        f32 = lambda v: torch.tensor([v], dtype=torch.float32)
+        with torch.no_grad():
+            out = drv.forward(cam["campos"], raydir, bg_color=bg, camrotc2w=cam["camrotc2w"], pixel_idx=pix, near=f32(cam["near"]),
+                              far=f32(cam["far"]), h=torch.tensor([cam["h"]]), w=torch.tensor([cam["w"]]),
+                              intrinsic=torch.from_numpy(cam["intrinsic"])[None])
+        assert float(out["coarse_is_background"].min()) < 0.5 and 0 < int(out["ray_mask"].sum()) < pix.shape[1]
+        np.savez_compressed(os.path.join(OUT, "driver_%s_ref.npz" % kind), raydir=raydir.numpy(), pixel_idx=pix.numpy(), bg=bg.numpy(),
+                            **{k: out[k].numpy() for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background",
+                                                           "coarse_mask", "queried_shading", "ray_mask")})
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["driver"]:
+        driver()
+        sys.exit(0)
     if sys.argv[1:] == ["frustum"]:
         frustum()
         sys.exit(0)
@@ -119,5 +169,6 @@ if __name__ == "__main__":
     ray_march()
     querier()
     frustum()
+    driver()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

@@ -28,6 +28,16 @@ from .query_frustum import lighting_fast_querier as lighting_fast_querier_p
 from .ray_march import alpha_blend, radiance_render, ray_dist_from_samples, ray_march, ray_march_compact
 
 
+def _as_reference_scalar(v, reduce):
+    """How NeuralPoints.forward of the reference hands near / far / h / w to the frustum querier (neural_points.py:786):
+    ``torch.min|max(v).cpu().numpy()``, a 0-d numpy array whose dtype (float32, int64) steers numpy's promotion in
+    get_hyperparameters; python numbers and numpy values pass through."""
+    if isinstance(v, (int, float, np.generic, np.ndarray)):
+        return v
+    t = torch.as_tensor(v)
+    return (t.min() if reduce == "min" else t.max()).cpu().numpy()
+
+
 class NeuralPoints(nn.Module):
     def __init__(self, num_channels, size, opt, device, checkpoint=None, feature_init_method='rand', reg_weight=0.,
                  feedforward=0):
@@ -155,11 +165,14 @@ class NeuralPoints(nn.Module):
             near = float(near) if isinstance(near, (int, float)) else float(torch.as_tensor(near).min())
             far = float(far) if isinstance(far, (int, float)) else float(torch.as_tensor(far).max())
         else:   # the frustum grid's voxel size is numpy arithmetic on these: tensors become 0-d arrays like :786
-            near = near if isinstance(near, (int, float)) else torch.as_tensor(near).min().cpu().numpy()
-            far = far if isinstance(far, (int, float)) else torch.as_tensor(far).max().cpu().numpy()
+            near, far = _as_reference_scalar(near, "min"), _as_reference_scalar(far, "max")
         pixel_idx = inputs.get("pixel_idx")
+        h, w, intrinsic = inputs.get("h"), inputs.get("w"), inputs.get("intrinsic")
+        if getattr(self.opt, "wcoord_query", 1) <= 0:
+            h, w = _as_reference_scalar(h, "max"), _as_reference_scalar(w, "max")
+            intrinsic = intrinsic.cpu().numpy()[0] if torch.is_tensor(intrinsic) else intrinsic        # :786
         sample_pidx, sample_loc, ray_mask_tensor, xyz_pers, sample_loc_w, sample_ray_dirs, vsize = self.get_point_indices(
-            inputs, camrotc2w, campos, pixel_idx, near, far, inputs.get("h"), inputs.get("w"), inputs.get("intrinsic"))
+            inputs, camrotc2w, campos, pixel_idx, near, far, h, w, intrinsic)
         sample_pnt_mask = sample_pidx >= 0
         B, R, SR, K = sample_pidx.shape
         flat = torch.clamp(sample_pidx, min=0).view(-1).long()
@@ -281,9 +294,10 @@ class NeuralPointsRayMarching(nn.Module):
             raise NotImplementedError("wcoord_query = 0 queries by pixel: pass pixel_idx, h, w and intrinsic (the ray-direction "
                                       "only callers - render_frame, RayShardedStep - are world-coordinate)")
         q = nps.querier
-        near = near if isinstance(near, (int, float)) else torch.as_tensor(near).min().cpu().numpy()
-        far = far if isinstance(far, (int, float)) else torch.as_tensor(far).max().cpu().numpy()
-        hp = q.get_hyperparameters(h, w, np.asarray(intrinsic), near, far)
+        near, far = _as_reference_scalar(near, "min"), _as_reference_scalar(far, "max")
+        h, w = _as_reference_scalar(h, "max"), _as_reference_scalar(w, "max")
+        intrinsic = intrinsic.cpu().numpy()[0] if torch.is_tensor(intrinsic) else np.asarray(intrinsic)   # neural_points.py:786
+        hp = q.get_hyperparameters(h, w, intrinsic, near, far)
         xp = xyz_pers if xyz_pers is not None else _query.w2pers(nps.xyz.detach(), camrotc2w[0], campos[0])
         raw = q.query_raw(pixel_idx.reshape(-1, 2).to(torch.int32).contiguous(), xp.reshape(-1, 3), hp)
         pidx, loc_pers = raw["sample_pidx"], raw["sample_loc"]                    # [R,SR,K], [R,SR,3]

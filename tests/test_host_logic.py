@@ -54,3 +54,21 @@ def test_frustum_driver_needs_pixels():
     m.neural_points = NeuralPoints(o.point_features_dim, 0, o, cpu)
     with pytest.raises(NotImplementedError, match="pixel"):
         m.sample(torch.zeros(1, 3), torch.zeros(1, 4, 3), torch.eye(3)[None], 0.1, 1.0)
+
+
+def test_scalars_reach_the_frustum_querier_as_in_the_reference():
+    """near / far / h / w arrive as tensors from the data loader; the reference turns them into 0-d numpy arrays
+    (neural_points.py:786) whose dtypes (float32, int64) steer numpy's promotion in get_hyperparameters."""
+    from pointnerf_b200.neural_points import _as_reference_scalar
+    h = _as_reference_scalar(torch.tensor([48, 48]), "max")
+    n = _as_reference_scalar(torch.tensor([0.3, 0.4]), "min")
+    assert isinstance(h, np.ndarray) and h.shape == () and h.dtype == np.int64 and int(h) == 48
+    assert isinstance(n, np.ndarray) and n.dtype == np.float32 and float(n) == float(np.float32(0.3))
+    assert _as_reference_scalar(48, "max") == 48 and _as_reference_scalar(0.3, "min") == 0.3
+    opt, _, cam, _ = syn.frustum_case("crop")
+    a = query_frustum.frustum_hyperparameters(opt, h=_as_reference_scalar(torch.tensor([cam["h"]]), "max"),
+                                              w=_as_reference_scalar(torch.tensor([cam["w"]]), "max"), intrinsic=cam["intrinsic"],
+                                              near_depth=_as_reference_scalar(torch.tensor([cam["near"]]), "min"),
+                                              far_depth=_as_reference_scalar(torch.tensor([cam["far"]]), "max"))
+    b = query_frustum.frustum_hyperparameters(opt, cam["h"], cam["w"], cam["intrinsic"], cam["near"], cam["far"])
+    assert a["scaled_vdim"].tolist() == b["scaled_vdim"].tolist() and np.allclose(a["vsize"], b["vsize"], rtol=1e-6)

@@ -541,3 +541,41 @@ def test_reference_hot_path_whole_equals_pipeline_oracle(kind):
     grads = torch.autograd.grad(loss_fn(out), list(leaves.values()) + [bg_r] + list(params.values()), allow_unused=True)
     for n, gr in zip(names, grads):
         assert gr is not None and rel_err(gr, ref["grads"][n]) < 1e-6, n
+
+
+@pytest.mark.parametrize("kind", ["world", "frustum"])
+def test_golden_reference_driver(kind):
+    """tests/golden/driver_*_ref.npz hold what the reference's WHOLE per-ray driver returned in the build container
+    (oracle/make_golden.py: driver); the pipeline oracle replays them bit for bit wherever the suite runs."""
+    from oracle import frustum_ref, make_golden, pipeline_ref
+    if kind == "frustum" and not frustum_ref.available():
+        pytest.skip("oracle/_ref/libpn_ref_querier_frustum.so not built")
+    z, wts = _load("driver_%s_ref.npz" % kind), _load("driver_weights.npz")
+    opt, tables, cam, raydir, pix, bg = make_golden.driver_case(kind)
+    assert np.array_equal(raydir.numpy(), z["raydir"]) and np.array_equal(pix.numpy(), z["pixel_idx"]) and np.array_equal(bg.numpy(), z["bg"])
+    if kind == "frustum":
+        cam = dict(cam, near=np.asarray(cam["near"], np.float32), far=np.asarray(cam["far"], np.float32))
+    sd = {k: torch.from_numpy(wts[k]) for k in wts.files}
+    out = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, need_grads=False, frustum_pix=pix if kind == "frustum" else None)
+    for k in ("coarse_raycolor", "coarse_point_opacity", "coarse_is_background", "coarse_mask", "queried_shading", "ray_mask"):
+        assert np.array_equal(out[k].numpy(), z[k]), k
+
+
+@needs_ref
+def test_frustum_hyperparameters_with_the_data_loader_types():
+    """h / w as int64 and near / far as float32 0-d arrays (what NeuralPoints.forward makes of the data loader's tensors,
+    neural_points.py:786): numpy then evaluates the image-plane extents in float64 - the product follows."""
+    import types
+    from oracle import ref_fragments as rf
+    from pointnerf_b200.neural_points import _as_reference_scalar as conv
+    from pointnerf_b200.query_frustum import frustum_hyperparameters
+    ghp = rf.function("models/neural_points/query_point_indices.py", "get_hyperparameters", class_name="lighting_fast_querier",
+                      extra_globals={"np": np, "np_to_gpuarray": lambda *a: list(a)})
+    for name in syn.FRUSTUM_CASES:
+        o, _, cam, _ = syn.frustum_case(name)
+        h, w = conv(torch.tensor([cam["h"]]), "max"), conv(torch.tensor([cam["w"]]), "max")
+        near, far = conv(torch.tensor([cam["near"]]), "min"), conv(torch.tensor([cam["far"]]), "max")
+        got = ghp(types.SimpleNamespace(opt=o, inverse=0), h, w, cam["intrinsic"], near, far)
+        want = frustum_hyperparameters(o, h, w, cam["intrinsic"], near, far)
+        for i, k in ((0, "radius_limit"), (1, "depth_limit"), (2, "ranges"), (3, "vsize"), (4, "vdim"), (5, "scaled_vsize"), (6, "scaled_vdim")):
+            assert np.array_equal(np.asarray(got[i]), np.asarray(want[k])) and np.asarray(got[i]).dtype == np.asarray(want[k]).dtype, (name, k)
