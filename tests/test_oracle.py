@@ -495,8 +495,9 @@ def test_reference_frustum_querier_class_equals_oracle_and_golden(name):
 
 
 @needs_ref
-@pytest.mark.parametrize("kind", ["world", "frustum"])
-def test_reference_hot_path_whole_equals_pipeline_oracle(kind):
+@pytest.mark.parametrize("kind,kw", [("world", {}), ("frustum", {}), ("world", dict(agg_intrp_order=1)),
+                                     ("frustum", dict(point_features_dim=63))])   # last: the DTU feed-forward trainer's shape
+def test_reference_hot_path_whole_equals_pipeline_oracle(kind, kw):
     """The reference's per-ray driver assembled from ITS OWN code (NeuralPointsRayMarching.forward + fill_invalid over
     NeuralPoints.forward over lighting_fast_querier over its kernels, with the unmodified PointAggregator / ray_march;
     oracle/ref_fragments.reference_hot_path) against oracle/pipeline_ref.run - the oracle every GPU step test compares with:
@@ -516,6 +517,11 @@ def test_reference_hot_path_whole_equals_pipeline_oracle(kind):
         cam_o = dict(cam, near=np.asarray(cam["near"], np.float32), far=np.asarray(cam["far"], np.float32))
     opt = copy.copy(opt)
     opt.is_train = 0
+    for k, v in kw.items():
+        setattr(opt, k, v)
+    if opt.point_features_dim != tables["points_embeding"].shape[-1]:
+        tables = dict(tables, points_embeding=torch.rand(1, tables["xyz"].shape[0], opt.point_features_dim,
+                                                         generator=torch.Generator().manual_seed(9)) - 0.5)
     g = torch.Generator().manual_seed(1)
     agg = tp.AggregatorPort(opt)
     with torch.no_grad():
