@@ -124,9 +124,10 @@ int pn_grid_build(const float* xyz, int64_t n_points, const pn_grid_params* para
  *   hit_count     int32[R]  number of kept samples (<= SR); ray_mask of :655 is hit_count > 0
  * ---------------------------------------------------------------------------------------------- */
 /* Jittered candidate depths (the per-ray part of near_far_linear_ray_generation, diff_ray_marching.py:369-386):
- *   seg = seg_base[d] * (1 + jitter * (uniform[r,d] - 0.5)); ends = near + cumsum(seg) (left to right, as the CPU chain);
+ *   seg = seg_base[d] * (1 + jitter * (uniform[r,d] - 0.5)); ends = near + cumsum(seg), the running sum accumulated in
+ *   DOUBLE left to right and rounded to float per element - what torch.cumsum computes on the host, the canonical chain;
  *   ts[r,d] = (ends[d-1] + ends[d]) / 2 with ends[-1] = near.  seg_base float[D] = t[1:] - t[:-1] of the linspace chain
- *   (caller, D+1 elements); uniform float[R,D] stands for the torch.rand draw of :373; ts float[R,D]. */
+ *   (caller, D+1 elements); uniform float[R,D] stands for the torch.rand draw of :373 (NULL: no jitter); ts float[R,D]. */
 int pn_sample_depths(const float* seg_base, const float* uniform, int64_t n_rays, int32_t D, float near_depth,
                      float jitter, float* ts, void* stream);
 int pn_ray_sample(const float* campos, const float* raydir, const float* ts, int64_t ts_rows,
@@ -304,6 +305,14 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
                     const pn_agg_weights* grad_w, int scatter_rows, float* grad_embedding,
                     float* grad_color, float* grad_dir, float* grad_conf, int32_t* touched_ids,
                     int32_t* n_touched, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* LeakyReLU activation pattern of a saved forward (what pn_agg_backward will differentiate through): 1 where the unit's
+ * output is > 0 (derivative 1), 0 where the derivative is leaky_slope.  pair_signs uint8[4, M, W]: block1.0, block1.2,
+ * block3.0, block3.2 (compact pair rows, ascending (slot, k)); sample_signs uint8[3, S, C]: color_branch.0 / .2 / .4 (compact
+ * sample rows).  The MLP is piecewise linear, so a reference backward evaluated under the SAME pattern is comparable at the
+ * full tolerance on every ray, units at a kink included (point_aggregators.py:547-571, 635). */
+int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S, int64_t M,
+                            uint8_t* pair_signs, uint8_t* sample_signs, void* stream);
 
 /* Makes `stream` wait for the point where the most recent pn_agg_backward on this device had produced its per-row
  * gradients (grad_embedding / grad_color / grad_dir / grad_conf, touched_ids, n_touched) - BEFORE the weight-gradient GEMMs

@@ -20,6 +20,13 @@ import torch.nn as nn
 TAU = 2e-5   # several times the forward rounding error of an fp32-class implementation (3xTF32 tensor cores: ~2e-6 of max) relative to the layer rms
 
 
+# Frozen-pattern parity (torch_port.LeakyReLUProbe, pipeline_ref.run(frozen_signs=...)): the oracle's backward is evaluated
+# under the activation pattern of the implementation being checked.  The pattern may differ from the oracle's own sign test
+# only on units with |pre-activation| < PATTERN_TOL * rms(layer): flipping such a unit moves the FORWARD by less than the
+# forward tolerance itself (1e-4 relative), i.e. both patterns are correct answers at the stated precision.
+PATTERN_TOL = 1e-4
+
+
 class KinkProbe:
     def __init__(self, agg, tau=TAU):
         self.tau = tau

@@ -15,7 +15,7 @@ from . import querier_ref, torch_port as tp
 
 
 def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend="port", uniform=None, need_grads=True,
-        loss_fn=None, dtype=torch.float32, kink_tau=None, frustum_pix=None):
+        loss_fn=None, dtype=torch.float32, kink_tau=None, frustum_pix=None, frozen_signs=None):
     """tables: dict from pointnerf_b200.synthetic.make_scene (torch-CPU); cam: make_camera; raydir [1,R,3];
     bg_color [C]; agg_state: state_dict of the aggregator (reference names).  loss = sum(coarse_raycolor * loss_weight)
     unless ``loss_fn(out)`` is given.  Returns the fill_invalid dictionary plus query intermediates and ``grads``.
@@ -29,6 +29,12 @@ def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend
     ``kink_tau``: additionally report ``out["kink_rays"]`` (bool [1,R_full]) - rays holding a sample with a hidden unit at
     a LeakyReLU kink (oracle/kinks.py); gradient tests give those rays zero loss weight.
 
+    ``frozen_signs`` = (pair_signs [4,M,W], sample_signs [3,S,C]) from pn_agg_activation_signs: the aggregator's LeakyReLUs
+    run with that activation pattern frozen (torch_port.LeakyReLUProbe), i.e. the reference backward CONDITIONED on the
+    pattern the checked forward produced; ``out["pattern_disagreement"]`` = (units where it differs from the oracle's own
+    sign test, all units, the largest |pre-activation| / rms(layer) among those) - the tests hold the last number to
+    kinks.TAU, so freezing can only adjudicate units at a kink, never hide an error.
+
     ``frustum_pix`` (int32 [1,R,2]): query with the perspective-frustum querier (oracle/frustum_ref.py, wcoord_query = 0)
     instead of the world-coordinate one; ``raydir`` is then unused (pers2w gives per-sample directions) and ``uniform`` is
     the [1,R',SR] draw of its sample jitter."""
@@ -39,6 +45,8 @@ def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend
     agg = tp.AggregatorPort(opt)
     agg.load_state_dict({k: v.detach().cpu().clone() for k, v in agg_state.items()})
     agg = agg.to(dt)
+    if frozen_signs is not None:
+        agg.freeze_pattern(frozen_signs[0], frozen_signs[1])
 
     if frustum_pix is not None:
         from . import frustum_ref
@@ -70,6 +78,8 @@ def run(opt, tables, cam, raydir, bg_color, agg_state, loss_weight=None, backend
     ray_color, _, opacity, acc_T, blend_w, bg_T, _ = tp.ray_march(ray_dist, ray_valid, decoded, bg)
     shading = torch.logical_not(torch.any(ray_valid, dim=-1, keepdim=True)).repeat(1, 1, 3).to(dt)
     out = tp.fill_invalid(ray_mask, bg, ray_color, bg_T, opacity, shading)
+    if frozen_signs is not None:
+        out["pattern_disagreement"] = agg.pattern_disagreement()
     out.update(kink_rays=kink_rays, ray_mask=ray_mask, sample_pidx=pidx, sample_loc_w=loc_w, sample_loc=loc_pers, decoded_features=decoded.detach(),
                ray_valid=ray_valid, ray_dist=ray_dist.detach(), weight=weight, conf_coefficient=conf_coef, extras=extras,
                compact=dict(ray_color=ray_color.detach(), opacity=opacity.detach(), acc_T=acc_T.detach(), bg_T=bg_T.detach()))

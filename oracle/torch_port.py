@@ -98,6 +98,27 @@ def gather_point_tables(sample_pidx, xyz, xyz_pers, embedding, color, pdir, conf
 # --------------------------------------------------------------------------
 # aggregator
 # --------------------------------------------------------------------------
+class LeakyReLUProbe(nn.LeakyReLU):
+    """nn.LeakyReLU (the reference's activation) that can (a) record its pre-activations and (b) run with a FROZEN
+    activation pattern: ``pattern`` bool [rows, units] - True: derivative 1, False: negative_slope - replaces the sign
+    test.  Forward and backward are then linear in the input, the same linear map a kernel whose forward produced that
+    pattern differentiates through; where pattern == (x > 0) nothing changes.  Units at a kink (|x| within rounding of 0)
+    are where two correct fp32 implementations may disagree on the pattern, and ONLY there may it differ (checked by the
+    tests through ``last_pre``)."""
+    pattern = None
+    record = False
+    last_pre = None
+
+    def forward(self, x):
+        if self.record:
+            self.last_pre = x.detach()
+        if self.pattern is None:
+            return F.leaky_relu(x, self.negative_slope)
+        pat = self.pattern.to(x.device)
+        assert pat.shape == x.shape, (pat.shape, x.shape)
+        return x * torch.where(pat, torch.ones((), dtype=x.dtype), torch.full((), self.negative_slope, dtype=x.dtype))
+
+
 class AggregatorPort(nn.Module):
     """Restates PointAggregator (models/aggregators/point_aggregators.py:218-348, 421-429, 488-646,
     724-816) for the in-scope configuration, with the reference's parameter names so that
@@ -119,13 +140,42 @@ class AggregatorPort(nn.Module):
         assert int(W / 2) == C, "fork: colour branch ends at shading_feature_num/2 channels (:335,343)"
 
         def act():
-            return nn.LeakyReLU(inplace=False)
+            return LeakyReLUProbe(inplace=False)
 
         self.block1 = nn.Sequential(nn.Linear(in1, W), act(), nn.Linear(W, W), act())
         self.block3 = nn.Sequential(nn.Linear(in3, W), act(), nn.Linear(W, W), act())
         self.alpha_branch = nn.Sequential(nn.Linear(W, 1))
         self.color_branch = nn.Sequential(nn.Linear(inc, C), act(), nn.Linear(C, C), act(),
                                           nn.Linear(C, C), act())
+
+    def activations(self):
+        """The seven LeakyReLUs in evaluation order: block1 (2), block3 (2) on pair rows; color_branch (3) on sample rows."""
+        return [self.block1[1], self.block1[3], self.block3[1], self.block3[3],
+                self.color_branch[1], self.color_branch[3], self.color_branch[5]]
+
+    def freeze_pattern(self, pair_signs, sample_signs, record=True):
+        """pair_signs [4,M,W], sample_signs [3,S,C] (bool / uint8; pn_agg_activation_signs layout) or (None, None)."""
+        acts = self.activations()
+        for i, a in enumerate(acts):
+            src = pair_signs if i < 4 else sample_signs
+            a.pattern = None if src is None else torch.as_tensor(src[i if i < 4 else i - 4]).bool().cpu()
+            a.record = record
+
+    def pattern_disagreement(self):
+        """After a frozen forward with record=True: (units whose frozen pattern differs from sign(pre-activation), total
+        units, max |pre| / rms(layer) over the differing units)."""
+        n_diff, n_all, worst = 0, 0, 0.0
+        for a in self.activations():
+            if a.pattern is None or a.last_pre is None:
+                continue
+            x = a.last_pre.double()
+            diff = a.pattern != (x > 0)
+            n_diff += int(diff.sum())
+            n_all += x.numel()
+            if diff.any():
+                rms = x.pow(2).mean().sqrt().clamp_min(1e-30)
+                worst = max(worst, float((x.abs()[diff] / rms).max()))
+        return n_diff, n_all, worst
 
     def forward(self, sampled_color, sampled_Rw2c, sampled_dir, sampled_conf, sampled_embedding,
                 sampled_xyz_pers, sampled_xyz, sample_pnt_mask, sample_loc, sample_loc_w,

@@ -105,6 +105,7 @@ def _declare(lib):
         "pn_compact_workspace_bytes": (c_int64, [c_int64]),
         "pn_compact_samples": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, c_int64, P]),
         "pn_agg_saved_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64]),
+        "pn_agg_activation_signs": (c_int, [POINTER(AggParams), P, c_int64, c_int64, c_int64, P, P, P]),
         "pn_agg_workspace_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64, c_int64, c_int]),
         "pn_agg_forward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, P, c_int64, P,
                                    c_int64, P]),

@@ -93,6 +93,8 @@ class _AggCall:
         self.grad_flat = None                 # backward: the MLP weight gradients, one contiguous buffer
         self.flat_tail, self.flat_tail_off = 0, 0   # extra zeroed floats appended to grad_flat for the caller, and where they start
         self.compact = None                   # optional CompactSamples built ahead of the call
+        self.export_signs = False             # checker hook: keep the forward's LeakyReLU pattern (pn_agg_activation_signs)
+        self.signs = None                     # (uint8 [4,M,W] pair layers, uint8 [3,S,C] colour layers)
 
 
 def _weights_struct(tensors):
@@ -190,6 +192,12 @@ class _AggFunction(torch.autograd.Function):
             _lib.check(lib.pn_agg_forward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(decoded),
                                           _lib.ptr(weight_out), _lib.ptr(saved), saved_bytes, _lib.ptr(ws), ws_bytes,
                                           _lib.stream()), "pn_agg_forward")
+            if call.export_signs:
+                ps = torch.empty((4, call.M, p.W), dtype=torch.uint8, device=dev)
+                ss = torch.empty((3, call.S, p.C), dtype=torch.uint8, device=dev)
+                _lib.check(lib.pn_agg_activation_signs(ctypes.byref(p), _lib.ptr(saved), saved_bytes, call.S, call.M, _lib.ptr(ps),
+                                                       _lib.ptr(ss), _lib.stream()), "pn_agg_activation_signs")
+                call.signs = (ps, ss)
         ctx.call, ctx.saved, ctx.saved_bytes = call, saved, saved_bytes
         ctx.tables = (embedding, color, pdir, conf)
         ctx.weights = weights
@@ -380,6 +388,7 @@ class PointAggregator(nn.Module):
         call.collect_touched = bool(getattr(self, "collect_touched", False))
         call.flat_tail = int(getattr(self, "flat_tail_floats", 0))
         call.compact = work_lists             # CompactSamples of sample_pidx queued earlier (None: built here, with its sync)
+        call.export_signs = bool(getattr(self, "export_signs", False))
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
         self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)
         weight = weight.view(R, SR, K) if want_weight else None
@@ -413,6 +422,8 @@ class PointAggregator(nn.Module):
                         pidx, sample_loc_w.detach().reshape(n_slots, 3).contiguous(),
                         sample_loc.detach().reshape(n_slots, 3).contiguous(),
                         sample_ray_dirs.detach().reshape(n_slots, 3).contiguous(), n_slots, T, False, want_w)
+        call.export_signs = bool(getattr(self, "export_signs", False))
+        self.last_call = call
         decoded, weight = _AggFunction.apply(call, sampled_embedding.reshape(T, -1), sampled_color.reshape(T, 3),
                                              sampled_dir.reshape(T, 3), sampled_conf.reshape(T), *self._weights())
         if not want_w:

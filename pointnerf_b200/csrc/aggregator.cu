@@ -63,6 +63,7 @@ static int64_t max3(int64_t a, int64_t b, int64_t c) { return a > b ? (a > c ? a
 }  // namespace pn
 
 using namespace pn;
+#define PN_TRY(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 
 extern "C" int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t M) {
     AggDims d;
@@ -157,6 +158,45 @@ extern "C" int64_t pn_agg_workspace_bytes(const pn_agg_params* p, int64_t S, int
     return backward ? carve_bwd(d, S, M, T, nullptr, 0, nullptr) : carve_fwd(d, nullptr, 0, nullptr);
 }
 
+// ---- LeakyReLU activation signs of a saved forward ------------------------------------------------------------
+// The MLP is piecewise linear: its backward is a function of the forward's activation pattern.  This entry exports the
+// pattern the backward of THIS forward will use (unit > 0 -> slope 1, else leaky_slope), so that a checker can evaluate a
+// reference backward conditioned on the same pattern: gradients are then comparable on every ray, including units whose
+// pre-activation is within rounding of zero (oracle/kinks.py).
+namespace pn {
+__global__ void __launch_bounds__(256) act_signs_kernel(const float* __restrict__ src, int64_t rows, int ld, int cols,
+                                                        uint8_t* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows * cols; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / cols;
+        const int c = (int)(i - r * cols);
+        out[i] = src[r * ld + c] > 0.f ? 1 : 0;
+    }
+}
+}  // namespace pn
+extern "C" int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S, int64_t M,
+                                       uint8_t* pair_signs, uint8_t* sample_signs, void* stream) {
+    AggDims d;
+    PN_TRY(make_dims(p, d));
+    PN_CHECK_ARG(saved && pair_signs && sample_signs, "pn_agg_activation_signs: null argument");
+    PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_activation_signs: saved buffer too small");
+    if (S <= 0 || M <= 0) return PN_OK;
+    Saved sv;
+    carve_saved(d, S, M, const_cast<void*>(saved), saved_bytes, &sv);
+    cudaStream_t st = (cudaStream_t)stream;
+    const float* pl[4] = {sv.H1, sv.X3, sv.H3, sv.H4};
+    const int pld[4] = {d.W, d.in3p, d.W, d.W};
+    for (int l = 0; l < 4; ++l) {
+        act_signs_kernel<<<(unsigned)(cdiv(M * d.W, 256) < 4096 ? cdiv(M * d.W, 256) : 4096), 256, 0, st>>>(pl[l], M, pld[l], d.W, pair_signs + (int64_t)l * M * d.W);
+        PN_LAUNCH_CHECK("act_signs");
+    }
+    const float* sl[3] = {sv.C1, sv.C2, sv.C3};
+    for (int l = 0; l < 3; ++l) {
+        act_signs_kernel<<<(unsigned)(cdiv(S * d.C, 256) < 4096 ? cdiv(S * d.C, 256) : 4096), 256, 0, st>>>(sl[l], S, d.C, d.C, sample_signs + (int64_t)l * S * d.C);
+        PN_LAUNCH_CHECK("act_signs");
+    }
+    return PN_OK;
+}
+
 static GemmNT nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int Kd,
                  const float* bias, int leaky, float slope) {
     GemmNT g;
@@ -164,7 +204,6 @@ static GemmNT nt(const float* A, int64_t lda, const float* B, int64_t ldb, float
     g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr; g.Bimg = nullptr;
     return g;
 }
-#define PN_TRY(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
 
 extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w, float* decoded,
                               float* weight_out, void* saved, int64_t saved_bytes, void* workspace, int64_t workspace_bytes,

@@ -350,9 +350,11 @@ __global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict
 using namespace pn;
 
 namespace pn {
-// Jittered mid-point depths: the scalar chain of near_far_linear_ray_generation
-// (diff_ray_marching.py:369-386) with every product and sum rounded separately and the running sum taken left to right,
-// i.e. exactly what the reference's torch ops compute on the CPU (torch's device cumsum associates differently).
+// Jittered mid-point depths: the scalar chain of near_far_linear_ray_generation (diff_ray_marching.py:369-386) as the
+// reference's torch ops evaluate it ON THE HOST - the canonical chain: every product and sum is rounded
+// separately in fp32, except the running sum of torch.cumsum, which torch's CPU kernel accumulates in DOUBLE
+// (at::acc_type<float, /*is_cuda=*/false>) left to right and rounds to fp32 per element.  (torch's CUDA cumsum is a
+// tree scan in fp32 whose association depends on the launch geometry: not reproducible, not a parity target.)
 __global__ void __launch_bounds__(256) sample_depths_kernel(const float* __restrict__ seg_base, const float* __restrict__ uniform,
                                                             int64_t n_rays, int D, float near, float jitter, float* __restrict__ ts) {
     // one warp per ray: lanes load / store 32 consecutive depths (coalesced) and form their segment lengths in parallel;
@@ -361,19 +363,20 @@ __global__ void __launch_bounds__(256) sample_depths_kernel(const float* __restr
     int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (r >= n_rays) return;
-    const float* u = uniform + r * D;
+    const float* u = uniform ? uniform + r * D : nullptr;
     float* out = ts + r * D;
-    float c = 0.f, prev_end = __fadd_rn(near, 0.f);
+    double c = 0.0;
+    float prev_end = __fadd_rn(near, 0.f);
     for (int d0 = 0; d0 < D; d0 += 32) {
         const int d = d0 + lane;
         float seg = 0.f;
-        if (d < D) seg = __fmul_rn(seg_base[d], __fadd_rn(1.f, __fmul_rn(jitter, __fsub_rn(u[d], 0.5f))));
+        if (d < D) seg = __fmul_rn(seg_base[d], __fadd_rn(1.f, __fmul_rn(jitter, __fsub_rn(u ? u[d] : 0.5f, 0.5f))));
         float mine = 0.f;
         const int n = D - d0 < 32 ? D - d0 : 32;
         for (int j = 0; j < n; ++j) {
             const float v = __shfl_sync(0xffffffffu, seg, j);
-            c = __fadd_rn(c, v);
-            const float end = __fadd_rn(near, c);
+            c = __dadd_rn(c, (double)v);
+            const float end = __fadd_rn(near, (float)c);
             const float mid = __fmul_rn(__fadd_rn(prev_end, end), 0.5f);
             if (lane == j) mine = mid;
             prev_end = end;
@@ -385,7 +388,7 @@ __global__ void __launch_bounds__(256) sample_depths_kernel(const float* __restr
 
 extern "C" int pn_sample_depths(const float* seg_base, const float* uniform, int64_t n_rays, int32_t D, float near_depth, float jitter,
                                 float* ts, void* stream) {
-    PN_CHECK_ARG(seg_base && uniform && ts && D > 0, "pn_sample_depths: bad argument");
+    PN_CHECK_ARG(seg_base && ts && D > 0, "pn_sample_depths: bad argument");   // uniform == NULL: no jitter (every draw 0.5)
     if (n_rays <= 0) return PN_OK;
     sample_depths_kernel<<<(unsigned)cdiv(n_rays * 32, 256), 256, 0, (cudaStream_t)stream>>>(seg_base, uniform, n_rays, D, near_depth, jitter, ts);
     PN_LAUNCH_CHECK("sample_depths");

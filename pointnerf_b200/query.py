@@ -31,35 +31,37 @@ def _depth_edges(dev, D, near, far):
     if e is None:
         if len(_EDGE_CACHE) > 64:
             _EDGE_CACHE.clear()
-        t = torch.linspace(0, 1, D + 1, device=dev).view(1, -1)
+        # evaluated by the host's torch ops (the canonical chain) and uploaded once per (D, near, far)
+        t = torch.linspace(0, 1, D + 1).view(1, -1)
         e = near * (1 - t) + far * t
-        e = (e, (e[..., 1:] - e[..., :-1]).reshape(-1).contiguous())
+        e = (e.to(dev), (e[..., 1:] - e[..., :-1]).reshape(-1).contiguous().to(dev))
         _EDGE_CACHE[key] = e
     return e
 
 
 def middle_point_ts(raydir, D, near, far, jitter=0.0, uniform=None):
     """Depths of the candidate samples: the scalar chain of near_far_linear_ray_generation
-    (models/rendering/diff_ray_marching.py:369-386), every operation rounded separately like the reference's torch ops.
-    Without jitter every ray has the same depths and one row [1,1,D] is returned (torch ops on D elements); with jitter
-    [1,R,D] from ONE kernel (pn_sample_depths) whose running sum goes left to right - bit-identical to the CPU chain,
-    which torch's device cumsum is not guaranteed to be (``uniform`` stands for the torch.rand draw of :373)."""
+    (models/rendering/diff_ray_marching.py:369-386) as the reference's torch ops evaluate it on the HOST (the canonical
+    chain: fp32 ops rounded one by one, the cumsum accumulated in double and rounded per element - torch's device cumsum
+    is a tree scan whose association is not reproducible).  Without jitter every ray has the same depths and one row
+    [1,1,D] is returned; with jitter [1,R,D].  On the device both come from ONE kernel (pn_sample_depths), bit-identical
+    to the host chain (tests/test_gpu_query.py); ``uniform`` stands for the torch.rand draw of :373."""
     dev = raydir.device
     t, base = _depth_edges(dev, int(D), float(near), float(far))
     R = raydir.shape[1]
+    if jitter != 0.0 and uniform is None:
+        uniform = torch.rand((raydir.shape[0], R, D), device=dev)
+    if raydir.is_cuda and raydir.shape[0] == 1:
+        rows = R if jitter != 0.0 else 1
+        u = uniform.reshape(R, D).float().contiguous() if jitter != 0.0 else None
+        ts = torch.empty((1, rows, D), dtype=torch.float32, device=dev)
+        _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base), _lib.ptr(u), rows, D, float(near), float(jitter), _lib.ptr(ts),
+                                               _lib.stream()), "pn_sample_depths")
+        return ts
     if jitter == 0.0:
         seg = (t[..., 1:] - t[..., :-1]).view(1, 1, D) * torch.ones((1, 1, D), device=dev)
         rows = 1
     else:
-        if uniform is None:
-            uniform = torch.rand((raydir.shape[0], R, D), device=dev)
-        if uniform.is_cuda and raydir.shape[0] == 1:
-            # one kernel for the per-ray part ([R,D] tensors); sums run left to right like the CPU chain
-            u = uniform.reshape(R, D).float().contiguous()
-            ts = torch.empty((1, R, D), dtype=torch.float32, device=dev)
-            _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base), _lib.ptr(u), R, D, float(near), float(jitter), _lib.ptr(ts),
-                                                   _lib.stream()), "pn_sample_depths")
-            return ts
         seg = (t[..., 1:] - t[..., :-1]) * (1 + jitter * (uniform - 0.5))
         rows = R
     ends = torch.cumsum(seg, dim=2)

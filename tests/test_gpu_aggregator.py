@@ -72,18 +72,21 @@ def test_forward_backward_matches_oracle(cuda_dev, R, SR, K, seed, kw):
     g = torch.Generator().manual_seed(seed + 100)
     wt_dec = torch.randn(1, R, SR, opt.shading_color_channel_num + 1, generator=g)
     wt_conf = torch.randn(1, R, SR, K, generator=g)
-    # samples with a hidden unit AT a LeakyReLU kink carry no loss weight (oracle/kinks.py): the forward is compared on
-    # every sample, the gradients on the rest - at the full 1e-4 tolerance, weight gradients included
-    ins64 = {k: (v.double() if torch.is_tensor(v) and v.is_floating_point() else v) for k, v in ins.items()}
-    amb = kinks.probe(port, lambda a: a(ins64["sampled_color"], ins64["sampled_Rw2c"], ins64["sampled_dir"], ins64["sampled_conf"],
-                                        ins64["sampled_embedding"], ins64["sampled_xyz_pers"], ins64["sampled_xyz"],
-                                        ins64["sample_pnt_mask"], ins64["sample_loc"], ins64["sample_loc_w"],
-                                        ins64["sample_ray_dirs"], (0.004,) * 3, 0), ins["sample_pnt_mask"])
-    assert float(amb.float().mean()) < 0.8
-    wt_dec = wt_dec * (~amb)[..., None]
-    o_ref, g_ref = run(port, ins, torch.device("cpu"), wt_dec, wt_conf)
-    o_64, g_64 = run(copy.deepcopy(port).double(), ins, torch.device("cpu"), wt_dec, wt_conf, dtype=torch.float64)
+    # forward: against the unconditioned oracle.  backward: the oracle's autograd under the LeakyReLU pattern of OUR forward
+    # (pn_agg_activation_signs; the MLP is piecewise linear, oracle/kinks.py) - every sample carries loss weight
+    mod.export_signs = True
     o, gr = run(mod, ins, cuda_dev, wt_dec, wt_conf)
+    signs = tuple(t.cpu() for t in mod.last_call.signs)
+    o_ref, _ = run(port, ins, torch.device("cpu"), wt_dec, wt_conf)
+    port64 = copy.deepcopy(port).double()
+    o_64, _ = run(port64, ins, torch.device("cpu"), wt_dec, wt_conf, dtype=torch.float64)
+    port.freeze_pattern(*signs)
+    port64.freeze_pattern(*signs)
+    o_cnd, g_ref = run(port, ins, torch.device("cpu"), wt_dec, wt_conf)
+    _, g_64 = run(port64, ins, torch.device("cpu"), wt_dec, wt_conf, dtype=torch.float64)
+    n_diff, n_all, worst = port64.pattern_disagreement()
+    assert n_all > 0 and n_diff <= 1e-4 * n_all + 1 and worst < kinks.PATTERN_TOL, (n_diff, n_all, worst)
+    assert_close(o_cnd[0], o_ref[0], "conditioned oracle forward")
     assert o[0].shape == o_ref[0].shape and o[0].dtype == torch.float32
     assert torch.equal(o[1].cpu(), o_ref[1]) and o[1].dtype == torch.bool
     assert_close(o[0], o_ref[0], "decoded_features", want64=o_64[0])

@@ -77,8 +77,7 @@ def test_query_points_matches_oracle(tiny_scene, cuda_dev, train):
     ts_dev = query.middle_point_ts(raydir.to(d), opt.z_depth_dim, cam["near"], cam["far"], jitter=0.3 if train else 0.0,
                                    uniform=uniform.to(d) if train else None)
     ts_ref = ex["ts"]
-    if not torch.equal(ts_dev.cpu().expand_as(ts_ref), ts_ref):
-        pytest.skip("device cumsum rounds differently from the CPU chain on this box; covered by test_query_with_given_ts")
+    assert torch.equal(ts_dev.cpu().expand_as(ts_ref), ts_ref), "pn_sample_depths differs from the host chain (double-accumulated cumsum)"
     out = q.query_points(pix.to(d), None, tables["xyz"][None].to(d), None, cam["h"], cam["w"], cam["intrinsic"],
                          np.float32(cam["near"]), np.float32(cam["far"]), raydir.to(d), cam["campos"].to(d),
                          cam["camrotc2w"].to(d), uniform=uniform.to(d) if train else None)
@@ -107,6 +106,46 @@ def test_query_with_given_ts(tiny_scene, cuda_dev):
     # rays that hit occupancy but found no neighbour: all -1
     assert (raw["sample_pidx"].cpu()[~sel] == -1).all()
     assert int(raw["candidates"].item()) > 0
+
+
+def test_query_with_given_jittered_ts(tiny_scene, cuda_dev):
+    """The oracle's PER-RAY jittered depths [1,R,D] handed to the device query: positions, mask and neighbour slots
+    bit-identical (independent of how either side produces its depths)."""
+    import copy
+    opt, tables, cam = tiny_scene
+    opt = copy.copy(opt)
+    opt.is_train = 1
+    raydir, pix = syn.make_rays(cam, syn.random_pixels(cam, 900, seed=4))
+    uniform = torch.rand(1, raydir.shape[1], opt.z_depth_dim, generator=torch.Generator().manual_seed(21))
+    (pidx, loc_pers, loc_w, dirs, ray_mask, vsize, ranges), ex = _oracle(opt, tables, cam, raydir, uniform=uniform)
+    assert tuple(ex["ts"].shape) == (1, raydir.shape[1], opt.z_depth_dim)
+    d = cuda_dev
+    q = query.lighting_fast_querier(d, opt)
+    raw = q.query_raw(tables["xyz"].to(d), raydir.to(d), cam["campos"].to(d), cam["near"], cam["far"], ts=ex["ts"].contiguous().to(d))
+    sel = raw["ray_any"].cpu() > 0
+    assert torch.equal(sel.to(torch.int8)[None], ray_mask)
+    assert torch.equal(raw["sample_loc_w"].cpu()[sel][None], loc_w)
+    assert torch.equal(raw["sample_pidx"].cpu()[sel][None], pidx)
+    assert (raw["sample_pidx"].cpu()[~sel] == -1).all()
+
+
+@pytest.mark.parametrize("D,near,far,jitter", [(400, 2.0, 6.0, 0.3), (400, 0.1, 8.0, 0.3), (300, 0.0, 100.0, 0.3), (37, 2.0, 6.0, 0.0),
+                                               (400, 2.0, 6.0, 0.0), (400, 0.0, 100.0, 0.0)])
+def test_sample_depths_equal_host_chain(cuda_dev, D, near, far, jitter):
+    """pn_sample_depths vs the reference's own sampler run on the host (oracle.ref_import is not available on the GPU
+    box, so the chain of diff_ray_marching.py:369-386 is spelled out with the same torch ops): bit-identical for the
+    near / far / D of every BASELINE config, with and without jitter."""
+    R = 513
+    u = torch.rand(1, R, D, generator=torch.Generator().manual_seed(D)) if jitter else None
+    t = torch.linspace(0, 1, D + 1).view(1, -1)
+    t = near * (1 - t) + far * t
+    seg = (t[..., 1:] - t[..., :-1]) * (1 + jitter * ((u if jitter else torch.full((1, 1, D), 0.5)) - 0.5))
+    ends = torch.cumsum(seg, dim=2)
+    ends = near + torch.cat([torch.zeros((1, ends.shape[1], 1)), ends], dim=2)
+    want = (ends[:, :, :-1] + ends[:, :, 1:]) / 2
+    raydir = torch.zeros(1, R, 3, device=cuda_dev)
+    got = query.middle_point_ts(raydir, D, near, far, jitter=jitter, uniform=u.to(cuda_dev) if jitter else None)
+    assert torch.equal(got.cpu(), want)
 
 
 def test_reference_kernels_agree_with_port(tiny_scene):

@@ -136,18 +136,14 @@ def test_step_with_frustum_querier_matches_oracle(cuda_dev):
     model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
                                    tables["points_conf"], Rw2c=tables["Rw2c"])
     sd = model.aggregator.state_dict()
-    kr = pipeline_ref.run(opt, tables, cam, None, bg, sd, need_grads=False, dtype=torch.float64, kink_tau=kinks.TAU,
-                          frustum_pix=pix)["kink_rays"]
-    keep = (~kr)[..., None].float()
-    assert float(keep.mean()) > 0.2
-    wt = wt * keep
+    model.aggregator.export_signs = True      # gradients are compared under the forward's own LeakyReLU pattern, on every ray
+    keep = torch.ones(1, R, 1)
     loss_fn = lambda o: ((o["coarse_raycolor"] * wt.to(o["coarse_raycolor"].dtype)).sum()
                          + (o["coarse_point_opacity"] ** 2 * keep.to(o["coarse_raycolor"].dtype)).sum() * 0.1)
-    ref = pipeline_ref.run(opt, tables, cam, None, bg, sd, loss_fn=loss_fn, frustum_pix=pix)
-    ref64 = pipeline_ref.run(opt, tables, cam, None, bg, sd, loss_fn=loss_fn, dtype=torch.float64, frustum_pix=pix)
+    ref = pipeline_ref.run(opt, tables, cam, None, bg, sd, need_grads=False, frustum_pix=pix)
+    ref64 = pipeline_ref.run(opt, tables, cam, None, bg, sd, need_grads=False, dtype=torch.float64, frustum_pix=pix)
     assert float(ref["coarse_is_background"].min()) < 0.5
     dev = cuda_dev
-    g_ref, g_ref64 = group_linear_grads(ref["grads"]), group_linear_grads(ref64["grads"])
     for fused in (False, True):   # the reference seams, then the fused driver (no ray compaction, no [R,SR,K,*] gathers)
         tag = "frustum fused " if fused else "frustum seams "
         for p_ in model.parameters():
@@ -164,6 +160,12 @@ def test_step_with_frustum_querier_matches_oracle(cuda_dev):
         for n in ("points_embeding", "points_conf", "points_dir", "points_color"):
             grads[n] = getattr(model.neural_points, n).grad.detach().cpu().clone()
         grads["bg_color"] = bg_d.grad.detach().cpu().clone()
+        signs = tuple(t.cpu() for t in model.aggregator.last_call.signs)
+        cnd = pipeline_ref.run(opt, tables, cam, None, bg, sd, loss_fn=loss_fn, frustum_pix=pix, frozen_signs=signs)
+        cnd64 = pipeline_ref.run(opt, tables, cam, None, bg, sd, loss_fn=loss_fn, dtype=torch.float64, frustum_pix=pix, frozen_signs=signs)
+        n_diff, n_all, worst = cnd64["pattern_disagreement"]
+        assert n_all > 0 and n_diff <= 1e-4 * n_all and worst < kinks.PATTERN_TOL, (tag, n_diff, n_all, worst)
+        g_ref, g_ref64 = group_linear_grads(cnd["grads"]), group_linear_grads(cnd64["grads"])
         for n, gr in group_linear_grads(grads).items():
             assert_close(gr, g_ref[n], tag + "grad " + n, want64=g_ref64[n])
     with pytest.raises(NotImplementedError):   # the frustum querier is addressed by pixel, not by ray direction

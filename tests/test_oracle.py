@@ -585,3 +585,42 @@ def test_frustum_hyperparameters_with_the_data_loader_types():
         want = frustum_hyperparameters(o, h, w, cam["intrinsic"], near, far)
         for i, k in ((0, "radius_limit"), (1, "depth_limit"), (2, "ranges"), (3, "vsize"), (4, "vdim"), (5, "scaled_vsize"), (6, "scaled_vdim")):
             assert np.array_equal(np.asarray(got[i]), np.asarray(want[k])) and np.asarray(got[i]).dtype == np.asarray(want[k]).dtype, (name, k)
+
+
+def test_frozen_activation_pattern_is_the_identity_on_the_oracles_own_pattern():
+    """torch_port.LeakyReLUProbe: freezing the aggregator oracle's LeakyReLUs to ITS OWN activation pattern changes neither
+    the forward nor any gradient bit (the conditioned backward is the ordinary backward wherever the patterns agree), and
+    flipping one unit that is far from its kink is reported by pattern_disagreement with a large margin."""
+    opt = make_opt()
+    torch.manual_seed(1)
+    port = tp.AggregatorPort(opt)
+    ins = _agg_inputs(F=opt.point_features_dim)
+    gk = ["sampled_color", "sampled_dir", "sampled_conf", "sampled_embedding"]
+    for k in gk:
+        ins[k].requires_grad_(True)
+    wt = None
+
+    def run():
+        nonlocal wt
+        o = port(*[ins[k] for k in ins], (0.004,) * 3, 0)
+        if wt is None:
+            wt = torch.randn(o[0].shape, generator=torch.Generator().manual_seed(3))
+        return o, torch.autograd.grad((o[0] * wt).sum(), [ins[k] for k in gk] + list(port.parameters()))
+    port.freeze_pattern(None, None, record=True)
+    o1, g1 = run()
+    pre = [a.last_pre.clone() for a in port.activations()]
+    pair = torch.stack([p > 0 for p in pre[:4]]).to(torch.uint8)
+    samp = torch.stack([p > 0 for p in pre[4:]]).to(torch.uint8)
+    port.freeze_pattern(pair, samp)
+    o2, g2 = run()
+    assert torch.equal(o1[0], o2[0])
+    for a, b in zip(g1, g2):
+        assert torch.equal(a, b)
+    assert port.pattern_disagreement()[0] == 0
+    # one flipped unit far from zero: detected, with its margin
+    j = int(pre[1].abs().argmax())
+    pair[1].view(-1)[j] ^= 1
+    port.freeze_pattern(pair, samp)
+    run()
+    n_diff, n_all, worst = port.pattern_disagreement()
+    assert n_diff >= 1 and worst > 1.0 and n_all == sum(p.numel() for p in pre)   # (the flip also moves units downstream)
