@@ -53,6 +53,19 @@ class NeuralPoints(nn.Module):
             opt.query_size = opt.kernel_size
         self.lighting_fast_querier = lighting_fast_querier_w if getattr(opt, "wcoord_query", 1) > 0 else lighting_fast_querier_p
         self.querier = self.lighting_fast_querier(device, opt)
+        # neural_points.py:240-300 (opt.load_points == 1): tables from a checkpoint's ``neural_points.*`` entries.  The
+        # cloud-file initialisers of that block (load_blender_cloud, construct_grid_points, feature_init_method) belong
+        # to scene set-up, outside the hot path: without a checkpoint the tables stay empty until set_points().
+        if checkpoint:
+            sd = torch.load(checkpoint, map_location=device) if isinstance(checkpoint, (str, bytes)) or hasattr(checkpoint, "read") else checkpoint
+            if "neural_points.xyz" not in sd or "neural_points.points_embeding" not in sd:
+                raise KeyError("checkpoint holds no neural_points.xyz / neural_points.points_embeding")
+            get = lambda k: sd.get("neural_points." + k)
+            self.set_points(get("xyz"), get("points_embeding"), points_color=get("points_color"), points_dir=get("points_dir"),
+                            points_conf=get("points_conf"), Rw2c=get("Rw2c"))
+        elif feature_init_method != 'rand' or size:
+            raise NotImplementedError("NeuralPoints without a checkpoint: the cloud-file / feature_init_method initialisers "
+                                      "(neural_points.py:246-292) are scene set-up, outside the hot path; call set_points()")
 
     def reset_querier(self):
         self.querier.clean_up()

@@ -17,7 +17,7 @@ import torch
 
 from . import _lib
 from ._lib import GridParams
-from .synthetic import grid_hyperparameters
+from .query_host import grid_hyperparameters
 
 
 _EDGE_CACHE = {}
@@ -156,11 +156,13 @@ class lighting_fast_querier:
         self.count = 0
         self._grid = None
         self._grid_key = None
+        self._grid_xyz = None       # the tensor the cached grid was built from: held so that its address cannot be recycled
         _lib.lib()  # fail now, loudly, if the CUDA library is missing
 
     def clean_up(self):
         self._grid = None
         self._grid_key = None
+        self._grid_xyz = None
 
     # -- grid cache -----------------------------------------------------------------------------
     def _key(self, xyz):
@@ -175,12 +177,16 @@ class lighting_fast_querier:
         return grid_hyperparameters(self.opt, mm[0], mm[1])
 
     def grid_for(self, xyz):
-        """xyz [N,3] float32 CUDA.  Rebuilds only when the point tensor (identity/version) or grid options changed."""
+        """xyz [N,3] float32 CUDA.  Rebuilds only when the point tensor (storage address + autograd version) or the grid
+        options changed.  The querier keeps a reference to the keyed tensor, so the caching allocator cannot hand its
+        address to a different cloud while the grid is cached (the reference rebuilds on every forward, :626).  In-place
+        edits that bypass the version counter (``.data``, raw pointers) need ``clean_up()``."""
         key = self._key(xyz)
         if self._grid is None or key != self._grid_key:
             hp = self.get_hyperparameters(self.opt.vsize, xyz[None], ranges=self.opt.ranges)
             self._grid = VoxelGrid(xyz, hp, self.opt.P, self.opt.max_o)
             self._grid_key = key
+            self._grid_xyz = xyz
             info = self._grid.info_host()
             if info[_lib.GI_OVER_MAX_O] or info[_lib.GI_OVER_P]:
                 warnings.warn("pointnerf_b200: %d occupied voxels (max_o=%s), %d voxels over P=%d points: the reference "

@@ -225,7 +225,9 @@ class RayShardedStep:
         lo, hi = (flat.data_ptr(), flat.data_ptr() + 4 * flat.numel()) if flat is not None else (0, 0)
         rest = [p for p in self.params if id(p) not in tset and not (lo <= p.grad.data_ptr() < hi)]
         mode, tail = None, None
-        if self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._cap_ev is not None:
+        # (pn_rows_pack / pn_rows_merge carry one row in <= 64 columns: F + 8 <= 64; wider tables take the dense all-reduce)
+        if (self.sparse and tables and tables[0].is_cuda and nps.points_embeding.requires_grad and self._cap_ev is not None
+                and int(nps.points_embeding.shape[-1]) <= 56):
             mode = "cuda"        # ids from the fused backward, pack / merge kernels of the C ABI
             call = self.model.aggregator.last_call
             n_rest = sum(p.numel() for p in rest)
