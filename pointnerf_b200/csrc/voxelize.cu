@@ -131,7 +131,9 @@ __global__ void voxel_reduce_kernel(const float* __restrict__ xyz, const unsigne
     for (int j = a; j < b; ++j) {
         int64_t p = idx[j];
         float dx = __fsub_rn(xyz[p * 3], cx), dy = __fsub_rn(xyz[p * 3 + 1], cy), dz = __fsub_rn(xyz[p * 3 + 2], cz);
-        float d = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        // torch.norm(., dim=-1) on the host (mvs_utils.py:556) accumulates its three squares as an FMA chain:
+        // fma(dz, dz, fma(dy, dy, dx * dx)); the same chain here makes residual ties, and hence the arg-min, bit-identical
+        float d = sqrtf(__fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx))));
         if (d < best) { best = d; bi = (int)p; }      // strict <: the smallest index wins ties
     }
     centroid[u * 3] = cx; centroid[u * 3 + 1] = cy; centroid[u * 3 + 2] = cz;

@@ -43,16 +43,31 @@ def test_probe_outputs_match_oracle(tiny_scene, cuda_dev):
     want = mp.unmask(ref["ray_mask"], want)
     hit = ref["ray_mask"][0] > 0
     assert int(hit.sum()) > 50
+    # (a) the probe kernel on the ORACLE's opacities / weights / indices: the arg-max slot is index work - bit-exact on every
+    #     hit ray (tie-break: the first maximum, like torch.max)
+    R_, SR_, K_ = raydir.shape[1], opt.SR, opt.K
+    dev = cuda_dev
+
+    def full(t, fill):      # [1,R'',...] of the kept rays -> [R,...]
+        o = torch.full((R_,) + tuple(t.shape[2:]), fill, dtype=t.dtype)
+        o[hit] = t[0]
+        return o
+    with torch.no_grad():
+        exact = model.probe_outputs(ref["coarse_point_opacity"][0].to(dev), ref["ray_mask"][0].to(torch.int32).to(dev),
+                                    full(ref["sample_loc_w"], 0.0).to(dev), full(ref["sample_pidx"].to(torch.int32), -1).to(dev),
+                                    full(ref["weight"].float(), 0.0).to(dev))
+    assert torch.equal(exact["ray_max_slot"].cpu()[0][hit], want["ray_max_slot"][0][hit].int())
+    assert torch.equal(exact["ray_max_sample_loc_w"].cpu()[0][hit], want["ray_max_sample_loc_w"][0][hit])
+    # (b) end to end: OUR opacities differ from the oracle's by fp32 rounding, so the arg-max may move between two samples
+    #     whose reference opacities tie to rounding (the reference's own choice there depends on its summation order)
     got_slot = out["ray_max_slot"].cpu()[0]
     same = (got_slot == want["ray_max_slot"][0].int()) & hit
-    # a different arg-max is only acceptable between samples whose reference opacities tie to rounding
     diff = hit & ~same
     if bool(diff.any()):
         op = ref["coarse_point_opacity"][0]
         a = op[diff].gather(1, got_slot[diff].long()[:, None])
         b = op[diff].gather(1, want["ray_max_slot"][0][diff][:, None])
         assert float((a - b).abs().max()) < 1e-6
-    assert int(same.sum()) >= int(hit.sum()) - 2
     assert bool((got_slot[~hit] == -1).all())
     for k in ("ray_max_shading_opacity", "ray_max_sample_loc_w", "ray_max_far_dist", "shading_avg_color", "shading_avg_dir",
               "shading_avg_conf", "shading_avg_embedding"):

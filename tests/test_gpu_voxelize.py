@@ -16,12 +16,9 @@ def _check(xyz, vox_res, dev, **box):
     assert torch.equal(got_g.cpu(), want_g), "voxel set / order differs"               # integer work: bit-exact
     assert torch.equal(got_inv.cpu().long(), inv)
     assert torch.equal(got_c.cpu(), want_c), "centroids (serial fp32 sums in point order) differ"
-    gm = got_m.cpu()
-    diff = gm != want_m
-    if bool(diff.any()):      # only between points whose residuals tie to rounding (torch.norm's reduction order is its own)
-        assert float((res[gm[diff]] - res[want_m[diff]]).abs().max()) <= 1e-6 * float(res.max())
-        assert bool((inv[gm[diff]] == inv[want_m[diff]]).all())
-    assert int(diff.sum()) <= max(2, len(gm) // 1000)
+    # index work: bit-exact.  Tie-break: the smallest residual (fp32, the host's fma chain of torch.norm), then the smallest
+    # point index (torch_scatter's scatter_min keeps the first minimum)
+    assert torch.equal(got_m.cpu(), want_m), "nearest-point indices differ"
 
 
 @pytest.mark.parametrize("n,vox_res", [(2, 4), (37, 3), (6000, 40), (50000, 100), (50000, 900)])
