@@ -218,6 +218,17 @@ int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, i
                        int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* workspace,
                        int64_t workspace_bytes, void* stream);
 
+/* pn_compact_samples for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same inputs, outputs and
+ * results as pn_compact_samples, but the workspace is a file-scope `static __device__` array inside the library (8.4 MB,
+ * held by every GPU that loads the library until the process exits) instead of a caller-owned buffer; the call allocates
+ * nothing and calls no allocating routine.  n_slots <= pn_compact_samples_static_max_slots() = 524 288 (4096 rays x 80
+ * samples = 327 680), larger batches are rejected with PN_ERR_ARG.  All calls on a device share the one array: calls that
+ * overlap on the GPU (different streams or host threads) race; serialise them or use pn_compact_samples. */
+int64_t pn_compact_samples_static_max_slots(void);
+int pn_compact_samples_static(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
+                              int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * 4. Point aggregator  (replaces the index_select gather of NeuralPoints.forward neural_points.py:788-799
  *    and PointAggregator.forward / linear / viewmlp, point_aggregators.py:729-816, 421-429, 488-646,

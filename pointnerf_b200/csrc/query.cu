@@ -516,3 +516,42 @@ extern "C" int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, i
     PN_LAUNCH_CHECK("slot_scatter");
     return PN_OK;
 }
+
+// ---- pn_compact_samples without any allocation by anybody ---------------------------------------------------------------
+// (no counterpart in the reference.)  Some callers cannot allocate device
+// memory around a call - code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc - and so
+// cannot hand pn_compact_samples its workspace.  This variant keeps the workspace in a file-scope device array of a fixed,
+// modest size: every GPU that loads the library holds these 8.4 MB until the process exits.  In HOST code the array's name
+// is a host-side stand-in, not a device address, so the address is asked for once per device (with that device current)
+// through cudaGetSymbolAddress and that pointer is what the kernels get.
+namespace pn {
+constexpr int64_t kStaticCompactMaxSlots = 524288;                       // 4096 rays x 80 samples = 327 680; 8192 x 24 = 196 608
+constexpr int64_t kStaticCompactBytes = 2 * kStaticCompactMaxSlots * 8 + 4096;   // packed + offs (uint64 per slot) + scan tile sums + total
+static __device__ __align__(256) unsigned char g_compact_scratch[kStaticCompactBytes];
+static void* g_compact_scratch_ptr[64] = {};                             // device address of the array, per device ordinal
+}  // namespace pn
+
+extern "C" int64_t pn_compact_samples_static_max_slots(void) { return kStaticCompactMaxSlots; }
+
+extern "C" int pn_compact_samples_static(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int32_t* sample_list,
+                                         int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* stream) {
+    PN_CHECK_ARG(n_slots <= kStaticCompactMaxSlots,
+                 "pn_compact_samples_static: n_slots = %lld exceeds the static scratch's maximum of %lld slots (use pn_compact_samples "
+                 "with a caller-owned workspace)", (long long)n_slots, (long long)kStaticCompactMaxSlots);
+    PN_CHECK_ARG(pn_compact_workspace_bytes(kStaticCompactMaxSlots) <= kStaticCompactBytes, "pn_compact_samples_static: scratch array undersized");
+    int dev = -1;
+    PN_CUDA(cudaGetDevice(&dev));
+    PN_CHECK_ARG(dev >= 0 && dev < 64, "pn_compact_samples_static: device ordinal %d out of range", dev);
+    if (!g_compact_scratch_ptr[dev]) {                                    // set-up, once per device, with that device current
+        void* ptr = nullptr;
+        PN_CUDA(cudaGetSymbolAddress(&ptr, g_compact_scratch));
+        PN_CHECK_ARG(ptr != nullptr, "pn_compact_samples_static: cudaGetSymbolAddress returned a null address");
+        g_compact_scratch_ptr[dev] = ptr;
+    }
+    // Every call shares the array and finds the previous call's contents in it.  Nothing has to start at zero: the per-slot
+    // counts, the scanned offsets, the tile sums and the total are all written before they are read, for exactly n_slots
+    // entries.  Calls that overlap on the GPU (two streams, two host threads) race on it.
+    return pn_compact_samples(sample_pidx, n_slots, K, sample_list, pair_start, pair_src, counts, slot_row,
+                              g_compact_scratch_ptr[dev], kStaticCompactBytes, stream);
+}
+
