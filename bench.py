@@ -556,11 +556,11 @@ def dominant_kernel_roofline(_lib, dev, M, peak, peaks, N=256, K=256, reps=20):
     B = torch.randn(N, K, device=dev) / 16
     C = torch.empty(M, N, device=dev)
     bias = torch.randn(N, device=dev)
-    img = torch.empty(lib.pn_debug_nt_image_bytes(N, K), dtype=torch.uint8, device=dev)
+    img = torch.empty(lib.pn_gemm_nt_image_bytes(N, K), dtype=torch.uint8, device=dev)
 
     def fn():
-        _lib.check(lib.pn_debug_gemm_nt(_lib.ptr(A), K, _lib.ptr(B), K, _lib.ptr(C), N, M, N, K, _lib.ptr(bias), 1, 0.01, _lib.ptr(img),
-                                        _lib.stream()), "pn_debug_gemm_nt")
+        _lib.check(lib.pn_gemm_nt(_lib.ptr(A), K, _lib.ptr(B), K, _lib.ptr(C), N, M, None, N, K, _lib.ptr(bias), 1, 0.01, _lib.ptr(img),
+                                  _lib.stream()), "pn_gemm_nt")
     for _ in range(3):
         fn()
     torch.cuda.synchronize()

@@ -39,30 +39,20 @@ int pn_abi_version(void);
 int64_t pn_launch_count(void);
 void pn_launch_count_reset(void);
 
-/* Arithmetic path of the aggregator MLP GEMMs (process-wide):
- *   1 (default) tcgen05 tensor cores, 3xTF32 split products with fp32 accumulation in TMEM (fp32-class accuracy);
- *   0           exact-fp32 SIMT GEMMs (the in-library reference the tensor-core path is validated against).
- * Both replace the cuBLAS SGEMMs behind nn.Linear in point_aggregators.py:547,571,605,635. */
-int pn_set_mlp_path(int path);
-int pn_get_mlp_path(void);
-/* bench-only switches of the NT GEMM: 256 selects the single-CTA kernel instead of the CTA-pair (cta_group::2) one;
- * on the single-CTA kernel 1: no MMA, 2: no A loads, 4: no B copies, 8: no C stores, 16: no A staging stores,
- * 32: no proxy fence, 64: no epilogue (results are garbage while any of bits 0-7 is set); 512: single-CTA TN kernel;
- * 1024: pn_agg_backward keeps everything on the caller's stream (default: the weight-gradient GEMMs trail the
- * data-gradient chain on a second stream, see aggregator.cu BwdStreams); 2048: 128-thread blocks in pn_knn_query. */
-void pn_debug_gemm_flags(int flags);
-/* Test hooks: one GEMM through the selected path (not used by the product path).
- *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias);  tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]
- * Operands 16-byte aligned, leading dimensions multiples of 4.  scratch: pn_debug_gemm_tn_scratch_floats floats. */
-int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd);
-/* image_scratch (pn_debug_nt_image_bytes bytes, or NULL): when given, B is first packed into the pre-split
- * pre-swizzled operand image the product path uses and streamed by TMA bulk copies. */
-int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M,
-                     int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch,
-                     void* stream);
-int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb);
-int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
-                     float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream);
+/* The two GEMM forms of the aggregator MLP (they replace the cuBLAS SGEMMs behind nn.Linear in point_aggregators.py:547,571,
+ * 605,635 and their autograd), exposed for kernel-level tests and the roofline leg of bench.py.  tcgen05 tensor cores,
+ * 3xTF32 split products (hi*lo + lo*hi + hi*hi) with fp32 accumulation in TMEM: fp32-class accuracy (~2e-6 of max).
+ *   nt: C[M,N] = act(A[M,Kd] * B[N,Kd]^T + bias)       (forward layers, data gradients; persistent CTA pairs)
+ *   tn: C[N,Kb] = A[M,N]^T * B[M,Kb], colsum[N] = sum_m A[m,:]   (weight / bias gradients; split over M, fixed-order sum)
+ * M_dev (device int32, may be NULL): the row count is min(*M_dev, M) and never reaches the host; M is then the capacity.
+ * Operands 16-byte aligned, leading dimensions multiples of 4.  image_scratch: pn_gemm_nt_image_bytes bytes (B is packed into
+ * the pre-split, pre-swizzled operand image that TMA bulk copies stream); scratch: pn_gemm_tn_scratch_floats floats. */
+int64_t pn_gemm_nt_image_bytes(int32_t N, int32_t Kd);
+int pn_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, const int32_t* M_dev,
+               int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream);
+int64_t pn_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb);
+int pn_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
+               float* colsum, int64_t M, const int32_t* M_dev, int32_t N, int32_t Kb, float* scratch, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 1. Voxel grid  (replaces claim_occ :243-303, map_coor2occ :305-340, fill_occ2pnts :342-387 and the
@@ -289,6 +279,11 @@ typedef struct pn_agg_inputs {
     const int32_t* pair_start;  /* [S+1] first compact pair of each valid sample      */
     const int32_t* pair_src;    /* [M] slot*K+k of each compact pair                  */
     int64_t n_slots, S, M, T;
+    /* counts: NULL - S and M above are the exact numbers of valid samples / pairs (the caller read them back);
+     *         device int32[2] = {S, M} as written by pn_compact_samples - the counts stay on the device, S and M above are
+     *         CAPACITIES (>= the true counts; every buffer sized by S / M is sized by them) and the whole pass is a fixed
+     *         launch sequence with no host read-back. */
+    const int32_t* counts;
 } pn_agg_inputs;
 
 int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t M);
@@ -320,10 +315,10 @@ int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_ag
 /* LeakyReLU activation pattern of a saved forward (what pn_agg_backward will differentiate through): 1 where the unit's
  * output is > 0 (derivative 1), 0 where the derivative is leaky_slope.  pair_signs uint8[4, M, W]: block1.0, block1.2,
  * block3.0, block3.2 (compact pair rows, ascending (slot, k)); sample_signs uint8[3, S, C]: color_branch.0 / .2 / .4 (compact
- * sample rows).  The MLP is piecewise linear, so a reference backward evaluated under the SAME pattern is comparable at the
+ * sample rows).  S_cap / M_cap: the S / M the saved buffer was sized with.  The MLP is piecewise linear, so a reference backward evaluated under the SAME pattern is comparable at the
  * full tolerance on every ray, units at a kink included (point_aggregators.py:547-571, 635). */
-int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S, int64_t M,
-                            uint8_t* pair_signs, uint8_t* sample_signs, void* stream);
+int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S_cap, int64_t M_cap,
+                            int64_t S, int64_t M, uint8_t* pair_signs, uint8_t* sample_signs, void* stream);
 
 /* Makes `stream` wait for the point where the most recent pn_agg_backward on this device had produced its per-row
  * gradients (grad_embedding / grad_color / grad_dir / grad_conf, touched_ids, n_touched) - BEFORE the weight-gradient GEMMs
@@ -394,24 +389,29 @@ int pn_composite_forward(const float* ray_features, const float* ray_dist, const
 /* Gradients w.r.t. ray_features [R,SR,C+1] and bg_color [C] (deterministic two-stage reduction over
  * rays).  Upstream gradients g_opacity/g_acc_T/g_blend_w [R,SR], g_bg_T [R], g_ray_color [R,C] may each be
  * NULL (= zero).  n_rows: rows of the compact ray_features (with slot_row; 0 / ignored for the dense layout) - the
- * per-row part of the backward then runs one warp per feature row instead of walking each ray.
+ * per-row part of the backward then runs one warp per feature row instead of walking each ray.  n_rows_dev (device int32,
+ * may be NULL): the row count is min(*n_rows_dev, n_rows) and stays on the device; n_rows is then the capacity.
  * workspace: pn_composite_workspace_bytes(n_rays, C, n_rows). */
 int64_t pn_composite_workspace_bytes(int64_t n_rays, int32_t C, int64_t n_rows);
 int pn_composite_backward(const float* ray_features, const float* ray_dist, const uint8_t* ray_valid,
                           const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T,
                           const float* bg_T, const float* g_ray_color, const float* g_opacity,
                           const float* g_acc_T, const float* g_blend_w, const float* g_bg_T,
-                          int64_t n_rays, int32_t SR, int32_t C, int64_t n_rows, float* g_features,
-                          float* g_bg_color, void* workspace, int64_t workspace_bytes, void* stream);
+                          int64_t n_rays, int32_t SR, int32_t C, int64_t n_rows, const int32_t* n_rows_dev,
+                          float* g_features, float* g_bg_color, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* Colour MSE of a batch of rays and its gradient in one pass (replaces torch.nn.MSELoss on coarse_raycolor,
  * base_rendering_model.py:543-550 `compute_losses`, and its autograd chain).
  *   loss[0] = inv_norm * sum_r w_r * sum_c (pred[r,c]-target[r,c])^2      grad[r,c] = 2*inv_norm*w_r*(pred-target)
- *   ray_weight float[n_rays] or NULL (=1; the reference's ray_mask selection is w in {0,1} with inv_norm = 1/(n_masked*C));
+ *   ray_weight float[n_rays] or NULL (= 1); ray_mask int32[n_rays] or NULL: rays with ray_mask <= 0 get weight 0 - the
+ *   reference's `ray_masked_coarse_raycolor` item (:543-550) is ray_mask = the query's per-ray neighbour flag with
+ *   inv_norm * *inv_norm_dev = 1 / (n_masked * C); inv_norm_dev (device float, may be NULL) lets that count - and, with ray
+ *   sharding, its sum over ranks - stay on the device.
  *   grad float[n_rays,C] or NULL.  Fixed-tree reduction: deterministic.  workspace >= pn_color_mse_workspace_bytes(). */
 int64_t pn_color_mse_workspace_bytes(void);
-int pn_color_mse(const float* pred, const float* target, const float* ray_weight, int64_t n_rays, int32_t C,
-                 float inv_norm, float* loss, float* grad, void* workspace, int64_t workspace_bytes, void* stream);
+int pn_color_mse(const float* pred, const float* target, const float* ray_weight, const int32_t* ray_mask, int64_t n_rays,
+                 int32_t C, float inv_norm, const float* inv_norm_dev, float* loss, float* grad, void* workspace,
+                 int64_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 5. Point-cloud maintenance between passes

@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -53,7 +53,7 @@ class AggWeights(Structure):
 class AggInputs(Structure):
     _fields_ = [(n, c_void_p) for n in ("xyz", "xyz_pers", "embedding", "color", "dir", "conf", "Rw2c", "sample_pidx",
                                         "sample_loc_w", "sample_loc", "ray_dirs", "sample_list", "pair_start", "pair_src")] + \
-               [(n, c_int64) for n in ("n_slots", "S", "M", "T")]
+               [(n, c_int64) for n in ("n_slots", "S", "M", "T")] + [("counts", c_void_p)]
 
 
 class AdamSegment(Structure):
@@ -84,12 +84,10 @@ def _declare(lib):
         "pn_abi_version": (c_int, []),
         "pn_launch_count": (c_int64, []),
         "pn_launch_count_reset": (None, []),
-        "pn_set_mlp_path": (c_int, [c_int]),
-        "pn_get_mlp_path": (c_int, []),
-        "pn_debug_nt_image_bytes": (c_int64, [c_int32, c_int32]),
-        "pn_debug_gemm_nt": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int64, c_int32, c_int32, P, c_int32, c_float, P, P]),
-        "pn_debug_gemm_tn_scratch_floats": (c_int64, [c_int64, c_int32, c_int32]),
-        "pn_debug_gemm_tn": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int32, P, c_int64, c_int32, c_int32, P, P]),
+        "pn_gemm_nt_image_bytes": (c_int64, [c_int32, c_int32]),
+        "pn_gemm_nt": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int64, P, c_int32, c_int32, P, c_int32, c_float, P, P]),
+        "pn_gemm_tn_scratch_floats": (c_int64, [c_int64, c_int32, c_int32]),
+        "pn_gemm_tn": (c_int, [P, c_int64, P, c_int64, P, c_int64, c_int32, P, c_int64, P, c_int32, c_int32, P, P]),
         "pn_grid_workspace_bytes": (c_int64, [c_int64, c_int64]),
         "pn_grid_build": (c_int, [P, c_int64, POINTER(GridParams), P, P, P, P, P, c_int64, P]),
         "pn_sample_depths": (c_int, [P, P, c_int64, c_int32, c_float, c_float, P, P]),
@@ -107,13 +105,12 @@ def _declare(lib):
         "pn_compact_samples_static_max_slots": (c_int64, []),
         "pn_compact_samples_static": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P]),
         "pn_agg_saved_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64]),
-        "pn_agg_activation_signs": (c_int, [POINTER(AggParams), P, c_int64, c_int64, c_int64, P, P, P]),
+        "pn_agg_activation_signs": (c_int, [POINTER(AggParams), P, c_int64, c_int64, c_int64, c_int64, c_int64, P, P, P]),
         "pn_agg_workspace_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64, c_int64, c_int]),
         "pn_agg_forward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, P, c_int64, P,
                                    c_int64, P]),
         "pn_agg_backward": (c_int, [POINTER(AggParams), POINTER(AggInputs), POINTER(AggWeights), P, P, c_int64,
                                     POINTER(AggWeights), c_int, P, P, P, P, P, P, P, c_int64, P]),
-        "pn_debug_gemm_flags": (None, [c_int]),
         "pn_agg_backward_wait_rows": (c_int, [P]),
         "pn_set_backward_schedule": (c_int, [c_int]),
         "pn_get_backward_schedule": (c_int, []),
@@ -123,11 +120,11 @@ def _declare(lib):
         "pn_ray_dist": (c_int, [P, P, c_int64, c_int32, c_float, c_int32, P, P]),
         "pn_composite_forward": (c_int, [P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P, P, P, P]),
         "pn_composite_workspace_bytes": (c_int64, [c_int64, c_int32, c_int64]),
-        "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int64, P, P, P,
+        "pn_composite_backward": (c_int, [P, P, P, P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int64, P, P, P, P,
                                           c_int64, P]),
         "pn_gather_clamp": (c_int, [P, c_int64, P, c_int64, c_float, c_float, P, P]),
         "pn_color_mse_workspace_bytes": (c_int64, []),
-        "pn_color_mse": (c_int, [P, P, P, c_int64, c_int32, c_float, P, P, P, c_int64, P]),
+        "pn_color_mse": (c_int, [P, P, P, P, c_int64, c_int32, c_float, P, P, P, P, c_int64, P]),
         "pn_probe_rays": (c_int, [P, P, P, P, P, P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float, c_float,
                                   P, P, P, P, P, P, P, P, P]),
         "pn_prune_workspace_bytes": (c_int64, [c_int64]),

@@ -87,6 +87,7 @@ class _AggCall:
         self.sample_pidx, self.sample_loc_w, self.sample_loc, self.ray_dirs = sample_pidx, sample_loc_w, sample_loc, ray_dirs
         self.n_slots, self.T, self.scatter_rows, self.want_weight = n_slots, T, scatter_rows, want_weight
         self.S = self.M = 0
+        self.counts_dev = None                # device int32[2] (S, M): set when the host does not read the counts back
         self.sample_list = self.pair_start = self.pair_src = self.slot_row = None
         self.collect_touched = False          # ask the backward for the sorted unique list of table rows it touched
         self.touched_ids = self.n_touched = None
@@ -112,6 +113,7 @@ def _inputs_struct(call, embedding, color, pdir, conf):
     a.ray_dirs = _lib.ptr(call.ray_dirs)
     a.sample_list, a.pair_start, a.pair_src = _lib.ptr(call.sample_list), _lib.ptr(call.pair_start), _lib.ptr(call.pair_src)
     a.n_slots, a.S, a.M, a.T = call.n_slots, call.S, call.M, call.T
+    a.counts = _lib.ptr(call.counts_dev)     # None: S / M are exact; else they are capacities and the counts stay on the device
     return a
 
 
@@ -195,8 +197,8 @@ class _AggFunction(torch.autograd.Function):
             if call.export_signs:
                 ps = torch.empty((4, call.M, p.W), dtype=torch.uint8, device=dev)
                 ss = torch.empty((3, call.S, p.C), dtype=torch.uint8, device=dev)
-                _lib.check(lib.pn_agg_activation_signs(ctypes.byref(p), _lib.ptr(saved), saved_bytes, call.S, call.M, _lib.ptr(ps),
-                                                       _lib.ptr(ss), _lib.stream()), "pn_agg_activation_signs")
+                _lib.check(lib.pn_agg_activation_signs(ctypes.byref(p), _lib.ptr(saved), saved_bytes, call.S, call.M, call.S, call.M,
+                                                       _lib.ptr(ps), _lib.ptr(ss), _lib.stream()), "pn_agg_activation_signs")
                 call.signs = (ps, ss)
         ctx.call, ctx.saved, ctx.saved_bytes = call, saved, saved_bytes
         ctx.tables = (embedding, color, pdir, conf)

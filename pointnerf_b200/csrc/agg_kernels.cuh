@@ -17,6 +17,24 @@ struct AggDims {
     float slope, dist_scale;
 };
 
+// Valid samples / pairs of the batch.  With in.counts (device int32[2], written by pn_compact_samples) the host never learns
+// them: in.S / in.M are then the CAPACITIES the buffers and launches were sized for, and every kernel walks its items with
+// a grid-stride loop bounded by the device value.
+__device__ __forceinline__ int64_t n_samples(const pn_agg_inputs& in) {
+    if (!in.counts) return in.S;
+    const int64_t v = (int64_t)__ldg(in.counts);
+    return v < in.S ? v : in.S;
+}
+__device__ __forceinline__ int64_t n_pairs(const pn_agg_inputs& in) {
+    if (!in.counts) return in.M;
+    const int64_t v = (int64_t)__ldg(in.counts + 1);
+    return v < in.M ? v : in.M;
+}
+__device__ __forceinline__ int64_t warp_id_global() { return ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; }
+__device__ __forceinline__ int64_t warps_total() { return ((int64_t)gridDim.x * blockDim.x) >> 5; }
+__device__ __forceinline__ int64_t thread_id_global() { return (int64_t)blockIdx.x * blockDim.x + threadIdx.x; }
+__device__ __forceinline__ int64_t threads_total() { return (int64_t)gridDim.x * blockDim.x; }
+
 __device__ __forceinline__ void rot3(const float* __restrict__ R, float x, float y, float z, float& ox, float& oy, float& oz) {
     // row-vector times R^T  ==  R * v
     ox = R[0] * x + R[1] * y + R[2] * z;
@@ -42,9 +60,9 @@ __device__ __forceinline__ void load_view(const pn_agg_inputs& in, const AggDims
 __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1,
                                                        float* __restrict__ X3, float4* __restrict__ pairv,
                                                        float* __restrict__ weight_out) {
-    int64_t si = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (si >= in.S) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t S = n_samples(in);
+  for (int64_t si = warp_id_global(); si < S; si += warps_total()) {
     int slot = in.sample_list[si];
     int p0 = in.pair_start[si], np = in.pair_start[si + 1] - p0;
     float sx = in.sample_loc_w[3 * (int64_t)slot], sy = in.sample_loc_w[3 * (int64_t)slot + 1], sz = in.sample_loc_w[3 * (int64_t)slot + 2];
@@ -95,6 +113,7 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
 #pragma unroll
         for (int i = 0; i < 6; ++i) park[i] = dd[i];
     }
+  }
 }
 
 // phase 2 of prep: block1 input row [emb | PE_ff(emb) | PE_df(dist) | 0-pad] of pair m; lane = channel.  The encoding
@@ -103,10 +122,10 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
 // in shared memory and leaves as whole float4s.
 __global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1) {
     extern __shared__ float prep_rows[];                 // blockDim.x / 32 rows of in1p floats
-    int64_t m = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (m >= in.M) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t M = n_pairs(in);
     float* srow = prep_rows + (threadIdx.x >> 5) * d.in1p;
+  for (int64_t m = warp_id_global(); m < M; m += warps_total()) {
     const int gj = in.sample_pidx[in.pair_src[m]];
     float* row = X1 + m * d.in1p;
     const int pe0 = d.F + 2 * d.ff * d.F;
@@ -143,6 +162,8 @@ __global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, Ag
     __syncwarp();
     float4* row4 = reinterpret_cast<float4*>(row);       // in1p % 4 == 0 and X1 is 16-byte aligned
     for (int c4 = lane; c4 < (d.in1p >> 2); c4 += 32) row4[c4] = *reinterpret_cast<const float4*>(srow + 4 * c4);
+    __syncwarp();                                        // the row buffer is reused by the warp's next pair
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -155,15 +176,19 @@ __global__ void __launch_bounds__(256) agg_reduce_kernel(pn_agg_inputs in, AggDi
                                                          float4* __restrict__ pairv, const float* __restrict__ wal,
                                                          const float* __restrict__ bal, float* __restrict__ FS,
                                                          float* __restrict__ alpha) {
-    int64_t si = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (si >= in.S) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t S = n_samples(in);
+    float wa[NW];
+#pragma unroll
+    for (int i = 0; i < NW; ++i) wa[i] = wal[lane + 32 * i];
+    const float b = bal[0];
+  for (int64_t si = warp_id_global(); si < S; si += warps_total()) {
     int slot = in.sample_list[si];
     int p0 = in.pair_start[si], np = in.pair_start[si + 1] - p0;
-    float wa[NW], acc[NW];
+    float acc[NW];
 #pragma unroll
-    for (int i = 0; i < NW; ++i) { wa[i] = wal[lane + 32 * i]; acc[i] = 0.f; }
-    float b = bal[0], a_s = 0.f;
+    for (int i = 0; i < NW; ++i) acc[i] = 0.f;
+    float a_s = 0.f;
     for (int j = 0; j < np; ++j) {
         int64_t m = p0 + j;
         float4 pv = pairv[m];
@@ -205,20 +230,22 @@ __global__ void __launch_bounds__(256) agg_reduce_kernel(pn_agg_inputs in, AggDi
         row[d.W + nq + q] = co;
     }
     for (int c = d.inc + lane; c < d.incp; c += 32) row[c] = 0.f;
+  }
 }
 
 // decoded[slot] = [alpha_s | C3[s, :]]
 __global__ void __launch_bounds__(256) agg_finish_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ alpha,
                                                          const float* __restrict__ C3, float* __restrict__ decoded) {
-    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int C1 = d.C + 1;
-    if (idx >= in.S * C1) return;
-    int64_t si = idx / C1;
-    int c = (int)(idx - si * C1);
-    int64_t orow = d.compact_out ? si : (int64_t)in.sample_list[si];
-    float v = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
-    if (c > 0 && d.order == 1) v = sigmoid_exact(v) * 1.002f - 0.001f;   // raw2out_color (:268-273), order 1 only in this fork
-    decoded[orow * C1 + c] = v;
+    const int C1 = d.C + 1;
+    const int64_t n = n_samples(in) * C1;
+    for (int64_t idx = thread_id_global(); idx < n; idx += threads_total()) {
+        int64_t si = idx / C1;
+        int c = (int)(idx - si * C1);
+        int64_t orow = d.compact_out ? si : (int64_t)in.sample_list[si];
+        float v = c == 0 ? alpha[si] : C3[si * d.C + c - 1];
+        if (c > 0 && d.order == 1) v = sigmoid_exact(v) * 1.002f - 0.001f;   // raw2out_color (:268-273), order 1 only in this fork
+        decoded[orow * C1 + c] = v;
+    }
 }
 
 // ------------------------------------ backward ------------------------------------------------
@@ -226,21 +253,22 @@ __global__ void __launch_bounds__(256) agg_finish_kernel(pn_agg_inputs in, AggDi
 __global__ void __launch_bounds__(256) agg_gout_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ g_decoded,
                                                        const float* __restrict__ C3, float* __restrict__ GC3,
                                                        float* __restrict__ galpha) {
-    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int C1 = d.C + 1;
-    if (idx >= in.S * C1) return;
-    int64_t si = idx / C1;
-    int c = (int)(idx - si * C1);
-    int64_t irow = d.compact_out ? si : (int64_t)in.sample_list[si];
-    float gv = g_decoded[irow * C1 + c];
-    if (c == 0) galpha[si] = gv;
-    else {
-        float c3 = C3[si * d.C + c - 1];
-        if (d.order == 1) {
-            float o = sigmoid_exact(c3);
-            gv *= 1.002f * o * (1.f - o);
+    const int C1 = d.C + 1;
+    const int64_t n = n_samples(in) * C1;
+    for (int64_t idx = thread_id_global(); idx < n; idx += threads_total()) {
+        int64_t si = idx / C1;
+        int c = (int)(idx - si * C1);
+        int64_t irow = d.compact_out ? si : (int64_t)in.sample_list[si];
+        float gv = g_decoded[irow * C1 + c];
+        if (c == 0) galpha[si] = gv;
+        else {
+            float c3 = C3[si * d.C + c - 1];
+            if (d.order == 1) {
+                float o = sigmoid_exact(c3);
+                gv *= 1.002f * o * (1.f - o);
+            }
+            GC3[si * d.C + c - 1] = gv * (c3 > 0.f ? 1.f : d.slope);
         }
-        GC3[si * d.C + c - 1] = gv * (c3 > 0.f ? 1.f : d.slope);
     }
 }
 
@@ -251,11 +279,13 @@ template <int NW>
 __global__ void __launch_bounds__(256) agg_reduce_bwd_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ H4,
                                                              const float4* __restrict__ pairv, const float* __restrict__ wal,
                                                              const float* __restrict__ GFS, const float* __restrict__ galpha,
-                                                             int64_t chunk, float* __restrict__ dPre4, int64_t ld4,
+                                                             float* __restrict__ dPre4, int64_t ld4,
                                                              float* __restrict__ PG, int pgw, float* __restrict__ partial) {
     __shared__ float sm[8][32 * NW + 1];
     int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int64_t s_begin = (int64_t)blockIdx.x * chunk, s_end = s_begin + chunk < in.S ? s_begin + chunk : in.S;
+    const int64_t S = n_samples(in);
+    const int64_t chunk = (S + gridDim.x - 1) / gridDim.x;       // CTA b owns samples [b * chunk, (b + 1) * chunk)
+    int64_t s_begin = (int64_t)blockIdx.x * chunk, s_end = s_begin + chunk < S ? s_begin + chunk : S;
     float wa[NW], gw[NW];
 #pragma unroll
     for (int i = 0; i < NW; ++i) { wa[i] = wal[lane + 32 * i]; gw[i] = 0.f; }
@@ -338,8 +368,8 @@ __global__ void __launch_bounds__(256) agg_alpha_final_kernel(const float* __res
 // block3 extras backward: thread per pair.  G3 [M, in3p] holds d/d(block3 input); columns W..W+6.
 __global__ void __launch_bounds__(256) agg_extras_bwd_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ G3,
                                                              float* __restrict__ PG, int pgw) {
-    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= in.M) return;
+    const int64_t M = n_pairs(in);
+  for (int64_t m = thread_id_global(); m < M; m += threads_total()) {
     int src = in.pair_src[m];
     int slot = src / d.K;
     float vx, vy, vz;
@@ -352,15 +382,16 @@ __global__ void __launch_bounds__(256) agg_extras_bwd_kernel(pn_agg_inputs in, A
     o[3] = R[0] * px + R[3] * py + R[6] * pz;  // R^T
     o[4] = R[1] * px + R[4] * py + R[7] * pz;
     o[5] = R[2] * px + R[5] * py + R[8] * pz;
+  }
 }
 
 // block1 input backward: warp per pair, lane = embedding channel.  d sin(e 2^f)/de = 2^f cos(e 2^f): the
 // cos / sin values are read back from the saved input row, no trigonometry is recomputed.
 __global__ void __launch_bounds__(256) agg_prep_bwd_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ X1,
                                                            const float* __restrict__ GX1, float* __restrict__ PG, int pgw) {
-    int64_t m = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (m >= in.M) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t M = n_pairs(in);
+  for (int64_t m = warp_id_global(); m < M; m += warps_total()) {
     const float* x = X1 + m * d.in1p;
     const float* g = GX1 + m * d.in1p;
     for (int c = lane; c < d.F; c += 32) {
@@ -372,15 +403,16 @@ __global__ void __launch_bounds__(256) agg_prep_bwd_kernel(pn_agg_inputs in, Agg
         }
         PG[m * pgw + c] = ge;
     }
+  }
 }
 
 // per-pair gradients -> dense [n_slots*K, *] layout of the reference's sampled_* tensors
 __global__ void __launch_bounds__(256) agg_scatter_dense_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ PG,
                                                                 int pgw, float* __restrict__ g_emb, float* __restrict__ g_color,
                                                                 float* __restrict__ g_dir, float* __restrict__ g_conf) {
-    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int cols = d.F + 7;
-    if (idx >= in.M * cols) return;
+    const int cols = d.F + 7;
+    const int64_t n = n_pairs(in) * cols;
+  for (int64_t idx = thread_id_global(); idx < n; idx += threads_total()) {
     int64_t m = idx / cols;
     int c = (int)(idx - m * cols);
     int64_t src = in.pair_src[m];
@@ -389,32 +421,36 @@ __global__ void __launch_bounds__(256) agg_scatter_dense_kernel(pn_agg_inputs in
     else if (c < d.F + 3) { if (g_color) g_color[src * 3 + (c - d.F)] = v; }
     else if (c < d.F + 6) { if (g_dir) g_dir[src * 3 + (c - d.F - 3)] = v; }
     else if (g_conf) g_conf[src] = v;
+  }
 }
 
 // ---- per-point segmented reduction (replaces the atomic index_add_ of index_select's backward) -----
 __global__ void __launch_bounds__(256) agg_key_count_kernel(pn_agg_inputs in, int* __restrict__ cnt, int* __restrict__ rank) {
-    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= in.M) return;
-    int g = in.sample_pidx[in.pair_src[m]];
-    rank[m] = atomicAdd(&cnt[g], 1);
+    const int64_t M = n_pairs(in);
+    for (int64_t m = thread_id_global(); m < M; m += threads_total()) {
+        int g = in.sample_pidx[in.pair_src[m]];
+        rank[m] = atomicAdd(&cnt[g], 1);
+    }
 }
 __global__ void __launch_bounds__(256) agg_key_place_kernel(pn_agg_inputs in, const int* __restrict__ start,
                                                             const int* __restrict__ rank, int* __restrict__ tmp) {
-    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= in.M) return;
-    int g = in.sample_pidx[in.pair_src[m]];
-    tmp[start[g] + rank[m]] = (int)m;
+    const int64_t M = n_pairs(in);
+    for (int64_t m = thread_id_global(); m < M; m += threads_total()) {
+        int g = in.sample_pidx[in.pair_src[m]];
+        tmp[start[g] + rank[m]] = (int)m;
+    }
 }
 __global__ void __launch_bounds__(256) agg_key_order_kernel(pn_agg_inputs in, const int* __restrict__ start,
                                                             const int* __restrict__ tmp, int* __restrict__ sorted,
                                                             int* __restrict__ skey) {
-    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= in.M) return;
-    int g = in.sample_pidx[in.pair_src[m]];
-    int s = start[g], e = start[g + 1], smaller = 0;
-    for (int j = s; j < e; ++j) smaller += (tmp[j] < (int)m);
-    sorted[s + smaller] = (int)m;
-    skey[s + smaller] = g;          // point index at each sorted position: segment boundaries without a gather chain
+    const int64_t M = n_pairs(in);
+    for (int64_t m = thread_id_global(); m < M; m += threads_total()) {
+        int g = in.sample_pidx[in.pair_src[m]];
+        int s = start[g], e = start[g + 1], smaller = 0;
+        for (int j = s; j < e; ++j) smaller += (tmp[j] < (int)m);
+        sorted[s + smaller] = (int)m;
+        skey[s + smaller] = g;          // point index at each sorted position: segment boundaries without a gather chain
+    }
 }
 // one warp per sorted position; only segment heads work.  Lanes own columns; rows are added in ascending
 // pair order, so the sum is reproducible run to run.
@@ -422,17 +458,17 @@ __global__ void __launch_bounds__(256) agg_segment_reduce_kernel(pn_agg_inputs i
                                                                  const int* __restrict__ sorted, const float* __restrict__ PG,
                                                                  int pgw, float* __restrict__ g_emb, float* __restrict__ g_color,
                                                                  float* __restrict__ g_dir, float* __restrict__ g_conf) {
-    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (i >= in.M) return;
-    const int g = skey[i];
-    if (i > 0 && skey[i - 1] == g) return;  // not the head of its segment
+    const int lane = threadIdx.x & 31;
+    const int64_t M = n_pairs(in);
     const int cols = d.F + 7;
+  for (int64_t i = warp_id_global(); i < M; i += warps_total()) {
+    const int g = skey[i];
+    if (i > 0 && skey[i - 1] == g) continue;  // not the head of its segment
     for (int c0 = 0; c0 < cols; c0 += 64) {               // 64 columns per walk of the segment (one walk when F <= 57)
         float a[2] = {0.f, 0.f};
-        for (int64_t j0 = i; j0 < in.M; j0 += 32) {       // rows of the segment, 32 sorted positions per probe
+        for (int64_t j0 = i; j0 < M; j0 += 32) {          // rows of the segment, 32 sorted positions per probe
             const int64_t j = j0 + lane;
-            const bool mine = j < in.M && skey[j] == g;
+            const bool mine = j < M && skey[j] == g;
             const int mrow = mine ? sorted[j] : -1;
             const unsigned mask = __ballot_sync(kFull, mine);
             const int cnt = mask == kFull ? 32 : __ffs(~mask) - 1;   // leading run that belongs to this segment
@@ -453,22 +489,24 @@ __global__ void __launch_bounds__(256) agg_segment_reduce_kernel(pn_agg_inputs i
             else if (g_conf) g_conf[g] = a[h];
         }
     }
+  }
 }
 
 // ---- touched rows (multi-GPU sparse gradient exchange) ----------------------------------------------------
 // flag[i] = 1 iff sorted position i is the head of its per-point segment
-__global__ void __launch_bounds__(256) agg_head_flag_kernel(int64_t M, const int* __restrict__ skey, int* __restrict__ flag) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= M) return;
-    flag[i] = (i == 0 || skey[i - 1] != skey[i]) ? 1 : 0;
+// (flag has `cap` entries: positions >= the device pair count are 0, so the scan over the capacity leaves rank[cap] = heads)
+__global__ void __launch_bounds__(256) agg_head_flag_kernel(pn_agg_inputs in, int64_t cap, const int* __restrict__ skey, int* __restrict__ flag) {
+    const int64_t M = n_pairs(in);
+    for (int64_t i = thread_id_global(); i < cap; i += threads_total())
+        flag[i] = (i < M && (i == 0 || skey[i - 1] != skey[i])) ? 1 : 0;
 }
 // ids[rank of head i among heads] = point index; heads are in ascending point order, so ids is sorted and unique
-__global__ void __launch_bounds__(256) agg_head_ids_kernel(int64_t M, const int* __restrict__ skey, const int* __restrict__ rank,
+__global__ void __launch_bounds__(256) agg_head_ids_kernel(pn_agg_inputs in, int64_t cap, const int* __restrict__ skey, const int* __restrict__ rank,
                                                            int* __restrict__ ids, int* __restrict__ n_touched) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0 && n_touched) n_touched[0] = rank[M];
-    if (i >= M) return;
-    if (i == 0 || skey[i - 1] != skey[i]) ids[rank[i]] = skey[i];
+    const int64_t M = n_pairs(in);
+    if (thread_id_global() == 0 && n_touched) n_touched[0] = rank[cap];
+    for (int64_t i = thread_id_global(); i < M; i += threads_total())
+        if (i == 0 || skey[i - 1] != skey[i]) ids[rank[i]] = skey[i];
 }
 
 }  // namespace pn

@@ -9,6 +9,11 @@
 //   reduce  : alpha_s = sum_k softplus(H4 w_a + b_a - 1) wc,  FS[S, :W] = sum_k H4 wc,  FS[S, W:] = PE(view)
 //   colour  : C1 = lrelu(FS Wc0^T + b), C2 = lrelu(C1 Wc2^T + b), C3 = lrelu(C2 Wc4^T + b)
 //   finish  : decoded[slot] = [alpha_s | C3]
+//
+// Row counts.  S and M are data dependent (pn_compact_samples counts them on the device).  With in->counts == NULL the
+// caller has read them back and in->S / in->M are exact.  With in->counts set nothing ever reaches the host: in->S / in->M
+// are CAPACITIES (buffers and launches are sized for them), every kernel reads the true counts from in->counts, the GEMMs
+// cut their tiles / reduction splits on the device, and the whole pass is a fixed sequence of launches.
 #include "agg_kernels.cuh"
 #include "gemm.cuh"
 
@@ -58,7 +63,15 @@ static int64_t carve_saved(const AggDims& d, int64_t S, int64_t M, void* p, int6
     return c.off;
 }
 
-static int64_t max3(int64_t a, int64_t b, int64_t c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+// launch geometry of the grid-stride kernels: enough blocks for the capacity, at most a few resident waves
+static unsigned grid_warp_items(int64_t items) {            // one warp per item, 8 warps per block
+    int64_t b = cdiv((items > 0 ? items : 1) * 32, 256), mx = (int64_t)kNumSMs * 8;
+    return (unsigned)(b < mx ? b : mx);
+}
+static unsigned grid_thread_items(int64_t items) {          // one thread per item
+    int64_t b = cdiv(items > 0 ? items : 1, 256), mx = (int64_t)kNumSMs * 8;
+    return (unsigned)(b < mx ? b : mx);
+}
 
 }  // namespace pn
 
@@ -72,24 +85,20 @@ extern "C" int64_t pn_agg_saved_bytes(const pn_agg_params* p, int64_t S, int64_t
 }
 
 namespace pn {
-struct FwdWs { float *W1a, *W3a, *Wc0; char *I1a, *I1b, *I3a, *I3b, *Ic0, *Ic2, *Ic4; };
+struct FwdWs { char *I1a, *I1b, *I3a, *I3b, *Ic0, *Ic2, *Ic4; };
 struct BwdWs {
-    float *W1aT, *W1bT, *W3aT, *W3bT, *Wc0T, *Wc2T, *Wc4T;
-    float *GA, *GB, *GA2, *GB2, *GA3, *GSa, *GSb, *GSc, *GSd, *galpha, *PG, *tn, *apart;
+    float *GA, *GB, *GA2, *GB2, *GA3, *GSa, *GSb, *GSc, *GSd, *galpha, *PG, *apart;
+    float* tn[7];                                    // split partials of the seven weight-gradient GEMMs (finished by ONE launch)
     char *J1a, *J1b, *J3a, *J3b, *Jc0, *Jc2, *Jc4;   // operand images of the TRANSPOSED weights (data gradients)
     int *cnt, *rank, *tmp, *sorted, *skey, *scan, *hflag, *hscan;
     int nblk_reduce;
-    int64_t chunk;
 };
 constexpr int kReduceBlocks = kNumSMs * 4;
 
 static int64_t carve_fwd(const AggDims& d, void* p, int64_t bytes, FwdWs* w) {
     Carver c(p, bytes);
     FwdWs t;
-    t.W1a = c.take<float>((int64_t)d.W * d.in1p);
-    t.W3a = c.take<float>((int64_t)d.W * d.in3p);
-    t.Wc0 = c.take<float>((int64_t)d.C * d.incp);
-    // operand images of the weights for the tensor-core path (gemm.cuh: pack_nt_image)
+    // operand images of the weights (gemm.cuh: pack_nt_image): pre-split, pre-swizzled, one TMA bulk copy per K chunk
     t.I1a = c.take<char>(nt_image_bytes(d.W, d.in1p));
     t.I1b = c.take<char>(nt_image_bytes(d.W, d.W));
     t.I3a = c.take<char>(nt_image_bytes(d.W, d.in3p));
@@ -104,13 +113,6 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     Carver c(p, bytes);
     int64_t m = M > 0 ? M : 1, s = S > 0 ? S : 1;
     BwdWs t;
-    t.W1aT = c.take<float>((int64_t)d.in1p * d.W);
-    t.W1bT = c.take<float>((int64_t)d.W * d.W);
-    t.W3aT = c.take<float>((int64_t)d.in3p * d.W);
-    t.W3bT = c.take<float>((int64_t)d.W * d.W);
-    t.Wc0T = c.take<float>((int64_t)d.incp * d.C);
-    t.Wc2T = c.take<float>((int64_t)d.C * d.C);
-    t.Wc4T = c.take<float>((int64_t)d.C * d.C);
     t.J1a = c.take<char>(nt_image_bytes(d.in1p, d.W));
     t.J1b = c.take<char>(nt_image_bytes(d.W, d.W));
     t.J3a = c.take<char>(nt_image_bytes(d.in3p, d.W));
@@ -132,11 +134,14 @@ static int64_t carve_bwd(const AggDims& d, int64_t S, int64_t M, int64_t T, void
     t.GSd = c.take<float>(s * d.incp);
     t.galpha = c.take<float>(s);
     t.PG = c.take<float>(m * (d.F + 8));
-    int64_t tn = max3(gemm_tn_scratch_floats(m, d.W, d.in1p), gemm_tn_scratch_floats(m, d.W, d.in3p),
-                      gemm_tn_scratch_floats(s, d.C, d.incp));
-    t.tn = c.take<float>(tn);
+    t.tn[0] = c.take<float>(gemm_tn_scratch_floats(s, d.C, d.C));       // color.4
+    t.tn[1] = c.take<float>(gemm_tn_scratch_floats(s, d.C, d.C));       // color.2
+    t.tn[2] = c.take<float>(gemm_tn_scratch_floats(s, d.C, d.incp));    // color.0
+    t.tn[3] = c.take<float>(gemm_tn_scratch_floats(m, d.W, d.W));       // block3.2
+    t.tn[4] = c.take<float>(gemm_tn_scratch_floats(m, d.W, d.in3p));    // block3.0
+    t.tn[5] = c.take<float>(gemm_tn_scratch_floats(m, d.W, d.W));       // block1.2
+    t.tn[6] = c.take<float>(gemm_tn_scratch_floats(m, d.W, d.in1p));    // block1.0
     t.nblk_reduce = (int)(s < kReduceBlocks ? s : kReduceBlocks);
-    t.chunk = cdiv(s, t.nblk_reduce);
     t.apart = c.take<float>((int64_t)kReduceBlocks * (d.W + 1));
     int64_t tt = T > 0 ? T : 1;
     t.cnt = c.take<int>(tt + 1);
@@ -173,35 +178,37 @@ __global__ void __launch_bounds__(256) act_signs_kernel(const float* __restrict_
     }
 }
 }  // namespace pn
-extern "C" int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S, int64_t M,
-                                       uint8_t* pair_signs, uint8_t* sample_signs, void* stream) {
+extern "C" int pn_agg_activation_signs(const pn_agg_params* p, const void* saved, int64_t saved_bytes, int64_t S_cap, int64_t M_cap,
+                                       int64_t S, int64_t M, uint8_t* pair_signs, uint8_t* sample_signs, void* stream) {
     AggDims d;
     PN_TRY(make_dims(p, d));
-    PN_CHECK_ARG(saved && pair_signs && sample_signs, "pn_agg_activation_signs: null argument");
-    PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_activation_signs: saved buffer too small");
+    PN_CHECK_ARG(saved && pair_signs && sample_signs && S <= S_cap && M <= M_cap, "pn_agg_activation_signs: bad argument");
+    PN_CHECK_ARG(saved_bytes >= carve_saved(d, S_cap, M_cap, nullptr, 0, nullptr), "pn_agg_activation_signs: saved buffer too small");
     if (S <= 0 || M <= 0) return PN_OK;
     Saved sv;
-    carve_saved(d, S, M, const_cast<void*>(saved), saved_bytes, &sv);
+    carve_saved(d, S_cap, M_cap, const_cast<void*>(saved), saved_bytes, &sv);
     cudaStream_t st = (cudaStream_t)stream;
     const float* pl[4] = {sv.H1, sv.X3, sv.H3, sv.H4};
     const int pld[4] = {d.W, d.in3p, d.W, d.W};
     for (int l = 0; l < 4; ++l) {
-        act_signs_kernel<<<(unsigned)(cdiv(M * d.W, 256) < 4096 ? cdiv(M * d.W, 256) : 4096), 256, 0, st>>>(pl[l], M, pld[l], d.W, pair_signs + (int64_t)l * M * d.W);
+        act_signs_kernel<<<grid_thread_items(M * d.W), 256, 0, st>>>(pl[l], M, pld[l], d.W, pair_signs + (int64_t)l * M * d.W);
         PN_LAUNCH_CHECK("act_signs");
     }
     const float* sl[3] = {sv.C1, sv.C2, sv.C3};
     for (int l = 0; l < 3; ++l) {
-        act_signs_kernel<<<(unsigned)(cdiv(S * d.C, 256) < 4096 ? cdiv(S * d.C, 256) : 4096), 256, 0, st>>>(sl[l], S, d.C, d.C, sample_signs + (int64_t)l * S * d.C);
+        act_signs_kernel<<<grid_thread_items(S * d.C), 256, 0, st>>>(sl[l], S, d.C, d.C, sample_signs + (int64_t)l * S * d.C);
         PN_LAUNCH_CHECK("act_signs");
     }
     return PN_OK;
 }
 
-static GemmNT nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int N, int Kd,
+// C[rows, N] = epilogue(A[rows, Kd] x image(B)^T); rows = min(*rows_dev, rows_cap) when the count lives on the device
+static GemmNT nt(const float* A, int64_t lda, const char* Bimg, float* C, int64_t ldc, int64_t rows_cap, const int32_t* rows_dev, int N, int Kd,
                  const float* bias, int leaky, float slope) {
     GemmNT g;
-    g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.Kd = Kd;
-    g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr; g.Bimg = nullptr;
+    g.A = A; g.lda = lda; g.B = nullptr; g.ldb = 0; g.C = C; g.ldc = ldc; g.M = rows_cap; g.N = N; g.Kd = Kd;
+    g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr; g.Bimg = Bimg;
+    g.Mdev = rows_dev;
     return g;
 }
 
@@ -211,51 +218,41 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     AggDims d;
     PN_TRY(make_dims(p, d));
     PN_CHECK_ARG(in && w && saved && (decoded || (p->compact_out && in->S == 0)), "pn_agg_forward: null argument");
-    const int64_t S = in->S, M = in->M;
+    const int64_t S = in->S, M = in->M;           // exact counts, or capacities when in->counts is set
     PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_forward: saved buffer too small");
     PN_CHECK_ARG(workspace_bytes >= carve_fwd(d, nullptr, 0, nullptr), "pn_agg_forward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
     if (!d.compact_out) PN_CUDA(cudaMemsetAsync(decoded, 0, in->n_slots * (int64_t)(d.C + 1) * sizeof(float), st));
     if (weight_out) PN_CUDA(cudaMemsetAsync(weight_out, 0, in->n_slots * (int64_t)d.K * sizeof(float), st));
     if (S <= 0 || M <= 0) return PN_OK;
+    const int32_t* Sdev = in->counts;
+    const int32_t* Mdev = in->counts ? in->counts + 1 : nullptr;
     Saved sv;
     carve_saved(d, S, M, saved, saved_bytes, &sv);
     FwdWs ws;
     carve_fwd(d, workspace, workspace_bytes, &ws);
-    // padded copies of the three weights whose input width is not a multiple of 16
-    if (mlp_path() != 1) {
-        PN_TRY(copy_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1a, d.in1p, st));
-        PN_TRY(copy_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3a, d.in3p, st));
-        PN_TRY(copy_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0, d.incp, st));
-    }
-
-    const bool tcp = mlp_path() == 1;
-    if (tcp) {
-        const PackJob jobs[7] = {{w->block1_0_w, d.in1, 1, d.W, d.in1, d.W, d.in1p, ws.I1a}, {w->block1_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I1b},
-                                 {w->block3_0_w, d.in3, 1, d.W, d.in3, d.W, d.in3p, ws.I3a}, {w->block3_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I3b},
-                                 {w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0},  {w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2},
-                                 {w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4}};
-        PN_TRY(pack_nt_images(jobs, 7, st));
-    }
-    auto with_img = [&](GemmNT g, const char* img) { g.Bimg = tcp ? img : nullptr; return g; };
-    agg_prep_kernel<<<(unsigned)cdiv(S * 32, 256), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
+    const PackJob jobs[7] = {{w->block1_0_w, d.in1, 1, d.W, d.in1, d.W, d.in1p, ws.I1a}, {w->block1_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I1b},
+                             {w->block3_0_w, d.in3, 1, d.W, d.in3, d.W, d.in3p, ws.I3a}, {w->block3_2_w, d.W, 1, d.W, d.W, d.W, d.W, ws.I3b},
+                             {w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0},  {w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2},
+                             {w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4}};
+    PN_TRY(pack_nt_images(jobs, 7, st));
+    agg_prep_kernel<<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
     PN_LAUNCH_CHECK("agg_prep");
-    agg_prep_rows_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
+    agg_prep_rows_kernel<<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
     PN_LAUNCH_CHECK("agg_prep_rows");
-    PN_TRY(gemm_nt(with_img(nt(sv.X1, d.in1p, ws.W1a, d.in1p, sv.H1, d.W, M, d.W, d.in1p, w->block1_0_b, 1, d.slope), ws.I1a), st));
-    PN_TRY(gemm_nt(with_img(nt(sv.H1, d.W, w->block1_2_w, d.W, sv.X3, d.in3p, M, d.W, d.W, w->block1_2_b, 1, d.slope), ws.I1b), st));
-    PN_TRY(gemm_nt(with_img(nt(sv.X3, d.in3p, ws.W3a, d.in3p, sv.H3, d.W, M, d.W, d.in3p, w->block3_0_b, 1, d.slope), ws.I3a), st));
-    PN_TRY(gemm_nt(with_img(nt(sv.H3, d.W, w->block3_2_w, d.W, sv.H4, d.W, M, d.W, d.W, w->block3_2_b, 1, d.slope), ws.I3b), st));
-    unsigned sblocks = (unsigned)cdiv(S * 32, 256);
+    PN_TRY(gemm_nt(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H3, d.W, ws.I3b, sv.H4, d.W, M, Mdev, d.W, d.W, w->block3_2_b, 1, d.slope), st));
     if (d.W == 256)
-        agg_reduce_kernel<8><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
+        agg_reduce_kernel<8><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     else
-        agg_reduce_kernel<4><<<sblocks, 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
+        agg_reduce_kernel<4><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     PN_LAUNCH_CHECK("agg_reduce");
-    PN_TRY(gemm_nt(with_img(nt(sv.FS, d.incp, ws.Wc0, d.incp, sv.C1, d.C, S, d.C, d.incp, w->color_0_b, 1, d.slope), ws.Ic0), st));
-    PN_TRY(gemm_nt(with_img(nt(sv.C1, d.C, w->color_2_w, d.C, sv.C2, d.C, S, d.C, d.C, w->color_2_b, 1, d.slope), ws.Ic2), st));
-    PN_TRY(gemm_nt(with_img(nt(sv.C2, d.C, w->color_4_w, d.C, sv.C3, d.C, S, d.C, d.C, w->color_4_b, 1, d.slope), ws.Ic4), st));
-    agg_finish_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
+    PN_TRY(gemm_nt(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope), st));
+    agg_finish_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");
     return PN_OK;
 }
@@ -267,7 +264,7 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
 // exposed.  The chain runs on a library-owned high-priority stream, the weight gradients on the caller's stream: CTAs of
 // whichever kernel is queued fill the SMs the other one's tail frees.  Events order the two (RAW per gradient buffer, one
 // WAR before the last chain GEMM reuses GA); the caller's stream joins the chain at the end, so for the caller the call is
-// still "enqueued on the given stream".
+// still "enqueued on the given stream" (and, under stream capture, the fork / join becomes two branches of the graph).
 namespace pn {
 struct BwdStreams {
     cudaStream_t chain = nullptr;
@@ -296,19 +293,7 @@ static BwdStreams* bwd_streams() {
 }
 static int g_bwd_two_streams = 1;
 static int g_bwd_chain_first = 0;    // pn_set_backward_schedule(2): all weight-gradient GEMMs after the data-gradient chain
-extern int g_knn_threads;
 }  // namespace pn
-
-static int zero_weight_grads(const AggDims& d, const pn_agg_weights* g, cudaStream_t st) {
-    struct { float* p; int64_t n; } items[] = {
-        {g->block1_0_w, (int64_t)d.W * d.in1}, {g->block1_0_b, d.W}, {g->block1_2_w, (int64_t)d.W * d.W}, {g->block1_2_b, d.W},
-        {g->block3_0_w, (int64_t)d.W * d.in3}, {g->block3_0_b, d.W}, {g->block3_2_w, (int64_t)d.W * d.W}, {g->block3_2_b, d.W},
-        {g->alpha_0_w, d.W}, {g->alpha_0_b, 1}, {g->color_0_w, (int64_t)d.C * d.inc}, {g->color_0_b, d.C},
-        {g->color_2_w, (int64_t)d.C * d.C}, {g->color_2_b, d.C}, {g->color_4_w, (int64_t)d.C * d.C}, {g->color_4_b, d.C}};
-    for (auto& it : items)
-        if (it.p) PN_CUDA(cudaMemsetAsync(it.p, 0, it.n * sizeof(float), st));
-    return PN_OK;
-}
 
 extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg_weights* w,
                                const float* grad_decoded, const void* saved, int64_t saved_bytes, const pn_agg_weights* gw,
@@ -318,10 +303,12 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     AggDims d;
     PN_TRY(make_dims(p, d));
     PN_CHECK_ARG(in && w && saved && gw && (grad_decoded || (p->compact_out && in->S == 0)), "pn_agg_backward: null argument");
-    const int64_t S = in->S, M = in->M, T = in->T;
+    const int64_t S = in->S, M = in->M, T = in->T;       // S, M: exact counts, or capacities when in->counts is set
     PN_CHECK_ARG(saved_bytes >= carve_saved(d, S, M, nullptr, 0, nullptr), "pn_agg_backward: saved buffer too small");
     PN_CHECK_ARG(workspace_bytes >= carve_bwd(d, S, M, T, nullptr, 0, nullptr), "pn_agg_backward: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
+    const int32_t* Sdev = in->counts;
+    const int32_t* Mdev = in->counts ? in->counts + 1 : nullptr;
     // row gradients default to zero (empty slots / unreferenced table rows)
     int64_t rows = scatter_rows ? T : in->n_slots * (int64_t)d.K;
     if (g_emb) PN_CUDA(cudaMemsetAsync(g_emb, 0, rows * d.F * sizeof(float), st));
@@ -330,38 +317,36 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     if (g_conf) PN_CUDA(cudaMemsetAsync(g_conf, 0, rows * sizeof(float), st));
     if (touched_ids && scatter_rows) PN_CUDA(cudaMemsetAsync(touched_ids, 0xFF, (M > 0 ? M : 1) * sizeof(int), st));
     if (n_touched) PN_CUDA(cudaMemsetAsync(n_touched, 0, sizeof(int), st));
-    if (S <= 0 || M <= 0) return zero_weight_grads(d, gw, st);
+    if (S <= 0 || M <= 0) {                               // (capacities are never 0 for a batch with slots)
+        struct { float* ptr; int64_t n; } items[] = {
+            {gw->block1_0_w, (int64_t)d.W * d.in1}, {gw->block1_0_b, d.W}, {gw->block1_2_w, (int64_t)d.W * d.W}, {gw->block1_2_b, d.W},
+            {gw->block3_0_w, (int64_t)d.W * d.in3}, {gw->block3_0_b, d.W}, {gw->block3_2_w, (int64_t)d.W * d.W}, {gw->block3_2_b, d.W},
+            {gw->alpha_0_w, d.W}, {gw->alpha_0_b, 1}, {gw->color_0_w, (int64_t)d.C * d.inc}, {gw->color_0_b, d.C},
+            {gw->color_2_w, (int64_t)d.C * d.C}, {gw->color_2_b, d.C}, {gw->color_4_w, (int64_t)d.C * d.C}, {gw->color_4_b, d.C}};
+        for (auto& it : items)
+            if (it.ptr) PN_CUDA(cudaMemsetAsync(it.ptr, 0, it.n * sizeof(float), st));
+        return PN_OK;
+    }
 
     Saved sv;
     carve_saved(d, S, M, const_cast<void*>(saved), saved_bytes, &sv);
     BwdWs ws;
     carve_bwd(d, S, M, T, workspace, workspace_bytes, &ws);
     const int pgw = d.F + 8;
-    // transposed (K-contiguous over the OUTPUT index) weight copies for the data-gradient GEMMs
     // block1.0's data gradient is only needed for the embedding-derived input columns [emb | PE(emb)]: the distance
     // encoding behind them has no trainable input (xyz_grad = 0), so the GEMM stops at column ng1 (224 of 288)
     const int ng1 = (int)align_up(d.F + 2 * d.ff * d.F, 16) < d.in1p ? (int)align_up(d.F + 2 * d.ff * d.F, 16) : d.in1p;
-    const bool tcp = mlp_path() == 1;
-    if (tcp) {   // images of W^T: B[n = input column, k = output unit] = W[k, n]
+    {   // images of W^T: B[n = input column, k = output unit] = W[k, n]
         const PackJob jobs[7] = {{w->block1_0_w, 1, d.in1, ng1 < d.in1 ? ng1 : d.in1, d.W, ng1, d.W, ws.J1a}, {w->block1_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J1b},
                                  {w->block3_0_w, 1, d.in3, d.in3, d.W, d.in3p, d.W, ws.J3a}, {w->block3_2_w, 1, d.W, d.W, d.W, d.W, d.W, ws.J3b},
                                  {w->color_0_w, 1, d.inc, d.inc, d.C, d.incp, d.C, ws.Jc0},  {w->color_2_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc2},
                                  {w->color_4_w, 1, d.C, d.C, d.C, d.C, d.C, ws.Jc4}};
         PN_TRY(pack_nt_images(jobs, 7, st));
-    } else {
-        PN_TRY(transpose_pad(w->block1_0_w, d.W, d.in1, d.in1, ws.W1aT, d.W, d.in1p, st));
-        PN_TRY(transpose_pad(w->block1_2_w, d.W, d.W, d.W, ws.W1bT, d.W, d.W, st));
-        PN_TRY(transpose_pad(w->block3_0_w, d.W, d.in3, d.in3, ws.W3aT, d.W, d.in3p, st));
-        PN_TRY(transpose_pad(w->block3_2_w, d.W, d.W, d.W, ws.W3bT, d.W, d.W, st));
-        PN_TRY(transpose_pad(w->color_0_w, d.C, d.inc, d.inc, ws.Wc0T, d.C, d.incp, st));
-        PN_TRY(transpose_pad(w->color_2_w, d.C, d.C, d.C, ws.Wc2T, d.C, d.C, st));
-        PN_TRY(transpose_pad(w->color_4_w, d.C, d.C, d.C, ws.Wc4T, d.C, d.C, st));
     }
-    auto IMG = [&](const char* img) { return tcp ? img : (const char*)nullptr; };
 
-    // ---- streams: hs = data-gradient chain, st = weight gradients (see BwdStreams); one stream when disabled / SIMT path
-    const bool chain_first = g_bwd_chain_first && tcp;
-    BwdStreams* bs = ((g_bwd_two_streams || chain_first) && tcp) ? bwd_streams() : nullptr;
+    // ---- streams: hs = data-gradient chain, st = weight gradients (see BwdStreams); one stream when disabled
+    const bool chain_first = g_bwd_chain_first != 0;
+    BwdStreams* bs = (g_bwd_two_streams || chain_first) ? bwd_streams() : nullptr;
     if (!bs) {
         BwdStreams* any = bwd_streams();
         if (any) any->chain_end_valid = false;
@@ -369,11 +354,13 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // chain_first: one stream, but the weight-gradient GEMMs are held back until the chain has finished and its end is
     // marked (chain_end) - a multi-GPU host exchanges the per-row gradients on another stream under those GEMMs
     cudaStream_t hs = (bs && !chain_first) ? bs->chain : st;
-    GemmTN held[8];
-    int n_held = 0;
-    auto wgrad = [&](const GemmTN& t) -> int {
-        if (chain_first) { held[n_held++] = t; return PN_OK; }
-        return gemm_tn(t, ws.tn, st);
+    struct Held { GemmTN t; float* scratch; int slot; } held[8];
+    TnFinish fin[8];
+    int n_held = 0, n_fin = 0;
+    auto wgrad = [&](GemmTN t, float* scratch) -> int {
+        const int slot = n_fin++;
+        if (chain_first) { held[n_held++] = Held{t, scratch, slot}; return PN_OK; }
+        return gemm_tn(t, scratch, &fin[slot], st);
     };
     int evi = 0;
     auto order = [&](cudaStream_t from, cudaStream_t to) -> int {   // work queued on `to` from now on sees everything queued on `from` so far
@@ -385,40 +372,33 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     };
     PN_TRY(order(st, hs));                      // inputs, zero-fills and weight images are ready
     // ---- colour branch (S rows): gradient buffers GSa -> GSb -> GSc -> GSd
-    agg_gout_kernel<<<(unsigned)cdiv(S * (d.C + 1), 256), 256, 0, hs>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
+    agg_gout_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, hs>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
     PN_LAUNCH_CHECK("agg_gout");
     PN_TRY(order(hs, st));
     {   // color.4
-        GemmTN t{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GSa, d.C, ws.Wc4T, d.C, ws.GSb, d.C, S, d.C, d.C, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.Jc4);
+        PN_TRY(wgrad(GemmTN{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C, Sdev}, ws.tn[0]));
+        GemmNT g = nt(ws.GSa, d.C, ws.Jc4, ws.GSb, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope);
         g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
         PN_TRY(gemm_nt(g, hs));
         PN_TRY(order(hs, st));
     }
     {   // color.2
-        GemmTN t{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GSb, d.C, ws.Wc2T, d.C, ws.GSc, d.C, S, d.C, d.C, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.Jc2);
+        PN_TRY(wgrad(GemmTN{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C, Sdev}, ws.tn[1]));
+        GemmNT g = nt(ws.GSb, d.C, ws.Jc2, ws.GSc, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope);
         g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
         PN_TRY(gemm_nt(g, hs));
         PN_TRY(order(hs, st));
     }
     {   // color.0: d/dFS (only the first W columns are consumed)
-        GemmTN t{ws.GSc, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GSc, d.C, ws.Wc0T, d.C, ws.GSd, d.incp, S, d.incp, d.C, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.Jc0);
-        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(wgrad(GemmTN{ws.GSc, d.C, sv.FS, d.incp, gw->color_0_w, d.inc, d.inc, gw->color_0_b, S, d.C, d.incp, Sdev}, ws.tn[2]));
+        PN_TRY(gemm_nt(nt(ws.GSc, d.C, ws.Jc0, ws.GSd, d.incp, S, Sdev, d.incp, d.C, nullptr, 0, d.slope), hs));
     }
     // ---- K-reduction and density head
     if (d.W == 256)
-        agg_reduce_bwd_kernel<8><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha, ws.chunk,
+        agg_reduce_bwd_kernel<8><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha,
                                                                  ws.GA, d.W, ws.PG, pgw, ws.apart);
     else
-        agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha, ws.chunk,
+        agg_reduce_bwd_kernel<4><<<ws.nblk_reduce, 256, 0, hs>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, ws.GSd, ws.galpha,
                                                                  ws.GA, d.W, ws.PG, pgw, ws.apart);
     PN_LAUNCH_CHECK("agg_reduce_bwd");
     agg_alpha_final_kernel<<<(unsigned)cdiv((int64_t)(d.W + 1) * 32, 256), 256, 0, hs>>>(ws.apart, ws.nblk_reduce, d.W, gw->alpha_0_w, gw->alpha_0_b);
@@ -426,10 +406,8 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     PN_TRY(order(hs, st));
     // ---- block3 (M rows).  GA = dPre4 [M,W]
     {   // block3.2
-        GemmTN t{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GA, d.W, ws.W3bT, d.W, ws.GB, d.W, M, d.W, d.W, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.J3b);
+        PN_TRY(wgrad(GemmTN{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W, Mdev}, ws.tn[3]));
+        GemmNT g = nt(ws.GA, d.W, ws.J3b, ws.GB, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope);
         g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, hs));  // GB = dPre3
         PN_TRY(order(hs, st));
@@ -440,44 +418,37 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
             ga_free = bs->ev[evi++];
             PN_CUDA(cudaEventRecord(ga_free, st));
         }
-        GemmTN t{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GB, d.W, ws.W3aT, d.W, ws.GA2, d.in3p, M, d.in3p, d.W, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.J3a);
+        PN_TRY(wgrad(GemmTN{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p, Mdev}, ws.tn[4]));
+        GemmNT g = nt(ws.GB, d.W, ws.J3a, ws.GA2, d.in3p, M, Mdev, d.in3p, d.W, nullptr, 0, d.slope);
         g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, hs));
     }
-    agg_extras_bwd_kernel<<<(unsigned)cdiv(M, 256), 256, 0, hs>>>(*in, d, ws.GA2, ws.PG, pgw);
+    agg_extras_bwd_kernel<<<grid_thread_items(M), 256, 0, hs>>>(*in, d, ws.GA2, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_extras_bwd");
     PN_TRY(order(hs, st));
     // ---- block1.  GA2[:, :W] = dPre2 (row stride in3p)
     {   // block1.2
-        GemmTN t{ws.GA2, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W};
-        PN_TRY(wgrad(t));
-        GemmNT g = nt(ws.GA2, d.in3p, ws.W1bT, d.W, ws.GB2, d.W, M, d.W, d.W, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.J1b);
+        PN_TRY(wgrad(GemmTN{ws.GA2, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W, Mdev}, ws.tn[5]));
+        GemmNT g = nt(ws.GA2, d.in3p, ws.J1b, ws.GB2, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope);
         g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
         PN_TRY(gemm_nt(g, hs));  // GB2 = dPre1
         PN_TRY(order(hs, st));
     }
     {   // block1.0: GA[M,in1p] = d/dX1 (GA is free again once block3.2's weight gradient has read dPre4)
-        GemmTN t{ws.GB2, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p};
-        PN_TRY(wgrad(t));
+        PN_TRY(wgrad(GemmTN{ws.GB2, d.W, sv.X1, d.in1p, gw->block1_0_w, d.in1, d.in1, gw->block1_0_b, M, d.W, d.in1p, Mdev}, ws.tn[6]));
         if (ga_free) PN_CUDA(cudaStreamWaitEvent(hs, ga_free, 0));
         // (chain_first: all four earlier gradient buffers are still awaited by held-back weight gradients -> GA3)
-        GemmNT g = nt(ws.GB2, d.W, ws.W1aT, d.W, chain_first ? ws.GA3 : ws.GA, d.in1p, M, ng1, d.W, nullptr, 0, d.slope);
-        g.Bimg = IMG(ws.J1a);
-        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(gemm_nt(nt(ws.GB2, d.W, ws.J1a, chain_first ? ws.GA3 : ws.GA, d.in1p, M, Mdev, ng1, d.W, nullptr, 0, d.slope), hs));
     }
-    agg_prep_bwd_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, sv.X1, chain_first ? ws.GA3 : ws.GA, ws.PG, pgw);
+    agg_prep_bwd_kernel<<<grid_warp_items(M), 256, 0, hs>>>(*in, d, sv.X1, chain_first ? ws.GA3 : ws.GA, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_prep_bwd");
     // ---- per-row gradients out
     if (!scatter_rows) {
-        agg_scatter_dense_kernel<<<(unsigned)cdiv(M * (d.F + 7), 256), 256, 0, hs>>>(*in, d, ws.PG, pgw, g_emb, g_color, g_dir, g_conf);
+        agg_scatter_dense_kernel<<<grid_thread_items(M * (d.F + 7)), 256, 0, hs>>>(*in, d, ws.PG, pgw, g_emb, g_color, g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_scatter_dense");
     } else {
         PN_CUDA(cudaMemsetAsync(ws.cnt, 0, (T + 1) * sizeof(int), hs));
-        unsigned mb = (unsigned)cdiv(M, 256);
+        const unsigned mb = grid_thread_items(M);
         agg_key_count_kernel<<<mb, 256, 0, hs>>>(*in, ws.cnt, ws.rank);
         PN_LAUNCH_CHECK("agg_key_count");
         PN_TRY(scan_exclusive_i32(ws.cnt, ws.cnt, T, true, ws.scan, hs));
@@ -485,14 +456,14 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         PN_LAUNCH_CHECK("agg_key_place");
         agg_key_order_kernel<<<mb, 256, 0, hs>>>(*in, ws.cnt, ws.tmp, ws.sorted, ws.skey);
         PN_LAUNCH_CHECK("agg_key_order");
-        agg_segment_reduce_kernel<<<(unsigned)cdiv(M * 32, 256), 256, 0, hs>>>(*in, d, ws.skey, ws.sorted, ws.PG, pgw, g_emb, g_color,
-                                                                               g_dir, g_conf);
+        agg_segment_reduce_kernel<<<grid_warp_items(M), 256, 0, hs>>>(*in, d, ws.skey, ws.sorted, ws.PG, pgw, g_emb, g_color,
+                                                                      g_dir, g_conf);
         PN_LAUNCH_CHECK("agg_segment_reduce");
         if (touched_ids) {   // sorted unique list of the table rows that received gradient
-            agg_head_flag_kernel<<<mb, 256, 0, hs>>>(M, ws.skey, ws.hflag);
+            agg_head_flag_kernel<<<mb, 256, 0, hs>>>(*in, M, ws.skey, ws.hflag);
             PN_LAUNCH_CHECK("agg_head_flag");
             PN_TRY(scan_exclusive_i32(ws.hflag, ws.hflag, M, true, ws.hscan, hs));
-            agg_head_ids_kernel<<<mb, 256, 0, hs>>>(M, ws.skey, ws.hflag, touched_ids, n_touched);
+            agg_head_ids_kernel<<<mb, 256, 0, hs>>>(*in, M, ws.skey, ws.hflag, touched_ids, n_touched);
             PN_LAUNCH_CHECK("agg_head_ids");
         }
     }
@@ -501,7 +472,8 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
         bs->chain_end_valid = true;
     }
     PN_TRY(order(hs, st));                      // the caller's stream joins the chain
-    for (int i = 0; i < n_held; ++i) PN_TRY(gemm_tn(held[i], ws.tn, st));
+    for (int i = 0; i < n_held; ++i) PN_TRY(gemm_tn(held[i].t, held[i].scratch, &fin[held[i].slot], st));
+    PN_TRY(tn_finish_batch(fin, n_fin, st));    // the seven split reductions in ONE launch
     return PN_OK;
 }
 
@@ -520,32 +492,18 @@ extern "C" int pn_agg_backward_wait_rows(void* stream) {
     return 1;
 }
 
-// ---- MLP path selection and GEMM test hooks ---------------------------------------------------------------
-extern "C" int pn_set_mlp_path(int path) {
-    PN_CHECK_ARG(path == 0 || path == 1, "pn_set_mlp_path: 0 (SIMT fp32) or 1 (tcgen05 3xTF32)");
-    set_mlp_path(path);
-    return PN_OK;
+// ---- the two GEMM building blocks of the MLP as entry points (kernel-level tests and the roofline leg of bench.py) --------
+extern "C" int64_t pn_gemm_nt_image_bytes(int32_t N, int32_t Kd) { return nt_image_bytes(N, Kd); }
+extern "C" int pn_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, const int32_t* M_dev,
+                          int32_t N, int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream) {
+    PN_CHECK_ARG(image_scratch, "pn_gemm_nt: image_scratch (pn_gemm_nt_image_bytes bytes) is required");
+    PN_TRY(pack_nt_image(B, ldb, 1, N, Kd, N, Kd, (char*)image_scratch, (cudaStream_t)stream));
+    return gemm_nt(nt(A, lda, (const char*)image_scratch, C, ldc, M, M_dev, N, Kd, bias, leaky, slope), (cudaStream_t)stream);
 }
-extern "C" int pn_get_mlp_path(void) { return mlp_path(); }
-extern "C" void pn_debug_gemm_flags(int flags) {
-    set_gemm_debug_flags(flags);
-    pn::g_bwd_two_streams = ((flags >> 10) & 1) ^ 1;   // 1024: the whole backward on the caller's stream
-}
-extern "C" int64_t pn_debug_nt_image_bytes(int32_t N, int32_t Kd) { return nt_image_bytes(N, Kd); }
-extern "C" int pn_debug_gemm_nt(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int64_t M, int32_t N,
-                                int32_t Kd, const float* bias, int32_t leaky, float slope, void* image_scratch, void* stream) {
-    GemmNT g = nt(A, lda, B, ldb, C, ldc, M, N, Kd, bias, leaky, slope);
-    if (image_scratch && mlp_path() == 1) {
-        PN_TRY(pack_nt_image(B, ldb, 1, N, Kd, N, Kd, (char*)image_scratch, (cudaStream_t)stream));
-        g.Bimg = (const char*)image_scratch;
-    }
-    return gemm_nt(g, (cudaStream_t)stream);
-}
-extern "C" int64_t pn_debug_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb) { return gemm_tn_scratch_floats(M, N, Kb); }
-extern "C" int pn_debug_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
-                                float* colsum, int64_t M, int32_t N, int32_t Kb, float* scratch, void* stream) {
-    GemmTN t{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb};
-    return gemm_tn(t, scratch, (cudaStream_t)stream);
+extern "C" int64_t pn_gemm_tn_scratch_floats(int64_t M, int32_t N, int32_t Kb) { return gemm_tn_scratch_floats(M, N, Kb); }
+extern "C" int pn_gemm_tn(const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc, int32_t Kout,
+                          float* colsum, int64_t M, const int32_t* M_dev, int32_t N, int32_t Kb, float* scratch, void* stream) {
+    return gemm_tn(GemmTN{A, lda, B, ldb, C, ldc, Kout, colsum, M, N, Kb, M_dev}, scratch, nullptr, (cudaStream_t)stream);
 }
 
 // ---- sparse exchange of per-point gradient rows between ranks (ray_shard.py) ---------------------------------

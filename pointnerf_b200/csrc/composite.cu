@@ -118,16 +118,17 @@ template <int NC>
 __global__ void __launch_bounds__(256) composite_bwd_rows_kernel(const float* __restrict__ feat, const uint8_t* __restrict__ valid,
                                                                  const int* __restrict__ row_slot, const float* __restrict__ opacity,
                                                                  const float* __restrict__ acc_T, const float* __restrict__ g_color,
-                                                                 int64_t n_rows, int SR, int C, float* __restrict__ g_feat) {
-    int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (row >= n_rows) return;
+                                                                 int64_t n_rows, const int* __restrict__ n_rows_dev, int SR, int C,
+                                                                 float* __restrict__ g_feat) {
+    const int lane = threadIdx.x & 31;
+    if (n_rows_dev) { const int64_t nd = (int64_t)__ldg(n_rows_dev); n_rows = nd < n_rows ? nd : n_rows; }   // n_rows: then the capacity
     const int C1 = C + 1;
+  for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < n_rows; row += ((int64_t)gridDim.x * blockDim.x) >> 5) {
     const int64_t slot = row_slot[row];
     float* grow = g_feat + row * C1;
     if (slot < 0) {                                     // row referenced by no slot: zero gradient
         for (int c = lane; c < C1; c += 32) grow[c] = 0.f;
-        return;
+        continue;
     }
     const int64_t ray = slot / SR;
     const float T = acc_T[slot], o = opacity[slot];
@@ -146,6 +147,7 @@ __global__ void __launch_bounds__(256) composite_bwd_rows_kernel(const float* __
     }
     if (live) dot = warp_sum(dot);
     if (lane == 0) grow[0] = live ? dot : 0.f;          // parked for pass 2, as in the per-ray kernel
+  }
 }
 
 template <int NC, bool PASS1>
@@ -279,17 +281,20 @@ __global__ void __launch_bounds__(256) bg_grad_final_kernel(const float* __restr
 // summation tree: the value is a pure function of the inputs (run-to-run and rank-count independent).
 constexpr int kLossBlocks = 128;
 __global__ void __launch_bounds__(256) color_mse_partial_kernel(const float* __restrict__ pred, const float* __restrict__ target,
-                                                                const float* __restrict__ ray_weight, int64_t n, int C,
-                                                                float inv_norm, float* __restrict__ partial,
-                                                                float* __restrict__ grad) {
+                                                                const float* __restrict__ ray_weight, const int* __restrict__ ray_mask,
+                                                                int64_t n, int C, float inv_norm, const float* __restrict__ inv_norm_dev,
+                                                                float* __restrict__ partial, float* __restrict__ grad) {
     __shared__ float red[8];
+    if (inv_norm_dev) inv_norm *= __ldg(inv_norm_dev);
     const float g2 = 2.f * inv_norm;
+    const bool weighted = ray_weight || ray_mask;
     float acc = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         float d = pred[i] - target[i];
         float w = ray_weight ? ray_weight[i / C] : 1.f;
+        if (ray_mask) w = ray_mask[i / C] > 0 ? w : 0.f;
         acc = __fmaf_rn(w * d, d, acc);
-        if (grad) grad[i] = ray_weight ? (g2 * w) * d : g2 * d;
+        if (grad) grad[i] = weighted ? (g2 * w) * d : g2 * d;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -303,8 +308,9 @@ __global__ void __launch_bounds__(256) color_mse_partial_kernel(const float* __r
     }
 }
 __global__ void __launch_bounds__(kLossBlocks) color_mse_final_kernel(const float* __restrict__ partial, float inv_norm,
-                                                                       float* __restrict__ loss) {
+                                                                       const float* __restrict__ inv_norm_dev, float* __restrict__ loss) {
     __shared__ float red[kLossBlocks / 32];
+    if (inv_norm_dev) inv_norm *= __ldg(inv_norm_dev);
     float acc = partial[threadIdx.x];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -405,7 +411,7 @@ extern "C" int pn_composite_backward(const float* ray_features, const float* ray
                                      const int32_t* slot_row, const float* bg_color, const float* opacity, const float* acc_T, const float* bg_T,
                                      const float* g_ray_color, const float* g_opacity, const float* g_acc_T,
                                      const float* g_blend_w, const float* g_bg_T, int64_t n_rays, int32_t SR, int32_t C,
-                                     int64_t n_rows, float* g_features, float* g_bg_color, void* workspace,
+                                     int64_t n_rows, const int32_t* n_rows_dev, float* g_features, float* g_bg_color, void* workspace,
                                      int64_t workspace_bytes, void* stream) {
     PN_CHECK_ARG(ray_features && ray_dist && ray_valid && opacity && acc_T && bg_T && g_features, "pn_composite_backward: null argument");
     PN_CHECK_ARG(C >= 1 && C <= 256 && SR > 0, "pn_composite_backward: C=%d SR=%d unsupported", C, SR);
@@ -421,8 +427,9 @@ extern "C" int pn_composite_backward(const float* ray_features, const float* ray
         PN_CUDA(cudaMemsetAsync(row_slot, 0xFF, n_rows * sizeof(int), st));
         slot_invert_kernel<<<(unsigned)cdiv(n_rays * SR, 256), 256, 0, st>>>(slot_row, n_rays * SR, n_rows, row_slot);
         PN_LAUNCH_CHECK("slot_invert");
-        PN_DISPATCH_NC(C, (composite_bwd_rows_kernel<NC><<<(unsigned)cdiv(n_rows * 32, 256), 256, 0, st>>>(
-                              ray_features, ray_valid, row_slot, opacity, acc_T, g_ray_color, n_rows, SR, C, g_features)));
+        const int64_t want = cdiv(n_rows * 32, 256), most = (int64_t)kNumSMs * 8;
+        PN_DISPATCH_NC(C, (composite_bwd_rows_kernel<NC><<<(unsigned)(want < most ? want : most), 256, 0, st>>>(
+                              ray_features, ray_valid, row_slot, opacity, acc_T, g_ray_color, n_rows, n_rows_dev, SR, C, g_features)));
         PN_LAUNCH_CHECK("composite_bwd_rows");
         PN_DISPATCH_NC(C, (composite_bwd_kernel<NC, false><<<blocks, 256, 0, st>>>(ray_features, ray_dist, ray_valid, slot_row, bg_color, opacity,
                                                                                  acc_T, bg_T, g_ray_color, g_opacity, g_acc_T, g_blend_w,
@@ -450,16 +457,17 @@ extern "C" int pn_composite_backward(const float* ray_features, const float* ray
 
 extern "C" int64_t pn_color_mse_workspace_bytes(void) { return (int64_t)kLossBlocks * sizeof(float); }
 
-extern "C" int pn_color_mse(const float* pred, const float* target, const float* ray_weight, int64_t n_rays, int32_t C,
-                            float inv_norm, float* loss, float* grad, void* workspace, int64_t workspace_bytes, void* stream) {
+extern "C" int pn_color_mse(const float* pred, const float* target, const float* ray_weight, const int32_t* ray_mask, int64_t n_rays,
+                            int32_t C, float inv_norm, const float* inv_norm_dev, float* loss, float* grad, void* workspace,
+                            int64_t workspace_bytes, void* stream) {
     PN_CHECK_ARG(loss && workspace, "pn_color_mse: null argument");
     PN_CHECK_ARG(n_rays >= 0 && C >= 1, "pn_color_mse: n_rays=%lld C=%d", (long long)n_rays, C);
     PN_CHECK_ARG(n_rays == 0 || (pred && target), "pn_color_mse: null argument");
     PN_CHECK_ARG(workspace_bytes >= pn_color_mse_workspace_bytes(), "pn_color_mse: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
-    color_mse_partial_kernel<<<kLossBlocks, 256, 0, st>>>(pred, target, ray_weight, n_rays * C, C, inv_norm, (float*)workspace, grad);
+    color_mse_partial_kernel<<<kLossBlocks, 256, 0, st>>>(pred, target, ray_weight, ray_mask, n_rays * C, C, inv_norm, inv_norm_dev, (float*)workspace, grad);
     PN_LAUNCH_CHECK("color_mse_partial");
-    color_mse_final_kernel<<<1, kLossBlocks, 0, st>>>((const float*)workspace, inv_norm, loss);
+    color_mse_final_kernel<<<1, kLossBlocks, 0, st>>>((const float*)workspace, inv_norm, inv_norm_dev, loss);
     PN_LAUNCH_CHECK("color_mse_final");
     return PN_OK;
 }

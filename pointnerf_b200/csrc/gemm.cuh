@@ -19,8 +19,9 @@ struct GemmNT {
     const float* bias;
     int leaky; float slope;
     const float* aux; int64_t ldaux; int aux_cols;
-    const int* rowmap;
-    const char* Bimg;   // optional: pre-split, pre-swizzled operand image of B (pack_nt_image); tensor-core path only
+    const int* rowmap;  // unused (kept so that positional initialisers stay valid)
+    const char* Bimg;   // pre-split, pre-swizzled operand image of B (pack_nt_image)
+    const int32_t* Mdev;  // optional DEVICE row count: rows = min(*Mdev, M); M is then the capacity the launch is sized for
 };
 int gemm_nt(const GemmNT& g, cudaStream_t st);
 // Operand image of a B matrix for the tensor-core NT GEMM: B[n, k] = src[n*s_n + k*s_k] for n < N, k < K, zero beyond,
@@ -28,7 +29,6 @@ int gemm_nt(const GemmNT& g, cudaStream_t st);
 // layout (128-byte swizzle) so that one TMA bulk copy per K chunk stages it.
 int64_t nt_image_bytes(int Np, int Kp);
 int pack_nt_image(const float* src, int64_t s_n, int64_t s_k, int N, int K, int Np, int Kp, char* img, cudaStream_t st);
-void set_gemm_debug_flags(int f);   // ablation switches of the NT image kernel (results become garbage)
 constexpr int kMaxPackJobs = 8;
 struct PackJob { const float* src; int64_t s_n, s_k; int N, K, Np, Kp; char* img; };
 int pack_nt_images(const PackJob* jobs, int n, cudaStream_t st);   // same images, one launch
@@ -44,18 +44,17 @@ struct GemmTN {
     float* C; int64_t ldc; int Kout;
     float* colsum;
     int64_t M; int N; int Kb;
+    const int32_t* Mdev;  // optional DEVICE row count (see GemmNT::Mdev)
 };
-int64_t gemm_tn_scratch_floats(int64_t M, int N, int Kb);
-int gemm_tn(const GemmTN& g, float* scratch, cudaStream_t st);
-
-// MLP arithmetic path (process-wide): 0 = exact-fp32 SIMT GEMMs, 1 = tcgen05 3xTF32 split products (default)
-int mlp_path();
-void set_mlp_path(int p);
-
-// dst[c*ldd + r] = src[r*lds + c] for r < rows, c < cols; dst columns rows..ldd-1 zero (weights only: small)
-int transpose_pad(const float* src, int rows, int cols, int64_t lds, float* dst, int64_t ldd, int dst_rows_padded,
-                  cudaStream_t st);
-// dst[r*ldd + c] = c < cols ? src[r*lds + c] : 0   for r < rows, c < ldd
-int copy_pad(const float* src, int rows, int cols, int64_t lds, float* dst, int64_t ldd, cudaStream_t st);
+// second stage (fixed-order sum of the split partials) of one TN GEMM; several are finished by one launch
+struct TnFinish {
+    const float* partial; const float* cpartial; int slots, N, Kb, Kout;
+    float* C; int64_t ldc; float* colsum; int64_t M; const int32_t* Mdev;
+};
+constexpr int kMaxTnJobs = 8;
+int64_t gemm_tn_scratch_floats(int64_t Mcap, int N, int Kb);
+// scratch: gemm_tn_scratch_floats floats, private to this GEMM until its finish has run.  fin == NULL: finished right away.
+int gemm_tn(const GemmTN& g, float* scratch, TnFinish* fin, cudaStream_t st);
+int tn_finish_batch(const TnFinish* jobs, int n, cudaStream_t st);
 
 }  // namespace pn

@@ -21,11 +21,9 @@ constexpr int TBM = 128;          // rows of A per CTA = TMEM lanes
 constexpr int TBK = 32;           // tf32 elements per 128-byte swizzle row
 constexpr int TMAXN = 256;
 constexpr int kLoadThreads = 256;
-constexpr int kThreads = kLoadThreads + 32;
 constexpr int A_BYTES = TBM * 128;              // 16 KB per (hi | lo)
 constexpr int B_BYTES = TMAXN * 128;            // 32 KB per (hi | lo)
 constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // 96 KB
-constexpr int NT_SMEM = 2 * STAGE_BYTES + 1024 + 256;
 
 __device__ __forceinline__ uint32_t sw128_off(int row, int chunk) {
     return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) << 4));
@@ -84,138 +82,6 @@ __device__ __forceinline__ void epilogue_via_smem(uint32_t tmem_d, int BN, float
 }
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 1) gemm_nt_tc_kernel(GemmNT g, int BN, int tmem_cols) {
-    extern __shared__ char smem_raw[];
-    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * STAGE_BYTES);  // full[2], empty[2], done
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int64_t m0 = (int64_t)blockIdx.x * TBM;
-    const int n0 = blockIdx.y * BN;
-    const int nk = (g.Kd + TBK - 1) / TBK;
-
-    if (t == 0) {
-        tc::mbar_init(&bars[0], kLoadThreads);
-        tc::mbar_init(&bars[1], kLoadThreads);
-        tc::mbar_init(&bars[2], 1);
-        tc::mbar_init(&bars[3], 1);
-        tc::mbar_init(&bars[4], 1);
-        tc::mbar_fence_init();
-    }
-    if (warp == 8) tc::tmem_alloc(tmem_slot, (uint32_t)tmem_cols);
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
-    const uint32_t tmem_d = *tmem_slot;
-
-    if (warp < 8) {
-        // ------------------------------------------------ operand staging
-        const int c = t & 7, r0 = t >> 3;            // 16-byte chunk, first row
-        const int nb = (BN + 31) >> 5;               // row groups of 32 in the B tile
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 ca[4], cb[8], na[4], nb4[8];
-        auto load = [&](int kc, float4 (&ra)[4], float4 (&rb)[8]) {
-            const int gk = kc * TBK + 4 * c;
-            const bool kok = gk < g.Kd;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int64_t m = m0 + r0 + 32 * i;
-                ra[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                int row = r0 + 32 * i;
-                int n = n0 + row;
-                rb[i] = (i < nb && kok && row < BN && n < g.N) ? __ldg(reinterpret_cast<const float4*>(g.B + (int64_t)n * g.ldb + gk)) : z4;
-            }
-        };
-        load(0, ca, cb);
-        for (int kc = 0; kc < nk; ++kc) {
-            const int s = kc & 1;
-            if (kc + 1 < nk) load(kc + 1, na, nb4);
-            tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
-            char* st = smem + s * STAGE_BYTES;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) split_store(st, st + A_BYTES, sw128_off(r0 + 32 * i, c), ca[i]);
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                if (i < nb) split_store(st + 2 * A_BYTES, st + 2 * A_BYTES + B_BYTES, sw128_off(r0 + 32 * i, c), cb[i]);
-            tc::fence_proxy_async();
-            tc::mbar_arrive(&bars[s]);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) ca[i] = na[i];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) cb[i] = nb4[i];
-        }
-        // ------------------------------------------------ epilogue: TMEM -> registers -> global
-        tc::mbar_wait(&bars[4], 0);
-        tc::fence_after_sync();
-        const int q = warp & 3, half = warp >> 2;
-        const int64_t m = m0 + q * 32 + lane;
-        const int nchunks = BN >> 4;
-        for (int j = half; j < nchunks; j += 2) {
-            float v[16];
-            tc::tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * 16), v);
-            if (m < g.M) {
-                const int nb0 = n0 + j * 16;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    int n = nb0 + i;
-                    if (n < g.N) {
-                        float x = v[i];
-                        if (g.bias) x += __ldg(g.bias + n);
-                        if (g.leaky) x = x > 0.f ? x : g.slope * x;
-                        if (g.aux && n < g.aux_cols) x *= (__ldg(g.aux + m * g.ldaux + n) > 0.f) ? 1.f : g.slope;
-                        v[i] = x;
-                    }
-                }
-                float* crow = g.C + m * g.ldc + nb0;
-                if (nb0 + 16 <= g.N && ((((uintptr_t)crow) & 15) == 0)) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        *reinterpret_cast<float4*>(crow + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (nb0 + i < g.N) crow[i] = v[i];
-                }
-            }
-        }
-        tc::fence_before_sync();
-    } else {
-      if (lane == 0) {
-        // ------------------------------------------------ MMA issue (one thread)
-        const uint32_t idesc = tc::idesc_tf32(TBM, BN, 0, 0);
-        const uint32_t sbase = tc::smem_u32(smem);
-        for (int kc = 0; kc < nk; ++kc) {
-            const int s = kc & 1;
-            tc::mbar_wait(&bars[s], (kc >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t a_hi = sbase + s * STAGE_BYTES, a_lo = a_hi + A_BYTES;
-            const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + B_BYTES;
-            int ksteps = (g.Kd - kc * TBK + 7) >> 3;
-            if (ksteps > 4) ksteps = 4;
-            for (int k = 0; k < ksteps; ++k) {
-                const uint32_t ko = 32u * k;
-                uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
-                uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
-                tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
-                tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
-                tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
-            }
-            tc::mma_commit(&bars[2 + s]);   // frees the stage when these MMAs have read it
-        }
-        tc::mma_commit(&bars[4]);           // accumulator complete
-      }
-      __syncwarp();
-    }
-    __syncthreads();
-    if (warp == 8) {
-        tc::fence_after_sync();
-        tc::tmem_dealloc(tmem_d, (uint32_t)tmem_cols);
-    }
-}
-
 // ---------------------------------------------------------------------------------------------------------------
 // TN: C[n, k] = sum_m A[m, n] * B[m, k].  The reduction index m is the slow dimension of both operands in global
 // memory, i.e. both are MN-major for the tensor core: a chunk of 32 reduction rows is staged as 128-byte panels
@@ -223,10 +89,23 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_nt_tc_kernel(GemmNT g, int B
 // ---------------------------------------------------------------------------------------------------------------
 // BKt <= 288 columns of B per CTA: above 256 the tile is issued as two MMAs per K-step (N1 = 160 and N2 = BKt - 160 columns,
 // both panel-aligned) into adjacent TMEM columns, so that A (the dPre tile) is staged ONCE for the whole weight row.
+// Split geometry of the TN reduction, a function of the row count M and the number of split slots the launch provides:
+// every slot reduces a contiguous slice of `rps` rows (a multiple of the 32-row chunk, at least 256); only the first
+// cdiv(M, rps) slots hold work.  Evaluated on the DEVICE when the row count lives there (GemmTN::Mdev).
+__host__ __device__ __forceinline__ int64_t tn_rows_per_split(int64_t M, int slots) {
+    int64_t r = ((M > 0 ? M : 1) + slots - 1) / slots;
+    r = (r + TBK - 1) / TBK * TBK;
+    return r < 256 ? 256 : r;
+}
+__device__ __forceinline__ int64_t tn_rows(const GemmTN& g) {
+    if (!g.Mdev) return g.M;
+    const int64_t md = (int64_t)__ldg(g.Mdev);
+    return md < g.M ? md : g.M;
+}
 constexpr int kTnLoad = 512;                 // staging threads of the TN kernel (16 warps) + 1 MMA warp
 constexpr int kTnThreads = kTnLoad + 32;
-__global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int BKt, int tmem_cols, int64_t rows_per_split,
-                                                                   float* __restrict__ partial, float* __restrict__ cpartial, int dbg) {
+__global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int BKt, int tmem_cols,
+                                                                   float* __restrict__ partial, float* __restrict__ cpartial) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     constexpr int PANEL = TBK * 128;                     // bytes of one 32-wide panel over a 32-row chunk
@@ -238,9 +117,12 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int j0 = blockIdx.x * BKt;       // first column of B (k of the weight)
     const int i0 = blockIdx.y * TBM;       // first column of A (n of the weight)
+    g.M = tn_rows(g);
+    const int64_t rows_per_split = tn_rows_per_split(g.M, (int)gridDim.z);
     const int64_t r_begin = (int64_t)blockIdx.z * rows_per_split;
     const int64_t r_end = r_begin + rows_per_split < g.M ? r_begin + rows_per_split : g.M;
     const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
+    if (nk == 0 && blockIdx.z > 0) return;      // an empty split slot (the finish reads only the first cdiv(M, rps) slots)
 
     if (t == 0) {
         tc::mbar_init(&bars[0], kTnLoad / 64);
@@ -283,12 +165,12 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int64_t rr = rb0 + ar0 + 8 * i;
-                ra[i] = (a_ok && rr < r_end && !(dbg & 2)) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
+                ra[i] = (a_ok && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.A + rr * g.lda + i0 + 4 * ac4)) : z4;
             }
 #pragma unroll
             for (int i = 0; i < NB; ++i) {
                 int64_t rr = rb0 + (brow[i] & 0xFF);
-                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end && !(dbg & 2)) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
+                rb[i] = (brow[i] >= 0 && !(brow[i] & 0x100) && rr < r_end) ? __ldg(reinterpret_cast<const float4*>(g.B + rr * g.ldb + j0 + 4 * bc4[i])) : z4;
             }
         };
         if (grp < nk) load(grp);
@@ -296,7 +178,7 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
             const int s = kc & 1;
             tc::mbar_wait(&bars[2 + s], ((kc >> 1) & 1) ^ 1);
             const uint32_t st = smem_u + (uint32_t)(s * stage_bytes);
-            if (!(dbg & 16)) {
+            {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 int row = ar0 + 8 * i;
@@ -363,7 +245,6 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
             const uint32_t b_hi = a_hi + 2 * A_BYTES, b_lo = b_hi + (uint32_t)b_bytes;
             int64_t rows = r_end - (r_begin + (int64_t)kc * TBK);
             int ksteps = rows >= TBK ? 4 : (int)((rows + 7) >> 3);
-            if (dbg & 1) ksteps = 0;
             for (int k = 0; k < ksteps; ++k) {
                 const uint32_t ko = 1024u * k;
                 uint64_t dah = tc::smem_desc_sw128(a_hi + ko, PANEL, 512, 1), dal = tc::smem_desc_sw128(a_lo + ko, PANEL, 512, 1);
@@ -391,273 +272,14 @@ __global__ void __launch_bounds__(kTnThreads, 1) gemm_tn_tc_kernel(GemmTN g, int
     }
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// NT with a pre-packed B image (the product path: B is always a weight matrix).  PERSISTENT: one CTA per SM walks the
-// output tiles; the accumulator is double-buffered in TMEM (2 x 256 columns) so that the epilogue of tile i (TMEM ->
-// registers -> per-warp shared-memory transpose -> coalesced global stores) overlaps the main loop of tile i + 1.
-//   warps 0-7    stage A: global fp32 -> registers (prefetched four K chunks ahead, across tile boundaries) -> split ->
-//                swizzled smem, 2 stages; warps 0-3 take the even chunks, warps 4-7 the odd ones
-//   warp  8      one thread issues the MMAs
-//   warp  9      one thread streams the B image: one TMA bulk copy (hi|lo block, <= 64 KB) per K chunk, 2 stages
-//   warps 10-17  epilogue: TMEM lane quadrant (warp & 3), 32 rows; the two warps of a quadrant alternate 32-column
-//                chunks (whole 128-byte row segments per store); the activation-mask rows of the NEXT tile are
-//                prefetched into L2 while the current one is written
-// ---------------------------------------------------------------------------------------------------------------
+// Constants shared by the persistent NT kernel below.
 namespace {
-constexpr int NSA = 2, NSB = 2;
 constexpr int A_STAGE = 2 * A_BYTES;                 // 32 KB (hi | lo)
 constexpr int B_STAGE = 2 * B_BYTES;                 // 64 KB (hi | lo) at BN = 256
 constexpr int kEpiWarps = 8;                         // two per TMEM lane quadrant, alternating 32-column chunks
 constexpr int SLAB_BYTES = 32 * 32 * 4;              // per epilogue warp: 32 rows x 32 floats, 16-byte chunks XOR-swizzled
-constexpr int IMG_SMEM = NSA * A_STAGE + NSB * B_STAGE + kEpiWarps * SLAB_BYTES + 1024 + 256;
 constexpr int kThreadsImg = kLoadThreads + 64 + 32 * kEpiWarps;
 }  // namespace
-
-__global__ void __launch_bounds__(kThreadsImg, 1) gemm_nt_img_kernel(GemmNT g, int BN, int n_tiles_n, int n_tiles_total, int dbg) {
-    extern __shared__ char smem_raw[];
-    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    char* smA = smem;
-    char* smB = smem + NSA * A_STAGE;
-    char* slabs = smB + NSB * B_STAGE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kEpiWarps * SLAB_BYTES);
-    uint64_t *fullA = bars, *emptyA = bars + 2, *fullB = bars + 4, *emptyB = bars + 6, *accFull = bars + 8, *accEmpty = bars + 10;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int nk = (g.Kd + TBK - 1) / TBK;
-    const uint32_t b_block = (uint32_t)(2 * BN * 128);
-    // tiles of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
-    const int my_tiles = n_tiles_total > (int)blockIdx.x ? (n_tiles_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    const int total_chunks = my_tiles * nk;
-
-    if (t == 0) {
-        for (int i = 0; i < NSA; ++i) { tc::mbar_init(&fullA[i], kLoadThreads / 64); tc::mbar_init(&emptyA[i], 1); }
-        for (int i = 0; i < NSB; ++i) { tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1); }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], kEpiWarps); }
-        tc::mbar_fence_init();
-    }
-    if (warp == 8) tc::tmem_alloc(tmem_slot, 512u);
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
-    const uint32_t tmem_base = *tmem_slot;
-
-    if (warp < 8) {
-        // ---------------------------------------------------------------- A staging
-        // Two groups of four warps alternate K chunks (group 0: even, group 1: odd).  fence.proxy.async carries a
-        // CTA-scope membar that waits for every outstanding access of the thread, prefetch loads included; with one
-        // group per chunk a thread's prefetch (issued right after its arrive, two of ITS chunks = four chunks ahead)
-        // has two chunk periods to land before the thread's next fence, so the DRAM round trip stays off the
-        // producer -> MMA critical path.
-        const int grp = warp >> 2, tt = t & 127;
-        const int c = tt & 7, r0 = tt >> 3;          // rows r0 + 16 i, 16-byte chunk c
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint32_t sA_u32 = tc::smem_u32(smA);
-        float4 ra[8], rb[8];
-        auto load = [&](int L, float4 (&r)[8]) {
-            const int it = L / nk, kc = L - it * nk;
-            const int tile = (int)blockIdx.x + it * (int)gridDim.x;
-            const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM;
-            const int gk = kc * TBK + 4 * c;
-            const bool kok = gk < g.Kd && !(dbg & 2);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                int64_t m = m0 + r0 + 16 * i;
-                r[i] = (kok && m < g.M) ? __ldg(reinterpret_cast<const float4*>(g.A + m * g.lda + gk)) : z4;
-            }
-        };
-        auto step = [&](int L, float4 (&cur)[8]) {
-            const int sa = L % NSA;
-            tc::mbar_wait(&emptyA[sa], ((L / NSA) & 1) ^ 1);
-            const uint32_t st = sA_u32 + (uint32_t)(sa * A_STAGE);
-            if (!(dbg & 16))
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint32_t off = sw128_off(r0 + 16 * i, c);
-                split_store_s(st + off, st + A_BYTES + off, cur[i]);
-            }
-            if (!(dbg & 32)) tc::fence_proxy_async();
-            __syncwarp();                                   // one arrival per warp: arrivals on one barrier word serialise
-            if (lane == 0) tc::mbar_arrive(&fullA[sa]);
-            if (L + 4 < total_chunks) load(L + 4, cur);
-        };
-        if (grp < total_chunks) load(grp, ra);
-        if (grp + 2 < total_chunks) load(grp + 2, rb);
-        for (int L = grp; L < total_chunks; L += 4) {
-            step(L, ra);
-            if (L + 2 < total_chunks) step(L + 2, rb);
-        }
-    } else if (warp == 8) {
-        // ---------------------------------------------------------------- MMA issue
-        if (lane == 0) {
-            const uint32_t idesc = tc::idesc_tf32(TBM, BN, 0, 0);
-            const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
-            int L = 0;
-            for (int it = 0; it < my_tiles; ++it) {
-                const int ab = it & 1;
-                tc::mbar_wait(&accEmpty[ab], ((it >> 1) & 1) ^ 1);
-                tc::fence_after_sync();
-                const uint32_t tmem_d = tmem_base + (uint32_t)(ab * 256);
-                for (int kc = 0; kc < nk; ++kc, ++L) {
-                    const int sa = L % NSA, sb = L % NSB;
-                    tc::mbar_wait(&fullB[sb], (L / NSB) & 1);
-                    tc::mbar_wait(&fullA[sa], (L / NSA) & 1);
-                    tc::fence_after_sync();
-                    const uint32_t a_hi = sA + sa * A_STAGE, a_lo = a_hi + A_BYTES;
-                    const uint32_t b_hi = sB + sb * B_STAGE, b_lo = b_hi + (uint32_t)(BN * 128);
-                    int ksteps = (g.Kd - kc * TBK + 7) >> 3;
-                    if (ksteps > 4) ksteps = 4;
-                    if (dbg & 1) ksteps = 0;
-                    for (int k = 0; k < ksteps; ++k) {
-                        const uint32_t ko = 32u * k;
-                        uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
-                        uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
-                        tc::mma_tf32(tmem_d, dah, dbl, idesc, (kc | k) != 0);
-                        tc::mma_tf32(tmem_d, dal, dbh, idesc, 1);
-                        tc::mma_tf32(tmem_d, dah, dbh, idesc, 1);
-                    }
-                    tc::mma_commit(&emptyA[sa]);
-                    tc::mma_commit(&emptyB[sb]);
-                }
-                tc::mma_commit(&accFull[ab]);
-            }
-        }
-        __syncwarp();
-    } else if (warp == 9) {
-        // ---------------------------------------------------------------- B image producer (TMA bulk copies)
-        if (lane == 0) {
-            int L = 0;
-            for (int it = 0; it < my_tiles; ++it) {
-                const int tile = (int)blockIdx.x + it * (int)gridDim.x;
-                const char* src = g.Bimg + (int64_t)(tile % n_tiles_n) * nk * b_block;
-                for (int kc = 0; kc < nk; ++kc, ++L) {
-                    const int sb = L % NSB;
-                    tc::mbar_wait(&emptyB[sb], ((L / NSB) & 1) ^ 1);
-                    if (dbg & 4) { tc::mbar_arrive(&fullB[sb]); continue; }
-                    tc::mbar_arrive_expect_tx(&fullB[sb], b_block);
-                    tc::bulk_g2s(smB + sb * B_STAGE, src + (int64_t)kc * b_block, b_block, &fullB[sb]);
-                }
-            }
-        }
-        __syncwarp();
-    } else {
-        // ---------------------------------------------------------------- epilogue (warps 10..17)
-        const int q = warp & 3;                       // TMEM lane quadrant this warp may access
-        const int half = (warp - 10) >> 2;            // chunks j with (j & 1) == half
-        const uint32_t slab = tc::smem_u32(slabs + (warp - 10) * SLAB_BYTES);
-        const bool vec_ok = (g.ldc % 4 == 0) && ((((uintptr_t)g.C) & 15) == 0) && (g.N % 4 == 0) &&
-                            (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
-                            (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
-        const int rsub = lane >> 3, c8 = lane & 7;    // store phase: 4 rows x 128 B per instruction
-        const int nch = (BN + 31) >> 5;
-        const int my_last = ((nch - 1 - half) & ~1) + half;            // last chunk of this warp (< half: it owns none)
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        // lane = row: one 128-byte line of the mask matrix per (row, chunk) of a tile, pulled into L2 ahead of its use
-        auto prefetch_aux = [&](int tile) {
-            if (!g.aux) return;
-            const int64_t m = (int64_t)(tile / n_tiles_n) * TBM + q * 32 + lane;
-            const int n0 = (tile % n_tiles_n) * BN;
-            if (m >= g.M) return;
-            for (int j = half; j < nch; j += 2) {
-                const int n = n0 + j * 32;
-                if (n < g.aux_cols) asm volatile("prefetch.global.L2 [%0];" ::"l"(g.aux + m * g.ldaux + n));
-            }
-        };
-        if (my_tiles > 0) prefetch_aux((int)blockIdx.x);
-        for (int it = 0; it < my_tiles; ++it) {
-            const int ab = it & 1;
-            const int tile = (int)blockIdx.x + it * (int)gridDim.x;
-            const int64_t m0 = (int64_t)(tile / n_tiles_n) * TBM + q * 32;
-            const int n0 = (tile % n_tiles_n) * BN;
-            if (it + 1 < my_tiles) prefetch_aux(tile + (int)gridDim.x);
-            tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
-            if (dbg & 64) {
-                tc::fence_before_sync();
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
-                continue;
-            }
-            for (int j = half; j < nch; j += 2) {
-                uint32_t lo16[16], hi16[16];
-                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32), lo16);
-                tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32 + 16), hi16);   // columns past BN: inside the 256 allocated, masked below
-                const int n = n0 + j * 32 + 4 * c8;
-                const bool ncol_ok = (j * 32 + 4 * c8 < BN) && n < g.N;
-                float4 bias4 = z4;
-                if (vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
-                tc::tmem_ld_wait();
-                if (j == my_last) {                   // accumulator fully read by this warp: hand it back to the MMA warp
-                    tc::fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {         // row = lane; 16-byte chunk i lands at i ^ (lane & 7): conflict-free both ways
-                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u,
-                               make_float4(__uint_as_float(lo16[4 * i]), __uint_as_float(lo16[4 * i + 1]), __uint_as_float(lo16[4 * i + 2]),
-                                           __uint_as_float(lo16[4 * i + 3])));
-                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u,
-                               make_float4(__uint_as_float(hi16[4 * i]), __uint_as_float(hi16[4 * i + 1]), __uint_as_float(hi16[4 * i + 2]),
-                                           __uint_as_float(hi16[4 * i + 3])));
-                }
-                __syncwarp();
-                const bool use_aux = vec_ok && ncol_ok && g.aux && n < g.aux_cols;
-                float4 aux4[8];
-                if (use_aux) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int64_t m = m0 + 4 * i + rsub;
-                        aux4[i] = m < g.M ? __ldg(reinterpret_cast<const float4*>(g.aux + m * g.ldaux + n)) : z4;
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int row = 4 * i + rsub;
-                    const int64_t m = m0 + row;
-                    float4 x4 = tc::lds128(slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u);
-                    if (m >= g.M || !ncol_ok || (dbg & 8)) continue;
-                    float x[4] = {x4.x, x4.y, x4.z, x4.w};
-                    if (vec_ok) {
-                        x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
-                        if (g.leaky) {
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) x[e] = x[e] > 0.f ? x[e] : g.slope * x[e];
-                        }
-                        if (use_aux) {
-                            const float4 a = aux4[i];
-                            x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
-                            x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
-                        }
-                        *reinterpret_cast<float4*>(g.C + m * g.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            if (n + e >= g.N) break;
-                            float y = x[e];
-                            if (g.bias) y += __ldg(g.bias + n + e);
-                            if (g.leaky) y = y > 0.f ? y : g.slope * y;
-                            if (g.aux && n + e < g.aux_cols) y *= (__ldg(g.aux + m * g.ldaux + n + e) > 0.f) ? 1.f : g.slope;
-                            g.C[m * g.ldc + n + e] = y;
-                        }
-                    }
-                }
-                __syncwarp();
-            }
-            if (my_last < half) {                     // this warp owns no chunk of the tile (BN <= 32): still release
-                tc::fence_before_sync();
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(&accEmpty[ab]);
-            }
-        }
-    }
-    tc::fence_before_sync();
-    __syncthreads();
-    if (warp == 8) {
-        tc::fence_after_sync();
-        tc::tmem_dealloc(tmem_base, 512u);
-    }
-}
 
 // ---------------------------------------------------------------------------------------------------------------
 // NT on CTA PAIRS (cta_group::2).  The two CTAs of a cluster sit on the two SMs of one TPC and compute one 256 x BN tile:
@@ -675,7 +297,7 @@ constexpr int IMG2_SMEM = NS2 * A_STAGE + NS2 * B2_STAGE + kEpiWarps * SLAB_BYTE
 }  // namespace
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
-    gemm_nt_img2_kernel(GemmNT g, int BN, int n_tiles_n, int n_ptiles_total) {
+    gemm_nt_img2_kernel(GemmNT g, int BN, int n_tiles_n) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     char* smA = smem;
@@ -689,6 +311,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
     const uint32_t rank = tc::cluster_ctarank();
     const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
     const int nk = (g.Kd + TBK - 1) / TBK;
+    // rows of A / C: a host value, or read from device memory (g.Mdev: the valid-pair / valid-sample count of the batch, which
+    // the host never learns - g.M is then only the capacity the launch was sized for)
+    if (g.Mdev) { const int64_t md = (int64_t)__ldg(g.Mdev); g.M = md < g.M ? md : g.M; }
+    const int n_ptiles_total = (int)((g.M + 2 * TBM - 1) / (2 * TBM)) * n_tiles_n;
     const uint32_t b_half = (uint32_t)(BN * 64);          // bytes of (BN / 2 rows x 128 B): one of hi | lo in this CTA
     const uint32_t b_block = (uint32_t)(2 * BN * 128);    // image block of one (n tile, K chunk)
     const int my_tiles = n_ptiles_total > pair ? (n_ptiles_total - pair + n_pairs - 1) / n_pairs : 0;
@@ -956,52 +582,21 @@ static int pick_bn(int N, int* n_tiles) {
 }
 static int tmem_cols_for(int bn) { return bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256; }
 
-static int g_gemm_dbg = 0;   // bench-only ablation switches of the NT image kernel (pn_debug_gemm_flags)
-static int g_tn_pairs = 1;   // TN GEMMs with two n tiles run on CTA pairs; debug flag bit 9 selects the single-CTA kernel
-static bool nk_rows_ok(int64_t rps) { return rps % 32 == 0; }
-static int g_nt_pairs = 1;   // NT GEMMs run on CTA pairs (cta_group::2); debug flag bit 8 selects the single-CTA kernel instead
-void set_gemm_debug_flags(int f) { g_gemm_dbg = f & 0xFF; g_nt_pairs = ((f >> 8) & 1) ^ 1; g_tn_pairs = ((f >> 9) & 1) ^ 1; }
-
-int gemm_nt_tc(const GemmNT& g, cudaStream_t st) {
-    PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0 && g.ldb % 4 == 0, "gemm_nt_tc: operands must be padded to 4 (Kd %d lda %lld ldb %lld)",
-                 g.Kd, (long long)g.lda, (long long)g.ldb);
-    PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_nt_tc: operands must be 16-byte aligned");
-    PN_CHECK_ARG(g.rowmap == nullptr, "gemm_nt_tc: rowmap unsupported");
+int gemm_nt(const GemmNT& g, cudaStream_t st) {
+    PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0, "gemm_nt: operands must be padded to 4 (Kd %d lda %lld)", g.Kd, (long long)g.lda);
+    PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && g.Bimg, "gemm_nt: A must be 16-byte aligned and B given as an operand image");
     if (g.M <= 0 || g.N <= 0) return PN_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
-        PN_CUDA(cudaFuncSetAttribute(gemm_nt_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NT_SMEM));
-        attr_set = true;
+    static bool attr_img2 = false;
+    if (!attr_img2) {
+        PN_CUDA(cudaFuncSetAttribute(gemm_nt_img2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG2_SMEM));
+        attr_img2 = true;
     }
     int n_tiles;
     int bn = pick_bn(g.N, &n_tiles);
-    dim3 grid((unsigned)cdiv(g.M, TBM), (unsigned)n_tiles);
-    if (g.Bimg) {
-        static bool attr_img = false;
-        if (!attr_img) {
-            PN_CUDA(cudaFuncSetAttribute(gemm_nt_img_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG_SMEM));
-            attr_img = true;
-        }
-        if (g_nt_pairs && g.M > TBM) {     // CTA pairs: 256-row tiles, one cluster of two CTAs per TPC
-            static bool attr_img2 = false;
-            if (!attr_img2) {
-                PN_CUDA(cudaFuncSetAttribute(gemm_nt_img2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG2_SMEM));
-                attr_img2 = true;
-            }
-            int ptotal = (int)(cdiv(g.M, 2 * TBM) * n_tiles);
-            int pairs = ptotal < kNumSMs / 2 ? ptotal : kNumSMs / 2;
-            gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles, ptotal);
-            PN_LAUNCH_CHECK("gemm_nt_img2");
-            return PN_OK;
-        }
-        int total = (int)(cdiv(g.M, TBM) * n_tiles);
-        int ctas = total < kNumSMs ? total : kNumSMs;
-        gemm_nt_img_kernel<<<ctas, kThreadsImg, IMG_SMEM, st>>>(g, bn, n_tiles, total, g_gemm_dbg);
-        PN_LAUNCH_CHECK("gemm_nt_img");
-        return PN_OK;
-    }
-    gemm_nt_tc_kernel<<<grid, kThreads, NT_SMEM, st>>>(g, bn, tmem_cols_for(bn));
-    PN_LAUNCH_CHECK("gemm_nt_tc");
+    int64_t ptotal = cdiv(g.M, 2 * TBM) * n_tiles;        // g.M: the row count, or its capacity when g.Mdev is given
+    int pairs = ptotal < kNumSMs / 2 ? (int)ptotal : kNumSMs / 2;
+    gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles);
+    PN_LAUNCH_CHECK("gemm_nt_img2");
     return PN_OK;
 }
 
@@ -1074,7 +669,7 @@ int pack_nt_images(const PackJob* jobs, int n, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int TNP_STAGES = 3;
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTnThreads, 1)
-    gemm_tn_pair_kernel(GemmTN g, int BKt2, int64_t rows_per_split, float* __restrict__ partial, float* __restrict__ cpartial) {
+    gemm_tn_pair_kernel(GemmTN g, int BKt2, float* __restrict__ partial, float* __restrict__ cpartial) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     constexpr int PANEL = TBK * 128;
@@ -1090,9 +685,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTnThreads, 1)
     const uint32_t rank = tc::cluster_ctarank();
     const int split = (int)blockIdx.x >> 1;
     const int i0 = (int)rank * TBM;        // first column of A (n of the weight) of this CTA
+    g.M = tn_rows(g);
+    const int64_t rows_per_split = tn_rows_per_split(g.M, (int)gridDim.x >> 1);
     const int64_t r_begin = (int64_t)split * rows_per_split;
     const int64_t r_end = r_begin + rows_per_split < g.M ? r_begin + rows_per_split : g.M;
     const int nk = r_end > r_begin ? (int)((r_end - r_begin + TBK - 1) / TBK) : 0;
+    if (nk == 0 && split > 0) return;           // an empty split slot: both CTAs of the pair leave (same M, same decision)
 
     if (t == 0) {
         for (int i = 0; i < TNP_STAGES; ++i) { tc::mbar_init(&full[i], kTnLoad / 64); tc::mbar_init(&empty[i], 1); tc::mbar_init(&peerFull[i], 1); }
@@ -1244,31 +842,66 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTnThreads, 1)
     }
 }
 
-// second stage of the TN reduction (kernels in gemm.cu)
-int tn_finish(const GemmTN& g, const float* partial, const float* cpartial, int splits, cudaStream_t st);
-// one CTA per SM: k tiles x n tiles x splits <= 148, each split a contiguous slice of the reduction rows
-static void tn_plan(int64_t M, int N, int Kb, int* bkt, int* k_tiles, int* n_tiles, int* splits, int64_t* rps) {
+// ---- second stage of the TN reductions: partials are combined in split order (deterministic).  All weight-gradient GEMMs
+// of a backward pass are finished by ONE launch (blockIdx.y = job): a launch per GEMM cost ~12 us each for microseconds of work.
+struct TnFinishBatch { TnFinish j[kMaxTnJobs]; };
+__global__ void __launch_bounds__(256) tn_finish_batch_kernel(TnFinishBatch b) {
+    const TnFinish& f = b.j[blockIdx.y];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t M = f.M;
+    if (f.Mdev) { const int64_t md = (int64_t)__ldg(f.Mdev); M = md < M ? md : M; }
+    const int64_t rps = tn_rows_per_split(M, f.slots);
+    const int splits = M > 0 ? (int)((M + rps - 1) / rps) : 0;
+    if (idx < f.N * f.Kb) {
+        const int n = idx / f.Kb, k = idx - n * f.Kb;
+        if (k >= f.Kout) return;
+        float acc = 0.f;
+        for (int z = 0; z < splits; ++z) acc += f.partial[(int64_t)z * f.N * f.Kb + idx];
+        f.C[(int64_t)n * f.ldc + k] = acc;
+    } else if (f.colsum && idx - f.N * f.Kb < f.N) {
+        const int n = idx - f.N * f.Kb;
+        float acc = 0.f;
+        for (int z = 0; z < splits; ++z) acc += f.cpartial[(int64_t)z * f.N + n];
+        f.colsum[n] = acc;
+    }
+}
+int tn_finish_batch(const TnFinish* jobs, int n, cudaStream_t st) {
+    PN_CHECK_ARG(n >= 0 && n <= kMaxTnJobs, "tn_finish_batch: at most %d jobs", kMaxTnJobs);
+    if (n == 0) return PN_OK;
+    TnFinishBatch b;
+    int64_t mx = 0;
+    for (int i = 0; i < n; ++i) {
+        b.j[i] = jobs[i];
+        int64_t e = (int64_t)jobs[i].N * jobs[i].Kb + (jobs[i].colsum ? jobs[i].N : 0);
+        if (e > mx) mx = e;
+    }
+    for (int i = n; i < kMaxTnJobs; ++i) b.j[i] = jobs[0];
+    tn_finish_batch_kernel<<<dim3((unsigned)cdiv(mx, 256), (unsigned)n), 256, 0, st>>>(b);
+    PN_LAUNCH_CHECK("tn_finish_batch");
+    return PN_OK;
+}
+
+// one CTA per SM: k tiles x n tiles x split slots <= 148; the slices themselves are cut on the device (tn_rows_per_split)
+static void tn_plan(int64_t Mcap, int N, int Kb, int* bkt, int* k_tiles, int* n_tiles, int* slots) {
     if (Kb <= 288) { *bkt = (int)align_up(Kb, 16); *k_tiles = 1; }
     else *bkt = pick_bn(Kb, k_tiles);
     *n_tiles = (int)cdiv(N, TBM);
     int s = kNumSMs / (*k_tiles * *n_tiles);
     if (s < 1) s = 1;
-    int64_t r = align_up(cdiv(M > 0 ? M : 1, s), TBK);
-    if (r < 256) r = 256;
-    *rps = r;
-    *splits = (int)cdiv(M > 0 ? M : 1, r);
+    int64_t most = cdiv(Mcap > 0 ? Mcap : 1, 256);      // a slice holds at least 256 rows
+    *slots = (int)(most < s ? most : s);
 }
 
-int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
-    PN_CHECK_ARG(g.lda % 4 == 0 && g.ldb % 4 == 0 && g.N % 4 == 0 && g.Kb % 4 == 0, "gemm_tn_tc: operands must be padded");
-    PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_tn_tc: operands must be 16-byte aligned");
-    int bkt, k_tiles, n_tiles, splits;
-    int64_t rps;
-    tn_plan(g.M, g.N, g.Kb, &bkt, &k_tiles, &n_tiles, &splits, &rps);
+int gemm_tn(const GemmTN& g, float* scratch, TnFinish* fin, cudaStream_t st) {
+    PN_CHECK_ARG(g.lda % 4 == 0 && g.ldb % 4 == 0 && g.N % 4 == 0 && g.Kb % 4 == 0, "gemm_tn: operands must be padded");
+    PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && ((uintptr_t)g.B & 15) == 0, "gemm_tn: operands must be 16-byte aligned");
+    int bkt, k_tiles, n_tiles, slots;
+    tn_plan(g.M, g.N, g.Kb, &bkt, &k_tiles, &n_tiles, &slots);
     float* partial = scratch;
-    float* cpartial = scratch + (int64_t)splits * g.N * g.Kb;
+    float* cpartial = g.colsum ? scratch + (int64_t)slots * g.N * g.Kb : nullptr;
+    TnFinish f{partial, cpartial, slots, g.N, g.Kb, g.Kout, g.C, g.ldc, g.colsum, g.M, g.Mdev};
     const int bkt2 = (int)align_up(g.Kb, 64);
-    if (g_tn_pairs && n_tiles == 2 && k_tiles == 1 && bkt2 <= 320 && nk_rows_ok(rps)) {   // CTA pairs: the two n tiles of a split
+    if (n_tiles == 2 && k_tiles == 1 && bkt2 <= 320) {   // CTA pairs: the two n tiles of a split
         const int n2 = bkt2 > 256 ? bkt2 - 256 : 0, n1 = bkt2 - n2;
         const int np2 = (n1 >> 6) + (n2 >> 6);
         const int stages_b = TNP_STAGES * (2 * A_BYTES + 2 * np2 * TBK * 128), tile_b = TBM * (bkt2 + 4) * 4;
@@ -1278,28 +911,27 @@ int gemm_tn_tc(const GemmTN& g, float* scratch, cudaStream_t st) {
             PN_CUDA(cudaFuncSetAttribute(gemm_tn_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
             attr2 = smem2;
         }
-        gemm_tn_pair_kernel<<<2 * splits, kTnThreads, smem2, st>>>(g, bkt2, rps, partial, g.colsum ? cpartial : nullptr);
+        gemm_tn_pair_kernel<<<2 * slots, kTnThreads, smem2, st>>>(g, bkt2, partial, cpartial);
         PN_LAUNCH_CHECK("gemm_tn_pair");
-        return tn_finish(g, partial, g.colsum ? cpartial : nullptr, splits, st);
+    } else {
+        const int npan = (bkt + 31) / 32;
+        const int smem_bytes = 2 * (2 * A_BYTES + 2 * npan * TBK * 128) + 1024 + 256;
+        static int attr_bytes = 0;
+        if (smem_bytes > attr_bytes) {
+            PN_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+            attr_bytes = smem_bytes;
+        }
+        dim3 grid((unsigned)k_tiles, (unsigned)n_tiles, (unsigned)slots);
+        gemm_tn_tc_kernel<<<grid, kTnThreads, smem_bytes, st>>>(g, bkt, bkt > 256 ? 512 : tmem_cols_for(bkt), partial, cpartial);
+        PN_LAUNCH_CHECK("gemm_tn_tc");
     }
-    const int npan = (bkt + 31) / 32;
-    const int smem_bytes = 2 * (2 * A_BYTES + 2 * npan * TBK * 128) + 1024 + 256;
-    static int attr_bytes = 0;
-    if (smem_bytes > attr_bytes) {
-        PN_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        attr_bytes = smem_bytes;
-    }
-    dim3 grid((unsigned)k_tiles, (unsigned)n_tiles, (unsigned)splits);
-    gemm_tn_tc_kernel<<<grid, kTnThreads, smem_bytes, st>>>(g, bkt, bkt > 256 ? 512 : tmem_cols_for(bkt), rps, partial,
-                                                         g.colsum ? cpartial : nullptr, g_gemm_dbg);
-    PN_LAUNCH_CHECK("gemm_tn_tc");
-    return tn_finish(g, partial, g.colsum ? cpartial : nullptr, splits, st);
+    if (fin) { *fin = f; return PN_OK; }
+    return tn_finish_batch(&f, 1, st);
 }
-int64_t gemm_tn_tc_scratch_floats(int64_t M, int N, int Kb) {
-    int bkt, k_tiles, n_tiles, splits;
-    int64_t rps;
-    tn_plan(M, N, Kb, &bkt, &k_tiles, &n_tiles, &splits, &rps);
-    return (int64_t)splits * ((int64_t)N * Kb + N) + 64;
+int64_t gemm_tn_scratch_floats(int64_t Mcap, int N, int Kb) {
+    int bkt, k_tiles, n_tiles, slots;
+    tn_plan(Mcap, N, Kb, &bkt, &k_tiles, &n_tiles, &slots);
+    return align_up((int64_t)slots * ((int64_t)N * Kb + N) + 64, 64);
 }
 
 }  // namespace pn

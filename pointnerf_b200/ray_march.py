@@ -45,7 +45,7 @@ def _check_funcs(render_func, blend_func):
 
 class _Composite(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, ray_features, ray_dist, ray_valid_u8, bg_color, want_color, slot_row=None):
+    def forward(ctx, ray_features, ray_dist, ray_valid_u8, bg_color, want_color, slot_row=None, n_rows_dev=None):
         lib = _lib.lib()
         R, SR = (int(v) for v in ray_dist.shape)       # ray_features: [R,SR,C+1], or [S,C+1] with slot_row (compact)
         C1 = int(ray_features.shape[-1])
@@ -68,7 +68,7 @@ class _Composite(torch.autograd.Function):
                                                 _lib.ptr(bg_T), _lib.stream()), "pn_composite_forward")
         ctx.set_materialize_grads(False)    # unused outputs arrive as None (NULL for the kernel), not as zero tensors to fill and read
         ctx.save_for_backward(feats, dist, ray_valid_u8, bg if bg is not None else torch.empty(0, device=dev), opacity, acc_T, bg_T)
-        ctx.has_bg, ctx.want_color, ctx.slot_row = bg is not None, want_color, slot_row
+        ctx.has_bg, ctx.want_color, ctx.slot_row, ctx.n_rows_dev = bg is not None, want_color, slot_row, n_rows_dev
         ctx.bg_shape = tuple(bg_color.shape) if bg_color is not None else None
         if ray_color is None:
             ray_color = torch.empty(0, device=dev)
@@ -91,7 +91,7 @@ class _Composite(torch.autograd.Function):
         need_bg = ctx.has_bg and ctx.needs_input_grad[3]
         g_bg = torch.empty((C,), dtype=torch.float32, device=dev) if need_bg else None
         if R == 0:
-            return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None, None
+            return g_feat, None, None, (torch.zeros(ctx.bg_shape, device=dev) if need_bg else None), None, None, None
         n_rows = int(feats.shape[0]) if ctx.slot_row is not None else 0
         ws_bytes = lib.pn_composite_workspace_bytes(R, C, n_rows)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -101,9 +101,9 @@ class _Composite(torch.autograd.Function):
                                              _lib.ptr(bg) if ctx.has_bg else None,
                                              _lib.ptr(opacity), _lib.ptr(acc_T), _lib.ptr(bg_T), _lib.ptr(g_color),
                                              _lib.ptr(c(g_opacity)), _lib.ptr(c(g_acc_T)), _lib.ptr(c(g_blend_w)),
-                                             _lib.ptr(c(g_bg_T)), R, SR, C, n_rows, _lib.ptr(g_k), _lib.ptr(g_bg), _lib.ptr(ws),
-                                             ws_bytes, _lib.stream()), "pn_composite_backward")
-        return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None, None
+                                             _lib.ptr(c(g_bg_T)), R, SR, C, n_rows, _lib.ptr(ctx.n_rows_dev), _lib.ptr(g_k), _lib.ptr(g_bg),
+                                             _lib.ptr(ws), ws_bytes, _lib.stream()), "pn_composite_backward")
+        return g_feat, None, None, (g_bg.view(ctx.bg_shape) if need_bg else None), None, None, None
 
 
 def _as_u8(mask):
@@ -112,15 +112,17 @@ def _as_u8(mask):
     return mask.view(torch.uint8) if mask.dtype in (torch.bool, torch.int8) else mask.to(torch.uint8)
 
 
-def ray_march_compact(ray_dist, ray_valid, features_compact, slot_row, bg_color=None):
+def ray_march_compact(ray_dist, ray_valid, features_compact, slot_row, bg_color=None, n_rows_dev=None):
     """Fused-path variant of ``ray_march``: ``features_compact`` [S,C+1] holds one row per valid sample and
-    ``slot_row`` int32 [R,SR] maps sample (r,s) to its row (-1: none).  Same 7-tuple minus ``point_color`` (None)."""
+    ``slot_row`` int32 [R,SR] maps sample (r,s) to its row (-1: none).  Same 7-tuple minus ``point_color`` (None).
+    ``n_rows_dev`` (device int32[1]): the number of valid rows when the host never learned it (``features_compact`` is then
+    allocated at capacity)."""
     B, R, SR = ray_dist.shape
     if B != 1:
         raise NotImplementedError("B = 1 only, like every caller of the reference")
     valid = _as_u8(ray_valid.reshape(R, SR))
     ray_color, opacity, acc_T, blend_w, bg_T = _Composite.apply(features_compact, ray_dist.reshape(R, SR), valid, bg_color, True,
-                                                                slot_row.reshape(R, SR).contiguous())
+                                                                slot_row.reshape(R, SR).contiguous(), n_rows_dev)
     bg_T = bg_T.view(B, R, 1)
     return (ray_color.view(B, R, features_compact.shape[-1] - 1), None, opacity.view(B, R, SR), acc_T.view(B, R, SR),
             blend_w.view(B, R, SR, 1), bg_T, bg_T)      # background_blend_weight = 1 * T: the same values
@@ -175,7 +177,7 @@ def ray_dist_from_samples(sample_loc, ray_valid, vsize, raydist_mode_unit=1):
 
 class _ColorMSE(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, pred, target, ray_weight, inv_norm):
+    def forward(ctx, pred, target, ray_weight, inv_norm, ray_mask=None, inv_norm_dev=None):
         lib = _lib.lib()
         C = int(pred.shape[-1])
         p = pred.detach().reshape(-1, C).contiguous().float()
@@ -189,23 +191,29 @@ class _ColorMSE(torch.autograd.Function):
         grad = torch.empty_like(p) if ctx.needs_input_grad[0] else None
         ws_bytes = lib.pn_color_mse_workspace_bytes()
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=p.device)
-        _lib.check(lib.pn_color_mse(_lib.ptr(p), _lib.ptr(t), _lib.ptr(w), int(p.shape[0]), C, float(inv_norm), _lib.ptr(loss),
-                                    _lib.ptr(grad), _lib.ptr(ws), ws_bytes, _lib.stream()), "pn_color_mse")
+        mk = ray_mask.detach().reshape(-1).contiguous() if ray_mask is not None else None
+        if mk is not None and (mk.dtype != torch.int32 or mk.numel() != p.shape[0]):
+            raise ValueError("color_mse: ray_mask must be int32 with one entry per ray")
+        _lib.check(lib.pn_color_mse(_lib.ptr(p), _lib.ptr(t), _lib.ptr(w), _lib.ptr(mk), int(p.shape[0]), C, float(inv_norm),
+                                    _lib.ptr(inv_norm_dev), _lib.ptr(loss), _lib.ptr(grad), _lib.ptr(ws), ws_bytes, _lib.stream()),
+                   "pn_color_mse")
         ctx.grad, ctx.shape = grad, tuple(pred.shape)
         return loss
 
     @staticmethod
     def backward(ctx, g):
         grad, ctx.grad = ctx.grad, None
-        return (grad * g).view(ctx.shape), None, None, None
+        return (grad * g).view(ctx.shape), None, None, None, None, None
 
 
-def color_mse(pred, target, ray_weight=None, norm=None):
+def color_mse(pred, target, ray_weight=None, norm=None, ray_mask=None, inv_norm_dev=None):
     """Colour loss of ``compute_losses`` (base_rendering_model.py:543-550: ``torch.nn.MSELoss`` of ``coarse_raycolor`` against
     ``gt_image``) with its gradient produced in the same pass.  pred, target [..., C]; ray_weight [...] or None (the
     ``ray_masked_*`` items: a {0,1} mask, ``norm`` = number of selected elements); norm: the divisor (default: pred.numel()).
+    ``ray_mask`` int32 [...]: rays with mask <= 0 get weight 0 (the query's per-ray neighbour flag, no float conversion);
+    ``inv_norm_dev`` (device float[1]): an extra factor of the normaliser that stays on the device (1 / masked count).
     Returns the 0-d loss; deterministic (fixed reduction tree)."""
     if not pred.is_cuda:
         raise _lib.LibraryError("color_mse needs CUDA tensors (there is no CPU path in this package)")
     n = float(norm) if norm is not None else float(max(pred.numel(), 1))
-    return _ColorMSE.apply(pred, target, ray_weight, 1.0 / n)
+    return _ColorMSE.apply(pred, target, ray_weight, 1.0 / n, ray_mask, inv_norm_dev)
