@@ -208,6 +208,16 @@ int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, int32_t K, i
                        int32_t* pair_start, int32_t* pair_src, int32_t* counts, int32_t* slot_row, void* workspace,
                        int64_t workspace_bytes, void* stream);
 
+/* pn_compact_samples under CAPACITIES, for callers that keep the counts on the device (pn_agg_inputs.counts): buffers and
+ * launches downstream are sized by S_cap samples / M_cap pairs instead of the read-back counts.  The lists keep the longest
+ * prefix of valid samples (slot order) that fits both capacities; later samples are dropped whole (slot_row = -1: they
+ * composite as empty space).  sample_list int32[min(n_slots, S_cap)], pair_start int32[min(n_slots, S_cap) + 1], pair_src
+ * int32[min(n_slots * K, M_cap)]; counts4 int32[4] = {S kept, M kept, S total, M total}: kept < total means the batch
+ * overflowed the capacities (the host checks it after the fact, e.g. from an asynchronous copy, and grows them). */
+int pn_compact_samples_capped(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int64_t S_cap, int64_t M_cap,
+                              int32_t* sample_list, int32_t* pair_start, int32_t* pair_src, int32_t* counts4,
+                              int32_t* slot_row, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* pn_compact_samples for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
  * forbid cudaMalloc).  No counterpart in the reference.  Same inputs, outputs and
  * results as pn_compact_samples, but the workspace is a file-scope `static __device__` array inside the library (8.4 MB,

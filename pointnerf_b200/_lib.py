@@ -102,6 +102,7 @@ def _declare(lib):
         "pn_w2pers": (c_int, [P, c_int64, P, P, P, P]),
         "pn_compact_workspace_bytes": (c_int64, [c_int64]),
         "pn_compact_samples": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P, c_int64, P]),
+        "pn_compact_samples_capped": (c_int, [P, c_int64, c_int32, c_int64, c_int64, P, P, P, P, P, P, c_int64, P]),
         "pn_compact_samples_static_max_slots": (c_int64, []),
         "pn_compact_samples_static": (c_int, [P, c_int64, c_int32, P, P, P, P, P, P]),
         "pn_agg_saved_bytes": (c_int64, [POINTER(AggParams), c_int64, c_int64]),

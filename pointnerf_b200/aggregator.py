@@ -120,26 +120,42 @@ def _inputs_struct(call, embedding, color, pdir, conf):
 class CompactSamples:
     """Work lists of valid samples / pairs (pn_compact_samples).  The kernels and the device->host copy of the two counts
     are queued at construction; ``counts()`` waits for that copy only - a caller that builds the lists early (the next
-    batch's sampling, queued before this batch's backward) never stalls the GPU on the read-back."""
+    batch's sampling, queued before this batch's backward) never stalls the GPU on the read-back.
 
-    def __init__(self, sample_pidx, n_slots, K):
+    ``caps=(S_cap, M_cap)``: capacity mode (pn_compact_samples_capped) - nothing is copied to the host, ``counts_dev``
+    (int32[4]: S kept, M kept, S total, M total) stays on the device, ``counts()`` returns the capacities."""
+
+    def __init__(self, sample_pidx, n_slots, K, caps=None):
         lib = _lib.lib()
         dev = sample_pidx.device
         self.n_slots = n_slots
         self._sm = None
+        self.counts_dev = None
         if n_slots == 0:
             z = torch.zeros(1, dtype=torch.int32, device=dev)
             self.sample_list, self.pair_start, self.pair_src = z, z.clone(), z.clone()
             self.slot_row = torch.zeros(0, dtype=torch.int32, device=dev)
             self._sm = (0, 0)
             return
+        ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        self.slot_row = torch.empty(n_slots, dtype=torch.int32, device=dev)
+        if caps is not None:
+            S_cap, M_cap = min(int(caps[0]), n_slots), min(int(caps[1]), n_slots * K)
+            self.sample_list = torch.empty(S_cap, dtype=torch.int32, device=dev)
+            self.pair_start = torch.empty(S_cap + 1, dtype=torch.int32, device=dev)
+            self.pair_src = torch.empty(M_cap, dtype=torch.int32, device=dev)
+            self.counts_dev = torch.empty(4, dtype=torch.int32, device=dev)
+            _lib.check(lib.pn_compact_samples_capped(_lib.ptr(sample_pidx), n_slots, K, S_cap, M_cap, _lib.ptr(self.sample_list),
+                                                     _lib.ptr(self.pair_start), _lib.ptr(self.pair_src), _lib.ptr(self.counts_dev),
+                                                     _lib.ptr(self.slot_row), _lib.ptr(ws), ws_bytes, _lib.stream()),
+                       "pn_compact_samples_capped")
+            self._sm = (S_cap, M_cap)
+            return
         self.sample_list = torch.empty(max(n_slots, 1), dtype=torch.int32, device=dev)
         self.pair_start = torch.empty(n_slots + 1, dtype=torch.int32, device=dev)
         self.pair_src = torch.empty(max(n_slots * K, 1), dtype=torch.int32, device=dev)
-        self.slot_row = torch.empty(n_slots, dtype=torch.int32, device=dev)
         counts = torch.empty(2, dtype=torch.int32, device=dev)
-        ws_bytes = lib.pn_compact_workspace_bytes(n_slots)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         _lib.check(lib.pn_compact_samples(_lib.ptr(sample_pidx), n_slots, K, _lib.ptr(self.sample_list), _lib.ptr(self.pair_start),
                                           _lib.ptr(self.pair_src), _lib.ptr(counts), _lib.ptr(self.slot_row), _lib.ptr(ws), ws_bytes,
                                           _lib.stream()), "pn_compact_samples")
@@ -149,7 +165,8 @@ class CompactSamples:
         self._event.record()
 
     def counts(self):
-        """(S, M): valid samples and valid (sample, neighbour) pairs - the one host read-back of the aggregator."""
+        """(S, M): valid samples and valid (sample, neighbour) pairs - the one host read-back of the aggregator (capacity
+        mode: the capacities, no read-back)."""
         if self._sm is None:
             self._event.synchronize()
             self._sm = (int(self._host[0]), int(self._host[1]))
@@ -167,85 +184,106 @@ def _shaped(grads, shapes):
     return tuple(None if g is None else g.view(sh) for g, sh in zip(grads, shapes))
 
 
+def agg_forward_raw(call, embedding, color, pdir, conf, weights):
+    """pn_agg_forward on already detached, contiguous tensors.  ``call.S`` / ``call.M`` are the exact counts, or - with
+    ``call.counts_dev`` set - the capacities every buffer is sized by.  Returns (decoded, weight_out | None, saved, saved_bytes)."""
+    lib = _lib.lib()
+    p = call.params
+    dev = embedding.device
+    decoded = torch.empty((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
+    weight_out = torch.empty((call.n_slots, p.K), dtype=torch.float32, device=dev) if call.want_weight else None
+    saved_bytes = lib.pn_agg_saved_bytes(ctypes.byref(p), call.S, call.M)
+    ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 0)
+    if saved_bytes < 0 or ws_bytes < 0:
+        raise _lib.LibraryError("pn_agg_*_bytes: " + lib.pn_last_error().decode())
+    saved = torch.empty(max(saved_bytes, 1), dtype=torch.uint8, device=dev)
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
+    ain = _inputs_struct(call, embedding, color, pdir, conf)
+    wst = _weights_struct(weights)
+    if call.n_slots > 0:
+        _lib.check(lib.pn_agg_forward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(decoded),
+                                      _lib.ptr(weight_out), _lib.ptr(saved), saved_bytes, _lib.ptr(ws), ws_bytes,
+                                      _lib.stream()), "pn_agg_forward")
+        if call.export_signs:
+            if call.counts_dev is not None:
+                raise _lib.LibraryError("export_signs needs the counts on the host")
+            ps = torch.empty((4, call.M, p.W), dtype=torch.uint8, device=dev)
+            ss = torch.empty((3, call.S, p.C), dtype=torch.uint8, device=dev)
+            _lib.check(lib.pn_agg_activation_signs(ctypes.byref(p), _lib.ptr(saved), saved_bytes, call.S, call.M, call.S, call.M,
+                                                   _lib.ptr(ps), _lib.ptr(ss), _lib.stream()), "pn_agg_activation_signs")
+            call.signs = (ps, ss)
+    return decoded, weight_out, saved, saved_bytes
+
+
+def agg_backward_raw(call, tables, weights, saved, saved_bytes, g_decoded, need=(True, True, True, True)):
+    """pn_agg_backward.  Returns (g_emb, g_col, g_dir, g_cnf, g_w): per-row gradients ([T,*] with scatter_rows, else
+    [n_slots*K,*]; None where ``need`` is False) and the MLP gradients as views of ONE flat buffer (``call.grad_flat``)."""
+    lib = _lib.lib()
+    p = call.params
+    embedding, color, pdir, conf = tables
+    dev = embedding.device
+    rows = call.T if call.scatter_rows else call.n_slots * p.K
+    g_emb = torch.empty((rows, p.F), dtype=torch.float32, device=dev) if need[0] else None
+    g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[1] else None
+    g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
+    g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[3] else None
+    # all MLP gradients live in ONE flat buffer (256-byte aligned segments): ray_shard all-reduces it in place
+    sizes = [(w.numel() + 63) // 64 * 64 for w in weights]
+    call.flat_tail_off = sum(sizes)       # + a caller-owned tail (ray_shard: bg gradient and row counts ride the same all-reduce)
+    call.grad_flat = torch.zeros(call.flat_tail_off + int(call.flat_tail), dtype=torch.float32, device=dev)
+    g_w = tuple(seg[:w.numel()].view(w.shape) for seg, w in zip(call.grad_flat.split(sizes + [int(call.flat_tail)]), weights))
+    if call.n_slots == 0:
+        for t in (g_emb, g_col, g_dir, g_cnf):
+            if t is not None:
+                t.zero_()
+        return g_emb, g_col, g_dir, g_cnf, g_w
+    ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 1)
+    ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
+    ain = _inputs_struct(call, embedding, color, pdir, conf)
+    wst, gst = _weights_struct(weights), _weights_struct(g_w)
+    if call.collect_touched and call.scatter_rows:
+        call.touched_ids = torch.empty(max(call.M, 1), dtype=torch.int32, device=dev)
+        call.n_touched = torch.empty(1, dtype=torch.int32, device=dev)
+    _lib.check(lib.pn_agg_backward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(g_decoded),
+                                   _lib.ptr(saved), saved_bytes, ctypes.byref(gst), 1 if call.scatter_rows else 0,
+                                   _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf),
+                                   _lib.ptr(call.touched_ids), _lib.ptr(call.n_touched), _lib.ptr(ws),
+                                   ws_bytes, _lib.stream()), "pn_agg_backward")
+    return g_emb, g_col, g_dir, g_cnf, g_w
+
+
 class _AggFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, call, embedding, color, pdir, conf, *weights):
-        lib = _lib.lib()
         p = call.params
-        dev = embedding.device
-        K = p.K
-        cs = call.compact if call.compact is not None else CompactSamples(call.sample_pidx, call.n_slots, K)
+        cs = call.compact if call.compact is not None else CompactSamples(call.sample_pidx, call.n_slots, p.K)
         call.S, call.M = cs.counts()
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
-        decoded = torch.empty((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
-        weight_out = torch.empty((call.n_slots, K), dtype=torch.float32, device=dev) if call.want_weight else None
-        saved_bytes = lib.pn_agg_saved_bytes(ctypes.byref(p), call.S, call.M)
-        ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 0)
-        if saved_bytes < 0 or ws_bytes < 0:
-            raise _lib.LibraryError("pn_agg_*_bytes: " + lib.pn_last_error().decode())
-        saved = torch.empty(max(saved_bytes, 1), dtype=torch.uint8, device=dev)
-        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
         weights = tuple(w.detach().contiguous() for w in weights)
         ctx.table_shapes = tuple(t.shape for t in (embedding, color, pdir, conf))
         embedding, color, pdir, conf = (t.detach().contiguous() for t in (embedding, color, pdir, conf))
-        ain = _inputs_struct(call, embedding, color, pdir, conf)
-        wst = _weights_struct(weights)
-        if call.n_slots > 0:
-            _lib.check(lib.pn_agg_forward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(decoded),
-                                          _lib.ptr(weight_out), _lib.ptr(saved), saved_bytes, _lib.ptr(ws), ws_bytes,
-                                          _lib.stream()), "pn_agg_forward")
-            if call.export_signs:
-                ps = torch.empty((4, call.M, p.W), dtype=torch.uint8, device=dev)
-                ss = torch.empty((3, call.S, p.C), dtype=torch.uint8, device=dev)
-                _lib.check(lib.pn_agg_activation_signs(ctypes.byref(p), _lib.ptr(saved), saved_bytes, call.S, call.M, call.S, call.M,
-                                                       _lib.ptr(ps), _lib.ptr(ss), _lib.stream()), "pn_agg_activation_signs")
-                call.signs = (ps, ss)
+        decoded, weight_out, saved, saved_bytes = agg_forward_raw(call, embedding, color, pdir, conf, weights)
         ctx.call, ctx.saved, ctx.saved_bytes = call, saved, saved_bytes
         ctx.tables = (embedding, color, pdir, conf)
         ctx.weights = weights
         if weight_out is None:
-            weight_out = torch.empty(0, device=dev)
+            weight_out = torch.empty(0, device=embedding.device)
         ctx.mark_non_differentiable(weight_out)
         ctx.set_materialize_grads(False)      # no zero tensor for the non-differentiable weight output
         return decoded, weight_out
 
     @staticmethod
     def backward(ctx, g_decoded, _g_weight):
-        lib = _lib.lib()
         call, p = ctx.call, ctx.call.params
-        embedding, color, pdir, conf = ctx.tables
-        dev = embedding.device
+        dev = ctx.tables[0].device
         if g_decoded is None:
             g_decoded = torch.zeros((call.S if p.compact_out else call.n_slots, p.C + 1), dtype=torch.float32, device=dev)
-        g_decoded = g_decoded.contiguous()
         need = ctx.needs_input_grad  # (call, embedding, color, dir, conf, *weights)
-        rows = call.T if call.scatter_rows else call.n_slots * p.K
-        g_emb = torch.empty((rows, p.F), dtype=torch.float32, device=dev) if need[1] else None
-        g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
-        g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[3] else None
-        g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[4] else None
-        # all MLP gradients live in ONE flat buffer (256-byte aligned segments): ray_shard all-reduces it in place
-        sizes = [(w.numel() + 63) // 64 * 64 for w in ctx.weights]
-        call.flat_tail_off = sum(sizes)       # + a caller-owned tail (ray_shard: bg gradient and row counts ride the same all-reduce)
-        call.grad_flat = torch.zeros(call.flat_tail_off + int(call.flat_tail), dtype=torch.float32, device=dev)
-        g_w = tuple(seg[:w.numel()].view(w.shape) for seg, w in zip(call.grad_flat.split(sizes + [int(call.flat_tail)]), ctx.weights))
-        ws_bytes = lib.pn_agg_workspace_bytes(ctypes.byref(p), call.S, call.M, call.T, 1)
-        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
-        ain = _inputs_struct(call, embedding, color, pdir, conf)
-        wst, gst = _weights_struct(ctx.weights), _weights_struct(g_w)
+        g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, ctx.tables, ctx.weights, ctx.saved, ctx.saved_bytes,
+                                                           g_decoded.contiguous(), need[1:5])
         if call.n_slots == 0:
-            for t in (g_emb, g_col, g_dir, g_cnf) + g_w:
-                if t is not None:
-                    t.zero_()
-            return (None,) + _shaped((g_emb, g_col, g_dir, g_cnf), ctx.table_shapes) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
-        if call.collect_touched and call.scatter_rows:
-            call.touched_ids = torch.empty(max(call.M, 1), dtype=torch.int32, device=dev)
-            call.n_touched = torch.empty(1, dtype=torch.int32, device=dev)
-        _lib.check(lib.pn_agg_backward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(g_decoded),
-                                       _lib.ptr(ctx.saved), ctx.saved_bytes, ctypes.byref(gst), 1 if call.scatter_rows else 0,
-                                       _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf),
-                                       _lib.ptr(call.touched_ids), _lib.ptr(call.n_touched), _lib.ptr(ws),
-                                       ws_bytes, _lib.stream()), "pn_agg_backward")
+            for t in g_w:
+                t.zero_()
         return (None,) + _shaped((g_emb, g_col, g_dir, g_cnf), ctx.table_shapes) + tuple(g if n else None for g, n in zip(g_w, need[5:]))
 
 

@@ -321,28 +321,45 @@ __global__ void __launch_bounds__(256) slot_scatter_kernel(const int* __restrict
                                                            const unsigned long long* __restrict__ total,
                                                            int* __restrict__ sample_list, int* __restrict__ pair_start,
                                                            int* __restrict__ pair_src, int* __restrict__ counts,
-                                                           int* __restrict__ slot_row) {
+                                                           int* __restrict__ slot_row, int64_t S_cap, int64_t M_cap, int capped) {
+    // Capacities (capped != 0): the lists keep the longest PREFIX of valid samples (in slot order) that fits S_cap samples
+    // and M_cap pairs; later samples are dropped whole (slot_row = -1), so every list the aggregator walks stays inside
+    // the buffers sized by the capacities.  counts = {S kept, M kept, S total, M total}: kept < total flags the overflow.
+    // (counts[0], counts[1] are zeroed by the host before the launch; offsets grow with the slot index, so the maxima
+    // below are the kept prefix's totals and the kept samples' own pair_start[si + 1] writes close the list.)
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s == 0) {
         unsigned long long t = *total;
-        counts[0] = (int)(t >> 32);
-        counts[1] = (int)(t & 0xffffffffu);
-        pair_start[t >> 32] = (int)(t & 0xffffffffu);
+        if (capped) {
+            counts[2] = (int)(t >> 32);
+            counts[3] = (int)(t & 0xffffffffu);
+            pair_start[0] = 0;
+        } else {
+            counts[0] = (int)(t >> 32);
+            counts[1] = (int)(t & 0xffffffffu);
+            pair_start[t >> 32] = (int)(t & 0xffffffffu);
+        }
     }
     if (s >= n_slots) return;
     unsigned long long o = offs[s];
     int si = (int)(o >> 32), pi = (int)(o & 0xffffffffu);
-    bool any = false;
-    for (int k = 0; k < K; ++k)
-        if (pidx[s * K + k] >= 0) {
-            pair_src[pi++] = (int)(s * K + k);
-            any = true;
-        }
-    if (any) {
+    int c = 0;
+    for (int k = 0; k < K; ++k) c += pidx[s * K + k] >= 0;
+    const bool any = c > 0;
+    const bool keep = any && (!capped || ((int64_t)si < S_cap && (int64_t)pi + c <= M_cap));
+    if (keep) {
+        const int p0 = pi;
+        for (int k = 0; k < K; ++k)
+            if (pidx[s * K + k] >= 0) pair_src[pi++] = (int)(s * K + k);
         sample_list[si] = (int)s;
-        pair_start[si] = (int)(o & 0xffffffffu);
+        pair_start[si] = p0;
+        if (capped) {
+            pair_start[si + 1] = pi;          // the next kept sample writes the same value; the last kept one closes the list
+            atomicMax(&counts[0], si + 1);
+            atomicMax(&counts[1], pi);
+        }
     }
-    if (slot_row) slot_row[s] = any ? si : -1;
+    if (slot_row) slot_row[s] = keep ? si : -1;
 }
 
 }  // namespace pn
@@ -512,7 +529,33 @@ extern "C" int pn_compact_samples(const int32_t* sample_pidx, int64_t n_slots, i
     int rc = scan_exclusive_u64(packed, offs, n_slots, total, scratch, st);
     if (rc) return rc;
     slot_scatter_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, offs, total, sample_list,
-                                                                      pair_start, pair_src, counts, slot_row);
+                                                                      pair_start, pair_src, counts, slot_row, 0, 0, 0);
+    PN_LAUNCH_CHECK("slot_scatter");
+    return PN_OK;
+}
+
+extern "C" int pn_compact_samples_capped(const int32_t* sample_pidx, int64_t n_slots, int32_t K, int64_t S_cap, int64_t M_cap,
+                                         int32_t* sample_list, int32_t* pair_start, int32_t* pair_src, int32_t* counts4,
+                                         int32_t* slot_row, void* workspace, int64_t workspace_bytes, void* stream) {
+    PN_CHECK_ARG(sample_pidx && sample_list && pair_start && pair_src && counts4, "pn_compact_samples_capped: null argument");
+    PN_CHECK_ARG(S_cap >= 1 && M_cap >= K, "pn_compact_samples_capped: capacities must hold at least one sample (S_cap >= 1, M_cap >= K)");
+    PN_CHECK_ARG(workspace_bytes >= pn_compact_workspace_bytes(n_slots), "pn_compact_samples_capped: workspace too small");
+    PN_CHECK_ARG(n_slots * (int64_t)K < 2147483647LL, "pn_compact_samples_capped: n_slots*K exceeds int32");
+    cudaStream_t st = (cudaStream_t)stream;
+    PN_CUDA(cudaMemsetAsync(counts4, 0, 4 * sizeof(int), st));
+    PN_CUDA(cudaMemsetAsync(pair_start, 0, sizeof(int), st));
+    if (n_slots <= 0) return PN_OK;
+    Carver ws(workspace, workspace_bytes);
+    unsigned long long* packed = ws.take<unsigned long long>(n_slots);
+    unsigned long long* offs = ws.take<unsigned long long>(n_slots);
+    unsigned long long* scratch = ws.take<unsigned long long>(scan_scratch_elems(n_slots));
+    unsigned long long* total = ws.take<unsigned long long>(1);
+    slot_count_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, packed);
+    PN_LAUNCH_CHECK("slot_count");
+    int rc = scan_exclusive_u64(packed, offs, n_slots, total, scratch, st);
+    if (rc) return rc;
+    slot_scatter_kernel<<<(unsigned)cdiv(n_slots, 256), 256, 0, st>>>(sample_pidx, n_slots, K, offs, total, sample_list,
+                                                                      pair_start, pair_src, counts4, slot_row, S_cap, M_cap, 1);
     PN_LAUNCH_CHECK("slot_scatter");
     return PN_OK;
 }

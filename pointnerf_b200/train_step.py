@@ -1,0 +1,315 @@
+"""The training step of the per-ray hot path as ONE replayable launch sequence (CUDA graphs), with no host read-back.
+
+``NeuralPointsRayMarching.forward`` + ``loss.backward()`` (neural_points_volumetric_model.py:272-352 under
+base_rendering_model.py:533-606 ``compute_losses`` / ``backward``) cost ~1.4 ms of host time per step when driven from
+Python (~60 kernel launches, ~30 tensor allocations, the autograd graph, one wait for the (S, M) counts) - as much as the
+kernels themselves take on a B200.  ``FusedTrainStep`` issues the same kernels in the same order through the same C-ABI
+entry points, but
+
+  * without autograd: the chain query -> gather + aggregator -> ray_dist -> ray_march -> colour loss and its backward is
+    fixed, so the backward entry points are called directly (``agg_backward_raw``, ``_Composite.backward``);
+  * without the host ever learning the number of valid samples / pairs: the work lists are built under CAPACITIES
+    (pn_compact_samples_capped), every kernel reads the true counts from device memory (pn_agg_inputs.counts), buffers are
+    sized by the capacities;
+  * captured once into two CUDA graphs - ``query`` (ray sampling, neighbour query, work lists, per-ray loss weights) and
+    ``step`` (forward, loss, backward) - and replayed: two graph launches per step instead of ~100 Python-level calls.
+    Between the two a multi-GPU run all-reduces the masked-ray count (4 bytes) that normalises ``ray_masked_*`` losses.
+
+Gradients land in static buffers that become the parameters' ``.grad`` (overwritten by the next step, the usual CUDA-graph
+training contract).  Capacities come from ``calibrate()`` (exact counts of sample batches + headroom); a batch that
+overflows them is truncated in slot order (later samples composite as empty space), flagged one step later through an
+asynchronous copy of the counts, and the capacities are grown for the following steps.
+"""
+import warnings
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from . import query as _query
+from .aggregator import CompactSamples, _AggCall, agg_backward_raw, agg_forward_raw
+from .ray_march import _ColorMSE, _Composite, _as_u8, ray_dist_from_samples
+
+
+class _Ctx:
+    """Stand-in for an autograd context: the Function bodies are called directly (no graph is recorded)."""
+
+    def __init__(self, needs_input_grad):
+        self.needs_input_grad = needs_input_grad
+        self.saved_tensors = ()
+
+    def save_for_backward(self, *tensors):
+        self.saved_tensors = tensors
+
+    def set_materialize_grads(self, value):
+        pass
+
+    def mark_non_differentiable(self, *tensors):
+        pass
+
+
+def color_loss_ray_weights(ray_any, items, weights, channels, global_rays, masked_count=None):
+    """Per-ray weights w_r such that  sum_i weights[i] * loss_i  =  sum_r w_r * sum_c (pred - gt)^2  for the colour-loss items
+    of ``compute_losses`` (base_rendering_model.py:543-560, 598-606; the + 1e-6 per item is a constant):
+        coarse_raycolor             MSELoss over all rays                          -> 1 / (R_global * C)
+        ray_masked_coarse_raycolor  MSELoss over rays with ray_mask > 0            -> [mask] / (n_masked_global * C)
+        ray_miss_coarse_raycolor    MSELoss over rays with ray_mask == 0, times their number  -> [1 - mask] / C
+    ``masked_count``: float tensor [1] with the GLOBAL number of masked rays (ray sharding: summed over ranks); default: the
+    local count.  Returns float32 [R]."""
+    mask = (ray_any.reshape(-1) > 0).to(torch.float32)
+    w = torch.zeros_like(mask)
+    for name, wt in zip(items, weights):
+        wt = float(wt)
+        if wt == 0.0:
+            continue
+        if name.startswith("ray_masked"):
+            cnt = masked_count if masked_count is not None else mask.sum().reshape(1)
+            w = w + mask * (wt / channels) / cnt.clamp_min(1.0)
+        elif name.startswith("ray_miss"):
+            w = w + (1.0 - mask) * (wt / channels)
+        elif name.startswith("ray_depth_masked"):
+            raise NotImplementedError("ray_depth_masked_* needs the MVS depth mask, outside the hot path")
+        else:
+            w = w + wt / float(global_rays * channels)
+    return w
+
+
+class FusedTrainStep:
+    """One training step (query -> forward -> colour loss -> backward) of ``NeuralPointsRayMarching`` as two CUDA graphs.
+
+    model:     NeuralPointsRayMarching on the world-coordinate querier (the tables, grid, MLP it holds are used in place)
+    bg_color:  nn.Parameter [C] (receives a gradient) or a plain tensor
+    rays:      rays per step on this rank (static: the graphs are captured for it); near / far: the camera's depth range
+    color_loss_items / color_loss_weights: as the reference's options of the same names (base_rendering_model.py:543-606)
+    caps:      (S_cap, M_cap) valid samples / pairs the buffers are sized for; default: ``calibrate()`` must be called
+    graph:     False runs the same launch sequence eagerly (tests; no capture)
+    group:     torch.distributed group for ray sharding (gradients: all-reduced by ``RayShardedStep``-style exchange in
+               ``reduce()``; the masked-ray count is all-reduced between the two graphs)
+    """
+
+    def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
+                 caps=None, graph=True, group=None):
+        o = model.opt
+        if getattr(o, "wcoord_query", 1) <= 0:
+            raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
+        self.model, self.bg, self.R, self.near, self.far = model, bg_color, int(rays), float(near), float(far)
+        self.items, self.item_weights = tuple(color_loss_items), tuple(float(w) for w in color_loss_weights)
+        assert len(self.items) == len(self.item_weights)
+        self.caps, self.use_graph, self.group = (tuple(int(c) for c in caps) if caps is not None else None), bool(graph), group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.dev = model.neural_points.xyz.device
+        R, D, C = self.R, int(o.z_depth_dim), int(o.shading_color_channel_num)
+        self.jitter = o.is_train > 0
+        # static inputs: ONE flat buffer [campos 3 | camrotc2w 9 | raydir R*3 | gt R*C | jitter draw R*D], segments padded to
+        # 64 floats - a loader uploads a batch with one copy (load_packed); the graphs read the views
+        sizes = [3, 9, R * 3, R * C] + ([R * D] if self.jitter else [])
+        offs, n = [], 0
+        for sz in sizes:
+            offs.append(n)
+            n += (sz + 63) // 64 * 64
+        self.inbuf = torch.zeros(n, dtype=torch.float32, device=self.dev)
+        self.in_offsets, self.in_sizes = offs, sizes
+        v = [self.inbuf[a:a + sz] for a, sz in zip(offs, sizes)]
+        self.campos, self.rot, self.raydir, self.gt = v[0].view(1, 3), v[1].view(1, 3, 3), v[2].view(1, R, 3), v[3].view(1, R, C)
+        self.uniform = v[4].view(1, R, D) if self.jitter else None
+        self.rot.copy_(torch.eye(3, device=self.dev)[None])
+        self.masked_count = torch.ones(1, dtype=torch.float32, device=self.dev)      # GLOBAL number of rays with neighbours
+        self.counts_host = torch.zeros(4, dtype=torch.int32).pin_memory()           # written by every replay (async copy in the graph)
+        self._needs_mask = any(w != 0.0 and (n.startswith("ray_masked") or n.startswith("ray_miss")) for n, w in zip(self.items, self.item_weights))
+        self._needs_count = any(w != 0.0 and n.startswith("ray_masked") for n, w in zip(self.items, self.item_weights))
+        self._g_query = self._g_step = None
+        self.loss = None
+        self.overflows = 0
+        self.q = {}          # tensors handed from the query graph to the step graph
+        self.grads = {}
+
+    # ---- inputs -------------------------------------------------------------------------------------------------------
+    def set_inputs(self, cam, raydir, gt, uniform=None):
+        """Copies one batch into the static input buffers (device or pinned host tensors; asynchronous)."""
+        if float(cam["near"]) != self.near or float(cam["far"]) != self.far:
+            raise ValueError("near / far are baked into the captured step (%g, %g)" % (self.near, self.far))
+        self.campos.copy_(cam["campos"].reshape(1, 3), non_blocking=True)
+        self.rot.copy_(cam["camrotc2w"].reshape(1, 3, 3), non_blocking=True)
+        self.raydir.copy_(raydir.reshape(1, self.R, 3), non_blocking=True)
+        self.gt.copy_(gt.reshape(self.gt.shape), non_blocking=True)
+        if self.jitter:
+            if uniform is None:
+                self.uniform.uniform_()
+            else:
+                self.uniform.copy_(uniform.reshape(self.uniform.shape), non_blocking=True)
+
+    def load_packed(self, flat):
+        """One copy of a whole batch laid out like ``inbuf`` (see ``in_offsets`` / ``in_sizes``)."""
+        self.inbuf.copy_(flat, non_blocking=True)
+
+    # ---- the launch sequence --------------------------------------------------------------------------------------------
+    def _query_body(self):
+        m, o = self.model, self.model.opt
+        nps = m.neural_points
+        xyz = nps.xyz.detach()
+        raw = nps.querier.query_raw(xyz, self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
+        q = self.q
+        q["pidx"], q["loc_w"], q["ray_any"] = raw["sample_pidx"], raw["sample_loc_w"], raw["ray_any"]
+        q["loc_pers"] = _query.w2pers(q["loc_w"], self.rot[0], self.campos[0])
+        q["xyz_pers"] = _query.w2pers(xyz, self.rot[0], self.campos[0])
+        R, SR, K = q["pidx"].shape
+        q["cs"] = CompactSamples(q["pidx"], R * SR, K, caps=self.caps)
+        if self._needs_count:
+            self.masked_count.copy_((q["ray_any"] > 0).sum().to(torch.float32).reshape(1))
+
+    def _step_body(self):
+        m, o, q = self.model, self.model.opt, self.q
+        nps, agg = m.neural_points, m.aggregator
+        pidx, cs = q["pidx"], q["cs"]
+        R, SR, K = pidx.shape
+        C = int(o.shading_color_channel_num)
+        tabs = (nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf)
+        T = int(nps.points_embeding.shape[-2])
+        call = _AggCall(agg._params(K, SR, True, o.vsize, True), nps.xyz.detach(), q["xyz_pers"], nps.Rw2c.detach().contiguous(),
+                        pidx, q["loc_w"], q["loc_pers"], self.raydir[0], R * SR, T, True, False)
+        call.S, call.M = cs.counts()
+        call.counts_dev = cs.counts_dev
+        call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
+        call.collect_touched = self.world > 1
+        weights = tuple(w.detach() for w in agg._weights())
+        tables = tuple(t.detach() for t in tabs)
+        decoded, _, saved, saved_bytes = agg_forward_raw(call, *tables, weights)
+        slot_row = cs.slot_row.view(R, SR)
+        ray_valid = slot_row >= 0
+        ray_dist = ray_dist_from_samples(q["loc_pers"][None], ray_valid[None], o.vsize, o.raydist_mode_unit)[0]
+        bg = self.bg.detach()
+        bg_grad = bool(getattr(self.bg, "requires_grad", False))
+        n_rows_dev = cs.counts_dev[0:1] if cs.counts_dev is not None else None
+        cctx = _Ctx((True, False, False, bg_grad, False, False, False))
+        ray_color, opacity, acc_T, blend_w, bg_T = _Composite.forward(cctx, decoded, ray_dist, _as_u8(ray_valid), bg, True, slot_row, n_rows_dev)
+        # colour loss: per-ray weights realise the reference's three item kinds; the plain MSE needs none
+        g_rays = self.R * self.world
+        if self._needs_mask:
+            w = color_loss_ray_weights(q["ray_any"], self.items, self.item_weights, C, g_rays, self.masked_count)
+            inv_norm = 1.0
+        else:
+            w, inv_norm = None, sum(self.item_weights) / float(g_rays * C)
+        lctx = _Ctx((True, False, False, False, False, False))
+        self.loss = _ColorMSE.forward(lctx, ray_color.view(1, R, C), self.gt, w, inv_norm)
+        g_feat, _, _, g_bg, _, _, _ = _Composite.backward(cctx, lctx.grad, None, None, None, None)
+        need = tuple(bool(t.requires_grad) for t in tabs)
+        g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, tables, weights, saved, saved_bytes, g_feat, need)
+        self.call = call
+        if cs.counts_dev is not None:
+            self.counts_host.copy_(cs.counts_dev, non_blocking=True)
+        self.out = {"coarse_raycolor": ray_color.view(1, R, C), "coarse_point_opacity": opacity.view(1, R, SR),
+                    "coarse_is_background": bg_T.view(1, R, 1), "ray_any": q["ray_any"]}
+        g = {"points_embeding": g_emb, "points_color": g_col, "points_dir": g_dir, "points_conf": g_cnf, "bg_color": g_bg}
+        for name, gw in zip(("block1.0.weight", "block1.0.bias", "block1.2.weight", "block1.2.bias", "block3.0.weight", "block3.0.bias",
+                             "block3.2.weight", "block3.2.bias", "alpha_branch.0.weight", "alpha_branch.0.bias", "color_branch.0.weight",
+                             "color_branch.0.bias", "color_branch.2.weight", "color_branch.2.bias", "color_branch.4.weight",
+                             "color_branch.4.bias"), g_w):
+            g[name] = gw
+        self.grads = g
+
+    # ---- capacities -----------------------------------------------------------------------------------------------------
+    def calibrate(self, batches, headroom=1.25, granule=4096):
+        """Sets the capacities from the exact counts of sample batches (dicts with cam / raydir / uniform as for
+        ``set_inputs``): max over the batches times ``headroom``, rounded up to ``granule``.  Host read-backs here only."""
+        o, nps = self.model.opt, self.model.neural_points
+        s_max = m_max = 1
+        for b in batches:
+            self.set_inputs(b["cam"], b["raydir"], b["gt"], b.get("uniform"))
+            raw = nps.querier.query_raw(nps.xyz.detach(), self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
+            R, SR, K = raw["sample_pidx"].shape
+            S, M = CompactSamples(raw["sample_pidx"], R * SR, K).counts()
+            s_max, m_max = max(s_max, S), max(m_max, M)
+        up = lambda v: int((int(v * headroom) + granule - 1) // granule * granule)
+        self.set_caps((up(s_max), up(m_max)))
+        return self.caps
+
+    def set_caps(self, caps):
+        R, SR, K = self.R, int(self.model.opt.SR), int(self.model.opt.K)
+        self.caps = (max(1, min(int(caps[0]), R * SR)), max(K, min(int(caps[1]), R * SR * K)))
+        self._g_query = self._g_step = None          # buffers are sized by the capacities: capture again
+
+    def invalidate(self):
+        """Call after the point set, the MLP's tensors or bg_color were REPLACED (prune / grow, load_state_dict into new
+        storage): the graphs hold their addresses."""
+        self._g_query = self._g_step = None
+
+    # ---- capture / replay -----------------------------------------------------------------------------------------------
+    def _capture(self):
+        if self.caps is None:
+            raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):               # warm-up outside capture: grid build, kernel attributes, library streams
+            for _ in range(2):
+                self._query_body()
+                self._step_body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self._g_query, self._g_step = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._g_query):
+            self._query_body()
+        with torch.cuda.graph(self._g_step, pool=self._g_query.pool()):
+            self._step_body()
+        self._bind_grads()
+
+    def _bind_grads(self):
+        nps, agg, g = self.model.neural_points, self.model.aggregator, self.grads
+        for name in ("points_embeding", "points_color", "points_dir", "points_conf"):
+            p = getattr(nps, name)
+            if p is not None and p.requires_grad and g.get(name) is not None:
+                p.grad = g[name].view(p.shape)
+        for name, p in agg.named_parameters():
+            p.grad = g[name]
+        if isinstance(self.bg, torch.nn.Parameter) and self.bg.requires_grad and g.get("bg_color") is not None:
+            self.bg.grad = g["bg_color"].view(self.bg.shape)
+
+    def _check_overflow(self):
+        c = self.counts_host              # written by the replays (a value from a step in flight is as good as any for this check)
+        if int(c[2]) > int(c[0]) or int(c[3]) > int(c[1]):
+            self.overflows += 1
+            warnings.warn("FusedTrainStep: a batch held %d valid samples / %d pairs, above the capacities %s: it was truncated "
+                          "in slot order; capacities grown" % (int(c[2]), int(c[3]), self.caps))
+            self.set_caps((max(self.caps[0], int(int(c[2]) * 1.25) + 4096), max(self.caps[1], int(int(c[3]) * 1.25) + 4096)))
+            self.counts_host.zero_()
+
+    def __call__(self, cam=None, raydir=None, gt=None, uniform=None, packed=None):
+        """Runs one step on the given batch (or on whatever ``set_inputs`` / ``load_packed`` put into the static buffers).
+        Returns the loss (0-d device tensor, static: copy it before the next step if it is read later)."""
+        if packed is not None:
+            self.load_packed(packed)
+        elif raydir is not None:
+            self.set_inputs(cam, raydir, gt, uniform)
+        if not self.use_graph:
+            if self.caps is None:
+                raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
+            self._query_body()
+            self._sync_masked_count()
+            self._step_body()
+            self._bind_grads()
+            return self.loss
+        self._check_overflow()
+        if self._g_step is None:
+            self._capture()
+        self._g_query.replay()
+        self._sync_masked_count()
+        self._g_step.replay()
+        return self.loss
+
+    def _sync_masked_count(self):
+        if self.world > 1 and self._needs_count:
+            dist.all_reduce(self.masked_count, op=dist.ReduceOp.SUM, group=self.group)
+
+    # ---- ray sharding: gradient exchange after the step (dense; the touched-row exchange lives in ray_shard.py) ---------
+    def reduce(self):
+        """All-reduce(SUM) of every gradient over the ranks of ``group``: the per-point tables in place, the MLP gradients as
+        the one flat buffer the backward wrote them into, bg_color.  Ranks normalise their losses by GLOBAL counts, so the
+        sum is the gradient of the whole batch."""
+        if self.world <= 1:
+            return
+        g = self.grads
+        hs = [dist.all_reduce(self.call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)]
+        for name in ("points_embeding", "points_color", "points_dir", "points_conf", "bg_color"):
+            if g.get(name) is not None:
+                hs.append(dist.all_reduce(g[name], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        for h in hs:
+            h.wait()
