@@ -606,6 +606,9 @@ def main():
     ap.add_argument("--bwd-schedule", type=int, default=None, help="pn_set_backward_schedule: 0 one stream, 1 interleaved, 2 chain first")
     ap.add_argument("--no-adam", action="store_true", help="skip the secondary timing of the step WITH the Adam updates")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
+    ap.add_argument("--eager", action="store_true", help="drive the step through autograd from Python (RayShardedStep) instead of the captured CUDA graphs (FusedTrainStep)")
+    ap.add_argument("--loss", default="lego", choices=["lego", "plain"],
+                    help="colour loss: 'lego' = the shipped per-scene items ray_masked / ray_miss / coarse_raycolor with weights 1 0 0 (dev_scripts/w_n360/lego.sh:152-153); 'plain' = MSE over all rays")
     args = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -656,11 +659,28 @@ def main():
     opt, tables, batches, bg = build_workload(args.workload, args.rays, n_pool, seed_base=100 + 1000 * rank)
     model = make_model(opt, tables, dev)
     bg_p = torch.nn.Parameter(bg.to(dev))
-    stepper = RayShardedStep(model, bg_p, sparse=not args.dense_allreduce)
+    stepper = RayShardedStep(model, bg_p, sparse=not args.dense_allreduce)     # autograd-driven step: --eager, and the per-stage timing leg
     dev_batches = [to_dev(b, dev) for b in batches]
     global_rays = args.rays * world
+    packed = [pack_pinned(b) for b in batches]
+    fstep = None
+    if not args.eager:
+        # the product's training step: two CUDA graphs per step, counts on the device (pointnerf_b200/train_step.py)
+        from pointnerf_b200.train_step import FusedTrainStep
+        items = ("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor") if args.loss == "lego" else ("coarse_raycolor",)
+        wts = (1.0, 0.0, 0.0) if args.loss == "lego" else (1.0,)
+        fstep = FusedTrainStep(model, bg_p, args.rays, batches[0]["cam"]["near"], batches[0]["cam"]["far"], color_loss_items=items,
+                               color_loss_weights=wts)
+        fstep.calibrate(dev_batches)
+        flat_dev = [hb.to(dev) for hb, _ in packed]                    # inputs resident in HBM for the headline number
+        assert flat_dev[0].numel() == fstep.inbuf.numel()
 
     def step(i):
+        if fstep is not None:
+            loss = fstep(packed=flat_dev[i % n_pool])                  # one device-to-device copy of the batch, two graph launches
+            if world > 1:
+                fstep.reduce(sparse=not args.dense_allreduce)
+            return loss
         # the training loop hands the NEXT batch along: its sampling / neighbour query is queued between this batch's
         # forward and backward (RayShardedStep.prefetch), so every step still runs one full query + forward + backward
         b, nb = dev_batches[i % n_pool], (dev_batches[(i + 1) % n_pool] if args.prefetch else None)
@@ -691,6 +711,8 @@ def main():
     e1.record()
     sync_all()
     launches = _lib.launch_count()
+    if fstep is not None:        # replays do not pass through the library's launch counter: kernels per replay (counted at capture) x steps
+        launches += fstep.launches_per_step * args.steps
     ms = e0.elapsed_time(e1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -701,7 +723,6 @@ def main():
 
     # ---- end to end: pinned host buffers -> H2D -> step -> D2H of the loss, every step
     _phase("timed loop done (%.3f ms/step); e2e loop" % (ms_total / args.steps))
-    packed = [pack_pinned(b) for b in batches]
     h2d = packed[0][1]["bytes"]
 
     e2e_next, e2e_pending = {}, []
@@ -713,7 +734,44 @@ def main():
         hbuf, meta = packed[i % n_pool]
         return unpack_dev(hbuf.to(dev, non_blocking=True), meta)
 
+    stage = [torch.empty_like(fstep.inbuf) for _ in range(2)] if fstep is not None else None
+    stage_ev = [None, None]
+
+    def e2e_step_graph(i):
+        # H2D of batch i + 1 from pinned host memory into a staging buffer on the copy stream (under this step's kernels);
+        # this step copies ITS staging buffer into the graphs' static inputs (device to device) and replays; the loss goes
+        # to pinned host memory every step and is read by the host one step later
+        main = torch.cuda.current_stream()
+        if stage_ev[i % 2] is None:
+            with torch.cuda.stream(copy_stream):
+                stage[i % 2].copy_(packed[i % n_pool][0], non_blocking=True)
+                stage_ev[i % 2] = torch.cuda.Event()
+                stage_ev[i % 2].record(copy_stream)
+        main.wait_event(stage_ev[i % 2])
+        stage_ev[i % 2] = None
+        fstep.load_packed(stage[i % 2])
+        done = torch.cuda.Event()
+        done.record(main)
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(done)                 # the other staging buffer was consumed by the previous step (stream order)
+            j = (i + 1) % 2
+            stage[j].copy_(packed[(i + 1) % n_pool][0], non_blocking=True)
+            stage_ev[j] = torch.cuda.Event()
+            stage_ev[j].record(copy_stream)
+        loss = fstep()
+        if world > 1:
+            fstep.reduce(sparse=not args.dense_allreduce)
+        buf = loss_host[i % 2]
+        buf.copy_(loss.reshape(1), non_blocking=True)          # D2H read of the step's result
+        ev = torch.cuda.Event()
+        ev.record()
+        e2e_pending.append((ev, buf))
+        if len(e2e_pending) > 1:
+            e2e_drain(1)
+
     def e2e_step(i):
+        if fstep is not None:
+            return e2e_step_graph(i)
         # step i uses the device copy made (from pinned host memory, inside the timed region) during step i - 1 when
         # prefetching; the H2D of batch i + 1 is issued before this step's kernels so that its sampling can be queued.
         # The loss of every step is copied to pinned host memory inside the step and read by the host one step later
@@ -894,6 +952,12 @@ def main():
                                                  "all-gather of the touched point-table gradient rows (ids + 39 floats, rank-ordered sum) + all-reduce of the 1.4 MB MLP gradients"))
                                       if world > 1 else ""),
                            "parallelism": "ray-sharded x%d, points+MLP replicated" % world,
+                           "driver": ("autograd from Python (RayShardedStep, --eager)" if fstep is None else
+                                      "FusedTrainStep: two CUDA graphs per step (query | forward + loss + backward), sample / pair counts stay on the device; "
+                                      "capacities S_cap=%d M_cap=%d (calibrated on the batch pool x1.25), %d overflows; %d library kernels per replayed step"
+                                      % (fstep.caps[0], fstep.caps[1], fstep.overflows, fstep.launches_per_step)),
+                           "loss": ("color_loss_items ray_masked_coarse_raycolor ray_miss_coarse_raycolor coarse_raycolor, weights 1 0 0 (lego.sh:152-153)"
+                                    if args.loss == "lego" else "coarse_raycolor MSE over all rays"),
                            "l2": "working set (point tables %.0f MB + per-step activations) exceeds the 126 MB L2; a pool of %d distinct ray batches is cycled"
                                  % (tables["xyz"].shape[0] * 42 * 4 / 1e6, n_pool),
                            "mean_valid_samples_per_batch": counts["S"] if counts else None,

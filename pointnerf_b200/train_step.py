@@ -115,6 +115,10 @@ class FusedTrainStep:
         self.rot.copy_(torch.eye(3, device=self.dev)[None])
         self.masked_count = torch.ones(1, dtype=torch.float32, device=self.dev)      # GLOBAL number of rays with neighbours
         self.counts_host = torch.zeros(4, dtype=torch.int32).pin_memory()           # written by every replay (async copy in the graph)
+        self.touched_host = torch.zeros(1, dtype=torch.int32).pin_memory()          # distinct table rows the last backward touched
+        self.row_cap = None          # ray sharding: rows per rank in the touched-row exchange (calibrate)
+        self._slots = None
+        self.launches_per_step = 0
         self._needs_mask = any(w != 0.0 and (n.startswith("ray_masked") or n.startswith("ray_miss")) for n, w in zip(self.items, self.item_weights))
         self._needs_count = any(w != 0.0 and n.startswith("ray_masked") for n, w in zip(self.items, self.item_weights))
         self._g_query = self._g_step = None
@@ -171,6 +175,8 @@ class FusedTrainStep:
         call.counts_dev = cs.counts_dev
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
         call.collect_touched = self.world > 1
+        if self.world > 1:                          # bg_color's gradient rides in the tail of the MLP gradient buffer: one all-reduce
+            call.flat_tail = (C + 63) // 64 * 64
         weights = tuple(w.detach() for w in agg._weights())
         tables = tuple(t.detach() for t in tabs)
         decoded, _, saved, saved_bytes = agg_forward_raw(call, *tables, weights)
@@ -195,8 +201,14 @@ class FusedTrainStep:
         need = tuple(bool(t.requires_grad) for t in tabs)
         g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, tables, weights, saved, saved_bytes, g_feat, need)
         self.call = call
+        if self.world > 1 and g_bg is not None:
+            tail = call.grad_flat[call.flat_tail_off:call.flat_tail_off + C]
+            tail.copy_(g_bg)
+            g_bg = tail
         if cs.counts_dev is not None:
             self.counts_host.copy_(cs.counts_dev, non_blocking=True)
+            if call.n_touched is not None:
+                self.touched_host.copy_(call.n_touched, non_blocking=True)
         self.out = {"coarse_raycolor": ray_color.view(1, R, C), "coarse_point_opacity": opacity.view(1, R, SR),
                     "coarse_is_background": bg_T.view(1, R, 1), "ray_any": q["ray_any"]}
         g = {"points_embeding": g_emb, "points_color": g_col, "points_dir": g_dir, "points_conf": g_cnf, "bg_color": g_bg}
@@ -212,15 +224,28 @@ class FusedTrainStep:
         """Sets the capacities from the exact counts of sample batches (dicts with cam / raydir / uniform as for
         ``set_inputs``): max over the batches times ``headroom``, rounded up to ``granule``.  Host read-backs here only."""
         o, nps = self.model.opt, self.model.neural_points
-        s_max = m_max = 1
+        s_max = m_max = u_max = 1
+        T = int(nps.points_embeding.shape[-2])
+        mark = torch.empty(T, dtype=torch.int32, device=self.dev)
+        cnt = torch.empty(1, dtype=torch.int32, device=self.dev)
         for b in batches:
             self.set_inputs(b["cam"], b["raydir"], b["gt"], b.get("uniform"))
             raw = nps.querier.query_raw(nps.xyz.detach(), self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
             R, SR, K = raw["sample_pidx"].shape
             S, M = CompactSamples(raw["sample_pidx"], R * SR, K).counts()
             s_max, m_max = max(s_max, S), max(m_max, M)
+            if self.world > 1:
+                _lib.check(_lib.lib().pn_count_touched_rows(_lib.ptr(raw["sample_pidx"]), raw["sample_pidx"].numel(), T, _lib.ptr(mark),
+                                                            _lib.ptr(cnt), _lib.stream()), "pn_count_touched_rows")
+                u_max = max(u_max, int(cnt.item()))
         up = lambda v: int((int(v * headroom) + granule - 1) // granule * granule)
-        self.set_caps((up(s_max), up(m_max)))
+        caps = [up(s_max), up(m_max), up(u_max)]
+        if self.world > 1:                          # the same capacities on every rank (the exchange needs equal row counts)
+            t = torch.tensor(caps, dtype=torch.int64, device=self.dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            caps = [int(v) for v in t.tolist()]
+        self.set_caps(caps[:2])
+        self.row_cap = min(caps[2], self.caps[1], T)
         return self.caps
 
     def set_caps(self, caps):
@@ -246,10 +271,12 @@ class FusedTrainStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self._g_query, self._g_step = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
         with torch.cuda.graph(self._g_query):
             self._query_body()
         with torch.cuda.graph(self._g_step, pool=self._g_query.pool()):
             self._step_body()
+        self.launches_per_step = int(_lib.launch_count() - n0)      # kernels of this library inside one replay of the two graphs
         self._bind_grads()
 
     def _bind_grads(self):
@@ -299,17 +326,43 @@ class FusedTrainStep:
         if self.world > 1 and self._needs_count:
             dist.all_reduce(self.masked_count, op=dist.ReduceOp.SUM, group=self.group)
 
-    # ---- ray sharding: gradient exchange after the step (dense; the touched-row exchange lives in ray_shard.py) ---------
-    def reduce(self):
-        """All-reduce(SUM) of every gradient over the ranks of ``group``: the per-point tables in place, the MLP gradients as
-        the one flat buffer the backward wrote them into, bg_color.  Ranks normalise their losses by GLOBAL counts, so the
-        sum is the gradient of the whole batch."""
+    # ---- ray sharding: gradient exchange after the step ----------------------------------------------------------------
+    def reduce(self, sparse=True):
+        """Sum of every gradient over the ranks of ``group``.  Ranks normalise their losses by GLOBAL counts, so the sum is
+        the gradient of the whole batch.  MLP gradients + bg_color: ONE all-reduce of the flat buffer the backward wrote
+        them into.  Per-point tables: ``sparse`` - all-gather of the rows this step touched ([id | F + 7 floats], row_cap
+        rows per rank from calibrate()) and a rank-ordered merge (pn_rows_pack / pn_rows_merge: identical bits on every
+        replica); else a dense all-reduce of the four tables."""
         if self.world <= 1:
             return
-        g = self.grads
-        hs = [dist.all_reduce(self.call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)]
-        for name in ("points_embeding", "points_color", "points_dir", "points_conf", "bg_color"):
-            if g.get(name) is not None:
-                hs.append(dist.all_reduce(g[name], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
-        for h in hs:
-            h.wait()
+        g, call, lib = self.grads, self.call, _lib.lib()
+        F = int(g["points_embeding"].shape[-1]) if g.get("points_embeding") is not None else 0
+        h_flat = dist.all_reduce(call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        if sparse and F and F <= 56 and call.touched_ids is not None and self.row_cap:
+            if int(self.touched_host[0]) > self.row_cap:         # flagged one step late, like the sample / pair capacities
+                self.overflows += 1
+                warnings.warn("FusedTrainStep: %d touched rows exceed the exchange capacity %d: grown" % (int(self.touched_host[0]), self.row_cap))
+                t = torch.tensor([int(int(self.touched_host[0]) * 1.25) + 4096], dtype=torch.int64, device=self.dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                self.row_cap = int(t.item())
+            cap = self.row_cap
+            packed = torch.empty((cap, F + 8), dtype=torch.float32, device=self.dev)
+            _lib.check(lib.pn_rows_pack(_lib.ptr(call.touched_ids), int(call.touched_ids.numel()), cap, F, _lib.ptr(g["points_embeding"]),
+                                        _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
+                                        _lib.ptr(packed), _lib.stream()), "pn_rows_pack")
+            gathered = torch.empty((self.world * cap, F + 8), dtype=torch.float32, device=self.dev)
+            dist.all_gather_into_tensor(gathered, packed, group=self.group)
+            T = int(g["points_embeding"].shape[0])
+            if self._slots is None or self._slots.numel() != T * self.world:
+                self._slots = torch.full((T * self.world,), -1, dtype=torch.int32, device=self.dev)
+            _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, T, _lib.ptr(self._slots), _lib.ptr(g["points_embeding"]),
+                                         _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
+                                         _lib.stream()), "pn_rows_merge")
+            self.exchange_bytes = (self.world - 1) * cap * (F + 8) * 4
+        else:
+            hs = [dist.all_reduce(g[n], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                  for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None]
+            for h in hs:
+                h.wait()
+            self.exchange_bytes = sum(g[n].numel() * 4 for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None)
+        h_flat.wait()
