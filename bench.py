@@ -670,14 +670,17 @@ def main():
         items = ("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor") if args.loss == "lego" else ("coarse_raycolor",)
         wts = (1.0, 0.0, 0.0) if args.loss == "lego" else (1.0,)
         fstep = FusedTrainStep(model, bg_p, args.rays, batches[0]["cam"]["near"], batches[0]["cam"]["far"], color_loss_items=items,
-                               color_loss_weights=wts)
+                               color_loss_weights=wts, pipeline=args.prefetch)
         fstep.calibrate(dev_batches)
         flat_dev = [hb.to(dev) for hb, _ in packed]                    # inputs resident in HBM for the headline number
         assert flat_dev[0].numel() == fstep.inbuf.numel()
+        if args.prefetch:
+            fstep.prime(packed=flat_dev[0])
+    shift = 1 if (fstep is not None and args.prefetch) else 0          # pipelined: step i is handed batch i + 1 (queried beside its backward)
 
     def step(i):
         if fstep is not None:
-            loss = fstep(packed=flat_dev[i % n_pool])                  # one device-to-device copy of the batch, two graph launches
+            loss = fstep(packed=flat_dev[(i + shift) % n_pool])        # one device-to-device copy of a batch, one or two graph launches
             if world > 1:
                 fstep.reduce(sparse=not args.dense_allreduce)
             return loss
@@ -744,7 +747,7 @@ def main():
         main = torch.cuda.current_stream()
         if stage_ev[i % 2] is None:
             with torch.cuda.stream(copy_stream):
-                stage[i % 2].copy_(packed[i % n_pool][0], non_blocking=True)
+                stage[i % 2].copy_(packed[(i + shift) % n_pool][0], non_blocking=True)
                 stage_ev[i % 2] = torch.cuda.Event()
                 stage_ev[i % 2].record(copy_stream)
         main.wait_event(stage_ev[i % 2])
@@ -755,7 +758,7 @@ def main():
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(done)                 # the other staging buffer was consumed by the previous step (stream order)
             j = (i + 1) % 2
-            stage[j].copy_(packed[(i + 1) % n_pool][0], non_blocking=True)
+            stage[j].copy_(packed[(i + 1 + shift) % n_pool][0], non_blocking=True)
             stage_ev[j] = torch.cuda.Event()
             stage_ev[j].record(copy_stream)
         loss = fstep()

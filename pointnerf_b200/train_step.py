@@ -83,12 +83,16 @@ class FusedTrainStep:
     color_loss_items / color_loss_weights: as the reference's options of the same names (base_rendering_model.py:543-606)
     caps:      (S_cap, M_cap) valid samples / pairs the buffers are sized for; default: ``calibrate()`` must be called
     graph:     False runs the same launch sequence eagerly (tests; no capture)
-    group:     torch.distributed group for ray sharding (gradients: all-reduced by ``RayShardedStep``-style exchange in
-               ``reduce()``; the masked-ray count is all-reduced between the two graphs)
+    group:     torch.distributed group for ray sharding (gradients: summed over ranks by ``reduce()``; the masked-ray count
+               is all-reduced between the query and the step)
+    pipeline:  the query of the NEXT batch runs inside the step graph, on a forked branch beside the backward (its kernels
+               are small and latency-bound, the backward's persistent GEMMs leave SMs idle at their tails).  Protocol:
+               ``prime(batch 0)`` once, then ``step(batch i + 1)`` runs forward + loss + backward of batch i and returns its
+               loss.  Every step still runs one full query + forward + backward.
     """
 
     def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
-                 caps=None, graph=True, group=None):
+                 caps=None, graph=True, group=None, pipeline=False):
         o = model.opt
         if getattr(o, "wcoord_query", 1) <= 0:
             raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
@@ -113,6 +117,14 @@ class FusedTrainStep:
         self.campos, self.rot, self.raydir, self.gt = v[0].view(1, 3), v[1].view(1, 3, 3), v[2].view(1, R, 3), v[3].view(1, R, C)
         self.uniform = v[4].view(1, R, D) if self.jitter else None
         self.rot.copy_(torch.eye(3, device=self.dev)[None])
+        # the batch the step works on: the inputs and query results are PUBLISHED into these persistent buffers by the query
+        # graph (or by the query branch at the end of a pipelined step), so that `inbuf` is free for the next batch
+        self.cur_in = torch.zeros_like(self.inbuf)
+        cv = [self.cur_in[a:a + sz] for a, sz in zip(offs, sizes)]
+        self.c_campos, self.c_rot, self.c_raydir, self.c_gt = cv[0].view(1, 3), cv[1].view(1, 3, 3), cv[2].view(1, R, 3), cv[3].view(1, R, C)
+        self.pipeline = bool(pipeline)
+        self._primed = False
+        self._side = None
         self.masked_count = torch.ones(1, dtype=torch.float32, device=self.dev)      # GLOBAL number of rays with neighbours
         self.counts_host = torch.zeros(4, dtype=torch.int32).pin_memory()           # written by every replay (async copy in the graph)
         self.touched_host = torch.zeros(1, dtype=torch.int32).pin_memory()          # distinct table rows the last backward touched
@@ -152,40 +164,53 @@ class FusedTrainStep:
         nps = m.neural_points
         xyz = nps.xyz.detach()
         raw = nps.querier.query_raw(xyz, self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
-        q = self.q
+        q = {}
         q["pidx"], q["loc_w"], q["ray_any"] = raw["sample_pidx"], raw["sample_loc_w"], raw["ray_any"]
         q["loc_pers"] = _query.w2pers(q["loc_w"], self.rot[0], self.campos[0])
-        q["xyz_pers"] = _query.w2pers(xyz, self.rot[0], self.campos[0])
         R, SR, K = q["pidx"].shape
-        q["cs"] = CompactSamples(q["pidx"], R * SR, K, caps=self.caps)
+        cs = CompactSamples(q["pidx"], R * SR, K, caps=self.caps)
+        q["sample_list"], q["pair_start"], q["pair_src"], q["slot_row"], q["counts"] = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row, cs.counts_dev
         if self._needs_count:
-            self.masked_count.copy_((q["ray_any"] > 0).sum().to(torch.float32).reshape(1))
+            q["masked"] = (q["ray_any"] > 0).sum().to(torch.float32).reshape(1)
+        return q
 
-    def _step_body(self):
+    def _publish(self, t):
+        """Query results + the inputs they belong to -> the persistent buffers the step reads."""
+        if not self.q or any(self.q[k].shape != v.shape for k, v in t.items() if k != "masked"):
+            self.q = {k: torch.empty_like(v) for k, v in t.items() if k != "masked"}       # (first call: outside any capture)
+        for k, v in t.items():
+            if k == "masked":
+                self.masked_count.copy_(v)
+            else:
+                self.q[k].copy_(v)
+        self.cur_in.copy_(self.inbuf)
+
+    def _step_body(self, prefetch=False):
         m, o, q = self.model, self.model.opt, self.q
         nps, agg = m.neural_points, m.aggregator
-        pidx, cs = q["pidx"], q["cs"]
+        pidx = q["pidx"]
         R, SR, K = pidx.shape
+        xyz_pers = _query.w2pers(nps.xyz.detach(), self.c_rot[0], self.c_campos[0])
         C = int(o.shading_color_channel_num)
         tabs = (nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf)
         T = int(nps.points_embeding.shape[-2])
-        call = _AggCall(agg._params(K, SR, True, o.vsize, True), nps.xyz.detach(), q["xyz_pers"], nps.Rw2c.detach().contiguous(),
-                        pidx, q["loc_w"], q["loc_pers"], self.raydir[0], R * SR, T, True, False)
-        call.S, call.M = cs.counts()
-        call.counts_dev = cs.counts_dev
-        call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
+        call = _AggCall(agg._params(K, SR, True, o.vsize, True), nps.xyz.detach(), xyz_pers, nps.Rw2c.detach().contiguous(),
+                        pidx, q["loc_w"], q["loc_pers"], self.c_raydir[0], R * SR, T, True, False)
+        call.S, call.M = int(q["sample_list"].numel()), int(q["pair_src"].numel())       # the capacities
+        call.counts_dev = q["counts"]
+        call.sample_list, call.pair_start, call.pair_src, call.slot_row = q["sample_list"], q["pair_start"], q["pair_src"], q["slot_row"]
         call.collect_touched = self.world > 1
         if self.world > 1:                          # bg_color's gradient rides in the tail of the MLP gradient buffer: one all-reduce
             call.flat_tail = (C + 63) // 64 * 64
         weights = tuple(w.detach() for w in agg._weights())
         tables = tuple(t.detach() for t in tabs)
         decoded, _, saved, saved_bytes = agg_forward_raw(call, *tables, weights)
-        slot_row = cs.slot_row.view(R, SR)
+        slot_row = q["slot_row"].view(R, SR)
         ray_valid = slot_row >= 0
         ray_dist = ray_dist_from_samples(q["loc_pers"][None], ray_valid[None], o.vsize, o.raydist_mode_unit)[0]
         bg = self.bg.detach()
         bg_grad = bool(getattr(self.bg, "requires_grad", False))
-        n_rows_dev = cs.counts_dev[0:1] if cs.counts_dev is not None else None
+        n_rows_dev = q["counts"][0:1]
         cctx = _Ctx((True, False, False, bg_grad, False, False, False))
         ray_color, opacity, acc_T, blend_w, bg_T = _Composite.forward(cctx, decoded, ray_dist, _as_u8(ray_valid), bg, True, slot_row, n_rows_dev)
         # colour loss: per-ray weights realise the reference's three item kinds; the plain MSE needs none
@@ -196,7 +221,13 @@ class FusedTrainStep:
         else:
             w, inv_norm = None, sum(self.item_weights) / float(g_rays * C)
         lctx = _Ctx((True, False, False, False, False, False))
-        self.loss = _ColorMSE.forward(lctx, ray_color.view(1, R, C), self.gt, w, inv_norm)
+        self.loss = _ColorMSE.forward(lctx, ray_color.view(1, R, C), self.c_gt, w, inv_norm)
+        nxt = None
+        if prefetch:        # the NEXT batch's query (inputs in `inbuf`) on a forked branch, beside this batch's backward
+            main = torch.cuda.current_stream()
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                nxt = self._query_body()
         g_feat, _, _, g_bg, _, _, _ = _Composite.backward(cctx, lctx.grad, None, None, None, None)
         need = tuple(bool(t.requires_grad) for t in tabs)
         g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, tables, weights, saved, saved_bytes, g_feat, need)
@@ -205,12 +236,11 @@ class FusedTrainStep:
             tail = call.grad_flat[call.flat_tail_off:call.flat_tail_off + C]
             tail.copy_(g_bg)
             g_bg = tail
-        if cs.counts_dev is not None:
-            self.counts_host.copy_(cs.counts_dev, non_blocking=True)
-            if call.n_touched is not None:
-                self.touched_host.copy_(call.n_touched, non_blocking=True)
+        self.counts_host.copy_(q["counts"], non_blocking=True)
+        if call.n_touched is not None:
+            self.touched_host.copy_(call.n_touched, non_blocking=True)
         self.out = {"coarse_raycolor": ray_color.view(1, R, C), "coarse_point_opacity": opacity.view(1, R, SR),
-                    "coarse_is_background": bg_T.view(1, R, 1), "ray_any": q["ray_any"]}
+                    "coarse_is_background": bg_T.view(1, R, 1), "ray_any": q["ray_any"].clone(), "slot_row": slot_row.clone()}
         g = {"points_embeding": g_emb, "points_color": g_col, "points_dir": g_dir, "points_conf": g_cnf, "bg_color": g_bg}
         for name, gw in zip(("block1.0.weight", "block1.0.bias", "block1.2.weight", "block1.2.bias", "block3.0.weight", "block3.0.bias",
                              "block3.2.weight", "block3.2.bias", "alpha_branch.0.weight", "alpha_branch.0.bias", "color_branch.0.weight",
@@ -218,6 +248,9 @@ class FusedTrainStep:
                              "color_branch.4.bias"), g_w):
             g[name] = gw
         self.grads = g
+        if prefetch:        # join; the next batch becomes the current one (after everything that read the current buffers)
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._publish(nxt)
 
     # ---- capacities -----------------------------------------------------------------------------------------------------
     def calibrate(self, batches, headroom=1.25, granule=4096):
@@ -264,18 +297,23 @@ class FusedTrainStep:
             raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
+        if self._side is None:
+            self._side = torch.cuda.Stream()
         with torch.cuda.stream(side):               # warm-up outside capture: grid build, kernel attributes, library streams
             for _ in range(2):
-                self._query_body()
-                self._step_body()
+                self._publish(self._query_body())
+                self._step_body(prefetch=self.pipeline)
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self._g_query, self._g_step = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         n0 = _lib.launch_count()
         with torch.cuda.graph(self._g_query):
-            self._query_body()
+            self._publish(self._query_body())
+        n1 = _lib.launch_count()
         with torch.cuda.graph(self._g_step, pool=self._g_query.pool()):
-            self._step_body()
+            self._step_body(prefetch=self.pipeline)
+        if self.pipeline:                           # a replayed step = forward + loss + backward + the next batch's query
+            n0 = n1
         self.launches_per_step = int(_lib.launch_count() - n0)      # kernels of this library inside one replay of the two graphs
         self._bind_grads()
 
@@ -306,21 +344,60 @@ class FusedTrainStep:
             self.load_packed(packed)
         elif raydir is not None:
             self.set_inputs(cam, raydir, gt, uniform)
+        if self.pipeline and not self._primed:
+            raise RuntimeError("FusedTrainStep(pipeline=True): call prime(first batch) before the first step")
         if not self.use_graph:
             if self.caps is None:
                 raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
-            self._query_body()
-            self._sync_masked_count()
-            self._step_body()
+            if self._side is None:
+                self._side = torch.cuda.Stream()
+            if not self.pipeline:
+                self._publish(self._query_body())
+                self._sync_masked_count()
+            self._step_body(prefetch=self.pipeline)
+            if self.pipeline:
+                self._sync_masked_count()
             self._bind_grads()
             return self.loss
         self._check_overflow()
         if self._g_step is None:
-            self._capture()
-        self._g_query.replay()
-        self._sync_masked_count()
+            self._recapture_keeping_current()
+        if not self.pipeline:
+            self._g_query.replay()
+            self._sync_masked_count()
         self._g_step.replay()
+        if self.pipeline:
+            self._sync_masked_count()      # the count of the batch just queried normalises the NEXT step's loss
         return self.loss
+
+    def prime(self, cam=None, raydir=None, gt=None, uniform=None, packed=None):
+        """pipeline=True: loads the FIRST batch and runs its query; the following ``step(next batch)`` calls work on it."""
+        if packed is not None:
+            self.load_packed(packed)
+        elif raydir is not None:
+            self.set_inputs(cam, raydir, gt, uniform)
+        if self.use_graph:
+            if self._g_step is None:
+                self._capture()
+            self._g_query.replay()
+        else:
+            if self.caps is None:
+                raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
+            self._publish(self._query_body())
+        self._sync_masked_count()
+        self._primed = True
+
+    def _recapture_keeping_current(self):
+        """(Re)capture.  The warm-up and the capture run the bodies on whatever `inbuf` holds and publish it; in pipeline mode
+        the CURRENT batch (queried by the previous step) must survive that: its inputs are put back and queried again."""
+        if not (self.pipeline and self._primed):
+            return self._capture()
+        keep_next, cur = self.inbuf.clone(), self.cur_in.clone()
+        self.inbuf.copy_(cur)
+        self._capture()
+        self._g_query.replay()             # the current batch again, under the new capacities
+        self._sync_masked_count()
+        self.inbuf.copy_(keep_next)
 
     def _sync_masked_count(self):
         if self.world > 1 and self._needs_count:

@@ -130,6 +130,37 @@ def test_graph_replay_equals_eager_sequence_bit_for_bit(cuda_dev):
     assert graphed.overflows == 0
 
 
+@pytest.mark.parametrize("graph", [False, True])
+def test_pipelined_steps_equal_plain_steps_bit_for_bit(cuda_dev, graph):
+    """pipeline=True: the next batch's query runs inside the step, beside the backward; every batch's loss and gradients are
+    the ones the plain sequence produces."""
+    R = 256
+    opt, model, batches, bg, cam = _setup(cuda_dev, R, 4)
+    items, weights = ("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor"), (1.0, 0.2, 0.1)
+    plain = FusedTrainStep(model, bg, R, cam["near"], cam["far"], color_loss_items=items, color_loss_weights=weights, graph=False)
+    caps = plain.calibrate(batches, headroom=1.3, granule=256)
+    want = []
+    for b in batches:
+        loss = plain(b["cam"], b["raydir"], b["gt"], b["uniform"]).clone()
+        want.append((loss, _fused_grads(model, bg), plain.out["coarse_raycolor"].clone()))
+    piped = FusedTrainStep(model, bg, R, cam["near"], cam["far"], color_loss_items=items, color_loss_weights=weights, caps=caps,
+                           graph=graph, pipeline=True)
+    with pytest.raises(RuntimeError):
+        piped(batches[0]["cam"], batches[0]["raydir"], batches[0]["gt"], batches[0]["uniform"])
+    b0 = batches[0]
+    piped.prime(b0["cam"], b0["raydir"], b0["gt"], b0["uniform"])
+    n = len(batches)
+    for i in range(2 * n):                        # step(batch i + 1) works on batch i
+        nb = batches[(i + 1) % n]
+        loss = piped(nb["cam"], nb["raydir"], nb["gt"], nb["uniform"]).clone()
+        got = _fused_grads(model, bg)
+        wl, wg, wc = want[i % n]
+        assert torch.equal(loss, wl), i
+        assert torch.equal(piped.out["coarse_raycolor"], wc)
+        for k in wg:
+            assert torch.equal(got[k], wg[k]), (i, k)
+
+
 def test_capacity_overflow_truncates_in_slot_order_is_flagged_and_grows(cuda_dev):
     R = 256
     opt, model, batches, bg, cam = _setup(cuda_dev, R, 1, train=0)
@@ -146,8 +177,8 @@ def test_capacity_overflow_truncates_in_slot_order_is_flagged_and_grows(cuda_dev
     assert c[2] == S and c[3] == M and c[0] == S // 2 and c[1] < M          # kept a prefix, reported the totals
     assert torch.isfinite(loss)
     # rays are processed in slot order: the rays whose samples all fit are rendered exactly as in the full run
-    slot_row = small.q["cs"].slot_row.view(R, opt.SR)
-    any_full = full.q["cs"].slot_row.view(R, opt.SR) >= 0
+    slot_row = small.out["slot_row"]
+    any_full = full.out["slot_row"] >= 0
     intact = ((slot_row >= 0) == any_full).all(-1)
     assert int(intact.sum()) > 10 and int((~intact).sum()) > 10
     assert torch.equal(small.out["coarse_raycolor"][0][intact], full.out["coarse_raycolor"][0][intact])
