@@ -62,7 +62,9 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
                                                        float* __restrict__ weight_out) {
     const int lane = threadIdx.x & 31;
     const int64_t S = n_samples(in);
-  for (int64_t si = warp_id_global(); si < S; si += warps_total()) {
+    const int64_t si = warp_id_global();                 // the launch covers the capacity: one sample per warp, no loop (registers)
+    if (si >= S) return;
+  {
     int slot = in.sample_list[si];
     int p0 = in.pair_start[si], np = in.pair_start[si + 1] - p0;
     float sx = in.sample_loc_w[3 * (int64_t)slot], sy = in.sample_loc_w[3 * (int64_t)slot + 1], sz = in.sample_loc_w[3 * (int64_t)slot + 2];
@@ -120,12 +122,14 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
 // interleaves (sin, cos) per (channel, frequency), so a lane owns short scattered runs of the row - stored directly,
 // every instruction would touch every 32-byte sector of the row (6x the L2 write transactions).  The row is assembled
 // in shared memory and leaves as whole float4s.
-__global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1) {
+__global__ void __launch_bounds__(256, 8) agg_prep_rows_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1) {
     extern __shared__ float prep_rows[];                 // blockDim.x / 32 rows of in1p floats
     const int lane = threadIdx.x & 31;
     const int64_t M = n_pairs(in);
     float* srow = prep_rows + (threadIdx.x >> 5) * d.in1p;
-  for (int64_t m = warp_id_global(); m < M; m += warps_total()) {
+    const int64_t m = warp_id_global();                  // the launch covers the capacity: one pair per warp, no loop (registers)
+    if (m >= M) return;
+  {
     const int gj = in.sample_pidx[in.pair_src[m]];
     float* row = X1 + m * d.in1p;
     const int pe0 = d.F + 2 * d.ff * d.F;
@@ -162,7 +166,6 @@ __global__ void __launch_bounds__(256) agg_prep_rows_kernel(pn_agg_inputs in, Ag
     __syncwarp();
     float4* row4 = reinterpret_cast<float4*>(row);       // in1p % 4 == 0 and X1 is 16-byte aligned
     for (int c4 = lane; c4 < (d.in1p >> 2); c4 += 32) row4[c4] = *reinterpret_cast<const float4*>(srow + 4 * c4);
-    __syncwarp();                                        // the row buffer is reused by the warp's next pair
   }
 }
 
@@ -182,7 +185,9 @@ __global__ void __launch_bounds__(256) agg_reduce_kernel(pn_agg_inputs in, AggDi
 #pragma unroll
     for (int i = 0; i < NW; ++i) wa[i] = wal[lane + 32 * i];
     const float b = bal[0];
-  for (int64_t si = warp_id_global(); si < S; si += warps_total()) {
+    const int64_t si = warp_id_global();                 // the launch covers the capacity: one sample per warp, no loop (registers)
+    if (si >= S) return;
+  {
     int slot = in.sample_list[si];
     int p0 = in.pair_start[si], np = in.pair_start[si + 1] - p0;
     float acc[NW];
@@ -276,7 +281,7 @@ __global__ void __launch_bounds__(256) agg_gout_kernel(pn_agg_inputs in, AggDims
 // the range.  dPre4[m,:] = (wc*g_fs + g_araw*w_alpha) * lrelu'(H4), conf gradient per pair, and the
 // density-head parameter gradients as per-CTA partials (summed in CTA order by agg_alpha_final_kernel).
 template <int NW>
-__global__ void __launch_bounds__(256) agg_reduce_bwd_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ H4,
+__global__ void __launch_bounds__(256, 4) agg_reduce_bwd_kernel(pn_agg_inputs in, AggDims d, const float* __restrict__ H4,
                                                              const float4* __restrict__ pairv, const float* __restrict__ wal,
                                                              const float* __restrict__ GFS, const float* __restrict__ galpha,
                                                              float* __restrict__ dPre4, int64_t ld4,
