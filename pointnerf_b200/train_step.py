@@ -92,7 +92,7 @@ class FusedTrainStep:
     """
 
     def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
-                 caps=None, graph=True, group=None, pipeline=False):
+                 caps=None, graph=True, group=None, pipeline=False, local_only=False):
         o = model.opt
         if getattr(o, "wcoord_query", 1) <= 0:
             raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
@@ -100,7 +100,7 @@ class FusedTrainStep:
         self.items, self.item_weights = tuple(color_loss_items), tuple(float(w) for w in color_loss_weights)
         assert len(self.items) == len(self.item_weights)
         self.caps, self.use_graph, self.group = (tuple(int(c) for c in caps) if caps is not None else None), bool(graph), group
-        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized() and not local_only) else 1
         self.dev = model.neural_points.xyz.device
         R, D, C = self.R, int(o.z_depth_dim), int(o.shading_color_channel_num)
         self.jitter = o.is_train > 0
@@ -443,3 +443,52 @@ class FusedTrainStep:
                 h.wait()
             self.exchange_bytes = sum(g[n].numel() * 4 for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None)
         h_flat.wait()
+
+
+def sharded_gradient_check(model, bg_color, batch, items, weights, group=None):
+    """Ray sharding against the single-process step, on every rank of ``group`` (collective: all ranks call it with the SAME
+    full batch - dict(cam, raydir [1,R,3], gt [1,R,C], uniform)).  Each rank steps on its contiguous slice of the rays.
+    Returns a dict: ``replicas_identical`` (the exchanged gradients are the same bits on every rank), ``sparse_vs_dense``
+    (touched-row exchange against the dense all-reduce, relative to the gradient's max; exactly 0 at two ranks, where a sum
+    of two terms has one order), ``sharded_vs_single`` (against this rank's own single-process gradient of the WHOLE batch,
+    masked-ray normaliser included; the sums run in a different order: <= 1e-4), ``ok``."""
+    from .ray_shard import shard_bounds
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    R = int(batch["raydir"].shape[1])
+    lo, hi = shard_bounds(R, world, rank)
+    if (hi - lo) * world != R:
+        raise ValueError("sharded_gradient_check: the ray count must divide by the world size")
+    near, far = batch["cam"]["near"], batch["cam"]["far"]
+    uni = batch.get("uniform")
+    shard = dict(cam=batch["cam"], raydir=batch["raydir"][:, lo:hi].contiguous(), gt=batch["gt"][:, lo:hi].contiguous(),
+                 uniform=uni[:, lo:hi].contiguous() if uni is not None else None)
+    order = ("points_embeding", "points_color", "points_dir", "points_conf", "bg_color")
+
+    def flat(step):
+        g = step.grads
+        names = [n for n in order if g.get(n) is not None] + sorted(n for n in g if n not in order)
+        return torch.cat([g[n].reshape(-1) for n in names]).clone()
+
+    single = FusedTrainStep(model, bg_color, R, near, far, items, weights, graph=False, local_only=True)
+    single.calibrate([batch], headroom=1.0, granule=256)
+    single(batch["cam"], batch["raydir"], batch["gt"], uni)
+    whole = flat(single)
+    st = FusedTrainStep(model, bg_color, hi - lo, near, far, items, weights, graph=True, group=group)
+    st.calibrate([shard], headroom=1.0, granule=256)
+    res = {}
+    for mode in ("sparse", "dense"):
+        st(shard["cam"], shard["raydir"], shard["gt"], shard["uniform"])
+        st.reduce(sparse=(mode == "sparse"))
+        res[mode] = flat(st)
+    scale = float(whole.abs().max())
+    e_sd = float((res["sparse"] - res["dense"]).abs().max()) / scale
+    e_sw = float((res["sparse"] - whole).abs().max()) / scale
+    gathered = [torch.empty_like(res["sparse"]) for _ in range(world)]
+    dist.all_gather(gathered, res["sparse"], group=group)
+    same = all(torch.equal(t, gathered[0]) for t in gathered)
+    ok = same and e_sd <= (0.0 if world == 2 else 1e-6) and e_sw <= 1e-4 and st.overflows == 0
+    flag = torch.tensor([1 if ok else 0], device=whole.device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return {"world": world, "rays": R, "replicas_identical": bool(same), "sparse_vs_dense": e_sd, "sharded_vs_single": e_sw,
+            "touched_rows_per_rank_cap": int(st.row_cap or 0), "loss_items": list(items), "ok": bool(int(flag))}
