@@ -201,6 +201,127 @@ def pin(batch):
 
 
 # ---------------------------------------------------------------------------------------------------------
+# the other BASELINE configurations as extra legs of the same JSON line (north_star: rays/s at 1/2/4/8 GPUs on the
+# 3 M-point and 20 M-point scenes; weak = fixed rays per GPU, strong = 65 536 rays per step split over the ranks)
+# ---------------------------------------------------------------------------------------------------------
+def build_scene_on_device(name, dev, rank, world):
+    """Scene for a bench leg.  Rank 0 generates the point positions (the 20 M-point cloud takes ~45 s of host time) and
+    broadcasts them; the per-point tables are drawn ON the device from a fixed seed (identical on every rank)."""
+    from pointnerf_b200 import synthetic as syn
+    opt = copy.copy(syn.config_opt(name))
+    opt.is_train = 1
+    if rank == 0:
+        _, tables = syn.make_scene(name)
+        xyz = tables["xyz"].to(dev)
+        n = torch.tensor([xyz.shape[0]], dtype=torch.int64, device=dev)
+    else:
+        xyz, n = None, torch.zeros(1, dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.broadcast(n, 0)
+        if rank != 0:
+            xyz = torch.empty((int(n.item()), 3), dtype=torch.float32, device=dev)
+        dist.broadcast(xyz, 0)
+    N, F = int(xyz.shape[0]), int(opt.point_features_dim)
+    g = torch.Generator(device=dev).manual_seed(4321)
+    d = torch.randn(1, N, 3, device=dev, generator=g)
+    tables = dict(xyz=xyz, points_embeding=torch.rand(1, N, F, device=dev, generator=g) - 0.5,
+                  points_conf=torch.rand(1, N, 1, device=dev, generator=g) * 0.9 + 0.1, points_dir=d / d.norm(dim=-1, keepdim=True),
+                  points_color=torch.randn(1, N, 3, device=dev, generator=g), Rw2c=torch.eye(3, device=dev))
+    return opt, tables
+
+
+def leg_batches(name, opt, rays, n_batches, seed_base, dev):
+    from pointnerf_b200 import synthetic as syn
+    C = int(opt.shading_color_channel_num)
+    out = []
+    for b in range(n_batches):
+        cam = syn.make_camera(name, view=1 + b % 3)      # (view 0 of the room scene looks at a corner: few rays meet geometry)
+        raydir, _ = syn.make_rays(cam, syn.random_pixels(cam, rays, seed=seed_base + b))
+        g = torch.Generator().manual_seed(seed_base * 7919 + b)
+        out.append(to_dev(dict(cam=cam, raydir=raydir, uniform=torch.rand(1, rays, opt.z_depth_dim, generator=g), gt=torch.rand(1, rays, C, generator=g)), dev))
+    return out
+
+
+def run_leg(tag, name, model, opt, rays, dev, rank, world, steps, items, wts, sparse, adam=False):
+    """One extra configuration through the product's training step (FusedTrainStep, pipelined graphs, touched-row exchange):
+    device-timed, max over ranks."""
+    from pointnerf_b200.train_step import FusedTrainStep
+    n_pool = 4
+    batches = leg_batches(name, opt, rays, n_pool, 500 + 1000 * rank, dev)
+    C = int(opt.shading_color_channel_num)
+    bg = torch.nn.Parameter(torch.rand(C, generator=torch.Generator().manual_seed(5)).to(dev))
+    st = FusedTrainStep(model, bg, rays, batches[0]["cam"]["near"], batches[0]["cam"]["far"], color_loss_items=items, color_loss_weights=wts,
+                        pipeline=True)
+    caps = st.calibrate(batches)
+    b0 = batches[0]
+    st.prime(b0["cam"], b0["raydir"], b0["gt"], b0["uniform"])
+    opts = None
+    if adam:
+        from pointnerf_b200.optim import Adam
+        nps_ = model.neural_points
+        opts = [Adam(list(model.aggregator.parameters()), lr=5e-4, betas=(0.9, 0.999)),
+                Adam([t for t in (nps_.points_embeding, nps_.points_conf, nps_.points_dir, nps_.points_color) if t is not None and t.requires_grad] + [bg],
+                     lr=2e-3, betas=(0.9, 0.999))]
+
+    def one(i):
+        nb = batches[(i + 1) % n_pool]
+        st(nb["cam"], nb["raydir"], nb["gt"], nb["uniform"])
+        if world > 1:
+            st.reduce(sparse=sparse)
+        if opts:
+            for o_ in opts:
+                o_.step()
+    for i in range(4):
+        one(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        one(4 + i)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    c = st.counts_host.tolist()
+    res = {"workload": "%s: %d points, %d rays/step/GPU x %d GPU(s), SR=%d K=%d" % (name, int(model.neural_points.xyz.shape[0]), rays, world, opt.SR, opt.K),
+           "ms_per_step": round(ms, 4), "rays_per_s": round(rays * world / (ms * 1e-3), 1), "steps": steps,
+           "valid_samples_last_batch": c[2], "valid_pairs_last_batch": c[3], "capacities": list(caps), "overflows": st.overflows,
+           "with_adam": bool(adam)}
+    if world > 1:
+        res["exchange_bytes_per_rank_per_step"] = int(getattr(st, "exchange_bytes", 0))
+        res["exchange"] = "touched rows (all-gather + rank-ordered merge)" if sparse else "dense all-reduce"
+    del st
+    return res
+
+
+def extra_legs(dev, rank, world, steps, sparse, only=None):
+    items, wts = ("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor"), (1.0, 0.0, 0.0)
+    out = {}
+    for name in ("cfg3", "cfg4"):
+        if only and name not in only:
+            continue
+        _phase("leg scene " + name)
+        opt, tables = build_scene_on_device(name, dev, rank, world)
+        model = make_model(opt, tables, dev)
+        del tables
+        if name == "cfg3":
+            out["cfg3_weak"] = run_leg("cfg3_weak", name, model, opt, 4096, dev, rank, world, steps, items, wts, sparse)
+        else:
+            out["cfg4_weak"] = run_leg("cfg4_weak", name, model, opt, 8192, dev, rank, world, steps, items, wts, sparse)
+            out["cfg4_strong"] = run_leg("cfg4_strong", name, model, opt, 65536 // world, dev, rank, world, max(steps // 2, 4), items, wts, sparse)
+            out["cfg4_weak_with_adam"] = run_leg("cfg4_weak_adam", name, model, opt, 8192, dev, rank, world, max(steps // 2, 4), items, wts, sparse, adam=True)
+        del model
+        torch.cuda.empty_cache()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
 # stage timing (CUDA events on the launching stream) -> roofline of the dominant stage
 # ---------------------------------------------------------------------------------------------------------
 class StageTimer:
@@ -606,6 +727,7 @@ def main():
     ap.add_argument("--bwd-schedule", type=int, default=None, help="pn_set_backward_schedule: 0 one stream, 1 interleaved, 2 chain first")
     ap.add_argument("--no-adam", action="store_true", help="skip the secondary timing of the step WITH the Adam updates")
     ap.add_argument("--dense-allreduce", action="store_true", help="all-reduce the full N x 39 point-table gradients instead of the touched rows")
+    ap.add_argument("--legs", default="auto", help="extra configurations in the same line: 'auto' = 'all' (cfg3 + cfg4 legs), 'none', or a comma list of cfg3,cfg4")
     ap.add_argument("--eager", action="store_true", help="drive the step through autograd from Python (RayShardedStep) instead of the captured CUDA graphs (FusedTrainStep)")
     ap.add_argument("--loss", default="lego", choices=["lego", "plain"],
                     help="colour loss: 'lego' = the shipped per-scene items ray_masked / ray_miss / coarse_raycolor with weights 1 0 0 (dev_scripts/w_n360/lego.sh:152-153); 'plain' = MSE over all rays")
@@ -830,6 +952,21 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = global_rays * args.steps / (float(t.item()) * 1e-3)
 
+    # ---- multi-GPU: gradient equality of the sharded step, and the 3 M / 20 M-point configurations
+    grad_check, legs = None, None
+    if world > 1 and fstep is not None:
+        _phase("sharded gradient check")
+        from pointnerf_b200.train_step import sharded_gradient_check
+        chk = to_dev(build_workload(args.workload, args.rays, 1, seed_base=77)[2][0], dev)     # the same batch on every rank
+        grad_check = sharded_gradient_check(model, bg_p, chk, items, wts)
+        fstep.invalidate()                 # the check's steps re-bound the parameters' .grad to their own buffers
+        if args.prefetch:
+            fstep.prime(packed=flat_dev[0])
+    want_legs = "all" if args.legs == "auto" else args.legs
+    if want_legs != "none" and fstep is not None:
+        legs = extra_legs(dev, rank, world, max(10, min(args.steps, 20)), not args.dense_allreduce,
+                          only=None if want_legs == "all" else want_legs.split(","))
+
     # ---- full-frame inference (all ranks: row blocks)
     _phase("e2e done; frame render")
     frame = None
@@ -970,6 +1107,7 @@ def main():
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, ("frame_%dx%d" % (frame["w"], frame["h"]) if frame else "frame_800x800"): frame,
+                "sharded_gradient_check": grad_check, "legs": legs,
                 "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint, "frustum_querier_wcoord0": frustum}
         _emit(line)
     if world > 1:
