@@ -251,26 +251,35 @@ def run_leg(tag, name, model, opt, rays, dev, rank, world, steps, items, wts, sp
     C = int(opt.shading_color_channel_num)
     bg = torch.nn.Parameter(torch.rand(C, generator=torch.Generator().manual_seed(5)).to(dev))
     st = FusedTrainStep(model, bg, rays, batches[0]["cam"]["near"], batches[0]["cam"]["far"], color_loss_items=items, color_loss_weights=wts,
-                        pipeline=True)
+                        pipeline=True, sparse_exchange=sparse)
     caps = st.calibrate(batches)
     b0 = batches[0]
     st.prime(b0["cam"], b0["raydir"], b0["gt"], b0["uniform"])
-    opts = None
+    opts, row_opt = None, None
     if adam:
-        from pointnerf_b200.optim import Adam
+        from pointnerf_b200.optim import Adam, RowAdam
         nps_ = model.neural_points
-        opts = [Adam(list(model.aggregator.parameters()), lr=5e-4, betas=(0.9, 0.999)),
-                Adam([t for t in (nps_.points_embeding, nps_.points_conf, nps_.points_dir, nps_.points_color) if t is not None and t.requires_grad] + [bg],
-                     lr=2e-3, betas=(0.9, 0.999))]
+        tabs_ = [t for t in (nps_.points_embeding, nps_.points_conf, nps_.points_dir, nps_.points_color) if t is not None and t.requires_grad]
+        opts = [Adam(list(model.aggregator.parameters()), lr=5e-4, betas=(0.9, 0.999))]
+        if adam == "rows":       # lazy Adam on the rows this step touched (an option: torch.optim.SparseAdam semantics)
+            row_opt = RowAdam(tabs_, lr=2e-3, betas=(0.9, 0.999))
+            opts.append(Adam([bg], lr=2e-3, betas=(0.9, 0.999)))
+        else:                    # the reference's dense Adam over every point row
+            opts.append(Adam(tabs_ + [bg], lr=2e-3, betas=(0.9, 0.999)))
 
     def one(i):
         nb = batches[(i + 1) % n_pool]
         st(nb["cam"], nb["raydir"], nb["gt"], nb["uniform"])
         if world > 1:
-            st.reduce(sparse=sparse)
+            st.reduce()
         if opts:
             for o_ in opts:
                 o_.step()
+        if row_opt is not None:
+            if world > 1 and sparse:
+                row_opt.step(st._gathered.view(torch.int32), stride=int(st._gathered.shape[1]))
+            else:
+                row_opt.step(st._touched_ids)
     for i in range(4):
         one(i)
     if world > 1:
@@ -292,7 +301,8 @@ def run_leg(tag, name, model, opt, rays, dev, rank, world, steps, items, wts, sp
     res = {"workload": "%s: %d points, %d rays/step/GPU x %d GPU(s), SR=%d K=%d" % (name, int(model.neural_points.xyz.shape[0]), rays, world, opt.SR, opt.K),
            "ms_per_step": round(ms, 4), "rays_per_s": round(rays * world / (ms * 1e-3), 1), "steps": steps,
            "valid_samples_last_batch": c[2], "valid_pairs_last_batch": c[3], "capacities": list(caps), "overflows": st.overflows,
-           "with_adam": bool(adam)}
+           "with_adam": ("dense torch.optim.Adam semantics (every point row, %.1f GB of traffic per step)" % (int(model.neural_points.xyz.shape[0]) * 39 * 28 / 1e9)
+                         if adam is True else "lazy: rows touched this step only (torch.optim.SparseAdam semantics)" if adam == "rows" else False)}
     if world > 1:
         res["exchange_bytes_per_rank_per_step"] = int(getattr(st, "exchange_bytes", 0))
         res["exchange"] = "touched rows (all-gather + rank-ordered merge)" if sparse else "dense all-reduce"
@@ -316,6 +326,7 @@ def extra_legs(dev, rank, world, steps, sparse, only=None):
             out["cfg4_weak"] = run_leg("cfg4_weak", name, model, opt, 8192, dev, rank, world, steps, items, wts, sparse)
             out["cfg4_strong"] = run_leg("cfg4_strong", name, model, opt, 65536 // world, dev, rank, world, max(steps // 2, 4), items, wts, sparse)
             out["cfg4_weak_with_adam"] = run_leg("cfg4_weak_adam", name, model, opt, 8192, dev, rank, world, max(steps // 2, 4), items, wts, sparse, adam=True)
+            out["cfg4_weak_with_row_adam"] = run_leg("cfg4_weak_row_adam", name, model, opt, 8192, dev, rank, world, max(steps // 2, 4), items, wts, sparse, adam="rows")
         del model
         torch.cuda.empty_cache()
     return out
@@ -792,7 +803,7 @@ def main():
         items = ("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor") if args.loss == "lego" else ("coarse_raycolor",)
         wts = (1.0, 0.0, 0.0) if args.loss == "lego" else (1.0,)
         fstep = FusedTrainStep(model, bg_p, args.rays, batches[0]["cam"]["near"], batches[0]["cam"]["far"], color_loss_items=items,
-                               color_loss_weights=wts, pipeline=args.prefetch)
+                               color_loss_weights=wts, pipeline=args.prefetch, sparse_exchange=not args.dense_allreduce)
         fstep.calibrate(dev_batches)
         flat_dev = [hb.to(dev) for hb, _ in packed]                    # inputs resident in HBM for the headline number
         assert flat_dev[0].numel() == fstep.inbuf.numel()
@@ -804,7 +815,7 @@ def main():
         if fstep is not None:
             loss = fstep(packed=flat_dev[(i + shift) % n_pool])        # one device-to-device copy of a batch, one or two graph launches
             if world > 1:
-                fstep.reduce(sparse=not args.dense_allreduce)
+                fstep.reduce()
             return loss
         # the training loop hands the NEXT batch along: its sampling / neighbour query is queued between this batch's
         # forward and backward (RayShardedStep.prefetch), so every step still runs one full query + forward + backward
@@ -885,7 +896,7 @@ def main():
             stage_ev[j].record(copy_stream)
         loss = fstep()
         if world > 1:
-            fstep.reduce(sparse=not args.dense_allreduce)
+            fstep.reduce()
         buf = loss_host[i % 2]
         buf.copy_(loss.reshape(1), non_blocking=True)          # D2H read of the step's result
         ev = torch.cuda.Event()

@@ -312,7 +312,9 @@ int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, const pn_agg
  *                      gradients of the reference's sampled_* tensors;
  *   scatter_rows == 1: summed per table row g into [T, *] arrays by a sorted segmented reduction (no
  *                      atomics; replaces the index_add_ backward of index_select), rows never referenced
- *                      are zero-filled. */
+ *                      are zero-filled;
+ *   scatter_rows == 2: as 1, but the [T, *] arrays are NOT zero-filled: the caller guarantees they are zero outside the
+ *                      rows this call writes (pn_rows_zero). */
 /* Streams: with the default schedule (pn_set_backward_schedule) part of the work runs on a library-owned stream that is
  * forked from and joined back into `stream` by events, so for the caller everything is still ordered on `stream`: work
  * queued on it afterwards sees every output, and the call never blocks the host. */
@@ -369,6 +371,12 @@ int pn_gather_clamp(const float* table, int64_t n_points, const int32_t* idx, in
  * sync after the backward.  mark: int32[n_points] scratch. */
 int pn_count_touched_rows(const int32_t* sample_pidx, int64_t n, int64_t n_points, int32_t* mark, int32_t* count,
                           void* stream);
+/* Zeroes the table rows named by ids[i * stride], i < n (negative: skipped), of the four [n_points, *] gradient tables: with
+ * pn_agg_backward(scatter_rows = 2) the caller keeps persistent gradient tables that are zero outside the rows a step
+ * touched, and clears those rows before the next step instead of four whole-table memsets (3.1 GB per step at 20 M points).
+ * stride: distance in int32 between ids (1 for touched_ids; F + 8 for the id column of a gathered row buffer). */
+int pn_rows_zero(const int32_t* ids, int64_t n, int64_t stride, int32_t F, float* g_emb, float* g_conf, float* g_dir,
+                 float* g_color, void* stream);
 int pn_rows_pack(const int32_t* ids, int64_t n_ids, int64_t cap, int32_t F, const float* g_emb,
                  const float* g_conf, const float* g_dir, const float* g_color, float* out, void* stream);
 int pn_rows_merge(const float* gathered, int32_t n_ranks, int64_t cap, int32_t F, int64_t n_points, int32_t* slots,
@@ -497,6 +505,21 @@ typedef struct pn_adam_segment {
 
 int pn_adam_step(const pn_adam_segment* segs, int32_t n_segs, double lr, double beta1, double beta2, double eps, int64_t step,
                  void* stream);
+
+/* Lazy (touched-row) Adam for the per-point tables: only rows ids[i * stride] >= 0, i < n, are updated, with the arithmetic of
+ * torch.optim.SparseAdam (moments of untouched rows stay as they are; bias corrections use the global `step`).  An explicit
+ * option with DIFFERENT semantics from the reference's dense torch.optim.Adam (mvs_points_volumetric_model.py:47-100), for
+ * clouds where the dense update (28 B x 39 floats x N per step: 21.8 GB at 20 M points) costs more than the step itself.
+ * Up to four tables [n_points, width] share one id list. */
+typedef struct pn_adam_rows_table {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int32_t width;
+} pn_adam_rows_table;
+int pn_adam_rows(const int32_t* ids, int64_t n, int64_t stride, const pn_adam_rows_table* tabs, int32_t n_tabs, double lr,
+                 double beta1, double beta2, double eps, int64_t step, void* stream);
 
 #ifdef __cplusplus
 }

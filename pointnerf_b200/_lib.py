@@ -60,6 +60,10 @@ class AdamSegment(Structure):
     _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p), ("n", c_int64)]
 
 
+class AdamRowsTable(Structure):
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p), ("width", c_int32)]
+
+
 class LibraryError(RuntimeError):
     pass
 
@@ -117,6 +121,8 @@ def _declare(lib):
         "pn_get_backward_schedule": (c_int, []),
         "pn_count_touched_rows": (c_int, [P, c_int64, c_int64, P, P, P]),
         "pn_rows_pack": (c_int, [P, c_int64, c_int64, c_int32, P, P, P, P, P, P]),
+        "pn_rows_zero": (c_int, [P, c_int64, c_int64, c_int32, P, P, P, P, P]),
+        "pn_adam_rows": (c_int, [P, c_int64, c_int64, POINTER(AdamRowsTable), c_int32, c_double, c_double, c_double, c_double, c_int64, P]),
         "pn_rows_merge": (c_int, [P, c_int32, c_int64, c_int32, c_int64, P, P, P, P, P, P]),
         "pn_ray_dist": (c_int, [P, P, c_int64, c_int32, c_float, c_int32, P, P]),
         "pn_composite_forward": (c_int, [P, P, P, P, P, c_int64, c_int32, c_int32, P, P, P, P, P, P]),

@@ -215,18 +215,26 @@ def agg_forward_raw(call, embedding, color, pdir, conf, weights):
     return decoded, weight_out, saved, saved_bytes
 
 
-def agg_backward_raw(call, tables, weights, saved, saved_bytes, g_decoded, need=(True, True, True, True)):
+def agg_backward_raw(call, tables, weights, saved, saved_bytes, g_decoded, need=(True, True, True, True), out=None):
     """pn_agg_backward.  Returns (g_emb, g_col, g_dir, g_cnf, g_w): per-row gradients ([T,*] with scatter_rows, else
-    [n_slots*K,*]; None where ``need`` is False) and the MLP gradients as views of ONE flat buffer (``call.grad_flat``)."""
+    [n_slots*K,*]; None where ``need`` is False) and the MLP gradients as views of ONE flat buffer (``call.grad_flat``).
+    ``out`` = (g_emb, g_col, g_dir, g_cnf): persistent [T,*] tables the caller keeps zero outside the rows a step touches
+    (pn_rows_zero) - they are written without the whole-table memsets (scatter_rows = 2); ``call.touched_ids`` /
+    ``call.n_touched`` may then be preset persistent buffers too."""
     lib = _lib.lib()
     p = call.params
     embedding, color, pdir, conf = tables
     dev = embedding.device
     rows = call.T if call.scatter_rows else call.n_slots * p.K
-    g_emb = torch.empty((rows, p.F), dtype=torch.float32, device=dev) if need[0] else None
-    g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[1] else None
-    g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
-    g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[3] else None
+    if out is not None:
+        if not call.scatter_rows:
+            raise ValueError("persistent gradient tables need scatter_rows")
+        g_emb, g_col, g_dir, g_cnf = out
+    else:
+        g_emb = torch.empty((rows, p.F), dtype=torch.float32, device=dev) if need[0] else None
+        g_col = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[1] else None
+        g_dir = torch.empty((rows, 3), dtype=torch.float32, device=dev) if need[2] else None
+        g_cnf = torch.empty((rows,), dtype=torch.float32, device=dev) if need[3] else None
     # all MLP gradients live in ONE flat buffer (256-byte aligned segments): ray_shard all-reduces it in place
     sizes = [(w.numel() + 63) // 64 * 64 for w in weights]
     call.flat_tail_off = sum(sizes)       # + a caller-owned tail (ray_shard: bg gradient and row counts ride the same all-reduce)
@@ -241,11 +249,11 @@ def agg_backward_raw(call, tables, weights, saved, saved_bytes, g_decoded, need=
     ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=dev)
     ain = _inputs_struct(call, embedding, color, pdir, conf)
     wst, gst = _weights_struct(weights), _weights_struct(g_w)
-    if call.collect_touched and call.scatter_rows:
+    if call.collect_touched and call.scatter_rows and call.touched_ids is None:
         call.touched_ids = torch.empty(max(call.M, 1), dtype=torch.int32, device=dev)
         call.n_touched = torch.empty(1, dtype=torch.int32, device=dev)
     _lib.check(lib.pn_agg_backward(ctypes.byref(p), ctypes.byref(ain), ctypes.byref(wst), _lib.ptr(g_decoded),
-                                   _lib.ptr(saved), saved_bytes, ctypes.byref(gst), 1 if call.scatter_rows else 0,
+                                   _lib.ptr(saved), saved_bytes, ctypes.byref(gst), (2 if out is not None else 1) if call.scatter_rows else 0,
                                    _lib.ptr(g_emb), _lib.ptr(g_col), _lib.ptr(g_dir), _lib.ptr(g_cnf),
                                    _lib.ptr(call.touched_ids), _lib.ptr(call.n_touched), _lib.ptr(ws),
                                    ws_bytes, _lib.stream()), "pn_agg_backward")

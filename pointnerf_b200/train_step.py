@@ -92,7 +92,7 @@ class FusedTrainStep:
     """
 
     def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
-                 caps=None, graph=True, group=None, pipeline=False, local_only=False):
+                 caps=None, graph=True, group=None, pipeline=False, local_only=False, sparse_exchange=True):
         o = model.opt
         if getattr(o, "wcoord_query", 1) <= 0:
             raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
@@ -129,6 +129,11 @@ class FusedTrainStep:
         self.counts_host = torch.zeros(4, dtype=torch.int32).pin_memory()           # written by every replay (async copy in the graph)
         self.touched_host = torch.zeros(1, dtype=torch.int32).pin_memory()          # distinct table rows the last backward touched
         self.row_cap = None          # ray sharding: rows per rank in the touched-row exchange (calibrate)
+        self._gtab = None            # persistent per-point gradient tables (zero outside the rows the last step touched)
+        self._touched_ids = self._n_touched = None
+        self._gathered = None        # ray sharding: the all-gathered rows of the last exchange (their ids are cleared next step)
+        self.sparse_exchange = bool(sparse_exchange)
+        self._full_zero = self.world > 1 and not self.sparse_exchange      # the dense all-reduce writes every row: whole-table clears
         self._slots = None
         self.launches_per_step = 0
         self._needs_mask = any(w != 0.0 and (n.startswith("ray_masked") or n.startswith("ray_miss")) for n, w in zip(self.items, self.item_weights))
@@ -199,7 +204,22 @@ class FusedTrainStep:
         call.S, call.M = int(q["sample_list"].numel()), int(q["pair_src"].numel())       # the capacities
         call.counts_dev = q["counts"]
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = q["sample_list"], q["pair_start"], q["pair_src"], q["slot_row"]
-        call.collect_touched = self.world > 1
+        call.collect_touched = True
+        # persistent gradient tables, zero outside the rows the previous step (and, sharded, the previous exchange) wrote:
+        # those rows are cleared here instead of four whole-table memsets per step (3.1 GB at 20 M points)
+        gt_ = self._grad_tables(T, int(nps.points_embeding.shape[-1]), int(q["pair_src"].numel()))
+        call.touched_ids, call.n_touched = self._touched_ids, self._n_touched
+        lib = _lib.lib()
+        F_ = int(nps.points_embeding.shape[-1])
+        if self._full_zero:
+            for t_ in gt_:
+                t_.zero_()
+        else:
+            _lib.check(lib.pn_rows_zero(_lib.ptr(self._touched_ids), int(self._touched_ids.numel()), 1, F_, _lib.ptr(gt_[0]), _lib.ptr(gt_[3]),
+                                        _lib.ptr(gt_[2]), _lib.ptr(gt_[1]), _lib.stream()), "pn_rows_zero")
+            if self._gathered is not None:
+                _lib.check(lib.pn_rows_zero(_lib.ptr(self._gathered.view(torch.int32)), int(self._gathered.shape[0]), F_ + 8, F_, _lib.ptr(gt_[0]),
+                                            _lib.ptr(gt_[3]), _lib.ptr(gt_[2]), _lib.ptr(gt_[1]), _lib.stream()), "pn_rows_zero")
         if self.world > 1:                          # bg_color's gradient rides in the tail of the MLP gradient buffer: one all-reduce
             call.flat_tail = (C + 63) // 64 * 64
         weights = tuple(w.detach() for w in agg._weights())
@@ -230,7 +250,9 @@ class FusedTrainStep:
                 nxt = self._query_body()
         g_feat, _, _, g_bg, _, _, _ = _Composite.backward(cctx, lctx.grad, None, None, None, None)
         need = tuple(bool(t.requires_grad) for t in tabs)
-        g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, tables, weights, saved, saved_bytes, g_feat, need)
+        if not all(need):
+            raise NotImplementedError("FusedTrainStep: all four per-point tables are trained (feat / color / dir / conf _grad = 1)")
+        g_emb, g_col, g_dir, g_cnf, g_w = agg_backward_raw(call, tables, weights, saved, saved_bytes, g_feat, need, out=gt_)
         self.call = call
         if self.world > 1 and g_bg is not None:
             tail = call.grad_flat[call.flat_tail_off:call.flat_tail_off + C]
@@ -251,6 +273,29 @@ class FusedTrainStep:
         if prefetch:        # join; the next batch becomes the current one (after everything that read the current buffers)
             torch.cuda.current_stream().wait_stream(self._side)
             self._publish(nxt)
+
+    def _grad_tables(self, T, F, m_cap):
+        if self._gtab is None or self._gtab[0].shape[0] != T or self._touched_ids.numel() != max(m_cap, 1):
+            dev = self.dev
+            self._gtab = (torch.zeros((T, F), dtype=torch.float32, device=dev), torch.zeros((T, 3), dtype=torch.float32, device=dev),
+                          torch.zeros((T, 3), dtype=torch.float32, device=dev), torch.zeros((T,), dtype=torch.float32, device=dev))
+            self._touched_ids = torch.full((max(m_cap, 1),), -1, dtype=torch.int32, device=dev)
+            self._n_touched = torch.zeros(1, dtype=torch.int32, device=dev)
+        return self._gtab
+
+    def _ensure_gathered(self):
+        """Ray sharding, touched-row exchange: the persistent all-gather buffer [world * row_cap, F + 8] (id column = -1)."""
+        if self.world <= 1 or not self.sparse_exchange:
+            return
+        F = int(self.model.neural_points.points_embeding.shape[-1])
+        if F > 56 or not self.row_cap:
+            raise RuntimeError("touched-row exchange: needs calibrate() (row capacity) and point_features_dim <= 56; "
+                               "pass sparse_exchange=False for the dense all-reduce")
+        rows = self.world * self.row_cap
+        if self._gathered is None or tuple(self._gathered.shape) != (rows, F + 8):
+            self._gathered = torch.zeros((rows, F + 8), dtype=torch.float32, device=self.dev)
+            self._gathered.view(torch.int32)[:, 0] = -1
+            self._packed = torch.zeros((self.row_cap, F + 8), dtype=torch.float32, device=self.dev)
 
     # ---- capacities -----------------------------------------------------------------------------------------------------
     def calibrate(self, batches, headroom=1.25, granule=4096):
@@ -299,6 +344,7 @@ class FusedTrainStep:
         side.wait_stream(torch.cuda.current_stream())
         if self._side is None:
             self._side = torch.cuda.Stream()
+        self._ensure_gathered()
         with torch.cuda.stream(side):               # warm-up outside capture: grid build, kernel attributes, library streams
             for _ in range(2):
                 self._publish(self._query_body())
@@ -351,6 +397,7 @@ class FusedTrainStep:
                 raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
             if self._side is None:
                 self._side = torch.cuda.Stream()
+            self._ensure_gathered()
             if not self.pipeline:
                 self._publish(self._query_body())
                 self._sync_masked_count()
@@ -383,6 +430,7 @@ class FusedTrainStep:
         else:
             if self.caps is None:
                 raise RuntimeError("FusedTrainStep: call calibrate(batches) or pass caps=(S_cap, M_cap) first")
+            self._ensure_gathered()
             self._publish(self._query_body())
         self._sync_masked_count()
         self._primed = True
@@ -404,7 +452,7 @@ class FusedTrainStep:
             dist.all_reduce(self.masked_count, op=dist.ReduceOp.SUM, group=self.group)
 
     # ---- ray sharding: gradient exchange after the step ----------------------------------------------------------------
-    def reduce(self, sparse=True):
+    def reduce(self):
         """Sum of every gradient over the ranks of ``group``.  Ranks normalise their losses by GLOBAL counts, so the sum is
         the gradient of the whole batch.  MLP gradients + bg_color: ONE all-reduce of the flat buffer the backward wrote
         them into.  Per-point tables: ``sparse`` - all-gather of the rows this step touched ([id | F + 7 floats], row_cap
@@ -415,19 +463,17 @@ class FusedTrainStep:
         g, call, lib = self.grads, self.call, _lib.lib()
         F = int(g["points_embeding"].shape[-1]) if g.get("points_embeding") is not None else 0
         h_flat = dist.all_reduce(call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        if sparse and F and F <= 56 and call.touched_ids is not None and self.row_cap:
-            if int(self.touched_host[0]) > self.row_cap:         # flagged one step late, like the sample / pair capacities
+        if self.sparse_exchange:
+            # (a step that touched more rows than row_cap loses the surplus rows' gradients: flagged through touched_host,
+            #  the capacity is raised by the caller's next calibrate(); calibrate() sizes it with headroom)
+            if int(self.touched_host[0]) > self.row_cap:
                 self.overflows += 1
-                warnings.warn("FusedTrainStep: %d touched rows exceed the exchange capacity %d: grown" % (int(self.touched_host[0]), self.row_cap))
-                t = torch.tensor([int(int(self.touched_host[0]) * 1.25) + 4096], dtype=torch.int64, device=self.dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
-                self.row_cap = int(t.item())
+                warnings.warn("FusedTrainStep: %d touched rows exceed the exchange capacity %d" % (int(self.touched_host[0]), self.row_cap))
             cap = self.row_cap
-            packed = torch.empty((cap, F + 8), dtype=torch.float32, device=self.dev)
+            packed, gathered = self._packed, self._gathered
             _lib.check(lib.pn_rows_pack(_lib.ptr(call.touched_ids), int(call.touched_ids.numel()), cap, F, _lib.ptr(g["points_embeding"]),
                                         _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
                                         _lib.ptr(packed), _lib.stream()), "pn_rows_pack")
-            gathered = torch.empty((self.world * cap, F + 8), dtype=torch.float32, device=self.dev)
             dist.all_gather_into_tensor(gathered, packed, group=self.group)
             T = int(g["points_embeding"].shape[0])
             if self._slots is None or self._slots.numel() != T * self.world:
@@ -474,21 +520,24 @@ def sharded_gradient_check(model, bg_color, batch, items, weights, group=None):
     single.calibrate([batch], headroom=1.0, granule=256)
     single(batch["cam"], batch["raydir"], batch["gt"], uni)
     whole = flat(single)
-    st = FusedTrainStep(model, bg_color, hi - lo, near, far, items, weights, graph=True, group=group)
-    st.calibrate([shard], headroom=1.0, granule=256)
     res = {}
     for mode in ("sparse", "dense"):
-        st(shard["cam"], shard["raydir"], shard["gt"], shard["uniform"])
-        st.reduce(sparse=(mode == "sparse"))
+        st = FusedTrainStep(model, bg_color, hi - lo, near, far, items, weights, graph=True, group=group, sparse_exchange=(mode == "sparse"))
+        st.calibrate([shard], headroom=1.0, granule=256)
+        for _ in range(2):          # twice: the second step runs on gradient tables the first one (and its exchange) wrote
+            st(shard["cam"], shard["raydir"], shard["gt"], shard["uniform"])
+            st.reduce()
         res[mode] = flat(st)
+        if mode == "sparse":
+            row_cap, overflows = int(st.row_cap or 0), st.overflows
     scale = float(whole.abs().max())
     e_sd = float((res["sparse"] - res["dense"]).abs().max()) / scale
     e_sw = float((res["sparse"] - whole).abs().max()) / scale
     gathered = [torch.empty_like(res["sparse"]) for _ in range(world)]
     dist.all_gather(gathered, res["sparse"], group=group)
     same = all(torch.equal(t, gathered[0]) for t in gathered)
-    ok = same and e_sd <= (0.0 if world == 2 else 1e-6) and e_sw <= 1e-4 and st.overflows == 0
+    ok = same and e_sd <= (0.0 if world == 2 else 1e-6) and e_sw <= 1e-4 and overflows == 0
     flag = torch.tensor([1 if ok else 0], device=whole.device)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
     return {"world": world, "rays": R, "replicas_identical": bool(same), "sparse_vs_dense": e_sd, "sharded_vs_single": e_sw,
-            "touched_rows_per_rank_cap": int(st.row_cap or 0), "loss_items": list(items), "ok": bool(int(flag))}
+            "touched_rows_per_rank_cap": row_cap, "loss_items": list(items), "ok": bool(int(flag))}

@@ -42,3 +42,37 @@ def test_adam_skips_missing_grads_and_views(cuda_dev):
     assert torch.allclose(p, torch.full_like(p, 0.9), atol=1e-6) and bool((q == 1).all()) and q not in opt.state
     opt.zero_grad()
     assert p.grad is None
+
+
+def test_row_adam_equals_torch_sparse_adam(cuda_dev):
+    """pn_adam_rows (lazy, touched-row Adam: an OPTION, not the reference's optimiser) against torch.optim.SparseAdam on the
+    same sparse gradients: parameters and both moments, rows outside the id list untouched, over several steps."""
+    from pointnerf_b200.optim import RowAdam
+    N = 5000
+    g = torch.Generator().manual_seed(3)
+    widths = (32, 1, 3, 3)
+    mine = [torch.nn.Parameter(torch.randn(1, N, w, generator=g).to(cuda_dev)) for w in widths]
+    ref = [torch.nn.Parameter(p.detach().clone().reshape(N, w)) for p, w in zip(mine, widths)]
+    opt = RowAdam(mine, lr=2e-3, betas=(0.9, 0.999))
+    ropt = torch.optim.SparseAdam(ref, lr=2e-3, betas=(0.9, 0.999))
+    for it in range(6):
+        ids = torch.unique(torch.randint(0, N, (400,), generator=g)).to(torch.int32)
+        padded = torch.cat([ids, torch.full((37,), -1, dtype=torch.int32)]).to(cuda_dev)      # the backward's list is -1 padded
+        for p, r, w in zip(mine, ref, widths):
+            dense = torch.zeros(N, w)
+            dense[ids.long()] = torch.randn(len(ids), w, generator=g)
+            p.grad = dense.reshape(p.shape).to(cuda_dev)
+            r.grad = torch.sparse_coo_tensor(ids.long()[None].to(cuda_dev), dense[ids.long()].to(cuda_dev), (N, w)).coalesce()
+        before = [p.detach().clone() for p in mine]
+        opt.step(padded)
+        ropt.step()
+        untouched = torch.ones(N, dtype=torch.bool)
+        untouched[ids.long()] = False
+        for p, r, b, w in zip(mine, ref, before, widths):
+            assert torch.equal(p.detach().reshape(N, w)[untouched], b.reshape(N, w)[untouched])
+            err = float((p.detach().reshape(N, w) - r.detach()).abs().max())
+            assert err <= 2e-7 * float(r.detach().abs().max()), (it, w, err)
+    for st, r in zip(opt.state, ref):
+        rs = ropt.state[r]
+        assert float((st["exp_avg"].reshape(rs["exp_avg"].shape) - rs["exp_avg"]).abs().max()) <= 1e-7 * float(rs["exp_avg"].abs().max())
+        assert float((st["exp_avg_sq"].reshape(rs["exp_avg_sq"].shape) - rs["exp_avg_sq"]).abs().max()) <= 1e-7 * float(rs["exp_avg_sq"].abs().max())
