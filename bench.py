@@ -646,6 +646,77 @@ def frustum_bench(dev):
     return res
 
 
+def reference_gpu_bench(model, opt, batch_dev, dev, reps=5):
+    """The reference's own querier kernels (kernel string -> sm_100a cubin, driver API: oracle/ref_gpu.py) beside the
+    product's query on the same batch, stage by stage (CUDA events, mean of `reps` after one warm-up).  The reference
+    rebuilds its grid on every forward (:626) and materialises the [R, D, 3] candidate positions; both are in its column."""
+    import ctypes
+    from oracle import ref_gpu
+    from pointnerf_b200 import query as pq
+    if not ref_gpu.available(int(opt.K)):
+        return {"unavailable": "oracle/_ref/ref_querier_sm100a_K%d.cubin not built" % int(opt.K)}
+    nps = model.neural_points
+    xyz = nps.xyz.detach()
+    q = nps.querier
+    raydir, campos, near, far, uni = batch_dev["raydir"], batch_dev["cam"]["campos"], batch_dev["cam"]["near"], batch_dev["cam"]["far"], batch_dev["uniform"]
+    grid = q.grid_for(xyz)
+    hp = grid.hp
+    n_layers = (int(opt.kernel_size[0]) + 1) // 2
+
+    def ev():
+        return torch.cuda.Event(enable_timing=True)
+    ours = {"grid_build_ms": 0.0, "depths_ms": 0.0, "ray_sample_ms": 0.0, "knn_query_ms": 0.0}
+    for it in range(reps + 1):
+        e = [ev() for _ in range(5)]
+        e[0].record()
+        g2 = pq.VoxelGrid(xyz, hp, opt.P, opt.max_o)
+        e[1].record()
+        ts = pq.middle_point_ts(raydir, opt.z_depth_dim, near, far, jitter=0.3 if opt.is_train > 0 else 0.0, uniform=uni)
+        e[2].record()
+        loc_w, hit = pq.ray_sample(g2, campos[0].contiguous(), raydir[0].contiguous(), ts.reshape(-1, ts.shape[-1]).contiguous(), opt.SR)
+        e[3].record()
+        pidx, ray_any = pq.knn_query(g2, xyz, loc_w, hit, opt.K, n_layers, float(hp["radius_limit2"]))
+        e[4].record()
+        torch.cuda.synchronize()
+        if it:
+            for k, a, b in (("grid_build_ms", 0, 1), ("depths_ms", 1, 2), ("ray_sample_ms", 2, 3), ("knn_query_ms", 3, 4)):
+                ours[k] += e[a].elapsed_time(e[b]) / reps
+    ref = ref_gpu.ReferenceGpuQuerier(opt, hp, dev)
+    xyz1 = xyz[None].contiguous()
+    rt = {}
+    raypos_ms = 0.0
+    for it in range(reps + 1):
+        a, b = ev(), ev()
+        a.record()
+        raypos = (campos[:, None, None, :] + raydir[:, :, None, :] * ts[:, :, :, None]).contiguous()      # diff_ray_marching.py:387
+        b.record()
+        t = {} if it == 0 else rt
+        pidx_r, loc_r, mask_r = ref.query(xyz1, raypos, timing=t)
+        if it:
+            raypos_ms += a.elapsed_time(b) / reps
+    rt = {k: v / reps for k, v in rt.items()}
+    rt["raypos_ms"] = raypos_ms
+    # agreement (sets: the reference's bucket order and slot-0 voxel depend on the hardware's atomic order)
+    both = (ray_any > 0) & (mask_r[0] > 0)
+    rows = (torch.cumsum((mask_r[0] > 0).long(), 0) - 1)[both]
+    so, sr = torch.sort(pidx[both], dim=-1)[0], torch.sort(pidx_r[0][rows], dim=-1)[0]
+    samp = (so >= 0).any(-1) | (sr >= 0).any(-1)
+    same = (so == sr).all(-1)
+    o_total, r_total = sum(ours.values()), sum(rt.values())
+    return {"rays": int(raydir.shape[1]), "points": int(xyz.shape[0]),
+            "ours_ms": {k: round(v, 4) for k, v in ours.items()}, "ours_total_ms": round(o_total, 4),
+            "ours_per_step_ms_grid_cached": round(o_total - ours["grid_build_ms"], 4),
+            "reference_kernels_ms": {k: round(v, 4) for k, v in rt.items()}, "reference_total_ms": round(r_total, 4),
+            "speedup_whole_query_reference_rebuilds_grid_each_forward": round(r_total / max(o_total - ours["grid_build_ms"], 1e-9), 2),
+            "speedup_like_for_like_with_grid_build": round(r_total / max(o_total, 1e-9), 2),
+            "knn_kernel_speedup": round(rt["knn_query_ms"] / max(ours["knn_query_ms"], 1e-9), 2),
+            "ray_mask_agreement": round(float(((ray_any > 0) == (mask_r[0] > 0)).float().mean()), 6),
+            "sample_positions_identical": bool(torch.equal(loc_w[both], loc_r[0][rows])),
+            "neighbour_sets_identical_frac": round(float(same[samp].float().mean()), 6),
+            "note": "reference = its own kernel string compiled by nvcc for sm_100a and launched with its geometry (%d threads per block) through the driver API; "
+                    "sets, not slot order, are compared: its atomics resolve in hardware order" % ref.thr}
+
+
 def psnr_vs_oracle(dev):
     """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
     oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
@@ -1077,6 +1148,14 @@ def main():
         _phase("maintenance kernels")
         maint = maintenance_bench(model, opt, dev_batches[0], bg_p.detach(), dev)
 
+    ref_gpu_res = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        _phase("reference querier kernels on the GPU")
+        try:
+            ref_gpu_res = reference_gpu_bench(model, opt, dev_batches[0], dev)
+        except Exception as e:
+            ref_gpu_res = {"error": repr(e)}
+
     frustum = None
     if rank == 0 and world == 1 and not args.no_sweep:
         _phase("frustum querier (wcoord_query = 0)")
@@ -1118,7 +1197,7 @@ def main():
                         "host_queue_ms_per_step": round(e2e_host_ms - e2e_wait_ms, 4), "host_wait_ms_per_step": round(e2e_wait_ms, 4)},
                 "host_queue_ms_per_step": round(host_ms, 4),
                 "roofline": roof, "cpu_baseline": cpu, "stages_ms_per_step": stages, ("frame_%dx%d" % (frame["w"], frame["h"]) if frame else "frame_800x800"): frame,
-                "sharded_gradient_check": grad_check, "legs": legs,
+                "sharded_gradient_check": grad_check, "legs": legs, "reference_gpu_kernels": ref_gpu_res,
                 "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint, "frustum_querier_wcoord0": frustum}
         _emit(line)
     if world > 1:

@@ -169,9 +169,29 @@ def _build_one(ref_py, out_so, launchers, force):
     return out_so
 
 
+def build_gpu(K: int, force: bool = False) -> str:
+    """The SAME kernel string, unmodified (``KN`` = K as the reference splices it, :116), compiled for the GPU:
+    ``nvcc -arch=sm_100a -cubin`` -> oracle/_ref/ref_querier_sm100a_K<K>.cubin, loaded by oracle/ref_gpu.py through the
+    driver API (what pycuda's SourceModule does).  The reference's GPU-side baseline on the B200."""
+    out = os.path.join(OUT_DIR, "ref_querier_sm100a_K%d.cubin" % K)
+    if os.path.isfile(out) and not force:
+        return out
+    os.makedirs(OUT_DIR, exist_ok=True)
+    with tempfile.TemporaryDirectory() as tmp:
+        cu = os.path.join(tmp, "ref_querier.cu")
+        with open(cu, "w") as f:
+            f.write(extract_kernel_source(K))
+        r = subprocess.run(["nvcc", "-arch=sm_100a", "-O3", "-cubin", "-w", "-o", out, cu], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed on the reference kernel string:\n" + r.stderr[-2000:])
+    return out
+
+
 def build(force: bool = False) -> str:
-    """Builds both libraries; returns the world-coordinate one (the hot path's)."""
+    """Builds both host libraries and the GPU cubins; returns the world-coordinate host library (the hot path's oracle)."""
     _build_one(REF_PY_FRUSTUM, OUT_SO_FRUSTUM, LAUNCHERS_FRUSTUM, force)
+    for K in (8, 16):
+        build_gpu(K, force)
     return _build_one(REF_PY, OUT_SO, LAUNCHERS, force)
 
 
