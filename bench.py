@@ -717,36 +717,50 @@ def reference_gpu_bench(model, opt, batch_dev, dev, reps=5):
                     "sets, not slot order, are compared: its atomics resolve in hardware order" % ref.thr}
 
 
-def psnr_vs_oracle(dev):
-    """PSNR delta (BASELINE.json metric, third item) on the `tiny` scene's full 48x48 frame: our render against the CPU
+def psnr_vs_oracle(dev, name="cfg1", chunk=14400):
+    """PSNR delta (BASELINE.json metric, third item) on a full frame of BASELINE configs[0] (`cfg1`: 200 K points, 400x400
+    view, 40 samples per ray, K = 8 - the configuration whose CPU path BASELINE.json names): our render against the CPU
     oracle's render of the same scene, and both against a synthetic ground truth (the oracle's render of the scene with
-    perturbed embeddings).  Part of the cpu_baseline leg (the oracle is the checker here, never the thing shipped)."""
-    from oracle import pipeline_ref
+    perturbed embeddings).  The oracle's frame time is configs[0]'s own number (forward render on the host cores, chunked
+    like run/train_ft.py:260-261).  Part of the cpu_baseline leg (the oracle is the checker here, never the thing shipped)."""
+    from oracle import pipeline_ref, querier_ref
     from pointnerf_b200 import synthetic as syn
-    opt, tables = syn.make_scene("tiny")
+    opt, tables = syn.make_scene(name)
     opt = copy.copy(opt)
     opt.is_train = 0
-    cam = syn.make_camera("tiny")
+    cam = syn.make_camera(name)
     raydir, _ = syn.make_rays(cam, syn.all_pixels(cam))
     model = make_model(opt, tables, dev)
     g = torch.Generator().manual_seed(5)
     bg = torch.rand(int(opt.shading_color_channel_num), generator=g)
     sd = {k: v.detach().cpu() for k, v in model.aggregator.state_dict().items()}
+    backend = "ref" if querier_ref.have_backend("ref") else "port"
     ours = model.render_frame(cam["campos"].to(dev), raydir.to(dev), bg.to(dev), cam["camrotc2w"].to(dev), cam["near"], cam["far"],
-                              chunk=1024)["coarse_raycolor"].cpu()
-    ref = pipeline_ref.run(opt, tables, cam, raydir, bg, sd, need_grads=False)["coarse_raycolor"]
+                              chunk=65536)["coarse_raycolor"].cpu()
+
+    def oracle_frame(tb):
+        t0 = time.perf_counter()
+        parts = [pipeline_ref.run(opt, tb, cam, raydir[:, s:s + chunk], bg, sd, need_grads=False, backend=backend)["coarse_raycolor"]
+                 for s in range(0, raydir.shape[1], chunk)]
+        return torch.cat(parts, dim=1), time.perf_counter() - t0
+    ref, cpu_s = oracle_frame(tables)
     t2 = dict(tables)
     t2["points_embeding"] = tables["points_embeding"] + 0.05 * torch.randn(tables["points_embeding"].shape, generator=g)
-    gt = pipeline_ref.run(opt, t2, cam, raydir, bg, sd, need_grads=False)["coarse_raycolor"]
+    gt, _ = oracle_frame(t2)
 
     def psnr(a, b):
         mse = float(((a.double() - b.double()) ** 2).mean())
         peak = float(gt.abs().max())
         return 10.0 * np.log10(peak * peak / max(mse, 1e-300))
     po, pr = psnr(ours, gt), psnr(ref, gt)
-    return {"scene": "tiny, full %dx%d frame, C=%d feature channels, peak = max|gt|" % (cam["h"], cam["w"], ref.shape[-1]),
+    del model
+    return {"scene": "%s (BASELINE configs[0]): %d points, full %dx%d frame, SR=%d K=%d, C=%d feature channels, peak = max|gt|"
+                     % (name, tables["xyz"].shape[0], cam["h"], cam["w"], opt.SR, opt.K, ref.shape[-1]),
             "ours_vs_oracle_db": round(psnr(ours, ref), 2), "ours_vs_gt_db": round(po, 4), "oracle_vs_gt_db": round(pr, 4),
-            "delta_db": round(abs(po - pr), 6), "max_abs_diff": float((ours - ref).abs().max())}
+            "delta_db": round(abs(po - pr), 6), "max_abs_diff": float((ours - ref).abs().max()),
+            "max_rel_to_scale": float((ours - ref).abs().max() / ref.abs().max()),
+            "cpu_forward_s_per_frame": round(cpu_s, 2), "cpu_cores": torch.get_num_threads(),
+            "cpu_kind": "reference querier kernels (host build) + port of the torch aggregator / ray_march, %d-ray chunks" % chunk}
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -784,7 +798,9 @@ def dominant_kernel_roofline(_lib, dev, M, peak, peaks, N=256, K=256, reps=20):
         pass
     return {"kernel": "gemm_nt_img2_kernel (aggregator MLP forward / data-gradient GEMM, CTA pairs, 3xTF32)", "bound": "tensor",
             "achieved": round(ach, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(ach / peak, 5), "traffic": traffic,
-            "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (%s); 3xTF32 ceiling = peak / 6" % peaks["source"],
+            "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst: the kernel is timed alone) (%s); 3xTF32 ceiling = peak / 6" % peaks["source"],
+            "traffic_source": "profiles/r01_traffic.json (one ncu --set full capture of this kernel at M = 134 826), scaled by M: not a measurement of this run",
+            "frac_of_3xtf32_ceiling": round(ach / (peak / 6.0), 4),
             "launch_us": round(us, 2), "flops_per_launch": fl, "algorithmic_bytes_per_launch": int(4 * (M * K + M * N + 2 * N * K)),
             "shape": [M, N, K], "mma_passes_per_product": 3}
 
@@ -800,7 +816,7 @@ def main():
                     help="do not queue the next batch's sampling/query between this batch's forward and backward")
     ap.add_argument("--workload", default="cfg2")
     ap.add_argument("--rays", type=int, default=4096, help="rays per batch per GPU")
-    ap.add_argument("--cpu-rays", type=int, default=1024, help="rays per CPU-oracle step (bounded sample)")
+    ap.add_argument("--cpu-rays", type=int, default=0, help="rays per CPU step of the reference arm (0 = whole batches: the same workload as our arm)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stages", action="store_true")
     ap.add_argument("--no-frame", action="store_true", help="skip the full-frame inference timing (ms per 800x800 frame)")
@@ -832,15 +848,18 @@ def main():
         agg = tp.AggregatorPort(opt)
         with torch.no_grad():
             agg.alpha_branch[0].bias.fill_(60.0)
-        v, spstep, backend = cpu_oracle_steps(opt, tables, batches, bg, agg.state_dict(), args.cpu_rays, args.steps, args.warmup)
-        sample = ("%d of the %d rays of each batch per step (bounded sample), fwd+bwd, %s querier + torch aggregator/ray_march restatement"
-                  % (args.cpu_rays, args.rays, "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port"))
+        cpu_rays = args.cpu_rays if args.cpu_rays > 0 else args.rays
+        v, spstep, backend = cpu_oracle_steps(opt, tables, batches, bg, agg.state_dict(), cpu_rays, args.steps, args.warmup)
+        sample = ("%s, fwd+bwd, %d steps; querier = %s, aggregator / ray_march = torch restatement of the reference modules (pinned to them bit for bit, tests/test_oracle.py)"
+                  % ("whole %d-ray batches of the workload" % args.rays if cpu_rays == args.rays else "%d of the %d rays of each batch per step" % (cpu_rays, args.rays),
+                     args.steps, "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port"))
         line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "%s: %d-point neural cloud, %d rays/batch, SR=%d, K=%d, D=%d, fwd+bwd" %
                            (args.workload, tables["xyz"].shape[0], args.rays, opt.SR, opt.K, opt.z_depth_dim)},
                 "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
+                                 "kind_detail": "reference querier kernels (host build of its own CUDA string) + port of its torch aggregator / ray_march" if backend == "ref" else "port",
                                  "sample": sample},
                 "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         _emit(line)
@@ -1105,10 +1124,10 @@ def main():
         agg_ms = (tot.get("agg_forward", 0.0) + tot.get("agg_backward", 0.0)) / n_stage_steps
         fl = agg_flops(opt, counts["S"], counts["M"], backward=True)
         achieved = fl / (agg_ms * 1e-3) / 1e12 if agg_ms > 0 else 0.0
-        peak = peaks["bf16_tflops_sustained"]
+        peak = peaks["bf16_tflops_sustained"]       # whole aggregator, timed inside the step: sustained peak
         # dominant kernel: the pair-level NT GEMM of the MLP (14 of the 21 GEMM launches of a step), timed live on its own
         # at the workload's shape (M = mean valid pairs of the batches, N = K = 256; operands 2 x 138 MB > L2)
-        dom = dominant_kernel_roofline(_lib, dev, int(round(counts["M"])), peak, peaks)
+        dom = dominant_kernel_roofline(_lib, dev, int(round(counts["M"])), peaks["bf16_tflops"], peaks)     # timed alone: burst peak
         roof = dict(dom)
         roof["aggregator"] = {"kernels": "pn_agg_forward + pn_agg_backward (21 GEMM launches + gather / reduce / scatter kernels)",
                               "achieved": round(achieved, 3), "unit": "TFLOP/s", "frac": round(achieved / peak, 5),
@@ -1138,6 +1157,7 @@ def main():
         cpu_steps = 6
         v, spstep, backend = cpu_oracle_steps(opt, tables, batches, bg, sd, args.rays, cpu_steps, 1)
         cpu = {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port" if backend == "port" else "reference",
+               "kind_detail": "reference querier kernels (host build of its own CUDA string) + port of its torch aggregator / ray_march" if backend == "ref" else "port",
                "sample": "%d steps of %d rays (whole batches of the workload) after 1 warm-up step, fwd+bwd, %.2f s/step; querier = %s, aggregator/ray_march = torch restatement of the reference modules"
                          % (cpu_steps, args.rays, spstep,
                             "reference kernels compiled for the host (oracle/_ref)" if backend == "ref" else "C port")}
