@@ -320,6 +320,23 @@ def extra_legs(dev, rank, world, steps, sparse, only=None):
         opt, tables = build_scene_on_device(name, dev, rank, world)
         model = make_model(opt, tables, dev)
         del tables
+        if rank == 0:       # grid (re)build of this cloud: what a prune / grow pass pays before the next query
+            from pointnerf_b200 import query as pq
+            nps_ = model.neural_points
+            g0 = nps_.querier.grid_for(nps_.xyz.detach())
+            ms_ = []
+            for _ in range(4):
+                a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a_.record()
+                pq.VoxelGrid(nps_.xyz.detach(), g0.hp, opt.P, opt.max_o)
+                b_.record()
+                torch.cuda.synchronize()
+                ms_.append(a_.elapsed_time(b_))
+            N_, V_ = int(nps_.xyz.shape[0]), int(g0.V)
+            algo = 32 * N_ + 16 * V_ + V_ // 8
+            out[name + "_grid_build"] = {"points": N_, "cells": V_, "ms": round(min(ms_[1:]), 4), "algorithmic_bytes": algo,
+                                         "GB/s": round(algo / (min(ms_[1:]) * 1e-3) / 1e9, 1),
+                                         "note": "pn_grid_build incl. its allocations (kernel time by CUDA events); the reference rebuilds its grid every forward"}
         if name == "cfg3":
             out["cfg3_weak"] = run_leg("cfg3_weak", name, model, opt, 4096, dev, rank, world, steps, items, wts, sparse)
         else:

@@ -326,34 +326,48 @@ class NeuralPointsRayMarching(nn.Module):
         return plan
 
     @torch.no_grad()
-    def render_frame(self, campos, raydir, bg_color, camrotc2w, near, far, chunk=65536, keys=("coarse_raycolor",), side_stream=True):
+    def render_frame(self, campos, raydir, bg_color, camrotc2w, near, far, chunk=65536, keys=("coarse_raycolor",), side_stream=True,
+                     pixel_idx=None, h=None, w=None, intrinsic=None):
         """Full-frame inference: the chunk loop of run/train_ft.py:test (:284-340, ``chunk_size = random_sample_size**2``
         rays per ``model.test()`` call) over raydir [1,R,3], forward only.  The sampling / neighbour query / work lists of
         chunk i+1 run on a second stream under the aggregator of chunk i (they are small latency-bound kernels, ~20 % of a
         frame when serialised), so neither they nor the (S, M) read-back of a chunk sit on the critical path; chunks reuse
         the same activation buffers through the caching allocator (nothing is kept for a backward).
-        Returns {key: [1,R,...]} for ``keys`` (any of the ``forward`` outputs)."""
-        R = int(raydir.shape[1])
+        Returns {key: [1,R,...]} for ``keys`` (any of the ``forward`` outputs).
+        Perspective-frustum querier (``wcoord_query = 0``, the DTU feed-forward scripts): rays are addressed by
+        ``pixel_idx`` int32 [1,R,2] (+ ``h``, ``w``, ``intrinsic``) instead of ``raydir``; the view's grid is a function of
+        the camera only and is rebuilt per chunk by the querier (0.13 ms at DTU size)."""
+        frustum = getattr(self.opt, "wcoord_query", 1) <= 0
+        if frustum and (pixel_idx is None or h is None or w is None or intrinsic is None):
+            raise NotImplementedError("wcoord_query = 0 renders by pixel: pass pixel_idx, h, w and intrinsic")
+        R = int(pixel_idx.shape[1]) if frustum else int(raydir.shape[1])
+        dev0 = pixel_idx.device if frustum else raydir.device
         if R == 0:
-            return {k: torch.zeros((1, 0, 0), device=raydir.device) for k in keys}
+            return {k: torch.zeros((1, 0, 0), device=dev0) for k in keys}
         starts = list(range(0, R, int(chunk)))
         outs = {k: [] for k in keys}
         main = torch.cuda.current_stream()
         side = None
-        if side_stream and raydir.is_cuda:
+        if side_stream and dev0.type == "cuda":
             side = getattr(self, "_frame_stream", None)
             if side is None:
                 side = self._frame_stream = torch.cuda.Stream()
         xp = _query.w2pers(self.neural_points.xyz.detach(), camrotc2w[0], campos[0])
 
+        def one(s):
+            if frustum:
+                return self.sample(campos, None, camrotc2w, near, far, xyz_pers=xp, pixel_idx=pixel_idx[:, s:s + chunk].contiguous(), h=h, w=w,
+                                   intrinsic=intrinsic)
+            return self.sample(campos, raydir[:, s:s + chunk], camrotc2w, near, far, xyz_pers=xp)
+
         def sample(s):
             if side is None:
-                return self.sample(campos, raydir[:, s:s + chunk], camrotc2w, near, far, xyz_pers=xp), None
+                return one(s), None
             # allocations from the side stream's pool only happen after this wait: every main-stream kernel that used the
             # plans freed so far has been queued before it
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                plan = self.sample(campos, raydir[:, s:s + chunk], camrotc2w, near, far, xyz_pers=xp)
+                plan = one(s)
                 done = torch.cuda.Event()
                 done.record(side)
             return plan, done
@@ -362,7 +376,8 @@ class NeuralPointsRayMarching(nn.Module):
             nxt, nxt_done = sample(starts[i + 1]) if i + 1 < len(starts) else (None, None)
             if done is not None:
                 main.wait_event(done)
-            o = self.forward(campos, raydir[:, s:s + chunk], bg_color=bg_color, camrotc2w=camrotc2w, near=near, far=far, plan=plan)
+            o = self.forward(campos, None if frustum else raydir[:, s:s + chunk], bg_color=bg_color, camrotc2w=camrotc2w, near=near, far=far,
+                             plan=plan)
             for k in keys:
                 outs[k].append(o[k])
             plan, done = nxt, nxt_done

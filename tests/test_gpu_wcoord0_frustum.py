@@ -205,3 +205,34 @@ def test_frustum_fused_equals_seams_with_jitter(cuda_dev):
     with torch.no_grad():
         o0 = model(cam["campos"].to(dev), None, fused=True, **kw)
     assert rel_err(o0["coarse_raycolor"], of["coarse_raycolor"]) > 1e-5      # the jitter did move the samples
+
+
+def test_render_frame_with_frustum_querier_equals_one_forward(cuda_dev):
+    """render_frame on the perspective-frustum querier (rays addressed by pixel index, chunked, query of chunk i + 1 on the
+    side stream): same image as one un-chunked forward over all pixels."""
+    opt, xyz, cam, pix = syn.frustum_case("dtu")
+    opt = copy.copy(opt)
+    opt.is_train = 0
+    _, tables = syn.make_scene("tiny")
+    dev = cuda_dev
+    pix = pix[:, :900]
+    torch.manual_seed(0)
+    model = NeuralPointsRayMarching(opt, device=dev)
+    with torch.no_grad():
+        model.aggregator.alpha_branch[0].bias.fill_(60.0)
+    model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                                   tables["points_conf"], Rw2c=tables["Rw2c"])
+    bg = torch.rand(opt.shading_color_channel_num, generator=torch.Generator().manual_seed(4)).to(dev)
+    kw = dict(h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"])
+    with torch.no_grad():
+        whole = model(cam["campos"].to(dev), None, bg_color=bg, camrotc2w=cam["camrotc2w"].to(dev), pixel_idx=pix.to(dev), near=cam["near"],
+                      far=cam["far"], **kw)
+        for side in (False, True):
+            fr = model.render_frame(cam["campos"].to(dev), None, bg, cam["camrotc2w"].to(dev), cam["near"], cam["far"], chunk=256,
+                                    keys=("coarse_raycolor", "ray_mask", "coarse_point_opacity"), side_stream=side, pixel_idx=pix.to(dev), **kw)
+            assert torch.equal(fr["ray_mask"], whole["ray_mask"])
+            assert torch.equal(fr["coarse_raycolor"], whole["coarse_raycolor"])
+            assert torch.equal(fr["coarse_point_opacity"], whole["coarse_point_opacity"])
+    assert int((whole["ray_mask"] > 0).sum()) > 100
+    with pytest.raises(NotImplementedError):
+        model.render_frame(cam["campos"].to(dev), torch.zeros(1, 10, 3, device=dev), bg, cam["camrotc2w"].to(dev), cam["near"], cam["far"])
