@@ -714,8 +714,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         const uint32_t sA_u32 = tc::smem_u32(smA);
         float4 ra[8], rb[8];
-        auto load = [&](int L, float4 (&r)[8]) {
+        // Returns false when the load is DEFERRED: in the odd last tile of a pair the layers of one tile follow each other
+        // directly, so the rows chunk L needs are stored by an epilogue that still waits for chunks this very thread has in
+        // its other register set - blocking here (a prefetch, four chunks ahead) would deadlock; the load is then done at
+        // the start of the chunk's own step, when everything before it is staged.  In full groups the dependency is two
+        // slots back (all its chunks precede every pending one): the prefetch may wait.
+        auto load = [&](int L, float4 (&r)[8], bool force) -> bool {
             const ChainPos p = chain_locate(g, L, full);
+            if (p.layer > 0 && p.s >= full * 2 * NL && !force) return false;
             const ChainLayerDev& ly = g.l[p.layer];
             const int ptile = pair + p.j * n_pairs;
             const int64_t m0 = (int64_t)ptile * (2 * TBM) + (int64_t)rank * TBM;
@@ -737,8 +743,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
                     r[i] = (kok && m < Mrows) ? __ldg(reinterpret_cast<const float4*>(ly.A + m * ly.lda + gk)) : z4;
                 }
             }
+            return true;
         };
-        auto step = [&](int L, float4 (&cur)[8]) {
+        auto step = [&](int L, float4 (&cur)[8], bool& have) {
+            if (!have) have = load(L, cur, true);
             const int sa = L % NS2;
             tc::mbar_wait(&emptyA[sa], ((L / NS2) & 1) ^ 1);
             const uint32_t st = sA_u32 + (uint32_t)(sa * A_STAGE);
@@ -750,13 +758,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             tc::fence_proxy_async();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&fullA[sa]);
-            if (L + 4 < total_chunks) load(L + 4, cur);
+            have = (L + 4 < total_chunks) ? load(L + 4, cur, false) : false;
         };
-        if (grp < total_chunks) load(grp, ra);
-        if (grp + 2 < total_chunks) load(grp + 2, rb);
+        bool have_a = false, have_b = false;
+        if (grp < total_chunks) have_a = load(grp, ra, false);
+        if (grp + 2 < total_chunks) have_b = load(grp + 2, rb, false);
         for (int L = grp; L < total_chunks; L += 4) {
-            step(L, ra);
-            if (L + 2 < total_chunks) step(L + 2, rb);
+            step(L, ra, have_a);
+            if (L + 2 < total_chunks) step(L + 2, rb, have_b);
         }
     } else if (warp == 8) {
         if (lane == 0 && rank == 0) {
