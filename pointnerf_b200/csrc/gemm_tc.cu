@@ -604,10 +604,12 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------------
 // NT CHAIN on CTA pairs: several layers of the MLP whose rows depend only on the same rows of the previous layer
 // (H1 = f(X1 W1a), X3 = f(H1 W1b), H3 = f(X3 W3a), H4 = f(H3 W3b); the colour branch; the data-gradient chains) run inside
-// ONE persistent kernel.  A CTA pair owns row tiles of 256 rows and walks, per GROUP of two of its tiles A and B, the slots
-// (A, layer 0), (B, layer 0), (A, layer 1), (B, layer 1), ...: the epilogue of a slot drains one half of TMEM while the
-// MMAs of the next slot (the other tile) fill the other half, exactly as tile i / tile i + 1 of the single-layer kernel,
-// and by the time (A, layer l + 1) is staged the epilogue of (A, layer l) has stored its rows.  Every CTA re-reads only the
+// ONE persistent kernel.  A CTA pair owns row tiles of 256 rows and walks, per GROUP of four of its tiles A..D, the slots
+// (A, layer 0), (B, 0), (C, 0), (D, 0), (A, layer 1), (B, 1), ...: the epilogue of a slot drains one half of TMEM while the
+// MMAs of the next slot fill the other half, exactly as tile i / tile i + 1 of the single-layer kernel, and (A, layer l + 1)
+// is staged four slots after (A, layer l) - its rows were stored long before, so the staging warps' prefetch never waits
+// (with groups of two the epilogue of slot s - 2 was still running when slot s wanted its rows: measured slower than one
+// launch per layer).  Every CTA re-reads only the
 // 128 rows it wrote itself, straight from L2 (ld.global.cg after an mbarrier the epilogue warps arrive on).
 // Against one launch per layer this removes the launch floors between the layers (pipeline fill and drain, ~16 us each),
 // packs the tail (2108 tile-layers on 74 pairs = 28.5 waves instead of 4 x 8 for the forward block1 + block3 chain at
@@ -632,37 +634,35 @@ struct GemmChainDev {
 };
 
 namespace {
-// chunk L of a pair's work -> (slot, layer, tile index j of the pair, K chunk)
-struct ChainPos { int s, layer, j, kc; };
-__device__ __forceinline__ ChainPos chain_locate(const GemmChainDev& g, int L, int full) {
+constexpr int kChainGroup = 4;       // tiles interleaved per group: a slot's input was stored kChainGroup slots earlier
+// chunk L of a pair's work -> (slot, layer, tile index j of the pair, K chunk, distance to the slot it depends on)
+struct ChainPos { int s, layer, j, kc, dep; };
+__device__ __forceinline__ ChainPos chain_locate(const GemmChainDev& g, int L, int my_tiles) {
     ChainPos p;
-    const int NL = g.n_layers, G = 2 * g.sumk;
-    int grp = L / G;
-    if (grp < full) {
-        int r = L - grp * G;
-        for (int l = 0; l < NL; ++l) {
-            const int nk = g.l[l].nk;
-            if (r < 2 * nk) {
-                const int u = r >= nk ? 1 : 0;
-                p.s = grp * 2 * NL + 2 * l + u; p.layer = l; p.j = 2 * grp + u; p.kc = r - u * nk;
-                return p;
-            }
-            r -= 2 * nk;
-        }
-    }
-    int r = L - full * G;
+    const int NL = g.n_layers, GS = kChainGroup, full = my_tiles / GS, rem = my_tiles - full * GS;
+    const int G = GS * g.sumk;
+    const int grp = L / G;
+    const bool tail = grp >= full;
+    const int cnt = tail ? rem : GS;
+    int r = tail ? L - full * G : L - grp * G;
+    const int base = tail ? full * GS * NL : grp * GS * NL;
+    p.dep = cnt;
     for (int l = 0; l < NL; ++l) {
         const int nk = g.l[l].nk;
-        if (r < nk || l == NL - 1) { p.s = full * 2 * NL + l; p.layer = l; p.j = 2 * full; p.kc = r; return p; }
-        r -= nk;
+        if (r < cnt * nk || l == NL - 1) {
+            const int u = r / nk;
+            p.s = base + l * cnt + u; p.layer = l; p.j = (tail ? full : grp) * GS + u; p.kc = r - u * nk;
+            return p;
+        }
+        r -= cnt * nk;
     }
     p.s = p.layer = p.j = p.kc = 0;
     return p;
 }
-__device__ __forceinline__ void chain_slot(const GemmChainDev& g, int s, int full, int& layer, int& j) {
-    const int NL = g.n_layers;
-    if (s < full * 2 * NL) { const int r = s % (2 * NL); layer = r >> 1; j = 2 * (s / (2 * NL)) + (r & 1); }
-    else { layer = s - full * 2 * NL; j = 2 * full; }
+__device__ __forceinline__ void chain_slot(const GemmChainDev& g, int s, int my_tiles, int& layer, int& j) {
+    const int NL = g.n_layers, GS = kChainGroup, full = my_tiles / GS, rem = my_tiles - full * GS;
+    if (s < full * GS * NL) { const int r = s % (GS * NL); layer = r / GS; j = (s / (GS * NL)) * GS + r % GS; }
+    else { const int r = s - full * GS * NL; layer = r / rem; j = full * GS + r % rem; }
 }
 }  // namespace
 
@@ -675,7 +675,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
     uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kEpiWarps * SLAB_BYTES);
     uint64_t *fullA = bars, *emptyA = bars + 3, *fullB = bars + 6, *emptyB = bars + 9, *peerFull = bars + 12, *accFull = bars + 15,
              *accEmpty = bars + 17, *outDone = bars + 19;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+    // outDone: 2 * kChainGroup barriers used round-robin by slot index - a waiter for slot s - dep (dep <= kChainGroup) must
+    // not find its barrier two phases further (parity waits tell only "this phase" from "the one before")
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19 + 2 * kChainGroup);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const uint32_t rank = tc::cluster_ctarank();
     const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
@@ -684,7 +686,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
     const int n_ptiles_total = (int)((Mrows + 2 * TBM - 1) / (2 * TBM));
     const int my_tiles = n_ptiles_total > pair ? (n_ptiles_total - pair + n_pairs - 1) / n_pairs : 0;
     const int NL = g.n_layers;
-    const int full = my_tiles >> 1;                       // groups of two tiles; an odd last tile runs its layers back to back
+    // tiles are taken in groups of kChainGroup: (A,0) (B,0) (C,0) (D,0) (A,1) ... ; the last group may hold fewer tiles
     const int total_slots = my_tiles * NL;
     const int total_chunks = my_tiles * g.sumk;
 
@@ -694,10 +696,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1);
             tc::mbar_init(&peerFull[i], 1);
         }
-        for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 2 * kEpiWarps);
-            tc::mbar_init(&outDone[i], kEpiWarps);        // this CTA's epilogue warps have stored the slot's rows
-        }
+        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 2 * kEpiWarps); }
+        for (int i = 0; i < 2 * kChainGroup; ++i) tc::mbar_init(&outDone[i], kEpiWarps);     // this CTA's epilogue warps have stored the slot's rows
         tc::mbar_fence_init();
     }
     if (warp == 8) tc::tmem_alloc2(tmem_slot, 512u);
@@ -720,8 +720,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
         // the start of the chunk's own step, when everything before it is staged.  In full groups the dependency is two
         // slots back (all its chunks precede every pending one): the prefetch may wait.
         auto load = [&](int L, float4 (&r)[8], bool force) -> bool {
-            const ChainPos p = chain_locate(g, L, full);
-            if (p.layer > 0 && p.s >= full * 2 * NL && !force) return false;
+            const ChainPos p = chain_locate(g, L, my_tiles);
+            if (p.layer > 0 && p.dep < 2 && !force) return false;
             const ChainLayerDev& ly = g.l[p.layer];
             const int ptile = pair + p.j * n_pairs;
             const int64_t m0 = (int64_t)ptile * (2 * TBM) + (int64_t)rank * TBM;
@@ -729,8 +729,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             const bool kok = gk < ly.Kd;
             if (p.layer > 0) {
                 // rows produced by this CTA's own epilogue of the slot of (same tile, previous layer)
-                const int sd = p.s - (p.s < full * 2 * NL ? 2 : 1);
-                tc::mbar_wait(&outDone[sd & 1], (uint32_t)((sd >> 1) & 1));
+                const int sd = p.s - p.dep;
+                tc::mbar_wait(&outDone[sd % (2 * kChainGroup)], (uint32_t)((sd / (2 * kChainGroup)) & 1));
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     int64_t m = m0 + r0 + 16 * i;
@@ -774,7 +774,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             int L = 0;
             for (int s = 0; s < total_slots; ++s) {
                 int layer, j;
-                chain_slot(g, s, full, layer, j);
+                chain_slot(g, s, my_tiles, layer, j);
                 const ChainLayerDev& ly = g.l[layer];
                 const uint32_t idesc = tc::idesc_tf32(2 * TBM, ly.BN, 0, 0);
                 const uint32_t b_half = (uint32_t)(ly.BN * 64);
@@ -822,7 +822,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             int L = 0;
             for (int s = 0; s < total_slots; ++s) {
                 int layer, j;
-                chain_slot(g, s, full, layer, j);
+                chain_slot(g, s, my_tiles, layer, j);
                 const ChainLayerDev& ly = g.l[layer];
                 const uint32_t b_half = (uint32_t)(ly.BN * 64), b_block = (uint32_t)(2 * ly.BN * 128);
                 const char* src = ly.Bimg + (int64_t)rank * b_half;
@@ -852,7 +852,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
         };
         for (int s = 0; s < total_slots; ++s) {
             int layer, j;
-            chain_slot(g, s, full, layer, j);
+            chain_slot(g, s, my_tiles, layer, j);
             const ChainLayerDev& ly = g.l[layer];
             const int BN = ly.BN;
             const bool vec_ok = (ly.ldc % 4 == 0) && ((((uintptr_t)ly.C) & 15) == 0) && (ly.N % 4 == 0) &&
@@ -932,7 +932,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm
             // this warp's rows of the slot are stored: the staging warps of THIS CTA may read them as the next layer's A
             __threadfence_block();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&outDone[ab]);
+            if (lane == 0) tc::mbar_arrive(&outDone[s % (2 * kChainGroup)]);
         }
     }
     tc::fence_before_sync();
