@@ -14,8 +14,6 @@
 // caller has read them back and in->S / in->M are exact.  With in->counts set nothing ever reaches the host: in->S / in->M
 // are CAPACITIES (buffers and launches are sized for them), every kernel reads the true counts from in->counts, the GEMMs
 // cut their tiles / reduction splits on the device, and the whole pass is a fixed sequence of launches.
-#include <stdlib.h>
-
 #include "agg_kernels.cuh"
 #include "gemm.cuh"
 
@@ -206,9 +204,6 @@ extern "C" int pn_agg_activation_signs(const pn_agg_params* p, const void* saved
     return PN_OK;
 }
 
-// PN_CHAIN_LAYERS=0 in the environment: one launch per layer instead of the chained kernels (A/B timing; same bits)
-static const int g_chain_layers = [] { const char* e = getenv("PN_CHAIN_LAYERS"); return (e && e[0] == '0') ? 0 : 1; }();
-
 // C[rows, N] = epilogue(A[rows, Kd] x image(B)^T); rows = min(*rows_dev, rows_cap) when the count lives on the device
 static GemmNT nt(const float* A, int64_t lda, const char* Bimg, float* C, int64_t ldc, int64_t rows_cap, const int32_t* rows_dev, int N, int Kd,
                  const float* bias, int leaky, float slope) {
@@ -247,28 +242,18 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     PN_LAUNCH_CHECK("agg_prep");
     agg_prep_rows_kernel<<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
     PN_LAUNCH_CHECK("agg_prep_rows");
-    {   // block1 + block3: four layers, one persistent kernel (rows of a layer depend on the same rows of the previous one)
-        const GemmNT chain[4] = {nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope),
-                                 nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope),
-                                 nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope),
-                                 nt(sv.H3, d.W, ws.I3b, sv.H4, d.W, M, Mdev, d.W, d.W, w->block3_2_b, 1, d.slope)};
-        PN_TRY(gemm_nt_chain(chain, g_chain_layers ? 4 : 1, st));
-        if (!g_chain_layers)
-            for (int i = 1; i < 4; ++i) PN_TRY(gemm_nt(chain[i], st));
-    }
+    PN_TRY(gemm_nt(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.H3, d.W, ws.I3b, sv.H4, d.W, M, Mdev, d.W, d.W, w->block3_2_b, 1, d.slope), st));
     if (d.W == 256)
         agg_reduce_kernel<8><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     else
         agg_reduce_kernel<4><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     PN_LAUNCH_CHECK("agg_reduce");
-    {   // colour branch: three layers, one kernel
-        const GemmNT chain[3] = {nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope),
-                                 nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope),
-                                 nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope)};
-        PN_TRY(gemm_nt_chain(chain, g_chain_layers ? 3 : 1, st));
-        if (!g_chain_layers)
-            for (int i = 1; i < 3; ++i) PN_TRY(gemm_nt(chain[i], st));
-    }
+    PN_TRY(gemm_nt(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope), st));
     agg_finish_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");
     return PN_OK;

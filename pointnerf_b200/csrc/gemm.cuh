@@ -24,10 +24,6 @@ struct GemmNT {
     const int32_t* Mdev;  // optional DEVICE row count: rows = min(*Mdev, M); M is then the capacity the launch is sized for
 };
 int gemm_nt(const GemmNT& g, cudaStream_t st);
-// Layers whose rows depend only on the same rows of the previous layer (layers[i + 1].A == layers[i].C), every N <= 256, in
-// ONE persistent kernel (gemm_tc.cu: gemm_nt_chain_kernel); anything else falls back to one gemm_nt per layer.
-constexpr int kMaxChain = 4;
-int gemm_nt_chain(const GemmNT* layers, int n, cudaStream_t st);
 // Operand image of a B matrix for the tensor-core NT GEMM: B[n, k] = src[n*s_n + k*s_k] for n < N, k < K, zero beyond,
 // logically padded to Np rows x Kp columns; split into TF32 hi/lo and stored tile by tile in the exact shared-memory
 // layout (128-byte swizzle) so that one TMA bulk copy per K chunk stages it.

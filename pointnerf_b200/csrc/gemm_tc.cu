@@ -600,389 +600,6 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
     return PN_OK;
 }
 
-
-// ---------------------------------------------------------------------------------------------------------------
-// NT CHAIN on CTA pairs: several layers of the MLP whose rows depend only on the same rows of the previous layer
-// (H1 = f(X1 W1a), X3 = f(H1 W1b), H3 = f(X3 W3a), H4 = f(H3 W3b); the colour branch; the data-gradient chains) run inside
-// ONE persistent kernel.  A CTA pair owns row tiles of 256 rows and walks, per GROUP of four of its tiles A..D, the slots
-// (A, layer 0), (B, 0), (C, 0), (D, 0), (A, layer 1), (B, 1), ...: the epilogue of a slot drains one half of TMEM while the
-// MMAs of the next slot fill the other half, exactly as tile i / tile i + 1 of the single-layer kernel, and (A, layer l + 1)
-// is staged four slots after (A, layer l) - its rows were stored long before, so the staging warps' prefetch never waits
-// (with groups of two the epilogue of slot s - 2 was still running when slot s wanted its rows: measured slower than one
-// launch per layer).  Every CTA re-reads only the
-// 128 rows it wrote itself, straight from L2 (ld.global.cg after an mbarrier the epilogue warps arrive on).
-// Against one launch per layer this removes the launch floors between the layers (pipeline fill and drain, ~16 us each),
-// packs the tail (2108 tile-layers on 74 pairs = 28.5 waves instead of 4 x 8 for the forward block1 + block3 chain at
-// cfg2) and turns the re-read of every hidden activation into an L2 hit.  Hidden activations are still WRITTEN: the
-// weight-gradient GEMMs of the backward need them.
-// Requirements: every layer's N <= 256 (one n tile), all layers the same rows; layer l + 1's A is layer l's C.
-// ---------------------------------------------------------------------------------------------------------------
-struct ChainLayerDev {
-    const float* A; int64_t lda;
-    const char* Bimg;
-    float* C; int64_t ldc;
-    const float* bias;
-    const float* aux; int64_t ldaux; int aux_cols;
-    int N, Kd, BN, nk, leaky;
-};
-struct GemmChainDev {
-    ChainLayerDev l[kMaxChain];
-    int n_layers, sumk;
-    int64_t M;
-    const int32_t* Mdev;
-    float slope;
-};
-
-namespace {
-constexpr int kChainGroup = 4;       // tiles interleaved per group: a slot's input was stored kChainGroup slots earlier
-// chunk L of a pair's work -> (slot, layer, tile index j of the pair, K chunk, distance to the slot it depends on)
-struct ChainPos { int s, layer, j, kc, dep; };
-__device__ __forceinline__ ChainPos chain_locate(const GemmChainDev& g, int L, int my_tiles) {
-    ChainPos p;
-    const int NL = g.n_layers, GS = kChainGroup, full = my_tiles / GS, rem = my_tiles - full * GS;
-    const int G = GS * g.sumk;
-    const int grp = L / G;
-    const bool tail = grp >= full;
-    const int cnt = tail ? rem : GS;
-    int r = tail ? L - full * G : L - grp * G;
-    const int base = tail ? full * GS * NL : grp * GS * NL;
-    p.dep = cnt;
-    for (int l = 0; l < NL; ++l) {
-        const int nk = g.l[l].nk;
-        if (r < cnt * nk || l == NL - 1) {
-            const int u = r / nk;
-            p.s = base + l * cnt + u; p.layer = l; p.j = (tail ? full : grp) * GS + u; p.kc = r - u * nk;
-            return p;
-        }
-        r -= cnt * nk;
-    }
-    p.s = p.layer = p.j = p.kc = 0;
-    return p;
-}
-__device__ __forceinline__ void chain_slot(const GemmChainDev& g, int s, int my_tiles, int& layer, int& j) {
-    const int NL = g.n_layers, GS = kChainGroup, full = my_tiles / GS, rem = my_tiles - full * GS;
-    if (s < full * GS * NL) { const int r = s % (GS * NL); layer = r / GS; j = (s / (GS * NL)) * GS + r % GS; }
-    else { const int r = s - full * GS * NL; layer = r / rem; j = full * GS + r % rem; }
-}
-}  // namespace
-
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1) gemm_nt_chain_kernel(const __grid_constant__ GemmChainDev g) {
-    extern __shared__ char smem_raw[];
-    char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    char* smA = smem;
-    char* smB = smem + NS2 * A_STAGE;
-    char* slabs = smB + NS2 * B2_STAGE;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + kEpiWarps * SLAB_BYTES);
-    uint64_t *fullA = bars, *emptyA = bars + 3, *fullB = bars + 6, *emptyB = bars + 9, *peerFull = bars + 12, *accFull = bars + 15,
-             *accEmpty = bars + 17, *outDone = bars + 19;
-    // outDone: 2 * kChainGroup barriers used round-robin by slot index - a waiter for slot s - dep (dep <= kChainGroup) must
-    // not find its barrier two phases further (parity waits tell only "this phase" from "the one before")
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19 + 2 * kChainGroup);
-    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const uint32_t rank = tc::cluster_ctarank();
-    const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
-    int64_t Mrows = g.M;                                  // (the parameter struct stays read-only: a written copy would live in local memory)
-    if (g.Mdev) { const int64_t md = (int64_t)__ldg(g.Mdev); Mrows = md < Mrows ? md : Mrows; }
-    const int n_ptiles_total = (int)((Mrows + 2 * TBM - 1) / (2 * TBM));
-    const int my_tiles = n_ptiles_total > pair ? (n_ptiles_total - pair + n_pairs - 1) / n_pairs : 0;
-    const int NL = g.n_layers;
-    // tiles are taken in groups of kChainGroup: (A,0) (B,0) (C,0) (D,0) (A,1) ... ; the last group may hold fewer tiles
-    const int total_slots = my_tiles * NL;
-    const int total_chunks = my_tiles * g.sumk;
-
-    if (t == 0) {
-        for (int i = 0; i < NS2; ++i) {
-            tc::mbar_init(&fullA[i], kLoadThreads / 64); tc::mbar_init(&emptyA[i], 1);
-            tc::mbar_init(&fullB[i], 1); tc::mbar_init(&emptyB[i], 1);
-            tc::mbar_init(&peerFull[i], 1);
-        }
-        for (int i = 0; i < 2; ++i) { tc::mbar_init(&accFull[i], 1); tc::mbar_init(&accEmpty[i], 2 * kEpiWarps); }
-        for (int i = 0; i < 2 * kChainGroup; ++i) tc::mbar_init(&outDone[i], kEpiWarps);     // this CTA's epilogue warps have stored the slot's rows
-        tc::mbar_fence_init();
-    }
-    if (warp == 8) tc::tmem_alloc2(tmem_slot, 512u);
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::cluster_sync();
-    tc::fence_after_sync();
-    const uint32_t tmem_base = *tmem_slot;
-
-    if (warp < 8) {
-        // ---------------------------------------------------------------- A staging (own 128 rows of the slot's tile)
-        const int grp = warp >> 2, tt = t & 127;
-        const int c = tt & 7, r0 = tt >> 3;
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint32_t sA_u32 = tc::smem_u32(smA);
-        float4 ra[8], rb[8];
-        // Returns false when the load is DEFERRED: in the odd last tile of a pair the layers of one tile follow each other
-        // directly, so the rows chunk L needs are stored by an epilogue that still waits for chunks this very thread has in
-        // its other register set - blocking here (a prefetch, four chunks ahead) would deadlock; the load is then done at
-        // the start of the chunk's own step, when everything before it is staged.  In full groups the dependency is two
-        // slots back (all its chunks precede every pending one): the prefetch may wait.
-        auto load = [&](int L, float4 (&r)[8], bool force) -> bool {
-            const ChainPos p = chain_locate(g, L, my_tiles);
-            if (p.layer > 0 && p.dep < 2 && !force) return false;
-            const ChainLayerDev& ly = g.l[p.layer];
-            const int ptile = pair + p.j * n_pairs;
-            const int64_t m0 = (int64_t)ptile * (2 * TBM) + (int64_t)rank * TBM;
-            const int gk = p.kc * TBK + 4 * c;
-            const bool kok = gk < ly.Kd;
-            if (p.layer > 0) {
-                // rows produced by this CTA's own epilogue of the slot of (same tile, previous layer)
-                const int sd = p.s - p.dep;
-                tc::mbar_wait(&outDone[sd % (2 * kChainGroup)], (uint32_t)((sd / (2 * kChainGroup)) & 1));
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    int64_t m = m0 + r0 + 16 * i;
-                    r[i] = (kok && m < Mrows) ? __ldcg(reinterpret_cast<const float4*>(ly.A + m * ly.lda + gk)) : z4;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    int64_t m = m0 + r0 + 16 * i;
-                    r[i] = (kok && m < Mrows) ? __ldg(reinterpret_cast<const float4*>(ly.A + m * ly.lda + gk)) : z4;
-                }
-            }
-            return true;
-        };
-        auto step = [&](int L, float4 (&cur)[8], bool& have) {
-            if (!have) have = load(L, cur, true);
-            const int sa = L % NS2;
-            tc::mbar_wait(&emptyA[sa], ((L / NS2) & 1) ^ 1);
-            const uint32_t st = sA_u32 + (uint32_t)(sa * A_STAGE);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const uint32_t off = sw128_off(r0 + 16 * i, c);
-                split_store_s(st + off, st + A_BYTES + off, cur[i]);
-            }
-            tc::fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&fullA[sa]);
-            have = (L + 4 < total_chunks) ? load(L + 4, cur, false) : false;
-        };
-        bool have_a = false, have_b = false;
-        if (grp < total_chunks) have_a = load(grp, ra, false);
-        if (grp + 2 < total_chunks) have_b = load(grp + 2, rb, false);
-        for (int L = grp; L < total_chunks; L += 4) {
-            step(L, ra, have_a);
-            if (L + 2 < total_chunks) step(L + 2, rb, have_b);
-        }
-    } else if (warp == 8) {
-        if (lane == 0 && rank == 0) {
-            // ---------------------------------------------------------------- MMA issue (leader)
-            const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
-            int L = 0;
-            for (int s = 0; s < total_slots; ++s) {
-                int layer, j;
-                chain_slot(g, s, my_tiles, layer, j);
-                const ChainLayerDev& ly = g.l[layer];
-                const uint32_t idesc = tc::idesc_tf32(2 * TBM, ly.BN, 0, 0);
-                const uint32_t b_half = (uint32_t)(ly.BN * 64);
-                const int ab = s & 1;
-                tc::mbar_wait_cluster(&accEmpty[ab], ((s >> 1) & 1) ^ 1);
-                tc::fence_after_sync();
-                const uint32_t tmem_d = tmem_base + (uint32_t)(ab * 256);
-                for (int kc = 0; kc < ly.nk; ++kc, ++L) {
-                    const int sg = L % NS2;
-                    const uint32_t ph = (uint32_t)((L / NS2) & 1);
-                    tc::mbar_wait(&fullB[sg], ph);
-                    tc::mbar_wait(&fullA[sg], ph);
-                    tc::mbar_wait_cluster(&peerFull[sg], ph);
-                    tc::fence_after_sync();
-                    const uint32_t a_hi = sA + sg * A_STAGE, a_lo = a_hi + A_BYTES;
-                    const uint32_t b_hi = sB + sg * B2_STAGE, b_lo = b_hi + b_half;
-                    int ksteps = (ly.Kd - kc * TBK + 7) >> 3;
-                    if (ksteps > 4) ksteps = 4;
-                    for (int k = 0; k < ksteps; ++k) {
-                        const uint32_t ko = 32u * k;
-                        uint64_t dah = tc::smem_desc_sw128(a_hi + ko, 16, 1024), dal = tc::smem_desc_sw128(a_lo + ko, 16, 1024);
-                        uint64_t dbh = tc::smem_desc_sw128(b_hi + ko, 16, 1024), dbl = tc::smem_desc_sw128(b_lo + ko, 16, 1024);
-                        tc::mma_tf32_2(tmem_d, dah, dbl, idesc, (kc | k) != 0);
-                        tc::mma_tf32_2(tmem_d, dal, dbh, idesc, 1);
-                        tc::mma_tf32_2(tmem_d, dah, dbh, idesc, 1);
-                    }
-                    tc::mma_commit_2(&emptyA[sg]);
-                    tc::mma_commit_2(&emptyB[sg]);
-                }
-                tc::mma_commit_2(&accFull[ab]);
-            }
-        } else if (lane == 0) {
-            for (int L = 0; L < total_chunks; ++L) {        // relay (peer): forward "stage full" to the leader
-                const int sg = L % NS2;
-                const uint32_t ph = (uint32_t)((L / NS2) & 1);
-                tc::mbar_wait(&fullB[sg], ph);
-                tc::mbar_wait(&fullA[sg], ph);
-                tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&peerFull[sg]), 0));
-            }
-        }
-        __syncwarp();
-    } else if (warp == 9) {
-        // ---------------------------------------------------------------- B image producer: this CTA's half of every block
-        if (lane == 0) {
-            int L = 0;
-            for (int s = 0; s < total_slots; ++s) {
-                int layer, j;
-                chain_slot(g, s, my_tiles, layer, j);
-                const ChainLayerDev& ly = g.l[layer];
-                const uint32_t b_half = (uint32_t)(ly.BN * 64), b_block = (uint32_t)(2 * ly.BN * 128);
-                const char* src = ly.Bimg + (int64_t)rank * b_half;
-                for (int kc = 0; kc < ly.nk; ++kc, ++L) {
-                    const int sg = L % NS2;
-                    tc::mbar_wait(&emptyB[sg], ((L / NS2) & 1) ^ 1);
-                    tc::mbar_arrive_expect_tx(&fullB[sg], 2 * b_half);
-                    const char* blk = src + (int64_t)kc * b_block;
-                    tc::bulk_g2s(smB + sg * B2_STAGE, blk, b_half, &fullB[sg]);
-                    tc::bulk_g2s(smB + sg * B2_STAGE + b_half, blk + (int64_t)ly.BN * 128, b_half, &fullB[sg]);
-                }
-            }
-        }
-        __syncwarp();
-    } else {
-        // ---------------------------------------------------------------- epilogue (warps 10..17), own 128 rows of every slot
-        const int q = warp & 3;
-        const int half = (warp - 10) >> 2;
-        const uint32_t slab = tc::smem_u32(slabs + (warp - 10) * SLAB_BYTES);
-        const int rsub = lane >> 3, c8 = lane & 7;
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint32_t accEmpty0 = tc::mapa(tc::smem_u32(&accEmpty[0]), 0);     // the leader's barriers
-        auto release = [&](int ab) {
-            tc::fence_before_sync();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive_cluster(accEmpty0 + 8u * (uint32_t)ab);
-        };
-        for (int s = 0; s < total_slots; ++s) {
-            int layer, j;
-            chain_slot(g, s, my_tiles, layer, j);
-            const ChainLayerDev& ly = g.l[layer];
-            const int BN = ly.BN;
-            const bool vec_ok = (ly.ldc % 4 == 0) && ((((uintptr_t)ly.C) & 15) == 0) && (ly.N % 4 == 0) &&
-                                (!ly.aux || (ly.ldaux % 4 == 0 && (((uintptr_t)ly.aux) & 15) == 0 && ly.aux_cols % 4 == 0)) &&
-                                (!ly.bias || (((uintptr_t)ly.bias) & 15) == 0);
-            const int nch = (BN + 31) >> 5;
-            const int my_last = ((nch - 1 - half) & ~1) + half;
-            const int ab = s & 1;
-            const int ptile = pair + j * n_pairs;
-            const int64_t m0 = (int64_t)ptile * (2 * TBM) + (int64_t)rank * TBM + q * 32;
-            tc::mbar_wait(&accFull[ab], (s >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
-            for (int jc = half; jc < nch; jc += 2) {
-                uint32_t lo16[16], hi16[16];
-                tc::tmem_ld16_issue(taddr + (uint32_t)(jc * 32), lo16);
-                tc::tmem_ld16_issue(taddr + (uint32_t)(jc * 32 + 16), hi16);
-                const int n = jc * 32 + 4 * c8;
-                const bool ncol_ok = (n < BN) && n < ly.N;
-                float4 bias4 = z4;
-                if (vec_ok && ncol_ok && ly.bias) bias4 = __ldg(reinterpret_cast<const float4*>(ly.bias + n));
-                tc::tmem_ld_wait();
-                if (jc == my_last) release(ab);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u,
-                               make_float4(__uint_as_float(lo16[4 * i]), __uint_as_float(lo16[4 * i + 1]), __uint_as_float(lo16[4 * i + 2]),
-                                           __uint_as_float(lo16[4 * i + 3])));
-                    tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u,
-                               make_float4(__uint_as_float(hi16[4 * i]), __uint_as_float(hi16[4 * i + 1]), __uint_as_float(hi16[4 * i + 2]),
-                                           __uint_as_float(hi16[4 * i + 3])));
-                }
-                __syncwarp();
-                const bool use_aux = vec_ok && ncol_ok && ly.aux && n < ly.aux_cols;
-                float4 aux4[8];
-                if (use_aux) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int64_t m = m0 + 4 * i + rsub;
-                        aux4[i] = m < Mrows ? __ldg(reinterpret_cast<const float4*>(ly.aux + m * ly.ldaux + n)) : z4;
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int row = 4 * i + rsub;
-                    const int64_t m = m0 + row;
-                    float4 x4 = tc::lds128(slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u);
-                    if (m >= Mrows || !ncol_ok) continue;
-                    float x[4] = {x4.x, x4.y, x4.z, x4.w};
-                    if (vec_ok) {
-                        x[0] += bias4.x; x[1] += bias4.y; x[2] += bias4.z; x[3] += bias4.w;
-                        if (ly.leaky) {
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) x[e] = x[e] > 0.f ? x[e] : g.slope * x[e];
-                        }
-                        if (use_aux) {
-                            const float4 a = aux4[i];
-                            x[0] *= a.x > 0.f ? 1.f : g.slope; x[1] *= a.y > 0.f ? 1.f : g.slope;
-                            x[2] *= a.z > 0.f ? 1.f : g.slope; x[3] *= a.w > 0.f ? 1.f : g.slope;
-                        }
-                        *reinterpret_cast<float4*>(ly.C + m * ly.ldc + n) = make_float4(x[0], x[1], x[2], x[3]);
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            if (n + e >= ly.N) break;
-                            float y = x[e];
-                            if (ly.bias) y += __ldg(ly.bias + n + e);
-                            if (ly.leaky) y = y > 0.f ? y : g.slope * y;
-                            if (ly.aux && n + e < ly.aux_cols) y *= (__ldg(ly.aux + m * ly.ldaux + n + e) > 0.f) ? 1.f : g.slope;
-                            ly.C[m * ly.ldc + n + e] = y;
-                        }
-                    }
-                }
-                __syncwarp();
-            }
-            if (my_last < half) release(ab);
-            // this warp's rows of the slot are stored: the staging warps of THIS CTA may read them as the next layer's A
-            __threadfence_block();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&outDone[s % (2 * kChainGroup)]);
-        }
-    }
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::cluster_sync();
-    if (warp == 8) {
-        tc::fence_after_sync();
-        tc::tmem_dealloc2(tmem_base, 512u);
-    }
-}
-
-int gemm_nt_chain(const GemmNT* layers, int n, cudaStream_t st) {
-    PN_CHECK_ARG(n >= 1 && n <= kMaxChain, "gemm_nt_chain: 1..%d layers", kMaxChain);
-    bool ok = true;
-    for (int i = 0; i < n; ++i) {
-        const GemmNT& a = layers[i];
-        PN_CHECK_ARG(a.Kd % 4 == 0 && a.lda % 4 == 0 && ((uintptr_t)a.A & 15) == 0 && a.Bimg, "gemm_nt_chain: layer %d operands", i);
-        if (a.N > TMAXN || a.M != layers[0].M || a.Mdev != layers[0].Mdev || a.slope != layers[0].slope) ok = false;
-        if (i > 0 && (a.A != layers[i - 1].C || a.lda != layers[i - 1].ldc || a.Kd > (int)align_up(layers[i - 1].N, 16) + 16)) ok = false;
-    }
-    if (!ok || n == 1) {            // not a chain this kernel can run: one launch per layer
-        for (int i = 0; i < n; ++i) {
-            int rc = gemm_nt(layers[i], st);
-            if (rc) return rc;
-        }
-        return PN_OK;
-    }
-    if (layers[0].M <= 0) return PN_OK;
-    static bool attr = false;
-    if (!attr) {
-        PN_CUDA(cudaFuncSetAttribute(gemm_nt_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, IMG2_SMEM));
-        attr = true;
-    }
-    GemmChainDev g;
-    g.n_layers = n; g.sumk = 0; g.M = layers[0].M; g.Mdev = layers[0].Mdev; g.slope = layers[0].slope;
-    for (int i = 0; i < kMaxChain; ++i) {
-        const GemmNT& a = layers[i < n ? i : 0];
-        ChainLayerDev& l = g.l[i];
-        int n_tiles;
-        l.A = a.A; l.lda = a.lda; l.Bimg = a.Bimg; l.C = a.C; l.ldc = a.ldc; l.bias = a.bias; l.aux = a.aux; l.ldaux = a.ldaux;
-        l.aux_cols = a.aux_cols; l.N = a.N; l.Kd = a.Kd; l.BN = pick_bn(a.N, &n_tiles); l.nk = (a.Kd + TBK - 1) / TBK; l.leaky = a.leaky;
-        if (i < n) g.sumk += l.nk;
-    }
-    int64_t ptotal = cdiv(g.M, 2 * TBM);
-    int pairs = ptotal < kNumSMs / 2 ? (int)ptotal : kNumSMs / 2;
-    gemm_nt_chain_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g);
-    PN_LAUNCH_CHECK("gemm_nt_chain");
-    return PN_OK;
-}
-
 int64_t nt_image_bytes(int Np, int Kp) {
     int n_tiles;
     int bn = pick_bn(Np, &n_tiles);
