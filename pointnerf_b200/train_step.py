@@ -92,7 +92,7 @@ class FusedTrainStep:
     """
 
     def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
-                 caps=None, graph=True, group=None, pipeline=False, local_only=False, sparse_exchange=True):
+                 caps=None, graph=True, group=None, pipeline=False, local_only=False, sparse_exchange=True, exchange_in_step=True):
         o = model.opt
         if getattr(o, "wcoord_query", 1) <= 0:
             raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
@@ -133,6 +133,11 @@ class FusedTrainStep:
         self._touched_ids = self._n_touched = None
         self._gathered = None        # ray sharding: the all-gathered rows of the last exchange (their ids are cleared next step)
         self.sparse_exchange = bool(sparse_exchange)
+        # ray sharding: the gradient exchange runs INSIDE the step (captured with it): the touched-row exchange starts where
+        # the backward's data-gradient chain ends (pn_agg_backward_wait_rows), on its own stream, under the trailing
+        # weight-gradient GEMMs; the MLP all-reduce follows them.  False: the caller runs reduce() after the step.
+        self.exchange_in_step = bool(exchange_in_step) and self.world > 1
+        self._comm = None
         self._full_zero = self.world > 1 and not self.sparse_exchange      # the dense all-reduce writes every row: whole-table clears
         self._slots = None
         self.launches_per_step = 0
@@ -258,6 +263,24 @@ class FusedTrainStep:
             tail = call.grad_flat[call.flat_tail_off:call.flat_tail_off + C]
             tail.copy_(g_bg)
             g_bg = tail
+        self.grads = {"points_embeding": g_emb, "points_color": g_col, "points_dir": g_dir, "points_conf": g_cnf, "bg_color": g_bg}
+        if self.exchange_in_step:
+            main = torch.cuda.current_stream()
+            if self.sparse_exchange:
+                if self._comm is None:
+                    self._comm = torch.cuda.Stream()
+                rc = _lib.lib().pn_agg_backward_wait_rows(self._comm.cuda_stream)     # fork at the end of the data-gradient chain
+                if rc < 0:
+                    _lib.check(rc, "pn_agg_backward_wait_rows")
+                if rc != 1:
+                    self._comm.wait_stream(main)
+                with torch.cuda.stream(self._comm):
+                    self._exchange_rows()
+            else:
+                self._exchange_dense()
+            dist.all_reduce(call.grad_flat, op=dist.ReduceOp.SUM, group=self.group)    # MLP gradients + bg_color (after the weight-gradient GEMMs)
+            if self.sparse_exchange:
+                main.wait_stream(self._comm)
         self.counts_host.copy_(q["counts"], non_blocking=True)
         if call.n_touched is not None:
             self.touched_host.copy_(call.n_touched, non_blocking=True)
@@ -296,6 +319,9 @@ class FusedTrainStep:
             self._gathered = torch.zeros((rows, F + 8), dtype=torch.float32, device=self.dev)
             self._gathered.view(torch.int32)[:, 0] = -1
             self._packed = torch.zeros((self.row_cap, F + 8), dtype=torch.float32, device=self.dev)
+        T = int(self.model.neural_points.points_embeding.shape[-2])
+        if self._slots is None or self._slots.numel() != T * self.world:       # (allocated here: never inside a capture)
+            self._slots = torch.full((T * self.world,), -1, dtype=torch.int32, device=self.dev)
 
     # ---- capacities -----------------------------------------------------------------------------------------------------
     def calibrate(self, batches, headroom=1.25, granule=4096):
@@ -452,42 +478,53 @@ class FusedTrainStep:
             dist.all_reduce(self.masked_count, op=dist.ReduceOp.SUM, group=self.group)
 
     # ---- ray sharding: gradient exchange after the step ----------------------------------------------------------------
+    def _exchange_rows(self):
+        """Touched-row exchange of the per-point gradient tables on the current stream (see reduce())."""
+        g, call, lib = self.grads, self.call, _lib.lib()
+        F = int(g["points_embeding"].shape[-1])
+        cap = self.row_cap
+        packed, gathered = self._packed, self._gathered
+        _lib.check(lib.pn_rows_pack(_lib.ptr(call.touched_ids), int(call.touched_ids.numel()), cap, F, _lib.ptr(g["points_embeding"]),
+                                    _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
+                                    _lib.ptr(packed), _lib.stream()), "pn_rows_pack")
+        dist.all_gather_into_tensor(gathered, packed, group=self.group)
+        T = int(g["points_embeding"].shape[0])
+        if self._slots is None or self._slots.numel() != T * self.world:
+            self._slots = torch.full((T * self.world,), -1, dtype=torch.int32, device=self.dev)
+        _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, T, _lib.ptr(self._slots), _lib.ptr(g["points_embeding"]),
+                                     _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
+                                     _lib.stream()), "pn_rows_merge")
+        self.exchange_bytes = (self.world - 1) * cap * (F + 8) * 4
+
+    def _exchange_dense(self):
+        g = self.grads
+        for n in ("points_embeding", "points_color", "points_dir", "points_conf"):
+            if g.get(n) is not None:
+                dist.all_reduce(g[n], op=dist.ReduceOp.SUM, group=self.group)
+        self.exchange_bytes = sum(g[n].numel() * 4 for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None)
+
     def reduce(self):
         """Sum of every gradient over the ranks of ``group``.  Ranks normalise their losses by GLOBAL counts, so the sum is
         the gradient of the whole batch.  MLP gradients + bg_color: ONE all-reduce of the flat buffer the backward wrote
-        them into.  Per-point tables: ``sparse`` - all-gather of the rows this step touched ([id | F + 7 floats], row_cap
-        rows per rank from calibrate()) and a rank-ordered merge (pn_rows_pack / pn_rows_merge: identical bits on every
-        replica); else a dense all-reduce of the four tables."""
+        them into.  Per-point tables: ``sparse_exchange`` - all-gather of the rows this step touched ([id | F + 7 floats],
+        row_cap rows per rank from calibrate()) and a rank-ordered merge (pn_rows_pack / pn_rows_merge: identical bits on
+        every replica); else a dense all-reduce of the four tables.  With ``exchange_in_step`` (default) all of this already
+        ran inside the step - captured in its graph, the row exchange under the trailing weight-gradient GEMMs - and this
+        call only checks the row capacity."""
         if self.world <= 1:
             return
-        g, call, lib = self.grads, self.call, _lib.lib()
-        F = int(g["points_embeding"].shape[-1]) if g.get("points_embeding") is not None else 0
-        h_flat = dist.all_reduce(call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        if self.sparse_exchange and int(self.touched_host[0]) > self.row_cap:
+            # (a step that touched more rows than row_cap loses the surplus rows' gradients: flagged here, one step late;
+            #  calibrate() sizes the capacity with headroom)
+            self.overflows += 1
+            warnings.warn("FusedTrainStep: %d touched rows exceed the exchange capacity %d" % (int(self.touched_host[0]), self.row_cap))
+        if self.exchange_in_step:
+            return
+        h_flat = dist.all_reduce(self.call.grad_flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         if self.sparse_exchange:
-            # (a step that touched more rows than row_cap loses the surplus rows' gradients: flagged through touched_host,
-            #  the capacity is raised by the caller's next calibrate(); calibrate() sizes it with headroom)
-            if int(self.touched_host[0]) > self.row_cap:
-                self.overflows += 1
-                warnings.warn("FusedTrainStep: %d touched rows exceed the exchange capacity %d" % (int(self.touched_host[0]), self.row_cap))
-            cap = self.row_cap
-            packed, gathered = self._packed, self._gathered
-            _lib.check(lib.pn_rows_pack(_lib.ptr(call.touched_ids), int(call.touched_ids.numel()), cap, F, _lib.ptr(g["points_embeding"]),
-                                        _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
-                                        _lib.ptr(packed), _lib.stream()), "pn_rows_pack")
-            dist.all_gather_into_tensor(gathered, packed, group=self.group)
-            T = int(g["points_embeding"].shape[0])
-            if self._slots is None or self._slots.numel() != T * self.world:
-                self._slots = torch.full((T * self.world,), -1, dtype=torch.int32, device=self.dev)
-            _lib.check(lib.pn_rows_merge(_lib.ptr(gathered), self.world, cap, F, T, _lib.ptr(self._slots), _lib.ptr(g["points_embeding"]),
-                                         _lib.ptr(g.get("points_conf")), _lib.ptr(g.get("points_dir")), _lib.ptr(g.get("points_color")),
-                                         _lib.stream()), "pn_rows_merge")
-            self.exchange_bytes = (self.world - 1) * cap * (F + 8) * 4
+            self._exchange_rows()
         else:
-            hs = [dist.all_reduce(g[n], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-                  for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None]
-            for h in hs:
-                h.wait()
-            self.exchange_bytes = sum(g[n].numel() * 4 for n in ("points_embeding", "points_color", "points_dir", "points_conf") if g.get(n) is not None)
+            self._exchange_dense()
         h_flat.wait()
 
 
