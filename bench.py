@@ -1238,8 +1238,15 @@ def main():
                 "train_step_with_adam": with_adam, "frame_sweep_cfg5": sweep, "maintenance": maint, "frustum_querier_wcoord0": frustum}
         _emit(line)
     if world > 1:
+        # (no destroy_process_group: with collectives captured in CUDA graphs ProcessGroupNCCL's teardown was seen to wait
+        #  forever on work handles recorded during the captures; the processes synchronise and leave)
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        _phase("done")
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     _phase("done")
     return 0
 

@@ -40,8 +40,10 @@ def main():
         ok = ok and res["ok"]
         if rank == 0:
             print(json.dumps(res))
-    dist.destroy_process_group()
-    return 0 if ok else 1
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    os._exit(0 if ok else 1)       # (no destroy_process_group after collectives captured in CUDA graphs: see bench.py)
 
 
 if __name__ == "__main__":
