@@ -226,3 +226,22 @@ def test_query_on_other_scene_shapes(cuda_dev, name):
     assert torch.equal(raw["sample_loc_w"][sel].cpu()[None], loc_w)
     assert torch.equal(raw["sample_pidx"][sel].cpu()[None], pidx), "neighbour slots differ from the oracle"
     assert np.array_equal(raw["grid"].hp["ranges"], ranges)
+
+
+def test_sample_depths_sequential_fallback_on_wild_segments(cuda_dev):
+    """pn_sample_depths takes a warp-parallel scan when the double running sum is provably exact (segments within 2^20 of each
+    other) and the sequential chain otherwise: segment lengths spanning 40 binary orders (and denormals) must still give the
+    host chain's bits."""
+    D, R = 400, 64
+    g = torch.Generator().manual_seed(5)
+    base = (torch.rand(D, generator=g) * 2.0 ** torch.randint(-60, -20, (D,), generator=g).float()).float()
+    base[::7] = 1e-41                                    # denormals
+    u = torch.rand(1, R, D, generator=g)
+    near, jitter = 0.25, 0.3
+    seg = base.view(1, 1, D) * (1 + jitter * (u - 0.5))
+    ends = near + torch.cat([torch.zeros(1, R, 1), torch.cumsum(seg, dim=2)], dim=2)
+    want = (ends[:, :, :-1] + ends[:, :, 1:]) / 2
+    ts = torch.empty((1, R, D), dtype=torch.float32, device=cuda_dev)
+    _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base.to(cuda_dev)), _lib.ptr(u.reshape(R, D).contiguous().to(cuda_dev)), R, D, near, jitter,
+                                           _lib.ptr(ts), _lib.stream()), "pn_sample_depths")
+    assert torch.equal(ts.cpu(), want)
