@@ -315,10 +315,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
     // the host never learns - g.M is then only the capacity the launch was sized for)
     if (g.Mdev) { const int64_t md = (int64_t)__ldg(g.Mdev); g.M = md < g.M ? md : g.M; }
     const int n_ptiles_total = (int)((g.M + 2 * TBM - 1) / (2 * TBM)) * n_tiles_n;
-    const uint32_t b_half = (uint32_t)(BN * 64);          // bytes of (BN / 2 rows x 128 B): one of hi | lo in this CTA
     const uint32_t b_block = (uint32_t)(2 * BN * 128);    // image block of one (n tile, K chunk)
-    const int my_tiles = n_ptiles_total > pair ? (n_ptiles_total - pair + n_pairs - 1) / n_pairs : 0;
+    // Work items.  Tile i of the (row tile, n tile) grid goes to pair i % n_pairs; the tiles of the LAST, partial wave (rem of
+    // them - the other pairs would idle for a whole tile time) are cut along n into ns column slices of BN / ns, one per pair:
+    // the tail then costs 1 / ns of a tile.  S = 19 K sample rows are 76 row tiles on 74 pairs: 1.25 tile times instead of 2.
+    const int full_waves = n_ptiles_total / n_pairs, rem = n_ptiles_total - full_waves * n_pairs;
+    int ns = 1;
+    if (n_tiles_n == 1 && rem > 0) {
+        if (rem * 4 <= n_pairs && BN % 128 == 0) ns = 4;
+        else if (rem * 2 <= n_pairs && BN % 64 == 0) ns = 2;
+    }
+    const int my_tiles = full_waves + (pair < rem * ns ? 1 : 0);
     const int total_chunks = my_tiles * nk;
+    struct Item { int64_t m0; int bn, n0, nt, img_row; };   // first row of the pair's 256 | width | first column | n tile | first image row
+    auto item = [&](int it) {
+        Item w;
+        if (it < full_waves) {
+            const int ptile = pair + it * n_pairs;
+            w.m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM); w.nt = ptile % n_tiles_n; w.bn = BN; w.n0 = w.nt * BN; w.img_row = 0;
+        } else {
+            const int ptile = full_waves * n_pairs + pair / ns, sl = pair % ns;
+            w.m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM); w.nt = ptile % n_tiles_n; w.bn = BN / ns; w.img_row = sl * w.bn;
+            w.n0 = w.nt * BN + w.img_row;
+        }
+        return w;
+    };
 
     if (t == 0) {
         for (int i = 0; i < NS2; ++i) {
@@ -345,8 +366,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
         float4 ra[8], rb[8];
         auto load = [&](int L, float4 (&r)[8]) {
             const int it = L / nk, kc = L - it * nk;
-            const int ptile = pair + it * n_pairs;
-            const int64_t m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM;
+            const int64_t m0 = item(it).m0 + (int64_t)rank * TBM;
             const int gk = kc * TBK + 4 * c;
             const bool kok = gk < g.Kd;
 #pragma unroll
@@ -378,7 +398,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
     } else if (warp == 8) {
         if (lane == 0 && rank == 0) {
             // ---------------------------------------------------------------- MMA issue (leader)
-            const uint32_t idesc = tc::idesc_tf32(2 * TBM, BN, 0, 0);
             const uint32_t sA = tc::smem_u32(smA), sB = tc::smem_u32(smB);
             int L = 0;
             for (int it = 0; it < my_tiles; ++it) {
@@ -386,6 +405,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                 tc::mbar_wait_cluster(&accEmpty[ab], ((it >> 1) & 1) ^ 1);
                 tc::fence_after_sync();
                 const uint32_t tmem_d = tmem_base + (uint32_t)(ab * 256);
+                const int bn = item(it).bn;
+                const uint32_t idesc = tc::idesc_tf32(2 * TBM, bn, 0, 0);
+                const uint32_t b_half = (uint32_t)(bn * 64);  // bytes of (bn / 2 rows x 128 B): one of hi | lo in this CTA
                 for (int kc = 0; kc < nk; ++kc, ++L) {
                     const int s = L % NS2;
                     const uint32_t ph = (uint32_t)((L / NS2) & 1);
@@ -426,8 +448,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
         if (lane == 0) {
             int L = 0;
             for (int it = 0; it < my_tiles; ++it) {
-                const int ptile = pair + it * n_pairs;
-                const char* src = g.Bimg + (int64_t)(ptile % n_tiles_n) * nk * b_block + (int64_t)rank * b_half;
+                const Item w = item(it);
+                const uint32_t b_half = (uint32_t)(w.bn * 64);
+                const char* src = g.Bimg + (int64_t)w.nt * nk * b_block + (int64_t)w.img_row * 128 + (int64_t)rank * b_half;
                 for (int kc = 0; kc < nk; ++kc, ++L) {
                     const int s = L % NS2;
                     tc::mbar_wait(&emptyB[s], ((L / NS2) & 1) ^ 1);
@@ -448,8 +471,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                             (!g.aux || (g.ldaux % 4 == 0 && (((uintptr_t)g.aux) & 15) == 0 && g.aux_cols % 4 == 0)) &&
                             (!g.bias || (((uintptr_t)g.bias) & 15) == 0);
         const int rsub = lane >> 3, c8 = lane & 7;
-        const int nch = (BN + 31) >> 5;
-        const int my_last = ((nch - 1 - half) & ~1) + half;
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         const uint32_t accEmpty0 = tc::mapa(tc::smem_u32(&accEmpty[0]), 0);     // the leader's barriers
         auto release = [&](int ab) {
@@ -457,23 +478,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
             __syncwarp();
             if (lane == 0) tc::mbar_arrive_cluster(accEmpty0 + 8u * (uint32_t)ab);
         };
-        auto prefetch_aux = [&](int ptile) {
+        auto prefetch_aux = [&](int it) {
             if (!g.aux) return;
-            const int64_t m = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM + q * 32 + lane;
-            const int n0 = (ptile % n_tiles_n) * BN;
+            const Item w = item(it);
+            const int64_t m = w.m0 + (int64_t)rank * TBM + q * 32 + lane;
+            const int n0 = w.n0, nch = (w.bn + 31) >> 5;
             if (m >= g.M) return;
             for (int j = half; j < nch; j += 2) {
                 const int n = n0 + j * 32;
                 if (n < g.aux_cols) asm volatile("prefetch.global.L2 [%0];" ::"l"(g.aux + m * g.ldaux + n));
             }
         };
-        if (my_tiles > 0) prefetch_aux(pair);
+        if (my_tiles > 0) prefetch_aux(0);
         for (int it = 0; it < my_tiles; ++it) {
             const int ab = it & 1;
-            const int ptile = pair + it * n_pairs;
-            const int64_t m0 = (int64_t)(ptile / n_tiles_n) * (2 * TBM) + (int64_t)rank * TBM + q * 32;
-            const int n0 = (ptile % n_tiles_n) * BN;
-            if (it + 1 < my_tiles) prefetch_aux(ptile + n_pairs);
+            const Item w = item(it);
+            const int BN = w.bn;                              // this item's width (a column slice in the last wave)
+            const int64_t m0 = w.m0 + (int64_t)rank * TBM + q * 32;
+            const int n0 = w.n0;
+            const int nch = (BN + 31) >> 5;
+            const int my_last = ((nch - 1 - half) & ~1) + half;
+            if (it + 1 < my_tiles) prefetch_aux(it + 1);
             tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
@@ -594,7 +619,9 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
     int n_tiles;
     int bn = pick_bn(g.N, &n_tiles);
     int64_t ptotal = cdiv(g.M, 2 * TBM) * n_tiles;        // g.M: the row count, or its capacity when g.Mdev is given
-    int pairs = ptotal < kNumSMs / 2 ? (int)ptotal : kNumSMs / 2;
+    // few tiles: the kernel cuts them into column slices (see its work-item comment), so up to 4 pairs share a row tile
+    const int max_slices = n_tiles == 1 ? (bn % 128 == 0 ? 4 : bn % 64 == 0 ? 2 : 1) : 1;
+    int pairs = ptotal * max_slices < kNumSMs / 2 ? (int)(ptotal * max_slices) : kNumSMs / 2;
     gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles);
     PN_LAUNCH_CHECK("gemm_nt_img2");
     return PN_OK;
