@@ -128,10 +128,7 @@ int pn_ray_sample(const float* campos, const float* raydir, const float* ts, int
 /* ------------------------------------------------------------------------------------------------
  * 3. Neighbour query  (replaces query_neigh_along_ray_layered :442-528)
  *
- * One block per ray; a warp takes runs of 4 consecutive kept samples, stages the runs' neighbourhood (cell bucket ranges
- * and the buckets' points) in shared memory once, and searches it for each sample of the run (north_star item 1:
- * "shared-memory-staged, radius-limited K-nearest search along each ray"); runs that exceed the staging buffers (256
- * cells / 320 points per warp) search global memory.  Candidates are visited in the reference's order - Chebyshev layer, then
+ * One warp per kept sample.  Candidates are visited in the reference's order - Chebyshev layer, then
  * x, y, z ascending, then bucket position - with d^2 = fma(z,z,fma(x,x,y*y)) (what nvcc emits for :498);
  * the K slots are filled and replaced exactly as :499-519 (so slot ARRANGEMENT matches, not only
  * the set), and the search stops after the first layer that has seen >= K in-radius candidates (:526).
@@ -145,14 +142,6 @@ int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* 
                  const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
                  float radius_limit2, int32_t* sample_pidx, int32_t* ray_any,
                  unsigned long long* n_candidates, void* stream);
-/* The same search with every sample reading cell ranges, bucket entries and points from global memory (one warp per
- * kept sample, no staging): the round-1 kernel, kept as the in-library check of the staged one (bit-identical outputs,
- * tests/test_gpu_query.py) and for A / B timing.  No reference counterpart of its own. */
-int pn_knn_query_direct(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
-                        const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
-                        const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
-                        float radius_limit2, int32_t* sample_pidx, int32_t* ray_any,
-                        unsigned long long* n_candidates, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * 3b. Perspective-frustum querier  (replaces get_occ_vox :265-314, near_vox_full :316-365,

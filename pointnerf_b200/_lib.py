@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 11
+ABI_VERSION = 10
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -98,8 +98,6 @@ def _declare(lib):
         "pn_ray_sample": (c_int, [P, P, P, c_int64, c_int64, c_int32, c_int32, POINTER(GridParams), P, P, P, P, P]),
         "pn_knn_query": (c_int, [P, POINTER(GridParams), P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float,
                                  P, P, P, P]),
-        "pn_knn_query_direct": (c_int, [P, POINTER(GridParams), P, P, P, P, P, c_int64, c_int32, c_int32, c_int32, c_float,
-                                        P, P, P, P]),
         "pn_frustum_grid_workspace_bytes": (c_int64, [c_int64, c_int64]),
         "pn_frustum_grid_build": (c_int, [P, c_int64, POINTER(GridParams), P, P, P, P, P, c_int64, P]),
         "pn_frustum_sample": (c_int, [P, c_int64, c_int32, POINTER(GridParams), POINTER(c_int32), P, P, P, P, P]),

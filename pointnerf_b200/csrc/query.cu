@@ -129,53 +129,6 @@ __global__ void __launch_bounds__(256) frustum_sample_kernel(const int* __restri
     }
 }
 
-// The K slots of one query sample, spread over the warp: lane k holds slot k (and k + 32 when K > 32).
-struct KnnSlots {
-    int pid[2];
-    float d2[2];
-    int seen, far_slot;
-    float far2;
-};
-// Insert this step's in-radius candidates (one per lane: in / d2 / pid) ONE BY ONE in lane (= sequence) order with warp-uniform
-// code that mirrors :499-519: fill the slots in arrival order, then replace the FIRST slot holding the maximum under the
-// strict '<' rule and rescan.
-__device__ __forceinline__ void knn_insert(KnnSlots& s, bool in, float d2, int pid, int K, int lane) {
-    unsigned m = __ballot_sync(kFull, in);
-    while (m) {
-        if (s.seen >= K) {   // slots full: only candidates closer than the current maximum can change anything,
-            m &= __ballot_sync(kFull, in && d2 < s.far2);   // and that maximum never grows - drop the rest at once
-            if (!m) break;
-        }
-        int src = __ffs(m) - 1;
-        m &= m - 1;
-        float cd = __shfl_sync(kFull, d2, src);
-        int cp = __shfl_sync(kFull, pid, src);
-        if (s.seen < K) {
-            if (lane == (s.seen & 31)) { s.pid[s.seen >> 5] = cp; s.d2[s.seen >> 5] = cd; }
-            if (cd > s.far2) { s.far2 = cd; s.far_slot = s.seen; }
-            ++s.seen;
-        } else {
-            ++s.seen;
-            if (cd < s.far2) {
-                if (lane == (s.far_slot & 31)) { s.pid[s.far_slot >> 5] = cp; s.d2[s.far_slot >> 5] = cd; }
-                // rescan: first slot holding the maximum, only if it exceeds the new value (:511-517)
-                float v0 = (lane < K) ? s.d2[0] : -1.f;
-                float v1 = (lane + 32 < K) ? s.d2[1] : -1.f;
-                float mx = fmaxf(v0, v1);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, o));
-                s.far2 = cd;
-                if (mx > cd) {
-                    unsigned b0m = __ballot_sync(kFull, v0 == mx);
-                    unsigned b1m = __ballot_sync(kFull, v1 == mx);
-                    s.far_slot = b0m ? (__ffs(b0m) - 1) : (32 + __ffs(b1m) - 1);
-                    s.far2 = mx;
-                }
-            }
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // Neighbour query.  One warp per (ray, slot).  Per layer the (2l+1)^3 cube is enumerated in x,y,z
 // order 32 cells at a time: each lane fetches one cell's [start, end) (non-ring / out-of-grid cells
@@ -228,7 +181,10 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
 
     // lane k (< K; K <= 32 per register set, larger K loops) keeps slot k
     // K up to 64 is supported with two slots per lane
-    KnnSlots st = {{-1, -1}, {0.f, 0.f}, 0, 0, 0.f};
+    int my_pid[2] = {-1, -1};
+    float my_d2[2] = {0.f, 0.f};
+    int seen = 0, far_slot = 0;
+    float far2 = 0.f;
     unsigned long long visited = 0;
 
     for (int layer = 0; layer < n_layers; ++layer) {
@@ -290,214 +246,49 @@ __global__ void __launch_bounds__(256) knn_kernel(const float* __restrict__ xyz,
                         in = (r2 == 0.f) || (d2 <= r2);
                     }
                 }
-                knn_insert(st, in, d2, pid, K, lane);
+                unsigned m = __ballot_sync(kFull, in);
+                while (m) {
+                    if (seen >= K) {   // slots full: only candidates closer than the current maximum can change anything,
+                        m &= __ballot_sync(kFull, in && d2 < far2);   // and that maximum never grows - drop the rest at once
+                        if (!m) break;
+                    }
+                    int src = __ffs(m) - 1;
+                    m &= m - 1;
+                    float cd = __shfl_sync(kFull, d2, src);
+                    int cp = __shfl_sync(kFull, pid, src);
+                    if (seen < K) {
+                        if (lane == (seen & 31)) { my_pid[seen >> 5] = cp; my_d2[seen >> 5] = cd; }
+                        if (cd > far2) { far2 = cd; far_slot = seen; }
+                        ++seen;
+                    } else {
+                        ++seen;
+                        if (cd < far2) {
+                            if (lane == (far_slot & 31)) { my_pid[far_slot >> 5] = cp; my_d2[far_slot >> 5] = cd; }
+                            // rescan: first slot holding the maximum, only if it exceeds the new value (:511-517)
+                            float v0 = (lane < K) ? my_d2[0] : -1.f;
+                            float v1 = (lane + 32 < K) ? my_d2[1] : -1.f;
+                            float mx = fmaxf(v0, v1);
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(kFull, mx, o));
+                            far2 = cd;
+                            if (mx > cd) {
+                                unsigned b0m = __ballot_sync(kFull, v0 == mx);
+                                unsigned b1m = __ballot_sync(kFull, v1 == mx);
+                                far_slot = b0m ? (__ffs(b0m) - 1) : (32 + __ffs(b1m) - 1);
+                                far2 = mx;
+                            }
+                        }
+                    }
+                }
             }
         }
-        if (!kFrustum && st.seen >= K) break;  // tested only after a whole layer (:526); the frustum kernel has no such exit
+        if (!kFrustum && seen >= K) break;  // tested only after a whole layer (:526); the frustum kernel has no such exit
     }
-    for (int k = lane; k < K; k += 32) out[k] = st.pid[k >> 5];
-    any_seen |= st.seen > 0;
+    for (int k = lane; k < K; k += 32) out[k] = my_pid[k >> 5];
+    any_seen |= seen > 0;
     if (kCount && n_cand && lane == 0) atomicAdd(n_cand, visited);
     }
     if (!kFrustum && lane == 0 && any_seen) ray_any[ray] = 1;  // benign same-value race across the ray's warps
-}
-
-// ------------------------------------------------------------------------------------------------
-// Shared-memory-staged neighbour query (world-coordinate grid).  One block per ray; a warp takes RUNS of kRun consecutive
-// hit samples of the ray.  Consecutive samples are about a voxel apart, so their (2L+1)^3 neighbourhoods overlap: the run's
-// bounding box of cells (the box of its two end samples, dilated by L, clipped to the grid) is staged ONCE - per cell the
-// clipped bucket length as a prefix sum, then every point of those buckets as (x, y, z, index) - with all lanes loading in
-// parallel (three dependent rounds of loads per run instead of three per sample), and each sample of the run then runs the
-// reference's layered search (same cell order, same bucket order, same insertion rule: knn_insert) against shared memory
-// only.  A run whose box or point count exceeds the staging buffers searches global memory like knn_kernel.
-// Bit-identical to knn_kernel by construction: the candidate SEQUENCE of every sample is unchanged.
-// ------------------------------------------------------------------------------------------------
-constexpr int kStWarps = 4;      // warps per block (ray)
-constexpr int kRun = 4;          // consecutive hit samples per run
-constexpr int kCellCap = 256;    // staged cells per warp
-constexpr int kPtCap = 320;      // staged points per warp
-
-template <bool kCount>
-__global__ void __launch_bounds__(32 * kStWarps) knn_staged_kernel(const float* __restrict__ xyz, QGrid g, const int* __restrict__ cell_start,
-                                                                   const int* __restrict__ bucket, const int* __restrict__ grid_info,
-                                                                   const float* __restrict__ loc_w, const int* __restrict__ hit_count,
-                                                                   int64_t n_rays, int SR, int K, int n_layers, float r2,
-                                                                   int* __restrict__ sample_pidx, int* __restrict__ ray_any,
-                                                                   unsigned long long* __restrict__ n_cand) {
-    __shared__ int s_off[kStWarps][kCellCap + 1];    // prefix sum of the staged cells' (clipped) bucket lengths, box order
-    __shared__ int s_start[kStWarps][kCellCap];      // bucket offset of each staged cell
-    __shared__ float4 s_pt[kStWarps][kPtCap];        // staged points: x, y, z, index bits
-    const int64_t ray = blockIdx.x;
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int hits = min(hit_count[ray], SR);
-    for (int i = hits * K + (int)threadIdx.x; i < SR * K; i += blockDim.x) sample_pidx[ray * SR * K + i] = -1;
-    if (hits == 0) return;
-    const int slot0_cell = grid_info[PN_GI_SLOT0_CELL];
-    const int L = n_layers - 1;
-    int* off = s_off[wib];
-    int* cst = s_start[wib];
-    float4* pts = s_pt[wib];
-    bool any_seen = false;
-    unsigned long long visited = 0;
-    for (int a = wib * kRun; a < hits; a += kStWarps * kRun) {
-        const int nrun = min(kRun, hits - a);
-        // lane i < nrun holds sample a + i
-        float mqx = 0.f, mqy = 0.f, mqz = 0.f;
-        int mfx = 0, mfy = 0, mfz = 0;
-        if (lane < nrun) {
-            const int64_t w = ray * SR + a + lane;
-            mqx = loc_w[3 * w]; mqy = loc_w[3 * w + 1]; mqz = loc_w[3 * w + 2];
-            mfx = voxel_coord(mqx, g.sx, g.vx); mfy = voxel_coord(mqy, g.sy, g.vy); mfz = voxel_coord(mqz, g.sz, g.vz);
-        }
-        // bounding box of the run's voxels (samples lie on a line: the box of the end samples holds the others, but a
-        // min / max over the run costs the same and assumes nothing)
-        int lox = mfx, loy = mfy, loz = mfz, hix = mfx, hiy = mfy, hiz = mfz;
-        {
-            const int f0x = __shfl_sync(kFull, mfx, 0), f0y = __shfl_sync(kFull, mfy, 0), f0z = __shfl_sync(kFull, mfz, 0);
-            if (lane >= nrun) { lox = hix = f0x; loy = hiy = f0y; loz = hiz = f0z; }
-#pragma unroll
-            for (int o = 1; o < kRun; o <<= 1) {
-                lox = min(lox, __shfl_xor_sync(kFull, lox, o)); hix = max(hix, __shfl_xor_sync(kFull, hix, o));
-                loy = min(loy, __shfl_xor_sync(kFull, loy, o)); hiy = max(hiy, __shfl_xor_sync(kFull, hiy, o));
-                loz = min(loz, __shfl_xor_sync(kFull, loz, o)); hiz = max(hiz, __shfl_xor_sync(kFull, hiz, o));
-            }
-            lox = __shfl_sync(kFull, lox, 0); hix = __shfl_sync(kFull, hix, 0);
-            loy = __shfl_sync(kFull, loy, 0); hiy = __shfl_sync(kFull, hiy, 0);
-            loz = __shfl_sync(kFull, loz, 0); hiz = __shfl_sync(kFull, hiz, 0);
-        }
-        lox = max(lox - L, 0); loy = max(loy - L, 0); loz = max(loz - L, 0);
-        hix = min(hix + L, g.dx - 1); hiy = min(hiy + L, g.dy - 1); hiz = min(hiz + L, g.dz - 1);
-        const int bx = hix - lox + 1, by = hiy - loy + 1, bz = hiz - loz + 1;
-        const int ncell = (bx > 0 && by > 0 && bz > 0) ? bx * by * bz : 0;
-        bool staged = ncell > 0 && ncell <= kCellCap && bx <= kCellCap && by <= kCellCap && bz <= kCellCap;
-        if (staged) {
-            // round 1: the cells' bucket ranges (every load of the round in flight at once) -> prefix sum in box order
-            constexpr int kCellIter = kCellCap / 32;
-            int c_start[kCellIter], c_cnt[kCellIter];
-#pragma unroll
-            for (int j = 0; j < kCellIter; ++j) {
-                const int bi = 32 * j + lane;
-                c_start[j] = 0; c_cnt[j] = 0;
-                if (bi < ncell) {
-                    const int ix = bi / (by * bz), r = bi - ix * (by * bz), iy = r / bz, iz = r - iy * bz;
-                    const int cell = ((lox + ix) * g.dy + (loy + iy)) * g.dz + (loz + iz);
-                    c_start[j] = cell_start[cell];
-                    c_cnt[j] = cell == slot0_cell ? -1 : cell_start[cell + 1];   // `if (voxel_idx > 0)` of fill_occ2pnts (:372)
-                }
-            }
-            int running = 0;
-#pragma unroll
-            for (int j = 0; j < kCellIter; ++j) {
-                if (32 * j < ncell) {                        // warp-uniform
-                    const int bi = 32 * j + lane;
-                    const int cnt = (bi < ncell && c_cnt[j] >= 0) ? min(c_cnt[j] - c_start[j], g.P) : 0;
-                    const int incl = warp_scan_incl(cnt, lane);
-                    if (bi < ncell) { off[bi] = running + incl - cnt; cst[bi] = c_start[j]; }
-                    running += __shfl_sync(kFull, incl, 31);
-                }
-            }
-            if (lane == 0) off[ncell] = running;
-            staged = running <= kPtCap;
-            __syncwarp();
-            if (staged) {
-                // rounds 2 + 3: the bucket entries, then the points - again all loads of a round before the first use
-                constexpr int kPtIter = kPtCap / 32;
-                int p_id[kPtIter];
-#pragma unroll
-                for (int j = 0; j < kPtIter; ++j) {
-                    const int p = 32 * j + lane;
-                    p_id[j] = -1;
-                    if (p < running) {
-                        int lo = 0, hi = ncell;             // last cell with off[cell] <= p (its bucket is non-empty)
-                        while (hi - lo > 1) {
-                            const int mid = (lo + hi) >> 1;
-                            if (off[mid] <= p) lo = mid; else hi = mid;
-                        }
-                        p_id[j] = bucket[cst[lo] + (p - off[lo])];
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < kPtIter; ++j) {
-                    const int p = 32 * j + lane;
-                    if (p < running) {
-                        const int64_t pid = p_id[j];
-                        pts[p] = make_float4(xyz[3 * pid], xyz[3 * pid + 1], xyz[3 * pid + 2], __int_as_float(p_id[j]));
-                    }
-                }
-                __syncwarp();
-            }
-        }
-        for (int si = 0; si < nrun; ++si) {
-            const float qx = __shfl_sync(kFull, mqx, si), qy = __shfl_sync(kFull, mqy, si), qz = __shfl_sync(kFull, mqz, si);
-            const int fx = __shfl_sync(kFull, mfx, si), fy = __shfl_sync(kFull, mfy, si), fz = __shfl_sync(kFull, mfz, si);
-            KnnSlots st = {{-1, -1}, {0.f, 0.f}, 0, 0, 0.f};
-            for (int layer = 0; layer < n_layers; ++layer) {
-                const int side = 2 * layer + 1, cube = side * side * side;
-                for (int c0 = 0; c0 < cube; c0 += 32) {
-                    // --- one cell per lane, x,y,z order
-                    const int ci = c0 + lane;
-                    int start = 0, cnt = 0;
-                    if (ci < cube) {
-                        const int ddx = ci / (side * side) - layer, rem = ci % (side * side);
-                        const int ddy = rem / side - layer, ddz = rem % side - layer;
-                        const bool visit = max(abs(ddx), max(abs(ddy), abs(ddz))) == layer;
-                        const int cx = fx + ddx, cy = fy + ddy, cz = fz + ddz;
-                        if (visit && cx >= 0 && cx < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz) {
-                            if (staged) {
-                                const int bi = ((cx - lox) * by + (cy - loy)) * bz + (cz - loz);
-                                start = off[bi];
-                                cnt = off[bi + 1] - start;
-                            } else {
-                                const int cell = (cx * g.dy + cy) * g.dz + cz;
-                                start = cell_start[cell];
-                                cnt = min(cell_start[cell + 1] - start, g.P);
-                                if (cell == slot0_cell) cnt = 0;
-                            }
-                        }
-                    }
-                    const int incl = warp_scan_incl(cnt, lane);
-                    const int excl = incl - cnt;
-                    const int total = __shfl_sync(kFull, incl, 31);
-                    if (kCount) visited += total;
-                    // --- candidates, 32 per step, in sequence order
-                    for (int b0 = 0; b0 < total; b0 += 32) {
-                        const int c = b0 + lane;
-                        int lo = 0;   // owner cell of candidate c: the LAST lane with excl <= c (excl is non-decreasing)
-#pragma unroll
-                        for (int step = 16; step > 0; step >>= 1) {
-                            const int probe = __shfl_sync(kFull, excl, lo + step);
-                            if (probe <= c) lo += step;
-                        }
-                        const int o_start = __shfl_sync(kFull, start, lo), o_excl = __shfl_sync(kFull, excl, lo);
-                        bool in = false;
-                        int pid = -1;
-                        float d2 = 0.f;
-                        if (c < total) {
-                            float px, py, pz;
-                            if (staged) {
-                                const float4 pt = pts[o_start + (c - o_excl)];
-                                px = pt.x; py = pt.y; pz = pt.z; pid = __float_as_int(pt.w);
-                            } else {
-                                pid = bucket[o_start + (c - o_excl)];
-                                px = xyz[3 * (int64_t)pid]; py = xyz[3 * (int64_t)pid + 1]; pz = xyz[3 * (int64_t)pid + 2];
-                            }
-                            const float x = __fsub_rn(px, qx), y = __fsub_rn(py, qy), z = __fsub_rn(pz, qz);
-                            d2 = __fmaf_rn(z, z, __fmaf_rn(x, x, __fmul_rn(y, y)));
-                            in = (r2 == 0.f) || (d2 <= r2);
-                        }
-                        knn_insert(st, in, d2, pid, K, lane);
-                    }
-                }
-                if (st.seen >= K) break;  // tested only after a whole layer (:526)
-            }
-            int* out = sample_pidx + (ray * SR + a + si) * K;
-            for (int k = lane; k < K; k += 32) out[k] = st.pid[k >> 5];
-            any_seen |= st.seen > 0;
-        }
-        __syncwarp();   // the next run overwrites the staging buffers
-    }
-    if (kCount && n_cand && lane == 0 && visited) atomicAdd(n_cand, visited);
-    if (lane == 0 && any_seen) ray_any[ray] = 1;  // benign same-value race across the ray's warps
 }
 
 __global__ void __launch_bounds__(256) w2pers_kernel(const float* __restrict__ xyz, int64_t n, const float* __restrict__ rot,
@@ -673,7 +464,8 @@ extern "C" int pn_ray_sample(const float* campos, const float* raydir, const flo
     return PN_OK;
 }
 
-static int knn_query_impl(bool staged, const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
+namespace pn { int g_knn_threads = 256; }
+extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
                             const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
                             const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
                             float radius_limit2, int32_t* sample_pidx, int32_t* ray_any, unsigned long long* n_candidates,
@@ -685,39 +477,19 @@ static int knn_query_impl(bool staged, const float* xyz, const pn_grid_params* p
     if (n_rays <= 0) return PN_OK;
     cudaStream_t st = (cudaStream_t)stream;
     PN_CUDA(cudaMemsetAsync(ray_any, 0, n_rays * sizeof(int), st));
-    const unsigned blocks = (unsigned)n_rays;
-    if (!staged) {
-        if (n_candidates)
-            knn_kernel<true, false><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays, SR, K,
-                                                            n_layers, radius_limit2, sample_pidx, ray_any, n_candidates, FrustumArgs{});
-        else
-            knn_kernel<false, false><<<blocks, 256, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays, SR, K,
-                                                             n_layers, radius_limit2, sample_pidx, ray_any, nullptr, FrustumArgs{});
-    } else if (n_candidates)
-        knn_staged_kernel<true><<<blocks, 32 * kStWarps, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays,
-                                                                  SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates);
+    unsigned blocks = (unsigned)n_rays;
+    // (pn_debug_gemm_flags(2048) selects 128-thread blocks, which fit next to a resident GEMM CTA of 576 threads x 96
+    // registers when the next batch's query runs under this batch's backward (ray_shard.py); measured: no difference there,
+    // and 110 us instead of 74 us when the query runs alone)
+    const int kKnnThreads = g_knn_threads;
+    if (n_candidates)
+        knn_kernel<true, false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, n_candidates, FrustumArgs{});
     else
-        knn_staged_kernel<false><<<blocks, 32 * kStWarps, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays,
-                                                                   SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr);
+        knn_kernel<false, false><<<blocks, kKnnThreads, 0, st>>>(xyz, to_q(params), cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count,
+                                                 n_rays, SR, K, n_layers, radius_limit2, sample_pidx, ray_any, nullptr, FrustumArgs{});
     PN_LAUNCH_CHECK("knn_query");
     return PN_OK;
-}
-
-extern "C" int pn_knn_query(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
-                            const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
-                            const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
-                            float radius_limit2, int32_t* sample_pidx, int32_t* ray_any, unsigned long long* n_candidates,
-                            void* stream) {
-    return knn_query_impl(true, xyz, params, cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays, SR, K, n_layers, radius_limit2,
-                          sample_pidx, ray_any, n_candidates, stream);
-}
-extern "C" int pn_knn_query_direct(const float* xyz, const pn_grid_params* params, const int32_t* cell_start,
-                                   const int32_t* bucket_pidx, const int32_t* grid_info, const float* sample_loc_w,
-                                   const int32_t* hit_count, int64_t n_rays, int32_t SR, int32_t K, int32_t n_layers,
-                                   float radius_limit2, int32_t* sample_pidx, int32_t* ray_any, unsigned long long* n_candidates,
-                                   void* stream) {
-    return knn_query_impl(false, xyz, params, cell_start, bucket_pidx, grid_info, sample_loc_w, hit_count, n_rays, SR, K, n_layers, radius_limit2,
-                          sample_pidx, ray_any, n_candidates, stream);
 }
 
 extern "C" int pn_frustum_sample(const int32_t* pixel_idx, int64_t n_rays, int32_t SR, const pn_grid_params* params,

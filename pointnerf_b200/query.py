@@ -119,17 +119,15 @@ def ray_sample(grid, campos, raydir, ts, SR, want_t=False):
     return (loc, hit, st) if want_t else (loc, hit)
 
 
-def knn_query(grid, xyz, sample_loc_w, hit_count, K, n_layers, radius_limit2, count_candidates=False, direct=False):
-    """-> sample_pidx int32 [R,SR,K], ray_any int32 [R] (, candidates visited).  direct=True: the unstaged kernel
-    (pn_knn_query_direct), same outputs - tests and A / B timing."""
+def knn_query(grid, xyz, sample_loc_w, hit_count, K, n_layers, radius_limit2, count_candidates=False):
+    """-> sample_pidx int32 [R,SR,K], ray_any int32 [R] (, candidates visited)."""
     lib = _lib.lib()
-    entry = lib.pn_knn_query_direct if direct else lib.pn_knn_query
     R, SR = int(sample_loc_w.shape[0]), int(sample_loc_w.shape[1])
     dev = xyz.device
     pidx = torch.empty((R, SR, K), dtype=torch.int32, device=dev)
     ray_any = torch.empty((R,), dtype=torch.int32, device=dev)
     cand = torch.zeros(1, dtype=torch.int64, device=dev) if count_candidates else None
-    _lib.check(entry(_lib.ptr(xyz), ctypes.byref(grid.params), _lib.ptr(grid.cell_start),
+    _lib.check(lib.pn_knn_query(_lib.ptr(xyz), ctypes.byref(grid.params), _lib.ptr(grid.cell_start),
                                 _lib.ptr(grid.bucket_pidx), _lib.ptr(grid.info), _lib.ptr(sample_loc_w),
                                 _lib.ptr(hit_count), R, SR, int(K), int(n_layers), float(radius_limit2),
                                 _lib.ptr(pidx), _lib.ptr(ray_any), _lib.ptr(cand), _lib.stream()), "pn_knn_query")

@@ -245,27 +245,3 @@ def test_sample_depths_sequential_fallback_on_wild_segments(cuda_dev):
     _lib.check(_lib.lib().pn_sample_depths(_lib.ptr(base.to(cuda_dev)), _lib.ptr(u.reshape(R, D).contiguous().to(cuda_dev)), R, D, near, jitter,
                                            _lib.ptr(ts), _lib.stream()), "pn_sample_depths")
     assert torch.equal(ts.cpu(), want)
-
-
-@pytest.mark.parametrize("name,rays", [("cfg2", 4096), ("tiny3", 600), ("tiny4", 600)])
-def test_staged_knn_equals_direct_kernel(cuda_dev, name, rays):
-    """pn_knn_query stages each run of 4 consecutive samples' neighbourhood in shared memory; pn_knn_query_direct reads global
-    memory per sample.  Same candidate sequence -> the same slots, ray flags and candidate counts, bit for bit, on a full
-    cfg2 training batch (short buckets: nearly every run staged) and on the deep-bucket miniatures (P = 30 / 26: runs whose
-    320-point buffer overflows take the global path inside the staged kernel)."""
-    opt, tables = syn.make_scene(name)
-    cam = syn.make_camera(name)
-    raydir, pix = syn.make_rays(cam, syn.random_pixels(cam, rays, seed=5))
-    d = cuda_dev
-    q = query.lighting_fast_querier(d, opt)
-    xyz = tables["xyz"].reshape(-1, 3).contiguous().to(d)
-    grid = q.grid_for(xyz)
-    uni = torch.rand(1, raydir.shape[1], opt.z_depth_dim, generator=torch.Generator().manual_seed(1)).to(d)
-    ts = query.middle_point_ts(raydir.to(d), opt.z_depth_dim, cam["near"], cam["far"], jitter=0.3, uniform=uni)
-    loc_w, hit = query.ray_sample(grid, cam["campos"].reshape(3).to(d), raydir.reshape(-1, 3).contiguous().to(d), ts[0], opt.SR)
-    n_layers = (int(opt.kernel_size[0]) + 1) // 2
-    r2 = float(grid.hp["radius_limit2"])
-    a = query.knn_query(grid, xyz, loc_w, hit, opt.K, n_layers, r2, count_candidates=True)
-    b = query.knn_query(grid, xyz, loc_w, hit, opt.K, n_layers, r2, count_candidates=True, direct=True)
-    assert int((a[0] >= 0).sum()) > 1000
-    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and int(a[2]) == int(b[2])
