@@ -654,6 +654,36 @@ def frustum_bench(dev):
                                               cam["far"], None, cam["campos"].to(dev), cam["camrotc2w"].to(dev)))
         entry.update(gpu_ms_kernels=round(ms_raw, 4), gpu_ms_query_points=round(ms_api, 4), rays_per_s=round(R / ms_api * 1e3, 1))
         res[tag] = entry
+    # one training step on this querier: FusedTrainStep (two CUDA graphs; the per-view grid build sits in the query graph)
+    try:
+        import copy
+        from pointnerf_b200.neural_points import NeuralPointsRayMarching
+        from pointnerf_b200.train_step import FusedTrainStep
+        topt = copy.copy(opt)
+        topt.is_train, topt.shpnt_jitter = 1, "uniform"
+        torch.manual_seed(0)
+        model = NeuralPointsRayMarching(topt, device=dev)
+        model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                                       tables["points_conf"], Rw2c=tables["Rw2c"])
+        R, C = 4096, int(topt.shading_color_channel_num)
+        g = torch.Generator().manual_seed(11)
+        bg = torch.nn.Parameter(torch.rand(C, generator=g).to(dev))
+        camd = dict(campos=cam["campos"].to(dev), camrotc2w=cam["camrotc2w"].to(dev), near=cam["near"], far=cam["far"])
+        pool = [dict(cam=camd, pixel_idx=torch.as_tensor(syn.random_pixels(cam, R, seed=50 + i), dtype=torch.int32).to(dev),
+                     gt=torch.rand(1, R, C, generator=g).to(dev), uniform=torch.rand(1, R, int(topt.SR), generator=g).to(dev)) for i in range(4)]
+        st = FusedTrainStep(model, bg, R, cam["near"], cam["far"], view=dict(h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"]))
+        st.calibrate(pool)
+        it = [0]
+
+        def one():
+            b = pool[it[0] % len(pool)]
+            it[0] += 1
+            st(b["cam"], None, b["gt"], b["uniform"], pixel_idx=b["pixel_idx"])
+        ms = timed(one, reps=20)
+        res["train_step_4096"] = {"ms_per_step": round(ms, 4), "rays_per_s": round(R / ms * 1e3, 1), "caps": list(st.caps), "overflows": st.overflows,
+                                  "note": "fwd + bwd of 4096 pixel-indexed rays, uniform depth jitter, grid of the view rebuilt every step"}
+    except Exception as e:      # a leg, not the headline: report and go on
+        res["train_step_4096"] = {"error": repr(e)[:300]}
     empty = torch.zeros((0, 2), dtype=torch.int32, device=dev)
     res["grid_build_ms"] = round(timed(lambda: q.query_raw(empty, xp_d, hp)), 4)
     V, N = int(np.prod(hp["scaled_vdim"])), int(xp_d.shape[0])

@@ -304,8 +304,8 @@ class NeuralPointsRayMarching(nn.Module):
         the ones the reference drops (ray_mask 0) simply keep no samples.  ``uniform``: [1,R,SR] draw of the jitter."""
         nps, o = self.neural_points, self.opt
         if pixel_idx is None or h is None or w is None or intrinsic is None:
-            raise NotImplementedError("wcoord_query = 0 queries by pixel: pass pixel_idx, h, w and intrinsic (the ray-direction "
-                                      "only callers - render_frame, RayShardedStep - are world-coordinate)")
+            raise NotImplementedError("wcoord_query = 0 queries by pixel: pass pixel_idx, h, w and intrinsic (RayShardedStep, which "
+                                      "knows rays by direction only, is world-coordinate)")
         q = nps.querier
         near, far = _as_reference_scalar(near, "min"), _as_reference_scalar(far, "max")
         h, w = _as_reference_scalar(h, "max"), _as_reference_scalar(w, "max")

@@ -22,6 +22,7 @@ asynchronous copy of the counts, and the capacities are grown for the following 
 """
 import warnings
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -77,7 +78,10 @@ def color_loss_ray_weights(ray_any, items, weights, channels, global_rays, maske
 class FusedTrainStep:
     """One training step (query -> forward -> colour loss -> backward) of ``NeuralPointsRayMarching`` as two CUDA graphs.
 
-    model:     NeuralPointsRayMarching on the world-coordinate querier (the tables, grid, MLP it holds are used in place)
+    model:     NeuralPointsRayMarching (the tables, grid, MLP it holds are used in place).  On the perspective-frustum querier
+               (``opt.wcoord_query = 0``, the DTU feed-forward scripts) rays are addressed by ``pixel_idx`` int32 [R,2] instead
+               of ``raydir``, and ``view=dict(h=, w=, intrinsic=)`` fixes the frustum the per-view grid is built in (like
+               near / far it is baked into the captured step); sample jitter: ``shpnt_jitter`` passfunc or uniform
     bg_color:  nn.Parameter [C] (receives a gradient) or a plain tensor
     rays:      rays per step on this rank (static: the graphs are captured for it); near / far: the camera's depth range
     color_loss_items / color_loss_weights: as the reference's options of the same names (base_rendering_model.py:543-606)
@@ -92,21 +96,34 @@ class FusedTrainStep:
     """
 
     def __init__(self, model, bg_color, rays, near, far, color_loss_items=("coarse_raycolor",), color_loss_weights=(1.0,),
-                 caps=None, graph=True, group=None, pipeline=False, local_only=False, sparse_exchange=True, exchange_in_step=True):
+                 caps=None, graph=True, group=None, pipeline=False, local_only=False, sparse_exchange=True, exchange_in_step=True,
+                 view=None):
         o = model.opt
-        if getattr(o, "wcoord_query", 1) <= 0:
-            raise NotImplementedError("FusedTrainStep drives the world-coordinate querier")
+        self.frustum = getattr(o, "wcoord_query", 1) <= 0
         self.model, self.bg, self.R, self.near, self.far = model, bg_color, int(rays), float(near), float(far)
+        self.hp = None
+        if self.frustum:
+            if view is None:
+                raise ValueError("FusedTrainStep on the frustum querier (wcoord_query = 0) needs view=dict(h=, w=, intrinsic=)")
+            if o.is_train > 0 and o.shpnt_jitter not in ("passfunc", "uniform"):
+                raise NotImplementedError("FusedTrainStep: shpnt_jitter %r draws inside the query; passfunc / uniform take the draw as an input"
+                                          % (o.shpnt_jitter,))
+            intr = view["intrinsic"]
+            intr = intr.cpu().numpy()[0] if torch.is_tensor(intr) else np.asarray(intr)
+            # the frustum's hyper-parameters are host arithmetic on the view (query_point_indices.py:34-98): once, here
+            self.hp = model.neural_points.querier.get_hyperparameters(view["h"], view["w"], intr, near, far)
         self.items, self.item_weights = tuple(color_loss_items), tuple(float(w) for w in color_loss_weights)
         assert len(self.items) == len(self.item_weights)
         self.caps, self.use_graph, self.group = (tuple(int(c) for c in caps) if caps is not None else None), bool(graph), group
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized() and not local_only) else 1
         self.dev = model.neural_points.xyz.device
         R, D, C = self.R, int(o.z_depth_dim), int(o.shading_color_channel_num)
-        self.jitter = o.is_train > 0
+        self.jitter = o.is_train > 0 and not (self.frustum and o.shpnt_jitter == "passfunc")
         # static inputs: ONE flat buffer [campos 3 | camrotc2w 9 | raydir R*3 | gt R*C | jitter draw R*D], segments padded to
-        # 64 floats - a loader uploads a batch with one copy (load_packed); the graphs read the views
-        sizes = [3, 9, R * 3, R * C] + ([R * D] if self.jitter else [])
+        # 64 floats - a loader uploads a batch with one copy (load_packed); the graphs read the views.  Frustum querier: the
+        # ray segment holds the pixel indices (R*2 int32 bit patterns) and the draw is per kept sample (R*SR)
+        SRo = int(o.SR)
+        sizes = [3, 9, R * (2 if self.frustum else 3), R * C] + ([R * (SRo if self.frustum else D)] if self.jitter else [])
         offs, n = [], 0
         for sz in sizes:
             offs.append(n)
@@ -114,14 +131,17 @@ class FusedTrainStep:
         self.inbuf = torch.zeros(n, dtype=torch.float32, device=self.dev)
         self.in_offsets, self.in_sizes = offs, sizes
         v = [self.inbuf[a:a + sz] for a, sz in zip(offs, sizes)]
-        self.campos, self.rot, self.raydir, self.gt = v[0].view(1, 3), v[1].view(1, 3, 3), v[2].view(1, R, 3), v[3].view(1, R, C)
-        self.uniform = v[4].view(1, R, D) if self.jitter else None
+        self.campos, self.rot, self.gt = v[0].view(1, 3), v[1].view(1, 3, 3), v[3].view(1, R, C)
+        self.raydir = None if self.frustum else v[2].view(1, R, 3)
+        self.pix = v[2].view(torch.int32).view(R, 2) if self.frustum else None
+        self.uniform = (v[4].view(1, R, SRo) if self.frustum else v[4].view(1, R, D)) if self.jitter else None
         self.rot.copy_(torch.eye(3, device=self.dev)[None])
         # the batch the step works on: the inputs and query results are PUBLISHED into these persistent buffers by the query
         # graph (or by the query branch at the end of a pipelined step), so that `inbuf` is free for the next batch
         self.cur_in = torch.zeros_like(self.inbuf)
         cv = [self.cur_in[a:a + sz] for a, sz in zip(offs, sizes)]
-        self.c_campos, self.c_rot, self.c_raydir, self.c_gt = cv[0].view(1, 3), cv[1].view(1, 3, 3), cv[2].view(1, R, 3), cv[3].view(1, R, C)
+        self.c_campos, self.c_rot, self.c_gt = cv[0].view(1, 3), cv[1].view(1, 3, 3), cv[3].view(1, R, C)
+        self.c_raydir = None if self.frustum else cv[2].view(1, R, 3)
         self.pipeline = bool(pipeline)
         self._primed = False
         self._side = None
@@ -150,13 +170,19 @@ class FusedTrainStep:
         self.grads = {}
 
     # ---- inputs -------------------------------------------------------------------------------------------------------
-    def set_inputs(self, cam, raydir, gt, uniform=None):
-        """Copies one batch into the static input buffers (device or pinned host tensors; asynchronous)."""
+    def set_inputs(self, cam, raydir, gt, uniform=None, pixel_idx=None):
+        """Copies one batch into the static input buffers (device or pinned host tensors; asynchronous).  Frustum querier:
+        ``pixel_idx`` int32 [.., R, 2] instead of ``raydir``, ``uniform`` [1,R,SR]."""
         if float(cam["near"]) != self.near or float(cam["far"]) != self.far:
             raise ValueError("near / far are baked into the captured step (%g, %g)" % (self.near, self.far))
         self.campos.copy_(cam["campos"].reshape(1, 3), non_blocking=True)
         self.rot.copy_(cam["camrotc2w"].reshape(1, 3, 3), non_blocking=True)
-        self.raydir.copy_(raydir.reshape(1, self.R, 3), non_blocking=True)
+        if self.frustum:
+            if pixel_idx is None:
+                raise ValueError("the frustum querier addresses rays by pixel_idx")
+            self.pix.copy_(pixel_idx.reshape(self.R, 2).to(torch.int32), non_blocking=True)
+        else:
+            self.raydir.copy_(raydir.reshape(1, self.R, 3), non_blocking=True)
         self.gt.copy_(gt.reshape(self.gt.shape), non_blocking=True)
         if self.jitter:
             if uniform is None:
@@ -173,10 +199,22 @@ class FusedTrainStep:
         m, o = self.model, self.model.opt
         nps = m.neural_points
         xyz = nps.xyz.detach()
-        raw = nps.querier.query_raw(xyz, self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
         q = {}
-        q["pidx"], q["loc_w"], q["ray_any"] = raw["sample_pidx"], raw["sample_loc_w"], raw["ray_any"]
-        q["loc_pers"] = _query.w2pers(q["loc_w"], self.rot[0], self.campos[0])
+        if self.frustum:
+            # per-view grid in perspective space -> column walk -> layered K-NN (no host sync), then the reference's torch tail:
+            # jitter of the sample depth, pers2w -> world positions and per-sample directions (query_point_indices.py:100-123)
+            qr = nps.querier
+            raw = qr.query_raw(self.pix, _query.w2pers(xyz, self.rot[0], self.campos[0]), self.hp)
+            loc_pers = raw["sample_loc"]
+            if self.uniform is not None:
+                loc_pers = qr.uniform(loc_pers[None], self.hp["vsize"], uniform=self.uniform)[0]
+            loc_w, dirs = qr.pers2w(loc_pers[None], self.rot, self.campos)
+            q["pidx"], q["loc_w"], q["loc_pers"], q["dirs"] = raw["sample_pidx"], loc_w[0].contiguous(), loc_pers.contiguous(), dirs[0].contiguous()
+            q["ray_any"] = raw["ray_mask"]       # the reference's ray mask on this querier: the ray's column holds an occupied depth
+        else:
+            raw = nps.querier.query_raw(xyz, self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
+            q["pidx"], q["loc_w"], q["ray_any"] = raw["sample_pidx"], raw["sample_loc_w"], raw["ray_any"]
+            q["loc_pers"] = _query.w2pers(q["loc_w"], self.rot[0], self.campos[0])
         R, SR, K = q["pidx"].shape
         cs = CompactSamples(q["pidx"], R * SR, K, caps=self.caps)
         q["sample_list"], q["pair_start"], q["pair_src"], q["slot_row"], q["counts"] = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row, cs.counts_dev
@@ -204,8 +242,9 @@ class FusedTrainStep:
         C = int(o.shading_color_channel_num)
         tabs = (nps.points_embeding, nps.points_color, nps.points_dir, nps.points_conf)
         T = int(nps.points_embeding.shape[-2])
-        call = _AggCall(agg._params(K, SR, True, o.vsize, True), nps.xyz.detach(), xyz_pers, nps.Rw2c.detach().contiguous(),
-                        pidx, q["loc_w"], q["loc_pers"], self.c_raydir[0], R * SR, T, True, False)
+        vsize = self.hp["vsize"] if self.frustum else o.vsize       # the frustum view's own voxel size feeds the distances
+        call = _AggCall(agg._params(K, SR, not self.frustum, vsize, True), nps.xyz.detach(), xyz_pers, nps.Rw2c.detach().contiguous(),
+                        pidx, q["loc_w"], q["loc_pers"], q["dirs"] if self.frustum else self.c_raydir[0], R * SR, T, True, False)
         call.S, call.M = int(q["sample_list"].numel()), int(q["pair_src"].numel())       # the capacities
         call.counts_dev = q["counts"]
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = q["sample_list"], q["pair_start"], q["pair_src"], q["slot_row"]
@@ -232,7 +271,7 @@ class FusedTrainStep:
         decoded, _, saved, saved_bytes = agg_forward_raw(call, *tables, weights)
         slot_row = q["slot_row"].view(R, SR)
         ray_valid = slot_row >= 0
-        ray_dist = ray_dist_from_samples(q["loc_pers"][None], ray_valid[None], o.vsize, o.raydist_mode_unit)[0]
+        ray_dist = ray_dist_from_samples(q["loc_pers"][None], ray_valid[None], vsize, o.raydist_mode_unit)[0]
         bg = self.bg.detach()
         bg_grad = bool(getattr(self.bg, "requires_grad", False))
         n_rows_dev = q["counts"][0:1]
@@ -333,8 +372,11 @@ class FusedTrainStep:
         mark = torch.empty(T, dtype=torch.int32, device=self.dev)
         cnt = torch.empty(1, dtype=torch.int32, device=self.dev)
         for b in batches:
-            self.set_inputs(b["cam"], b["raydir"], b["gt"], b.get("uniform"))
-            raw = nps.querier.query_raw(nps.xyz.detach(), self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
+            self.set_inputs(b["cam"], b.get("raydir"), b["gt"], b.get("uniform"), pixel_idx=b.get("pixel_idx"))
+            if self.frustum:
+                raw = {"sample_pidx": nps.querier.query_raw(self.pix, _query.w2pers(nps.xyz.detach(), self.rot[0], self.campos[0]), self.hp)["sample_pidx"]}
+            else:
+                raw = nps.querier.query_raw(nps.xyz.detach(), self.raydir, self.campos, self.near, self.far, uniform=self.uniform)
             R, SR, K = raw["sample_pidx"].shape
             S, M = CompactSamples(raw["sample_pidx"], R * SR, K).counts()
             s_max, m_max = max(s_max, S), max(m_max, M)
@@ -409,13 +451,13 @@ class FusedTrainStep:
             self.set_caps((max(self.caps[0], int(int(c[2]) * 1.25) + 4096), max(self.caps[1], int(int(c[3]) * 1.25) + 4096)))
             self.counts_host.zero_()
 
-    def __call__(self, cam=None, raydir=None, gt=None, uniform=None, packed=None):
+    def __call__(self, cam=None, raydir=None, gt=None, uniform=None, packed=None, pixel_idx=None):
         """Runs one step on the given batch (or on whatever ``set_inputs`` / ``load_packed`` put into the static buffers).
         Returns the loss (0-d device tensor, static: copy it before the next step if it is read later)."""
         if packed is not None:
             self.load_packed(packed)
-        elif raydir is not None:
-            self.set_inputs(cam, raydir, gt, uniform)
+        elif raydir is not None or pixel_idx is not None:
+            self.set_inputs(cam, raydir, gt, uniform, pixel_idx=pixel_idx)
         if self.pipeline and not self._primed:
             raise RuntimeError("FusedTrainStep(pipeline=True): call prime(first batch) before the first step")
         if not self.use_graph:
@@ -443,12 +485,12 @@ class FusedTrainStep:
             self._sync_masked_count()      # the count of the batch just queried normalises the NEXT step's loss
         return self.loss
 
-    def prime(self, cam=None, raydir=None, gt=None, uniform=None, packed=None):
+    def prime(self, cam=None, raydir=None, gt=None, uniform=None, packed=None, pixel_idx=None):
         """pipeline=True: loads the FIRST batch and runs its query; the following ``step(next batch)`` calls work on it."""
         if packed is not None:
             self.load_packed(packed)
-        elif raydir is not None:
-            self.set_inputs(cam, raydir, gt, uniform)
+        elif raydir is not None or pixel_idx is not None:
+            self.set_inputs(cam, raydir, gt, uniform, pixel_idx=pixel_idx)
         if self.use_graph:
             if self._g_step is None:
                 self._capture()

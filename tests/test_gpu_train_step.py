@@ -200,3 +200,53 @@ def test_color_loss_ray_weights_formula():
     assert torch.allclose(w, want, rtol=1e-6)
     w2 = color_loss_ray_weights(ray_any, ("ray_masked_x",), (1.0,), channels=4, global_rays=12, masked_count=torch.tensor([7.0]))
     assert torch.allclose(w2, m / (7 * 4), rtol=1e-6)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+@pytest.mark.parametrize("items,weights", [(("coarse_raycolor",), (1.0,)),
+                                           (("ray_masked_coarse_raycolor", "ray_miss_coarse_raycolor", "coarse_raycolor"), (1.0, 0.5, 0.25))])
+def test_fused_step_on_frustum_querier(cuda_dev, graph, items, weights):
+    """wcoord_query = 0 (the DTU feed-forward scripts): rays by pixel index, the per-view grid built inside the query graph,
+    per-sample directions from pers2w, the view's own voxel size, uniform depth jitter fed as an input - against the
+    autograd path of NeuralPointsRayMarching on the same querier (held to the CPU oracle by test_gpu_wcoord0_frustum.py)."""
+    dev = cuda_dev
+    opt, xyz, cam, pix = syn.frustum_case("dtu")
+    opt = copy.copy(opt)
+    opt.is_train, opt.shpnt_jitter = 1, "uniform"
+    _, tables = syn.make_scene("tiny")
+    torch.manual_seed(0)
+    model = NeuralPointsRayMarching(opt, device=dev)
+    with torch.no_grad():
+        model.aggregator.alpha_branch[0].bias.fill_(60.0)
+    model.neural_points.set_points(tables["xyz"], tables["points_embeding"], tables["points_color"], tables["points_dir"],
+                                   tables["points_conf"], Rw2c=tables["Rw2c"])
+    R, C = 300, opt.shading_color_channel_num
+    g = torch.Generator().manual_seed(3)
+    bg = torch.nn.Parameter(torch.rand(C, generator=g).to(dev))
+    view = dict(h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"])
+    camd = dict(campos=cam["campos"].to(dev), camrotc2w=cam["camrotc2w"].to(dev), near=cam["near"], far=cam["far"])
+    step = FusedTrainStep(model, bg, R, cam["near"], cam["far"], color_loss_items=items, color_loss_weights=weights, graph=graph, view=view)
+    batches = []
+    for b in range(3):
+        sel = torch.randperm(pix.shape[1], generator=g)[:R]
+        batches.append(dict(cam=camd, pixel_idx=pix[:, sel].to(dev), gt=torch.rand(1, R, C, generator=g).to(dev),
+                            uniform=torch.rand(1, R, opt.SR, generator=g).to(dev)))
+    step.calibrate(batches, headroom=1.5, granule=256)
+    n_const = 1e-6 * len(items)
+    for b in batches:
+        for p in list(model.parameters()) + [bg]:
+            p.grad = None
+        out = model(camd["campos"], None, bg_color=bg, camrotc2w=camd["camrotc2w"], pixel_idx=b["pixel_idx"], near=cam["near"], far=cam["far"],
+                    h=cam["h"], w=cam["w"], intrinsic=cam["intrinsic"], uniform=b["uniform"].clone())
+        assert 0 < int((out["ray_mask"] > 0).sum()) < R
+        loss_ref = _reference_losses(out, b["gt"], items, weights)
+        loss_ref.backward()
+        g_ref = _fused_grads(model, bg)
+        loss = step(b["cam"], None, b["gt"], b["uniform"], pixel_idx=b["pixel_idx"])
+        loss_ref = float(loss_ref.detach())
+        assert abs(float(loss) + n_const - loss_ref) <= 2e-6 * abs(loss_ref) + 1e-9
+        assert torch.equal(step.out["coarse_raycolor"], out["coarse_raycolor"].detach())
+        got = _fused_grads(model, bg)
+        for n in g_ref:
+            assert_close(got[n].reshape(g_ref[n].shape), g_ref[n], "frustum step grad " + n, tol=1e-5)
+    assert step.overflows == 0
