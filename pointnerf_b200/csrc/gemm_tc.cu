@@ -11,6 +11,8 @@
 //   warp 8: one elected thread issues tcgen05.mma and commits to mbarriers.
 // gemm_tn_tc:  C[n, k] = sum_m A[m, n] * B[m, k]                (weight gradients; both operands MN-major)
 //   CTA tile 128(n) x BK(k) over a slice of the reduction rows m; fixed-order second-stage reduction.
+#include <cuda.h>
+
 #include "gemm.cuh"
 #include "tc.cuh"
 
@@ -297,7 +299,7 @@ constexpr int IMG2_SMEM = NS2 * A_STAGE + NS2 * B2_STAGE + kEpiWarps * SLAB_BYTE
 }  // namespace
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
-    gemm_nt_img2_kernel(GemmNT g, int BN, int n_tiles_n) {
+    gemm_nt_img2_kernel(GemmNT g, int BN, int n_tiles_n, const __grid_constant__ CUtensorMap tmC, int tma_store) {
     extern __shared__ char smem_raw[];
     char* smem = (char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     char* smA = smem;
@@ -317,8 +319,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
     const int n_ptiles_total = (int)((g.M + 2 * TBM - 1) / (2 * TBM)) * n_tiles_n;
     const uint32_t b_block = (uint32_t)(2 * BN * 128);    // image block of one (n tile, K chunk)
     // Work items.  Tile i of the (row tile, n tile) grid goes to pair i % n_pairs; the tiles of the LAST, partial wave (rem of
-    // them - the other pairs would idle for a whole tile time) are cut along n into ns column slices of BN / ns, one per pair:
-    // the tail then costs 1 / ns of a tile.  S = 19 K sample rows are 76 row tiles on 74 pairs: 1.25 tile times instead of 2.
+    // them, the other pairs would idle for a whole tile time) are cut along n into ns column slices of BN / ns, one per pair:
+    // the tail then costs 1 / ns of a tile.  At S = 19 K sample rows (76 row tiles on 74 pairs) that is 1.25 tile times
+    // instead of 2; at M = 135 K pair rows 7.25 instead of 8.
     const int full_waves = n_ptiles_total / n_pairs, rem = n_ptiles_total - full_waves * n_pairs;
     int ns = 1;
     if (n_tiles_n == 1 && rem > 0) {
@@ -327,7 +330,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
     }
     const int my_tiles = full_waves + (pair < rem * ns ? 1 : 0);
     const int total_chunks = my_tiles * nk;
-    struct Item { int64_t m0; int bn, n0, nt, img_row; };   // first row of the pair's 256 | width | first column | n tile | first image row
+    struct Item { int64_t m0; int bn, n0, nt, img_row; };   // rows m0.. of this pair | slice width | first column | n tile | first image row
     auto item = [&](int it) {
         Item w;
         if (it < full_waves) {
@@ -502,16 +505,57 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
             tc::mbar_wait(&accFull[ab], (it >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * 256);
+            // does this warp's 32-row group lie inside the valid rows?  (then whole 32 x 32 chunks leave as ONE TMA store)
+            const bool rows_full = tma_store && vec_ok && m0 + 32 <= g.M;
             for (int j = half; j < nch; j += 2) {
                 uint32_t lo16[16], hi16[16];
                 tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32), lo16);
                 tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32 + 16), hi16);
                 const int n = n0 + j * 32 + 4 * c8;
                 const bool ncol_ok = (j * 32 + 4 * c8 < BN) && n < g.N;
+                const bool by_tma = rows_full && !g.aux && j * 32 + 32 <= BN && n0 + j * 32 + 32 <= g.N;
                 float4 bias4 = z4;
-                if (vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                if (!by_tma && vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+                // the slab is free once the previous chunk's bulk store has READ it
+                if (tma_store) {
+                    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                    __syncwarp();
+                }
                 tc::tmem_ld_wait();
                 if (j == my_last) release(ab);
+                if (by_tma) {
+                    // Whole sub-tile inside the matrix, no activation mask: bias + LeakyReLU in the TMEM layout (a thread owns one
+                    // row; the 32 bias values are warp-uniform loads, four floats at a time so that nothing else stays live), ONE
+                    // swizzled store pass, and the 32 x 32 box leaves through TMA: 8 + 8 LSU instructions per sub-tile instead of
+                    // 8 STS + 8 LDS + 8 STG - the LSU queue is what the latency-bound roles of this kernel wait in
+                    const float* bj = g.bias ? g.bias + n0 + j * 32 : nullptr;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        float4 b0 = z4, b1 = z4;
+                        if (bj) { b0 = __ldg(reinterpret_cast<const float4*>(bj + 4 * i)); b1 = __ldg(reinterpret_cast<const float4*>(bj + 16 + 4 * i)); }
+                        float4 y = make_float4(__uint_as_float(lo16[4 * i]) + b0.x, __uint_as_float(lo16[4 * i + 1]) + b0.y,
+                                               __uint_as_float(lo16[4 * i + 2]) + b0.z, __uint_as_float(lo16[4 * i + 3]) + b0.w);
+                        float4 z = make_float4(__uint_as_float(hi16[4 * i]) + b1.x, __uint_as_float(hi16[4 * i + 1]) + b1.y,
+                                               __uint_as_float(hi16[4 * i + 2]) + b1.z, __uint_as_float(hi16[4 * i + 3]) + b1.w);
+                        if (g.leaky) {
+                            y.x = y.x > 0.f ? y.x : g.slope * y.x; y.y = y.y > 0.f ? y.y : g.slope * y.y;
+                            y.z = y.z > 0.f ? y.z : g.slope * y.z; y.w = y.w > 0.f ? y.w : g.slope * y.w;
+                            z.x = z.x > 0.f ? z.x : g.slope * z.x; z.y = z.y > 0.f ? z.y : g.slope * z.y;
+                            z.z = z.z > 0.f ? z.z : g.slope * z.z; z.w = z.w > 0.f ? z.w : g.slope * z.w;
+                        }
+                        tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u, y);
+                        tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u, z);
+                    }
+                    tc::fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) {
+                        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(reinterpret_cast<uint64_t>(&tmC)),
+                                     "r"(n0 + j * 32), "r"((int)m0), "r"(slab)
+                                     : "memory");
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    continue;
+                }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u,
@@ -535,7 +579,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                 for (int i = 0; i < 8; ++i) {
                     const int row = 4 * i + rsub;
                     const int64_t m = m0 + row;
-                    float4 x4 = tc::lds128(slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u);
+                    const uint32_t saddr = slab + (uint32_t)(row * 32 + 4 * (c8 ^ (row & 7))) * 4u;
+                    float4 x4 = tc::lds128(saddr);
                     if (m >= g.M || !ncol_ok) continue;
                     float x[4] = {x4.x, x4.y, x4.z, x4.w};
                     if (vec_ok) {
@@ -566,6 +611,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
             }
             if (my_last < half) release(ab);
         }
+        if (tma_store && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -619,10 +665,23 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
     int n_tiles;
     int bn = pick_bn(g.N, &n_tiles);
     int64_t ptotal = cdiv(g.M, 2 * TBM) * n_tiles;        // g.M: the row count, or its capacity when g.Mdev is given
-    // few tiles: the kernel cuts them into column slices (see its work-item comment), so up to 4 pairs share a row tile
+    // few tiles: the kernel cuts them into column slices (see its work-item comment), so up to 4 pairs share a tile
     const int max_slices = n_tiles == 1 ? (bn % 128 == 0 ? 4 : bn % 64 == 0 ? 2 : 1) : 1;
     int pairs = ptotal * max_slices < kNumSMs / 2 ? (int)(ptotal * max_slices) : kNumSMs / 2;
-    gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles);
+    // the C tile leaves through TMA (one 32 x 32 box per epilogue warp and chunk) when the layout allows a tensor map
+    CUtensorMap tmC;
+    memset(&tmC, 0, sizeof(tmC));
+    int tma_store = 0;
+    if (g.N >= 32 && g.ldc % 4 == 0 && (((uintptr_t)g.C) & 15) == 0 && g.M < (int64_t)1 << 31) {
+        const cuuint64_t dims[2] = {(cuuint64_t)g.N, (cuuint64_t)g.M};
+        const cuuint64_t strides[1] = {(cuuint64_t)g.ldc * 4};
+        const cuuint32_t box[2] = {32, 32}, estr[2] = {1, 1};
+        CUresult r = cuTensorMapEncodeTiled(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)g.C, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        PN_CHECK_ARG(r == CUDA_SUCCESS, "gemm_nt: cuTensorMapEncodeTiled failed (%d)", (int)r);
+        tma_store = 1;
+    }
+    gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles, tmC, tma_store);
     PN_LAUNCH_CHECK("gemm_nt_img2");
     return PN_OK;
 }
