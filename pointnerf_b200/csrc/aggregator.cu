@@ -43,6 +43,10 @@ static int make_dims(const pn_agg_params* p, AggDims& d) {
 struct Saved {
     float *X1, *H1, *X3, *H3, *H4, *FS, *C1, *C2, *C3, *alpha;
     float4* pairv;
+    // LeakyReLU sign bits of H1, H2 (= X3[:, :W]), H3 (W / 32 words per pair row) and C1, C2 (C / 32 words per sample row),
+    // written by the forward GEMMs' epilogues for every full group of 32 rows: the data-gradient GEMMs then read 4 B per row
+    // and sub-tile for their mask instead of 128 B of the activation
+    uint32_t *sH1, *sH2, *sH3, *sC1, *sC2;
 };
 static int64_t carve_saved(const AggDims& d, int64_t S, int64_t M, void* p, int64_t bytes, Saved* sv) {
     Carver c(p, bytes);
@@ -59,6 +63,11 @@ static int64_t carve_saved(const AggDims& d, int64_t S, int64_t M, void* p, int6
     t.C2 = c.take<float>(s * d.C);
     t.C3 = c.take<float>(s * d.C);
     t.alpha = c.take<float>(s);
+    t.sH1 = c.take<uint32_t>(m * cdiv(d.W, 32));
+    t.sH2 = c.take<uint32_t>(m * cdiv(d.W, 32));
+    t.sH3 = c.take<uint32_t>(m * cdiv(d.W, 32));
+    t.sC1 = c.take<uint32_t>(s * cdiv(d.C, 32));
+    t.sC2 = c.take<uint32_t>(s * cdiv(d.C, 32));
     if (sv) *sv = t;
     return c.off;
 }
@@ -211,6 +220,18 @@ static GemmNT nt(const float* A, int64_t lda, const char* Bimg, float* C, int64_
     g.A = A; g.lda = lda; g.B = nullptr; g.ldb = 0; g.C = C; g.ldc = ldc; g.M = rows_cap; g.N = N; g.Kd = Kd;
     g.bias = bias; g.leaky = leaky; g.slope = slope; g.aux = nullptr; g.ldaux = 0; g.aux_cols = 0; g.rowmap = nullptr; g.Bimg = Bimg;
     g.Mdev = rows_dev;
+    g.sign_out = nullptr; g.sign_in = nullptr; g.sign_ld = 0;
+    return g;
+}
+// layers whose width is whole 32-bit words (and at least one TMA box) keep their activation signs as bits
+static bool sign_ok(int width) { return width % 32 == 0 && width >= 32; }
+static GemmNT with_sign_out(GemmNT g, uint32_t* bits, int width) {
+    if (sign_ok(width)) { g.sign_out = bits; g.sign_ld = width / 32; }
+    return g;
+}
+static GemmNT with_mask(GemmNT g, const uint32_t* bits, const float* act, int64_t ldact, int width) {
+    g.aux = act; g.ldaux = ldact; g.aux_cols = width;
+    if (sign_ok(width)) { g.sign_in = bits; g.sign_ld = width / 32; }
     return g;
 }
 
@@ -242,17 +263,17 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     PN_LAUNCH_CHECK("agg_prep");
     agg_prep_rows_kernel<<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
     PN_LAUNCH_CHECK("agg_prep_rows");
-    PN_TRY(gemm_nt(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), sv.sH1, d.W), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), sv.sH2, d.W), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), sv.sH3, d.W), st));
     PN_TRY(gemm_nt(nt(sv.H3, d.W, ws.I3b, sv.H4, d.W, M, Mdev, d.W, d.W, w->block3_2_b, 1, d.slope), st));
     if (d.W == 256)
         agg_reduce_kernel<8><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     else
         agg_reduce_kernel<4><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     PN_LAUNCH_CHECK("agg_reduce");
-    PN_TRY(gemm_nt(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), st));
-    PN_TRY(gemm_nt(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), sv.sC1, d.C), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), sv.sC2, d.C), st));
     PN_TRY(gemm_nt(nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope), st));
     agg_finish_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");
@@ -386,16 +407,12 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     PN_TRY(order(hs, st));
     {   // color.4
         PN_TRY(wgrad(GemmTN{ws.GSa, d.C, sv.C2, d.C, gw->color_4_w, d.C, d.C, gw->color_4_b, S, d.C, d.C, Sdev}, ws.tn[0]));
-        GemmNT g = nt(ws.GSa, d.C, ws.Jc4, ws.GSb, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope);
-        g.aux = sv.C2; g.ldaux = d.C; g.aux_cols = d.C;
-        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(gemm_nt(with_mask(nt(ws.GSa, d.C, ws.Jc4, ws.GSb, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope), sv.sC2, sv.C2, d.C, d.C), hs));
         PN_TRY(order(hs, st));
     }
     {   // color.2
         PN_TRY(wgrad(GemmTN{ws.GSb, d.C, sv.C1, d.C, gw->color_2_w, d.C, d.C, gw->color_2_b, S, d.C, d.C, Sdev}, ws.tn[1]));
-        GemmNT g = nt(ws.GSb, d.C, ws.Jc2, ws.GSc, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope);
-        g.aux = sv.C1; g.ldaux = d.C; g.aux_cols = d.C;
-        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(gemm_nt(with_mask(nt(ws.GSb, d.C, ws.Jc2, ws.GSc, d.C, S, Sdev, d.C, d.C, nullptr, 0, d.slope), sv.sC1, sv.C1, d.C, d.C), hs));
         PN_TRY(order(hs, st));
     }
     {   // color.0: d/dFS (only the first W columns are consumed)
@@ -416,9 +433,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // ---- block3 (M rows).  GA = dPre4 [M,W]
     {   // block3.2
         PN_TRY(wgrad(GemmTN{ws.GA, d.W, sv.H3, d.W, gw->block3_2_w, d.W, d.W, gw->block3_2_b, M, d.W, d.W, Mdev}, ws.tn[3]));
-        GemmNT g = nt(ws.GA, d.W, ws.J3b, ws.GB, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope);
-        g.aux = sv.H3; g.ldaux = d.W; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, hs));  // GB = dPre3
+        PN_TRY(gemm_nt(with_mask(nt(ws.GA, d.W, ws.J3b, ws.GB, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope), sv.sH3, sv.H3, d.W, d.W), hs));  // GB = dPre3
         PN_TRY(order(hs, st));
     }
     cudaEvent_t ga_free = nullptr;              // recorded on st once block3.2's weight gradient has read GA (dPre4)
@@ -428,9 +443,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
             PN_CUDA(cudaEventRecord(ga_free, st));
         }
         PN_TRY(wgrad(GemmTN{ws.GB, d.W, sv.X3, d.in3p, gw->block3_0_w, d.in3, d.in3, gw->block3_0_b, M, d.W, d.in3p, Mdev}, ws.tn[4]));
-        GemmNT g = nt(ws.GB, d.W, ws.J3a, ws.GA2, d.in3p, M, Mdev, d.in3p, d.W, nullptr, 0, d.slope);
-        g.aux = sv.X3; g.ldaux = d.in3p; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, hs));
+        PN_TRY(gemm_nt(with_mask(nt(ws.GB, d.W, ws.J3a, ws.GA2, d.in3p, M, Mdev, d.in3p, d.W, nullptr, 0, d.slope), sv.sH2, sv.X3, d.in3p, d.W), hs));
     }
     agg_extras_bwd_kernel<<<grid_thread_items(M), 256, 0, hs>>>(*in, d, ws.GA2, ws.PG, pgw);
     PN_LAUNCH_CHECK("agg_extras_bwd");
@@ -438,9 +451,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     // ---- block1.  GA2[:, :W] = dPre2 (row stride in3p)
     {   // block1.2
         PN_TRY(wgrad(GemmTN{ws.GA2, d.in3p, sv.H1, d.W, gw->block1_2_w, d.W, d.W, gw->block1_2_b, M, d.W, d.W, Mdev}, ws.tn[5]));
-        GemmNT g = nt(ws.GA2, d.in3p, ws.J1b, ws.GB2, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope);
-        g.aux = sv.H1; g.ldaux = d.W; g.aux_cols = d.W;
-        PN_TRY(gemm_nt(g, hs));  // GB2 = dPre1
+        PN_TRY(gemm_nt(with_mask(nt(ws.GA2, d.in3p, ws.J1b, ws.GB2, d.W, M, Mdev, d.W, d.W, nullptr, 0, d.slope), sv.sH1, sv.H1, d.W, d.W), hs));  // GB2 = dPre1
         PN_TRY(order(hs, st));
     }
     {   // block1.0: GA[M,in1p] = d/dX1 (GA is free again once block3.2's weight gradient has read dPre4)

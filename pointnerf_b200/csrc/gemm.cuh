@@ -9,7 +9,11 @@ namespace pn {
 // epilogue, in this order:
 //   v += bias[n]                                 (bias != null)
 //   v  = v > 0 ? v : slope * v                   (leaky != 0)
+//   sign_out[m*sign_ld + n/32] bit n%32 = v > 0  (sign_out != null; N % 32 == 0; written for every FULL group of 32 rows: what a
+//                                                 later data-gradient GEMM needs of this layer's output, 1 bit per value)
 //   v *= aux[m*ldaux + n] > 0 ? 1 : slope        (aux != null and n < aux_cols: LeakyReLU backward mask)
+//                                                 with sign_in != null (bits of the same aux, sign_ld = aux_cols / 32) the full
+//                                                 32 x 32 sub-tiles read the bits instead of the values
 //   C[rowmap ? rowmap[m] : m][n] = v             (row stride ldc)
 struct GemmNT {
     const float* A; int64_t lda;
@@ -22,6 +26,7 @@ struct GemmNT {
     const int* rowmap;  // unused (kept so that positional initialisers stay valid)
     const char* Bimg;   // pre-split, pre-swizzled operand image of B (pack_nt_image)
     const int32_t* Mdev;  // optional DEVICE row count: rows = min(*Mdev, M); M is then the capacity the launch is sized for
+    uint32_t* sign_out; const uint32_t* sign_in; int sign_ld;   // activation sign bits, sign_ld words per row
 };
 int gemm_nt(const GemmNT& g, cudaStream_t st);
 // Operand image of a B matrix for the tensor-core NT GEMM: B[n, k] = src[n*s_n + k*s_k] for n < N, k < K, zero beyond,

@@ -513,7 +513,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                 tc::tmem_ld16_issue(taddr + (uint32_t)(j * 32 + 16), hi16);
                 const int n = n0 + j * 32 + 4 * c8;
                 const bool ncol_ok = (j * 32 + 4 * c8 < BN) && n < g.N;
-                const bool by_tma = rows_full && !g.aux && j * 32 + 32 <= BN && n0 + j * 32 + 32 <= g.N;
+                const bool by_tma = rows_full && (!g.aux || g.sign_in) && j * 32 + 32 <= BN && n0 + j * 32 + 32 <= g.N;
                 float4 bias4 = z4;
                 if (!by_tma && vec_ok && ncol_ok && g.bias) bias4 = __ldg(reinterpret_cast<const float4*>(g.bias + n));
                 // the slab is free once the previous chunk's bulk store has READ it
@@ -529,6 +529,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                     // swizzled store pass, and the 32 x 32 box leaves through TMA: 8 + 8 LSU instructions per sub-tile instead of
                     // 8 STS + 8 LDS + 8 STG - the LSU queue is what the latency-bound roles of this kernel wait in
                     const float* bj = g.bias ? g.bias + n0 + j * 32 : nullptr;
+                    const int64_t mrow = m0 + lane;
+                    // LeakyReLU mask of a data gradient: the 32 sign bits of this row's columns (two words when the sub-tile
+                    // does not start on a word; columns past the masked ones read as positive)
+                    uint32_t mbits = 0xffffffffu;
+                    if (g.sign_in) {
+                        const int c0 = n0 + j * 32, wi = c0 >> 5;
+                        const uint32_t w0 = wi < g.sign_ld ? __ldg(g.sign_in + mrow * g.sign_ld + wi) : 0xffffffffu;
+                        const uint32_t w1 = ((c0 & 31) && wi + 1 < g.sign_ld) ? __ldg(g.sign_in + mrow * g.sign_ld + wi + 1) : 0xffffffffu;
+                        mbits = __funnelshift_r(w0, w1, c0 & 31);
+                    }
+                    uint32_t obits = 0;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         float4 b0 = z4, b1 = z4;
@@ -543,9 +554,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsImg, 1)
                             z.x = z.x > 0.f ? z.x : g.slope * z.x; z.y = z.y > 0.f ? z.y : g.slope * z.y;
                             z.z = z.z > 0.f ? z.z : g.slope * z.z; z.w = z.w > 0.f ? z.w : g.slope * z.w;
                         }
+                        if (g.sign_in) {
+                            const uint32_t a = mbits >> (4 * i), b = mbits >> (16 + 4 * i);
+                            y.x *= (a & 1u) ? 1.f : g.slope; y.y *= (a & 2u) ? 1.f : g.slope; y.z *= (a & 4u) ? 1.f : g.slope; y.w *= (a & 8u) ? 1.f : g.slope;
+                            z.x *= (b & 1u) ? 1.f : g.slope; z.y *= (b & 2u) ? 1.f : g.slope; z.z *= (b & 4u) ? 1.f : g.slope; z.w *= (b & 8u) ? 1.f : g.slope;
+                        }
+                        if (g.sign_out) {
+                            obits |= ((y.x > 0.f ? 1u : 0u) | (y.y > 0.f ? 2u : 0u) | (y.z > 0.f ? 4u : 0u) | (y.w > 0.f ? 8u : 0u)) << (4 * i);
+                            obits |= ((z.x > 0.f ? 1u : 0u) | (z.y > 0.f ? 2u : 0u) | (z.z > 0.f ? 4u : 0u) | (z.w > 0.f ? 8u : 0u)) << (16 + 4 * i);
+                        }
                         tc::sts128(slab + (uint32_t)(lane * 32 + 4 * (i ^ (lane & 7))) * 4u, y);
                         tc::sts128(slab + (uint32_t)(lane * 32 + 4 * ((i + 4) ^ (lane & 7))) * 4u, z);
                     }
+                    if (g.sign_out) g.sign_out[mrow * g.sign_ld + ((n0 + j * 32) >> 5)] = obits;
                     tc::fence_proxy_async();
                     __syncwarp();
                     if (lane == 0) {
@@ -681,6 +702,10 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
         PN_CHECK_ARG(r == CUDA_SUCCESS, "gemm_nt: cuTensorMapEncodeTiled failed (%d)", (int)r);
         tma_store = 1;
     }
+    // the sign-bit forms live on the TMA path only: writer and reader must both take it, or the bits are never written
+    PN_CHECK_ARG(!(g.sign_out || g.sign_in) || (tma_store && g.sign_ld > 0 && (!g.sign_out || (g.N % 32 == 0 && bn % 32 == 0 && g.sign_ld * 32 >= g.N)) &&
+                                                (!g.sign_in || (g.aux && g.aux_cols == g.sign_ld * 32)) && (!g.bias || (((uintptr_t)g.bias) & 15) == 0)),
+                 "gemm_nt: sign bits need the TMA epilogue (N %d ldc %lld sign_ld %d)", g.N, (long long)g.ldc, g.sign_ld);
     gemm_nt_img2_kernel<<<2 * pairs, kThreadsImg, IMG2_SMEM, st>>>(g, bn, n_tiles, tmC, tma_store);
     PN_LAUNCH_CHECK("gemm_nt_img2");
     return PN_OK;
