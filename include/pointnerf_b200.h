@@ -259,6 +259,8 @@ typedef struct pn_agg_params {
     int32_t intrp_order; /* agg_intrp_order: 2 (or 0) = one density per neighbour, interpolated over K (:603-646, every shipped
                             per-scene script); 1 = features interpolated over K, then one density per sample and
                             raw2out_color (sigmoid, act_super scaling) on the colour (:573-599, the DTU feed-forward configs) */
+    int32_t forward_only; /* 1: no pn_agg_backward follows on this `saved` buffer (inference): the forward skips what only the
+                             backward reads (the LeakyReLU sign bits its GEMM epilogues pack, ~6 % of the forward) */
 } pn_agg_params;
 
 /* nn.Linear parameters, weight [out,in] row-major fp32 (state_dict names of the reference) */

@@ -14,7 +14,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "lib", "libpointnerf_b200.so")
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 GRID_INFO_LEN = 8
 GI_N_OCC, GI_FIRST_POINT, GI_SLOT0_CELL, GI_N_INSIDE, GI_MAX_COUNT, GI_OVER_P, GI_OVER_MAX_O = range(7)
@@ -33,7 +33,7 @@ class FrustumQuery(Structure):
 class AggParams(Structure):
     _fields_ = [("F", c_int32), ("feat_freqs", c_int32), ("dist_freqs", c_int32), ("view_freqs", c_int32),
                 ("W", c_int32), ("C", c_int32), ("K", c_int32), ("dirs_per_ray", c_int32), ("SR", c_int32),
-                ("leaky_slope", c_float), ("dist_scale", c_float), ("compact_out", c_int32), ("intrp_order", c_int32)]
+                ("leaky_slope", c_float), ("dist_scale", c_float), ("compact_out", c_int32), ("intrp_order", c_int32), ("forward_only", c_int32)]
 
 
 WEIGHT_FIELDS = ("block1_0_w", "block1_0_b", "block1_2_w", "block1_2_b", "block3_0_w", "block3_0_b",

@@ -264,6 +264,7 @@ class _AggFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, call, embedding, color, pdir, conf, *weights):
         p = call.params
+        p.forward_only = 0 if any(ctx.needs_input_grad) else 1       # inference: the forward skips what only a backward reads
         cs = call.compact if call.compact is not None else CompactSamples(call.sample_pidx, call.n_slots, p.K)
         call.S, call.M = cs.counts()
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
@@ -404,6 +405,7 @@ class PointAggregator(nn.Module):
         p.W, p.C, p.K, p.SR = int(o.shading_feature_num), int(o.shading_color_channel_num), int(K), int(SR)
         p.dirs_per_ray = int(dirs_per_ray)
         p.leaky_slope = 0.01
+        p.forward_only = 0
         p.dist_scale = 1.0 if o.dist_xyz_deno == 0 else 1.0 / float(o.dist_xyz_deno * np.linalg.norm(vsize))
         return p
 

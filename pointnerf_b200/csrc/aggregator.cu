@@ -225,8 +225,8 @@ static GemmNT nt(const float* A, int64_t lda, const char* Bimg, float* C, int64_
 }
 // layers whose width is whole 32-bit words (and at least one TMA box) keep their activation signs as bits
 static bool sign_ok(int width) { return width % 32 == 0 && width >= 32; }
-static GemmNT with_sign_out(GemmNT g, uint32_t* bits, int width) {
-    if (sign_ok(width)) { g.sign_out = bits; g.sign_ld = width / 32; }
+static GemmNT with_sign_out(GemmNT g, uint32_t* bits, int width, bool wanted) {
+    if (wanted && sign_ok(width)) { g.sign_out = bits; g.sign_ld = width / 32; }
     return g;
 }
 static GemmNT with_mask(GemmNT g, const uint32_t* bits, const float* act, int64_t ldact, int width) {
@@ -259,21 +259,22 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
                              {w->color_0_w, d.inc, 1, d.C, d.inc, d.C, d.incp, ws.Ic0},  {w->color_2_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic2},
                              {w->color_4_w, d.C, 1, d.C, d.C, d.C, d.C, ws.Ic4}};
     PN_TRY(pack_nt_images(jobs, 7, st));
+    const bool bwd_follows = !p->forward_only;
     agg_prep_kernel<<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
     PN_LAUNCH_CHECK("agg_prep");
     agg_prep_rows_kernel<<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
     PN_LAUNCH_CHECK("agg_prep_rows");
-    PN_TRY(gemm_nt(with_sign_out(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), sv.sH1, d.W), st));
-    PN_TRY(gemm_nt(with_sign_out(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), sv.sH2, d.W), st));
-    PN_TRY(gemm_nt(with_sign_out(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), sv.sH3, d.W), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), sv.sH1, d.W, bwd_follows), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), sv.sH2, d.W, bwd_follows), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.X3, d.in3p, ws.I3a, sv.H3, d.W, M, Mdev, d.W, d.in3p, w->block3_0_b, 1, d.slope), sv.sH3, d.W, bwd_follows), st));
     PN_TRY(gemm_nt(nt(sv.H3, d.W, ws.I3b, sv.H4, d.W, M, Mdev, d.W, d.W, w->block3_2_b, 1, d.slope), st));
     if (d.W == 256)
         agg_reduce_kernel<8><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     else
         agg_reduce_kernel<4><<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.H4, sv.pairv, w->alpha_0_w, w->alpha_0_b, sv.FS, sv.alpha);
     PN_LAUNCH_CHECK("agg_reduce");
-    PN_TRY(gemm_nt(with_sign_out(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), sv.sC1, d.C), st));
-    PN_TRY(gemm_nt(with_sign_out(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), sv.sC2, d.C), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), sv.sC1, d.C, bwd_follows), st));
+    PN_TRY(gemm_nt(with_sign_out(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), sv.sC2, d.C, bwd_follows), st));
     PN_TRY(gemm_nt(nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope), st));
     agg_finish_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");

@@ -166,7 +166,7 @@ int scan_exclusive_i32(const int* in, int* out, int64_t n, bool write_total_at_e
 
 extern "C" {
 const char* pn_last_error(void) { return pn::g_err; }
-int pn_abi_version(void) { return 10; }
+int pn_abi_version(void) { return 11; }
 int64_t pn_launch_count(void) { return pn::g_launches.load(); }
 void pn_launch_count_reset(void) { pn::g_launches.store(0); }
 }

@@ -674,6 +674,23 @@ static int pick_bn(int N, int* n_tiles) {
 }
 static int tmem_cols_for(int bn) { return bn <= 32 ? 32 : bn <= 64 ? 64 : bn <= 128 ? 128 : 256; }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point: the library keeps no link-time dependency on libcuda
+// (it must load, and answer its size queries, on a machine without a driver)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
 int gemm_nt(const GemmNT& g, cudaStream_t st) {
     PN_CHECK_ARG(g.Kd % 4 == 0 && g.lda % 4 == 0, "gemm_nt: operands must be padded to 4 (Kd %d lda %lld)", g.Kd, (long long)g.lda);
     PN_CHECK_ARG(((uintptr_t)g.A & 15) == 0 && g.Bimg, "gemm_nt: A must be 16-byte aligned and B given as an operand image");
@@ -697,10 +714,13 @@ int gemm_nt(const GemmNT& g, cudaStream_t st) {
         const cuuint64_t dims[2] = {(cuuint64_t)g.N, (cuuint64_t)g.M};
         const cuuint64_t strides[1] = {(cuuint64_t)g.ldc * 4};
         const cuuint32_t box[2] = {32, 32}, estr[2] = {1, 1};
-        CUresult r = cuTensorMapEncodeTiled(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)g.C, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        PN_CHECK_ARG(r == CUDA_SUCCESS, "gemm_nt: cuTensorMapEncodeTiled failed (%d)", (int)r);
-        tma_store = 1;
+        EncodeTiledFn enc = encode_tiled();
+        if (enc) {
+            CUresult r = enc(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)g.C, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            PN_CHECK_ARG(r == CUDA_SUCCESS, "gemm_nt: cuTensorMapEncodeTiled failed (%d)", (int)r);
+            tma_store = 1;
+        }
     }
     // the sign-bit forms live on the TMA path only: writer and reader must both take it, or the bits are never written
     PN_CHECK_ARG(!(g.sign_out || g.sign_in) || (tma_store && g.sign_ld > 0 && (!g.sign_out || (g.N % 32 == 0 && bn % 32 == 0 && g.sign_ld * 32 >= g.N)) &&
