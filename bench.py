@@ -814,7 +814,7 @@ def psnr_vs_oracle(dev, name="cfg1", chunk=14400):
 def dominant_kernel_roofline(_lib, dev, M, peak, peaks, N=256, K=256, reps=20):
     """gemm_nt_img2_kernel at [M,K] x [N,K]^T through the C ABI's GEMM hook, CUDA events on the launching stream.
     ALGORITHMIC flops = 2*M*N*K (the kernel issues 3x that as TF32 MMAs: hi*lo, lo*hi, hi*hi); traffic = DRAM bytes of one
-    launch from the committed ncu --set full capture (profiles/r01_traffic.json), scaled by M."""
+    launch from the committed ncu --set full capture (profiles/r02_ncu_full_gemm_nt_final.json), scaled by M."""
     lib = _lib.lib()
     A = torch.randn(M, K, device=dev)
     B = torch.randn(N, K, device=dev) / 16
@@ -839,14 +839,14 @@ def dominant_kernel_roofline(_lib, dev, M, peak, peaks, N=256, K=256, reps=20):
     ach = fl / (us * 1e-6) / 1e12
     traffic = None
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))["gemm_nt_img2_kernel"]
-        traffic = int((tr["dram_bytes_read"] + tr["dram_bytes_write"]) * (M / tr["M"]))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_full_gemm_nt_final.json")))["metrics"]
+        traffic = int((float(tr["dram__bytes_read.sum [Mbyte]"]) + float(tr["dram__bytes_write.sum [Mbyte]"])) * 1e6 * (M / 134826))
     except Exception:
         pass
     return {"kernel": "gemm_nt_img2_kernel (aggregator MLP forward / data-gradient GEMM, CTA pairs, 3xTF32)", "bound": "tensor",
             "achieved": round(ach, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(ach / peak, 5), "traffic": traffic,
             "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst: the kernel is timed alone) (%s); 3xTF32 ceiling = peak / 6" % peaks["source"],
-            "traffic_source": "profiles/r01_traffic.json (one ncu --set full capture of this kernel at M = 134 826), scaled by M: not a measurement of this run",
+            "traffic_source": "profiles/r02_ncu_full_gemm_nt_final.json (one ncu --set full capture of this kernel, this build, at M = 134 826), scaled by M: not a measurement of this run",
             "frac_of_3xtf32_ceiling": round(ach / (peak / 6.0), 4),
             "launch_us": round(us, 2), "flops_per_launch": fl, "algorithmic_bytes_per_launch": int(4 * (M * K + M * N + 2 * N * K)),
             "shape": [M, N, K], "mma_passes_per_product": 3}
