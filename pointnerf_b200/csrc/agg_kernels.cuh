@@ -122,50 +122,57 @@ __global__ void __launch_bounds__(256) agg_prep_kernel(pn_agg_inputs in, AggDims
 // interleaves (sin, cos) per (channel, frequency), so a lane owns short scattered runs of the row - stored directly,
 // every instruction would touch every 32-byte sector of the row (6x the L2 write transactions).  The row is assembled
 // in shared memory and leaves as whole float4s.
+// The kernel is issue-bound (ncu: 76 % issue slots, ALU 45 %: index arithmetic of the scattered shared-memory stores and loop
+// control on run-time F / ff / df), so the shipped shape (F = 32, 3 feature and 5 distance frequencies) is compiled with the
+// three as constants - every loop unrolls and the store offsets fold; kF = 0 keeps the run-time form for other shapes.
+template <int kF, int kFF, int kDF>
 __global__ void __launch_bounds__(256, 8) agg_prep_rows_kernel(pn_agg_inputs in, AggDims d, float* __restrict__ X1) {
     extern __shared__ float prep_rows[];                 // blockDim.x / 32 rows of in1p floats
     const int lane = threadIdx.x & 31;
     const int64_t M = n_pairs(in);
-    float* srow = prep_rows + (threadIdx.x >> 5) * d.in1p;
+    const int F = kF ? kF : d.F, ff = kF ? kFF : d.ff, df = kF ? kDF : d.df;
+    const int in1 = kF ? kF + 2 * kFF * kF + 12 * kDF : d.in1, in1p = kF ? (in1 + 15) / 16 * 16 : d.in1p;
+    float* srow = prep_rows + (threadIdx.x >> 5) * in1p;
     const int64_t m = warp_id_global();                  // the launch covers the capacity: one pair per warp, no loop (registers)
     if (m >= M) return;
   {
     const int gj = in.sample_pidx[in.pair_src[m]];
-    float* row = X1 + m * d.in1p;
-    const int pe0 = d.F + 2 * d.ff * d.F;
-    float r[6];
+    float* row = X1 + m * in1p;
+    const int pe0 = F + 2 * ff * F;
+    float rv = lane < 6 ? row[pe0 + lane] : 0.f;         // lane = axis: the parked offset component
 #pragma unroll
-    for (int i = 0; i < 6; ++i) r[i] = row[pe0 + i];
-    for (int c = lane; c < d.F; c += 32) {
-        float e = in.embedding[(int64_t)gj * d.F + c];
+    for (int c = lane; c < F; c += 32) {
+        float e = in.embedding[(int64_t)gj * F + c];
         srow[c] = e;
         // frequencies are powers of two: one accurate sincosf, then double-angle steps (each adds ~2 ulp of absolute
         // error on values in [-1, 1]; at most 15 steps, far inside the 1e-4 budget)
         float s, co;
         sincosf(e, &s, &co);
-        for (int f = 0; f < d.ff; ++f) {
-            srow[d.F + (c * d.ff + f) * 2] = s;
-            srow[d.F + (c * d.ff + f) * 2 + 1] = co;
+#pragma unroll
+        for (int f = 0; f < ff; ++f) {
+            srow[F + (c * ff + f) * 2] = s;
+            srow[F + (c * ff + f) * 2 + 1] = co;
             const float s2 = 2.f * s * co, c2 = (co - s) * (co + s);
             s = s2; co = c2;
         }
     }
-    if (lane < 6) {                                       // lane = axis: all df frequencies of one offset component
-        const float v = lane == 0 ? r[0] : lane == 1 ? r[1] : lane == 2 ? r[2] : lane == 3 ? r[3] : lane == 4 ? r[4] : r[5];
+    if (lane < 6) {                                       // all df frequencies of one offset component
         float s, co;
-        sincosf(v, &s, &co);
-        for (int f = 0; f < d.df; ++f) {
-            const int q = lane * d.df + f;
+        sincosf(rv, &s, &co);
+#pragma unroll
+        for (int f = 0; f < df; ++f) {
+            const int q = lane * df + f;
             srow[pe0 + 2 * q] = s;
             srow[pe0 + 2 * q + 1] = co;
             const float s2 = 2.f * s * co, c2 = (co - s) * (co + s);
             s = s2; co = c2;
         }
     }
-    for (int c = d.in1 + lane; c < d.in1p; c += 32) srow[c] = 0.f;
+    for (int c = in1 + lane; c < in1p; c += 32) srow[c] = 0.f;
     __syncwarp();
     float4* row4 = reinterpret_cast<float4*>(row);       // in1p % 4 == 0 and X1 is 16-byte aligned
-    for (int c4 = lane; c4 < (d.in1p >> 2); c4 += 32) row4[c4] = *reinterpret_cast<const float4*>(srow + 4 * c4);
+#pragma unroll
+    for (int c4 = lane; c4 < (in1p >> 2); c4 += 32) row4[c4] = *reinterpret_cast<const float4*>(srow + 4 * c4);
   }
 }
 

@@ -262,7 +262,10 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     const bool bwd_follows = !p->forward_only;
     agg_prep_kernel<<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.X1, sv.X3, sv.pairv, weight_out);
     PN_LAUNCH_CHECK("agg_prep");
-    agg_prep_rows_kernel<<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
+    if (d.F == 32 && d.ff == 3 && d.df == 5)
+        agg_prep_rows_kernel<32, 3, 5><<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
+    else
+        agg_prep_rows_kernel<0, 0, 0><<<grid_warp_items(M), 256, 8 * d.in1p * sizeof(float), st>>>(*in, d, sv.X1);
     PN_LAUNCH_CHECK("agg_prep_rows");
     PN_TRY(gemm_nt(with_sign_out(nt(sv.X1, d.in1p, ws.I1a, sv.H1, d.W, M, Mdev, d.W, d.in1p, w->block1_0_b, 1, d.slope), sv.sH1, d.W, bwd_follows), st));
     PN_TRY(gemm_nt(with_sign_out(nt(sv.H1, d.W, ws.I1b, sv.X3, d.in3p, M, Mdev, d.W, d.W, w->block1_2_b, 1, d.slope), sv.sH2, d.W, bwd_follows), st));
