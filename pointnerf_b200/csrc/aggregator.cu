@@ -279,7 +279,7 @@ extern "C" int pn_agg_forward(const pn_agg_params* p, const pn_agg_inputs* in, c
     PN_TRY(gemm_nt(with_sign_out(nt(sv.FS, d.incp, ws.Ic0, sv.C1, d.C, S, Sdev, d.C, d.incp, w->color_0_b, 1, d.slope), sv.sC1, d.C, bwd_follows), st));
     PN_TRY(gemm_nt(with_sign_out(nt(sv.C1, d.C, ws.Ic2, sv.C2, d.C, S, Sdev, d.C, d.C, w->color_2_b, 1, d.slope), sv.sC2, d.C, bwd_follows), st));
     PN_TRY(gemm_nt(nt(sv.C2, d.C, ws.Ic4, sv.C3, d.C, S, Sdev, d.C, d.C, w->color_4_b, 1, d.slope), st));
-    agg_finish_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
+    agg_finish_kernel<<<grid_warp_items(S), 256, 0, st>>>(*in, d, sv.alpha, sv.C3, decoded);
     PN_LAUNCH_CHECK("agg_finish");
     return PN_OK;
 }
@@ -406,7 +406,7 @@ extern "C" int pn_agg_backward(const pn_agg_params* p, const pn_agg_inputs* in, 
     };
     PN_TRY(order(st, hs));                      // inputs, zero-fills and weight images are ready
     // ---- colour branch (S rows): gradient buffers GSa -> GSb -> GSc -> GSd
-    agg_gout_kernel<<<grid_thread_items(S * (d.C + 1)), 256, 0, hs>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
+    agg_gout_kernel<<<grid_warp_items(S), 256, 0, hs>>>(*in, d, grad_decoded, sv.C3, ws.GSa, ws.galpha);
     PN_LAUNCH_CHECK("agg_gout");
     PN_TRY(order(hs, st));
     {   // color.4

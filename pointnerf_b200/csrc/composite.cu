@@ -289,12 +289,20 @@ __global__ void __launch_bounds__(256) color_mse_partial_kernel(const float* __r
     const float g2 = 2.f * inv_norm;
     const bool weighted = ray_weight || ray_mask;
     float acc = 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    // ray index of element i, carried along instead of a 64-bit division per element (same elements in the same order)
+    const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t r = i0 / C;
+    int c = (int)(i0 - r * C);
+    const int64_t dr = stride / C;
+    const int dc = (int)(stride - dr * C);
+    for (int64_t i = i0; i < n; i += stride) {
         float d = pred[i] - target[i];
-        float w = ray_weight ? ray_weight[i / C] : 1.f;
-        if (ray_mask) w = ray_mask[i / C] > 0 ? w : 0.f;
+        float w = ray_weight ? ray_weight[r] : 1.f;
+        if (ray_mask) w = ray_mask[r] > 0 ? w : 0.f;
         acc = __fmaf_rn(w * d, d, acc);
         if (grad) grad[i] = weighted ? (g2 * w) * d : g2 * d;
+        r += dr; c += dc;
+        if (c >= C) { c -= C; ++r; }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
