@@ -268,6 +268,21 @@ class FusedTrainStep:
             call.flat_tail = (C + 63) // 64 * 64
         weights = tuple(w.detach() for w in agg._weights())
         tables = tuple(t.detach() for t in tabs)
+        # colour loss: per-ray weights realise the reference's three item kinds; the plain MSE needs none.  They depend on the
+        # query (and the global masked count) only: eight small torch launches, forked here beside the forward instead of
+        # sitting between compositing and the loss
+        g_rays = self.R * self.world
+        w_fork = None
+        if self._needs_mask:
+            main0 = torch.cuda.current_stream()
+            self._side.wait_stream(main0)
+            with torch.cuda.stream(self._side):
+                w = color_loss_ray_weights(q["ray_any"], self.items, self.item_weights, C, g_rays, self.masked_count)
+                w_fork = torch.cuda.Event()
+                w_fork.record(self._side)
+            inv_norm = 1.0
+        else:
+            w, inv_norm = None, sum(self.item_weights) / float(g_rays * C)
         decoded, _, saved, saved_bytes = agg_forward_raw(call, *tables, weights)
         slot_row = q["slot_row"].view(R, SR)
         ray_valid = slot_row >= 0
@@ -277,13 +292,9 @@ class FusedTrainStep:
         n_rows_dev = q["counts"][0:1]
         cctx = _Ctx((True, False, False, bg_grad, False, False, False))
         ray_color, opacity, acc_T, blend_w, bg_T = _Composite.forward(cctx, decoded, ray_dist, _as_u8(ray_valid), bg, True, slot_row, n_rows_dev)
-        # colour loss: per-ray weights realise the reference's three item kinds; the plain MSE needs none
-        g_rays = self.R * self.world
-        if self._needs_mask:
-            w = color_loss_ray_weights(q["ray_any"], self.items, self.item_weights, C, g_rays, self.masked_count)
-            inv_norm = 1.0
-        else:
-            w, inv_norm = None, sum(self.item_weights) / float(g_rays * C)
+        if w_fork is not None:
+            torch.cuda.current_stream().wait_event(w_fork)
+            w.record_stream(torch.cuda.current_stream())
         lctx = _Ctx((True, False, False, False, False, False))
         self.loss = _ColorMSE.forward(lctx, ray_color.view(1, R, C), self.c_gt, w, inv_norm)
         nxt = None
