@@ -264,7 +264,6 @@ class _AggFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, call, embedding, color, pdir, conf, *weights):
         p = call.params
-        p.forward_only = 0 if any(ctx.needs_input_grad) else 1       # inference: the forward skips what only a backward reads
         cs = call.compact if call.compact is not None else CompactSamples(call.sample_pidx, call.n_slots, p.K)
         call.S, call.M = cs.counts()
         call.sample_list, call.pair_start, call.pair_src, call.slot_row = cs.sample_list, cs.pair_start, cs.pair_src, cs.slot_row
@@ -439,6 +438,9 @@ class PointAggregator(nn.Module):
         call.flat_tail = int(getattr(self, "flat_tail_floats", 0))
         call.compact = work_lists             # CompactSamples of sample_pidx queued earlier (None: built here, with its sync)
         call.export_signs = bool(getattr(self, "export_signs", False))
+        # inference (torch.no_grad, or nothing that wants a gradient): the forward skips what only a backward reads
+        wants_grad = torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in (embedding, color, pdir, conf, *self._weights()))
+        call.params.forward_only = 0 if wants_grad else 1
         decoded, weight = _AggFunction.apply(call, embedding, color, pdir, conf, *self._weights())
         self.last_call = call      # work lists of the most recent fused call (ray_shard: touched point rows)
         weight = weight.view(R, SR, K) if want_weight else None

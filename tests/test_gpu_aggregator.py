@@ -151,6 +151,13 @@ def test_fused_tables_match_gathered(cuda_dev, tiny_scene):
     assert torch.equal(dec, dec2)
     for a, b in zip(grads, grads2):
         assert torch.equal(a, b)
+    # inference (no gradient wanted: pn_agg_params.forward_only = 1, the GEMM epilogues skip the sign-bit packing): same bits
+    with torch.no_grad():
+        dec3, _ = mod.forward_tables(xyz.to(d), xyz_pers.to(d), leaves["points_embeding"][0], leaves["points_color"][0],
+                                     leaves["points_dir"][0], leaves["points_conf"][0, :, 0], Rw2c.to(d), pidx.to(d), loc_pers.to(d),
+                                     loc_w.to(d), dirs.to(d), opt.vsize, dirs_per_ray=True, want_weight=True)
+    assert mod.last_call.params.forward_only == 1
+    assert torch.equal(dec, dec3)
 
 
 def test_no_valid_samples_and_empty(cuda_dev):
